@@ -1,0 +1,80 @@
+"""CPU: the numpy oracle against the fixtures produced by the real reference
+(oracle/gen_golden.py).  This is the pin SURVEY.md section 8(c) asks for."""
+import numpy as np
+import pytest
+
+from conftest import assert_close_f32, assert_masks_close, load_golden, unpack_masks
+from oracle import synth, yolact_np as O
+from oracle.gen_golden import digest
+
+
+def test_anchor_counts():
+    assert O.get_anchors((550, 550)).shape == (19248, 4)
+    assert O.get_anchors((544, 544)).shape == (18525, 4)
+    assert synth.yolact_dims(550) == (19248, 138)
+    assert synth.yolact_dims(544) == (18525, 136)
+
+
+def test_stage_known_answers():
+    g = load_golden("yolact_stages")
+    assert_close_f32(O.decode_boxes(g["pred"], g["anchors"]), g["decoded"], 1e-6, "decode_boxes")
+    dec = g["decoded"]
+    iou = O.jaccard(dec[:90], dec[40:150])
+    assert np.array_equal(iou, g["iou"]), "jaccard must be bit-exact (separate fp32 ops)"
+    for tag, (thr, top_k, max_det) in {"f1": (0.5, 200, 100), "f2": (0.3, 50, 20)}.items():
+        b, s, c, k = O.fast_non_max_suppression(g["nms_box"], g["nms_scores"], g["nms_coef"], thr, top_k, max_det)
+        assert np.array_equal(s, g[tag + "_score"]) and np.array_equal(c, g[tag + "_cls"])
+        assert np.array_equal(b, g[tag + "_box"]) and np.array_equal(k, g[tag + "_coef"])
+    assert np.array_equal(O.yolact_correct_boxes(g["raw"], (123, 77)), g["corrected"])
+    assert np.array_equal(O.crop(g["maps"], g["crop_boxes"]), g["cropped"])
+    assert_close_f32(O.upsample_bilinear(g["small"], 47, 29), g["up"], 1e-6, "upsample")
+    assert_close_f32(O.upsample_bilinear(g["small"], 7, 5), g["down"], 1e-6, "downsample")
+
+
+def _check_decode_nms(g, res):
+    boxes, scores, cls, arg, masks = res
+    assert np.array_equal(scores, g["scores"]), "scores (keep set) must be bit-exact"
+    assert np.array_equal(cls, g["class_ids"]) and cls.dtype == np.int64
+    assert_close_f32(boxes, g["boxes"], 1e-5, "boxes")
+    assert_masks_close(masks, unpack_masks(g), 1e-3, "masks")
+    assert float(np.mean(arg != g["masks_arg"])) <= 1e-3
+    assert arg.dtype == np.int64 and masks.dtype == np.bool_
+
+
+@pytest.mark.parametrize("name", ["yolact_tiny_a", "yolact_tiny_b", "yolact_tiny_one"])
+def test_tiny_end_to_end(name):
+    g = load_golden(name)
+    res = O.decode_nms((g["box"], g["conf"], g["coef"], g["proto"]), g["anchors"], float(g["confidence"]),
+                       float(g["nms_iou"]), g["image_shape"])
+    assert not bool(g["is_none"])
+    _check_decode_nms(g, res)
+
+
+def test_no_survivor_returns_nones():
+    g = load_golden("yolact_tiny_none")
+    assert bool(g["is_none"])
+    res = O.decode_nms((g["box"], g["conf"], g["coef"], g["proto"]), g["anchors"], float(g["confidence"]),
+                       float(g["nms_iou"]), g["image_shape"])
+    assert res == (None,) * 5
+
+
+@pytest.mark.parametrize("name", ["yolact_550_coco", "yolact_550_coco_sparse", "yolact_544_voc_1080p"])
+def test_full_size_end_to_end(name):
+    g = load_golden(name)
+    size, c = int(g["input_size"]), int(g["num_classes"])
+    a, p = synth.yolact_dims(size)
+    box, conf, coef, proto = [t.numpy() for t in synth.yolact_heads(int(g["seed"]), a, num_classes=c, proto=p,
+                                                                     objects=int(g["objects"]))]
+    assert digest(box, conf, coef, proto) == str(g["input_digest"]), "synthetic generator drifted"
+    anchors = O.get_anchors((size, size)).astype(np.float32)
+    res = O.decode_nms((box, conf, coef, proto), anchors, float(g["confidence"]), float(g["nms_iou"]), g["image_shape"])
+    _check_decode_nms(g, res)
+
+
+def test_verseg_fast_nms():
+    g = load_golden("verseg_fastnms")
+    box, score, coef = [t.numpy() for t in synth.verseg_boxes(int(g["seed"]), int(g["n"]))]
+    assert digest(box, score, coef) == str(g["input_digest"])
+    b, s, c, k = O.fast_non_max_suppression(box, score, coef, 0.5, int(g["top_k"]), int(g["max_det"]))
+    assert np.array_equal(s, g["score"]) and np.array_equal(b, g["box"]) and np.array_equal(c, g["cls"])
+    assert digest(k) == str(g["coef_digest"])
