@@ -1,0 +1,150 @@
+/* isb.h -- C ABI of libisb.so: B200 (sm_100a) kernels for the instance-segmentation
+ * post-processing path of Leyan529/InstanceSegmentation-.
+ *
+ * The reference has no FFI layer; its boundary for this path is a set of Python call
+ * signatures.  Each entry point below names the reference
+ * function(s) it replaces as file:line under the reference tree.  All pointers are plain
+ * DEVICE pointers unless the name says `_host`; tensors are dense row-major float32 /
+ * int64 / uint8 exactly as the reference lays them out.  Nothing here depends on torch.
+ *
+ * Conventions
+ *   - every call returns an isb_status (0 = ok, < 0 = error); the message is available
+ *     from isb_last_error(handle).  "No detections" is a value (count 0), not an error.
+ *   - all kernels are enqueued on the caller's stream; no call synchronises the device
+ *     except the `_host` variants (which must, to hand back host buffers).
+ *   - a handle is bound to one device and is not thread-safe: one handle per (device,
+ *     stream) in flight.
+ */
+#ifndef ISB_H_
+#define ISB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ISB_API __attribute__((visibility("default")))
+
+#define ISB_VERSION 100 /* 0.1.0 */
+#define ISB_NUM_COEF 32 /* prototype / coefficient channels (reference nets/yolact.py:70-111) */
+#define ISB_MAX_DET_LIMIT 1024
+
+typedef struct isb_handle isb_handle;
+typedef void* isb_stream; /* cudaStream_t */
+
+typedef enum {
+  ISB_OK = 0,
+  ISB_ERR_BAD_ARG = -1,  /* null pointer, bad shape, misaligned pointer                 */
+  ISB_ERR_CUDA = -2,     /* a CUDA runtime call failed                                  */
+  ISB_ERR_LIMIT = -3,    /* request exceeds the isb_limits the handle was created with  */
+  ISB_ERR_OVERFLOW = -4  /* reported by a `_host` call: candidate buffer too small      */
+} isb_status;
+
+/* Upper bounds the workspace is sized for.  Zero fields take the defaults in brackets. */
+typedef struct {
+  int32_t max_batch;      /* images per call                                    [64]    */
+  int32_t max_anchors;    /* anchors / rows per image                           [19248] */
+  int32_t max_classes;    /* foreground classes                                 [80]    */
+  int32_t max_det;        /* detections kept per image, <= ISB_MAX_DET_LIMIT    [100]   */
+  int32_t max_top_k;      /* per-class Fast-NMS window                          [200]   */
+  int64_t cand_capacity;  /* (anchor,class) candidates buffered per image       [16384] */
+} isb_limits;
+
+ISB_API int isb_version(void);
+ISB_API int isb_create(int device, const isb_limits* limits, isb_handle** out);
+ISB_API void isb_destroy(isb_handle* h);
+ISB_API const char* isb_last_error(const isb_handle* h);
+ISB_API size_t isb_workspace_bytes(const isb_handle* h);
+/* Number of kernels this library has launched through the handle (bench `gpu_launches`). */
+ISB_API int64_t isb_launch_count(const isb_handle* h);
+
+/* ------------------------------------------------------------------------------------
+ * YOLACT Detect + mask assembly, fused, for a batch of images.
+ * Replaces BBoxUtility.decode_nms, inst_model/yolact/utils/utils_bbox.py:170-243
+ * (traditional_nms=False branch), i.e. decode_boxes :11, score filter :193-204,
+ * fast_non_max_suppression :50-100, second threshold :208-212, yolact_correct_boxes :142,
+ * matmul+sigmoid :223, bilinear upsample :227-229, crop :154-168, argmax :236, >0.5 :241.
+ * ---------------------------------------------------------------------------------- */
+typedef struct {
+  int32_t batch;        /* B                                                            */
+  int32_t num_anchors;  /* A                                                            */
+  int32_t num_classes;  /* C, INCLUDING the background column 0                         */
+  int32_t num_coef;     /* K, must equal ISB_NUM_COEF                                   */
+  int32_t proto_h, proto_w;
+  int32_t out_h, out_w; /* image_shape (H, W) the masks are upsampled to                */
+  const float* box;     /* [B,A,4]  raw box regressions                                 */
+  const float* conf;    /* [B,A,C]  softmaxed class scores                              */
+  const float* coef;    /* [B,A,K]  mask coefficients                                   */
+  const float* proto;   /* [B,Ph,Pw,K] prototypes, channels last                        */
+  const float* anchors; /* [A,4]    priors (cx,cy,w,h), shared by the batch             */
+  float confidence;
+  float nms_iou;
+  int32_t top_k;        /* reference default 200 (utils_bbox.py:50)                     */
+  int32_t max_det;      /* reference default 100                                        */
+} isb_yolact_in;
+
+typedef struct {
+  float* boxes;          /* [B,max_det,4] pixel corners, rows >= counts[b] untouched    */
+  float* scores;         /* [B,max_det]                                                 */
+  int64_t* class_ids;    /* [B,max_det]  0-based foreground class                       */
+  int64_t* masks_arg;    /* [B,H,W]      per-pixel argmax over detections               */
+  uint8_t* masks;        /* B slots of mask_slot_bytes; slot b holds bool [H,W,m_b]
+                            densely packed with m_b = counts[b] innermost               */
+  int64_t mask_slot_bytes; /* >= H*W*max_det, multiple of 16                            */
+  int32_t* counts;       /* [B] m_b; 0 = no detection (reference returns 5x None);
+                            -1 = candidate buffer overflow (raise cand_capacity)        */
+} isb_yolact_out;
+
+ISB_API int isb_yolact_detect(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out, isb_stream stream);
+
+/* Same computation with HOST buffers (pinned recommended): copies the five inputs to the
+ * device, runs isb_yolact_detect, copies every output back and synchronises.  All
+ * pointers in `in` / `out` are host pointers.  This is the end-to-end path bench.py
+ * reports as `e2e`.  Returns ISB_ERR_OVERFLOW if any counts[b] is -1. */
+ISB_API int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out, isb_stream stream);
+
+/* ------------------------------------------------------------------------------------
+ * Stage entry points (known-answer tests call these one by one; BBoxUtility's public
+ * helper methods map onto them).
+ * ---------------------------------------------------------------------------------- */
+
+/* utils_bbox.py:11-25 decode_boxes(pred_box[n,4], anchors[n,4], variances) -> [n,4] */
+ISB_API int isb_decode_boxes(isb_handle* h, const float* pred, const float* anchors, int64_t n, float var0, float var1,
+                     float* out, isb_stream stream);
+
+/* utils_bbox.py:27-48 jaccard: a [nb,na,4], b [nb,nbx,4] -> iou [nb,na,nbx] */
+ISB_API int isb_jaccard(isb_handle* h, const float* a, const float* b, int32_t batch, int32_t na, int32_t nb, int32_t iscrowd,
+                float* out, isb_stream stream);
+
+/* utils_bbox.py:50-100 fast_non_max_suppression(box[n,4], scores[n,C], coef[n,K]).
+ * Outputs sized for max_det rows; *count (device int32) receives the number of rows. */
+ISB_API int isb_fast_nms(isb_handle* h, const float* box, const float* scores, const float* coef, int32_t n,
+                 int32_t num_fg_classes, int32_t num_coef, float nms_iou, int32_t top_k, int32_t max_det,
+                 float* out_box, float* out_score, int64_t* out_class, float* out_coef, int32_t* count,
+                 isb_stream stream);
+
+/* utils_bbox.py:142-152 yolact_correct_boxes(boxes[m,4], (H,W)) -> [m,4] */
+ISB_API int isb_correct_boxes(isb_handle* h, const float* boxes, int64_t m, int32_t out_h, int32_t out_w, float* out,
+                      isb_stream stream);
+
+/* utils_bbox.py:154-168 crop(masks[H,W,m] float32, boxes[m,4]) -> [H,W,m] float32 */
+ISB_API int isb_crop(isb_handle* h, const float* masks, const float* boxes, int32_t hgt, int32_t wid, int32_t m, float* out,
+             isb_stream stream);
+
+/* utils_bbox.py:223 inner product only: proto[Ph,Pw,K] @ coef[m,K]^T -> logits [Ph,Pw,m] */
+ISB_API int isb_mask_logits(isb_handle* h, const float* proto, const float* coef, int32_t proto_h, int32_t proto_w, int32_t m,
+                    float* out, isb_stream stream);
+
+/* utils_bbox.py:223-241 for one image with m known on the host:
+ * sigmoid(proto@coef^T) -> bilinear to (H,W) -> crop by boxes_px -> argmax, >0.5.
+ * masks: bool [H,W,m] (uint8), masks_arg: int64 [H,W]. */
+ISB_API int isb_mask_assemble(isb_handle* h, const float* proto, const float* coef, const float* boxes_px, int32_t proto_h,
+                      int32_t proto_w, int32_t m, int32_t out_h, int32_t out_w, int64_t* masks_arg, uint8_t* masks,
+                      isb_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ISB_H_ */

@@ -1,0 +1,162 @@
+"""ctypes binding of libisb.so (include/isb.h).  Fails loudly if the library is absent."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "libisb.so")
+
+ISB_NUM_COEF = 32
+ISB_MAX_DET_LIMIT = 1024
+ISB_OK, ISB_ERR_BAD_ARG, ISB_ERR_CUDA, ISB_ERR_LIMIT, ISB_ERR_OVERFLOW = 0, -1, -2, -3, -4
+
+# every exported symbol of include/isb.h (tests check the library exports exactly these)
+SYMBOLS = (
+    "isb_version", "isb_create", "isb_destroy", "isb_last_error", "isb_workspace_bytes", "isb_launch_count",
+    "isb_yolact_detect", "isb_yolact_detect_host", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
+    "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_assemble",
+)
+
+
+class IsbError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(f"libisb status {status}: {message}")
+        self.status = status
+
+
+class Limits(C.Structure):
+    _fields_ = [("max_batch", C.c_int32), ("max_anchors", C.c_int32), ("max_classes", C.c_int32),
+                ("max_det", C.c_int32), ("max_top_k", C.c_int32), ("cand_capacity", C.c_int64)]
+
+
+class YolactIn(C.Structure):
+    _fields_ = [("batch", C.c_int32), ("num_anchors", C.c_int32), ("num_classes", C.c_int32), ("num_coef", C.c_int32),
+                ("proto_h", C.c_int32), ("proto_w", C.c_int32), ("out_h", C.c_int32), ("out_w", C.c_int32),
+                ("box", C.c_void_p), ("conf", C.c_void_p), ("coef", C.c_void_p), ("proto", C.c_void_p),
+                ("anchors", C.c_void_p), ("confidence", C.c_float), ("nms_iou", C.c_float),
+                ("top_k", C.c_int32), ("max_det", C.c_int32)]
+
+
+class YolactOut(C.Structure):
+    _fields_ = [("boxes", C.c_void_p), ("scores", C.c_void_p), ("class_ids", C.c_void_p), ("masks_arg", C.c_void_p),
+                ("masks", C.c_void_p), ("mask_slot_bytes", C.c_int64), ("counts", C.c_void_p)]
+
+
+_lib = None
+_lock = threading.Lock()
+
+
+def load():
+    """Load libisb.so once.  No fallback: a missing library is an error."""
+    global _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a).  This package has no CPU or PyTorch fallback.")
+        lib = C.CDLL(LIB_PATH)
+        vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+        lib.isb_version.restype = C.c_int
+        lib.isb_create.argtypes = [C.c_int, C.POINTER(Limits), C.POINTER(vp)]
+        lib.isb_destroy.argtypes = [vp]
+        lib.isb_destroy.restype = None
+        lib.isb_last_error.argtypes = [vp]
+        lib.isb_last_error.restype = C.c_char_p
+        lib.isb_workspace_bytes.argtypes = [vp]
+        lib.isb_workspace_bytes.restype = C.c_size_t
+        lib.isb_launch_count.argtypes = [vp]
+        lib.isb_launch_count.restype = i64
+        lib.isb_yolact_detect.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactOut), vp]
+        lib.isb_yolact_detect_host.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactOut), vp]
+        lib.isb_decode_boxes.argtypes = [vp, vp, vp, i64, f32, f32, vp, vp]
+        lib.isb_jaccard.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp, vp]
+        lib.isb_fast_nms.argtypes = [vp, vp, vp, vp, i32, i32, i32, f32, i32, i32, vp, vp, vp, vp, vp, vp]
+        lib.isb_correct_boxes.argtypes = [vp, vp, i64, i32, i32, vp, vp]
+        lib.isb_crop.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
+        lib.isb_mask_logits.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
+        lib.isb_mask_assemble.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp]
+        for name in SYMBOLS:
+            fn = getattr(lib, name)
+            if name not in ("isb_destroy", "isb_last_error", "isb_workspace_bytes", "isb_launch_count", "isb_version"):
+                fn.restype = C.c_int
+        _lib = lib
+        return lib
+
+
+class Handle:
+    """Owns one isb_handle (per device).  `limits` are the sizes the workspace supports."""
+
+    def __init__(self, device, **limits):
+        self.lib = load()
+        self.device = int(device)
+        self.limits = Limits(**limits)
+        ptr = C.c_void_p()
+        rc = self.lib.isb_create(self.device, C.byref(self.limits), C.byref(ptr))
+        self._h = ptr
+        if rc != ISB_OK:
+            msg = self.lib.isb_last_error(ptr).decode() if ptr else "allocation failed"
+            if ptr:
+                self.lib.isb_destroy(ptr)
+            self._h = None
+            raise IsbError(rc, msg)
+
+    @property
+    def ptr(self):
+        if self._h is None:
+            raise RuntimeError("isb handle already destroyed")
+        return self._h
+
+    def check(self, rc):
+        if rc != ISB_OK:
+            raise IsbError(rc, self.lib.isb_last_error(self.ptr).decode())
+
+    @property
+    def launch_count(self):
+        return int(self.lib.isb_launch_count(self.ptr))
+
+    @property
+    def workspace_bytes(self):
+        return int(self.lib.isb_workspace_bytes(self.ptr))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None:
+            self.lib.isb_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_DEFAULTS = dict(max_batch=1, max_anchors=19248, max_classes=80, max_det=100, max_top_k=200, cand_capacity=16384)
+_handles = {}
+
+
+def get_handle(device, **needs):
+    """Cached per-device handle whose limits cover `needs`; re-created (bigger) when they do not."""
+    device = int(device)
+    cur = _handles.get(device)
+    want = dict(_DEFAULTS)
+    if cur is not None:
+        want = {k: getattr(cur.limits, k) for k in _DEFAULTS}
+    grow = cur is None
+    for k, v in needs.items():
+        if int(v) > want[k]:
+            want[k] = int(v)
+            grow = True
+    if grow:
+        if cur is not None:
+            cur.close()
+        cur = Handle(device, **want)
+        _handles[device] = cur
+    return cur
+
+
+def total_launches():
+    return sum(h.launch_count for h in _handles.values())

@@ -1,0 +1,378 @@
+// C-ABI entry points of libisb.so (see include/isb.h): argument validation, workspace
+// management and kernel sequencing.  No torch, no exceptions, plain pointers and sizes.
+#include <new>
+
+#include "isb_common.cuh"
+
+namespace isb {
+int configure_fast_nms(isb_handle* h);
+int configure_masks(isb_handle* h);
+int configure_candidates(isb_handle* h);
+int launch_decode_boxes(isb_handle*, const float*, const float*, int64_t, float, float, float*, cudaStream_t);
+int launch_jaccard(isb_handle*, const float*, const float*, int, int, int, int, float*, cudaStream_t);
+int launch_correct_boxes(isb_handle*, const float*, int64_t, int, int, float*, cudaStream_t);
+int launch_crop(isb_handle*, const float*, const float*, int, int, int, float*, cudaStream_t);
+int launch_bounds(isb_handle*, const float*, int, int, int, DetBounds*, cudaStream_t);
+int launch_mask_logits(isb_handle*, const float*, const float*, int64_t, int, float*, cudaStream_t);
+}  // namespace isb
+
+using namespace isb;
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+static inline bool aligned4(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 3) == 0; }
+
+extern "C" int isb_version(void) { return ISB_VERSION; }
+
+extern "C" const char* isb_last_error(const isb_handle* h) { return h ? h->err : "null handle"; }
+extern "C" size_t isb_workspace_bytes(const isb_handle* h) { return h ? h->ws_bytes : 0; }
+extern "C" int64_t isb_launch_count(const isb_handle* h) { return h ? h->launches : 0; }
+
+static void free_ws(isb_handle* h) {
+  cudaFree(h->cand_count);
+  cudaFree(h->cand_keys);
+  cudaFree(h->det_keys);
+  cudaFree(h->cand_box);
+  cudaFree(h->det_coef);
+  cudaFree(h->det_bounds);
+  cudaFree(h->stage);
+}
+
+extern "C" void isb_destroy(isb_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  free_ws(h);
+  delete h;
+}
+
+extern "C" int isb_create(int device, const isb_limits* limits, isb_handle** out) {
+  if (!out) return ISB_ERR_BAD_ARG;
+  *out = nullptr;
+  isb_handle* h = new (std::nothrow) isb_handle();
+  if (!h) return ISB_ERR_CUDA;
+  memset(h, 0, sizeof(*h));
+  *out = h;  // returned even on failure so that isb_last_error() can be read; caller destroys it
+  h->device = device;
+  isb_limits L;
+  memset(&L, 0, sizeof(L));
+  if (limits) L = *limits;
+  if (L.max_batch <= 0) L.max_batch = 64;
+  if (L.max_anchors <= 0) L.max_anchors = 19248;
+  if (L.max_classes <= 0) L.max_classes = 80;
+  if (L.max_det <= 0) L.max_det = 100;
+  if (L.max_top_k <= 0) L.max_top_k = 200;
+  if (L.cand_capacity <= 0) L.cand_capacity = 16384;
+  if (L.max_det > ISB_MAX_DET_LIMIT) ISB_FAIL(h, ISB_ERR_LIMIT, "max_det %d > %d", L.max_det, ISB_MAX_DET_LIMIT);
+  if (L.max_anchors > (1 << kRowBits)) ISB_FAIL(h, ISB_ERR_LIMIT, "max_anchors %d > 2^%d", L.max_anchors, kRowBits);
+  if (L.max_classes >= (1 << kClassBits)) ISB_FAIL(h, ISB_ERR_LIMIT, "max_classes %d >= 2^%d", L.max_classes, kClassBits);
+  if (L.cand_capacity > (1ll << 30)) ISB_FAIL(h, ISB_ERR_LIMIT, "cand_capacity too large");
+  h->lim = L;
+  h->cand_cap_pow2 = next_pow2((int)L.cand_capacity);
+  ISB_CUDA(h, cudaSetDevice(device));
+  cudaDeviceProp prop;
+  ISB_CUDA(h, cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) ISB_FAIL(h, ISB_ERR_CUDA, "libisb is built for sm_100a only; device %d is sm_%d%d", device, prop.major, prop.minor);
+  h->num_sms = prop.multiProcessorCount;
+  const size_t B = (size_t)L.max_batch, cap = (size_t)h->cand_cap_pow2;
+  size_t total = 0;
+#define WS_ALLOC(field, bytes)                                   \
+  do {                                                           \
+    ISB_CUDA(h, cudaMalloc((void**)&h->field, (bytes)));         \
+    total += (bytes);                                            \
+  } while (0)
+  WS_ALLOC(cand_count, B * sizeof(int32_t));
+  WS_ALLOC(cand_keys, B * cap * sizeof(uint64_t));
+  WS_ALLOC(det_keys, B * cap * sizeof(uint64_t));
+  WS_ALLOC(cand_box, B * cap * sizeof(float4));
+  WS_ALLOC(det_coef, B * (size_t)L.max_det * ISB_NUM_COEF * sizeof(float));
+  WS_ALLOC(det_bounds, B * (size_t)L.max_det * sizeof(DetBounds));
+#undef WS_ALLOC
+  h->ws_bytes = total;
+  int rc;
+  if ((rc = configure_candidates(h)) != ISB_OK) return rc;
+  if ((rc = configure_fast_nms(h)) != ISB_OK) return rc;
+  if ((rc = configure_masks(h)) != ISB_OK) return rc;
+  h->err[0] = 0;
+  return ISB_OK;
+}
+
+// ----------------------------------------------------------------------------------- YOLACT
+static int check_yolact(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (!in || !out) ISB_FAIL(h, ISB_ERR_BAD_ARG, "null in/out struct");
+  if (!in->box || !in->conf || !in->coef || !in->proto || !in->anchors) ISB_FAIL(h, ISB_ERR_BAD_ARG, "null input tensor");
+  if (!out->boxes || !out->scores || !out->class_ids || !out->masks_arg || !out->masks || !out->counts)
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "null output tensor");
+  if (in->batch <= 0 || in->num_anchors <= 0 || in->num_classes < 2 || in->proto_h <= 0 || in->proto_w <= 0 ||
+      in->out_h <= 0 || in->out_w <= 0 || in->top_k <= 0 || in->max_det <= 0)
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "non-positive dimension");
+  if (in->num_coef != ISB_NUM_COEF) ISB_FAIL(h, ISB_ERR_BAD_ARG, "num_coef must be %d, got %d", ISB_NUM_COEF, in->num_coef);
+  if (in->batch > h->lim.max_batch) ISB_FAIL(h, ISB_ERR_LIMIT, "batch %d > max_batch %d", in->batch, h->lim.max_batch);
+  if (in->num_anchors > h->lim.max_anchors) ISB_FAIL(h, ISB_ERR_LIMIT, "num_anchors %d > max_anchors %d", in->num_anchors, h->lim.max_anchors);
+  if (in->num_classes - 1 > h->lim.max_classes) ISB_FAIL(h, ISB_ERR_LIMIT, "classes %d > max_classes %d", in->num_classes - 1, h->lim.max_classes);
+  if (in->max_det > h->lim.max_det) ISB_FAIL(h, ISB_ERR_LIMIT, "max_det %d > limit %d", in->max_det, h->lim.max_det);
+  if (in->top_k > h->lim.max_top_k) ISB_FAIL(h, ISB_ERR_LIMIT, "top_k %d > limit %d", in->top_k, h->lim.max_top_k);
+  if (out->mask_slot_bytes < (int64_t)in->out_h * in->out_w * in->max_det || (out->mask_slot_bytes & 15))
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_slot_bytes must be >= H*W*max_det and a multiple of 16");
+  return ISB_OK;
+}
+
+static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out, cudaStream_t s) {
+  if (!aligned16(in->box) || !aligned16(in->coef) || !aligned16(in->proto) || !aligned16(in->anchors) ||
+      !aligned4(in->conf) || !aligned16(out->boxes) || !aligned16(out->masks))
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "box/coef/proto/anchors/boxes/masks must be 16-byte aligned, conf 4-byte aligned");
+  int rc;
+  CandParams cp;
+  cp.scores = in->conf;
+  cp.rows = in->num_anchors;
+  cp.ncols = in->num_classes;
+  cp.col0 = 1;  // utils_bbox.py:193 drops the background column
+  cp.use_threshold = 1;
+  cp.threshold = in->confidence;
+  cp.batch = in->batch;
+  if ((rc = launch_candidates(h, cp, s)) != ISB_OK) return rc;
+
+  NmsParams np;
+  memset(&np, 0, sizeof(np));
+  np.batch = in->batch;
+  np.pred_box = reinterpret_cast<const float4*>(in->box);
+  np.anchors = reinterpret_cast<const float4*>(in->anchors);
+  np.boxes = nullptr;
+  np.coef = in->coef;
+  np.rows = in->num_anchors;
+  np.nms_iou = in->nms_iou;
+  np.top_k = in->top_k;
+  np.max_det = in->max_det;
+  np.correct = 1;
+  np.out_h = in->out_h;
+  np.out_w = in->out_w;
+  np.out_box = out->boxes;
+  np.out_score = out->scores;
+  np.out_class = out->class_ids;
+  np.out_coef = nullptr;  // coefficients of kept detections go to the workspace
+  np.out_count = out->counts;
+  if ((rc = launch_fast_nms(h, np, s)) != ISB_OK) return rc;
+
+  MaskParams mp;
+  memset(&mp, 0, sizeof(mp));
+  mp.batch = in->batch;
+  mp.proto = in->proto;
+  mp.coef = h->det_coef;
+  mp.bounds = h->det_bounds;
+  mp.counts = out->counts;
+  mp.m_fixed = -1;
+  mp.det_stride = h->lim.max_det;
+  mp.proto_h = in->proto_h;
+  mp.proto_w = in->proto_w;
+  mp.out_h = in->out_h;
+  mp.out_w = in->out_w;
+  mp.masks_arg = out->masks_arg;
+  mp.masks = out->masks;
+  mp.mask_slot_bytes = out->mask_slot_bytes;
+  return launch_masks(h, mp, s);
+}
+
+extern "C" int isb_yolact_detect(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out, isb_stream stream) {
+  int rc = check_yolact(h, in, out);
+  if (rc != ISB_OK) return rc;
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  return yolact_detect_device(h, in, out, (cudaStream_t)stream);
+}
+
+static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+extern "C" int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out,
+                                      isb_stream stream) {
+  int rc = check_yolact(h, in, out);
+  if (rc != ISB_OK) return rc;
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t B = in->batch, A = in->num_anchors, C = in->num_classes, K = ISB_NUM_COEF;
+  const size_t HW = (size_t)in->out_h * in->out_w, D = in->max_det;
+  const size_t n_box = B * A * 4 * 4, n_conf = B * A * C * 4, n_coef = B * A * K * 4,
+               n_proto = B * (size_t)in->proto_h * in->proto_w * K * 4, n_anc = A * 4 * 4;
+  const size_t o_box = B * D * 16, o_score = B * D * 4, o_cls = B * D * 8, o_arg = B * HW * 8,
+               o_mask = B * (size_t)out->mask_slot_bytes, o_cnt = B * 4;
+  const size_t need = up256(n_box) + up256(n_conf) + up256(n_coef) + up256(n_proto) + up256(n_anc) + up256(o_box) +
+                      up256(o_score) + up256(o_cls) + up256(o_arg) + up256(o_mask) + up256(o_cnt);
+  if (need > h->stage_bytes) {
+    ISB_CUDA(h, cudaStreamSynchronize(s));
+    cudaFree(h->stage);
+    h->stage = nullptr;
+    h->stage_bytes = 0;
+    ISB_CUDA(h, cudaMalloc(&h->stage, need));
+    h->stage_bytes = need;
+  }
+  char* p = static_cast<char*>(h->stage);
+  auto take = [&](size_t bytes) { char* r = p; p += up256(bytes); return r; };
+  isb_yolact_in din = *in;
+  isb_yolact_out dout = *out;
+  din.box = (const float*)take(n_box);
+  din.conf = (const float*)take(n_conf);
+  din.coef = (const float*)take(n_coef);
+  din.proto = (const float*)take(n_proto);
+  din.anchors = (const float*)take(n_anc);
+  dout.boxes = (float*)take(o_box);
+  dout.scores = (float*)take(o_score);
+  dout.class_ids = (int64_t*)take(o_cls);
+  dout.masks_arg = (int64_t*)take(o_arg);
+  dout.masks = (uint8_t*)take(o_mask);
+  dout.counts = (int32_t*)take(o_cnt);
+  ISB_CUDA(h, cudaMemcpyAsync((void*)din.box, in->box, n_box, cudaMemcpyHostToDevice, s));
+  ISB_CUDA(h, cudaMemcpyAsync((void*)din.conf, in->conf, n_conf, cudaMemcpyHostToDevice, s));
+  ISB_CUDA(h, cudaMemcpyAsync((void*)din.coef, in->coef, n_coef, cudaMemcpyHostToDevice, s));
+  ISB_CUDA(h, cudaMemcpyAsync((void*)din.proto, in->proto, n_proto, cudaMemcpyHostToDevice, s));
+  ISB_CUDA(h, cudaMemcpyAsync((void*)din.anchors, in->anchors, n_anc, cudaMemcpyHostToDevice, s));
+  rc = yolact_detect_device(h, &din, &dout, s);
+  if (rc != ISB_OK) return rc;
+  ISB_CUDA(h, cudaMemcpyAsync(out->counts, dout.counts, o_cnt, cudaMemcpyDeviceToHost, s));
+  ISB_CUDA(h, cudaMemcpyAsync(out->boxes, dout.boxes, o_box, cudaMemcpyDeviceToHost, s));
+  ISB_CUDA(h, cudaMemcpyAsync(out->scores, dout.scores, o_score, cudaMemcpyDeviceToHost, s));
+  ISB_CUDA(h, cudaMemcpyAsync(out->class_ids, dout.class_ids, o_cls, cudaMemcpyDeviceToHost, s));
+  ISB_CUDA(h, cudaMemcpyAsync(out->masks_arg, dout.masks_arg, o_arg, cudaMemcpyDeviceToHost, s));
+  ISB_CUDA(h, cudaStreamSynchronize(s));  // counts are needed to size the mask copies
+  bool overflow = false;
+  for (size_t b = 0; b < B; ++b) {
+    const int m = out->counts[b];
+    if (m < 0) { overflow = true; continue; }
+    if (m == 0) continue;
+    ISB_CUDA(h, cudaMemcpyAsync(out->masks + b * (size_t)out->mask_slot_bytes, dout.masks + b * (size_t)out->mask_slot_bytes,
+                                HW * (size_t)m, cudaMemcpyDeviceToHost, s));
+  }
+  ISB_CUDA(h, cudaStreamSynchronize(s));
+  if (overflow) ISB_FAIL(h, ISB_ERR_OVERFLOW, "candidate buffer overflow: raise isb_limits.cand_capacity (now %lld)", (long long)h->lim.cand_capacity);
+  return ISB_OK;
+}
+
+// ----------------------------------------------------------------------------------- stages
+extern "C" int isb_decode_boxes(isb_handle* h, const float* pred, const float* anchors, int64_t n, float var0, float var1,
+                                float* out, isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (n < 0 || !out || (n > 0 && (!pred || !anchors))) ISB_FAIL(h, ISB_ERR_BAD_ARG, "decode_boxes: bad argument");
+  if (!aligned16(pred) || !aligned16(anchors) || !aligned16(out)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "decode_boxes: pointers must be 16-byte aligned");
+  if (n == 0) return ISB_OK;
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  return launch_decode_boxes(h, pred, anchors, n, var0, var1, out, (cudaStream_t)stream);
+}
+
+extern "C" int isb_jaccard(isb_handle* h, const float* a, const float* b, int32_t batch, int32_t na, int32_t nb,
+                           int32_t iscrowd, float* out, isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (batch < 0 || na < 0 || nb < 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "jaccard: negative size");
+  if ((int64_t)batch * na * nb == 0) return ISB_OK;
+  if (!a || !b || !out || !aligned16(a) || !aligned16(b)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "jaccard: null or misaligned pointer");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  return launch_jaccard(h, a, b, batch, na, nb, iscrowd, out, (cudaStream_t)stream);
+}
+
+extern "C" int isb_fast_nms(isb_handle* h, const float* box, const float* scores, const float* coef, int32_t n,
+                            int32_t num_fg_classes, int32_t num_coef, float nms_iou, int32_t top_k, int32_t max_det,
+                            float* out_box, float* out_score, int64_t* out_class, float* out_coef, int32_t* count,
+                            isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (!count || !out_box || !out_score || !out_class || !out_coef) ISB_FAIL(h, ISB_ERR_BAD_ARG, "fast_nms: null output");
+  if (n < 0 || num_fg_classes <= 0 || top_k <= 0 || max_det <= 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "fast_nms: bad size");
+  if (num_coef != ISB_NUM_COEF) ISB_FAIL(h, ISB_ERR_BAD_ARG, "fast_nms: num_coef must be %d", ISB_NUM_COEF);
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n == 0) {
+    ISB_CUDA(h, cudaMemsetAsync(count, 0, sizeof(int32_t), s));
+    return ISB_OK;
+  }
+  if (!box || !scores || !coef || !aligned16(box) || !aligned16(coef) || !aligned16(out_box) || !aligned16(out_coef))
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "fast_nms: null or misaligned pointer");
+  if (n > h->lim.max_anchors) ISB_FAIL(h, ISB_ERR_LIMIT, "fast_nms: n %d > max_anchors %d", n, h->lim.max_anchors);
+  if (num_fg_classes > h->lim.max_classes) ISB_FAIL(h, ISB_ERR_LIMIT, "fast_nms: classes %d > max_classes %d", num_fg_classes, h->lim.max_classes);
+  if (max_det > h->lim.max_det) ISB_FAIL(h, ISB_ERR_LIMIT, "fast_nms: max_det %d > limit %d", max_det, h->lim.max_det);
+  if (top_k > h->lim.max_top_k) ISB_FAIL(h, ISB_ERR_LIMIT, "fast_nms: top_k %d > limit %d", top_k, h->lim.max_top_k);
+  if ((int64_t)n * num_fg_classes > h->lim.cand_capacity)
+    ISB_FAIL(h, ISB_ERR_LIMIT, "fast_nms: n*classes = %lld > cand_capacity %lld", (long long)n * num_fg_classes, (long long)h->lim.cand_capacity);
+  int rc;
+  CandParams cp;
+  cp.scores = scores;
+  cp.rows = n;
+  cp.ncols = num_fg_classes;
+  cp.col0 = 0;
+  cp.use_threshold = 0;  // the stand-alone method ranks every entry (utils_bbox.py:55-64)
+  cp.threshold = 0.0f;
+  cp.batch = 1;
+  if ((rc = launch_candidates(h, cp, s)) != ISB_OK) return rc;
+  NmsParams np;
+  memset(&np, 0, sizeof(np));
+  np.batch = 1;
+  np.boxes = reinterpret_cast<const float4*>(box);
+  np.coef = coef;
+  np.rows = n;
+  np.nms_iou = nms_iou;
+  np.top_k = top_k;
+  np.max_det = max_det;
+  np.correct = 0;
+  np.out_box = out_box;
+  np.out_score = out_score;
+  np.out_class = out_class;
+  np.out_coef = out_coef;
+  np.out_count = count;
+  return launch_fast_nms(h, np, s);
+}
+
+extern "C" int isb_correct_boxes(isb_handle* h, const float* boxes, int64_t m, int32_t out_h, int32_t out_w, float* out,
+                                 isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (m < 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "correct_boxes: negative m");
+  if (m == 0) return ISB_OK;
+  if (!boxes || !out || !aligned16(boxes) || !aligned16(out)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "correct_boxes: null or misaligned pointer");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  return launch_correct_boxes(h, boxes, m, out_h, out_w, out, (cudaStream_t)stream);
+}
+
+extern "C" int isb_crop(isb_handle* h, const float* masks, const float* boxes, int32_t hgt, int32_t wid, int32_t m,
+                        float* out, isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (hgt < 0 || wid < 0 || m < 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "crop: negative size");
+  if ((int64_t)hgt * wid * m == 0) return ISB_OK;
+  if (!masks || !boxes || !out || !aligned16(boxes)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "crop: null or misaligned pointer");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  return launch_crop(h, masks, boxes, hgt, wid, m, out, (cudaStream_t)stream);
+}
+
+extern "C" int isb_mask_logits(isb_handle* h, const float* proto, const float* coef, int32_t proto_h, int32_t proto_w,
+                               int32_t m, float* out, isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (proto_h < 0 || proto_w < 0 || m < 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_logits: negative size");
+  if ((int64_t)proto_h * proto_w * m == 0) return ISB_OK;
+  if (!proto || !coef || !out || !aligned16(proto) || !aligned16(coef)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_logits: null or misaligned pointer");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  return launch_mask_logits(h, proto, coef, (int64_t)proto_h * proto_w, m, out, (cudaStream_t)stream);
+}
+
+extern "C" int isb_mask_assemble(isb_handle* h, const float* proto, const float* coef, const float* boxes_px,
+                                 int32_t proto_h, int32_t proto_w, int32_t m, int32_t out_h, int32_t out_w,
+                                 int64_t* masks_arg, uint8_t* masks, isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (proto_h <= 0 || proto_w <= 0 || out_h <= 0 || out_w <= 0 || m < 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_assemble: bad size");
+  if (m == 0) return ISB_OK;
+  if (m > h->lim.max_det) ISB_FAIL(h, ISB_ERR_LIMIT, "mask_assemble: m %d > max_det %d", m, h->lim.max_det);
+  if (!proto || !coef || !boxes_px || !masks_arg || !masks || !aligned16(proto) || !aligned16(coef) ||
+      !aligned16(boxes_px) || !aligned16(masks))
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_assemble: null or misaligned pointer");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = launch_bounds(h, boxes_px, m, out_h, out_w, h->det_bounds, s);
+  if (rc != ISB_OK) return rc;
+  MaskParams mp;
+  memset(&mp, 0, sizeof(mp));
+  mp.batch = 1;
+  mp.proto = proto;
+  mp.coef = coef;
+  mp.bounds = h->det_bounds;
+  mp.counts = nullptr;
+  mp.m_fixed = m;
+  mp.det_stride = m;
+  mp.proto_h = proto_h;
+  mp.proto_w = proto_w;
+  mp.out_h = out_h;
+  mp.out_w = out_w;
+  mp.masks_arg = masks_arg;
+  mp.masks = masks;
+  mp.mask_slot_bytes = (((int64_t)out_h * out_w * m) + 15) & ~15ll;
+  return launch_masks(h, mp, s);
+}

@@ -1,0 +1,270 @@
+// Internal shared declarations for libisb.so (not part of the public ABI).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "isb.h"
+
+namespace isb {
+
+// ---------------------------------------------------------------------------------------
+// Candidate key layout (64 bit).  Ascending unsigned order of `cand key` is
+//   class ascending, score descending, row (anchor) ascending
+// and of `det key` is score descending, class ascending, row ascending -- the order the
+// reference produces when its two sorts (utils_bbox.py:61, :94) are stable.
+// ---------------------------------------------------------------------------------------
+constexpr int kRowBits = 20;    // < 1 Mi anchors / rows
+constexpr int kClassBits = 12;  // < 4096 foreground classes
+constexpr uint64_t kRowMask = (1ull << kRowBits) - 1;
+constexpr uint64_t kClassMask = (1ull << kClassBits) - 1;
+constexpr uint64_t kPadKey = ~0ull;
+
+__host__ __device__ inline uint32_t float_desc_bits(float f) {
+  // monotone map float -> uint32 such that larger floats give SMALLER integers
+  uint32_t u;
+#ifdef __CUDA_ARCH__
+  u = __float_as_uint(f);
+#else
+  memcpy(&u, &f, 4);
+#endif
+  u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);  // ascending orderable
+  return ~u;
+}
+__host__ __device__ inline float float_from_desc_bits(uint32_t d) {
+  uint32_t u = ~d;
+  u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(u);
+#else
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+#endif
+}
+__host__ __device__ inline uint64_t make_cand_key(uint32_t cls, float score, uint32_t row) {
+  return ((uint64_t)cls << (32 + kRowBits)) | ((uint64_t)float_desc_bits(score) << kRowBits) | row;
+}
+__host__ __device__ inline uint32_t cand_class(uint64_t k) { return (uint32_t)(k >> (32 + kRowBits)); }
+__host__ __device__ inline uint32_t cand_row(uint64_t k) { return (uint32_t)(k & kRowMask); }
+__host__ __device__ inline uint32_t cand_score_bits(uint64_t k) { return (uint32_t)(k >> kRowBits); }
+__host__ __device__ inline uint64_t det_key_from_cand(uint64_t k) {
+  return ((uint64_t)cand_score_bits(k) << 32) | ((uint64_t)cand_class(k) << kRowBits) | cand_row(k);
+}
+__host__ __device__ inline uint32_t det_class(uint64_t k) { return (uint32_t)((k >> kRowBits) & kClassMask); }
+__host__ __device__ inline uint32_t det_row(uint64_t k) { return (uint32_t)(k & kRowMask); }
+__host__ __device__ inline float det_score(uint64_t k) { return float_from_desc_bits((uint32_t)(k >> 32)); }
+
+// Per-detection record the mask kernel consumes (written by the NMS kernel).
+struct DetBounds {
+  int32_t xlo, xhi, ylo, yhi;  // half-open integer pixel ranges equivalent to the float crop tests
+};
+
+// ---------------------------------------------------------------------------------------
+// fp32 building blocks shared by the fused path and the stage entry points, so both give
+// the same bits.  The library is compiled with -fmad=false: every +,-,* below is one
+// IEEE-rounded operation, in the reference's order.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 decode_box(float4 p, float4 a, float var0, float var1) {
+  // utils_bbox.py:17-24
+  float cx = a.x + (p.x * var0) * a.z;
+  float cy = a.y + (p.y * var0) * a.w;
+  float w = a.z * expf(p.z * var1);
+  float h = a.w * expf(p.w * var1);
+  float x1 = cx - w / 2.0f;
+  float y1 = cy - h / 2.0f;
+  return make_float4(x1, y1, w + x1, h + y1);
+}
+
+__device__ __forceinline__ float box_area(float4 b) { return (b.z - b.x) * (b.w - b.y); }
+
+__device__ __forceinline__ float iou_pair(float4 a, float area_a, float4 b, float area_b) {
+  // utils_bbox.py:38-47: inter / ((area_a + area_b) - inter), no eps
+  float dx = fmaxf(fminf(a.z, b.z) - fmaxf(a.x, b.x), 0.0f);
+  float dy = fmaxf(fminf(a.w, b.w) - fmaxf(a.y, b.y), 0.0f);
+  float inter = dx * dy;
+  return inter / ((area_a + area_b) - inter);
+}
+
+__device__ __forceinline__ float4 correct_box(float4 b, float wf, float hf) {
+  // utils_bbox.py:147-151 (note :149 uses the already-updated x1y1)
+  float x1 = b.x * wf, y1 = b.y * hf, x2 = b.z * wf, y2 = b.w * hf;
+  x1 = fminf(x1, x2);
+  y1 = fminf(y1, y2);
+  x2 = fmaxf(x1, x2);
+  y2 = fmaxf(y1, y2);
+  x1 = fmaxf(x1, 0.0f);
+  y1 = fmaxf(y1, 0.0f);
+  x2 = fminf(x2, wf);
+  y2 = fminf(y2, hf);
+  return make_float4(x1, y1, x2, y2);
+}
+
+// Integer pixel range [lo, hi) equivalent to the float tests (col >= v1) && (col < v2) of
+// utils_bbox.py:162-165 for integer-valued col in [0, size).
+__device__ __forceinline__ void crop_range(float v1, float v2, int size, int& lo, int& hi) {
+  float l = ceilf(v1), u = ceilf(v2);
+  lo = (l <= 0.0f) ? 0 : (l >= (float)size ? size : (int)l);
+  hi = (u <= 0.0f) ? 0 : (u >= (float)size ? size : (int)u);
+  if (!(v1 == v1) || !(v2 == v2)) { lo = 0; hi = 0; }  // NaN compares false everywhere
+}
+
+__device__ __forceinline__ float sigmoidf_ref(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+// Bilinear source index / weight, aten area_pixel_compute_source_index +
+// guard_index_and_lambda with align_corners=False (reached from utils_bbox.py:228).
+__device__ __forceinline__ void bilinear_src(int dst, float scale, int in_size, int& i0, int& i1, float& l0, float& l1) {
+  float src = scale * ((float)dst + 0.5f) - 0.5f;
+  if (src < 0.0f) src = 0.0f;
+  int f = (int)floorf(src);
+  i0 = f < in_size - 1 ? f : in_size - 1;
+  float lam = src - (float)i0;
+  lam = fminf(fmaxf(lam, 0.0f), 1.0f);
+  l1 = lam;
+  l0 = 1.0f - lam;
+  i1 = i0 + (i0 < in_size - 1 ? 1 : 0);
+}
+
+// ---------------------------------------------------------------------------------------
+// sm_100a async-copy helpers (1-D bulk TMA + mbarrier); SASS: UBLKCP / SYNCS.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// global -> shared bulk copy; dst/src 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// shared -> global bulk store (bulk async-group completion).
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__host__ __device__ inline int next_pow2(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+}  // namespace isb
+
+// ---------------------------------------------------------------------------------------
+// Handle
+// ---------------------------------------------------------------------------------------
+struct isb_handle {
+  int device;
+  int num_sms;
+  isb_limits lim;
+  int64_t cand_cap_pow2;  // per-image capacity of the key arrays (power of two)
+  char err[512];
+  int64_t launches;
+  size_t ws_bytes;
+  // workspace (device)
+  int32_t* cand_count;   // [max_batch]
+  uint64_t* cand_keys;   // [max_batch][cand_cap_pow2]
+  uint64_t* det_keys;    // [max_batch][cand_cap_pow2]   kept keys (global fallback of the NMS kernel)
+  float4* cand_box;      // [max_batch][cand_cap_pow2]   decoded boxes (global fallback)
+  float* det_coef;       // [max_batch][max_det][K]
+  isb::DetBounds* det_bounds;  // [max_batch][max_det]
+  // device staging for the *_host entry points (allocated on first use)
+  void* stage;
+  size_t stage_bytes;
+};
+
+#define ISB_FAIL(h, code, ...)                          \
+  do {                                                  \
+    snprintf((h)->err, sizeof((h)->err), __VA_ARGS__);  \
+    return (code);                                      \
+  } while (0)
+
+#define ISB_CUDA(h, expr)                                                                    \
+  do {                                                                                       \
+    cudaError_t e_ = (expr);                                                                 \
+    if (e_ != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
+  } while (0)
+
+#define ISB_LAUNCH_CHECK(h, name)                                                                 \
+  do {                                                                                            \
+    cudaError_t e_ = cudaGetLastError();                                                          \
+    if (e_ != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "launch %s: %s", name, cudaGetErrorString(e_)); \
+    (h)->launches++;                                                                              \
+  } while (0)
+
+// Kernel launchers implemented in the other translation units.
+namespace isb {
+
+struct CandParams {
+  const float* scores;   // [B, rows, ncols]
+  int32_t rows, ncols;   // ncols includes skipped leading columns
+  int32_t col0;          // first column that is a foreground class (1 for conf with background, 0 for stage call)
+  int32_t use_threshold; // 0: every entry is a candidate
+  float threshold;
+  int32_t batch;
+};
+int launch_candidates(isb_handle* h, const CandParams& p, cudaStream_t s);
+
+struct NmsParams {
+  int32_t batch;
+  // box source: either raw regressions + anchors (decode) or ready boxes
+  const float4* pred_box;  // [B, rows] (decode mode) or nullptr
+  const float4* anchors;   // [rows]
+  const float4* boxes;     // [B, rows] ready boxes (stage mode) or nullptr
+  const float* coef;       // [B, rows, K]
+  int32_t rows;
+  float nms_iou;
+  int32_t top_k, max_det;
+  int32_t correct;         // 1: scale/clamp to pixels and emit crop bounds (fused path)
+  int32_t out_h, out_w;
+  float* out_box;          // [B, max_det, 4]
+  float* out_score;        // [B, max_det]
+  int64_t* out_class;      // [B, max_det]
+  float* out_coef;         // [B, max_det, K]
+  int32_t* out_count;      // [B]
+};
+int launch_fast_nms(isb_handle* h, const NmsParams& p, cudaStream_t s);
+
+struct MaskParams {
+  int32_t batch;
+  const float* proto;        // [B, Ph, Pw, K]
+  const float* coef;         // [B, max_det_stride, K]
+  const DetBounds* bounds;   // [B, max_det_stride]
+  const int32_t* counts;     // [B]   device; or nullptr when m_fixed >= 0
+  int32_t m_fixed;
+  int32_t det_stride;        // rows between images in coef / bounds
+  int32_t proto_h, proto_w, out_h, out_w;
+  int64_t* masks_arg;        // [B, H, W]
+  uint8_t* masks;            // B slots
+  int64_t mask_slot_bytes;
+};
+int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s);
+
+}  // namespace isb

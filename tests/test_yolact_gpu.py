@@ -1,0 +1,222 @@
+"""GPU parity tests for the YOLACT path: the CUDA kernels (through the C ABI, via the
+BBoxUtility drop-in) against the reference-generated golden fixtures and the numpy oracle."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import assert_close_f32, assert_masks_close, load_golden, unpack_masks
+from oracle import synth, yolact_np as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def bu():
+    assert torch.cuda.is_available()
+    from isb import _lib
+    _lib.load()  # must be the in-tree libisb.so; raises if missing
+    from isb.yolact import BBoxUtility
+    return BBoxUtility()
+
+
+def dev(x):
+    return torch.as_tensor(np.asarray(x)).cuda()
+
+
+def host(t):
+    return t.cpu().numpy()
+
+
+# ------------------------------------------------------------------------------- stage KATs
+def test_decode_boxes(bu):
+    g = load_golden("yolact_stages")
+    out = host(bu.decode_boxes(dev(g["pred"]), dev(g["anchors"])))
+    assert_close_f32(out, g["decoded"], 1e-5, "decode_boxes")
+
+
+def test_jaccard_bit_exact(bu):
+    g = load_golden("yolact_stages")
+    dec = g["decoded"]
+    out = host(bu.jaccard(dev(dec[:90]), dev(dec[40:150])))
+    assert np.array_equal(out, g["iou"])
+    # batched form
+    a = np.stack([dec[:50], dec[50:100]])
+    out3 = host(bu.jaccard(dev(a), dev(a)))
+    assert np.array_equal(out3, O.jaccard(a, a))
+
+
+@pytest.mark.parametrize("tag,thr,top_k,max_det", [("f1", 0.5, 200, 100), ("f2", 0.3, 50, 20)])
+def test_fast_nms_stage(bu, tag, thr, top_k, max_det):
+    g = load_golden("yolact_stages")
+    b, s, c, k = bu.fast_non_max_suppression(dev(g["nms_box"]), dev(g["nms_scores"]), dev(g["nms_coef"]), thr, top_k, max_det)
+    assert np.array_equal(host(s), g[tag + "_score"])
+    assert np.array_equal(host(c), g[tag + "_cls"]) and c.dtype == torch.int64
+    assert np.array_equal(host(b), g[tag + "_box"])
+    assert np.array_equal(host(k), g[tag + "_coef"])
+
+
+def test_correct_boxes_and_crop_bit_exact(bu):
+    g = load_golden("yolact_stages")
+    assert np.array_equal(host(bu.yolact_correct_boxes(dev(g["raw"]), np.array([123, 77]))), g["corrected"])
+    assert np.array_equal(host(bu.crop(dev(g["maps"]), dev(g["crop_boxes"]))), g["cropped"])
+
+
+def test_mask_logits_within_1e5(bu):
+    gen = torch.Generator().manual_seed(3)
+    proto = torch.relu(torch.randn(138, 138, 32, generator=gen))
+    coef = torch.tanh(torch.randn(100, 32, generator=gen))
+    ref = torch.matmul(proto.double(), coef.double().t()).numpy()
+    out = host(bu.mask_logits(proto.cuda(), coef.cuda()))
+    assert_close_f32(out, ref, 1e-5, "mask logits")
+
+
+def test_assemble_masks_vs_oracle(bu):
+    gen = torch.Generator().manual_seed(4)
+    proto = torch.relu(torch.randn(23, 31, 32, generator=gen))
+    coef = torch.tanh(torch.randn(13, 32, generator=gen))
+    shape = (61, 90)
+    raw = torch.rand(13, 4, generator=gen)
+    boxes = O.yolact_correct_boxes(raw.numpy(), shape)
+    boxes[3] = [0, 0, shape[1], shape[0]]          # a full-image detection
+    boxes[5] = [10.5, 7.25, 10.5, 30.0]            # empty box
+    arg_ref, m_ref = O.assemble_masks(proto.numpy(), coef.numpy(), boxes, shape)
+    arg, m = bu.assemble_masks(proto.cuda(), coef.cuda(), dev(boxes), shape)
+    assert m.dtype == torch.bool and arg.dtype == torch.int64
+    assert_masks_close(host(m), m_ref, 1e-3, "masks")
+    assert float(np.mean(host(arg) != arg_ref)) <= 1e-3
+
+
+def test_assemble_masks_downsample_and_many(bu):
+    # H < P (tile shrinks to keep the prototype footprint bounded) and m > 256 (several list rounds)
+    gen = torch.Generator().manual_seed(6)
+    proto = torch.relu(torch.randn(40, 36, 32, generator=gen))
+    shape = (17, 23)
+    m = 300
+    coef = torch.tanh(torch.randn(m, 32, generator=gen))
+    boxes = O.yolact_correct_boxes(torch.rand(m, 4, generator=gen).numpy(), shape)
+    arg_ref, m_ref = O.assemble_masks(proto.numpy(), coef.numpy(), boxes, shape)
+    arg, mk = bu.assemble_masks(proto.cuda(), coef.cuda(), dev(boxes), shape)
+    assert_masks_close(host(mk), m_ref, 1e-3, "masks")
+    assert float(np.mean(host(arg) != arg_ref)) <= 2e-3
+
+
+# ------------------------------------------------------------------------------- end to end
+def _check(g, res):
+    boxes, scores, cls, arg, masks = res
+    assert boxes.dtype == torch.float32 and scores.dtype == torch.float32 and cls.dtype == torch.int64
+    assert arg.dtype == torch.int64 and masks.dtype == torch.bool and masks.is_contiguous()
+    assert np.array_equal(host(scores), g["scores"]), "keep set / scores must be bit-exact"
+    assert np.array_equal(host(cls), g["class_ids"])
+    assert_close_f32(host(boxes), g["boxes"], 1e-5, "boxes")
+    assert_masks_close(host(masks), unpack_masks(g), 1e-3, "masks")
+    assert float(np.mean(host(arg) != g["masks_arg"])) <= 1e-3
+
+
+@pytest.mark.parametrize("name", ["yolact_tiny_a", "yolact_tiny_b", "yolact_tiny_one"])
+def test_tiny_end_to_end(bu, name):
+    g = load_golden(name)
+    res = bu.decode_nms((dev(g["box"])[None], dev(g["conf"])[None], dev(g["coef"])[None], dev(g["proto"])[None]),
+                        dev(g["anchors"]), float(g["confidence"]), float(g["nms_iou"]), g["image_shape"])
+    _check(g, res)
+
+
+def test_no_survivor_returns_nones(bu):
+    g = load_golden("yolact_tiny_none")
+    res = bu.decode_nms((dev(g["box"])[None], dev(g["conf"])[None], dev(g["coef"])[None], dev(g["proto"])[None]),
+                        dev(g["anchors"]), float(g["confidence"]), float(g["nms_iou"]), g["image_shape"])
+    assert res == (None,) * 5
+
+
+def _full_inputs(g):
+    size, c = int(g["input_size"]), int(g["num_classes"])
+    a, p = synth.yolact_dims(size)
+    heads = synth.yolact_heads(int(g["seed"]), a, num_classes=c, proto=p, objects=int(g["objects"]))
+    anchors = torch.from_numpy(O.get_anchors((size, size))).float()
+    return heads, anchors
+
+
+@pytest.mark.parametrize("name", ["yolact_550_coco", "yolact_550_coco_sparse", "yolact_544_voc_1080p"])
+def test_full_size_end_to_end(bu, name):
+    g = load_golden(name)
+    (box, conf, coef, proto), anchors = _full_inputs(g)
+    res = bu.decode_nms((box[None].cuda(), conf[None].cuda(), coef[None].cuda(), proto[None].cuda()), anchors.cuda(),
+                        float(g["confidence"]), float(g["nms_iou"]), g["image_shape"])
+    _check(g, res)
+
+
+def test_batch_equals_single_and_oracle(bu):
+    a, p = synth.yolact_dims(550)
+    anchors = torch.from_numpy(O.get_anchors((550, 550))).float()
+    bsz = 5
+    box, conf, coef, proto = synth.yolact_batch(2000, bsz, a, num_classes=81, proto=p)
+    conf[3] = conf[3] * 0.0 + 0.001                        # image 3: nothing passes -> count 0
+    res = bu.decode_nms_batch((box.cuda(), conf.cuda(), coef.cuda(), proto.cuda()), anchors.cuda(), 0.05, 0.5, (550, 550))
+    counts = host(res.counts)
+    assert counts[3] == 0 and (counts[[0, 1, 2, 4]] == 100).all()
+    for b in (0, 1, 4):
+        single = bu.decode_nms((box[b:b + 1].cuda(), conf[b:b + 1].cuda(), coef[b:b + 1].cuda(), proto[b:b + 1].cuda()),
+                               anchors.cuda(), 0.05, 0.5, np.array([550, 550]))
+        batched = res.image(b)
+        for x, y in zip(single, batched):
+            assert torch.equal(x, y)
+    ref = O.decode_nms((box[1].numpy(), conf[1].numpy(), coef[1].numpy(), proto[1].numpy()), anchors.numpy(), 0.05, 0.5, (550, 550))
+    got = res.image(1)
+    assert np.array_equal(host(got[1]), ref[1]) and np.array_equal(host(got[2]), ref[2])
+    assert_masks_close(host(got[4]), ref[4], 1e-3, "masks")
+    assert res.image(3) == (None,) * 5
+
+
+def test_verseg_fast_nms(bu):
+    g = load_golden("verseg_fastnms")
+    box, score, coef = synth.verseg_boxes(int(g["seed"]), int(g["n"]))
+    b, s, c, k = bu.fast_non_max_suppression(box.cuda(), score.cuda(), coef.cuda(), 0.5, int(g["top_k"]), int(g["max_det"]))
+    assert np.array_equal(host(s), g["score"]) and np.array_equal(host(b), g["box"]) and np.array_equal(host(c), g["cls"])
+
+
+def test_candidate_overflow_grows_workspace(bu, monkeypatch):
+    # confidence 0 makes every (anchor, class) entry a candidate: 600*5 = 3000 per image, more than
+    # the 1024 the workspace is created with here -> counts = -1 -> the shim grows it and reruns
+    from isb import _lib
+    for hd in _lib._handles.values():
+        hd.close()
+    _lib._handles.clear()
+    monkeypatch.setitem(_lib._DEFAULTS, "cand_capacity", 1024)
+    g = load_golden("yolact_tiny_a")
+    args = ((dev(g["box"])[None], dev(g["conf"])[None], dev(g["coef"])[None], dev(g["proto"])[None]), dev(g["anchors"]))
+    res = bu.decode_nms(*args, 0.0, 0.5, g["image_shape"])
+    ref = O.decode_nms((g["box"], g["conf"], g["coef"], g["proto"]), g["anchors"], 0.0, 0.5, g["image_shape"])
+    assert np.array_equal(host(res[1]), ref[1]) and np.array_equal(host(res[2]), ref[2])
+    assert_masks_close(host(res[4]), ref[4], 1e-3, "masks")
+    assert _lib.get_handle(0).limits.cand_capacity >= 3000
+
+
+# ------------------------------------------------------------------------------- full-size properties
+def test_benchmark_size_properties(bu):
+    """B = 64 at COCO 550^2 (BASELINE.json configs[1]): properties that need no oracle."""
+    a, p = synth.yolact_dims(550)
+    anchors = torch.from_numpy(O.get_anchors((550, 550))).float().cuda()
+    bsz = 64
+    one = synth.yolact_batch(3000, 4, a, num_classes=81, proto=p)
+    box, conf, coef, proto = [t.cuda().repeat((bsz // 4,) + (1,) * (t.dim() - 1)) for t in one]
+    r1 = bu.decode_nms_batch((box, conf, coef, proto), anchors, 0.05, 0.5, (550, 550))
+    r2 = bu.decode_nms_batch((box, conf, coef, proto), anchors, 0.05, 0.5, (550, 550))
+    torch.cuda.synchronize()
+    counts = host(r1.counts)
+    assert (counts > 0).all() and (counts <= 100).all()
+    assert torch.equal(r1.counts, r2.counts)
+    for b in (0, 17, 63):
+        m = int(counts[b])
+        bx, sc, cl, arg, mk = r1.image(b, m)
+        bx2, sc2, cl2, arg2, mk2 = r2.image(b, m)
+        assert torch.equal(mk, mk2) and torch.equal(arg, arg2) and torch.equal(sc, sc2)      # idempotent
+        assert torch.equal(mk, r1.image(b % 4, m)[4])                                       # replicas agree
+        s = host(sc)
+        assert (np.diff(s) <= 0).all() and (s > 0.05).all()                                 # sorted, thresholded
+        bxh = host(bx)
+        assert (bxh[:, 0] >= 0).all() and (bxh[:, 2] <= 550).all() and (bxh[:, 1] >= 0).all() and (bxh[:, 3] <= 550).all()
+        mkh, argh = host(mk), host(arg)
+        ys, xs, js = np.nonzero(mkh)
+        assert (xs >= bxh[js, 0]).all() and (xs < bxh[js, 2]).all() and (ys >= bxh[js, 1]).all() and (ys < bxh[js, 3]).all()
+        assert ((argh >= 0) & (argh < m)).all()
+        cy, cx = np.nonzero(mkh.any(axis=2))
+        assert mkh[cy, cx, argh[cy, cx]].all()            # the arg-max detection is > 0.5 wherever any is
