@@ -60,6 +60,14 @@ ISB_API size_t isb_workspace_bytes(const isb_handle* h);
 /* Number of kernels this library has launched through the handle (bench `gpu_launches`). */
 ISB_API int64_t isb_launch_count(const isb_handle* h);
 
+/* Per-stage device timing of isb_yolact_detect, taken with CUDA events recorded on the launch
+ * stream between the kernels (no synchronisation while recording).  isb_profile_begin arms a
+ * ring of `max_calls` slots (0 disables); every following isb_yolact_detect call fills one slot;
+ * isb_profile_read synchronises on the last slot and returns, per stage (0 = candidate filter,
+ * 1 = sort + Fast NMS, 2 = mask assembly), the summed milliseconds over the recorded calls. */
+ISB_API int isb_profile_begin(isb_handle* h, int32_t max_calls);
+ISB_API int isb_profile_read(isb_handle* h, double stage_ms[3], int32_t* calls);
+
 /* ------------------------------------------------------------------------------------
  * YOLACT Detect + mask assembly, fused, for a batch of images.
  * Replaces BBoxUtility.decode_nms, inst_model/yolact/utils/utils_bbox.py:170-243

@@ -15,6 +15,7 @@ ISB_OK, ISB_ERR_BAD_ARG, ISB_ERR_CUDA, ISB_ERR_LIMIT, ISB_ERR_OVERFLOW = 0, -1, 
 # every exported symbol of include/isb.h (tests check the library exports exactly these)
 SYMBOLS = (
     "isb_version", "isb_create", "isb_destroy", "isb_last_error", "isb_workspace_bytes", "isb_launch_count",
+    "isb_profile_begin", "isb_profile_read",
     "isb_yolact_detect", "isb_yolact_detect_host", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
     "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_assemble",
 )
@@ -70,6 +71,8 @@ def load():
         lib.isb_workspace_bytes.restype = C.c_size_t
         lib.isb_launch_count.argtypes = [vp]
         lib.isb_launch_count.restype = i64
+        lib.isb_profile_begin.argtypes = [vp, i32]
+        lib.isb_profile_read.argtypes = [vp, C.POINTER(C.c_double * 3), C.POINTER(i32)]
         lib.isb_yolact_detect.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactOut), vp]
         lib.isb_yolact_detect_host.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactOut), vp]
         lib.isb_decode_boxes.argtypes = [vp, vp, vp, i64, f32, f32, vp, vp]
@@ -121,6 +124,16 @@ class Handle:
     @property
     def workspace_bytes(self):
         return int(self.lib.isb_workspace_bytes(self.ptr))
+
+    def profile_begin(self, max_calls):
+        self.check(self.lib.isb_profile_begin(self.ptr, int(max_calls)))
+
+    def profile_read(self):
+        """-> ([ms_candidates, ms_nms, ms_masks] summed over the recorded calls, calls)"""
+        ms = (C.c_double * 3)()
+        n = C.c_int32()
+        self.check(self.lib.isb_profile_read(self.ptr, C.byref(ms), C.byref(n)))
+        return [ms[0], ms[1], ms[2]], int(n.value)
 
     def close(self):
         if getattr(self, "_h", None) is not None:

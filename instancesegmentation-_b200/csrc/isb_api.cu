@@ -27,7 +27,48 @@ extern "C" const char* isb_last_error(const isb_handle* h) { return h ? h->err :
 extern "C" size_t isb_workspace_bytes(const isb_handle* h) { return h ? h->ws_bytes : 0; }
 extern "C" int64_t isb_launch_count(const isb_handle* h) { return h ? h->launches : 0; }
 
+static void free_profile(isb_handle* h) {
+  if (h->prof_events) {
+    for (int i = 0; i < h->prof_cap * 4; ++i) cudaEventDestroy(h->prof_events[i]);
+    delete[] h->prof_events;
+  }
+  h->prof_events = nullptr;
+  h->prof_cap = h->prof_used = 0;
+}
+
+extern "C" int isb_profile_begin(isb_handle* h, int32_t max_calls) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (max_calls < 0 || max_calls > (1 << 16)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "profile_begin: bad max_calls");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  free_profile(h);
+  if (max_calls == 0) return ISB_OK;
+  h->prof_events = new (std::nothrow) cudaEvent_t[(size_t)max_calls * 4];
+  if (!h->prof_events) ISB_FAIL(h, ISB_ERR_CUDA, "profile_begin: out of host memory");
+  for (int i = 0; i < max_calls * 4; ++i) ISB_CUDA(h, cudaEventCreate(&h->prof_events[i]));
+  h->prof_cap = max_calls;
+  return ISB_OK;
+}
+
+extern "C" int isb_profile_read(isb_handle* h, double stage_ms[3], int32_t* calls) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (!stage_ms || !calls) ISB_FAIL(h, ISB_ERR_BAD_ARG, "profile_read: null output");
+  stage_ms[0] = stage_ms[1] = stage_ms[2] = 0.0;
+  *calls = h->prof_used;
+  if (h->prof_used == 0) return ISB_OK;
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_CUDA(h, cudaEventSynchronize(h->prof_events[(size_t)(h->prof_used - 1) * 4 + 3]));
+  for (int c = 0; c < h->prof_used; ++c)
+    for (int st = 0; st < 3; ++st) {
+      float ms = 0.f;
+      ISB_CUDA(h, cudaEventElapsedTime(&ms, h->prof_events[(size_t)c * 4 + st], h->prof_events[(size_t)c * 4 + st + 1]));
+      stage_ms[st] += ms;
+    }
+  h->prof_used = 0;
+  return ISB_OK;
+}
+
 static void free_ws(isb_handle* h) {
+  free_profile(h);
   cudaFree(h->cand_count);
   cudaFree(h->cand_keys);
   cudaFree(h->det_keys);
@@ -121,6 +162,8 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const is
       !aligned4(in->conf) || !aligned16(out->boxes) || !aligned16(out->masks))
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "box/coef/proto/anchors/boxes/masks must be 16-byte aligned, conf 4-byte aligned");
   int rc;
+  cudaEvent_t* ev = (h->prof_events && h->prof_used < h->prof_cap) ? h->prof_events + (size_t)h->prof_used * 4 : nullptr;
+  if (ev) ISB_CUDA(h, cudaEventRecord(ev[0], s));
   CandParams cp;
   cp.scores = in->conf;
   cp.rows = in->num_anchors;
@@ -130,6 +173,7 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const is
   cp.threshold = in->confidence;
   cp.batch = in->batch;
   if ((rc = launch_candidates(h, cp, s)) != ISB_OK) return rc;
+  if (ev) ISB_CUDA(h, cudaEventRecord(ev[1], s));
 
   NmsParams np;
   memset(&np, 0, sizeof(np));
@@ -151,6 +195,7 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const is
   np.out_coef = nullptr;  // coefficients of kept detections go to the workspace
   np.out_count = out->counts;
   if ((rc = launch_fast_nms(h, np, s)) != ISB_OK) return rc;
+  if (ev) ISB_CUDA(h, cudaEventRecord(ev[2], s));
 
   MaskParams mp;
   memset(&mp, 0, sizeof(mp));
@@ -168,7 +213,12 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const is
   mp.masks_arg = out->masks_arg;
   mp.masks = out->masks;
   mp.mask_slot_bytes = out->mask_slot_bytes;
-  return launch_masks(h, mp, s);
+  if ((rc = launch_masks(h, mp, s)) != ISB_OK) return rc;
+  if (ev) {
+    ISB_CUDA(h, cudaEventRecord(ev[3], s));
+    h->prof_used++;
+  }
+  return ISB_OK;
 }
 
 extern "C" int isb_yolact_detect(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out, isb_stream stream) {

@@ -198,6 +198,9 @@ struct isb_handle {
   // device staging for the *_host entry points (allocated on first use)
   void* stage;
   size_t stage_bytes;
+  // optional per-stage event ring (isb_profile_begin / isb_profile_read)
+  cudaEvent_t* prof_events;  // [prof_cap][4]
+  int32_t prof_cap, prof_used;
 };
 
 #define ISB_FAIL(h, code, ...)                          \

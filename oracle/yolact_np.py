@@ -183,11 +183,10 @@ def upsample_bilinear(maps, out_h, out_w):
     maps = np.asarray(maps, dtype=F32)
     y0, y1, hy0, hy1 = _linear_index_weights(maps.shape[1], out_h)
     x0, x1, wx0, wx1 = _linear_index_weights(maps.shape[2], out_w)
-    top = maps[:, y0, :]
-    bot = maps[:, y1, :]
-    t = top[:, :, x0] * wx0 + top[:, :, x1] * wx1
-    b = bot[:, :, x0] * wx0 + bot[:, :, x1] * wx1
-    return (t * hy0[None, :, None] + b * hy1[None, :, None]).astype(F32)
+    # horizontal pass on the small map first: row[py, x] = w0*p[py, x0] + w1*p[py, x1]; the vertical
+    # pass then combines two such rows -- the same values in the same order as the nested form.
+    rows = maps[:, :, x0] * wx0 + maps[:, :, x1] * wx1
+    return (rows[:, y0, :] * hy0[None, :, None] + rows[:, y1, :] * hy1[None, :, None]).astype(F32)
 
 
 # --------------------------------------------------------------------------- Y11
