@@ -70,6 +70,7 @@ extern "C" int isb_profile_read(isb_handle* h, double stage_ms[3], int32_t* call
 static void free_ws(isb_handle* h) {
   free_profile(h);
   cudaFree(h->cand_count);
+  cudaFree(h->work_counter);
   cudaFree(h->cand_keys);
   cudaFree(h->det_keys);
   cudaFree(h->cand_box);
@@ -121,6 +122,7 @@ extern "C" int isb_create(int device, const isb_limits* limits, isb_handle** out
     total += (bytes);                                            \
   } while (0)
   WS_ALLOC(cand_count, B * sizeof(int32_t));
+  WS_ALLOC(work_counter, 256);
   WS_ALLOC(cand_keys, B * cap * sizeof(uint64_t));
   WS_ALLOC(det_keys, B * cap * sizeof(uint64_t));
   WS_ALLOC(cand_box, B * cap * sizeof(float4));

@@ -190,6 +190,7 @@ struct isb_handle {
   size_t ws_bytes;
   // workspace (device)
   int32_t* cand_count;   // [max_batch]
+  int32_t* work_counter; // [1] dynamic work counter of the mask kernel
   uint64_t* cand_keys;   // [max_batch][cand_cap_pow2]
   uint64_t* det_keys;    // [max_batch][cand_cap_pow2]   kept keys (global fallback of the NMS kernel)
   float4* cand_box;      // [max_batch][cand_cap_pow2]   decoded boxes (global fallback)
