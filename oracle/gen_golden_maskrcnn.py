@@ -1,0 +1,147 @@
+"""Generate tests/golden/maskrcnn_*.npz from the REAL reference functions + installed torchvision.
+
+Build container only:   PYTHONDONTWRITEBYTECODE=1 python -m oracle.gen_golden_maskrcnn
+"""
+from __future__ import annotations
+
+import functools
+import sys
+import types
+from collections import OrderedDict
+
+import numpy as np
+import torch
+
+from .gen_golden import REF, _save, digest
+
+sys.dont_write_bytecode = True
+
+
+def _ref():
+    if REF not in sys.path:
+        sys.path.insert(0, REF)
+    from inst_model.Mask_RCNN.net.network_files import boxes, det_utils, roi_head, rpn_function, transform
+    return types.SimpleNamespace(boxes=boxes, det_utils=det_utils, roi_head=roi_head, rpn=rpn_function, transform=transform)
+
+
+def clustered_boxes(g, n, extent=(800.0, 600.0), clusters=40, jitter=6.0):
+    ctr = torch.rand(clusters, 2, generator=g) * torch.tensor(extent)
+    size = torch.rand(clusters, 2, generator=g) * 120 + 20
+    pick = torch.randint(0, clusters, (n,), generator=g)
+    c = ctr[pick] + torch.randn(n, 2, generator=g) * jitter
+    s = size[pick] * (1 + torch.randn(n, 2, generator=g) * 0.08)
+    return torch.cat([c - s / 2, c + s / 2], 1).contiguous()
+
+
+def stages(name, seed):
+    from torchvision.ops import MultiScaleRoIAlign
+    R = _ref()
+    g = torch.Generator().manual_seed(seed)
+    out = {}
+    # --- M1 decode_single: RPN weights (k=1) and box-head weights (k=6 classes), incl. clamp of dw/dh
+    n = 400
+    xy = torch.rand(n, 2, generator=g) * 700
+    prop = torch.cat([xy, xy + torch.rand(n, 2, generator=g) * 250 + 4], 1)
+    rel1 = torch.randn(n, 4, generator=g) * 0.6
+    rel6 = torch.randn(n, 24, generator=g) * 3.0
+    rel6[:7, 2::4] = 60.0   # hits bbox_xform_clip
+    out.update(dec_boxes=prop.numpy(), dec_rel1=rel1.numpy(), dec_rel6=rel6.numpy(),
+               dec_out1=R.det_utils.BoxCoder((1.0, 1.0, 1.0, 1.0)).decode_single(rel1, prop).numpy(),
+               dec_out6=R.det_utils.BoxCoder((10.0, 10.0, 5.0, 5.0)).decode_single(rel6, prop).numpy())
+    # --- clip / small boxes
+    wild = torch.randn(300, 4, generator=g) * 500 + 300
+    out.update(clip_in=wild.numpy(), clip_out=R.boxes.clip_boxes_to_image(wild, (600, 800)).numpy(),
+               small_keep=R.boxes.remove_small_boxes(R.boxes.clip_boxes_to_image(wild, (600, 800)), 1.0).numpy())
+    # --- nms / batched_nms on clustered boxes, with score ties, two thresholds
+    nb = clustered_boxes(g, 2500)
+    sc = torch.rand(2500, generator=g)
+    sc[::7] = torch.round(sc[::7] * 20) / 20          # ties
+    idx = torch.randint(0, 5, (2500,), generator=g)
+    out.update(nms_boxes=nb.numpy(), nms_scores=sc.numpy(), nms_idxs=idx.numpy(),
+               nms_keep_05=R.boxes.nms(nb, sc, 0.5).numpy(), nms_keep_07=R.boxes.nms(nb, sc, 0.7).numpy(),
+               bnms_keep_05=R.boxes.batched_nms(nb, sc, idx, 0.5).numpy(),
+               bnms_keep_07=R.boxes.batched_nms(nb, sc, idx, 0.7).numpy())
+    # adversarial near-threshold pairs: IoU of (unit-height) boxes [0,w] and [d,w+d] is (w-d)/(w+d)
+    adv = []
+    for k in range(200):
+        w = 100.0 + k
+        d = w * (1 - 0.5) / (1 + 0.5) + (k % 5 - 2) * 1e-5 * w      # IoU within ~1e-5 of 0.5
+        adv += [[0.0, 10.0 * k, w, 10.0 * k + 5.0], [d, 10.0 * k, w + d, 10.0 * k + 5.0]]
+    adv = torch.tensor(adv, dtype=torch.float32)
+    asc = torch.rand(adv.shape[0], generator=g)
+    out.update(adv_boxes=adv.numpy(), adv_scores=asc.numpy(), adv_keep=R.boxes.nms(adv, asc, 0.5).numpy())
+    # --- MultiScaleRoIAlign, small channel count, 7x7 and 14x14
+    feats = [torch.randn(1, 8, 200 // 2 ** i, 336 // 2 ** i, generator=g) for i in range(4)]
+    from . import synth
+    rois = synth.roi_boxes(seed + 5, 120, (800, 1333))
+    fd = OrderedDict((str(i), f) for i, f in enumerate(feats))
+    for size in (7, 14):
+        m = MultiScaleRoIAlign(["0", "1", "2", "3"], size, 2)
+        out[f"roi_out{size}"] = m(fd, [rois], [(800, 1333)]).numpy()
+    out.update(roi_boxes=rois.numpy(), **{f"roi_feat{i}": f.numpy() for i, f in enumerate(feats)})
+    # --- M7 / M8 / M9
+    logits = torch.randn(12, 6, 28, 28, generator=g) * 3
+    labels = torch.randint(1, 6, (12,), generator=g)
+    out.update(inf_logits=logits.numpy(), inf_labels=labels.numpy(),
+               inf_out=R.roi_head.maskrcnn_inference(logits, [labels])[0].numpy())
+    pb = clustered_boxes(g, 24, extent=(500.0, 400.0), clusters=24)
+    pb[0] = torch.tensor([-3.2, -2.0, 40.5, 50.0])          # partly outside (top-left)
+    pb[1] = torch.tensor([500.0, 480.0, 560.0, 551.0])      # partly outside (bottom-right)
+    pb[2] = torch.tensor([100.2, 100.7, 100.9, 101.1])      # sub-pixel box -> 1x1 / 2x2 paste
+    probs = torch.rand(24, 1, 28, 28, generator=g)
+    out.update(paste_masks=probs.numpy(), paste_boxes=pb.numpy(),
+               paste_out=R.transform.paste_masks_in_image(probs, pb, (544, 544)).numpy(),
+               resize_out=R.transform.resize_boxes(pb, (800, 1216), (544, 544)).numpy())
+    _save(name, **out)
+
+
+def rpn_filter(name, seed, image_hw=(800, 1344), image_shape=(800, 1333)):
+    from . import synth
+    R = _ref()
+    anchors, deltas, logits, per_level = synth.rpn_heads(seed, image_hw)
+    coder = R.det_utils.BoxCoder((1.0, 1.0, 1.0, 1.0))
+    proposals = coder.decode_single(deltas, anchors)
+    stub = types.SimpleNamespace(min_size=1.0, score_thresh=0.0, nms_thresh=0.7,
+                                 pre_nms_top_n=lambda: 1000, post_nms_top_n=lambda: 1000)
+    stub._get_top_n_idx = functools.partial(R.rpn.RegionProposalNetwork._get_top_n_idx, stub)
+    boxes, scores = R.rpn.RegionProposalNetwork.filter_proposals(stub, proposals[None], logits[None], [image_shape], per_level)
+    _save(name, seed=seed, image_hw=np.array(image_hw), image_shape=np.array(image_shape),
+          input_digest=digest(anchors.numpy(), deltas.numpy(), logits.numpy()),
+          boxes=boxes[0].numpy(), scores=scores[0].numpy())
+
+
+def box_post(name, seed, num_classes=21, image_shape=(800, 1333)):
+    from . import synth
+    R = _ref()
+    proposals, logits, reg = synth.box_head_outputs(seed, 1000, num_classes, image_shape)
+    stub = types.SimpleNamespace(box_coder=R.det_utils.BoxCoder((10.0, 10.0, 5.0, 5.0)), score_thresh=0.05,
+                                 nms_thresh=0.5, detection_per_img=100)
+    b, s, l = R.roi_head.RoIHeads.postprocess_detections(stub, logits, reg, [proposals], [image_shape])
+    _save(name, seed=seed, num_classes=num_classes, image_shape=np.array(image_shape),
+          input_digest=digest(proposals.numpy(), logits.numpy(), reg.numpy()),
+          softmax=torch.softmax(logits, -1).numpy(), boxes=b[0].numpy(), scores=s[0].numpy(), labels=l[0].numpy())
+
+
+def roi_full(name, seed):
+    """Config-4 size: 256-channel FPN at 800x1344, 1000 RoIs 7x7 -> store 24 RoIs of the output."""
+    from torchvision.ops import MultiScaleRoIAlign
+    from . import synth
+    feats = synth.fpn_features(seed, 256)
+    rois = synth.roi_boxes(seed + 1, 1000)
+    fd = OrderedDict((str(i), f) for i, f in enumerate(feats))
+    out7 = MultiScaleRoIAlign(["0", "1", "2", "3"], 7, 2)(fd, [rois], [(800, 1333)])
+    out14 = MultiScaleRoIAlign(["0", "1", "2", "3"], 14, 2)(fd, [rois[:100]], [(800, 1333)])
+    pick = np.arange(0, 1000, 42)
+    _save(name, seed=seed, pick=pick, out7=out7[pick].numpy().astype(np.float16 if False else np.float32)[:, ::8],
+          out14=out14[::10, ::16].numpy(), sum7=float(out7.double().sum()), sum14=float(out14.double().sum()))
+
+
+def main():
+    stages("maskrcnn_stages", 31)
+    rpn_filter("maskrcnn_rpn_filter", 4001)
+    box_post("maskrcnn_box_post", 4101)
+    roi_full("maskrcnn_roi_full", 4201)
+
+
+if __name__ == "__main__":
+    main()

@@ -76,3 +76,88 @@ def verseg_boxes(seed, n=5000, num_coef=32):
     score = torch.rand(n, 1, generator=g) * 0.9 + 0.05
     coef = torch.tanh(torch.randn(n, num_coef, generator=g))
     return box.contiguous(), score.contiguous(), coef.contiguous()
+
+
+# --------------------------------------------------------------------------- Mask R-CNN side
+FPN_STRIDES = (4, 8, 16, 32, 64)
+
+
+def fpn_shapes(image_hw=(800, 1344), strides=FPN_STRIDES):
+    """Feature sizes of '0'..'3','pool' for a padded image (ceil division, as conv/pool strides give)."""
+    h, w = image_hw
+    out = []
+    for s in strides:
+        out.append((-(-h // s), -(-w // s)))
+    return out
+
+
+def rpn_anchors(image_hw=(800, 1344), sizes=(32, 64, 128, 256, 512), ratios=(0.5, 1.0, 2.0)):
+    """Plausible RPN anchor grid (level-major, cell-major, ratio-minor): [A,4] float32 corners and
+    anchors-per-level.  800x1344 gives 201600/50400/12600/3150/819 = 268569 anchors."""
+    per_level, out = [], []
+    for (fh, fw), stride, size in zip(fpn_shapes(image_hw), FPN_STRIDES, sizes):
+        r = torch.tensor(ratios)
+        hr = torch.sqrt(r)
+        ws, hs = size / hr, size * hr
+        base = torch.stack([-ws, -hs, ws, hs], 1) / 2
+        ys, xs = torch.meshgrid(torch.arange(fh) * stride, torch.arange(fw) * stride, indexing="ij")
+        shift = torch.stack([xs, ys, xs, ys], -1).reshape(-1, 1, 4).float()
+        a = (shift + base[None]).reshape(-1, 4)
+        out.append(a)
+        per_level.append(a.shape[0])
+    return torch.cat(out).contiguous(), per_level
+
+
+def rpn_heads(seed, image_hw=(800, 1344), objects=25):
+    """Synthetic RPN outputs for one image: anchors [A,4], deltas [A,4], objectness logits [A],
+    anchors_per_level.  Logits are noise around -4 with `objects` clusters of boosted anchors, so the
+    per-level top-1000 are spatially clustered and NMS has real work."""
+    g = torch.Generator().manual_seed(int(seed))
+    anchors, per_level = rpn_anchors(image_hw)
+    a = anchors.shape[0]
+    deltas = torch.randn(a, 4, generator=g) * torch.tensor([0.1, 0.1, 0.2, 0.2])
+    logits = torch.randn(a, generator=g) * 1.5 - 4.0
+    ctr = (anchors[:, :2] + anchors[:, 2:]) / 2
+    for _ in range(objects):
+        c = torch.rand(2, generator=g) * torch.tensor([float(image_hw[1]), float(image_hw[0])])
+        rad = float(torch.rand(1, generator=g)) * 120 + 30
+        near = ((ctr - c).abs().max(dim=1).values < rad)
+        logits[near] += torch.rand(int(near.sum()), generator=g) * 6.0 + 2.0
+    return anchors, deltas.contiguous(), logits.contiguous(), per_level
+
+
+def roi_boxes(seed, n, image_hw=(800, 1333)):
+    """n plausible proposal boxes inside the image, log-uniform sizes 8..700 px (all FPN levels)."""
+    g = torch.Generator().manual_seed(int(seed))
+    h, w = image_hw
+    ctr = torch.rand(n, 2, generator=g) * torch.tensor([float(w), float(h)])
+    size = torch.exp(torch.rand(n, 2, generator=g) * 4.5 + 2.0)
+    b = torch.cat([ctr - size / 2, ctr + size / 2], 1)
+    b[:, 0::2] = b[:, 0::2].clamp(0, w)
+    b[:, 1::2] = b[:, 1::2].clamp(0, h)
+    keep = ((b[:, 2] - b[:, 0]) >= 2) & ((b[:, 3] - b[:, 1]) >= 2)
+    b[~keep] = torch.tensor([10.0, 10.0, 60.0, 80.0])
+    return b.contiguous()
+
+
+def fpn_features(seed, channels=256, image_hw=(800, 1344), levels=4):
+    """Synthetic FPN maps '0'..'3': list of [1,C,H_l,W_l] float32."""
+    g = torch.Generator().manual_seed(int(seed))
+    return [torch.randn(1, channels, fh, fw, generator=g) for (fh, fw) in fpn_shapes(image_hw)[:levels]]
+
+
+def box_head_outputs(seed, n=1000, num_classes=21, image_hw=(800, 1333), hot=60):
+    """Synthetic box-head outputs: proposals [n,4], class_logits [n,C], box_regression [n,4C]."""
+    g = torch.Generator().manual_seed(int(seed))
+    proposals = roi_boxes(seed + 1, n, image_hw)
+    # clustered duplicates so per-class NMS suppresses
+    src = torch.randint(0, max(n // 8, 1), (n,), generator=g)
+    proposals = (proposals[src] + torch.randn(n, 4, generator=g) * 4.0)
+    proposals = torch.cat([torch.min(proposals[:, :2], proposals[:, 2:] - 2), proposals[:, 2:]], 1).contiguous()
+    logits = torch.randn(n, num_classes, generator=g)
+    logits[:, 0] += 3.0
+    rows = torch.randint(0, n, (hot * 4,), generator=g)
+    cls = torch.randint(1, num_classes, (hot * 4,), generator=g)
+    logits[rows, cls] += torch.rand(hot * 4, generator=g) * 6.0 + 2.0
+    reg = torch.randn(n, 4 * num_classes, generator=g) * torch.tensor([1.0, 1.0, 0.5, 0.5]).repeat(num_classes)
+    return proposals, logits.contiguous(), reg.contiguous()

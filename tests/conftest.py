@@ -24,14 +24,19 @@ def unpack_masks(g):
     return np.unpackbits(g["masks_packed"])[:n].reshape(shape).astype(bool)
 
 
-def assert_close_f32(actual, expected, tol=1e-5, what=""):
-    """|a-e| <= tol * max(|e|, 1): the 1e-5 relative bar with an absolute floor."""
+def assert_close_f32(actual, expected, tol=1e-5, what="", scale=None):
+    """|a-e| <= tol * max(|e|, 1[, scale]): the 1e-5 relative bar with an absolute floor.
+    `scale` (broadcastable) raises the floor where a result is a difference of large terms, e.g. a box
+    corner = centre - width/2: there the error is relative to the box extent, not to the corner value."""
     actual = np.asarray(actual, dtype=np.float64)
     expected = np.asarray(expected, dtype=np.float64)
     assert actual.shape == expected.shape, f"{what}: shape {actual.shape} vs {expected.shape}"
     if actual.size == 0:
         return
-    err = np.abs(actual - expected) / np.maximum(np.abs(expected), 1.0)
+    den = np.maximum(np.abs(expected), 1.0)
+    if scale is not None:
+        den = np.maximum(den, np.broadcast_to(np.asarray(scale, dtype=np.float64), den.shape))
+    err = np.abs(actual - expected) / den
     assert np.nanmax(err) <= tol, f"{what}: max scaled error {np.nanmax(err):.3e} > {tol}"
 
 
