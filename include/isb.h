@@ -152,6 +152,60 @@ ISB_API int isb_mask_assemble(isb_handle* h, const float* proto, const float* co
                       int32_t proto_w, int32_t m, int32_t out_h, int32_t out_w, int64_t* masks_arg, uint8_t* masks,
                       isb_stream stream);
 
+/* ------------------------------------------------------------------------------------
+ * Mask R-CNN side (inst_model/Mask_RCNN/net/network_files/...)
+ * ---------------------------------------------------------------------------------- */
+
+/* det_utils.py:224-267 BoxCoder.decode_single: rel_codes [n,4k], boxes [n,4] -> out [n,4k];
+ * weights (wx,wy,ww,wh) = (1,1,1,1) for the RPN (rpn_function.py:352), (10,10,5,5) for the box head
+ * (roi_head.py:187); clip = log(1000/16) (det_utils.py:146). */
+ISB_API int isb_box_decode(isb_handle* h, const float* rel_codes, const float* boxes, int64_t n, int32_t k, float wx, float wy,
+                   float ww, float wh, float clip, float* out, isb_stream stream);
+
+/* boxes.py:7-35 nms -> torch.ops.torchvision.nms: keep [n] int64 receives the kept indices in
+ * decreasing score order, *count (device int32) their number. */
+ISB_API int isb_nms(isb_handle* h, const float* boxes, const float* scores, int32_t n, double iou_threshold, int64_t* keep,
+            int32_t* count, isb_stream stream);
+
+/* boxes.py:38-83 batched_nms: idxs [n] int64 categories; coordinates are offset by
+ * idx * (boxes.max() + 1) in float32 before the IoU, exactly as the reference does. */
+ISB_API int isb_batched_nms(isb_handle* h, const float* boxes, const float* scores, const int64_t* idxs, int32_t n,
+                    double iou_threshold, int64_t* keep, int32_t* count, isb_stream stream);
+
+/* torchvision MultiScaleRoIAlign.forward (constructed at faster_rcnn_framework.py:326-329 and
+ * mask_rcnn.py:150, called at roi_head.py:491,540). */
+typedef struct {
+  int32_t num_levels;       /* 1..8 feature maps, finest first                              */
+  const float* feat[8];     /* [N,C,H_l,W_l] float32                                         */
+  int32_t feat_h[8];
+  int32_t feat_w[8];
+  float scale[8];           /* spatial scale of each level, 2^-k (poolers.py _infer_scale)   */
+  int32_t k_min, k_max;     /* LevelMapper bounds: -log2(scale[0]), -log2(scale[last])       */
+  int32_t canonical_scale;  /* 224 */
+  int32_t canonical_level;  /* 4   */
+  int32_t channels;
+  int32_t out_h, out_w;
+  int32_t sampling_ratio;   /* > 0 (the reference always passes 2)                            */
+} isb_roi_align_cfg;
+/* boxes [K,4] in image coordinates, batch_idx [K] int32 image index of each box (NULL = all 0),
+ * out [K,C,out_h,out_w]. */
+ISB_API int isb_ms_roi_align(isb_handle* h, const isb_roi_align_cfg* cfg, const float* boxes, const int32_t* batch_idx,
+                     int32_t num_rois, float* out, isb_stream stream);
+
+/* roi_head.py:59-91 maskrcnn_inference: logits [m,C,S,S], labels [m] int64 -> out [m,1,S,S] =
+ * sigmoid(logits[i, labels[i]]). */
+ISB_API int isb_mask_select_sigmoid(isb_handle* h, const float* logits, const int64_t* labels, int32_t m, int32_t num_classes,
+                            int32_t mask_size, float* out, isb_stream stream);
+
+/* transform.py:462-484 resize_boxes: boxes [m,4] scaled by new/orig per axis. */
+ISB_API int isb_resize_boxes(isb_handle* h, const float* boxes, int64_t m, int32_t orig_h, int32_t orig_w, int32_t new_h,
+                     int32_t new_w, float* out, isb_stream stream);
+
+/* transform.py:212-230 paste_masks_in_image: masks [m,1,S,S] probabilities, boxes [m,4] ->
+ * out float32 [m,1,im_h,im_w]. */
+ISB_API int isb_paste_masks(isb_handle* h, const float* masks, const float* boxes, int32_t m, int32_t mask_size,
+                    int32_t padding, int32_t im_h, int32_t im_w, float* out, isb_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -18,6 +18,8 @@ SYMBOLS = (
     "isb_profile_begin", "isb_profile_read",
     "isb_yolact_detect", "isb_yolact_detect_host", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
     "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_assemble",
+    "isb_box_decode", "isb_nms", "isb_batched_nms", "isb_ms_roi_align", "isb_mask_select_sigmoid", "isb_resize_boxes",
+    "isb_paste_masks",
 )
 
 
@@ -43,6 +45,13 @@ class YolactIn(C.Structure):
 class YolactOut(C.Structure):
     _fields_ = [("boxes", C.c_void_p), ("scores", C.c_void_p), ("class_ids", C.c_void_p), ("masks_arg", C.c_void_p),
                 ("masks", C.c_void_p), ("mask_slot_bytes", C.c_int64), ("counts", C.c_void_p)]
+
+
+class RoiAlignCfg(C.Structure):
+    _fields_ = [("num_levels", C.c_int32), ("feat", C.c_void_p * 8), ("feat_h", C.c_int32 * 8), ("feat_w", C.c_int32 * 8),
+                ("scale", C.c_float * 8), ("k_min", C.c_int32), ("k_max", C.c_int32), ("canonical_scale", C.c_int32),
+                ("canonical_level", C.c_int32), ("channels", C.c_int32), ("out_h", C.c_int32), ("out_w", C.c_int32),
+                ("sampling_ratio", C.c_int32)]
 
 
 _lib = None
@@ -82,6 +91,14 @@ def load():
         lib.isb_crop.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
         lib.isb_mask_logits.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
         lib.isb_mask_assemble.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp]
+        f64 = C.c_double
+        lib.isb_box_decode.argtypes = [vp, vp, vp, i64, i32, f32, f32, f32, f32, f32, vp, vp]
+        lib.isb_nms.argtypes = [vp, vp, vp, i32, f64, vp, vp, vp]
+        lib.isb_batched_nms.argtypes = [vp, vp, vp, vp, i32, f64, vp, vp, vp]
+        lib.isb_ms_roi_align.argtypes = [vp, C.POINTER(RoiAlignCfg), vp, vp, i32, vp, vp]
+        lib.isb_mask_select_sigmoid.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
+        lib.isb_resize_boxes.argtypes = [vp, vp, i64, i32, i32, i32, i32, vp, vp]
+        lib.isb_paste_masks.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]
         for name in SYMBOLS:
             fn = getattr(lib, name)
             if name not in ("isb_destroy", "isb_last_error", "isb_workspace_bytes", "isb_launch_count", "isb_version"):

@@ -77,6 +77,12 @@ static void free_ws(isb_handle* h) {
   cudaFree(h->det_coef);
   cudaFree(h->det_bounds);
   cudaFree(h->stage);
+  cudaFree(h->nms_keys);
+  cudaFree(h->nms_sbox);
+  cudaFree(h->nms_order);
+  cudaFree(h->nms_mask);
+  cudaFree(h->nms_scalars);
+  cudaFree(h->scratch);
 }
 
 extern "C" void isb_destroy(isb_handle* h) {
@@ -134,6 +140,7 @@ extern "C" int isb_create(int device, const isb_limits* limits, isb_handle** out
   if ((rc = configure_candidates(h)) != ISB_OK) return rc;
   if ((rc = configure_fast_nms(h)) != ISB_OK) return rc;
   if ((rc = configure_masks(h)) != ISB_OK) return rc;
+  if ((rc = configure_nms(h)) != ISB_OK) return rc;
   h->err[0] = 0;
   return ISB_OK;
 }
@@ -249,6 +256,12 @@ extern "C" int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, co
   if (need > h->stage_bytes) {
     ISB_CUDA(h, cudaStreamSynchronize(s));
     cudaFree(h->stage);
+  cudaFree(h->nms_keys);
+  cudaFree(h->nms_sbox);
+  cudaFree(h->nms_order);
+  cudaFree(h->nms_mask);
+  cudaFree(h->nms_scalars);
+  cudaFree(h->scratch);
     h->stage = nullptr;
     h->stage_bytes = 0;
     ISB_CUDA(h, cudaMalloc(&h->stage, need));

@@ -199,6 +199,16 @@ struct isb_handle {
   // device staging for the *_host entry points (allocated on first use)
   void* stage;
   size_t stage_bytes;
+  // Mask R-CNN side: NMS workspace, grown on demand (ensure_nms_ws)
+  int64_t nms_cap;         // boxes the arrays below hold
+  uint64_t* nms_keys;      // [pow2(nms_cap)]
+  float4* nms_sbox;        // [nms_cap]  boxes in score order (offset by class for batched NMS)
+  int32_t* nms_order;      // [nms_cap]  original index per sorted position
+  uint64_t* nms_mask;      // [nms_cap][ceil(nms_cap/64)] suppression bits
+  uint32_t* nms_scalars;   // [8] max-coordinate (orderable bits), counters
+  // generic scratch for the fused RPN / box-head pipelines (ensure_scratch)
+  void* scratch;
+  size_t scratch_bytes;
   // optional per-stage event ring (isb_profile_begin / isb_profile_read)
   cudaEvent_t* prof_events;  // [prof_cap][4]
   int32_t prof_cap, prof_used;
@@ -270,5 +280,44 @@ struct MaskParams {
   int64_t mask_slot_bytes;
 };
 int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s);
+
+struct RoiLevels {
+  const float* feat[8];
+  int h[8], w[8];
+  float scale[8];
+  int num_levels;
+  int k_min, k_max;
+  float canonical_scale, canonical_level, eps;
+};
+
+int launch_box_decode(isb_handle* h, const float* rel, const float* boxes, int64_t n, int k, const float w[4], float clip,
+                      float* out, cudaStream_t s);
+int launch_mask_select_sigmoid(isb_handle* h, const float* logits, const int64_t* labels, int m, int num_classes, int plane,
+                               float* out, cudaStream_t s);
+int launch_resize_boxes(isb_handle* h, const float* in, int64_t m, float rw, float rh, float* out, cudaStream_t s);
+int launch_paste_masks(isb_handle* h, const float* masks, const float* boxes, int m, int S, int pad, int im_h, int im_w,
+                       float* out, cudaStream_t s);
+int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, const int32_t* batch_idx, int num_rois,
+                        int channels, int oh, int ow, int sr, float* out, cudaStream_t s);
+int configure_nms(isb_handle* h);
+
+int launch_sort_u64(isb_handle* h, uint64_t* keys, int n_pow2, cudaStream_t s);
+int ensure_nms_ws(isb_handle* h, int64_t n);
+int ensure_scratch(isb_handle* h, size_t bytes);
+
+// Greedy NMS (torchvision semantics) over boxes/scores on the device.
+struct NmsCall {
+  const float4* boxes;     // [n]
+  const float* scores;     // [n]
+  const int64_t* idxs64;   // batched NMS categories as int64 (boxes.py:38) or nullptr
+  const int32_t* idxs32;   // ... or as int32 (internal pipelines) or nullptr
+  int32_t n_max;           // upper bound of n known on the host (sizes grids and workspace)
+  const int32_t* n_dev;    // actual n on the device, or nullptr when n == n_max
+  double iou_threshold;
+  int32_t max_keep;        // stop after this many kept boxes (<= 0: no limit)
+  int64_t* keep;           // [n_max] kept original indices, score-descending
+  int32_t* count;          // [1]
+};
+int launch_nms(isb_handle* h, const NmsCall& c, cudaStream_t s);
 
 }  // namespace isb

@@ -1,0 +1,259 @@
+// Greedy NMS with torchvision semantics, and the batched (per-category) form.
+//
+// Replaces boxes.py:7-35 `nms` (-> torch.ops.torchvision.nms) and boxes.py:38-83 `batched_nms`.
+// Semantics reproduced exactly (validated against the installed op, tests/golden/maskrcnn_stages):
+//   * boxes are visited by descending score, ties by ascending index (the op sorts stably);
+//   * a visited, unsuppressed box suppresses every later box with
+//       inter / ((area_i + area_j) - inter) > iou_threshold,   all in float32,
+//     the comparison being against the threshold as a DOUBLE (so the float threshold used here is the
+//     largest float <= the double);
+//   * batched_nms adds idx * (max_coordinate + 1) to every coordinate IN FLOAT32 before the IoU
+//     (boxes.py:74-81), which costs mantissa bits -- reproduced, not "fixed".
+//
+// Pipeline (all on the caller's stream, no host sync):
+//   keys (~score | index) -> bitonic sort -> gather boxes in score order (+offset) ->
+//   64x64-tiled upper-triangular suppression bitmask (shared-memory column tile, one 64-bit word per
+//   row and column block) -> single-CTA greedy scan over 64-box chunks (diagonal word resolved
+//   serially from shared memory, kept rows OR-ed into the removed bitmap in parallel) ->
+//   ordered compaction of the kept indices.
+#include <math.h>
+
+#include "isb_common.cuh"
+
+namespace isb {
+
+constexpr int kScanThreads = 1024;
+
+__global__ void nms_max_coord_kernel(const float4* __restrict__ boxes, int n_max, const int32_t* __restrict__ n_dev,
+                                     uint32_t* __restrict__ scalars) {
+  const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  float m = -INFINITY;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 b = boxes[i];
+    m = fmaxf(fmaxf(m, fmaxf(b.x, b.y)), fmaxf(b.z, b.w));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomicMin(&scalars[0], float_desc_bits(m));  // smaller desc-bits == larger float
+}
+
+__global__ void nms_keys_kernel(const float* __restrict__ scores, int n_max, const int32_t* __restrict__ n_dev,
+                                int n_pow2, uint64_t* __restrict__ keys) {
+  const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pow2; i += gridDim.x * blockDim.x)
+    keys[i] = i < n ? (((uint64_t)float_desc_bits(scores[i]) << 32) | (uint32_t)i) : kPadKey;
+}
+
+__global__ void nms_gather_kernel(const uint64_t* __restrict__ keys, const float4* __restrict__ boxes,
+                                  const int64_t* __restrict__ idxs64, const int32_t* __restrict__ idxs32, int n_max,
+                                  const int32_t* __restrict__ n_dev, const uint32_t* __restrict__ scalars,
+                                  float4* __restrict__ sbox, int32_t* __restrict__ order) {
+  const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  const bool batched = idxs64 || idxs32;
+  float step = 0.0f;
+  if (batched) step = float_from_desc_bits(scalars[0]) + 1.0f;  // boxes.py:78  (max_coordinate + 1)
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+    const int i = (int)(uint32_t)keys[p];
+    float4 b = boxes[i];
+    if (batched) {
+      const float off = (idxs64 ? (float)idxs64[i] : (float)idxs32[i]) * step;  // idxs.to(boxes) * (max + 1)
+      b.x += off; b.y += off; b.z += off; b.w += off;                          // boxes + offsets[:, None]
+    }
+    sbox[p] = b;
+    order[p] = i;
+  }
+}
+
+__device__ __forceinline__ float tv_iou(float4 a, float area_a, float4 b, float area_b) {
+  const float w = fmaxf(0.0f, fminf(a.z, b.z) - fmaxf(a.x, b.x));
+  const float hgt = fmaxf(0.0f, fminf(a.w, b.w) - fmaxf(a.y, b.y));
+  const float inter = w * hgt;
+  return inter / ((area_a + area_b) - inter);
+}
+
+// grid (col_block, row_block), 64 threads; only col_block >= row_block does work.
+__global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__ sbox, int n_max,
+                                                      const int32_t* __restrict__ n_dev, float thr, int words,
+                                                      uint64_t* __restrict__ mask) {
+  const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  const int rb = blockIdx.y, cb = blockIdx.x;
+  if (cb < rb || rb * 64 >= n || cb * 64 >= n) return;
+  __shared__ float4 cbox[64];
+  __shared__ float carea[64];
+  const int t = threadIdx.x;
+  const int cj = cb * 64 + t;
+  if (cj < n) {
+    cbox[t] = sbox[cj];
+    carea[t] = box_area(cbox[t]);
+  }
+  __syncthreads();
+  const int ri = rb * 64 + t;
+  if (ri >= n) return;
+  const float4 a = sbox[ri];
+  const float aa = box_area(a);
+  const int ncol = min(64, n - cb * 64);
+  uint64_t bits = 0;
+  const int j0 = (rb == cb) ? t + 1 : 0;
+  for (int j = j0; j < ncol; ++j)
+    if (tv_iou(a, aa, cbox[j], carea[j]) > thr) bits |= 1ull << j;
+  mask[(size_t)ri * words + cb] = bits;
+}
+
+// Single CTA: resolve the greedy chain chunk by chunk and compact the kept indices.
+__global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(const uint64_t* __restrict__ mask,
+                                                                const int32_t* __restrict__ order, int n_max,
+                                                                const int32_t* __restrict__ n_dev, int words, int max_keep,
+                                                                int64_t* __restrict__ keep, int32_t* __restrict__ count) {
+  extern __shared__ uint64_t s_dyn[];  // removed[words] | keptbits[words]
+  __shared__ uint64_t s_diag[64];
+  __shared__ uint64_t s_kept;
+  __shared__ int s_total;
+  __shared__ int s_stop;
+  const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  const int nwords = (n + 63) >> 6;
+  uint64_t* removed = s_dyn;
+  uint64_t* keptbits = s_dyn + words;
+  const int tid = threadIdx.x;
+  for (int w = tid; w < nwords; w += kScanThreads) { removed[w] = 0; keptbits[w] = 0; }
+  if (tid == 0) { s_total = 0; s_stop = 0; }
+  __syncthreads();
+  for (int c = 0; c < nwords; ++c) {
+    if (tid < 64) {
+      const int r = c * 64 + tid;
+      s_diag[tid] = r < n ? mask[(size_t)r * words + c] : 0ull;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      uint64_t cur = removed[c], kept = 0;
+      const int lim = min(64, n - c * 64);
+      int total = s_total;
+      for (int b = 0; b < lim; ++b) {
+        if (!((cur >> b) & 1ull)) {
+          kept |= 1ull << b;
+          cur |= s_diag[b];
+          if (max_keep > 0 && ++total >= max_keep) { s_stop = 1; break; }
+        }
+      }
+      if (max_keep <= 0) total += __popcll(kept);
+      s_total = total;
+      s_kept = kept;
+      keptbits[c] = kept;
+    }
+    __syncthreads();
+    if (s_stop) break;
+    const uint64_t kept = s_kept;
+    for (int w = c + 1 + tid; w < nwords; w += kScanThreads) {
+      uint64_t acc = 0, k = kept;
+      while (k) {
+        const int b = __ffsll((long long)k) - 1;
+        k &= k - 1;
+        acc |= mask[(size_t)(c * 64 + b) * words + w];
+      }
+      removed[w] |= acc;
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+  // ordered compaction: thread per word, serial prefix by thread 0 (nwords is small)
+  __shared__ int s_base[1];
+  if (tid == 0) {
+    int run = 0;
+    for (int w = 0; w < nwords; ++w) {
+      const int c = __popcll(keptbits[w]);
+      removed[w] = (uint64_t)run;  // reuse as prefix
+      run += c;
+    }
+    s_base[0] = run;
+    *count = run;
+  }
+  __syncthreads();
+  for (int w = tid; w < nwords; w += kScanThreads) {
+    uint64_t k = keptbits[w];
+    int pos = (int)removed[w];
+    while (k) {
+      const int b = __ffsll((long long)k) - 1;
+      k &= k - 1;
+      keep[pos++] = (int64_t)order[w * 64 + b];
+    }
+  }
+}
+
+static void free_nms_ws(isb_handle* h) {
+  cudaFree(h->nms_keys);
+  cudaFree(h->nms_sbox);
+  cudaFree(h->nms_order);
+  cudaFree(h->nms_mask);
+  h->nms_keys = nullptr; h->nms_sbox = nullptr; h->nms_order = nullptr; h->nms_mask = nullptr;
+  h->nms_cap = 0;
+}
+
+int ensure_nms_ws(isb_handle* h, int64_t n) {
+  if (!h->nms_scalars) ISB_CUDA(h, cudaMalloc((void**)&h->nms_scalars, 64));
+  if (n <= h->nms_cap) return ISB_OK;
+  if (n > (1 << 17)) ISB_FAIL(h, ISB_ERR_LIMIT, "nms over %lld boxes exceeds the 131072-box limit", (long long)n);
+  ISB_CUDA(h, cudaDeviceSynchronize());
+  free_nms_ws(h);
+  int64_t cap = 8192;
+  while (cap < n) cap <<= 1;
+  const int64_t words = (cap + 63) / 64;
+  ISB_CUDA(h, cudaMalloc((void**)&h->nms_keys, (size_t)cap * 8));
+  ISB_CUDA(h, cudaMalloc((void**)&h->nms_sbox, (size_t)cap * 16));
+  ISB_CUDA(h, cudaMalloc((void**)&h->nms_order, (size_t)cap * 4));
+  ISB_CUDA(h, cudaMalloc((void**)&h->nms_mask, (size_t)cap * words * 8));
+  h->nms_cap = cap;
+  h->ws_bytes += (size_t)cap * (28 + words * 8);
+  return ISB_OK;
+}
+
+int ensure_scratch(isb_handle* h, size_t bytes) {
+  if (bytes <= h->scratch_bytes) return ISB_OK;
+  ISB_CUDA(h, cudaDeviceSynchronize());
+  cudaFree(h->scratch);
+  h->scratch = nullptr;
+  h->scratch_bytes = 0;
+  ISB_CUDA(h, cudaMalloc(&h->scratch, bytes));
+  h->scratch_bytes = bytes;
+  return ISB_OK;
+}
+
+int configure_nms(isb_handle* h) {
+  ISB_CUDA(h, cudaFuncSetAttribute(nms_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  return ISB_OK;
+}
+
+int launch_nms(isb_handle* h, const NmsCall& c, cudaStream_t s) {
+  int rc = ensure_nms_ws(h, c.n_max);
+  if (rc != ISB_OK) return rc;
+  if (c.n_max == 0) {
+    ISB_CUDA(h, cudaMemsetAsync(c.count, 0, sizeof(int32_t), s));
+    return ISB_OK;
+  }
+  const int n = c.n_max;
+  const int n_pow2 = next_pow2(n);
+  const int words = (n + 63) / 64;
+  // largest float <= the double threshold: (double)ovr > thr  <=>  ovr > thr_f for float ovr
+  float thr_f = (float)c.iou_threshold;
+  if ((double)thr_f > c.iou_threshold) thr_f = nextafterf(thr_f, -INFINITY);
+  const bool batched = c.idxs64 || c.idxs32;
+  const int blocks = (n + 255) / 256 < 4 * h->num_sms ? (n + 255) / 256 : 4 * h->num_sms;
+  if (batched) {
+    ISB_CUDA(h, cudaMemsetAsync(h->nms_scalars, 0xff, sizeof(uint32_t), s));
+    nms_max_coord_kernel<<<blocks, 256, 0, s>>>(c.boxes, n, c.n_dev, h->nms_scalars);
+    ISB_LAUNCH_CHECK(h, "nms_max_coord_kernel");
+  }
+  nms_keys_kernel<<<(n_pow2 + 255) / 256, 256, 0, s>>>(c.scores, n, c.n_dev, n_pow2, h->nms_keys);
+  ISB_LAUNCH_CHECK(h, "nms_keys_kernel");
+  if ((rc = launch_sort_u64(h, h->nms_keys, n_pow2, s)) != ISB_OK) return rc;
+  nms_gather_kernel<<<blocks, 256, 0, s>>>(h->nms_keys, c.boxes, c.idxs64, c.idxs32, n, c.n_dev, h->nms_scalars,
+                                           h->nms_sbox, h->nms_order);
+  ISB_LAUNCH_CHECK(h, "nms_gather_kernel");
+  nms_mask_kernel<<<dim3(words, words), 64, 0, s>>>(h->nms_sbox, n, c.n_dev, thr_f, words, h->nms_mask);
+  ISB_LAUNCH_CHECK(h, "nms_mask_kernel");
+  const size_t smem = (size_t)words * 16;
+  if (smem > 64 * 1024) ISB_FAIL(h, ISB_ERR_LIMIT, "nms scan shared memory");
+  nms_scan_kernel<<<1, kScanThreads, smem, s>>>(h->nms_mask, h->nms_order, n, c.n_dev, words, c.max_keep, c.keep, c.count);
+  ISB_LAUNCH_CHECK(h, "nms_scan_kernel");
+  return ISB_OK;
+}
+
+}  // namespace isb

@@ -1,0 +1,175 @@
+"""Drop-ins for the Mask R-CNN post-processing functions of the reference
+(inst_model/Mask_RCNN/net/network_files/...): same names, argument order and return types; the work
+is done by libisb.so on the tensors' CUDA device and current stream.
+
+    nms, batched_nms                  boxes.py:7, :38
+    decode_single                     det_utils.py:224  (BoxCoder.decode_single)
+    MultiScaleRoIAlign                torchvision module constructed at faster_rcnn_framework.py:326, mask_rcnn.py:150
+    maskrcnn_inference                roi_head.py:59
+    resize_boxes, paste_masks_in_image  transform.py:462, :212
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+import torch
+import torchvision
+
+from . import _lib
+from ._lib import RoiAlignCfg, get_handle
+from .yolact import _cuda_f32, _ptr, _stream
+
+BBOX_XFORM_CLIP = math.log(1000.0 / 16)  # det_utils.py:146
+
+
+def _call(dev, fn):
+    h = get_handle(dev.index)
+    with torch.cuda.device(dev):
+        h.check(fn(h))
+
+
+# ---------------------------------------------------------------------------- boxes.py
+def nms(boxes, scores, iou_threshold):
+    """boxes.py:7-35: int64 indices of kept boxes, in decreasing order of score."""
+    boxes = _cuda_f32(boxes, "boxes")
+    scores = _cuda_f32(scores, "scores").to(boxes.device)
+    dev, n = boxes.device, boxes.shape[0]
+    keep = torch.empty((max(n, 1),), dtype=torch.int64, device=dev)
+    count = torch.zeros((1,), dtype=torch.int32, device=dev)
+    _call(dev, lambda h: h.lib.isb_nms(h.ptr, _ptr(boxes), _ptr(scores), n, float(iou_threshold), _ptr(keep), _ptr(count),
+                                       _stream(dev)))
+    return keep[: int(count.item())]
+
+
+def batched_nms(boxes, scores, idxs, iou_threshold):
+    """boxes.py:38-83: NMS per category via the reference's float32 coordinate-offset trick."""
+    boxes = _cuda_f32(boxes, "boxes")
+    dev = boxes.device
+    if boxes.numel() == 0:  # boxes.py:66-67
+        return torch.empty((0,), dtype=torch.int64, device=dev)
+    scores = _cuda_f32(scores, "scores").to(dev)
+    idxs = idxs.to(device=dev, dtype=torch.int64).contiguous()
+    n = boxes.shape[0]
+    keep = torch.empty((n,), dtype=torch.int64, device=dev)
+    count = torch.zeros((1,), dtype=torch.int32, device=dev)
+    _call(dev, lambda h: h.lib.isb_batched_nms(h.ptr, _ptr(boxes), _ptr(scores), _ptr(idxs), n, float(iou_threshold),
+                                               _ptr(keep), _ptr(count), _stream(dev)))
+    return keep[: int(count.item())]
+
+
+# ---------------------------------------------------------------------------- det_utils.py
+def decode_single(rel_codes, boxes, weights=(1.0, 1.0, 1.0, 1.0), bbox_xform_clip=BBOX_XFORM_CLIP):
+    """det_utils.py:224-267 `BoxCoder.decode_single`: rel_codes [N,4k], boxes [N,4] -> [N,4k]."""
+    rel = _cuda_f32(rel_codes, "rel_codes")
+    dev = rel.device
+    boxes = _cuda_f32(boxes, "boxes").to(dev)
+    n, k = rel.shape[0], rel.shape[1] // 4
+    out = torch.empty_like(rel)
+    wx, wy, ww, wh = [float(w) for w in weights]
+    _call(dev, lambda h: h.lib.isb_box_decode(h.ptr, _ptr(rel), _ptr(boxes), n, k, wx, wy, ww, wh, float(bbox_xform_clip),
+                                              _ptr(out), _stream(dev)))
+    return out
+
+
+class BoxCoder(object):
+    """Inference half of det_utils.py:140-267 (decode / decode_single); encode is training-only."""
+
+    def __init__(self, weights, bbox_xform_clip=BBOX_XFORM_CLIP):
+        self.weights = weights
+        self.bbox_xform_clip = bbox_xform_clip
+
+    def decode_single(self, rel_codes, boxes):
+        return decode_single(rel_codes, boxes.to(rel_codes.dtype), self.weights, self.bbox_xform_clip)
+
+    def decode(self, rel_codes, boxes):
+        assert isinstance(boxes, (list, tuple))
+        assert isinstance(rel_codes, torch.Tensor)
+        concat = torch.cat(boxes, dim=0)
+        box_sum = concat.shape[0]
+        pred = self.decode_single(rel_codes, concat)
+        if box_sum > 0:
+            pred = pred.reshape(box_sum, -1, 4)
+        return pred
+
+
+# ---------------------------------------------------------------------------- MultiScaleRoIAlign
+def _infer_scale(feat_h, image_h):
+    # poolers.py `_infer_scale`: 2 ** round(log2(feat / img)), float32 log2 as torch.tensor(...).log2()
+    approx = float(feat_h) / float(image_h)
+    return 2.0 ** float(np.round(np.log2(np.float32(approx))))
+
+
+class MultiScaleRoIAlign(torchvision.ops.MultiScaleRoIAlign):
+    """Same constructor and forward signature as torchvision's module (it subclasses it so that the
+    reference's isinstance checks at faster_rcnn_framework.py:282 / mask_rcnn.py:138 pass); forward runs
+    the level mapping, sampling and scatter in one CUDA kernel."""
+
+    def forward(self, x, boxes, image_shapes):
+        feats = [v for k, v in x.items() if k in self.featmap_names]
+        feats = [_cuda_f32(f, "feature map") for f in feats]
+        dev = feats[0].device
+        if self.scales is None:
+            max_h = max(s[0] for s in image_shapes)
+            self.scales = [_infer_scale(f.shape[-2], max_h) for f in feats]
+            self._k_min = int(-np.log2(np.float32(self.scales[0])))
+            self._k_max = int(-np.log2(np.float32(self.scales[-1])))
+        concat = _cuda_f32(torch.cat(boxes, dim=0), "boxes").to(dev)
+        k = concat.shape[0]
+        batch_idx = None
+        if len(boxes) > 1:
+            batch_idx = torch.cat([torch.full((b.shape[0],), i, dtype=torch.int32, device=dev) for i, b in enumerate(boxes)])
+        c = feats[0].shape[1]
+        oh, ow = self.output_size
+        out = torch.empty((k, c, oh, ow), dtype=torch.float32, device=dev)
+        cfg = RoiAlignCfg()
+        cfg.num_levels = len(feats)
+        for i, f in enumerate(feats):
+            cfg.feat[i] = f.data_ptr()
+            cfg.feat_h[i], cfg.feat_w[i] = f.shape[-2], f.shape[-1]
+            cfg.scale[i] = self.scales[i]
+        cfg.k_min, cfg.k_max = self._k_min, self._k_max
+        cfg.canonical_scale, cfg.canonical_level = int(self.canonical_scale), int(self.canonical_level)
+        cfg.channels, cfg.out_h, cfg.out_w, cfg.sampling_ratio = c, oh, ow, int(self.sampling_ratio)
+        bptr = _ptr(batch_idx) if batch_idx is not None else C.c_void_p(0)
+        _call(dev, lambda h: h.lib.isb_ms_roi_align(h.ptr, C.byref(cfg), _ptr(concat), bptr, k, _ptr(out), _stream(dev)))
+        return out
+
+
+# ---------------------------------------------------------------------------- roi_head.py
+def maskrcnn_inference(x, labels):
+    """roi_head.py:59-91: x [m,C,S,S] mask logits, labels list of int64 tensors -> list of [m_i,1,S,S]."""
+    x = _cuda_f32(x, "mask logits")
+    dev = x.device
+    boxes_per_image = [label.shape[0] for label in labels]
+    lab = torch.cat(labels).to(device=dev, dtype=torch.int64).contiguous()
+    m, c, s = x.shape[0], x.shape[1], x.shape[-1]
+    out = torch.empty((m, 1, s, s), dtype=torch.float32, device=dev)
+    _call(dev, lambda h: h.lib.isb_mask_select_sigmoid(h.ptr, _ptr(x), _ptr(lab), m, c, s, _ptr(out), _stream(dev)))
+    return out.split(boxes_per_image, dim=0)
+
+
+# ---------------------------------------------------------------------------- transform.py
+def resize_boxes(boxes, original_size, new_size):
+    """transform.py:462-484."""
+    boxes = _cuda_f32(boxes, "boxes")
+    dev = boxes.device
+    out = torch.empty_like(boxes)
+    _call(dev, lambda h: h.lib.isb_resize_boxes(h.ptr, _ptr(boxes), boxes.shape[0], int(original_size[0]), int(original_size[1]),
+                                                int(new_size[0]), int(new_size[1]), _ptr(out), _stream(dev)))
+    return out
+
+
+def paste_masks_in_image(masks, boxes, img_shape, padding=1):
+    """transform.py:212-230: masks [m,1,S,S] probabilities, boxes [m,4] -> float32 [m,1,H,W]."""
+    masks = _cuda_f32(masks, "masks")
+    dev = masks.device
+    boxes = _cuda_f32(boxes, "boxes").to(dev)
+    im_h, im_w = int(img_shape[0]), int(img_shape[1])
+    m, s = masks.shape[0], masks.shape[-1]
+    out = torch.empty((m, 1, im_h, im_w), dtype=torch.float32, device=dev)
+    if m > 0:
+        _call(dev, lambda h: h.lib.isb_paste_masks(h.ptr, _ptr(masks), _ptr(boxes), m, s, int(padding), im_h, im_w, _ptr(out),
+                                                   _stream(dev)))
+    return out
