@@ -206,6 +206,28 @@ ISB_API int isb_resize_boxes(isb_handle* h, const float* boxes, int64_t m, int32
 ISB_API int isb_paste_masks(isb_handle* h, const float* masks, const float* boxes, int32_t m, int32_t mask_size,
                     int32_t padding, int32_t im_h, int32_t im_w, float* out, isb_stream stream);
 
+/* rpn_function.py:434-458 _get_top_n_idx + :460-529 filter_proposals, for ONE image:
+ * proposals [A,4] (already decoded, rpn_function.py:624), objectness [A] logits, anchors_per_level
+ * (HOST array of num_levels ints).  Per-level top pre_nms_top_n by logit, sigmoid, clip to the image,
+ * drop boxes with a side < min_size and scores < score_thresh, batched NMS per level, keep
+ * post_nms_top_n.  out_boxes [post,4], out_scores [post], *out_count (device int32). */
+ISB_API int isb_rpn_filter(isb_handle* h, const float* proposals, const float* objectness, const int32_t* anchors_per_level,
+                   int32_t num_levels, int32_t img_h, int32_t img_w, int32_t pre_nms_top_n, int32_t post_nms_top_n,
+                   double nms_thresh, float score_thresh, float min_size, float* out_boxes, float* out_scores,
+                   int32_t* out_count, isb_stream stream);
+
+/* roi_head.py:366-457 postprocess_detections for ONE image: class_logits [R,C] (softmax applied here,
+ * :401) OR class_probs [R,C] already softmaxed (pass the other as NULL), box_regression [R,4C],
+ * proposals [R,4].  Decode (weights wx..wh, clip), clip to the image, drop background, score >
+ * score_thresh, drop boxes with a side < 1, batched NMS per class, keep detections_per_img.
+ * out_boxes [D,4], out_scores [D], out_labels [D] int64, *out_count (device int32; -1 if class_probs
+ * rows do not sum to 1 and the candidate bound R*floor(1/score_thresh) was exceeded). */
+ISB_API int isb_box_postprocess(isb_handle* h, const float* class_logits, const float* class_probs, const float* box_regression,
+                        const float* proposals, int32_t num_rois, int32_t num_classes, int32_t img_h, int32_t img_w,
+                        float wx, float wy, float ww, float wh, float clip, float score_thresh, double nms_thresh,
+                        int32_t detections_per_img, float* out_boxes, float* out_scores, int64_t* out_labels,
+                        int32_t* out_count, isb_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,377 @@
+// Fused Mask R-CNN proposal / detection filters, one image per call, no host synchronisation:
+//   isb_rpn_filter       = RegionProposalNetwork._get_top_n_idx + filter_proposals
+//                          (rpn_function.py:434-458, :460-529)
+//   isb_box_postprocess  = RoIHeads.postprocess_detections (roi_head.py:366-457)
+// Both end in the batched NMS of nms.cu with a device-side box count.
+#include <math.h>
+
+#include "isb_common.cuh"
+
+namespace isb {
+
+struct LevelOffsets { int start[9]; int num_levels; };
+
+// ---- RPN: keys (level | ~logit | anchor) for the per-level top-k (rpn_function.py:447-456) ----
+__global__ void rpn_keys_kernel(const float* __restrict__ objectness, LevelOffsets lv, int n, int n_pow2,
+                                uint64_t* __restrict__ keys) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pow2; i += gridDim.x * blockDim.x) {
+    uint64_t k = kPadKey;
+    if (i < n) {
+      int l = 0;
+      while (l + 1 < lv.num_levels && i >= lv.start[l + 1]) ++l;
+      k = make_cand_key((uint32_t)l, objectness[i], (uint32_t)i);
+    }
+    keys[i] = k;
+  }
+}
+
+__device__ __forceinline__ int lower_bound_u64(const uint64_t* __restrict__ keys, int n, uint64_t v) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (keys[mid] < v) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+__device__ __forceinline__ float4 clip_box(float4 b, float wf, float hf) {
+  // boxes.py:108-138: x to [0, W], y to [0, H]
+  b.x = fminf(fmaxf(b.x, 0.0f), wf);
+  b.z = fminf(fmaxf(b.z, 0.0f), wf);
+  b.y = fminf(fmaxf(b.y, 0.0f), hf);
+  b.w = fminf(fmaxf(b.w, 0.0f), hf);
+  return b;
+}
+
+// Single CTA: walk the levels' top-k in order, clip, drop small / low-score boxes, compact in order.
+__global__ void __launch_bounds__(1024) rpn_select_kernel(const uint64_t* __restrict__ keys, int n_pow2,
+                                                          const float4* __restrict__ proposals, int num_levels,
+                                                          int pre_top_n, float img_w, float img_h, float min_size,
+                                                          float score_thresh, float4* __restrict__ cbox,
+                                                          float* __restrict__ cscore, int32_t* __restrict__ clvl,
+                                                          int32_t* __restrict__ n_out) {
+  __shared__ int s_wcount[32];
+  __shared__ int s_base;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_base = 0;
+  __syncthreads();
+  for (int l = 0; l < num_levels; ++l) {
+    const int start = lower_bound_u64(keys, n_pow2, (uint64_t)l << (32 + kRowBits));
+    const int end = lower_bound_u64(keys, n_pow2, (uint64_t)(l + 1) << (32 + kRowBits));
+    const int k = min(pre_top_n, end - start);
+    for (int r0 = 0; r0 < k; r0 += 1024) {
+      const int r = r0 + tid;
+      bool ok = false;
+      float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+      float sc = 0.f;
+      if (r < k) {
+        const uint64_t key = keys[start + r];
+        b = clip_box(proposals[cand_row(key)], img_w, img_h);                       // :509
+        sc = sigmoidf_ref(float_from_desc_bits(cand_score_bits(key)));              // :502
+        ok = (b.z - b.x >= min_size) && (b.w - b.y >= min_size) && (sc >= score_thresh);  // :512, :517
+      }
+      const unsigned bal = __ballot_sync(0xffffffffu, ok);
+      if (lane == 0) s_wcount[warp] = __popc(bal);
+      __syncthreads();
+      int off = s_base, tot = 0;
+#pragma unroll
+      for (int w = 0; w < 32; ++w) {
+        const int c = s_wcount[w];
+        if (w < warp) off += c;
+        tot += c;
+      }
+      if (ok) {
+        const int slot = off + __popc(bal & ((1u << lane) - 1u));
+        cbox[slot] = b;
+        cscore[slot] = sc;
+        clvl[slot] = l;
+      }
+      __syncthreads();
+      if (tid == 0) s_base += tot;
+      __syncthreads();
+    }
+  }
+  if (tid == 0) *n_out = s_base;
+}
+
+__global__ void rpn_gather_kernel(const int64_t* __restrict__ keep, const int32_t* __restrict__ count,
+                                  const float4* __restrict__ cbox, const float* __restrict__ cscore, int max_out,
+                                  float4* __restrict__ out_boxes, float* __restrict__ out_scores,
+                                  int32_t* __restrict__ out_count) {
+  const int n = min(*count, max_out);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int64_t k = keep[i];
+    out_boxes[i] = cbox[k];
+    out_scores[i] = cscore[k];
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) *out_count = n;
+}
+
+// ---- box head: one warp per proposal row ----------------------------------------------------
+__device__ __forceinline__ float4 rcnn_decode_one(float4 rel, float4 b, float wx, float wy, float ww, float wh, float clip) {
+  const float width = b.z - b.x, height = b.w - b.y;
+  const float ctr_x = b.x + 0.5f * width, ctr_y = b.y + 0.5f * height;
+  const float dx = rel.x / wx, dy = rel.y / wy;
+  const float dw = fminf(rel.z / ww, clip), dh = fminf(rel.w / wh, clip);
+  const float pcx = dx * width + ctr_x, pcy = dy * height + ctr_y;
+  const float pw = expf(dw) * width, ph = expf(dh) * height;
+  return make_float4(pcx - 0.5f * pw, pcy - 0.5f * ph, pcx + 0.5f * pw, pcy + 0.5f * ph);
+}
+
+struct BoxPostParams {
+  const float* logits;   // [R, C] or nullptr
+  const float* probs;    // [R, C] softmaxed, or nullptr (then logits are softmaxed here, roi_head.py:401)
+  const float4* reg;     // [R, C] float4
+  const float4* proposals;  // [R]
+  int R, C;
+  float wx, wy, ww, wh, clip, img_w, img_h, score_thresh;
+};
+
+// pass 0: count candidates per row (row_count); pass 1: write them at row_offset in class order.
+template <int PASS>
+__global__ void __launch_bounds__(256) boxpost_rows_kernel(BoxPostParams p, int32_t* __restrict__ row_count,
+                                                           const int32_t* __restrict__ row_offset, int n_cap,
+                                                           float4* __restrict__ cbox, float* __restrict__ cscore,
+                                                           int32_t* __restrict__ clabel) {
+  const int lane = threadIdx.x & 31;
+  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= p.R) return;
+  float mx = -INFINITY, sum = 0.0f;
+  if (!p.probs) {
+    for (int c = lane; c < p.C; c += 32) mx = fmaxf(mx, p.logits[(size_t)r * p.C + c]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    for (int c = lane; c < p.C; c += 32) sum += expf(p.logits[(size_t)r * p.C + c] - mx);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  }
+  const float4 prop = p.proposals[r];
+  int written = 0;
+  const int base = PASS ? row_offset[r] : 0;
+  for (int c0 = 1; c0 < p.C; c0 += 32) {   // background class 0 dropped (roi_head.py:423-425)
+    const int c = c0 + lane;
+    bool ok = false;
+    float sc = 0.f;
+    float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < p.C) {
+      sc = p.probs ? p.probs[(size_t)r * p.C + c] : expf(p.logits[(size_t)r * p.C + c] - mx) / sum;
+      if (sc > p.score_thresh) {                                                         // :437
+        b = clip_box(rcnn_decode_one(p.reg[(size_t)r * p.C + c], prop, p.wx, p.wy, p.ww, p.wh, p.clip), p.img_w, p.img_h);
+        ok = (b.z - b.x >= 1.0f) && (b.w - b.y >= 1.0f);                                 // :442 min_size = 1
+      }
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, ok);
+    if (PASS && ok) {
+      const int slot = base + written + __popc(bal & ((1u << lane) - 1u));
+      if (slot < n_cap) {
+        cbox[slot] = b;
+        cscore[slot] = sc;
+        clabel[slot] = c;
+      }
+    }
+    written += __popc(bal);
+  }
+  if (!PASS && lane == 0) row_count[r] = written;
+}
+
+// single CTA exclusive scan of the row counts; total (clamped to n_cap) -> n_out, overflow flag -> n_out[1]
+__global__ void __launch_bounds__(1024) boxpost_scan_kernel(const int32_t* __restrict__ row_count, int R, int n_cap,
+                                                            int32_t* __restrict__ row_offset, int32_t* __restrict__ n_out) {
+  __shared__ int s_w[32];
+  __shared__ int s_run;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_run = 0;
+  __syncthreads();
+  for (int r0 = 0; r0 < R; r0 += 1024) {
+    const int r = r0 + tid;
+    const int v = r < R ? row_count[r] : 0;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_w[warp] = incl;
+    __syncthreads();
+    int woff = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < 32; ++w) {
+      const int c = s_w[w];
+      if (w < warp) woff += c;
+      tot += c;
+    }
+    if (r < R) row_offset[r] = s_run + woff + incl - v;
+    __syncthreads();
+    if (tid == 0) s_run += tot;
+    __syncthreads();
+  }
+  if (tid == 0) {
+    n_out[0] = min(s_run, n_cap);
+    n_out[1] = s_run > n_cap ? 1 : 0;
+  }
+}
+
+__global__ void boxpost_gather_kernel(const int64_t* __restrict__ keep, const int32_t* __restrict__ count,
+                                      const int32_t* __restrict__ overflow, const float4* __restrict__ cbox,
+                                      const float* __restrict__ cscore, const int32_t* __restrict__ clabel, int max_out,
+                                      float4* __restrict__ out_boxes, float* __restrict__ out_scores,
+                                      int64_t* __restrict__ out_labels, int32_t* __restrict__ out_count) {
+  const int n = min(*count, max_out);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int64_t k = keep[i];
+    out_boxes[i] = cbox[k];
+    out_scores[i] = cscore[k];
+    out_labels[i] = (int64_t)clabel[k];
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) *out_count = *overflow ? -1 : n;
+}
+
+static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+}  // namespace isb
+
+using namespace isb;
+
+extern "C" int isb_rpn_filter(isb_handle* h, const float* proposals, const float* objectness,
+                              const int32_t* anchors_per_level, int32_t num_levels, int32_t img_h, int32_t img_w,
+                              int32_t pre_nms_top_n, int32_t post_nms_top_n, double nms_thresh, float score_thresh,
+                              float min_size, float* out_boxes, float* out_scores, int32_t* out_count, isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (!proposals || !objectness || !anchors_per_level || !out_boxes || !out_scores || !out_count)
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "rpn_filter: null pointer");
+  if (num_levels < 1 || num_levels > 8 || pre_nms_top_n <= 0 || post_nms_top_n <= 0)
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "rpn_filter: 1..8 levels and positive top-n required");
+  if ((reinterpret_cast<uintptr_t>(proposals) & 15) || (reinterpret_cast<uintptr_t>(out_boxes) & 15))
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "rpn_filter: proposals / out_boxes must be 16-byte aligned");
+  LevelOffsets lv;
+  memset(&lv, 0, sizeof(lv));
+  lv.num_levels = num_levels;
+  int64_t total = 0, cand_max = 0;
+  for (int l = 0; l < num_levels; ++l) {
+    if (anchors_per_level[l] < 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "rpn_filter: negative level size");
+    lv.start[l] = (int)total;
+    total += anchors_per_level[l];
+    cand_max += anchors_per_level[l] < pre_nms_top_n ? anchors_per_level[l] : pre_nms_top_n;
+  }
+  lv.start[num_levels] = (int)total;
+  if (total > (1 << kRowBits)) ISB_FAIL(h, ISB_ERR_LIMIT, "rpn_filter: %lld anchors > 2^%d", (long long)total, kRowBits);
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (total == 0) {
+    ISB_CUDA(h, cudaMemsetAsync(out_count, 0, sizeof(int32_t), s));
+    return ISB_OK;
+  }
+  const int n = (int)total, n_pow2 = next_pow2(n), cmax = (int)cand_max;
+  const size_t b_keys = up256((size_t)n_pow2 * 8), b_box = up256((size_t)cmax * 16), b_sc = up256((size_t)cmax * 4),
+               b_lvl = up256((size_t)cmax * 4), b_keep = up256((size_t)cmax * 8);
+  int rc = ensure_scratch(h, b_keys + b_box + b_sc + b_lvl + b_keep + 512);
+  if (rc != ISB_OK) return rc;
+  if ((rc = ensure_nms_ws(h, cmax)) != ISB_OK) return rc;
+  char* p = static_cast<char*>(h->scratch);
+  uint64_t* keys = (uint64_t*)p;  p += b_keys;
+  float4* cbox = (float4*)p;      p += b_box;
+  float* cscore = (float*)p;      p += b_sc;
+  int32_t* clvl = (int32_t*)p;    p += b_lvl;
+  int64_t* keep = (int64_t*)p;    p += b_keep;
+  int32_t* n_dev = (int32_t*)p;   // [0] candidates, [2] kept count
+  const int blocks = (n_pow2 + 255) / 256 < 8 * h->num_sms ? (n_pow2 + 255) / 256 : 8 * h->num_sms;
+  rpn_keys_kernel<<<blocks, 256, 0, s>>>(objectness, lv, n, n_pow2, keys);
+  ISB_LAUNCH_CHECK(h, "rpn_keys_kernel");
+  if ((rc = launch_sort_u64(h, keys, n_pow2, s)) != ISB_OK) return rc;
+  rpn_select_kernel<<<1, 1024, 0, s>>>(keys, n_pow2, reinterpret_cast<const float4*>(proposals), num_levels, pre_nms_top_n,
+                                       (float)img_w, (float)img_h, min_size, score_thresh, cbox, cscore, clvl, n_dev);
+  ISB_LAUNCH_CHECK(h, "rpn_select_kernel");
+  NmsCall c;
+  memset(&c, 0, sizeof(c));
+  c.boxes = cbox;
+  c.scores = cscore;
+  c.idxs32 = clvl;
+  c.n_max = cmax;
+  c.n_dev = n_dev;
+  c.iou_threshold = nms_thresh;
+  c.max_keep = post_nms_top_n;
+  c.keep = keep;
+  c.count = n_dev + 2;
+  if ((rc = launch_nms(h, c, s)) != ISB_OK) return rc;
+  rpn_gather_kernel<<<8, 256, 0, s>>>(keep, n_dev + 2, cbox, cscore, post_nms_top_n, reinterpret_cast<float4*>(out_boxes),
+                                      out_scores, out_count);
+  ISB_LAUNCH_CHECK(h, "rpn_gather_kernel");
+  return ISB_OK;
+}
+
+extern "C" int isb_box_postprocess(isb_handle* h, const float* class_logits, const float* class_probs,
+                                   const float* box_regression, const float* proposals, int32_t num_rois,
+                                   int32_t num_classes, int32_t img_h, int32_t img_w, float wx, float wy, float ww,
+                                   float wh, float clip, float score_thresh, double nms_thresh, int32_t detections_per_img,
+                                   float* out_boxes, float* out_scores, int64_t* out_labels, int32_t* out_count,
+                                   isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if ((!class_logits && !class_probs) || !box_regression || !proposals || !out_boxes || !out_scores || !out_labels ||
+      !out_count)
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "box_postprocess: null pointer");
+  if (num_rois < 0 || num_classes < 2 || detections_per_img <= 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "box_postprocess: bad size");
+  if ((reinterpret_cast<uintptr_t>(box_regression) & 15) || (reinterpret_cast<uintptr_t>(proposals) & 15) ||
+      (reinterpret_cast<uintptr_t>(out_boxes) & 15))
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "box_postprocess: box_regression / proposals / out_boxes must be 16-byte aligned");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (num_rois == 0) {
+    ISB_CUDA(h, cudaMemsetAsync(out_count, 0, sizeof(int32_t), s));
+    return ISB_OK;
+  }
+  // probabilities of one row sum to 1, so fewer than 1/thresh classes can exceed the threshold
+  int per_row = num_classes - 1;
+  if (score_thresh > 0.0f) {
+    const int lim = (int)floorf(1.0f / score_thresh);
+    if (lim < per_row) per_row = lim > 1 ? lim : 1;
+  }
+  const int64_t cap64 = (int64_t)num_rois * per_row;
+  if (cap64 > (1 << 17)) ISB_FAIL(h, ISB_ERR_LIMIT, "box_postprocess: up to %lld candidates exceed the NMS limit", (long long)cap64);
+  const int n_cap = (int)cap64;
+  const size_t b_cnt = up256((size_t)num_rois * 4), b_box = up256((size_t)n_cap * 16), b_sc = up256((size_t)n_cap * 4),
+               b_keep = up256((size_t)n_cap * 8);
+  int rc = ensure_scratch(h, 2 * b_cnt + b_box + 2 * b_sc + b_keep + 512);
+  if (rc != ISB_OK) return rc;
+  if ((rc = ensure_nms_ws(h, n_cap)) != ISB_OK) return rc;
+  char* p = static_cast<char*>(h->scratch);
+  int32_t* row_count = (int32_t*)p;   p += b_cnt;
+  int32_t* row_offset = (int32_t*)p;  p += b_cnt;
+  float4* cbox = (float4*)p;          p += b_box;
+  float* cscore = (float*)p;          p += b_sc;
+  int32_t* clabel = (int32_t*)p;      p += b_sc;
+  int64_t* keep = (int64_t*)p;        p += b_keep;
+  int32_t* n_dev = (int32_t*)p;       // [0] candidates, [1] overflow, [2] kept count
+  BoxPostParams bp;
+  bp.logits = class_probs ? nullptr : class_logits;
+  bp.probs = class_probs;
+  bp.reg = reinterpret_cast<const float4*>(box_regression);
+  bp.proposals = reinterpret_cast<const float4*>(proposals);
+  bp.R = num_rois;
+  bp.C = num_classes;
+  bp.wx = wx; bp.wy = wy; bp.ww = ww; bp.wh = wh; bp.clip = clip;
+  bp.img_w = (float)img_w; bp.img_h = (float)img_h;
+  bp.score_thresh = score_thresh;
+  const int row_blocks = (num_rois + 7) / 8;
+  boxpost_rows_kernel<0><<<row_blocks, 256, 0, s>>>(bp, row_count, nullptr, n_cap, nullptr, nullptr, nullptr);
+  ISB_LAUNCH_CHECK(h, "boxpost_rows_kernel<0>");
+  boxpost_scan_kernel<<<1, 1024, 0, s>>>(row_count, num_rois, n_cap, row_offset, n_dev);
+  ISB_LAUNCH_CHECK(h, "boxpost_scan_kernel");
+  boxpost_rows_kernel<1><<<row_blocks, 256, 0, s>>>(bp, nullptr, row_offset, n_cap, cbox, cscore, clabel);
+  ISB_LAUNCH_CHECK(h, "boxpost_rows_kernel<1>");
+  NmsCall c;
+  memset(&c, 0, sizeof(c));
+  c.boxes = cbox;
+  c.scores = cscore;
+  c.idxs32 = clabel;
+  c.n_max = n_cap;
+  c.n_dev = n_dev;
+  c.iou_threshold = nms_thresh;
+  c.max_keep = detections_per_img;
+  c.keep = keep;
+  c.count = n_dev + 2;
+  if ((rc = launch_nms(h, c, s)) != ISB_OK) return rc;
+  boxpost_gather_kernel<<<4, 256, 0, s>>>(keep, n_dev + 2, n_dev + 1, cbox, cscore, clabel, detections_per_img,
+                                          reinterpret_cast<float4*>(out_boxes), out_scores, out_labels, out_count);
+  ISB_LAUNCH_CHECK(h, "boxpost_gather_kernel");
+  return ISB_OK;
+}

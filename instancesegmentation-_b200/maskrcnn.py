@@ -94,6 +94,58 @@ class BoxCoder(object):
         return pred
 
 
+# ---------------------------------------------------------------------------- rpn_function.py
+def filter_proposals(proposals, objectness, image_shape, num_anchors_per_level, pre_nms_top_n=1000, post_nms_top_n=1000,
+                     nms_thresh=0.7, score_thresh=0.0, min_size=1.0):
+    """rpn_function.py:460-529 (+ _get_top_n_idx :434) for one image: proposals [A,4] decoded boxes,
+    objectness [A] logits.  Returns (boxes [k,4], scores [k]).  Defaults: faster_rcnn_framework.py:261-270."""
+    proposals = _cuda_f32(proposals, "proposals").reshape(-1, 4)
+    dev = proposals.device
+    objectness = _cuda_f32(objectness, "objectness").to(dev).reshape(-1)
+    levels = (C.c_int32 * len(num_anchors_per_level))(*[int(v) for v in num_anchors_per_level])
+    post = int(post_nms_top_n)
+    out_b = torch.empty((post, 4), dtype=torch.float32, device=dev)
+    out_s = torch.empty((post,), dtype=torch.float32, device=dev)
+    count = torch.zeros((1,), dtype=torch.int32, device=dev)
+    _call(dev, lambda h: h.lib.isb_rpn_filter(h.ptr, _ptr(proposals), _ptr(objectness), levels, len(num_anchors_per_level),
+                                              int(image_shape[0]), int(image_shape[1]), int(pre_nms_top_n), post,
+                                              float(nms_thresh), float(score_thresh), float(min_size), _ptr(out_b),
+                                              _ptr(out_s), _ptr(count), _stream(dev)))
+    k = int(count.item())
+    return out_b[:k], out_s[:k]
+
+
+# ---------------------------------------------------------------------------- roi_head.py
+def postprocess_detections(class_logits, box_regression, proposals, image_shape, weights=(10.0, 10.0, 5.0, 5.0),
+                           score_thresh=0.05, nms_thresh=0.5, detections_per_img=100, bbox_xform_clip=BBOX_XFORM_CLIP,
+                           class_probs=None):
+    """roi_head.py:366-457 for one image.  Returns (boxes [k,4], scores [k], labels int64 [k]).
+    `class_probs` (softmaxed scores) may be given instead of logits."""
+    reg = _cuda_f32(box_regression, "box_regression")
+    dev = reg.device
+    props = _cuda_f32(proposals, "proposals").to(dev)
+    logits = _cuda_f32(class_logits, "class_logits").to(dev) if class_probs is None else None
+    probs = _cuda_f32(class_probs, "class_probs").to(dev) if class_probs is not None else None
+    r = props.shape[0]
+    c = (probs if probs is not None else logits).shape[-1]
+    d = int(detections_per_img)
+    out_b = torch.empty((d, 4), dtype=torch.float32, device=dev)
+    out_s = torch.empty((d,), dtype=torch.float32, device=dev)
+    out_l = torch.empty((d,), dtype=torch.int64, device=dev)
+    count = torch.zeros((1,), dtype=torch.int32, device=dev)
+    null = C.c_void_p(0)
+    wx, wy, ww, wh = [float(w) for w in weights]
+    _call(dev, lambda h: h.lib.isb_box_postprocess(h.ptr, _ptr(logits) if logits is not None else null,
+                                                   _ptr(probs) if probs is not None else null, _ptr(reg), _ptr(props), r, c,
+                                                   int(image_shape[0]), int(image_shape[1]), wx, wy, ww, wh,
+                                                   float(bbox_xform_clip), float(score_thresh), float(nms_thresh), d,
+                                                   _ptr(out_b), _ptr(out_s), _ptr(out_l), _ptr(count), _stream(dev)))
+    k = int(count.item())
+    if k < 0:
+        raise RuntimeError("postprocess_detections: class_probs rows exceed the candidate bound (do they sum to 1?)")
+    return out_b[:k], out_s[:k], out_l[:k]
+
+
 # ---------------------------------------------------------------------------- MultiScaleRoIAlign
 def _infer_scale(feat_h, image_h):
     # poolers.py `_infer_scale`: 2 ** round(log2(feat / img)), float32 log2 as torch.tensor(...).log2()

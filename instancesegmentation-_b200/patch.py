@@ -1,0 +1,77 @@
+"""Install the B200 drop-ins into the reference's modules without editing the reference tree.
+
+    import sys; sys.path.insert(0, "/path/to/InstanceSegmentation-")
+    import isb.patch; isb.patch.install()
+    # eval.py / predict.py now run the CUDA post-processing path
+
+What is rebound:
+  inst_model.yolact.yolact.BBoxUtility                      -> isb.yolact.BBoxUtility   (yolact.py:81,158,240,272)
+  ...network_files.boxes.nms / batched_nms                  -> isb.maskrcnn.*           (rpn_function.py:521, roi_head.py:446)
+  ...network_files.transform.paste_masks_in_image / resize_boxes -> isb.maskrcnn.*      (transform.py:410,415)
+  ...network_files.roi_head.maskrcnn_inference              -> isb.maskrcnn.maskrcnn_inference (roi_head.py:555)
+  torchvision MultiScaleRoIAlign instances of a built model -> isb.maskrcnn.MultiScaleRoIAlign (swap_roi_pools)
+"""
+from __future__ import annotations
+
+import importlib
+
+from . import maskrcnn, yolact
+
+_REBIND = [
+    ("inst_model.yolact.yolact", "BBoxUtility", lambda: yolact.BBoxUtility),
+    ("inst_model.Mask_RCNN.net.network_files.boxes", "nms", lambda: maskrcnn.nms),
+    ("inst_model.Mask_RCNN.net.network_files.boxes", "batched_nms", lambda: maskrcnn.batched_nms),
+    ("inst_model.Mask_RCNN.net.network_files.transform", "paste_masks_in_image", lambda: maskrcnn.paste_masks_in_image),
+    ("inst_model.Mask_RCNN.net.network_files.transform", "resize_boxes", lambda: maskrcnn.resize_boxes),
+    ("inst_model.Mask_RCNN.net.network_files.roi_head", "maskrcnn_inference", lambda: maskrcnn.maskrcnn_inference),
+]
+
+
+def install(only=None, strict=False):
+    """Rebind the reference's names to the drop-ins.  Returns the list of (module, name) rebound.
+    Modules that cannot be imported (missing optional dependencies such as cv2) are skipped unless
+    `strict`."""
+    done = []
+    for mod_name, attr, getter in _REBIND:
+        if only is not None and attr not in only:
+            continue
+        try:
+            mod = importlib.import_module(mod_name)
+        except Exception:
+            if strict:
+                raise
+            continue
+        if not hasattr(mod, "_isb_original"):
+            mod._isb_original = {}
+        mod._isb_original.setdefault(attr, getattr(mod, attr))
+        setattr(mod, attr, getter())
+        done.append((mod_name, attr))
+    return done
+
+
+def uninstall():
+    for mod_name, attr, _ in _REBIND:
+        try:
+            mod = importlib.import_module(mod_name)
+        except Exception:
+            continue
+        orig = getattr(mod, "_isb_original", {})
+        if attr in orig:
+            setattr(mod, attr, orig.pop(attr))
+
+
+def swap_roi_pools(model):
+    """Replace the torchvision MultiScaleRoIAlign modules of a built Mask R-CNN (roi_heads.box_roi_pool,
+    roi_heads.mask_roi_pool; faster_rcnn_framework.py:326-329, mask_rcnn.py:150) by the CUDA drop-in,
+    keeping their configuration."""
+    import torchvision
+    swapped = []
+    for name in ("box_roi_pool", "mask_roi_pool"):
+        heads = getattr(model, "roi_heads", None)
+        pool = getattr(heads, name, None)
+        if isinstance(pool, torchvision.ops.MultiScaleRoIAlign) and not isinstance(pool, maskrcnn.MultiScaleRoIAlign):
+            new = maskrcnn.MultiScaleRoIAlign(pool.featmap_names, pool.output_size, pool.sampling_ratio,
+                                              canonical_scale=pool.canonical_scale, canonical_level=pool.canonical_level)
+            setattr(heads, name, new)
+            swapped.append(name)
+    return swapped
