@@ -69,6 +69,11 @@ extern "C" int isb_profile_read(isb_handle* h, double stage_ms[3], int32_t* call
 
 static void free_ws(isb_handle* h) {
   free_profile(h);
+  for (int l = 0; l < 3; ++l) {
+    if (h->lane_stream[l]) cudaStreamDestroy(h->lane_stream[l]);
+    if (h->lane_event[l]) cudaEventDestroy(h->lane_event[l]);
+  }
+  if (h->fork_event) cudaEventDestroy(h->fork_event);
   cudaFree(h->cand_count);
   cudaFree(h->work_counter);
   cudaFree(h->cand_keys);
@@ -141,6 +146,7 @@ extern "C" int isb_create(int device, const isb_limits* limits, isb_handle** out
   if ((rc = configure_fast_nms(h)) != ISB_OK) return rc;
   if ((rc = configure_masks(h)) != ISB_OK) return rc;
   if ((rc = configure_nms(h)) != ISB_OK) return rc;
+  if ((rc = configure_mask_gemm_tc(h)) != ISB_OK) return rc;
   h->err[0] = 0;
   return ISB_OK;
 }
@@ -210,8 +216,8 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const is
   memset(&mp, 0, sizeof(mp));
   mp.batch = in->batch;
   mp.proto = in->proto;
-  mp.coef = h->det_coef;
-  mp.bounds = h->det_bounds;
+  mp.coef = h->det_coef + (size_t)h->ws_b0 * h->lim.max_det * ISB_NUM_COEF;
+  mp.bounds = h->det_bounds + (size_t)h->ws_b0 * h->lim.max_det;
   mp.counts = out->counts;
   mp.m_fixed = -1;
   mp.det_stride = h->lim.max_det;
@@ -256,12 +262,6 @@ extern "C" int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, co
   if (need > h->stage_bytes) {
     ISB_CUDA(h, cudaStreamSynchronize(s));
     cudaFree(h->stage);
-  cudaFree(h->nms_keys);
-  cudaFree(h->nms_sbox);
-  cudaFree(h->nms_order);
-  cudaFree(h->nms_mask);
-  cudaFree(h->nms_scalars);
-  cudaFree(h->scratch);
     h->stage = nullptr;
     h->stage_bytes = 0;
     ISB_CUDA(h, cudaMalloc(&h->stage, need));
@@ -282,28 +282,77 @@ extern "C" int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, co
   dout.masks_arg = (int64_t*)take(o_arg);
   dout.masks = (uint8_t*)take(o_mask);
   dout.counts = (int32_t*)take(o_cnt);
-  ISB_CUDA(h, cudaMemcpyAsync((void*)din.box, in->box, n_box, cudaMemcpyHostToDevice, s));
-  ISB_CUDA(h, cudaMemcpyAsync((void*)din.conf, in->conf, n_conf, cudaMemcpyHostToDevice, s));
-  ISB_CUDA(h, cudaMemcpyAsync((void*)din.coef, in->coef, n_coef, cudaMemcpyHostToDevice, s));
-  ISB_CUDA(h, cudaMemcpyAsync((void*)din.proto, in->proto, n_proto, cudaMemcpyHostToDevice, s));
+  // Sub-batch pipeline over kLanes streams: while chunk c computes and streams its masks to the host, chunk
+  // c+1 is already uploading (PCIe is full duplex) -- H2D, kernels and D2H of different chunks overlap.
+  constexpr int kLanes = 3;
+  for (int l = 0; l < kLanes; ++l) {
+    if (!h->lane_stream[l]) ISB_CUDA(h, cudaStreamCreateWithFlags(&h->lane_stream[l], cudaStreamNonBlocking));
+    if (!h->lane_event[l]) ISB_CUDA(h, cudaEventCreateWithFlags(&h->lane_event[l], cudaEventDisableTiming));
+  }
+  if (!h->fork_event) ISB_CUDA(h, cudaEventCreateWithFlags(&h->fork_event, cudaEventDisableTiming));
   ISB_CUDA(h, cudaMemcpyAsync((void*)din.anchors, in->anchors, n_anc, cudaMemcpyHostToDevice, s));
-  rc = yolact_detect_device(h, &din, &dout, s);
-  if (rc != ISB_OK) return rc;
-  ISB_CUDA(h, cudaMemcpyAsync(out->counts, dout.counts, o_cnt, cudaMemcpyDeviceToHost, s));
-  ISB_CUDA(h, cudaMemcpyAsync(out->boxes, dout.boxes, o_box, cudaMemcpyDeviceToHost, s));
-  ISB_CUDA(h, cudaMemcpyAsync(out->scores, dout.scores, o_score, cudaMemcpyDeviceToHost, s));
-  ISB_CUDA(h, cudaMemcpyAsync(out->class_ids, dout.class_ids, o_cls, cudaMemcpyDeviceToHost, s));
-  ISB_CUDA(h, cudaMemcpyAsync(out->masks_arg, dout.masks_arg, o_arg, cudaMemcpyDeviceToHost, s));
-  ISB_CUDA(h, cudaStreamSynchronize(s));  // counts are needed to size the mask copies
+  ISB_CUDA(h, cudaEventRecord(h->fork_event, s));
+  for (int l = 0; l < kLanes; ++l) ISB_CUDA(h, cudaStreamWaitEvent(h->lane_stream[l], h->fork_event, 0));
+  const int chunk = (int)(B >= 24 ? 8 : (B + kLanes - 1) / kLanes);
+  const int nchunks = (int)((B + chunk - 1) / chunk);
+  const size_t slot = (size_t)out->mask_slot_bytes, PP = (size_t)in->proto_h * in->proto_w * K;
   bool overflow = false;
-  for (size_t b = 0; b < B; ++b) {
-    const int m = out->counts[b];
-    if (m < 0) { overflow = true; continue; }
-    if (m == 0) continue;
-    ISB_CUDA(h, cudaMemcpyAsync(out->masks + b * (size_t)out->mask_slot_bytes, dout.masks + b * (size_t)out->mask_slot_bytes,
-                                HW * (size_t)m, cudaMemcpyDeviceToHost, s));
+  auto finalize = [&](int c) -> int {  // chunk c's counts are on the host: size and enqueue its mask copies
+    const int lane = c % kLanes;
+    ISB_CUDA(h, cudaEventSynchronize(h->lane_event[lane]));
+    const size_t b0 = (size_t)c * chunk, b1 = b0 + chunk < B ? b0 + chunk : B;
+    for (size_t b = b0; b < b1; ++b) {
+      const int m = out->counts[b];
+      if (m < 0) { overflow = true; continue; }
+      if (m == 0) continue;
+      ISB_CUDA(h, cudaMemcpyAsync(out->masks + b * slot, dout.masks + b * slot, HW * (size_t)m, cudaMemcpyDeviceToHost,
+                                  h->lane_stream[lane]));
+    }
+    return ISB_OK;
+  };
+  rc = ISB_OK;
+  for (int c = 0; c < nchunks && rc == ISB_OK; ++c) {
+    const int lane = c % kLanes;
+    cudaStream_t st = h->lane_stream[lane];
+    const size_t b0 = (size_t)c * chunk, nb = (b0 + chunk < B ? b0 + chunk : B) - b0;
+    ISB_CUDA(h, cudaMemcpyAsync((char*)din.box + b0 * A * 16, (const char*)in->box + b0 * A * 16, nb * A * 16, cudaMemcpyHostToDevice, st));
+    ISB_CUDA(h, cudaMemcpyAsync((char*)din.conf + b0 * A * C * 4, (const char*)in->conf + b0 * A * C * 4, nb * A * C * 4, cudaMemcpyHostToDevice, st));
+    ISB_CUDA(h, cudaMemcpyAsync((char*)din.coef + b0 * A * K * 4, (const char*)in->coef + b0 * A * K * 4, nb * A * K * 4, cudaMemcpyHostToDevice, st));
+    ISB_CUDA(h, cudaMemcpyAsync((char*)din.proto + b0 * PP * 4, (const char*)in->proto + b0 * PP * 4, nb * PP * 4, cudaMemcpyHostToDevice, st));
+    isb_yolact_in cin = din;
+    isb_yolact_out cout = dout;
+    cin.batch = (int32_t)nb;
+    cin.box = din.box + b0 * A * 4;
+    cin.conf = din.conf + b0 * A * C;
+    cin.coef = din.coef + b0 * A * K;
+    cin.proto = din.proto + b0 * PP;
+    cout.boxes = dout.boxes + b0 * D * 4;
+    cout.scores = dout.scores + b0 * D;
+    cout.class_ids = dout.class_ids + b0 * D;
+    cout.masks_arg = dout.masks_arg + b0 * HW;
+    cout.masks = dout.masks + b0 * slot;
+    cout.counts = dout.counts + b0;
+    h->ws_b0 = (int32_t)b0;
+    h->ws_lane = lane;
+    rc = yolact_detect_device(h, &cin, &cout, st);
+    h->ws_b0 = 0;
+    h->ws_lane = 0;
+    if (rc != ISB_OK) break;
+    ISB_CUDA(h, cudaMemcpyAsync(out->counts + b0, cout.counts, nb * 4, cudaMemcpyDeviceToHost, st));
+    ISB_CUDA(h, cudaEventRecord(h->lane_event[lane], st));
+    ISB_CUDA(h, cudaMemcpyAsync(out->boxes + b0 * D * 4, cout.boxes, nb * D * 16, cudaMemcpyDeviceToHost, st));
+    ISB_CUDA(h, cudaMemcpyAsync(out->scores + b0 * D, cout.scores, nb * D * 4, cudaMemcpyDeviceToHost, st));
+    ISB_CUDA(h, cudaMemcpyAsync(out->class_ids + b0 * D, cout.class_ids, nb * D * 8, cudaMemcpyDeviceToHost, st));
+    ISB_CUDA(h, cudaMemcpyAsync(out->masks_arg + b0 * HW, cout.masks_arg, nb * HW * 8, cudaMemcpyDeviceToHost, st));
+    if (c >= kLanes - 1) rc = finalize(c - (kLanes - 1));
+  }
+  for (int c = nchunks - (kLanes - 1) > 0 ? nchunks - (kLanes - 1) : 0; c < nchunks && rc == ISB_OK; ++c) rc = finalize(c);
+  for (int l = 0; l < kLanes; ++l) {  // join (also on the error path, so the lanes are idle when we return)
+    cudaEventRecord(h->lane_event[l], h->lane_stream[l]);
+    cudaStreamWaitEvent(s, h->lane_event[l], 0);
   }
   ISB_CUDA(h, cudaStreamSynchronize(s));
+  if (rc != ISB_OK) return rc;
   if (overflow) ISB_FAIL(h, ISB_ERR_OVERFLOW, "candidate buffer overflow: raise isb_limits.cand_capacity (now %lld)", (long long)h->lim.cand_capacity);
   return ISB_OK;
 }
@@ -406,7 +455,7 @@ extern "C" int isb_mask_logits(isb_handle* h, const float* proto, const float* c
   if ((int64_t)proto_h * proto_w * m == 0) return ISB_OK;
   if (!proto || !coef || !out || !aligned16(proto) || !aligned16(coef)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_logits: null or misaligned pointer");
   ISB_CUDA(h, cudaSetDevice(h->device));
-  return launch_mask_logits(h, proto, coef, (int64_t)proto_h * proto_w, m, out, (cudaStream_t)stream);
+  return launch_mask_logits_tc(h, proto, coef, (int64_t)proto_h * proto_w, m, out, (cudaStream_t)stream);
 }
 
 extern "C" int isb_mask_assemble(isb_handle* h, const float* proto, const float* coef, const float* boxes_px,

@@ -199,6 +199,12 @@ struct isb_handle {
   // device staging for the *_host entry points (allocated on first use)
   void* stage;
   size_t stage_bytes;
+  // sub-batch pipelining (isb_yolact_detect_host): image offset into the per-image workspace arrays and
+  // the lane whose work counter / stream the next launches use
+  int32_t ws_b0, ws_lane;
+  cudaStream_t lane_stream[3];
+  cudaEvent_t lane_event[3];
+  cudaEvent_t fork_event;
   // Mask R-CNN side: NMS workspace, grown on demand (ensure_nms_ws)
   int64_t nms_cap;         // boxes the arrays below hold
   uint64_t* nms_keys;      // [pow2(nms_cap)]
@@ -300,6 +306,9 @@ int launch_paste_masks(isb_handle* h, const float* masks, const float* boxes, in
 int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, const int32_t* batch_idx, int num_rois,
                         int channels, int oh, int ow, int sr, float* out, cudaStream_t s);
 int configure_nms(isb_handle* h);
+int configure_mask_gemm_tc(isb_handle* h);
+int launch_mask_logits_tc(isb_handle* h, const float* proto, const float* coef, int64_t npix, int m, float* out,
+                          cudaStream_t s);
 
 int launch_sort_u64(isb_handle* h, uint64_t* keys, int n_pow2, cudaStream_t s);
 int ensure_nms_ws(isb_handle* h, int64_t n);

@@ -100,9 +100,10 @@ int launch_candidates(isb_handle* h, const CandParams& p, cudaStream_t s) {
   // tile bytes + 16 of alignment head + 16 of round-up slack
   const size_t smem = (size_t)p.ncols * 4 * kCandThreads + 32;
   if (smem > kCandSmemMax) ISB_FAIL(h, ISB_ERR_LIMIT, "score rows of %d columns do not fit the candidate tile", p.ncols);
-  ISB_CUDA(h, cudaMemsetAsync(h->cand_count, 0, sizeof(int32_t) * p.batch, s));
+  ISB_CUDA(h, cudaMemsetAsync(h->cand_count + h->ws_b0, 0, sizeof(int32_t) * p.batch, s));
   dim3 grid((p.rows + kCandThreads - 1) / kCandThreads, p.batch);
-  candidates_kernel<<<grid, kCandThreads, smem, s>>>(p, h->cand_count, h->cand_keys, h->lim.cand_capacity,
+  candidates_kernel<<<grid, kCandThreads, smem, s>>>(p, h->cand_count + h->ws_b0, h->cand_keys + (size_t)h->ws_b0 * h->cand_cap_pow2,
+                                                     h->lim.cand_capacity,
                                                      h->cand_cap_pow2);
   ISB_LAUNCH_CHECK(h, "candidates_kernel");
   return ISB_OK;

@@ -300,8 +300,9 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   if (per_sm > 4) per_sm = 4;
   int64_t grid = (int64_t)h->num_sms * per_sm;
   if (grid > total_units) grid = total_units;
-  ISB_CUDA(h, cudaMemsetAsync(h->work_counter, 0, sizeof(int), s));
-  mask_assemble_kernel<<<(unsigned)grid, kMaskThreads, L.total, s>>>(p, g, h->work_counter);
+  int* counter = h->work_counter + h->ws_lane;
+  ISB_CUDA(h, cudaMemsetAsync(counter, 0, sizeof(int), s));
+  mask_assemble_kernel<<<(unsigned)grid, kMaskThreads, L.total, s>>>(p, g, counter);
   ISB_LAUNCH_CHECK(h, "mask_assemble_kernel");
   return ISB_OK;
 }

@@ -168,9 +168,11 @@ int configure_fast_nms(isb_handle* h) {
 }
 
 int launch_fast_nms(isb_handle* h, const NmsParams& p, cudaStream_t s) {
-  fast_nms_kernel<<<p.batch, kNmsThreads, kNmsSmem, s>>>(p, h->cand_count, h->cand_keys, h->det_keys, h->cand_box,
-                                                         h->lim.cand_capacity, h->cand_cap_pow2, h->det_coef,
-                                                         h->det_bounds, h->lim.max_det);
+  const size_t b0 = (size_t)h->ws_b0, cap2 = (size_t)h->cand_cap_pow2;
+  fast_nms_kernel<<<p.batch, kNmsThreads, kNmsSmem, s>>>(
+      p, h->cand_count + b0, h->cand_keys + b0 * cap2, h->det_keys + b0 * cap2, h->cand_box + b0 * cap2,
+      h->lim.cand_capacity, h->cand_cap_pow2, h->det_coef + b0 * h->lim.max_det * ISB_NUM_COEF,
+      h->det_bounds + b0 * h->lim.max_det, h->lim.max_det);
   ISB_LAUNCH_CHECK(h, "fast_nms_kernel");
   return ISB_OK;
 }

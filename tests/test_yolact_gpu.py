@@ -220,3 +220,46 @@ def test_benchmark_size_properties(bu):
         assert ((argh >= 0) & (argh < m)).all()
         cy, cx = np.nonzero(mkh.any(axis=2))
         assert mkh[cy, cx, argh[cy, cx]].all()            # the arg-max detection is > 0.5 wherever any is
+
+
+@pytest.mark.parametrize("bsz", [1, 7, 26])
+def test_detect_host_matches_device(bu, bsz):
+    """isb_yolact_detect_host (pinned host buffers, 3-lane H2D/compute/D2H pipeline) == device path."""
+    import ctypes as C
+    from isb import _lib
+    g = load_golden("yolact_tiny_a")
+    gen = torch.Generator().manual_seed(bsz)
+    a, c = g["conf"].shape
+    ph, pw, k = g["proto"].shape
+    box = torch.from_numpy(g["box"])[None].repeat(bsz, 1, 1) + torch.randn(bsz, a, 4, generator=gen) * 0.05
+    conf = torch.from_numpy(g["conf"])[None].repeat(bsz, 1, 1) * (torch.rand(bsz, a, 1, generator=gen) * 0.5 + 0.5)
+    coef = torch.from_numpy(g["coef"])[None].repeat(bsz, 1, 1)
+    proto = torch.from_numpy(g["proto"])[None].repeat(bsz, 1, 1, 1) + torch.rand(bsz, ph, pw, k, generator=gen) * 0.1
+    if bsz > 2:
+        conf[2] = 0.0                              # an image with no detections
+    anchors = torch.from_numpy(g["anchors"])
+    hgt, wid = int(g["image_shape"][0]), int(g["image_shape"][1])
+    d = 100
+    ref = bu.decode_nms_batch((box.cuda(), conf.cuda(), coef.cuda(), proto.cuda()), anchors.cuda(), 0.05, 0.5, (hgt, wid))
+    torch.cuda.synchronize()
+    slot = (hgt * wid * d + 15) // 16 * 16
+    pin = [t.contiguous().pin_memory() for t in (box, conf, coef, proto, anchors)]
+    hb, hs = torch.zeros((bsz, d, 4)).pin_memory(), torch.zeros((bsz, d)).pin_memory()
+    hc = torch.zeros((bsz, d), dtype=torch.int64).pin_memory()
+    ha = torch.zeros((bsz, hgt, wid), dtype=torch.int64).pin_memory()
+    hm = torch.zeros((bsz, slot), dtype=torch.uint8).pin_memory()
+    hn = torch.zeros((bsz,), dtype=torch.int32).pin_memory()
+    h = _lib.get_handle(0, max_batch=bsz, max_anchors=a, max_classes=c - 1)
+    yin = _lib.YolactIn(bsz, a, c, k, ph, pw, hgt, wid, pin[0].data_ptr(), pin[1].data_ptr(), pin[2].data_ptr(),
+                        pin[3].data_ptr(), pin[4].data_ptr(), 0.05, 0.5, 200, d)
+    yout = _lib.YolactOut(hb.data_ptr(), hs.data_ptr(), hc.data_ptr(), ha.data_ptr(), hm.data_ptr(), slot, hn.data_ptr())
+    h.check(h.lib.isb_yolact_detect_host(h.ptr, C.byref(yin), C.byref(yout), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    counts = ref.counts.cpu()
+    assert torch.equal(hn, counts)
+    for b in range(bsz):
+        m = int(counts[b])
+        if m == 0:
+            continue
+        assert torch.equal(hb[b, :m], ref.boxes[b, :m].cpu()) and torch.equal(hs[b, :m], ref.scores[b, :m].cpu())
+        assert torch.equal(hc[b, :m], ref.class_ids[b, :m].cpu()) and torch.equal(ha[b], ref.masks_arg[b].cpu())
+        assert torch.equal(hm[b, : hgt * wid * m], ref.masks_raw[b, : hgt * wid * m].cpu())
