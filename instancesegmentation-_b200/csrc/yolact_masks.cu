@@ -26,9 +26,11 @@
 namespace isb {
 
 constexpr int kMaskThreads = 256;
+constexpr int kMaskWarps = kMaskThreads / 32;
 constexpr int kStripRowsMax = 8;
 constexpr int kFootH = 6;          // prototype rows a strip may touch
-constexpr int kSFloats = 6144;     // sigmoid-map chunk (24 KB)
+constexpr int kSFloats = 2048;     // sigmoid-map chunk (8 KB)
+constexpr int kZeroBytes = 8192;   // zero source of the bulk (TMA) stores
 constexpr int kStripPixMax = 16384;
 
 struct MaskGeom {
@@ -38,63 +40,83 @@ struct MaskGeom {
   int list_cap;        // detections per image upper bound
 };
 
+// per-column bilinear table entry: source index pair and weight (image independent)
+struct ColTap { int32_t idx; float l1; };  // idx = ix0 | (ix1 - ix0) << 16
+
 struct MaskSmem {
-  size_t off_best, off_arg, off_s, off_bounds, off_list, off_soff, total;
+  size_t off_zero, off_best, off_arg, off_s, off_xtab, off_bounds, off_list, off_soff, off_pa, off_fw, total;
 };
 __host__ __device__ inline MaskSmem mask_smem(int rows, int out_w, int list_cap) {
   MaskSmem L;
   size_t o = 0;
   const size_t npix = (size_t)rows * out_w;
+  L.off_zero = o;   o += kZeroBytes;
   L.off_best = o;   o += npix * 4;
   L.off_arg = o;    o += ((npix * 2 + 15) & ~(size_t)15);
   L.off_s = o;      o += (size_t)kSFloats * 4;
+  L.off_xtab = o;   o += (size_t)out_w * sizeof(ColTap);
+  o = (o + 15) & ~(size_t)15;
   L.off_bounds = o; o += (size_t)list_cap * sizeof(DetBounds);
   L.off_list = o;   o += (size_t)list_cap * 4;
   L.off_soff = o;   o += (size_t)(list_cap + 1) * 4;
+  L.off_pa = o;     o += (size_t)list_cap * 2;
+  L.off_fw = o;     o += (size_t)list_cap * 2;
   L.total = (o + 15) & ~(size_t)15;
   return L;
 }
 
-// zero [g, g+nbytes) with the whole CTA: byte head / 16-byte body / byte tail
-__device__ __forceinline__ void cta_zero_bytes(uint8_t* g, int64_t nbytes, int tid) {
+// Zero [g, g+nbytes): the 16-byte aligned body goes out as bulk (TMA) stores from the CTA's zero buffer, issued
+// by thread 0 and completing asynchronously; the < 16-byte head and tail are plain byte stores.
+__device__ __forceinline__ void cta_zero_async(uint8_t* g, int64_t nbytes, const uint8_t* zsrc, int tid) {
   int head = (int)((16 - (reinterpret_cast<uintptr_t>(g) & 15)) & 15);
   if (head > nbytes) head = (int)nbytes;
+  const int64_t body = (nbytes - head) & ~(int64_t)15;
+  const int tail = (int)(nbytes - head - body);
   if (tid < head) g[tid] = 0;
-  uint4* body = reinterpret_cast<uint4*>(g + head);
-  const int64_t nvec = (nbytes - head) >> 4;
-  const uint4 z = make_uint4(0, 0, 0, 0);
-  int64_t v = tid;
-  // 4 independent stores in flight per thread per trip
-  for (; v + 3 * kMaskThreads < nvec; v += 4 * kMaskThreads) {
-    body[v] = z;
-    body[v + kMaskThreads] = z;
-    body[v + 2 * kMaskThreads] = z;
-    body[v + 3 * kMaskThreads] = z;
+  if (tid >= 32 && tid - 32 < tail) g[head + body + (tid - 32)] = 0;
+  if (tid == 0) {
+    uint8_t* d = g + head;
+    for (int64_t off = 0; off < body; off += kZeroBytes)
+      bulk_s2g(d + off, zsrc, (uint32_t)(body - off < kZeroBytes ? body - off : kZeroBytes));
   }
-  for (; v < nvec; v += kMaskThreads) body[v] = z;
-  const int tail = (int)(nbytes - head - (nvec << 4));
-  if (tid < tail) g[head + (nvec << 4) + tid] = 0;
 }
 
 __global__ void __launch_bounds__(kMaskThreads, 4)
 mask_assemble_kernel(MaskParams p, MaskGeom g, int* __restrict__ work_counter) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ int s_unit;
-  __shared__ int s_wcount[kMaskThreads / 32];
+  __shared__ int s_wcount[kMaskWarps];
   __shared__ int s_nlist;
 
   const int H = p.out_h, W = p.out_w;
   const MaskSmem L = mask_smem(g.rows, W, g.list_cap);
+  const uint8_t* s_zero = smem_raw + L.off_zero;
   float* s_best = reinterpret_cast<float*>(smem_raw + L.off_best);
   uint16_t* s_arg = reinterpret_cast<uint16_t*>(smem_raw + L.off_arg);
   float* s_S = reinterpret_cast<float*>(smem_raw + L.off_s);
+  ColTap* s_xtab = reinterpret_cast<ColTap*>(smem_raw + L.off_xtab);
   DetBounds* s_bounds = reinterpret_cast<DetBounds*>(smem_raw + L.off_bounds);
   int* s_list = reinterpret_cast<int*>(smem_raw + L.off_list);
   int* s_soff = reinterpret_cast<int*>(smem_raw + L.off_soff);
+  int16_t* s_pa = reinterpret_cast<int16_t*>(smem_raw + L.off_pa);
+  int16_t* s_fw = reinterpret_cast<int16_t*>(smem_raw + L.off_fw);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int total_units = p.batch * g.strips_per_img;
   int cached_img = -1;
+
+  // ---- once per CTA: zero source of the bulk stores, per-column bilinear taps -------------------
+  for (int i = tid; i < kZeroBytes / 16; i += kMaskThreads) reinterpret_cast<uint4*>(smem_raw + L.off_zero)[i] = make_uint4(0, 0, 0, 0);
+  for (int x = tid; x < W; x += kMaskThreads) {
+    int ix0, ix1;
+    float l0, l1;
+    bilinear_src(x, g.scale_x, p.proto_w, ix0, ix1, l0, l1);
+    ColTap t;
+    t.idx = ix0 | ((ix1 - ix0) << 16);
+    t.l1 = l1;
+    s_xtab[x] = t;
+  }
+  fence_proxy_async();  // the zero buffer is read by the async proxy
 
   while (true) {
     __syncthreads();  // everyone is done with the previous unit's shared memory (and s_unit)
@@ -111,6 +133,11 @@ mask_assemble_kernel(MaskParams p, MaskGeom g, int* __restrict__ work_counter) {
     uint8_t* out_img = p.masks + (size_t)b * p.mask_slot_bytes;
     int64_t* arg_img = p.masks_arg + (size_t)b * H * W;
 
+    // ---- 1. zero-fill (the HBM write stream), asynchronous -----------------------------------
+    cta_zero_async(out_img + (int64_t)y0 * W * m, (int64_t)(y1 - y0) * W * m, s_zero, tid);
+    cta_zero_async(reinterpret_cast<uint8_t*>(arg_img + (int64_t)y0 * W), (int64_t)(y1 - y0) * W * 8, s_zero, tid);
+    if (tid == 0) bulk_commit();
+
     // ---- detection bounds of this image -> shared memory (once per image change) ----------
     if (b != cached_img) {
       const DetBounds* gb = p.bounds + (size_t)b * p.det_stride;
@@ -118,18 +145,15 @@ mask_assemble_kernel(MaskParams p, MaskGeom g, int* __restrict__ work_counter) {
       cached_img = b;
     }
     if (tid == 0) s_nlist = 0;
-
-    // ---- 1. zero-fill (the HBM write stream) ------------------------------------------------
-    cta_zero_bytes(out_img + (int64_t)y0 * W * m, (int64_t)(y1 - y0) * W * m, tid);
-    cta_zero_bytes(reinterpret_cast<uint8_t*>(arg_img + (int64_t)y0 * W), (int64_t)(y1 - y0) * W * 8, tid);
-    __syncthreads();  // s_bounds / s_nlist visible; zero stores ordered before the patches below
+    __syncthreads();  // s_bounds / s_nlist visible
 
     // ---- list the detections whose crop rectangle meets the strip (ordered) ----------------
     for (int base = 0; base < m; base += kMaskThreads) {
       const int j = base + tid;
       bool hit = false;
+      DetBounds bd;
       if (j < m) {
-        const DetBounds bd = s_bounds[j];
+        bd = s_bounds[j];
         hit = bd.ylo < y1 && bd.yhi > y0 && bd.xlo < bd.xhi;
       }
       const unsigned bal = __ballot_sync(0xffffffffu, hit);
@@ -137,12 +161,20 @@ mask_assemble_kernel(MaskParams p, MaskGeom g, int* __restrict__ work_counter) {
       __syncthreads();
       int off = s_nlist, tot = 0;
 #pragma unroll
-      for (int w = 0; w < kMaskThreads / 32; ++w) {
+      for (int w = 0; w < kMaskWarps; ++w) {
         const int c = s_wcount[w];
         if (w < warp) off += c;
         tot += c;
       }
-      if (hit) s_list[off + __popc(bal & ((1u << lane) - 1u))] = j;
+      if (hit) {
+        const int pos = off + __popc(bal & ((1u << lane) - 1u));
+        const int pa = s_xtab[bd.xlo].idx & 0xffff;
+        const ColTap tb = s_xtab[bd.xhi - 1];
+        const int pb = (tb.idx & 0xffff) + (tb.idx >> 16);
+        s_list[pos] = j;
+        s_pa[pos] = (int16_t)pa;
+        s_fw[pos] = (int16_t)(pb - pa + 1);
+      }
       __syncthreads();
       if (tid == 0) s_nlist += tot;
       __syncthreads();
@@ -151,7 +183,8 @@ mask_assemble_kernel(MaskParams p, MaskGeom g, int* __restrict__ work_counter) {
     if (nlist == 0) continue;
 
     // ---- 2. patch ------------------------------------------------------------------------------
-    const int npix = (y1 - y0) * W;
+    const int nrows = y1 - y0;
+    const int npix = nrows * W;
     for (int q = tid; q < npix; q += kMaskThreads) { s_best[q] = 0.0f; s_arg[q] = 0; }
 
     int py_min, py_max, t0, t1;
@@ -163,6 +196,7 @@ mask_assemble_kernel(MaskParams p, MaskGeom g, int* __restrict__ work_counter) {
     const float* proto_img = p.proto + (size_t)b * p.proto_h * p.proto_w * ISB_NUM_COEF;
     const float* coef_img = p.coef + (size_t)b * p.det_stride * ISB_NUM_COEF;
 
+    bool zero_landed = false;
     int c0 = 0;
     while (c0 < nlist) {
       // chunk = as many listed detections as fit the S buffer (thread 0 lays it out)
@@ -171,13 +205,9 @@ mask_assemble_kernel(MaskParams p, MaskGeom g, int* __restrict__ work_counter) {
         int used = 0, li = c0;
         s_soff[0] = 0;
         while (li < nlist) {
-          const DetBounds bd = s_bounds[s_list[li]];
-          int pa, pb;
-          bilinear_src(bd.xlo, g.scale_x, p.proto_w, pa, t1, f0, f1);
-          bilinear_src(bd.xhi - 1, g.scale_x, p.proto_w, t0, pb, f0, f1);
-          const int need = FH * (pb - pa + 1);
+          const int need = FH * s_fw[li];
           if (used + need > kSFloats && li > c0) break;
-          if (need > kSFloats) __trap();  // proto_w <= 1024 is enforced on the host
+          if (need > kSFloats) __trap();  // proto_w <= kSFloats / kFootH is enforced on the host
           used += need;
           ++li;
           s_soff[li - c0] = used;
@@ -196,11 +226,7 @@ mask_assemble_kernel(MaskParams p, MaskGeom g, int* __restrict__ work_counter) {
           if (s_soff[mid] <= t) lo = mid; else hi = mid - 1;
         }
         const int j = s_list[c0 + lo];
-        const DetBounds bd = s_bounds[j];
-        int pa, pb;
-        bilinear_src(bd.xlo, g.scale_x, p.proto_w, pa, t1, f0, f1);
-        bilinear_src(bd.xhi - 1, g.scale_x, p.proto_w, t0, pb, f0, f1);
-        const int fw = pb - pa + 1;
+        const int pa = s_pa[c0 + lo], fw = s_fw[c0 + lo];
         const int f = t - s_soff[lo];
         const int fy = f / fw, fx = f - fy * fw;
         const float4* pp = reinterpret_cast<const float4*>(
@@ -217,47 +243,51 @@ mask_assemble_kernel(MaskParams p, MaskGeom g, int* __restrict__ work_counter) {
         }
         s_S[t] = sigmoidf_ref(acc);
       }
+      if (!zero_landed) {  // the zero stream must be complete before bytes are set on top of it
+        if (tid == 0) { bulk_wait0(); fence_proxy_async_all(); }
+        zero_landed = true;
+      }
       __syncthreads();
-      // ---- interpolate, threshold, arg-max over (box x strip); pixel owner = (row*W+col) % 256 --
-      for (int li = 0; li < nc; ++li) {
-        const int j = s_list[c0 + li];
-        const DetBounds bd = s_bounds[j];
-        int pa, pb;
-        bilinear_src(bd.xlo, g.scale_x, p.proto_w, pa, t1, f0, f1);
-        bilinear_src(bd.xhi - 1, g.scale_x, p.proto_w, t0, pb, f0, f1);
-        const int fw = pb - pa + 1;
-        const float* S = s_S + s_soff[li];
-        const int ra = max(bd.ylo, y0), rb = min(bd.yhi, y1);
-        for (int y = ra; y < rb; ++y) {
-          const int rowbase = (y - y0) * W;
-          int x = bd.xlo + ((tid - (rowbase + bd.xlo)) & (kMaskThreads - 1));
-          if (x >= bd.xhi) continue;
-          int iy0, iy1;
-          float ly0, ly1;
-          bilinear_src(y, g.scale_y, p.proto_h, iy0, iy1, ly0, ly1);
-          const float* S0 = S + (iy0 - py_min) * fw - pa;
-          const float* S1 = S + (iy1 - py_min) * fw - pa;
-          for (; x < bd.xhi; x += kMaskThreads) {
-            int ix0, ix1;
-            float lx0, lx1;
-            bilinear_src(x, g.scale_x, p.proto_w, ix0, ix1, lx0, lx1);
+      // ---- interpolate, threshold, arg-max: warp w owns row w of the strip, lanes stride the box width;
+      //      a warp visits the detections in ascending index, so "first max wins" like torch.argmax -------
+      for (int r = warp; r < nrows; r += kMaskWarps) {
+        const int y = y0 + r;
+        int iy0, iy1;
+        float ly0, ly1;
+        bilinear_src(y, g.scale_y, p.proto_h, iy0, iy1, ly0, ly1);
+        float* brow = s_best + r * W;
+        uint16_t* arow = s_arg + r * W;
+        uint8_t* orow = out_img + (int64_t)y * W * m;
+        for (int li = 0; li < nc; ++li) {
+          const int j = s_list[c0 + li];
+          const DetBounds bd = s_bounds[j];
+          if (y < bd.ylo || y >= bd.yhi) continue;  // warp-uniform
+          const int pa = s_pa[c0 + li], fw = s_fw[c0 + li];
+          const float* S0 = s_S + s_soff[li] + (iy0 - py_min) * fw - pa;
+          const float* S1 = s_S + s_soff[li] + (iy1 - py_min) * fw - pa;
+          for (int x = bd.xlo + lane; x < bd.xhi; x += 32) {
+            const ColTap tb = s_xtab[x];
+            const int ix0 = tb.idx & 0xffff, ix1 = ix0 + (tb.idx >> 16);
+            const float lx1 = tb.l1, lx0 = 1.0f - lx1;
             const float top = lx0 * S0[ix0] + lx1 * S0[ix1];
             const float bot = lx0 * S1[ix0] + lx1 * S1[ix1];
             const float v = ly0 * top + ly1 * bot;
-            const int q = rowbase + x;
-            if (v > 0.5f) out_img[((int64_t)y * W + x) * m + j] = 1;
-            if (v > s_best[q]) { s_best[q] = v; s_arg[q] = (uint16_t)j; }
+            if (v > 0.5f) orow[(int64_t)x * m + j] = 1;
+            if (v > brow[x]) { brow[x] = v; arow[x] = (uint16_t)j; }
           }
+          __syncwarp();  // lanes own different pixels in the next detection
         }
       }
       c0 = c1;
     }
+    __syncthreads();
     // arg-max rows: only pixels whose arg-max is not detection 0 differ from the zeros written above
     for (int q = tid; q < npix; q += kMaskThreads) {
       const int a = s_arg[q];
       if (a) arg_img[(int64_t)y0 * W + q] = (int64_t)a;
     }
   }
+  if (tid == 0) bulk_wait0();  // the zero buffer must outlive every bulk store that reads it
 }
 
 // ---- host side ----------------------------------------------------------------------------
@@ -276,7 +306,8 @@ int configure_masks(isb_handle* h) {
 }
 
 int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
-  if (p.proto_w > 1024) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports prototype width <= 1024, got %d", p.proto_w);
+  if (p.proto_w * kFootH > kSFloats || p.proto_w >= 65536)
+    ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports prototype width <= %d, got %d", kSFloats / kFootH, p.proto_w);
   if (p.out_w > kStripPixMax) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports output width <= %d, got %d", kStripPixMax, p.out_w);
   MaskGeom g;
   g.rows = pick_rows(p.proto_h, p.out_h, kStripRowsMax, kFootH);
