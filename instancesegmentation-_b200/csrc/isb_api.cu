@@ -81,6 +81,8 @@ static void free_ws(isb_handle* h) {
   cudaFree(h->cand_box);
   cudaFree(h->det_coef);
   cudaFree(h->det_bounds);
+  cudaFree(h->det_rec);
+  cudaFree(h->smap);
   cudaFree(h->stage);
   cudaFree(h->nms_keys);
   cudaFree(h->nms_sbox);
@@ -139,6 +141,7 @@ extern "C" int isb_create(int device, const isb_limits* limits, isb_handle** out
   WS_ALLOC(cand_box, B * cap * sizeof(float4));
   WS_ALLOC(det_coef, B * (size_t)L.max_det * ISB_NUM_COEF * sizeof(float));
   WS_ALLOC(det_bounds, B * (size_t)L.max_det * sizeof(DetBounds));
+  WS_ALLOC(det_rec, B * (size_t)L.max_det * sizeof(DetRec));
 #undef WS_ALLOC
   h->ws_bytes = total;
   int rc;

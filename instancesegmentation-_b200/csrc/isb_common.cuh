@@ -62,6 +62,17 @@ struct DetBounds {
   int32_t xlo, xhi, ylo, yhi;  // half-open integer pixel ranges equivalent to the float crop tests
 };
 
+// Per-detection record the mask compose kernel consumes (written by the sigmoid-map kernel):
+// crop ranges, offset of the detection's sigmoid map in the per-image scratch and its prototype
+// footprint (first column / row, width / height).
+struct __align__(16) DetRec {
+  int32_t xlo, xhi, ylo, yhi;
+  int32_t soff;
+  int16_t pa, pya, fw, fh;
+  int32_t j;
+};
+static_assert(sizeof(DetRec) == 32, "DetRec is two 16-byte words");
+
 // ---------------------------------------------------------------------------------------
 // fp32 building blocks shared by the fused path and the stage entry points, so both give
 // the same bits.  The library is compiled with -fmad=false: every +,-,* below is one
@@ -166,6 +177,7 @@ __device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, u
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // orders async-proxy accesses (bulk stores) against generic-proxy accesses, all state spaces
@@ -199,6 +211,9 @@ struct isb_handle {
   float4* cand_box;      // [max_batch][cand_cap_pow2]   decoded boxes (global fallback)
   float* det_coef;       // [max_batch][max_det][K]
   isb::DetBounds* det_bounds;  // [max_batch][max_det]
+  isb::DetRec* det_rec;        // [max_batch][max_det]
+  float* smap;                 // sigmoid-map scratch of the mask kernels, grown on demand
+  size_t smap_floats;
   // device staging for the *_host entry points (allocated on first use)
   void* stage;
   size_t stage_bytes;

@@ -6,108 +6,149 @@
 // [H, W, m] float tensors (121 MB each at 550^2, m = 100); here nothing but the outputs ever
 // reaches HBM.
 //
-// Work decomposition ("strips").  The bool output of one image is one contiguous byte stream of
-// H*W*m bytes (m innermost), so R full output rows are one contiguous byte range.  A work unit
-// is (image, strip of R rows); CTAs pull units from an atomic counter.
-//   1. zero-fill: the strip's byte range and its int64 arg-max rows are streamed out as 16-byte
-//      zero stores (pure write stream -- this is where the HBM bytes go);
-//   2. patch: only for detections whose crop rectangle meets the strip, the sigmoid map
-//      S[det][footprint] is computed for the prototype pixels under (box  x  strip), every pixel
-//      of (box  x  strip) interpolates it, and the bytes that are > 0.5 are set with byte stores
-//      that land in L2 on top of the zeros written a few microseconds earlier (one DRAM write per
-//      sector).  A pixel is always owned by the same thread ((row*W + col) mod 256), so the
-//      running arg-max lives in shared memory without atomics and detections are visited in
-//      ascending index ("first max wins", as torch.argmax).
-// Work is proportional to box area; HBM traffic is the algorithmic minimum: one write of every
-// output byte plus the prototype pixels that boxes touch.
+// Two kernels:
+//   K3a sigmoid_map_kernel  one CTA per detection: S_j = sigmoid(proto . coef_j) over the prototype
+//       pixels under detection j's crop box only (its "footprint", plus the bilinear halo), written to
+//       an L2-resident scratch (about 0.1 MB per image at the benchmark's box sizes).  Everything outside
+//       a crop box is zero after :230, so nothing else is ever needed.
+//   K3b mask_compose_kernel  the output of one image is ONE contiguous byte stream of H*W pixels x m
+//       bytes (m innermost).  A work unit is a contiguous range of kUnitPx pixels; CTAs pull units from an
+//       atomic counter and cut them into tiles of <= 512 pixels.  One thread owns one pixel of the tile:
+//       it walks the detections whose box covers it in ascending index (warp-level culling first),
+//       interpolates S with aten's align_corners=False arithmetic, keeps the running arg-max in
+//       registers ("first max wins", as torch.argmax), and sets the pixel's > 0.5 bytes in a shared-memory
+//       image of the tile (byte stride m: conflict-free for m = 100).  The finished tile leaves the SM
+//       as ONE bulk (TMA) store, double-buffered, so every output byte is written exactly once, in full
+//       lines, asynchronously; the int64 arg-max goes out as coalesced 8-byte stores.  Tiles stay
+//       zero except for the bytes their owner warp set, which it clears again after the store has
+//       read the buffer.
 // Bound: HBM write bandwidth (302 500*m + 2 420 000 bytes per image at 550^2).
 #include "isb_common.cuh"
 
 namespace isb {
 
-constexpr int kMaskThreads = 256;
-constexpr int kMaskWarps = kMaskThreads / 32;
-constexpr int kStripRowsMax = 8;
-constexpr int kFootH = 6;          // prototype rows a strip may touch
-constexpr int kSFloats = 2048;     // sigmoid-map chunk (8 KB)
-constexpr int kZeroBytes = 8192;   // zero source of the bulk (TMA) stores
-constexpr int kStripPixMax = 16384;
+constexpr int kCompThreads = 512;
+constexpr int kCompWarps = kCompThreads / 32;
+constexpr int kUnitPx = 4096;         // pixels per work unit (8 tiles of 512)
+constexpr int kSmapThreads = 128;
 
-struct MaskGeom {
-  int rows;            // output rows per strip
-  int strips_per_img;
+struct CompGeom {
+  int units_per_img;
   float scale_y, scale_x;
   int list_cap;        // detections per image upper bound
+  int buf_bytes;       // bytes of one tile buffer (multiple of 128)
+  int64_t s_cap;       // floats of sigmoid-map scratch per image
 };
 
 // per-column bilinear table entry: source index pair and weight (image independent)
 struct ColTap { int32_t idx; float l1; };  // idx = ix0 | (ix1 - ix0) << 16
 
-struct MaskSmem {
-  size_t off_zero, off_best, off_arg, off_s, off_xtab, off_bounds, off_list, off_soff, off_pa, off_fw, total;
-};
-__host__ __device__ inline MaskSmem mask_smem(int rows, int out_w, int list_cap) {
-  MaskSmem L;
-  size_t o = 0;
-  const size_t npix = (size_t)rows * out_w;
-  L.off_zero = o;   o += kZeroBytes;
-  L.off_best = o;   o += npix * 4;
-  L.off_arg = o;    o += ((npix * 2 + 15) & ~(size_t)15);
-  L.off_s = o;      o += (size_t)kSFloats * 4;
-  L.off_xtab = o;   o += (size_t)out_w * sizeof(ColTap);
-  o = (o + 15) & ~(size_t)15;
-  L.off_bounds = o; o += (size_t)list_cap * sizeof(DetBounds);
-  L.off_list = o;   o += (size_t)list_cap * 4;
-  L.off_soff = o;   o += (size_t)(list_cap + 1) * 4;
-  L.off_pa = o;     o += (size_t)list_cap * 2;
-  L.off_fw = o;     o += (size_t)list_cap * 2;
-  L.total = (o + 15) & ~(size_t)15;
-  return L;
+// prototype footprint of a crop box: first column/row and extent (0 x 0 for an empty box)
+__device__ __forceinline__ void det_footprint(const DetBounds& bd, float sy, float sx, int ph, int pw, int& pa, int& pya,
+                                              int& fw, int& fh) {
+  pa = pya = fw = fh = 0;
+  if (bd.xlo >= bd.xhi || bd.ylo >= bd.yhi) return;
+  int t0, t1, pb, pyb;
+  float f0, f1;
+  bilinear_src(bd.xlo, sx, pw, pa, t1, f0, f1);
+  bilinear_src(bd.xhi - 1, sx, pw, t0, pb, f0, f1);
+  bilinear_src(bd.ylo, sy, ph, pya, t1, f0, f1);
+  bilinear_src(bd.yhi - 1, sy, ph, t0, pyb, f0, f1);
+  fw = pb - pa + 1;
+  fh = pyb - pya + 1;
 }
 
-// Zero [g, g+nbytes): the 16-byte aligned body goes out as bulk (TMA) stores from the CTA's zero buffer, issued
-// by thread 0 and completing asynchronously; the < 16-byte head and tail are plain byte stores.
-__device__ __forceinline__ void cta_zero_async(uint8_t* g, int64_t nbytes, const uint8_t* zsrc, int tid) {
-  int head = (int)((16 - (reinterpret_cast<uintptr_t>(g) & 15)) & 15);
-  if (head > nbytes) head = (int)nbytes;
-  const int64_t body = (nbytes - head) & ~(int64_t)15;
-  const int tail = (int)(nbytes - head - body);
-  if (tid < head) g[tid] = 0;
-  if (tid >= 32 && tid - 32 < tail) g[head + body + (tid - 32)] = 0;
+// ---- K3a -----------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kSmapThreads)
+sigmoid_map_kernel(MaskParams p, float scale_y, float scale_x, DetRec* __restrict__ rec, float* __restrict__ smap,
+                   int64_t s_cap) {
+  __shared__ int s_part[kSmapThreads / 32];
+  const int b = blockIdx.y, j = blockIdx.x, tid = threadIdx.x;
+  const int m = p.counts ? p.counts[b] : p.m_fixed;
+  if (j >= m) return;
+  const DetBounds* bounds = p.bounds + (size_t)b * p.det_stride;
+  // offset of this detection's map = total footprint of the detections before it
+  int part = 0;
+  for (int jj = tid; jj < j; jj += kSmapThreads) {
+    int pa, pya, fw, fh;
+    det_footprint(bounds[jj], scale_y, scale_x, p.proto_h, p.proto_w, pa, pya, fw, fh);
+    part += fw * fh;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  if ((tid & 31) == 0) s_part[tid >> 5] = part;
+  __syncthreads();
+  int soff = 0;
+#pragma unroll
+  for (int w = 0; w < kSmapThreads / 32; ++w) soff += s_part[w];
+  const DetBounds bd = bounds[j];
+  int pa, pya, fw, fh;
+  det_footprint(bd, scale_y, scale_x, p.proto_h, p.proto_w, pa, pya, fw, fh);
   if (tid == 0) {
-    uint8_t* d = g + head;
-    for (int64_t off = 0; off < body; off += kZeroBytes)
-      bulk_s2g(d + off, zsrc, (uint32_t)(body - off < kZeroBytes ? body - off : kZeroBytes));
+    DetRec r;
+    r.xlo = bd.xlo; r.xhi = bd.xhi; r.ylo = bd.ylo; r.yhi = bd.yhi;
+    r.soff = soff;
+    r.pa = (int16_t)pa; r.pya = (int16_t)pya; r.fw = (int16_t)fw; r.fh = (int16_t)fh;
+    r.j = j;
+    rec[(size_t)b * p.det_stride + j] = r;
+  }
+  const int items = fw * fh;
+  if (items == 0) return;
+  const float4* cf = reinterpret_cast<const float4*>(p.coef + ((size_t)b * p.det_stride + j) * ISB_NUM_COEF);
+  float4 c[ISB_NUM_COEF / 4];
+#pragma unroll
+  for (int q = 0; q < ISB_NUM_COEF / 4; ++q) c[q] = __ldg(cf + q);
+  const float* proto_img = p.proto + (size_t)b * p.proto_h * p.proto_w * ISB_NUM_COEF;
+  float* S = smap + (size_t)b * s_cap + soff;
+  for (int t = tid; t < items; t += kSmapThreads) {
+    const int fy = t / fw, fx = t - fy * fw;
+    const float4* pp = reinterpret_cast<const float4*>(
+        proto_img + ((size_t)(pya + fy) * p.proto_w + (pa + fx)) * ISB_NUM_COEF);
+    float acc = 0.0f;
+#pragma unroll
+    for (int q = 0; q < ISB_NUM_COEF / 4; ++q) {
+      const float4 a = __ldg(pp + q);
+      acc = fmaf(a.x, c[q].x, acc);
+      acc = fmaf(a.y, c[q].y, acc);
+      acc = fmaf(a.z, c[q].z, acc);
+      acc = fmaf(a.w, c[q].w, acc);
+    }
+    S[t] = sigmoidf_ref(acc);
   }
 }
 
-__global__ void __launch_bounds__(kMaskThreads, 4)
-mask_assemble_kernel(MaskParams p, MaskGeom g, int* __restrict__ work_counter) {
+// ---- K3b -----------------------------------------------------------------------------------
+// zero buf[a, b) with one warp: 16-byte interior, byte edges (never touches a byte outside [a, b))
+__device__ __forceinline__ void warp_clear(uint8_t* buf, int a, int b, int lane) {
+  const int a16 = (a + 15) & ~15, b16 = b & ~15;
+  if (a16 >= b16) {
+    for (int i = a + lane; i < b; i += 32) buf[i] = 0;
+    return;
+  }
+  if (a + lane < a16) buf[a + lane] = 0;
+  if (b16 + lane < b) buf[b16 + lane] = 0;
+  for (int v = a16 + lane * 16; v < b16; v += 32 * 16) *reinterpret_cast<uint4*>(buf + v) = make_uint4(0, 0, 0, 0);
+}
+
+__global__ void __launch_bounds__(kCompThreads, 2)
+mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, const float* __restrict__ smap,
+                    int* __restrict__ work_counter) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ int s_unit;
-  __shared__ int s_wcount[kMaskWarps];
+  __shared__ int s_wcount[kCompWarps];
   __shared__ int s_nlist;
 
   const int H = p.out_h, W = p.out_w;
-  const MaskSmem L = mask_smem(g.rows, W, g.list_cap);
-  const uint8_t* s_zero = smem_raw + L.off_zero;
-  float* s_best = reinterpret_cast<float*>(smem_raw + L.off_best);
-  uint16_t* s_arg = reinterpret_cast<uint16_t*>(smem_raw + L.off_arg);
-  float* s_S = reinterpret_cast<float*>(smem_raw + L.off_s);
-  ColTap* s_xtab = reinterpret_cast<ColTap*>(smem_raw + L.off_xtab);
-  DetBounds* s_bounds = reinterpret_cast<DetBounds*>(smem_raw + L.off_bounds);
-  int* s_list = reinterpret_cast<int*>(smem_raw + L.off_list);
-  int* s_soff = reinterpret_cast<int*>(smem_raw + L.off_soff);
-  int16_t* s_pa = reinterpret_cast<int16_t*>(smem_raw + L.off_pa);
-  int16_t* s_fw = reinterpret_cast<int16_t*>(smem_raw + L.off_fw);
+  ColTap* s_xtab = reinterpret_cast<ColTap*>(smem_raw + 2 * (size_t)g.buf_bytes);
+  DetRec* s_det = reinterpret_cast<DetRec*>(smem_raw + 2 * (size_t)g.buf_bytes + (((size_t)W * sizeof(ColTap) + 31) & ~(size_t)31));
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int total_units = p.batch * g.strips_per_img;
-  int cached_img = -1;
+  const int total_units = p.batch * g.units_per_img;
+  const int HW = H * W;
 
-  // ---- once per CTA: zero source of the bulk stores, per-column bilinear taps -------------------
-  for (int i = tid; i < kZeroBytes / 16; i += kMaskThreads) reinterpret_cast<uint4*>(smem_raw + L.off_zero)[i] = make_uint4(0, 0, 0, 0);
-  for (int x = tid; x < W; x += kMaskThreads) {
+  // ---- once per CTA: clean tile buffers, per-column bilinear taps ---------------------------------
+  for (int i = tid; i < 2 * g.buf_bytes / 16; i += kCompThreads) reinterpret_cast<uint4*>(smem_raw)[i] = make_uint4(0, 0, 0, 0);
+  for (int x = tid; x < W; x += kCompThreads) {
     int ix0, ix1;
     float l0, l1;
     bilinear_src(x, g.scale_x, p.proto_w, ix0, ix1, l0, l1);
@@ -116,225 +157,202 @@ mask_assemble_kernel(MaskParams p, MaskGeom g, int* __restrict__ work_counter) {
     t.l1 = l1;
     s_xtab[x] = t;
   }
-  fence_proxy_async();  // the zero buffer is read by the async proxy
+  int dlo0 = 0, dhi0 = 0, dlo1 = 0, dhi1 = 0;  // this warp's dirty byte range in each buffer
+  unsigned tile_no = 0;
 
   while (true) {
-    __syncthreads();  // everyone is done with the previous unit's shared memory (and s_unit)
+    __syncthreads();  // everyone is done with the previous unit's list (and s_unit)
     if (tid == 0) s_unit = atomicAdd(work_counter, 1);
     __syncthreads();
     const int unit = s_unit;
     if (unit >= total_units) break;
-    const int b = unit / g.strips_per_img;
-    const int strip = unit - b * g.strips_per_img;
+    const int b = unit / g.units_per_img;
+    const int u = unit - b * g.units_per_img;
     const int m = p.counts ? p.counts[b] : p.m_fixed;
     if (m <= 0) continue;  // nothing to write for this image (the reference returns None)
-    const int y0 = strip * g.rows;
-    const int y1 = min(y0 + g.rows, H);
+    const int px0 = u * kUnitPx;
+    const int px1 = min(px0 + kUnitPx, HW);
+    const int ya = px0 / W, yb = (px1 - 1) / W;  // rows the unit touches
     uint8_t* out_img = p.masks + (size_t)b * p.mask_slot_bytes;
-    int64_t* arg_img = p.masks_arg + (size_t)b * H * W;
+    int64_t* arg_img = p.masks_arg + (size_t)b * HW;
+    const float* S_img = smap + (size_t)b * g.s_cap;
 
-    // ---- 1. zero-fill (the HBM write stream), asynchronous -----------------------------------
-    cta_zero_async(out_img + (int64_t)y0 * W * m, (int64_t)(y1 - y0) * W * m, s_zero, tid);
-    cta_zero_async(reinterpret_cast<uint8_t*>(arg_img + (int64_t)y0 * W), (int64_t)(y1 - y0) * W * 8, s_zero, tid);
-    if (tid == 0) bulk_commit();
-
-    // ---- detection bounds of this image -> shared memory (once per image change) ----------
-    if (b != cached_img) {
-      const DetBounds* gb = p.bounds + (size_t)b * p.det_stride;
-      for (int j = tid; j < m; j += kMaskThreads) s_bounds[j] = gb[j];
-      cached_img = b;
-    }
+    // ---- list the detections whose crop rectangle meets the unit's rows (ascending index) ---------
     if (tid == 0) s_nlist = 0;
-    __syncthreads();  // s_bounds / s_nlist visible
-
-    // ---- list the detections whose crop rectangle meets the strip (ordered) ----------------
-    for (int base = 0; base < m; base += kMaskThreads) {
+    __syncthreads();
+    for (int base = 0; base < m; base += kCompThreads) {
       const int j = base + tid;
       bool hit = false;
-      DetBounds bd;
+      DetRec r;
       if (j < m) {
-        bd = s_bounds[j];
-        hit = bd.ylo < y1 && bd.yhi > y0 && bd.xlo < bd.xhi;
+        r = rec[(size_t)b * p.det_stride + j];
+        hit = r.ylo <= yb && r.yhi > ya && r.xlo < r.xhi;
       }
       const unsigned bal = __ballot_sync(0xffffffffu, hit);
       if (lane == 0) s_wcount[warp] = __popc(bal);
       __syncthreads();
       int off = s_nlist, tot = 0;
 #pragma unroll
-      for (int w = 0; w < kMaskWarps; ++w) {
+      for (int w = 0; w < kCompWarps; ++w) {
         const int c = s_wcount[w];
         if (w < warp) off += c;
         tot += c;
       }
-      if (hit) {
-        const int pos = off + __popc(bal & ((1u << lane) - 1u));
-        const int pa = s_xtab[bd.xlo].idx & 0xffff;
-        const ColTap tb = s_xtab[bd.xhi - 1];
-        const int pb = (tb.idx & 0xffff) + (tb.idx >> 16);
-        s_list[pos] = j;
-        s_pa[pos] = (int16_t)pa;
-        s_fw[pos] = (int16_t)(pb - pa + 1);
-      }
+      if (hit) s_det[off + __popc(bal & ((1u << lane) - 1u))] = r;
       __syncthreads();
       if (tid == 0) s_nlist += tot;
       __syncthreads();
     }
     const int nlist = s_nlist;
-    if (nlist == 0) continue;
+    const int tile_px = min(kCompThreads, ((g.buf_bytes - 16) / m) & ~31);
 
-    // ---- 2. patch ------------------------------------------------------------------------------
-    const int nrows = y1 - y0;
-    const int npix = nrows * W;
-    for (int q = tid; q < npix; q += kMaskThreads) { s_best[q] = 0.0f; s_arg[q] = 0; }
-
-    int py_min, py_max, t0, t1;
-    float f0, f1;
-    bilinear_src(y0, g.scale_y, p.proto_h, py_min, t1, f0, f1);
-    bilinear_src(y1 - 1, g.scale_y, p.proto_h, t0, py_max, f0, f1);
-    const int FH = py_max - py_min + 1;
-    if (FH > kFootH) __trap();  // host strip sizing guarantees this never happens
-    const float* proto_img = p.proto + (size_t)b * p.proto_h * p.proto_w * ISB_NUM_COEF;
-    const float* coef_img = p.coef + (size_t)b * p.det_stride * ISB_NUM_COEF;
-
-    bool zero_landed = false;
-    int c0 = 0;
-    while (c0 < nlist) {
-      // chunk = as many listed detections as fit the S buffer (thread 0 lays it out)
-      __syncthreads();  // previous chunk's S consumed; s_best init done
-      if (tid == 0) {
-        int used = 0, li = c0;
-        s_soff[0] = 0;
-        while (li < nlist) {
-          const int need = FH * s_fw[li];
-          if (used + need > kSFloats && li > c0) break;
-          if (need > kSFloats) __trap();  // proto_w <= kSFloats / kFootH is enforced on the host
-          used += need;
-          ++li;
-          s_soff[li - c0] = used;
-        }
-        s_nlist = li;  // reuse as "chunk end"
-      }
+    // ---- tiles ----------------------------------------------------------------------------------------
+    for (int q0 = px0; q0 < px1; q0 += tile_px, ++tile_no) {
+      const int nt = min(tile_px, px1 - q0);
+      const int par = tile_no & 1;
+      uint8_t* buf = smem_raw + (par ? g.buf_bytes : 0);
+      uint8_t* g0 = out_img + (int64_t)q0 * m;
+      const int shift = (int)(reinterpret_cast<uintptr_t>(g0) & 15);
+      // the bulk store issued from this buffer two tiles ago must have finished reading it
+      if (tid == 0) bulk_wait_read1();
       __syncthreads();
-      const int c1 = s_nlist;
-      const int nc = c1 - c0;
-      const int items = s_soff[nc];
-      // ---- S[det][fy][fx] = sigmoid(proto . coef) ------------------------------------------
-      for (int t = tid; t < items; t += kMaskThreads) {
-        int lo = 0, hi = nc - 1;  // last li with s_soff[li] <= t
-        while (lo < hi) {
-          const int mid = (lo + hi + 1) >> 1;
-          if (s_soff[mid] <= t) lo = mid; else hi = mid - 1;
-        }
-        const int j = s_list[c0 + lo];
-        const int pa = s_pa[c0 + lo], fw = s_fw[c0 + lo];
-        const int f = t - s_soff[lo];
-        const int fy = f / fw, fx = f - fy * fw;
-        const float4* pp = reinterpret_cast<const float4*>(
-            proto_img + ((size_t)(py_min + fy) * p.proto_w + (pa + fx)) * ISB_NUM_COEF);
-        const float4* cf = reinterpret_cast<const float4*>(coef_img + (size_t)j * ISB_NUM_COEF);
-        float acc = 0.0f;
-#pragma unroll
-        for (int q = 0; q < ISB_NUM_COEF / 4; ++q) {
-          const float4 a = __ldg(pp + q), c = __ldg(cf + q);
-          acc = fmaf(a.x, c.x, acc);
-          acc = fmaf(a.y, c.y, acc);
-          acc = fmaf(a.z, c.z, acc);
-          acc = fmaf(a.w, c.w, acc);
-        }
-        s_S[t] = sigmoidf_ref(acc);
+      {
+        const int dlo = par ? dlo1 : dlo0, dhi = par ? dhi1 : dhi0;
+        if (dhi > dlo) warp_clear(buf, dlo, dhi, lane);
       }
-      if (!zero_landed) {  // the zero stream must be complete before bytes are set on top of it
-        if (tid == 0) { bulk_wait0(); fence_proxy_async_all(); }
-        zero_landed = true;
-      }
-      __syncthreads();
-      // ---- interpolate, threshold, arg-max: warp w owns row w of the strip, lanes stride the box width;
-      //      a warp visits the detections in ascending index, so "first max wins" like torch.argmax -------
-      for (int r = warp; r < nrows; r += kMaskWarps) {
-        const int y = y0 + r;
+      const bool active = tid < nt;
+      const int q = q0 + tid;
+      const int y = active ? q / W : 0, x = active ? q - y * W : 0;
+      float best = 0.0f;
+      int arg = 0;
+      bool anyset = false;
+      const int wq0 = q0 + warp * 32;
+      if (wq0 < q0 + nt) {  // warp has pixels in this tile
+        const int wq1 = min(wq0 + 32, q0 + nt);
+        const int wy0 = wq0 / W, wy1 = (wq1 - 1) / W;
+        int wxa = 0, wxb = W;
+        if (wy0 == wy1) { wxa = wq0 - wy0 * W; wxb = wxa + (wq1 - wq0); }
         int iy0, iy1;
         float ly0, ly1;
         bilinear_src(y, g.scale_y, p.proto_h, iy0, iy1, ly0, ly1);
-        float* brow = s_best + r * W;
-        uint16_t* arow = s_arg + r * W;
-        uint8_t* orow = out_img + (int64_t)y * W * m;
-        for (int li = 0; li < nc; ++li) {
-          const int j = s_list[c0 + li];
-          const DetBounds bd = s_bounds[j];
-          if (y < bd.ylo || y >= bd.yhi) continue;  // warp-uniform
-          const int pa = s_pa[c0 + li], fw = s_fw[c0 + li];
-          const float* S0 = s_S + s_soff[li] + (iy0 - py_min) * fw - pa;
-          const float* S1 = s_S + s_soff[li] + (iy1 - py_min) * fw - pa;
-          for (int x = bd.xlo + lane; x < bd.xhi; x += 32) {
-            const ColTap tb = s_xtab[x];
-            const int ix0 = tb.idx & 0xffff, ix1 = ix0 + (tb.idx >> 16);
-            const float lx1 = tb.l1, lx0 = 1.0f - lx1;
-            const float top = lx0 * S0[ix0] + lx1 * S0[ix1];
-            const float bot = lx0 * S1[ix0] + lx1 * S1[ix1];
-            const float v = ly0 * top + ly1 * bot;
-            if (v > 0.5f) orow[(int64_t)x * m + j] = 1;
-            if (v > brow[x]) { brow[x] = v; arow[x] = (uint16_t)j; }
+        const ColTap tb = s_xtab[x];
+        const int ix0 = tb.idx & 0xffff, ix1 = ix0 + (tb.idx >> 16);
+        const float lx1 = tb.l1, lx0 = 1.0f - lx1;
+        uint8_t* mypix = buf + shift + tid * m;
+        for (int base = 0; base < nlist; base += 32) {
+          bool hit = false;
+          if (base + lane < nlist) {
+            const int4 bb = *reinterpret_cast<const int4*>(&s_det[base + lane]);  // xlo, xhi, ylo, yhi
+            hit = bb.z <= wy1 && bb.w > wy0 && bb.x < wxb && bb.y > wxa;
           }
-          __syncwarp();  // lanes own different pixels in the next detection
+          unsigned bal = __ballot_sync(0xffffffffu, hit);
+          while (bal) {
+            const int k = __ffs(bal) - 1;
+            bal &= bal - 1;
+            const DetRec r = s_det[base + k];
+            if (active && y >= r.ylo && y < r.yhi && x >= r.xlo && x < r.xhi) {
+              const float* S = S_img + r.soff;
+              const int fw = r.fw;
+              const int r0 = (iy0 - r.pya) * fw - r.pa, r1 = (iy1 - r.pya) * fw - r.pa;
+              const float top = lx0 * __ldg(S + r0 + ix0) + lx1 * __ldg(S + r0 + ix1);
+              const float bot = lx0 * __ldg(S + r1 + ix0) + lx1 * __ldg(S + r1 + ix1);
+              const float v = ly0 * top + ly1 * bot;
+              if (v > 0.5f) { mypix[r.j] = 1; anyset = true; }
+              if (v > best) { best = v; arg = r.j; }
+            }
+          }
         }
+        if (active) arg_img[q] = (int64_t)arg;
       }
-      c0 = c1;
-    }
-    __syncthreads();
-    // arg-max rows: only pixels whose arg-max is not detection 0 differ from the zeros written above
-    for (int q = tid; q < npix; q += kMaskThreads) {
-      const int a = s_arg[q];
-      if (a) arg_img[(int64_t)y0 * W + q] = (int64_t)a;
+      {  // remember what this warp dirtied
+        const unsigned sb = __ballot_sync(0xffffffffu, anyset);
+        int dlo = 0, dhi = 0;
+        if (sb) {
+          dlo = shift + (warp * 32 + (__ffs(sb) - 1)) * m;
+          dhi = shift + (warp * 32 + (32 - __clz(sb))) * m;
+        }
+        if (par) { dlo1 = dlo; dhi1 = dhi; } else { dlo0 = dlo; dhi0 = dhi; }
+      }
+      fence_proxy_async();  // this thread's shared-memory writes -> visible to the bulk store
+      __syncthreads();
+      // ---- the tile leaves as one bulk store (16-byte aligned interior) + < 16-byte edges ---------
+      uint8_t* g1 = g0 + (int64_t)nt * m;
+      const int head = (16 - shift) & 15;
+      const int64_t nbytes = (int64_t)nt * m;
+      if (nbytes <= head) {
+        if (tid == 0) bulk_commit();  // one (possibly empty) group per tile keeps the wait_group arithmetic exact
+        if (tid >= 64 && tid - 64 < nbytes) g0[tid - 64] = buf[shift + (tid - 64)];
+      } else {
+        const int64_t body = (nbytes - head) & ~(int64_t)15;
+        const int tail = (int)(nbytes - head - body);
+        if (tid == 0) {
+          if (body > 0) bulk_s2g(g0 + head, buf + shift + head, (uint32_t)body);
+          bulk_commit();
+        }
+        if (tid >= 64 && tid - 64 < head) g0[tid - 64] = buf[shift + (tid - 64)];
+        if (tid >= 96 && tid - 96 < tail) g1[-tail + (tid - 96)] = buf[shift + head + body + (tid - 96)];
+      }
     }
   }
-  if (tid == 0) bulk_wait0();  // the zero buffer must outlive every bulk store that reads it
+  if (tid == 0) bulk_wait_read0();  // shared memory must outlive every bulk store that reads it
 }
 
 // ---- host side ----------------------------------------------------------------------------
-static int pick_rows(int in_size, int out_size, int rows_max, int foot_cap) {
-  const float scale = (float)in_size / (float)out_size;
-  int t = rows_max;
-  while (t > 1 && (int)floorf(scale * (float)(t - 1)) + 3 > foot_cap) --t;
-  return t;
-}
-
-static constexpr int kMaskSmemMax = 200 * 1024;
+static constexpr int kCompSmemTwo = 111 * 1024;   // two CTAs per SM
+static constexpr int kCompSmemOne = 200 * 1024;   // one CTA per SM (very large detection counts)
 
 int configure_masks(isb_handle* h) {
-  ISB_CUDA(h, cudaFuncSetAttribute(mask_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaskSmemMax));
+  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
+  return ISB_OK;
+}
+
+static int ensure_smap(isb_handle* h, size_t floats) {
+  if (floats <= h->smap_floats) return ISB_OK;
+  ISB_CUDA(h, cudaDeviceSynchronize());
+  cudaFree(h->smap);
+  h->smap = nullptr;
+  h->smap_floats = 0;
+  ISB_CUDA(h, cudaMalloc((void**)&h->smap, floats * sizeof(float)));
+  h->smap_floats = floats;
   return ISB_OK;
 }
 
 int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
-  if (p.proto_w * kFootH > kSFloats || p.proto_w >= 65536)
-    ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports prototype width <= %d, got %d", kSFloats / kFootH, p.proto_w);
-  if (p.out_w > kStripPixMax) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports output width <= %d, got %d", kStripPixMax, p.out_w);
-  MaskGeom g;
-  g.rows = pick_rows(p.proto_h, p.out_h, kStripRowsMax, kFootH);
-  while (g.rows > 1 && g.rows * p.out_w > kStripPixMax) --g.rows;
-  g.strips_per_img = (p.out_h + g.rows - 1) / g.rows;
+  if (p.proto_w >= 32768 || p.proto_h >= 32768) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports prototype sides < 32768");
+  if ((int64_t)p.out_h * p.out_w >= (1ll << 31) / 8) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly: output image too large");
+  if (p.det_stride > h->lim.max_det) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly: %d detections > max_det %d", p.det_stride, h->lim.max_det);
+  CompGeom g;
+  const int64_t hw = (int64_t)p.out_h * p.out_w;
+  g.units_per_img = (int)((hw + kUnitPx - 1) / kUnitPx);
   g.scale_y = (float)p.proto_h / (float)p.out_h;
   g.scale_x = (float)p.proto_w / (float)p.out_w;
   g.list_cap = p.m_fixed >= 0 ? (p.m_fixed > 0 ? p.m_fixed : 1) : p.det_stride;
-  MaskSmem L = mask_smem(g.rows, p.out_w, g.list_cap);
-  // prefer >= 4 resident CTAs per SM (<= 55 KB each) as long as a strip keeps >= 2 rows
-  while ((L.total > (size_t)kMaskSmemMax && g.rows > 1) || (L.total > 55 * 1024 && g.rows > 2)) {
-    --g.rows;
-    g.strips_per_img = (p.out_h + g.rows - 1) / g.rows;
-    L = mask_smem(g.rows, p.out_w, g.list_cap);
-  }
-  if (L.total > (size_t)kMaskSmemMax) ISB_FAIL(h, ISB_ERR_LIMIT, "mask kernel shared memory %zu exceeds %d", L.total, kMaskSmemMax);
-  const int64_t total_units = (int64_t)p.batch * g.strips_per_img;
+  g.s_cap = (int64_t)h->lim.max_det * p.proto_h * p.proto_w;  // worst case: every box covers the whole image
+  const size_t fixed = (((size_t)p.out_w * sizeof(ColTap) + 31) & ~(size_t)31) + (size_t)g.list_cap * sizeof(DetRec);
+  const size_t want = ((size_t)kCompThreads * g.list_cap + 16 + 127) & ~(size_t)127;  // a full 512-pixel tile
+  const size_t need = ((size_t)32 * g.list_cap + 16 + 127) & ~(size_t)127;            // at least one warp of pixels
+  size_t budget = kCompSmemTwo;
+  if (fixed + 2 * need > budget) budget = kCompSmemOne;
+  if (fixed + 2 * need > budget) ISB_FAIL(h, ISB_ERR_LIMIT, "mask compose: %d detections x width %d exceed shared memory", g.list_cap, p.out_w);
+  size_t buf = ((budget - fixed) / 2) & ~(size_t)127;
+  if (buf > want) buf = want;
+  g.buf_bytes = (int)buf;
+  const size_t smem = fixed + 2 * buf;
+  int rc = ensure_smap(h, (size_t)h->lim.max_batch * (size_t)g.s_cap);
+  if (rc != ISB_OK) return rc;
+  const int64_t total_units = (int64_t)p.batch * g.units_per_img;
   if (total_units == 0) return ISB_OK;
-  int per_sm = (int)((220 * 1024) / (L.total + 1024));
-  if (per_sm < 1) per_sm = 1;
-  if (per_sm > 4) per_sm = 4;
+  DetRec* rec = h->det_rec + (size_t)h->ws_b0 * h->lim.max_det;
+  float* smap = h->smap + (size_t)h->ws_b0 * g.s_cap;
+  sigmoid_map_kernel<<<dim3(g.list_cap, p.batch), kSmapThreads, 0, s>>>(p, g.scale_y, g.scale_x, rec, smap, g.s_cap);
+  ISB_LAUNCH_CHECK(h, "sigmoid_map_kernel");
+  const int per_sm = smem + 1024 <= (size_t)kCompSmemTwo + 2048 ? 2 : 1;
   int64_t grid = (int64_t)h->num_sms * per_sm;
   if (grid > total_units) grid = total_units;
   int* counter = h->work_counter + h->ws_lane;
   ISB_CUDA(h, cudaMemsetAsync(counter, 0, sizeof(int), s));
-  mask_assemble_kernel<<<(unsigned)grid, kMaskThreads, L.total, s>>>(p, g, counter);
-  ISB_LAUNCH_CHECK(h, "mask_assemble_kernel");
+  mask_compose_kernel<<<(unsigned)grid, kCompThreads, smem, s>>>(p, g, rec, smap, counter);
+  ISB_LAUNCH_CHECK(h, "mask_compose_kernel");
   return ISB_OK;
 }
 
