@@ -302,10 +302,10 @@ def run_gpu(args):
         n_img = bsz * world * args.steps
         m_sum = float(counts.sum())
         hw = shape[0] * shape[1]
-        # algorithmic bytes of ONE mask-kernel launch: prototypes + per-detection coefficients and crop
-        # bounds in, int64 arg-max map and bool [H,W,m] masks out
-        mask_bytes = bsz * (p * p * 32 * 4 + hw * 8) + m_sum * (hw + 128 + 16)
-        mask_ms = stage_ms[2] / max(calls, 1)
+        # algorithmic bytes of ONE mask_compose_kernel launch: per-detection records in, int64 arg-max map
+        # and bool [H,W,m] masks out (the sigmoid maps it samples are an L2-resident intermediate, not counted)
+        mask_bytes = bsz * hw * 8 + m_sum * (hw + 32)
+        mask_ms = stage_ms[3] / max(calls, 1)
         peak, peak_src = measured_peak()
         achieved = mask_bytes / (mask_ms * 1e-3) / 1e9
         path_bytes = bsz * 13_865_696 + 302_528 * m_sum  # SURVEY 8(d) bytes(m), whole path, per GPU
@@ -317,11 +317,11 @@ def run_gpu(args):
                 "e2e": {"value": bsz * world / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "steps": e2e_steps, "api": "isb_yolact_detect_host (pinned host buffers)"},
                 "gpu_launches": launches,
-                "roofline": {"bound": "hbm", "kernel": "mask_assemble_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "roofline": {"bound": "hbm", "kernel": "mask_compose_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": tr["dram_bytes_per_launch"] if tr else None,
                              "peak_source": peak_src, "algorithmic_bytes_per_launch": mask_bytes, "kernel_ms": mask_ms,
                              "stage_ms": {"candidates": stage_ms[0] / max(calls, 1), "sort_nms": stage_ms[1] / max(calls, 1),
-                                          "masks": mask_ms},
+                                          "sigmoid_maps": stage_ms[2] / max(calls, 1), "mask_compose": mask_ms},
                              "path_achieved_gbs": path_bytes / (ms / args.steps * 1e-3) / 1e9,
                              "path_frac": path_bytes / (ms / args.steps * 1e-3) / 1e9 / peak,
                              "mean_detections": m_sum / bsz},

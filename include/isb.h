@@ -64,9 +64,9 @@ ISB_API int64_t isb_launch_count(const isb_handle* h);
  * stream between the kernels (no synchronisation while recording).  isb_profile_begin arms a
  * ring of `max_calls` slots (0 disables); every following isb_yolact_detect call fills one slot;
  * isb_profile_read synchronises on the last slot and returns, per stage (0 = candidate filter,
- * 1 = sort + Fast NMS, 2 = mask assembly), the summed milliseconds over the recorded calls. */
+ * 1 = sort + Fast NMS, 2 = sigmoid maps, 3 = mask compose), the summed milliseconds over the recorded calls. */
 ISB_API int isb_profile_begin(isb_handle* h, int32_t max_calls);
-ISB_API int isb_profile_read(isb_handle* h, double stage_ms[3], int32_t* calls);
+ISB_API int isb_profile_read(isb_handle* h, double stage_ms[4], int32_t* calls);
 
 /* ------------------------------------------------------------------------------------
  * YOLACT Detect + mask assembly, fused, for a batch of images.

@@ -81,7 +81,7 @@ def load():
         lib.isb_launch_count.argtypes = [vp]
         lib.isb_launch_count.restype = i64
         lib.isb_profile_begin.argtypes = [vp, i32]
-        lib.isb_profile_read.argtypes = [vp, C.POINTER(C.c_double * 3), C.POINTER(i32)]
+        lib.isb_profile_read.argtypes = [vp, C.POINTER(C.c_double * 4), C.POINTER(i32)]
         lib.isb_yolact_detect.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactOut), vp]
         lib.isb_yolact_detect_host.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactOut), vp]
         lib.isb_decode_boxes.argtypes = [vp, vp, vp, i64, f32, f32, vp, vp]
@@ -149,11 +149,11 @@ class Handle:
         self.check(self.lib.isb_profile_begin(self.ptr, int(max_calls)))
 
     def profile_read(self):
-        """-> ([ms_candidates, ms_nms, ms_masks] summed over the recorded calls, calls)"""
-        ms = (C.c_double * 3)()
+        """-> ([ms_candidates, ms_nms, ms_sigmoid_maps, ms_compose] summed over the recorded calls, calls)"""
+        ms = (C.c_double * 4)()
         n = C.c_int32()
         self.check(self.lib.isb_profile_read(self.ptr, C.byref(ms), C.byref(n)))
-        return [ms[0], ms[1], ms[2]], int(n.value)
+        return [ms[0], ms[1], ms[2], ms[3]], int(n.value)
 
     def close(self):
         if getattr(self, "_h", None) is not None:

@@ -12,7 +12,7 @@ int launch_decode_boxes(isb_handle*, const float*, const float*, int64_t, float,
 int launch_jaccard(isb_handle*, const float*, const float*, int, int, int, int, float*, cudaStream_t);
 int launch_correct_boxes(isb_handle*, const float*, int64_t, int, int, float*, cudaStream_t);
 int launch_crop(isb_handle*, const float*, const float*, int, int, int, float*, cudaStream_t);
-int launch_bounds(isb_handle*, const float*, int, int, int, DetBounds*, cudaStream_t);
+int launch_det_layout(isb_handle*, const float*, int, int, int, int, int, DetRec*, int32_t*, cudaStream_t);
 int launch_mask_logits(isb_handle*, const float*, const float*, int64_t, int, float*, cudaStream_t);
 }  // namespace isb
 
@@ -29,7 +29,7 @@ extern "C" int64_t isb_launch_count(const isb_handle* h) { return h ? h->launche
 
 static void free_profile(isb_handle* h) {
   if (h->prof_events) {
-    for (int i = 0; i < h->prof_cap * 4; ++i) cudaEventDestroy(h->prof_events[i]);
+    for (int i = 0; i < h->prof_cap * 5; ++i) cudaEventDestroy(h->prof_events[i]);
     delete[] h->prof_events;
   }
   h->prof_events = nullptr;
@@ -42,25 +42,25 @@ extern "C" int isb_profile_begin(isb_handle* h, int32_t max_calls) {
   ISB_CUDA(h, cudaSetDevice(h->device));
   free_profile(h);
   if (max_calls == 0) return ISB_OK;
-  h->prof_events = new (std::nothrow) cudaEvent_t[(size_t)max_calls * 4];
+  h->prof_events = new (std::nothrow) cudaEvent_t[(size_t)max_calls * 5];
   if (!h->prof_events) ISB_FAIL(h, ISB_ERR_CUDA, "profile_begin: out of host memory");
-  for (int i = 0; i < max_calls * 4; ++i) ISB_CUDA(h, cudaEventCreate(&h->prof_events[i]));
+  for (int i = 0; i < max_calls * 5; ++i) ISB_CUDA(h, cudaEventCreate(&h->prof_events[i]));
   h->prof_cap = max_calls;
   return ISB_OK;
 }
 
-extern "C" int isb_profile_read(isb_handle* h, double stage_ms[3], int32_t* calls) {
+extern "C" int isb_profile_read(isb_handle* h, double stage_ms[4], int32_t* calls) {
   if (!h) return ISB_ERR_BAD_ARG;
   if (!stage_ms || !calls) ISB_FAIL(h, ISB_ERR_BAD_ARG, "profile_read: null output");
-  stage_ms[0] = stage_ms[1] = stage_ms[2] = 0.0;
+  stage_ms[0] = stage_ms[1] = stage_ms[2] = stage_ms[3] = 0.0;
   *calls = h->prof_used;
   if (h->prof_used == 0) return ISB_OK;
   ISB_CUDA(h, cudaSetDevice(h->device));
-  ISB_CUDA(h, cudaEventSynchronize(h->prof_events[(size_t)(h->prof_used - 1) * 4 + 3]));
+  ISB_CUDA(h, cudaEventSynchronize(h->prof_events[(size_t)(h->prof_used - 1) * 5 + 4]));
   for (int c = 0; c < h->prof_used; ++c)
-    for (int st = 0; st < 3; ++st) {
+    for (int st = 0; st < 4; ++st) {
       float ms = 0.f;
-      ISB_CUDA(h, cudaEventElapsedTime(&ms, h->prof_events[(size_t)c * 4 + st], h->prof_events[(size_t)c * 4 + st + 1]));
+      ISB_CUDA(h, cudaEventElapsedTime(&ms, h->prof_events[(size_t)c * 5 + st], h->prof_events[(size_t)c * 5 + st + 1]));
       stage_ms[st] += ms;
     }
   h->prof_used = 0;
@@ -80,8 +80,8 @@ static void free_ws(isb_handle* h) {
   cudaFree(h->det_keys);
   cudaFree(h->cand_box);
   cudaFree(h->det_coef);
-  cudaFree(h->det_bounds);
   cudaFree(h->det_rec);
+  cudaFree(h->smap_total);
   cudaFree(h->smap);
   cudaFree(h->stage);
   cudaFree(h->nms_keys);
@@ -121,7 +121,7 @@ extern "C" int isb_create(int device, const isb_limits* limits, isb_handle** out
   if (L.max_classes >= (1 << kClassBits)) ISB_FAIL(h, ISB_ERR_LIMIT, "max_classes %d >= 2^%d", L.max_classes, kClassBits);
   if (L.cand_capacity > (1ll << 30)) ISB_FAIL(h, ISB_ERR_LIMIT, "cand_capacity too large");
   h->lim = L;
-  h->cand_cap_pow2 = next_pow2((int)L.cand_capacity);
+  h->cand_cap_pow2 = next_pow2((int)L.cand_capacity) < 64 ? 64 : next_pow2((int)L.cand_capacity);
   ISB_CUDA(h, cudaSetDevice(device));
   cudaDeviceProp prop;
   ISB_CUDA(h, cudaGetDeviceProperties(&prop, device));
@@ -140,8 +140,8 @@ extern "C" int isb_create(int device, const isb_limits* limits, isb_handle** out
   WS_ALLOC(det_keys, B * cap * sizeof(uint64_t));
   WS_ALLOC(cand_box, B * cap * sizeof(float4));
   WS_ALLOC(det_coef, B * (size_t)L.max_det * ISB_NUM_COEF * sizeof(float));
-  WS_ALLOC(det_bounds, B * (size_t)L.max_det * sizeof(DetBounds));
   WS_ALLOC(det_rec, B * (size_t)L.max_det * sizeof(DetRec));
+  WS_ALLOC(smap_total, B * sizeof(int32_t));
 #undef WS_ALLOC
   h->ws_bytes = total;
   int rc;
@@ -180,7 +180,7 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const is
       !aligned4(in->conf) || !aligned16(out->boxes) || !aligned16(out->masks))
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "box/coef/proto/anchors/boxes/masks must be 16-byte aligned, conf 4-byte aligned");
   int rc;
-  cudaEvent_t* ev = (h->prof_events && h->prof_used < h->prof_cap) ? h->prof_events + (size_t)h->prof_used * 4 : nullptr;
+  cudaEvent_t* ev = (h->prof_events && h->prof_used < h->prof_cap) ? h->prof_events + (size_t)h->prof_used * 5 : nullptr;
   if (ev) ISB_CUDA(h, cudaEventRecord(ev[0], s));
   CandParams cp;
   cp.scores = in->conf;
@@ -207,6 +207,8 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const is
   np.correct = 1;
   np.out_h = in->out_h;
   np.out_w = in->out_w;
+  np.proto_h = in->proto_h;
+  np.proto_w = in->proto_w;
   np.out_box = out->boxes;
   np.out_score = out->scores;
   np.out_class = out->class_ids;
@@ -220,7 +222,6 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const is
   mp.batch = in->batch;
   mp.proto = in->proto;
   mp.coef = h->det_coef + (size_t)h->ws_b0 * h->lim.max_det * ISB_NUM_COEF;
-  mp.bounds = h->det_bounds + (size_t)h->ws_b0 * h->lim.max_det;
   mp.counts = out->counts;
   mp.m_fixed = -1;
   mp.det_stride = h->lim.max_det;
@@ -231,9 +232,12 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const is
   mp.masks_arg = out->masks_arg;
   mp.masks = out->masks;
   mp.mask_slot_bytes = out->mask_slot_bytes;
-  if ((rc = launch_masks(h, mp, s)) != ISB_OK) return rc;
+  h->prof_mid = ev ? ev[3] : nullptr;  // recorded between the sigmoid-map and the compose kernel
+  rc = launch_masks(h, mp, s);
+  h->prof_mid = nullptr;
+  if (rc != ISB_OK) return rc;
   if (ev) {
-    ISB_CUDA(h, cudaEventRecord(ev[3], s));
+    ISB_CUDA(h, cudaEventRecord(ev[4], s));
     h->prof_used++;
   }
   return ISB_OK;
@@ -473,14 +477,13 @@ extern "C" int isb_mask_assemble(isb_handle* h, const float* proto, const float*
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_assemble: null or misaligned pointer");
   ISB_CUDA(h, cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
-  int rc = launch_bounds(h, boxes_px, m, out_h, out_w, h->det_bounds, s);
+  int rc = launch_det_layout(h, boxes_px, m, out_h, out_w, proto_h, proto_w, h->det_rec, h->smap_total, s);
   if (rc != ISB_OK) return rc;
   MaskParams mp;
   memset(&mp, 0, sizeof(mp));
   mp.batch = 1;
   mp.proto = proto;
   mp.coef = coef;
-  mp.bounds = h->det_bounds;
   mp.counts = nullptr;
   mp.m_fixed = m;
   mp.det_stride = m;

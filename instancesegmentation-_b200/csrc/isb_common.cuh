@@ -138,6 +138,83 @@ __device__ __forceinline__ void bilinear_src(int dst, float scale, int in_size, 
   i1 = i0 + (i0 < in_size - 1 ? 1 : 0);
 }
 
+// prototype footprint of a crop box: first column/row and extent (0 x 0 for an empty box)
+__device__ __forceinline__ void det_footprint(const DetBounds& bd, float sy, float sx, int ph, int pw, int& pa, int& pya,
+                                              int& fw, int& fh) {
+  pa = pya = fw = fh = 0;
+  if (bd.xlo >= bd.xhi || bd.ylo >= bd.yhi) return;
+  int t0, t1, pb, pyb;
+  float f0, f1;
+  bilinear_src(bd.xlo, sx, pw, pa, t1, f0, f1);
+  bilinear_src(bd.xhi - 1, sx, pw, t0, pb, f0, f1);
+  bilinear_src(bd.ylo, sy, ph, pya, t1, f0, f1);
+  bilinear_src(bd.yhi - 1, sy, ph, t0, pyb, f0, f1);
+  fw = pb - pa + 1;
+  fh = pyb - pya + 1;
+}
+
+// Eight elements of sigmoid maps, computed by 8 cooperating lanes (q = lane & 7): element i of the group is
+// S = sigmoid(proto_vec_i . coef_vec_i) (utils_bbox.py:223 restricted to the prototype pixels a crop box can
+// reach).  Every lane passes the 128-byte prototype / coefficient vectors of ITS element (pp, cf); for each of
+// the 8 elements the pointers are broadcast and lane q loads channels 4q..4q+3, so a vector is read as one
+// coalesced line.  The 8 x 8 partial sums are then transpose-reduced with a fixed xor butterfly (4, 2, 1):
+// lane q returns the complete dot product of element q -- same summation order everywhere this is used.
+__device__ __forceinline__ float smap_dot8(const float4* pp, const float4* cf, int q) {
+  float part[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int src = (threadIdx.x & 24) | i;
+    const float4* pi = reinterpret_cast<const float4*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(pp), src));
+    const float4* ci = reinterpret_cast<const float4*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(cf), src));
+    const float4 a = __ldg(pi + q), c = __ldg(ci + q);
+    float acc = a.x * c.x;
+    acc = fmaf(a.y, c.y, acc);
+    acc = fmaf(a.z, c.z, acc);
+    acc = fmaf(a.w, c.w, acc);
+    part[i] = acc;
+  }
+  float r4[4], r2[2];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const bool up = (q & 4) != 0;
+    const float recv = __shfl_xor_sync(0xffffffffu, up ? part[j] : part[j + 4], 4);
+    r4[j] = (up ? part[j + 4] : part[j]) + recv;
+  }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const bool up = (q & 2) != 0;
+    const float recv = __shfl_xor_sync(0xffffffffu, up ? r4[j] : r4[j + 2], 2);
+    r2[j] = (up ? r4[j + 2] : r4[j]) + recv;
+  }
+  const bool up = (q & 1) != 0;
+  const float recv = __shfl_xor_sync(0xffffffffu, up ? r2[0] : r2[1], 1);
+  return (up ? r2[1] : r2[0]) + recv;
+}
+
+// Exclusive prefix sum of one int per thread over a CTA of up to 1024 threads (warp shuffles + one
+// shared word per warp); every thread must call it.  Returns the exclusive sum, *total the CTA sum.
+__device__ __forceinline__ int cta_exclusive_scan(int v, int* s_warp /* [32] */, int* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int u = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += u;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  int off = 0, tot = 0;
+  const int nw = (blockDim.x + 31) >> 5;
+  for (int w = 0; w < nw; ++w) {
+    const int c = s_warp[w];
+    if (w < warp) off += c;
+    tot += c;
+  }
+  __syncthreads();
+  *total = tot;
+  return off + incl - v;
+}
+
 // ---------------------------------------------------------------------------------------
 // sm_100a async-copy helpers (1-D bulk TMA + mbarrier); SASS: UBLKCP / SYNCS.
 // ---------------------------------------------------------------------------------------
@@ -210,8 +287,8 @@ struct isb_handle {
   uint64_t* det_keys;    // [max_batch][cand_cap_pow2]   kept keys (global fallback of the NMS kernel)
   float4* cand_box;      // [max_batch][cand_cap_pow2]   decoded boxes (global fallback)
   float* det_coef;       // [max_batch][max_det][K]
-  isb::DetBounds* det_bounds;  // [max_batch][max_det]
   isb::DetRec* det_rec;        // [max_batch][max_det]
+  int32_t* smap_total;         // [max_batch] sigmoid-map elements per image
   float* smap;                 // sigmoid-map scratch of the mask kernels, grown on demand
   size_t smap_floats;
   // device staging for the *_host entry points (allocated on first use)
@@ -234,7 +311,8 @@ struct isb_handle {
   void* scratch;
   size_t scratch_bytes;
   // optional per-stage event ring (isb_profile_begin / isb_profile_read)
-  cudaEvent_t* prof_events;  // [prof_cap][4]
+  cudaEvent_t* prof_events;  // [prof_cap][5]
+  cudaEvent_t prof_mid;      // set while a profiled call is inside launch_masks
   int32_t prof_cap, prof_used;
 };
 
@@ -282,6 +360,7 @@ struct NmsParams {
   int32_t top_k, max_det;
   int32_t correct;         // 1: scale/clamp to pixels and emit crop bounds (fused path)
   int32_t out_h, out_w;
+  int32_t proto_h, proto_w; // fused path: prototype size (footprints of the sigmoid maps)
   float* out_box;          // [B, max_det, 4]
   float* out_score;        // [B, max_det]
   int64_t* out_class;      // [B, max_det]
@@ -294,7 +373,6 @@ struct MaskParams {
   int32_t batch;
   const float* proto;        // [B, Ph, Pw, K]
   const float* coef;         // [B, max_det_stride, K]
-  const DetBounds* bounds;   // [B, max_det_stride]
   const int32_t* counts;     // [B]   device; or nullptr when m_fixed >= 0
   int32_t m_fixed;
   int32_t det_stride;        // rows between images in coef / bounds
@@ -304,6 +382,8 @@ struct MaskParams {
   int64_t mask_slot_bytes;
 };
 int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s);
+// grows the sigmoid-map scratch for the handle's limits; returns floats per image in *s_cap
+int ensure_mask_scratch(isb_handle* h, int proto_h, int proto_w, int64_t* s_cap);
 
 struct RoiLevels {
   const float* feat[8];

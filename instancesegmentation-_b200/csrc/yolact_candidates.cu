@@ -6,105 +6,93 @@
 // 64-bit key (class | ~score | row); see DESIGN.md "Exact shortcut" for why entries <= confidence
 // can never change the result.
 //
-// HBM-bound: the score tensor [B, A, C] is read exactly once (6.2 MB / image at COCO 550).
-// A CTA owns ROWS_PER_CTA consecutive rows = one contiguous byte range, pulled into shared memory
-// by a single 1-D bulk-TMA copy (UBLKCP) signalled on an mbarrier; rows are then scanned from
-// shared memory with an odd word stride (C = 81, 21, ...), which is bank-conflict free.
+// HBM-read-bound: the score tensor [B, A, C] is read exactly once (6.2 MB / image at COCO 550) as a flat
+// stream of 16-byte vectors, four independent loads in flight per thread.  Passing entries are rare (about
+// 1 in 1500 at confidence 0.05) apart from the background column, so the common path is
+// load + 4 compares; only a vector with a passing entry pays for the (row, class) index arithmetic and one
+// atomicAdd on the image's candidate counter.  The order of the emitted keys is irrelevant: the NMS kernel
+// sorts them, and keys are unique.
 #include "isb_common.cuh"
 
 namespace isb {
 
-constexpr int kCandThreads = 128;  // one row per thread
+constexpr int kCandThreads = 256;
+constexpr int kCandUnroll = 4;
+constexpr int kCandCtasPerImage = 32;
+
+__device__ __forceinline__ void cand_emit(const CandParams& p, int b, uint32_t e, float s, int32_t* __restrict__ cand_count,
+                                          uint64_t* __restrict__ dst, int64_t cap) {
+  const uint32_t row = e / (uint32_t)p.ncols;
+  const int c = (int)(e - row * (uint32_t)p.ncols);
+  if (c < p.col0) return;
+  if (p.use_threshold) {
+    const int pos = atomicAdd(&cand_count[b], 1);
+    if (pos < cap) dst[pos] = make_cand_key((uint32_t)(c - p.col0), s, row);  // past the capacity: dropped, NMS reports overflow
+  } else {
+    dst[(size_t)row * (p.ncols - p.col0) + (c - p.col0)] = make_cand_key((uint32_t)(c - p.col0), s, row);
+  }
+}
 
 __global__ void __launch_bounds__(kCandThreads)
 candidates_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_t* __restrict__ cand_keys, int64_t cap,
                   int64_t key_stride) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ __align__(8) uint64_t bar;
-  __shared__ int warp_tot[kCandThreads / 32];
-  __shared__ int cta_base;
-
   const int b = blockIdx.y;
-  const int row0 = blockIdx.x * kCandThreads;
-  const int nrows = min(kCandThreads, p.rows - row0);
-  const int tid = threadIdx.x;
-
-  // contiguous byte range of this tile, widened to 16-byte boundaries
-  const char* g0 = reinterpret_cast<const char*>(p.scores + ((size_t)b * p.rows + row0) * p.ncols);
-  const uintptr_t ga = reinterpret_cast<uintptr_t>(g0);
-  const uint32_t head = (uint32_t)(ga & 15);
-  const uint32_t bytes = (head + (uint32_t)nrows * p.ncols * 4u + 15u) & ~15u;
-
-  if (tid == 0) mbar_init(&bar, 1);
-  __syncthreads();
-  if (tid == 0) {
-    mbar_expect_tx(&bar, bytes);
-    bulk_g2s(smem_raw, g0 - head, bytes, &bar);
-  }
-  mbar_wait(&bar, 0);
-
-  const float* tile = reinterpret_cast<const float*>(smem_raw + head);
-  const float* row = tile + (size_t)tid * p.ncols;
-
-  // pass 1: count this row's candidates
-  int cnt = 0;
-  if (tid < nrows) {
-    if (p.use_threshold) {
-      for (int c = p.col0; c < p.ncols; ++c) cnt += (row[c] > p.threshold) ? 1 : 0;
-    } else {
-      cnt = p.ncols - p.col0;
-    }
-  }
-  // block exclusive scan
-  int incl = cnt;
+  const uint32_t per_img = (uint32_t)p.rows * (uint32_t)p.ncols;
+  const float* img = p.scores + (size_t)b * per_img;
+  uint64_t* dst = cand_keys + (size_t)b * key_stride;
+  const float thr = p.threshold;
+  const bool all = !p.use_threshold;
+  // 16-byte aligned body of this image's flat score range; scalar head and tail
+  const uint32_t head = min(per_img, (uint32_t)(((16 - (reinterpret_cast<uintptr_t>(img) & 15)) & 15) >> 2));
+  const uint32_t nvec = (per_img - head) >> 2;
+  const float4* body = reinterpret_cast<const float4*>(img + head);
+  const uint32_t stride = gridDim.x * kCandThreads;
+  uint32_t v = blockIdx.x * kCandThreads + threadIdx.x;
+  for (; v + (kCandUnroll - 1) * stride < nvec; v += kCandUnroll * stride) {
+    float4 x[kCandUnroll];
 #pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    int v = __shfl_up_sync(0xffffffffu, incl, o);
-    if ((tid & 31) >= o) incl += v;
-  }
-  if ((tid & 31) == 31) warp_tot[tid >> 5] = incl;
-  __syncthreads();
-  int warp_off = 0, total = 0;
+    for (int u = 0; u < kCandUnroll; ++u) x[u] = __ldcs(body + v + u * stride);  // streamed once: evict first
 #pragma unroll
-  for (int w = 0; w < kCandThreads / 32; ++w) {
-    int t = warp_tot[w];
-    if (w < (tid >> 5)) warp_off += t;
-    total += t;
-  }
-  if (total == 0) return;
-  if (tid == 0) cta_base = atomicAdd(&cand_count[b], total);
-  __syncthreads();
-  int64_t pos = (int64_t)cta_base + warp_off + incl - cnt;
-
-  // pass 2: emit keys (positions past the capacity are dropped; the NMS kernel reports overflow)
-  if (tid < nrows && cnt > 0) {
-    uint64_t* dst = cand_keys + (size_t)b * key_stride;
-    for (int c = p.col0; c < p.ncols; ++c) {
-      float s = row[c];
-      if (!p.use_threshold || s > p.threshold) {
-        if (pos < cap) dst[pos] = make_cand_key((uint32_t)(c - p.col0), s, (uint32_t)(row0 + tid));
-        ++pos;
+    for (int u = 0; u < kCandUnroll; ++u) {
+      if (all || x[u].x > thr || x[u].y > thr || x[u].z > thr || x[u].w > thr) {
+        const uint32_t e = head + 4 * (v + u * stride);
+        if (all || x[u].x > thr) cand_emit(p, b, e, x[u].x, cand_count, dst, cap);
+        if (all || x[u].y > thr) cand_emit(p, b, e + 1, x[u].y, cand_count, dst, cap);
+        if (all || x[u].z > thr) cand_emit(p, b, e + 2, x[u].z, cand_count, dst, cap);
+        if (all || x[u].w > thr) cand_emit(p, b, e + 3, x[u].w, cand_count, dst, cap);
       }
     }
   }
+  for (; v < nvec; v += stride) {
+    const float4 x = __ldcs(body + v);
+    const uint32_t e = head + 4 * v;
+    if (all || x.x > thr) cand_emit(p, b, e, x.x, cand_count, dst, cap);
+    if (all || x.y > thr) cand_emit(p, b, e + 1, x.y, cand_count, dst, cap);
+    if (all || x.z > thr) cand_emit(p, b, e + 2, x.z, cand_count, dst, cap);
+    if (all || x.w > thr) cand_emit(p, b, e + 3, x.w, cand_count, dst, cap);
+  }
+  if (blockIdx.x == 0) {
+    const uint32_t tail0 = head + 4 * nvec;
+    for (uint32_t e = threadIdx.x; e < head; e += kCandThreads)
+      if (all || img[e] > thr) cand_emit(p, b, e, img[e], cand_count, dst, cap);
+    for (uint32_t e = tail0 + threadIdx.x; e < per_img; e += kCandThreads)
+      if (all || img[e] > thr) cand_emit(p, b, e, img[e], cand_count, dst, cap);
+    if (all && threadIdx.x == 0) cand_count[b] = p.rows * (p.ncols - p.col0);
+  }
 }
 
-static constexpr size_t kCandSmemMax = 200 * 1024;
-
-int configure_candidates(isb_handle* h) {
-  ISB_CUDA(h, cudaFuncSetAttribute(candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCandSmemMax));
-  return ISB_OK;
-}
+int configure_candidates(isb_handle* h) { (void)h; return ISB_OK; }
 
 int launch_candidates(isb_handle* h, const CandParams& p, cudaStream_t s) {
-  // tile bytes + 16 of alignment head + 16 of round-up slack
-  const size_t smem = (size_t)p.ncols * 4 * kCandThreads + 32;
-  if (smem > kCandSmemMax) ISB_FAIL(h, ISB_ERR_LIMIT, "score rows of %d columns do not fit the candidate tile", p.ncols);
+  if ((int64_t)p.rows * p.ncols >= (1ll << 31)) ISB_FAIL(h, ISB_ERR_LIMIT, "score tensor of one image exceeds 2^31 elements");
   ISB_CUDA(h, cudaMemsetAsync(h->cand_count + h->ws_b0, 0, sizeof(int32_t) * p.batch, s));
-  dim3 grid((p.rows + kCandThreads - 1) / kCandThreads, p.batch);
-  candidates_kernel<<<grid, kCandThreads, smem, s>>>(p, h->cand_count + h->ws_b0, h->cand_keys + (size_t)h->ws_b0 * h->cand_cap_pow2,
-                                                     h->lim.cand_capacity,
-                                                     h->cand_cap_pow2);
+  const int64_t nvec = ((int64_t)p.rows * p.ncols) / 4;
+  int ctas = (int)((nvec + (int64_t)kCandThreads * kCandUnroll - 1) / ((int64_t)kCandThreads * kCandUnroll));
+  if (ctas > kCandCtasPerImage) ctas = kCandCtasPerImage;
+  if (ctas < 1) ctas = 1;
+  dim3 grid(ctas, p.batch);
+  candidates_kernel<<<grid, kCandThreads, 0, s>>>(p, h->cand_count + h->ws_b0, h->cand_keys + (size_t)h->ws_b0 * h->cand_cap_pow2,
+                                                  h->lim.cand_capacity, h->cand_cap_pow2);
   ISB_LAUNCH_CHECK(h, "candidates_kernel");
   return ISB_OK;
 }

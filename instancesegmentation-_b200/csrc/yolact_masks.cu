@@ -7,7 +7,7 @@
 // reaches HBM.
 //
 // Two kernels:
-//   K3a sigmoid_map_kernel  one CTA per detection: S_j = sigmoid(proto . coef_j) over the prototype
+//   K3a sigmoid_map_kernel  S_j = sigmoid(proto . coef_j) for every detection j over the prototype
 //       pixels under detection j's crop box only (its "footprint", plus the bilinear halo), written to
 //       an L2-resident scratch (about 0.1 MB per image at the benchmark's box sizes).  Everything outside
 //       a crop box is zero after :230, so nothing else is ever needed.
@@ -30,7 +30,8 @@ namespace isb {
 constexpr int kCompThreads = 512;
 constexpr int kCompWarps = kCompThreads / 32;
 constexpr int kUnitPx = 4096;         // pixels per work unit (8 tiles of 512)
-constexpr int kSmapThreads = 128;
+constexpr int kSmapThreads = 256;
+constexpr int kSmapCtasPerSm = 4;     // persistent CTAs of the sigmoid-map kernel
 
 struct CompGeom {
   int units_per_img;
@@ -43,77 +44,90 @@ struct CompGeom {
 // per-column bilinear table entry: source index pair and weight (image independent)
 struct ColTap { int32_t idx; float l1; };  // idx = ix0 | (ix1 - ix0) << 16
 
-// prototype footprint of a crop box: first column/row and extent (0 x 0 for an empty box)
-__device__ __forceinline__ void det_footprint(const DetBounds& bd, float sy, float sx, int ph, int pw, int& pa, int& pya,
-                                              int& fw, int& fh) {
-  pa = pya = fw = fh = 0;
-  if (bd.xlo >= bd.xhi || bd.ylo >= bd.yhi) return;
-  int t0, t1, pb, pyb;
-  float f0, f1;
-  bilinear_src(bd.xlo, sx, pw, pa, t1, f0, f1);
-  bilinear_src(bd.xhi - 1, sx, pw, t0, pb, f0, f1);
-  bilinear_src(bd.ylo, sy, ph, pya, t1, f0, f1);
-  bilinear_src(bd.yhi - 1, sy, ph, t0, pyb, f0, f1);
-  fw = pb - pa + 1;
-  fh = pyb - pya + 1;
-}
-
 // ---- K3a -----------------------------------------------------------------------------------
+// The sigmoid-map elements of one image are one flat range [0, total_b) laid out detection after detection
+// (DetRec.soff and the per-image totals come from the NMS kernel / the layout kernel).  The batch is cut into
+// tickets of kSmapChunk elements, dealt round-robin to the CTAs, so the work is balanced whatever the box
+// sizes (one image with large boxes does not leave the other SMs idle).  A ticket is mapped to
+// (image, chunk) through the per-image ticket prefix every CTA builds in shared memory; the image's
+// records sit in shared memory too, and the owning detection of an element is found by binary search.
+// Dependent global round trips per CTA: totals -> records -> prototype vectors.
+constexpr int kSmapChunk = 512;                            // elements per ticket
+constexpr int kSmapMaxBatch = 1024;
+
 __global__ void __launch_bounds__(kSmapThreads)
-sigmoid_map_kernel(MaskParams p, float scale_y, float scale_x, DetRec* __restrict__ rec, float* __restrict__ smap,
-                   int64_t s_cap) {
-  __shared__ int s_part[kSmapThreads / 32];
-  const int b = blockIdx.y, j = blockIdx.x, tid = threadIdx.x;
-  const int m = p.counts ? p.counts[b] : p.m_fixed;
-  if (j >= m) return;
-  const DetBounds* bounds = p.bounds + (size_t)b * p.det_stride;
-  // offset of this detection's map = total footprint of the detections before it
-  int part = 0;
-  for (int jj = tid; jj < j; jj += kSmapThreads) {
-    int pa, pya, fw, fh;
-    det_footprint(bounds[jj], scale_y, scale_x, p.proto_h, p.proto_w, pa, pya, fw, fh);
-    part += fw * fh;
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-  if ((tid & 31) == 0) s_part[tid >> 5] = part;
-  __syncthreads();
-  int soff = 0;
-#pragma unroll
-  for (int w = 0; w < kSmapThreads / 32; ++w) soff += s_part[w];
-  const DetBounds bd = bounds[j];
-  int pa, pya, fw, fh;
-  det_footprint(bd, scale_y, scale_x, p.proto_h, p.proto_w, pa, pya, fw, fh);
-  if (tid == 0) {
-    DetRec r;
-    r.xlo = bd.xlo; r.xhi = bd.xhi; r.ylo = bd.ylo; r.yhi = bd.yhi;
-    r.soff = soff;
-    r.pa = (int16_t)pa; r.pya = (int16_t)pya; r.fw = (int16_t)fw; r.fh = (int16_t)fh;
-    r.j = j;
-    rec[(size_t)b * p.det_stride + j] = r;
-  }
-  const int items = fw * fh;
-  if (items == 0) return;
-  const float4* cf = reinterpret_cast<const float4*>(p.coef + ((size_t)b * p.det_stride + j) * ISB_NUM_COEF);
-  float4 c[ISB_NUM_COEF / 4];
-#pragma unroll
-  for (int q = 0; q < ISB_NUM_COEF / 4; ++q) c[q] = __ldg(cf + q);
-  const float* proto_img = p.proto + (size_t)b * p.proto_h * p.proto_w * ISB_NUM_COEF;
-  float* S = smap + (size_t)b * s_cap + soff;
-  for (int t = tid; t < items; t += kSmapThreads) {
-    const int fy = t / fw, fx = t - fy * fw;
-    const float4* pp = reinterpret_cast<const float4*>(
-        proto_img + ((size_t)(pya + fy) * p.proto_w + (pa + fx)) * ISB_NUM_COEF);
-    float acc = 0.0f;
-#pragma unroll
-    for (int q = 0; q < ISB_NUM_COEF / 4; ++q) {
-      const float4 a = __ldg(pp + q);
-      acc = fmaf(a.x, c[q].x, acc);
-      acc = fmaf(a.y, c[q].y, acc);
-      acc = fmaf(a.z, c[q].z, acc);
-      acc = fmaf(a.w, c[q].w, acc);
+sigmoid_map_kernel(MaskParams p, const DetRec* __restrict__ rec, const int32_t* __restrict__ totals,
+                   float* __restrict__ smap, int64_t s_cap) {
+  extern __shared__ __align__(16) unsigned char s_dyn[];  // DetRec s_rec[list_cap]
+  __shared__ int s_cstart[kSmapMaxBatch + 1];             // first ticket of every image
+  __shared__ int s_scan[32];
+  DetRec* s_rec = reinterpret_cast<DetRec*>(s_dyn);
+  const int tid = threadIdx.x;
+  int carry = 0;
+  for (int base = 0; base < p.batch; base += kSmapThreads) {
+    const int b = base + tid;
+    int chunks = 0;
+    if (b < p.batch) {
+      const int m = p.counts ? p.counts[b] : p.m_fixed;
+      if (m > 0) chunks = (totals[b] + kSmapChunk - 1) / kSmapChunk;
     }
-    S[t] = sigmoidf_ref(acc);
+    int tot;
+    const int excl = cta_exclusive_scan(chunks, s_scan, &tot);
+    if (b < p.batch) s_cstart[b] = carry + excl;
+    carry += tot;
+  }
+  if (tid == 0) s_cstart[p.batch] = carry;
+  __syncthreads();
+  const int ntickets = carry;
+  int cached = -1, m = 0, total = 0;
+  const int per_cta = (ntickets + gridDim.x - 1) / gridDim.x;  // contiguous tickets: a CTA stays within one or two images
+  const int ticket_end = min(ntickets, ((int)blockIdx.x + 1) * per_cta);
+  for (int ticket = blockIdx.x * per_cta; ticket < ticket_end; ++ticket) {
+    int lo = 0, hi = p.batch - 1;  // image: last b with s_cstart[b] <= ticket
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (s_cstart[mid] <= ticket) lo = mid; else hi = mid - 1;
+    }
+    const int b = lo;
+    if (b != cached) {  // CTA-uniform
+      __syncthreads();  // previous image's records consumed
+      m = p.counts ? p.counts[b] : p.m_fixed;
+      total = totals[b];
+      const DetRec* rimg = rec + (size_t)b * p.det_stride;
+      for (int j = tid; j < m; j += kSmapThreads) s_rec[j] = rimg[j];
+      cached = b;
+      __syncthreads();
+    }
+    const int t0 = (ticket - s_cstart[b]) * kSmapChunk;
+    const float* proto_img = p.proto + (size_t)b * p.proto_h * p.proto_w * ISB_NUM_COEF;
+    const float* coef_img = p.coef + (size_t)b * p.det_stride * ISB_NUM_COEF;
+    float* S = smap + (size_t)b * s_cap;
+    // a group of 8 lanes takes 8 consecutive elements per pass: each lane resolves (detection, pixel) of its own
+    // element, the loads and partial sums are shared across the group (smap_dot8)
+    const int q = tid & 7;
+    int l = 0;
+    DetRec r = s_rec[0];
+#pragma unroll
+    for (int i = 0; i < kSmapChunk / kSmapThreads; ++i) {
+      const int t = t0 + i * kSmapThreads + tid;
+      const bool on = t < total;  // lanes past the end recompute the last element: the shuffles need every lane
+      const int tt = on ? t : total - 1;
+      if (tt < r.soff || tt >= r.soff + (int)r.fw * (int)r.fh) {
+        int h2 = m - 1;  // last j with soff <= t (empty footprints share an offset: take the last)
+        l = 0;
+        while (l < h2) {
+          const int mid = (l + h2 + 1) >> 1;
+          if (s_rec[mid].soff <= tt) l = mid; else h2 = mid - 1;
+        }
+        r = s_rec[l];
+      }
+      const int f = tt - r.soff, fw = r.fw;
+      const int fy = f / fw, fx = f - fy * fw;
+      const float4* pp = reinterpret_cast<const float4*>(proto_img + ((size_t)(r.pya + fy) * p.proto_w + (r.pa + fx)) * ISB_NUM_COEF);
+      const float4* cf = reinterpret_cast<const float4*>(coef_img + (size_t)l * ISB_NUM_COEF);
+      const float v = sigmoidf_ref(smap_dot8(pp, cf, q));
+      if (on) S[t] = v;
+    }
   }
 }
 
@@ -317,6 +331,11 @@ static int ensure_smap(isb_handle* h, size_t floats) {
   return ISB_OK;
 }
 
+int ensure_mask_scratch(isb_handle* h, int proto_h, int proto_w, int64_t* s_cap) {
+  *s_cap = (int64_t)h->lim.max_det * proto_h * proto_w;  // worst case: every box covers the whole image
+  return ensure_smap(h, (size_t)h->lim.max_batch * (size_t)*s_cap);
+}
+
 int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   if (p.proto_w >= 32768 || p.proto_h >= 32768) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports prototype sides < 32768");
   if ((int64_t)p.out_h * p.out_w >= (1ll << 31) / 8) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly: output image too large");
@@ -327,7 +346,6 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   g.scale_y = (float)p.proto_h / (float)p.out_h;
   g.scale_x = (float)p.proto_w / (float)p.out_w;
   g.list_cap = p.m_fixed >= 0 ? (p.m_fixed > 0 ? p.m_fixed : 1) : p.det_stride;
-  g.s_cap = (int64_t)h->lim.max_det * p.proto_h * p.proto_w;  // worst case: every box covers the whole image
   const size_t fixed = (((size_t)p.out_w * sizeof(ColTap) + 31) & ~(size_t)31) + (size_t)g.list_cap * sizeof(DetRec);
   const size_t want = ((size_t)kCompThreads * g.list_cap + 16 + 127) & ~(size_t)127;  // a full 512-pixel tile
   const size_t need = ((size_t)32 * g.list_cap + 16 + 127) & ~(size_t)127;            // at least one warp of pixels
@@ -338,20 +356,23 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   if (buf > want) buf = want;
   g.buf_bytes = (int)buf;
   const size_t smem = fixed + 2 * buf;
-  int rc = ensure_smap(h, (size_t)h->lim.max_batch * (size_t)g.s_cap);
+  int rc = ensure_mask_scratch(h, p.proto_h, p.proto_w, &g.s_cap);
   if (rc != ISB_OK) return rc;
   const int64_t total_units = (int64_t)p.batch * g.units_per_img;
   if (total_units == 0) return ISB_OK;
   DetRec* rec = h->det_rec + (size_t)h->ws_b0 * h->lim.max_det;
   float* smap = h->smap + (size_t)h->ws_b0 * g.s_cap;
-  sigmoid_map_kernel<<<dim3(g.list_cap, p.batch), kSmapThreads, 0, s>>>(p, g.scale_y, g.scale_x, rec, smap, g.s_cap);
+  if (p.batch > kSmapMaxBatch) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports at most %d images per call", kSmapMaxBatch);
+  int* counters = h->work_counter + h->ws_lane;
+  ISB_CUDA(h, cudaMemsetAsync(counters, 0, sizeof(int), s));
+  sigmoid_map_kernel<<<h->num_sms * kSmapCtasPerSm, kSmapThreads, (size_t)g.list_cap * sizeof(DetRec), s>>>(
+      p, rec, h->smap_total + h->ws_b0, smap, g.s_cap);
   ISB_LAUNCH_CHECK(h, "sigmoid_map_kernel");
+  if (h->prof_mid) ISB_CUDA(h, cudaEventRecord(h->prof_mid, s));
   const int per_sm = smem + 1024 <= (size_t)kCompSmemTwo + 2048 ? 2 : 1;
   int64_t grid = (int64_t)h->num_sms * per_sm;
   if (grid > total_units) grid = total_units;
-  int* counter = h->work_counter + h->ws_lane;
-  ISB_CUDA(h, cudaMemsetAsync(counter, 0, sizeof(int), s));
-  mask_compose_kernel<<<(unsigned)grid, kCompThreads, smem, s>>>(p, g, rec, smap, counter);
+  mask_compose_kernel<<<(unsigned)grid, kCompThreads, smem, s>>>(p, g, rec, smap, counters);
   ISB_LAUNCH_CHECK(h, "mask_compose_kernel");
   return ISB_OK;
 }

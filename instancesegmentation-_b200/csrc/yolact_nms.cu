@@ -24,22 +24,73 @@ namespace isb {
 
 constexpr int kNmsThreads = 1024;
 constexpr int kSmemCand = 4096;
+constexpr size_t kNmsSmem = (size_t)kSmemCand * (8 + 8 + 16);  // keys, kept keys, boxes
 
-__device__ void bitonic_sort_u64(uint64_t* k, int n /* power of two */) {
-  for (int size = 2; size <= n; size <<= 1) {
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+// Compare-exchange of register-resident keys across the lanes of a warp: element index i, partner i ^ stride.
+__device__ __forceinline__ void cmpx_lane(uint64_t& v, int i, int stride, int size) {
+  const uint64_t o = __shfl_xor_sync(0xffffffffu, v, stride);
+  const bool lower = (i & stride) == 0;
+  const bool asc = (i & size) == 0;  // size > stride, so both partners agree
+  const bool take_min = lower == asc;
+  v = ((v < o) == take_min) ? v : o;
+}
+
+// Strides 32, 16, .., 1 of merge level `size` (>= 64) for one 64-key block, in registers.
+__device__ __forceinline__ void bitonic_tail64(uint64_t* k, int base, int size, int lane) {
+  const int ia = base + lane, ib = ia + 32;
+  uint64_t a = k[ia], b = k[ib];
+  if ((a > b) == ((ia & size) == 0)) { const uint64_t t = a; a = b; b = t; }
+#pragma unroll
+  for (int stride = 16; stride > 0; stride >>= 1) {
+    cmpx_lane(a, ia, stride, size);
+    cmpx_lane(b, ib, stride, size);
+  }
+  k[ia] = a;
+  k[ib] = b;
+}
+
+// Ascending bitonic sort of n keys (n a power of two >= 64) by the whole CTA.  Every compare-exchange
+// with stride <= 32 runs on register-resident keys through warp shuffles (a warp owns a 64-key block);
+// only the strides >= 64 go through memory with a CTA barrier: 18 barriers instead of 55 at n = 1024.
+__device__ void bitonic_sort_u64(uint64_t* k, int n) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  __syncthreads();
+  for (int blk = warp; blk < (n >> 6); blk += nwarps) {  // sizes 2..64 without touching memory in between
+    const int base = blk << 6, ia = base + lane, ib = ia + 32;
+    uint64_t a = k[ia], b = k[ib];
+#pragma unroll
+    for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        cmpx_lane(a, ia, stride, size);
+        cmpx_lane(b, ib, stride, size);
+      }
+    }
+    if ((a > b) == ((ia & 64) == 0)) { const uint64_t t = a; a = b; b = t; }
+#pragma unroll
+    for (int stride = 16; stride > 0; stride >>= 1) {
+      cmpx_lane(a, ia, stride, 64);
+      cmpx_lane(b, ib, stride, 64);
+    }
+    k[ia] = a;
+    k[ib] = b;
+  }
+  for (int size = 128; size <= n; size <<= 1) {
+    for (int stride = size >> 1; stride >= 64; stride >>= 1) {
       __syncthreads();
       for (int t = threadIdx.x; t < (n >> 1); t += blockDim.x) {
-        int lo = 2 * t - (t & (stride - 1));
-        int hi = lo + stride;
-        bool asc = (lo & size) == 0;
-        uint64_t a = k[lo], b = k[hi];
+        const int lo = 2 * t - (t & (stride - 1));
+        const int hi = lo + stride;
+        const bool asc = (lo & size) == 0;
+        const uint64_t a = k[lo], b = k[hi];
         if ((a > b) == asc) {
           k[lo] = b;
           k[hi] = a;
         }
       }
     }
+    __syncthreads();
+    for (int blk = warp; blk < (n >> 6); blk += nwarps) bitonic_tail64(k, blk << 6, size, lane);
   }
   __syncthreads();
 }
@@ -54,9 +105,11 @@ __device__ __forceinline__ float4 load_box(const NmsParams& p, int b, uint32_t r
 __global__ void __launch_bounds__(kNmsThreads, 1)
 fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* __restrict__ g_keys,
                 uint64_t* __restrict__ g_det, float4* __restrict__ g_box, int64_t cap, int64_t stride,
-                float* __restrict__ det_coef_ws, DetBounds* __restrict__ det_bounds_ws, int ws_det_stride) {
+                float* __restrict__ det_coef_ws, DetRec* __restrict__ det_rec_ws, int32_t* __restrict__ smap_total_ws,
+                int ws_det_stride) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_kept;
+  __shared__ int s_scan[32];
 
   const int b = blockIdx.x;
   const int tid = threadIdx.x;
@@ -70,7 +123,7 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
     if (tid == 0) p.out_count[b] = 0;
     return;
   }
-  const int np2 = next_pow2(n);
+  const int np2 = max(64, next_pow2(n));
   const bool in_smem = np2 <= kSmemCand;
   uint64_t* keys = in_smem ? reinterpret_cast<uint64_t*>(smem_raw) : g_keys + (size_t)b * stride;
   uint64_t* dkeys = in_smem ? reinterpret_cast<uint64_t*>(smem_raw) + kSmemCand : g_det + (size_t)b * stride;
@@ -111,8 +164,14 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
       const float aj = box_area(bj);
       for (int i = start; i < j; ++i) {
         const float4 bi = cbox[i];
-        float v = iou_pair(bi, box_area(bi), bj, aj);
-        if (!(v <= p.nms_iou)) { keep = false; break; }
+        // utils_bbox.py:38-47, with the division skipped when the boxes are disjoint: 0 / union is +-0 for
+        // every finite non-zero union, and thr_ok already established 0 <= nms_iou
+        const float dx = fmaxf(fminf(bi.z, bj.z) - fmaxf(bi.x, bj.x), 0.0f);
+        const float dy = fmaxf(fminf(bi.w, bj.w) - fmaxf(bi.y, bj.y), 0.0f);
+        const float inter = dx * dy;
+        const float uni = (box_area(bi) + aj) - inter;
+        if (inter == 0.0f && uni != 0.0f && fabsf(uni) <= 3.402823466e38f) continue;
+        if (!(inter / uni <= p.nms_iou)) { keep = false; break; }
       }
     }
     if (keep) {
@@ -124,27 +183,44 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
 
   // ---- 4. global order: score desc, class asc, row asc; keep max_det --------------------
   const int kept = s_kept;
-  const int kp2 = next_pow2(kept);
+  const int kp2 = max(64, next_pow2(kept));
   for (int i = kept + tid; i < kp2; i += kNmsThreads) dkeys[i] = kPadKey;
   bitonic_sort_u64(dkeys, kp2);
   const int m = min(kept, p.max_det);
 
   // ---- 5. outputs -----------------------------------------------------------------------
   const float wf = (float)p.out_w, hf = (float)p.out_h;
-  for (int d = tid; d < m; d += kNmsThreads) {
-    const uint64_t k = dkeys[d];
-    const uint32_t row = det_row(k);
-    float4 bx = load_box(p, b, row);
-    if (p.correct) {
-      bx = correct_box(bx, wf, hf);
-      DetBounds db;
-      crop_range(bx.x, bx.z, p.out_w, db.xlo, db.xhi);
-      crop_range(bx.y, bx.w, p.out_h, db.ylo, db.yhi);
-      det_bounds_ws[(size_t)b * ws_det_stride + d] = db;
+  const float sy = (float)p.proto_h / hf, sx = (float)p.proto_w / wf;
+  for (int d0 = 0; d0 < m; d0 += kNmsThreads) {  // max_det <= 1024: one trip
+    const int d = d0 + tid;
+    DetRec rc;
+    int items = 0;
+    if (d < m) {
+      const uint64_t k = dkeys[d];
+      const uint32_t row = det_row(k);
+      float4 bx = load_box(p, b, row);
+      if (p.correct) {
+        bx = correct_box(bx, wf, hf);
+        DetBounds db;
+        crop_range(bx.x, bx.z, p.out_w, db.xlo, db.xhi);
+        crop_range(bx.y, bx.w, p.out_h, db.ylo, db.yhi);
+        int pa, pya, fw, fh;
+        det_footprint(db, sy, sx, p.proto_h, p.proto_w, pa, pya, fw, fh);
+        rc.xlo = db.xlo; rc.xhi = db.xhi; rc.ylo = db.ylo; rc.yhi = db.yhi;
+        rc.pa = (int16_t)pa; rc.pya = (int16_t)pya; rc.fw = (int16_t)fw; rc.fh = (int16_t)fh;
+        rc.j = d;
+        items = fw * fh;
+      }
+      reinterpret_cast<float4*>(p.out_box)[(size_t)b * p.max_det + d] = bx;
+      p.out_score[(size_t)b * p.max_det + d] = det_score(k);
+      p.out_class[(size_t)b * p.max_det + d] = (int64_t)det_class(k);
     }
-    reinterpret_cast<float4*>(p.out_box)[(size_t)b * p.max_det + d] = bx;
-    p.out_score[(size_t)b * p.max_det + d] = det_score(k);
-    p.out_class[(size_t)b * p.max_det + d] = (int64_t)det_class(k);
+    if (p.correct) {  // offsets of the detections' sigmoid maps in the per-image scratch (mask kernels)
+      int total;
+      rc.soff = cta_exclusive_scan(items, s_scan, &total);
+      if (d < m) det_rec_ws[(size_t)b * ws_det_stride + d] = rc;
+      if (tid == 0) smap_total_ws[b] = total;  // max_det <= 1024: the single trip's total is the image's
+    }
   }
   // coefficient rows: one warp-quarter (8 lanes x float4) per detection
   {
@@ -160,7 +236,6 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
   if (tid == 0) p.out_count[b] = m;
 }
 
-static constexpr size_t kNmsSmem = (size_t)kSmemCand * (8 + 8 + 16);
 
 int configure_fast_nms(isb_handle* h) {
   ISB_CUDA(h, cudaFuncSetAttribute(fast_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kNmsSmem));
@@ -172,7 +247,7 @@ int launch_fast_nms(isb_handle* h, const NmsParams& p, cudaStream_t s) {
   fast_nms_kernel<<<p.batch, kNmsThreads, kNmsSmem, s>>>(
       p, h->cand_count + b0, h->cand_keys + b0 * cap2, h->det_keys + b0 * cap2, h->cand_box + b0 * cap2,
       h->lim.cand_capacity, h->cand_cap_pow2, h->det_coef + b0 * h->lim.max_det * ISB_NUM_COEF,
-      h->det_bounds + b0 * h->lim.max_det, h->lim.max_det);
+      h->det_rec + b0 * h->lim.max_det, h->smap_total + b0, h->lim.max_det);
   ISB_LAUNCH_CHECK(h, "fast_nms_kernel");
   return ISB_OK;
 }

@@ -54,15 +54,32 @@ __global__ void crop_kernel(const float* __restrict__ masks, const float4* __res
   }
 }
 
-// pixel-space boxes -> integer crop ranges for the mask kernel (stage entry isb_mask_assemble)
-__global__ void bounds_kernel(const float4* __restrict__ boxes, int m, int hgt, int wid, DetBounds* __restrict__ out) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= m) return;
-  const float4 bx = boxes[j];
-  DetBounds db;
-  crop_range(bx.x, bx.z, wid, db.xlo, db.xhi);
-  crop_range(bx.y, bx.w, hgt, db.ylo, db.yhi);
-  out[j] = db;
+// pixel-space boxes -> per-detection records of the mask kernels: integer crop ranges, prototype footprint and
+// the offset of the detection's sigmoid map (stage entry isb_mask_assemble; the fused path does this in the
+// NMS kernel).  One CTA, m <= 1024.
+__global__ void __launch_bounds__(1024) det_layout_kernel(const float4* __restrict__ boxes, int m, int hgt, int wid,
+                                                          int proto_h, int proto_w, DetRec* __restrict__ out,
+                                                          int32_t* __restrict__ total_out) {
+  __shared__ int s_scan[32];
+  const int j = threadIdx.x;
+  DetRec rc;
+  int items = 0;
+  if (j < m) {
+    const float4 bx = boxes[j];
+    DetBounds db;
+    crop_range(bx.x, bx.z, wid, db.xlo, db.xhi);
+    crop_range(bx.y, bx.w, hgt, db.ylo, db.yhi);
+    int pa, pya, fw, fh;
+    det_footprint(db, (float)proto_h / (float)hgt, (float)proto_w / (float)wid, proto_h, proto_w, pa, pya, fw, fh);
+    rc.xlo = db.xlo; rc.xhi = db.xhi; rc.ylo = db.ylo; rc.yhi = db.yhi;
+    rc.pa = (int16_t)pa; rc.pya = (int16_t)pya; rc.fw = (int16_t)fw; rc.fh = (int16_t)fh;
+    rc.j = j;
+    items = fw * fh;
+  }
+  int total;
+  rc.soff = cta_exclusive_scan(items, s_scan, &total);
+  if (j < m) out[j] = rc;
+  if (j == 0) *total_out = total;
 }
 
 // utils_bbox.py:223 inner product: logits[pix, j] = sum_k proto[pix, k] * coef[j, k]
@@ -124,9 +141,10 @@ int launch_crop(isb_handle* h, const float* masks, const float* boxes, int hgt, 
   ISB_LAUNCH_CHECK(h, "crop_kernel");
   return ISB_OK;
 }
-int launch_bounds(isb_handle* h, const float* boxes, int m, int hgt, int wid, DetBounds* out, cudaStream_t s) {
-  bounds_kernel<<<(m + 127) / 128, 128, 0, s>>>(reinterpret_cast<const float4*>(boxes), m, hgt, wid, out);
-  ISB_LAUNCH_CHECK(h, "bounds_kernel");
+int launch_det_layout(isb_handle* h, const float* boxes, int m, int hgt, int wid, int proto_h, int proto_w, DetRec* out,
+                      int32_t* total_out, cudaStream_t s) {
+  det_layout_kernel<<<1, 1024, 0, s>>>(reinterpret_cast<const float4*>(boxes), m, hgt, wid, proto_h, proto_w, out, total_out);
+  ISB_LAUNCH_CHECK(h, "det_layout_kernel");
   return ISB_OK;
 }
 int launch_mask_logits(isb_handle* h, const float* proto, const float* coef, int64_t npix, int m, float* out,
