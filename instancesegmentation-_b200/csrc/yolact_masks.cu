@@ -29,7 +29,8 @@ namespace isb {
 
 constexpr int kCompThreads = 512;
 constexpr int kCompWarps = kCompThreads / 32;
-constexpr int kUnitPx = 4096;         // pixels per work unit (8 tiles of 512)
+constexpr int kUnitPx = 4096;         // pixels per work unit (128 segments of 32)
+constexpr int kYTabRows = 64;         // rows of a unit with tabulated bilinear taps (more: computed directly)
 constexpr int kSmapThreads = 256;
 constexpr int kSmapCtasPerSm = 4;     // persistent CTAs of the sigmoid-map kernel
 
@@ -37,7 +38,7 @@ struct CompGeom {
   int units_per_img;
   float scale_y, scale_x;
   int list_cap;        // detections per image upper bound
-  int buf_bytes;       // bytes of one tile buffer (multiple of 128)
+  int buf_bytes;       // bytes of one warp's segment buffer (multiple of 16), two per warp
   int64_t s_cap;       // floats of sigmoid-map scratch per image
 };
 
@@ -151,18 +152,23 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
   __shared__ int s_unit;
   __shared__ int s_wcount[kCompWarps];
   __shared__ int s_nlist;
+  __shared__ ColTap s_ytab[kYTabRows];
 
   const int H = p.out_h, W = p.out_w;
-  ColTap* s_xtab = reinterpret_cast<ColTap*>(smem_raw + 2 * (size_t)g.buf_bytes);
-  DetRec* s_det = reinterpret_cast<DetRec*>(smem_raw + 2 * (size_t)g.buf_bytes + (((size_t)W * sizeof(ColTap) + 31) & ~(size_t)31));
-
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nwarps = blockDim.x >> 5;
+  // layout: [nwarps][2] segment buffers | column taps | listed detection records
+  uint8_t* wbuf = smem_raw + (size_t)warp * 2 * g.buf_bytes;
+  const size_t off_tab = (size_t)nwarps * 2 * g.buf_bytes;
+  ColTap* s_xtab = reinterpret_cast<ColTap*>(smem_raw + off_tab);
+  DetRec* s_det = reinterpret_cast<DetRec*>(smem_raw + off_tab + (((size_t)W * sizeof(ColTap) + 31) & ~(size_t)31));
+
   const int total_units = p.batch * g.units_per_img;
   const int HW = H * W;
 
-  // ---- once per CTA: clean tile buffers, per-column bilinear taps ---------------------------------
-  for (int i = tid; i < 2 * g.buf_bytes / 16; i += kCompThreads) reinterpret_cast<uint4*>(smem_raw)[i] = make_uint4(0, 0, 0, 0);
-  for (int x = tid; x < W; x += kCompThreads) {
+  // ---- once per CTA: clean segment buffers, per-column bilinear taps -----------------------------
+  for (int i = tid; i < nwarps * 2 * g.buf_bytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem_raw)[i] = make_uint4(0, 0, 0, 0);
+  for (int x = tid; x < W; x += blockDim.x) {
     int ix0, ix1;
     float l0, l1;
     bilinear_src(x, g.scale_x, p.proto_w, ix0, ix1, l0, l1);
@@ -171,8 +177,8 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
     t.l1 = l1;
     s_xtab[x] = t;
   }
-  int dlo0 = 0, dhi0 = 0, dlo1 = 0, dhi1 = 0;  // this warp's dirty byte range in each buffer
-  unsigned tile_no = 0;
+  int dlo0 = 0, dhi0 = 0, dlo1 = 0, dhi1 = 0;  // this warp's dirty byte range in each of its buffers
+  unsigned seg_no = 0;
 
   while (true) {
     __syncthreads();  // everyone is done with the previous unit's list (and s_unit)
@@ -191,10 +197,20 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
     int64_t* arg_img = p.masks_arg + (size_t)b * HW;
     const float* S_img = smap + (size_t)b * g.s_cap;
 
-    // ---- list the detections whose crop rectangle meets the unit's rows (ascending index) ---------
+    // ---- per-row bilinear taps of the unit's rows, detections that meet those rows (ascending index) ----
+    const bool ytab_ok = yb - ya < kYTabRows;
+    if (ytab_ok && tid <= yb - ya) {
+      int iy0, iy1;
+      float l0, l1;
+      bilinear_src(ya + tid, g.scale_y, p.proto_h, iy0, iy1, l0, l1);
+      ColTap t;
+      t.idx = iy0 | ((iy1 - iy0) << 16);
+      t.l1 = l1;
+      s_ytab[tid] = t;
+    }
     if (tid == 0) s_nlist = 0;
     __syncthreads();
-    for (int base = 0; base < m; base += kCompThreads) {
+    for (int base = 0; base < m; base += blockDim.x) {
       const int j = base + tid;
       bool hit = false;
       DetRec r;
@@ -206,8 +222,7 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
       if (lane == 0) s_wcount[warp] = __popc(bal);
       __syncthreads();
       int off = s_nlist, tot = 0;
-#pragma unroll
-      for (int w = 0; w < kCompWarps; ++w) {
+      for (int w = 0; w < nwarps; ++w) {
         const int c = s_wcount[w];
         if (w < warp) off += c;
         tot += c;
@@ -218,97 +233,99 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
       __syncthreads();
     }
     const int nlist = s_nlist;
-    const int tile_px = min(kCompThreads, ((g.buf_bytes - 16) / m) & ~31);
 
-    // ---- tiles ----------------------------------------------------------------------------------------
-    for (int q0 = px0; q0 < px1; q0 += tile_px, ++tile_no) {
-      const int nt = min(tile_px, px1 - q0);
-      const int par = tile_no & 1;
-      uint8_t* buf = smem_raw + (par ? g.buf_bytes : 0);
+    // ---- segments of 32 pixels: every warp runs its own, independently of the other warps ---------------
+    int xq = (px0 - ya * W) + warp * 32 + lane, yq = ya;  // this lane's pixel in the warp's first segment
+    while (xq >= W) { xq -= W; ++yq; }
+    for (int q0 = px0 + warp * 32; q0 < px1; q0 += nwarps * 32, ++seg_no) {
+      const int nt = min(32, px1 - q0);
+      const int par = seg_no & 1;
+      uint8_t* buf = wbuf + (par ? g.buf_bytes : 0);
       uint8_t* g0 = out_img + (int64_t)q0 * m;
       const int shift = (int)(reinterpret_cast<uintptr_t>(g0) & 15);
-      // the bulk store issued from this buffer two tiles ago must have finished reading it
-      if (tid == 0) bulk_wait_read1();
-      __syncthreads();
+      // the bulk store issued from this buffer two segments ago must have finished reading it
+      if (lane == 0) bulk_wait_read1();
+      __syncwarp();
       {
         const int dlo = par ? dlo1 : dlo0, dhi = par ? dhi1 : dhi0;
-        if (dhi > dlo) warp_clear(buf, dlo, dhi, lane);
+        if (dhi > dlo) {
+          warp_clear(buf, dlo, dhi, lane);
+          __syncwarp();
+        }
       }
-      const bool active = tid < nt;
-      const int q = q0 + tid;
-      const int y = active ? q / W : 0, x = active ? q - y * W : 0;
+      const bool active = lane < nt;
+      const int y = yq, x = xq;
+      const int wy0 = __shfl_sync(0xffffffffu, y, 0), wy1 = __shfl_sync(0xffffffffu, y, nt - 1);
+      int wxa = 0, wxb = W;
+      if (wy0 == wy1) { wxa = __shfl_sync(0xffffffffu, x, 0); wxb = wxa + nt; }
+      int iy0, iy1;
+      float ly0, ly1;
+      if (ytab_ok) {
+        const ColTap ty = s_ytab[min(y, yb) - ya];
+        iy0 = ty.idx & 0xffff; iy1 = iy0 + (ty.idx >> 16);
+        ly1 = ty.l1; ly0 = 1.0f - ly1;
+      } else {
+        bilinear_src(min(y, H - 1), g.scale_y, p.proto_h, iy0, iy1, ly0, ly1);
+      }
+      const ColTap tb = s_xtab[x];
+      const int ix0 = tb.idx & 0xffff, ix1 = ix0 + (tb.idx >> 16);
+      const float lx1 = tb.l1, lx0 = 1.0f - lx1;
+      uint8_t* mypix = buf + shift + lane * m;
       float best = 0.0f;
       int arg = 0;
       bool anyset = false;
-      const int wq0 = q0 + warp * 32;
-      if (wq0 < q0 + nt) {  // warp has pixels in this tile
-        const int wq1 = min(wq0 + 32, q0 + nt);
-        const int wy0 = wq0 / W, wy1 = (wq1 - 1) / W;
-        int wxa = 0, wxb = W;
-        if (wy0 == wy1) { wxa = wq0 - wy0 * W; wxb = wxa + (wq1 - wq0); }
-        int iy0, iy1;
-        float ly0, ly1;
-        bilinear_src(y, g.scale_y, p.proto_h, iy0, iy1, ly0, ly1);
-        const ColTap tb = s_xtab[x];
-        const int ix0 = tb.idx & 0xffff, ix1 = ix0 + (tb.idx >> 16);
-        const float lx1 = tb.l1, lx0 = 1.0f - lx1;
-        uint8_t* mypix = buf + shift + tid * m;
-        for (int base = 0; base < nlist; base += 32) {
-          bool hit = false;
-          if (base + lane < nlist) {
-            const int4 bb = *reinterpret_cast<const int4*>(&s_det[base + lane]);  // xlo, xhi, ylo, yhi
-            hit = bb.z <= wy1 && bb.w > wy0 && bb.x < wxb && bb.y > wxa;
-          }
-          unsigned bal = __ballot_sync(0xffffffffu, hit);
-          while (bal) {
-            const int k = __ffs(bal) - 1;
-            bal &= bal - 1;
-            const DetRec r = s_det[base + k];
-            if (active && y >= r.ylo && y < r.yhi && x >= r.xlo && x < r.xhi) {
-              const float* S = S_img + r.soff;
-              const int fw = r.fw;
-              const int r0 = (iy0 - r.pya) * fw - r.pa, r1 = (iy1 - r.pya) * fw - r.pa;
-              const float top = lx0 * __ldg(S + r0 + ix0) + lx1 * __ldg(S + r0 + ix1);
-              const float bot = lx0 * __ldg(S + r1 + ix0) + lx1 * __ldg(S + r1 + ix1);
-              const float v = ly0 * top + ly1 * bot;
-              if (v > 0.5f) { mypix[r.j] = 1; anyset = true; }
-              if (v > best) { best = v; arg = r.j; }
-            }
+      for (int base = 0; base < nlist; base += 32) {
+        bool hit = false;
+        if (base + lane < nlist) {
+          const int4 bb = *reinterpret_cast<const int4*>(&s_det[base + lane]);  // xlo, xhi, ylo, yhi
+          hit = bb.z <= wy1 && bb.w > wy0 && bb.x < wxb && bb.y > wxa;
+        }
+        unsigned bal = __ballot_sync(0xffffffffu, hit);
+        while (bal) {
+          const int k = __ffs(bal) - 1;
+          bal &= bal - 1;
+          const DetRec r = s_det[base + k];
+          if (active && y >= r.ylo && y < r.yhi && x >= r.xlo && x < r.xhi) {
+            const float* S = S_img + r.soff;
+            const int fw = r.fw;
+            const int r0 = (iy0 - r.pya) * fw - r.pa, r1 = (iy1 - r.pya) * fw - r.pa;
+            const float top = lx0 * __ldg(S + r0 + ix0) + lx1 * __ldg(S + r0 + ix1);
+            const float bot = lx0 * __ldg(S + r1 + ix0) + lx1 * __ldg(S + r1 + ix1);
+            const float v = ly0 * top + ly1 * bot;
+            if (v > 0.5f) { mypix[r.j] = 1; anyset = true; }
+            if (v > best) { best = v; arg = r.j; }
           }
         }
-        if (active) arg_img[q] = (int64_t)arg;
       }
+      if (active) arg_img[q0 + lane] = (int64_t)arg;
       {  // remember what this warp dirtied
         const unsigned sb = __ballot_sync(0xffffffffu, anyset);
         int dlo = 0, dhi = 0;
         if (sb) {
-          dlo = shift + (warp * 32 + (__ffs(sb) - 1)) * m;
-          dhi = shift + (warp * 32 + (32 - __clz(sb))) * m;
+          dlo = shift + (__ffs(sb) - 1) * m;
+          dhi = shift + (32 - __clz(sb)) * m;
         }
         if (par) { dlo1 = dlo; dhi1 = dhi; } else { dlo0 = dlo; dhi0 = dhi; }
       }
-      fence_proxy_async();  // this thread's shared-memory writes -> visible to the bulk store
-      __syncthreads();
-      // ---- the tile leaves as one bulk store (16-byte aligned interior) + < 16-byte edges ---------
-      uint8_t* g1 = g0 + (int64_t)nt * m;
-      const int head = (16 - shift) & 15;
-      const int64_t nbytes = (int64_t)nt * m;
-      if (nbytes <= head) {
-        if (tid == 0) bulk_commit();  // one (possibly empty) group per tile keeps the wait_group arithmetic exact
-        if (tid >= 64 && tid - 64 < nbytes) g0[tid - 64] = buf[shift + (tid - 64)];
-      } else {
-        const int64_t body = (nbytes - head) & ~(int64_t)15;
-        const int tail = (int)(nbytes - head - body);
-        if (tid == 0) {
-          if (body > 0) bulk_s2g(g0 + head, buf + shift + head, (uint32_t)body);
-          bulk_commit();
-        }
-        if (tid >= 64 && tid - 64 < head) g0[tid - 64] = buf[shift + (tid - 64)];
-        if (tid >= 96 && tid - 96 < tail) g1[-tail + (tid - 96)] = buf[shift + head + body + (tid - 96)];
+      fence_proxy_async();  // this lane's shared-memory writes -> visible to the bulk store
+      __syncwarp();
+      // ---- the segment leaves as one bulk store (16-byte aligned interior) + < 16-byte edges ---------
+      const int nbytes = nt * m;
+      const int head = min((16 - shift) & 15, nbytes);
+      const int body = (nbytes - head) & ~15;
+      const int tail = nbytes - head - body;
+      if (lane == 0) {
+        if (body > 0) bulk_s2g(g0 + head, buf + shift + head, (uint32_t)body);
+        bulk_commit();  // one (possibly empty) group per segment keeps the wait_group arithmetic exact
       }
+      if (lane < head) g0[lane] = buf[shift + lane];
+      if (lane >= 16 && lane - 16 < tail) g0[head + body + (lane - 16)] = buf[shift + head + body + (lane - 16)];
+      // this lane's pixel in the warp's next segment
+      xq += nwarps * 32;
+      while (xq >= W) { xq -= W; ++yq; }
     }
   }
-  if (tid == 0) bulk_wait_read0();  // shared memory must outlive every bulk store that reads it
+  if (lane == 0) bulk_wait_read0();  // shared memory must outlive every bulk store that reads it
 }
 
 // ---- host side ----------------------------------------------------------------------------
@@ -347,15 +364,18 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   g.scale_x = (float)p.proto_w / (float)p.out_w;
   g.list_cap = p.m_fixed >= 0 ? (p.m_fixed > 0 ? p.m_fixed : 1) : p.det_stride;
   const size_t fixed = (((size_t)p.out_w * sizeof(ColTap) + 31) & ~(size_t)31) + (size_t)g.list_cap * sizeof(DetRec);
-  const size_t want = ((size_t)kCompThreads * g.list_cap + 16 + 127) & ~(size_t)127;  // a full 512-pixel tile
-  const size_t need = ((size_t)32 * g.list_cap + 16 + 127) & ~(size_t)127;            // at least one warp of pixels
+  const size_t buf = ((size_t)32 * g.list_cap + 16 + 15) & ~(size_t)15;  // 32 pixels x m bytes + alignment shift
+  // as many warps (each with two segment buffers) as fit: two CTAs per SM if that gives >= 8 warps, else one
   size_t budget = kCompSmemTwo;
-  if (fixed + 2 * need > budget) budget = kCompSmemOne;
-  if (fixed + 2 * need > budget) ISB_FAIL(h, ISB_ERR_LIMIT, "mask compose: %d detections x width %d exceed shared memory", g.list_cap, p.out_w);
-  size_t buf = ((budget - fixed) / 2) & ~(size_t)127;
-  if (buf > want) buf = want;
+  int nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
+  if (nwarps < 8) {
+    budget = kCompSmemOne;
+    nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
+  }
+  if (nwarps > kCompWarps) nwarps = kCompWarps;
+  if (nwarps < 1) ISB_FAIL(h, ISB_ERR_LIMIT, "mask compose: %d detections x width %d exceed shared memory", g.list_cap, p.out_w);
   g.buf_bytes = (int)buf;
-  const size_t smem = fixed + 2 * buf;
+  const size_t smem = fixed + (size_t)nwarps * 2 * buf;
   int rc = ensure_mask_scratch(h, p.proto_h, p.proto_w, &g.s_cap);
   if (rc != ISB_OK) return rc;
   const int64_t total_units = (int64_t)p.batch * g.units_per_img;
@@ -369,10 +389,10 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
       p, rec, h->smap_total + h->ws_b0, smap, g.s_cap);
   ISB_LAUNCH_CHECK(h, "sigmoid_map_kernel");
   if (h->prof_mid) ISB_CUDA(h, cudaEventRecord(h->prof_mid, s));
-  const int per_sm = smem + 1024 <= (size_t)kCompSmemTwo + 2048 ? 2 : 1;
+  const int per_sm = budget == (size_t)kCompSmemTwo ? 2 : 1;
   int64_t grid = (int64_t)h->num_sms * per_sm;
   if (grid > total_units) grid = total_units;
-  mask_compose_kernel<<<(unsigned)grid, kCompThreads, smem, s>>>(p, g, rec, smap, counters);
+  mask_compose_kernel<<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, counters);
   ISB_LAUNCH_CHECK(h, "mask_compose_kernel");
   return ISB_OK;
 }
