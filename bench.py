@@ -194,7 +194,7 @@ def run_gpu(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         # before CUDA is initialised in this process (workers are forked)
-        secs, n_img, workers = cpu_port_rounds(4, budget_s=30.0)
+        secs, n_img, workers = cpu_port_rounds(24, budget_s=20.0)
         cpu = {"value": n_img * (len(secs) - 1) / sum(secs[1:]), "unit": UNIT, "cores": workers, "kind": "port",
                "sample": f"{len(secs) - 1} timed rounds (+1 warm-up) of {n_img} images of the same workload ({workers} single-thread "
                          f"processes x 1 image, {sum(secs[1:]):.1f} s): numpy restatement of the reference's torch code"}
