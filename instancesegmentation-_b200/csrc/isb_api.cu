@@ -85,6 +85,8 @@ static void free_ws(isb_handle* h) {
   cudaFree(h->smap);
   cudaFree(h->stage);
   cudaFree(h->nms_keys);
+  cudaFree(h->nms_keys2);
+  cudaFree(h->nms_rank);
   cudaFree(h->nms_sbox);
   cudaFree(h->nms_order);
   cudaFree(h->nms_mask);

@@ -303,6 +303,8 @@ struct isb_handle {
   // Mask R-CNN side: NMS workspace, grown on demand (ensure_nms_ws)
   int64_t nms_cap;         // boxes the arrays below hold
   uint64_t* nms_keys;      // [pow2(nms_cap)]
+  uint64_t* nms_keys2;     // [nms_cap]  rank-sorted keys
+  int32_t* nms_rank;       // [nms_cap]  rank scratch of the rank sort
   float4* nms_sbox;        // [nms_cap]  boxes in score order (offset by class for batched NMS)
   int32_t* nms_order;      // [nms_cap]  original index per sorted position
   uint64_t* nms_mask;      // [nms_cap][ceil(nms_cap/64)] suppression bits
@@ -310,6 +312,7 @@ struct isb_handle {
   // generic scratch for the fused RPN / box-head pipelines (ensure_scratch)
   void* scratch;
   size_t scratch_bytes;
+  int roi_configured;      // ms_roi_align_kernel's dynamic shared memory limit has been raised
   // optional per-stage event ring (isb_profile_begin / isb_profile_read)
   cudaEvent_t* prof_events;  // [prof_cap][5]
   cudaEvent_t prof_mid;      // set while a profiled call is inside launch_masks
@@ -409,6 +412,9 @@ int launch_mask_logits_tc(isb_handle* h, const float* proto, const float* coef, 
                           cudaStream_t s);
 
 int launch_sort_u64(isb_handle* h, uint64_t* keys, int n_pow2, cudaStream_t s);
+int launch_rank_sort_u64(isb_handle* h, const uint64_t* keys, int n_max, const int32_t* n_dev, int32_t* rank, uint64_t* out,
+                         cudaStream_t s);
+constexpr int kRankSortMax = 32768;  // above this the O(n^2) rank sort loses to the bitonic network
 int ensure_nms_ws(isb_handle* h, int64_t n);
 int ensure_scratch(isb_handle* h, size_t bytes);
 

@@ -64,20 +64,18 @@ __global__ void nms_gather_kernel(const uint64_t* __restrict__ keys, const float
   }
 }
 
-__device__ __forceinline__ float tv_iou(float4 a, float area_a, float4 b, float area_b) {
-  const float w = fmaxf(0.0f, fminf(a.z, b.z) - fmaxf(a.x, b.x));
-  const float hgt = fmaxf(0.0f, fminf(a.w, b.w) - fmaxf(a.y, b.y));
-  const float inter = w * hgt;
-  return inter / ((area_a + area_b) - inter);
-}
-
-// grid (col_block, row_block), 64 threads; only col_block >= row_block does work.
+// Suppression matrix, FULL and symmetric: bit j of mask[i][j / 64] is set iff i != j and IoU(i, j) > thr, so
+// row i restricted to j < i is "who can suppress i" (what the scan needs) without a transpose.
+// grid (col_block, row_block), 64 threads: thread t owns row rb * 64 + t against the 64 boxes of the column
+// block staged in shared memory.  Disjoint pairs (the vast majority) skip the division: 0 / union is +-0 for every
+// finite non-zero union, and the slow path of the IEEE division for a zero numerator is the most expensive
+// thing in the loop.
 __global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__ sbox, int n_max,
                                                       const int32_t* __restrict__ n_dev, float thr, int words,
                                                       uint64_t* __restrict__ mask) {
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   const int rb = blockIdx.y, cb = blockIdx.x;
-  if (cb < rb || rb * 64 >= n || cb * 64 >= n) return;
+  if (rb * 64 >= n || cb * 64 >= n) return;
   __shared__ float4 cbox[64];
   __shared__ float carea[64];
   const int t = threadIdx.x;
@@ -92,98 +90,118 @@ __global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__
   const float4 a = sbox[ri];
   const float aa = box_area(a);
   const int ncol = min(64, n - cb * 64);
+  const bool zero_hits = 0.0f > thr;  // a zero IoU suppresses only for a negative threshold
   uint64_t bits = 0;
-  const int j0 = (rb == cb) ? t + 1 : 0;
-  for (int j = j0; j < ncol; ++j)
-    if (tv_iou(a, aa, cbox[j], carea[j]) > thr) bits |= 1ull << j;
+  for (int j = 0; j < ncol; ++j) {
+    const float4 c = cbox[j];
+    const float w = fmaxf(0.0f, fminf(a.z, c.z) - fmaxf(a.x, c.x));
+    const float hgt = fmaxf(0.0f, fminf(a.w, c.w) - fmaxf(a.y, c.y));
+    const float inter = w * hgt;
+    const float uni = (aa + carea[j]) - inter;
+    bool hit;
+    if (inter == 0.0f && uni != 0.0f && fabsf(uni) <= 3.402823466e38f) hit = zero_hits;
+    else hit = inter / uni > thr;
+    if (hit) bits |= 1ull << j;
+  }
+  if (rb == cb) bits &= ~(1ull << t);  // a box does not suppress itself
   mask[(size_t)ri * words + cb] = bits;
 }
 
-// Single CTA: resolve the greedy chain chunk by chunk and compact the kept indices.
+// Single CTA: greedy NMS resolved 1024 boxes at a time by fixed-point iteration.
+//   keep(i) = alive0(i) and no kept j < i of the chunk overlaps i,
+//   alive0(i) = no kept box of an earlier chunk overlaps i.
+// Starting from keep = alive0 the iteration alternates between over- and under-estimates of the greedy answer and
+// settles after (length of the longest suppression chain) rounds, typically < 10; a round is 16 AND steps on
+// register-resident words of the thread's own matrix row plus one ballot.  Thread t owns box chunk * 1024 + t.
+// Replaces a 64-box-at-a-time scan that paid one global round trip and three barriers per 64 boxes.
+constexpr int kScanChunkWords = kScanThreads / 64;  // 16
+
 __global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(const uint64_t* __restrict__ mask,
                                                                 const int32_t* __restrict__ order, int n_max,
                                                                 const int32_t* __restrict__ n_dev, int words, int max_keep,
                                                                 int64_t* __restrict__ keep, int32_t* __restrict__ count) {
-  extern __shared__ uint64_t s_dyn[];  // removed[words] | keptbits[words]
-  __shared__ uint64_t s_diag[64];
-  __shared__ uint64_t s_kept;
+  extern __shared__ uint64_t s_kept[];            // [words] kept bitmap over all boxes (score order)
+  __shared__ uint32_t s_cur[kScanThreads / 32];   // this round's keep bits of the chunk, one ballot per warp
+  __shared__ int s_warp_cnt[kScanThreads / 32];
   __shared__ int s_total;
-  __shared__ int s_stop;
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   const int nwords = (n + 63) >> 6;
-  uint64_t* removed = s_dyn;
-  uint64_t* keptbits = s_dyn + words;
-  const int tid = threadIdx.x;
-  for (int w = tid; w < nwords; w += kScanThreads) { removed[w] = 0; keptbits[w] = 0; }
-  if (tid == 0) { s_total = 0; s_stop = 0; }
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int w = tid; w < nwords; w += kScanThreads) s_kept[w] = 0;
+  if (tid == 0) s_total = 0;
   __syncthreads();
-  for (int c = 0; c < nwords; ++c) {
-    if (tid < 64) {
-      const int r = c * 64 + tid;
-      s_diag[tid] = r < n ? mask[(size_t)r * words + c] : 0ull;
+  const int nchunks = (n + kScanThreads - 1) / kScanThreads;
+  for (int c = 0; c < nchunks; ++c) {
+    const int i = c * kScanThreads + tid;
+    const int w0 = c * kScanChunkWords;                 // first word of this chunk
+    const int wn = min(kScanChunkWords, nwords - w0);    // words of this chunk
+    const uint64_t* row = mask + (size_t)i * words;
+    // alive0: not overlapped by any kept box of an earlier chunk
+    bool alive = i < n;
+    if (alive) {
+      uint64_t acc = 0;
+      for (int w = 0; w < w0; ++w) acc |= row[w] & s_kept[w];
+      alive = acc == 0;
     }
-    __syncthreads();
-    if (tid == 0) {
-      uint64_t cur = removed[c], kept = 0;
-      const int lim = min(64, n - c * 64);
-      int total = s_total;
-      for (int b = 0; b < lim; ++b) {
-        if (!((cur >> b) & 1ull)) {
-          kept |= 1ull << b;
-          cur |= s_diag[b];
-          if (max_keep > 0 && ++total >= max_keep) { s_stop = 1; break; }
-        }
+    // own row inside the chunk, restricted to j < i
+    uint64_t d[kScanChunkWords];
+#pragma unroll
+    for (int w = 0; w < kScanChunkWords; ++w) {
+      uint64_t v = 0;
+      if (alive && w < wn && w * 64 < tid) {
+        v = row[w0 + w];
+        if ((w + 1) * 64 > tid) v &= (1ull << (tid - w * 64)) - 1ull;
       }
-      if (max_keep <= 0) total += __popcll(kept);
-      s_total = total;
-      s_kept = kept;
-      keptbits[c] = kept;
+      d[w] = v;
     }
-    __syncthreads();
-    if (s_stop) break;
-    const uint64_t kept = s_kept;
-    for (int w = c + 1 + tid; w < nwords; w += kScanThreads) {
-      uint64_t acc = 0, k = kept;
-      while (k) {
-        const int b = __ffsll((long long)k) - 1;
-        k &= k - 1;
-        acc |= mask[(size_t)(c * 64 + b) * words + w];
+    bool kp = alive;
+    while (true) {
+      const uint32_t bal = __ballot_sync(0xffffffffu, kp);
+      if (lane == 0) s_cur[warp] = bal;
+      __syncthreads();
+      bool hit = false;
+#pragma unroll
+      for (int w = 0; w < kScanChunkWords; ++w) {
+        const uint64_t kw = (uint64_t)s_cur[2 * w] | ((uint64_t)s_cur[2 * w + 1] << 32);
+        hit |= (d[w] & kw) != 0;
       }
-      removed[w] |= acc;
+      const bool nk = alive && !hit;
+      // the barrier also orders this round's reads of s_cur before the next round's writes
+      const int changed = __syncthreads_or(nk != kp);
+      kp = nk;
+      if (!changed) break;
     }
+    // count, cut at max_keep (in score order), publish
+    const uint32_t bal = __ballot_sync(0xffffffffu, kp);
+    if (lane == 0) s_warp_cnt[warp] = __popc(bal);
     __syncthreads();
-  }
-  __syncthreads();
-  // ordered compaction: thread per word, serial prefix by thread 0 (nwords is small)
-  __shared__ int s_base[1];
-  if (tid == 0) {
-    int run = 0;
-    for (int w = 0; w < nwords; ++w) {
-      const int c = __popcll(keptbits[w]);
-      removed[w] = (uint64_t)run;  // reuse as prefix
-      run += c;
+    int before = s_total, chunk_total = 0;
+    for (int w = 0; w < kScanThreads / 32; ++w) {
+      const int cw = s_warp_cnt[w];
+      if (w < warp) before += cw;
+      chunk_total += cw;
     }
-    s_base[0] = run;
-    *count = run;
+    const int my_pos = before + __popc(bal & ((1u << lane) - 1u));  // kept boxes before this one
+    if (max_keep > 0 && my_pos >= max_keep) kp = false;
+    const uint32_t bal2 = __ballot_sync(0xffffffffu, kp);
+    if (lane == 0 && (warp >> 1) < wn) reinterpret_cast<uint32_t*>(s_kept + w0)[warp] = bal2;
+    if (kp) keep[my_pos] = (int64_t)order[i];
+    __syncthreads();
+    if (tid == 0) s_total = (max_keep > 0 && s_total + chunk_total > max_keep) ? max_keep : s_total + chunk_total;
+    __syncthreads();
+    if (max_keep > 0 && s_total >= max_keep) break;
   }
-  __syncthreads();
-  for (int w = tid; w < nwords; w += kScanThreads) {
-    uint64_t k = keptbits[w];
-    int pos = (int)removed[w];
-    while (k) {
-      const int b = __ffsll((long long)k) - 1;
-      k &= k - 1;
-      keep[pos++] = (int64_t)order[w * 64 + b];
-    }
-  }
+  if (tid == 0) *count = s_total;
 }
 
 static void free_nms_ws(isb_handle* h) {
   cudaFree(h->nms_keys);
+  cudaFree(h->nms_keys2);
+  cudaFree(h->nms_rank);
   cudaFree(h->nms_sbox);
   cudaFree(h->nms_order);
   cudaFree(h->nms_mask);
-  h->nms_keys = nullptr; h->nms_sbox = nullptr; h->nms_order = nullptr; h->nms_mask = nullptr;
+  h->nms_keys = nullptr; h->nms_keys2 = nullptr; h->nms_rank = nullptr; h->nms_sbox = nullptr; h->nms_order = nullptr; h->nms_mask = nullptr;
   h->nms_cap = 0;
 }
 
@@ -197,11 +215,13 @@ int ensure_nms_ws(isb_handle* h, int64_t n) {
   while (cap < n) cap <<= 1;
   const int64_t words = (cap + 63) / 64;
   ISB_CUDA(h, cudaMalloc((void**)&h->nms_keys, (size_t)cap * 8));
+  ISB_CUDA(h, cudaMalloc((void**)&h->nms_keys2, (size_t)cap * 8));
+  ISB_CUDA(h, cudaMalloc((void**)&h->nms_rank, (size_t)cap * 4));
   ISB_CUDA(h, cudaMalloc((void**)&h->nms_sbox, (size_t)cap * 16));
   ISB_CUDA(h, cudaMalloc((void**)&h->nms_order, (size_t)cap * 4));
   ISB_CUDA(h, cudaMalloc((void**)&h->nms_mask, (size_t)cap * words * 8));
   h->nms_cap = cap;
-  h->ws_bytes += (size_t)cap * (28 + words * 8);
+  h->ws_bytes += (size_t)cap * (40 + words * 8);
   return ISB_OK;
 }
 
@@ -243,13 +263,19 @@ int launch_nms(isb_handle* h, const NmsCall& c, cudaStream_t s) {
   }
   nms_keys_kernel<<<(n_pow2 + 255) / 256, 256, 0, s>>>(c.scores, n, c.n_dev, n_pow2, h->nms_keys);
   ISB_LAUNCH_CHECK(h, "nms_keys_kernel");
-  if ((rc = launch_sort_u64(h, h->nms_keys, n_pow2, s)) != ISB_OK) return rc;
-  nms_gather_kernel<<<blocks, 256, 0, s>>>(h->nms_keys, c.boxes, c.idxs64, c.idxs32, n, c.n_dev, h->nms_scalars,
+  const uint64_t* sorted = h->nms_keys;
+  if (n <= kRankSortMax) {
+    if ((rc = launch_rank_sort_u64(h, h->nms_keys, n, c.n_dev, h->nms_rank, h->nms_keys2, s)) != ISB_OK) return rc;
+    sorted = h->nms_keys2;
+  } else if ((rc = launch_sort_u64(h, h->nms_keys, n_pow2, s)) != ISB_OK) {
+    return rc;
+  }
+  nms_gather_kernel<<<blocks, 256, 0, s>>>(sorted, c.boxes, c.idxs64, c.idxs32, n, c.n_dev, h->nms_scalars,
                                            h->nms_sbox, h->nms_order);
   ISB_LAUNCH_CHECK(h, "nms_gather_kernel");
   nms_mask_kernel<<<dim3(words, words), 64, 0, s>>>(h->nms_sbox, n, c.n_dev, thr_f, words, h->nms_mask);
   ISB_LAUNCH_CHECK(h, "nms_mask_kernel");
-  const size_t smem = (size_t)words * 16;
+  const size_t smem = (size_t)words * 8;
   if (smem > 64 * 1024) ISB_FAIL(h, ISB_ERR_LIMIT, "nms scan shared memory");
   nms_scan_kernel<<<1, kScanThreads, smem, s>>>(h->nms_mask, h->nms_order, n, c.n_dev, words, c.max_keep, c.keep, c.count);
   ISB_LAUNCH_CHECK(h, "nms_scan_kernel");

@@ -75,23 +75,32 @@ __device__ __forceinline__ float padded_at(const float* __restrict__ mk, int S, 
   return (yy >= 0 && yy < S && xx >= 0 && xx < S) ? __ldg(mk + yy * S + xx) : 0.0f;
 }
 
+// IDX = uint32_t whenever m*H*W < 2^32 (always, for real image sizes): the flat element index -> (mask, row, col)
+// arithmetic is then 32-bit; the 64-bit instantiation exists for completeness.
+template <typename IDX>
 __global__ void __launch_bounds__(256) paste_masks_kernel(const float* __restrict__ masks, const float4* __restrict__ boxes,
                                                           int m, int S, int pad, int im_h, int im_w,
                                                           float* __restrict__ out) {
-  const int64_t total = (int64_t)m * im_h * im_w;
-  const int64_t nvec = (total + 3) >> 2;
+  const IDX plane = (IDX)im_h * (IDX)im_w;
+  const IDX total = (IDX)m * plane;
+  const IDX nvec = (total + 3) >> 2;
   const int Sp = S + 2 * pad;
   const float scale = (float)((double)Sp / (double)S);  // transform.py:178, cast to the tensor dtype at :156
-  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t e0 = v << 2;
-    int64_t pix = e0 % ((int64_t)im_h * im_w);
-    int i = (int)(e0 / ((int64_t)im_h * im_w));
-    int y = (int)(pix / im_w), x = (int)(pix - (int64_t)y * im_w);
+  for (IDX v = (IDX)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (IDX)gridDim.x * blockDim.x) {
+    const IDX e0 = v << 2;
+    int i = (int)(e0 / plane);
+    const IDX pix = e0 - (IDX)i * plane;
+    int y = (int)(pix / (IDX)im_w), x = (int)(pix - (IDX)y * (IDX)im_w);
+    // fast path: the 4 elements lie in one row of one mask and entirely outside its box -> one zero store
+    PasteBox pb = paste_box(__ldg(boxes + i), scale);
+    if (x + 3 < im_w && e0 + 3 < total && (y < pb.y0 || y > pb.y1 || x + 3 < pb.x0 || x > pb.x1)) {
+      __stcs(reinterpret_cast<float4*>(out) + v, make_float4(0.f, 0.f, 0.f, 0.f));
+      continue;
+    }
     float vals[4];
-    int cur = -1;
-    PasteBox pb = {0, 0, 0, 0};
-    int w = 1, hgt = 1;
-    float sx = 0.f, sy = 0.f;
+    int cur = i;
+    int w = max(pb.x1 - pb.x0 + 1, 1), hgt = max(pb.y1 - pb.y0 + 1, 1);
+    float sx = (float)Sp / (float)w, sy = (float)Sp / (float)hgt;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       float r = 0.0f;
@@ -120,7 +129,7 @@ __global__ void __launch_bounds__(256) paste_masks_kernel(const float* __restric
       vals[k] = r;
     }
     if (e0 + 3 < total) {
-      reinterpret_cast<float4*>(out)[v] = make_float4(vals[0], vals[1], vals[2], vals[3]);
+      __stcs(reinterpret_cast<float4*>(out) + v, make_float4(vals[0], vals[1], vals[2], vals[3]));
     } else {
       for (int k = 0; k < 4 && e0 + k < total; ++k) out[e0 + k] = vals[k];
     }
@@ -149,14 +158,69 @@ __device__ __forceinline__ AxisSample axis_sample(float v, int size) {
 }
 
 constexpr int kRoiThreads = 256;
-constexpr int kRoiAxisMax = 128;  // out * sampling_ratio per axis
+constexpr int kRoiAxisMax = 128;      // out * sampling_ratio per axis
+constexpr int kRoiBufFloats = 4096;   // one staging buffer (16 KB); two of them + one offset table per CTA
 
+__device__ __forceinline__ void cp_async4(uint32_t dst_smem, const void* src_gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_smem), "l"(src_gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// sample of one axis in COMPACT coordinates: positions of its two taps in the list of distinct rows (columns)
+// the RoI touches, interpolation weight, validity
+struct TapSample { int32_t idx; float l; };  // idx = lo | hi << 8 | bad << 16
+
+// One thread: distinct tap coordinates of an axis, in ascending order, and every sample's positions in that list.
+// The samples are monotone along the axis, so a new coordinate is either one of the last two listed or larger.
+__device__ void build_tap_list(const AxisSample* __restrict__ smp, int n, int* __restrict__ list, int* __restrict__ n_list,
+                               TapSample* __restrict__ out) {
+  int cnt = 0;
+  for (int t = 0; t < n; ++t) {
+    const AxisSample a = smp[t];
+    TapSample ts;
+    ts.l = a.l;
+    ts.idx = 1 << 16;
+    if (!a.bad) {
+      int pos[2];
+      const int v[2] = {a.lo, a.hi};
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        if (cnt >= 1 && list[cnt - 1] == v[k]) pos[k] = cnt - 1;
+        else if (cnt >= 2 && list[cnt - 2] == v[k]) pos[k] = cnt - 2;
+        else { list[cnt] = v[k]; pos[k] = cnt++; }
+      }
+      ts.idx = pos[0] | (pos[1] << 8);
+    }
+    out[t] = ts;
+  }
+  *n_list = cnt;
+}
+
+// grid (RoI, channel group).  The CTA works out the RoI's FPN level and its (y, x) sample tables once, then the
+// lists of DISTINCT feature rows and columns those samples touch (at most 2 * out * sampling_ratio each, whatever
+// the RoI's size or aspect ratio) and a table of their global offsets.  Channel chunk by channel chunk the
+// ny x nx tap tile is gathered into shared memory with asynchronous copies (cp.async, double-buffered: chunk
+// k+1 is in flight while chunk k is reduced) -- one table look-up and one copy per element, no per-row
+// arithmetic -- and every output bin takes its 2 x 2 samples x 4 taps from shared memory.  The features are
+// NCHW, so a direct per-output gather costs one L1 wavefront per lane (the one-thread-per-output kernel this
+// replaces was L1-wavefront bound).  TMA tensor tiles are not usable in general here: the row pitch of an FPN
+// level need not be a multiple of 16 bytes (42 floats at the coarsest level of an 800 x 1344 input).
+// SR > 0: sampling ratio known at compile time (the reference always passes 2); SR == 0: run-time value.
+template <int SR>
 __global__ void __launch_bounds__(kRoiThreads) ms_roi_align_kernel(RoiLevels L, const float4* __restrict__ boxes,
                                                                    const int32_t* __restrict__ batch_idx, int channels,
-                                                                   int oh, int ow, int sr, float* __restrict__ out) {
+                                                                   int oh, int ow, int sr_rt, int cpc, float* __restrict__ out) {
+  const int sr = SR > 0 ? SR : sr_rt;
+  extern __shared__ __align__(16) float s_buf[];  // [2][kRoiBufFloats] tiles | [kRoiBufFloats] int offsets
   __shared__ AxisSample ys[kRoiAxisMax], xs[kRoiAxisMax];
-  __shared__ int s_level;
-  const int r = blockIdx.x, tid = threadIdx.x;
+  __shared__ TapSample tys[kRoiAxisMax], txs[kRoiAxisMax];
+  __shared__ int ylist[2 * kRoiAxisMax], xlist[2 * kRoiAxisMax];
+  __shared__ int s_level, s_ny, s_nx;
+  int* s_goff = reinterpret_cast<int*>(s_buf + 2 * kRoiBufFloats);
+  const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int cbase = blockIdx.y * cpc, cend = min(channels, cbase + cpc);
   const float4 b = boxes[r];
   if (tid == 0) {
     int lvl = 0;
@@ -175,41 +239,112 @@ __global__ void __launch_bounds__(kRoiThreads) ms_roi_align_kernel(RoiLevels L, 
   const float start_w = b.x * ss, start_h = b.y * ss, end_w = b.z * ss, end_h = b.w * ss;
   const float roi_w = fmaxf(end_w - start_w, 1.0f), roi_h = fmaxf(end_h - start_h, 1.0f);
   const float bin_h = roi_h / (float)oh, bin_w = roi_w / (float)ow;
-  for (int t = tid; t < oh * sr; t += kRoiThreads) {
+  const int ny = oh * sr, nx = ow * sr;
+  for (int t = tid; t < ny; t += kRoiThreads) {
     const int ph = t / sr, iy = t - ph * sr;
     ys[t] = axis_sample(start_h + (float)ph * bin_h + (((float)iy + 0.5f) * bin_h) / (float)sr, fh);
   }
-  for (int t = tid; t < ow * sr; t += kRoiThreads) {
+  for (int t = tid; t < nx; t += kRoiThreads) {
     const int pw = t / sr, ix = t - pw * sr;
     xs[t] = axis_sample(start_w + (float)pw * bin_w + (((float)ix + 0.5f) * bin_w) / (float)sr, fw);
   }
   __syncthreads();
+  if (tid == 0) build_tap_list(ys, ny, ylist, &s_ny, tys);
+  if (tid == 32) build_tap_list(xs, nx, xlist, &s_nx, txs);
+  __syncthreads();
+  const int nyl = s_ny, nxl = s_nx, plane = nyl * nxl;
   const float count = (float)max(sr * sr, 1);
   const int bins = oh * ow;
   const int img = batch_idx ? batch_idx[r] : 0;
   const float* fbase = L.feat[lvl] + (size_t)img * channels * fh * fw;
   float* obase = out + (size_t)r * channels * bins;
-  for (int o = tid; o < channels * bins; o += kRoiThreads) {
-    const int c = o / bins, bin = o - c * bins;
-    const int ph = bin / ow, pw = bin - ph * ow;
-    const float* plane = fbase + (size_t)c * fh * fw;
-    float acc = 0.0f;
-    for (int iy = 0; iy < sr; ++iy) {
-      const AxisSample sy = ys[ph * sr + iy];
-      for (int ix = 0; ix < sr; ++ix) {
-        const AxisSample sx = xs[pw * sr + ix];
-        float val = 0.0f;
-        if (!(sy.bad | sx.bad)) {
-          const float w1 = sy.h * sx.h, w2 = sy.h * sx.l, w3 = sy.l * sx.h, w4 = sy.l * sx.l;
-          const float v1 = __ldg(plane + sy.lo * fw + sx.lo), v2 = __ldg(plane + sy.lo * fw + sx.hi);
-          const float v3 = __ldg(plane + sy.hi * fw + sx.lo), v4 = __ldg(plane + sy.hi * fw + sx.hi);
-          val = ((w1 * v1 + w2 * v2) + w3 * v3) + w4 * v4;
-        }
-        acc += val;
-      }
-    }
-    obase[o] = acc / count;
+  if (plane == 0) {  // every sample falls outside the map: zeros
+    for (int o = cbase * bins + tid; o < cend * bins; o += kRoiThreads) obase[o] = 0.0f;
+    return;
   }
+  if (plane > kRoiBufFloats || nyl > 255 || nxl > 255) {  // very large out * sampling_ratio: direct gather
+    for (int o = cbase * bins + tid; o < cend * bins; o += kRoiThreads) {
+      const int c = o / bins, bin = o - c * bins;
+      const int ph = bin / ow, pw = bin - ph * ow;
+      const float* pl = fbase + (size_t)c * fh * fw;
+      float acc = 0.0f;
+      for (int iy = 0; iy < sr; ++iy) {
+        const AxisSample sy = ys[ph * sr + iy];
+        for (int ix = 0; ix < sr; ++ix) {
+          const AxisSample sx = xs[pw * sr + ix];
+          float val = 0.0f;
+          if (!(sy.bad | sx.bad)) {
+            const float w1 = sy.h * sx.h, w2 = sy.h * sx.l, w3 = sy.l * sx.h, w4 = sy.l * sx.l;
+            const float v1 = __ldg(pl + sy.lo * fw + sx.lo), v2 = __ldg(pl + sy.lo * fw + sx.hi);
+            const float v3 = __ldg(pl + sy.hi * fw + sx.lo), v4 = __ldg(pl + sy.hi * fw + sx.hi);
+            val = ((w1 * v1 + w2 * v2) + w3 * v3) + w4 * v4;
+          }
+          acc += val;
+        }
+      }
+      obase[o] = acc / count;
+    }
+    return;
+  }
+  for (int i = tid; i < plane; i += kRoiThreads) {
+    const int yi = i / nxl, xi = i - yi * nxl;
+    s_goff[i] = ylist[yi] * fw + xlist[xi];
+  }
+  __syncthreads();
+  const int cg = min(kRoiBufFloats / plane, cend - cbase);
+  const uint32_t sbase = smem_u32(s_buf);
+  const int nchunks = (cend - cbase + cg - 1) / cg;
+  // chunk k: channels [cbase + k * cg, ...) gathered into buffer k & 1, a warp per channel
+#define ROI_STAGE(K)                                                                     \
+  do {                                                                                   \
+    const int c0_ = cbase + (K) * cg, nc_ = min(cg, cend - c0_);                         \
+    const uint32_t dst_ = sbase + (((K) & 1) * kRoiBufFloats) * 4u;                      \
+    for (int c = warp; c < nc_; c += kRoiThreads / 32) {                                 \
+      const float* src_ = fbase + (size_t)(c0_ + c) * fh * fw;                           \
+      const uint32_t d_ = dst_ + (uint32_t)(c * plane) * 4u;                             \
+      for (int i = lane; i < plane; i += 32) cp_async4(d_ + 4u * i, src_ + s_goff[i]);   \
+    }                                                                                    \
+    cp_async_commit();                                                                   \
+  } while (0)
+  ROI_STAGE(0);
+  for (int k = 0; k < nchunks; ++k) {
+    const int c0 = cbase + k * cg, nc = min(cg, cend - c0);
+    if (k + 1 < nchunks) {
+      ROI_STAGE(k + 1);
+      cp_async_wait1();
+    } else {
+      cp_async_wait0();
+    }
+    __syncthreads();
+    const float* tile = s_buf + (k & 1) * kRoiBufFloats;
+    for (int o = tid; o < nc * bins; o += kRoiThreads) {
+      const int c = o / bins, bin = o - c * bins;
+      const int ph = bin / ow, pw = bin - ph * ow;
+      const int pbase = c * plane;
+      float acc = 0.0f;
+#pragma unroll
+      for (int iy = 0; iy < (SR > 0 ? SR : sr); ++iy) {
+        const TapSample sy = tys[ph * sr + iy];
+        const float syl = sy.l, syh = 1.0f - syl;
+        const int rlo = pbase + (sy.idx & 0xff) * nxl, rhi = pbase + ((sy.idx >> 8) & 0xff) * nxl;
+#pragma unroll
+        for (int ix = 0; ix < (SR > 0 ? SR : sr); ++ix) {
+          const TapSample sx = txs[pw * sr + ix];
+          float val = 0.0f;
+          if (!((sy.idx | sx.idx) >> 16)) {
+            const float sxl = sx.l, sxh = 1.0f - sxl;
+            const int xlo = sx.idx & 0xff, xhi = (sx.idx >> 8) & 0xff;
+            const float w1 = syh * sxh, w2 = syh * sxl, w3 = syl * sxh, w4 = syl * sxl;
+            val = ((w1 * tile[rlo + xlo] + w2 * tile[rlo + xhi]) + w3 * tile[rhi + xlo]) + w4 * tile[rhi + xhi];
+          }
+          acc += val;
+        }
+      }
+      obase[(size_t)c0 * bins + o] = acc / count;
+    }
+    __syncthreads();  // buffer (k & 1) is free for chunk k + 2
+  }
+#undef ROI_STAGE
 }
 
 // ---------------------------------------------------------------------------- launchers
@@ -244,16 +379,38 @@ int launch_resize_boxes(isb_handle* h, const float* in, int64_t m, float rw, flo
 }
 int launch_paste_masks(isb_handle* h, const float* masks, const float* boxes, int m, int S, int pad, int im_h, int im_w,
                        float* out, cudaStream_t s) {
-  const int64_t nvec = ((int64_t)m * im_h * im_w + 3) / 4;
-  paste_masks_kernel<<<grid_for(nvec, 256, h->num_sms, 32), 256, 0, s>>>(masks, reinterpret_cast<const float4*>(boxes), m, S,
-                                                                         pad, im_h, im_w, out);
+  const int64_t total = (int64_t)m * im_h * im_w, nvec = (total + 3) / 4;
+  if (total + 4 < (1ll << 32))
+    paste_masks_kernel<uint32_t><<<grid_for(nvec, 256, h->num_sms, 8), 256, 0, s>>>(masks, reinterpret_cast<const float4*>(boxes),
+                                                                                    m, S, pad, im_h, im_w, out);
+  else
+    paste_masks_kernel<unsigned long long><<<grid_for(nvec, 256, h->num_sms, 8), 256, 0, s>>>(
+        masks, reinterpret_cast<const float4*>(boxes), m, S, pad, im_h, im_w, out);
   ISB_LAUNCH_CHECK(h, "paste_masks_kernel");
   return ISB_OK;
 }
 int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, const int32_t* batch_idx, int num_rois,
                         int channels, int oh, int ow, int sr, float* out, cudaStream_t s) {
-  ms_roi_align_kernel<<<num_rois, kRoiThreads, 0, s>>>(L, reinterpret_cast<const float4*>(boxes), batch_idx, channels, oh,
-                                                       ow, sr, out);
+  if (!h->roi_configured) {
+    ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(3 * kRoiBufFloats * sizeof(float))));
+    ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(3 * kRoiBufFloats * sizeof(float))));
+    h->roi_configured = 1;
+  }
+  // channel groups per RoI: enough CTAs to fill the GPU about a dozen times over, at least 8 channels each
+  int groups = (12 * h->num_sms + num_rois - 1) / num_rois;
+  if (groups > (channels + 7) / 8) groups = (channels + 7) / 8;
+  if (groups < 1) groups = 1;
+  int cpc = (channels + groups - 1) / groups;
+  cpc = (cpc + 7) & ~7;
+  groups = (channels + cpc - 1) / cpc;
+  if (sr == 2)
+    ms_roi_align_kernel<2><<<dim3(num_rois, groups), kRoiThreads, 3 * kRoiBufFloats * sizeof(float), s>>>(
+        L, reinterpret_cast<const float4*>(boxes), batch_idx, channels, oh, ow, sr, cpc, out);
+  else
+    ms_roi_align_kernel<0><<<dim3(num_rois, groups), kRoiThreads, 3 * kRoiBufFloats * sizeof(float), s>>>(
+        L, reinterpret_cast<const float4*>(boxes), batch_idx, channels, oh, ow, sr, cpc, out);
   ISB_LAUNCH_CHECK(h, "ms_roi_align_kernel");
   return ISB_OK;
 }

@@ -10,16 +10,112 @@
 namespace isb {
 
 struct LevelOffsets { int start[9]; int num_levels; };
+struct LevelTopK { int k[8]; };  // min(pre_nms_top_n, level size)
 
-// ---- RPN: keys (level | ~logit | anchor) for the per-level top-k (rpn_function.py:447-456) ----
-__global__ void rpn_keys_kernel(const float* __restrict__ objectness, LevelOffsets lv, int n, int n_pow2,
-                                uint64_t* __restrict__ keys) {
+// ---- RPN: exact per-level top-k by radix select (rpn_function.py:447-456) ------------------------------
+// Every anchor has a unique 52-bit rank key  ~logit (32 bits, smaller = better) | anchor index (20 bits), i.e.
+// score descending with ties by ascending index.  The k-th smallest key of each level is found digit by digit
+// (11, 11, 11, 11, 8 bits): pass p histograms the digit of the anchors that match the prefix chosen so far; the
+// next launch resolves that histogram (every CTA redundantly, 2048 bins) before it filters.  The objectness
+// map (1 MB, L2-resident) is read six times; nothing is sorted until the exactly k survivors per level are
+// known, so the full sort of 2^19 keys this replaces shrinks to one of 8192.
+constexpr int kSelBins = 2048;
+constexpr int kSelPasses = 5;
+constexpr int kSelThreads = 256;
+__device__ __constant__ int kSelShift[kSelPasses] = {41, 30, 19, 8, 0};
+__device__ __constant__ int kSelBits[kSelPasses] = {11, 11, 11, 11, 8};
+
+struct SelState { unsigned long long prefix; int k_rem; int pad; };
+
+__device__ __forceinline__ uint64_t rpn_rank_key(float logit, uint32_t index) {
+  return ((uint64_t)float_desc_bits(logit) << kRowBits) | index;
+}
+
+// Resolve the histogram of pass `p` (p >= 0) given the state before it: pick the digit whose cumulative count
+// reaches k_rem.  Called by all threads of a 256-thread CTA; the result is returned to every thread.
+__device__ SelState sel_resolve(SelState st, const int* __restrict__ hist, int p, int* s_scan /* [32] */, int* s_res /* [2] */) {
+  const int tid = threadIdx.x;
+  int v[kSelBins / kSelThreads];
+  int sum = 0;
+#pragma unroll
+  for (int i = 0; i < kSelBins / kSelThreads; ++i) { v[i] = hist[tid * (kSelBins / kSelThreads) + i]; sum += v[i]; }
+  int total;
+  int excl = cta_exclusive_scan(sum, s_scan, &total);
+  if (excl < st.k_rem && st.k_rem <= excl + sum) {  // exactly one thread
+    int b = 0;
+#pragma unroll
+    for (int i = 0; i < kSelBins / kSelThreads; ++i) {
+      if (excl + v[i] >= st.k_rem) { b = i; break; }
+      excl += v[i];
+    }
+    s_res[0] = tid * (kSelBins / kSelThreads) + b;
+    s_res[1] = st.k_rem - excl;
+  }
+  __syncthreads();
+  SelState out;
+  out.prefix = (st.prefix << kSelBits[p]) | (unsigned long long)s_res[0];
+  out.k_rem = s_res[1];
+  out.pad = 0;
+  __syncthreads();
+  return out;
+}
+
+// pass < kSelPasses: histogram the pass's digit.  pass == kSelPasses: emit the anchors whose key is <= the k-th key.
+// grid (chunks, levels); hist [passes][levels][kSelBins]; state [passes + 1][levels] (state[0] = initial).
+__global__ void __launch_bounds__(kSelThreads) rpn_select_pass_kernel(const float* __restrict__ objectness, LevelOffsets lv,
+                                                                      LevelTopK topk, int pass, int* __restrict__ hist,
+                                                                      SelState* __restrict__ state, int num_levels,
+                                                                      int pre_top_n, uint64_t* __restrict__ cand_keys,
+                                                                      int32_t* __restrict__ cand_count) {
+  __shared__ int s_hist[kSelBins];
+  __shared__ int s_scan[32];
+  __shared__ int s_res[2];
+  const int l = blockIdx.y, tid = threadIdx.x;
+  const int begin = lv.start[l], end = lv.start[l + 1];
+  if (begin >= end) return;
+  // state[p] = prefix / remaining rank after the histogram of pass p - 1 has been resolved (written by launch p)
+  SelState st;
+  st.prefix = 0; st.k_rem = topk.k[l]; st.pad = 0;
+  if (pass > 0) {
+    if (pass > 1) st = state[(size_t)(pass - 1) * num_levels + l];
+    st = sel_resolve(st, hist + ((size_t)(pass - 1) * num_levels + l) * kSelBins, pass - 1, s_scan, s_res);
+    if (blockIdx.x == 0 && tid == 0) state[(size_t)pass * num_levels + l] = st;
+  }
+  if (pass < kSelPasses) {
+    for (int i = tid; i < kSelBins; i += kSelThreads) s_hist[i] = 0;
+    __syncthreads();
+    const int shift = kSelShift[pass], mask = (1 << kSelBits[pass]) - 1;
+    for (int i = begin + blockIdx.x * kSelThreads + tid; i < end; i += gridDim.x * kSelThreads) {
+      const uint64_t key = rpn_rank_key(objectness[i], (uint32_t)i);
+      if (pass == 0 || (key >> (shift + kSelBits[pass])) == st.prefix) atomicAdd(&s_hist[(int)(key >> shift) & mask], 1);
+    }
+    __syncthreads();
+    int* gh = hist + ((size_t)pass * num_levels + l) * kSelBins;
+    for (int i = tid; i < kSelBins; i += kSelThreads)
+      if (s_hist[i]) atomicAdd(&gh[i], s_hist[i]);
+  } else {
+    const uint64_t kth = st.prefix;  // all 52 bits resolved
+    uint64_t* dst = cand_keys + (size_t)l * pre_top_n;
+    for (int i = begin + blockIdx.x * kSelThreads + tid; i < end; i += gridDim.x * kSelThreads) {
+      const float logit = objectness[i];
+      if (rpn_rank_key(logit, (uint32_t)i) <= kth) {
+        const int pos = atomicAdd(&cand_count[l], 1);
+        dst[pos] = make_cand_key((uint32_t)l, logit, (uint32_t)i);  // exactly min(pre_top_n, level size) of these
+      }
+    }
+  }
+}
+
+// candidate keys of all levels (unordered within a level) -> one padded array for the sort
+__global__ void rpn_pack_keys_kernel(const uint64_t* __restrict__ cand_keys, LevelOffsets lv, int pre_top_n, int n_pow2,
+                                     uint64_t* __restrict__ keys) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pow2; i += gridDim.x * blockDim.x) {
     uint64_t k = kPadKey;
-    if (i < n) {
-      int l = 0;
-      while (l + 1 < lv.num_levels && i >= lv.start[l + 1]) ++l;
-      k = make_cand_key((uint32_t)l, objectness[i], (uint32_t)i);
+    int rem = i;
+    for (int l = 0; l < lv.num_levels; ++l) {
+      const int kl = min(pre_top_n, lv.start[l + 1] - lv.start[l]);
+      if (rem < kl) { k = cand_keys[(size_t)l * pre_top_n + rem]; break; }
+      rem -= kl;
     }
     keys[i] = k;
   }
@@ -44,7 +140,7 @@ __device__ __forceinline__ float4 clip_box(float4 b, float wf, float hf) {
 }
 
 // Single CTA: walk the levels' top-k in order, clip, drop small / low-score boxes, compact in order.
-__global__ void __launch_bounds__(1024) rpn_select_kernel(const uint64_t* __restrict__ keys, int n_pow2,
+__global__ void __launch_bounds__(1024) rpn_select_kernel(const uint64_t* __restrict__ keys, LevelTopK topk,
                                                           const float4* __restrict__ proposals, int num_levels,
                                                           int pre_top_n, float img_w, float img_h, float min_size,
                                                           float score_thresh, float4* __restrict__ cbox,
@@ -55,10 +151,9 @@ __global__ void __launch_bounds__(1024) rpn_select_kernel(const uint64_t* __rest
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_base = 0;
   __syncthreads();
-  for (int l = 0; l < num_levels; ++l) {
-    const int start = lower_bound_u64(keys, n_pow2, (uint64_t)l << (32 + kRowBits));
-    const int end = lower_bound_u64(keys, n_pow2, (uint64_t)(l + 1) << (32 + kRowBits));
-    const int k = min(pre_top_n, end - start);
+  int start = 0;
+  for (int l = 0; l < num_levels; start += topk.k[l], ++l) {  // the sorted keys hold exactly topk.k[l] entries per level
+    const int k = topk.k[l];
     for (int r0 = 0; r0 < k; r0 += 1024) {
       const int r = r0 + tid;
       bool ok = false;
@@ -261,10 +356,14 @@ extern "C" int isb_rpn_filter(isb_handle* h, const float* proposals, const float
     ISB_CUDA(h, cudaMemsetAsync(out_count, 0, sizeof(int32_t), s));
     return ISB_OK;
   }
-  const int n = (int)total, n_pow2 = next_pow2(n), cmax = (int)cand_max;
+  const int cmax = (int)cand_max, n_pow2 = next_pow2(cmax);
   const size_t b_keys = up256((size_t)n_pow2 * 8), b_box = up256((size_t)cmax * 16), b_sc = up256((size_t)cmax * 4),
-               b_lvl = up256((size_t)cmax * 4), b_keep = up256((size_t)cmax * 8);
-  int rc = ensure_scratch(h, b_keys + b_box + b_sc + b_lvl + b_keep + 512);
+               b_lvl = up256((size_t)cmax * 4), b_keep = up256((size_t)cmax * 8),
+               b_cand = up256((size_t)num_levels * pre_nms_top_n * 8), b_sorted = up256((size_t)cmax * 8),
+               b_rank = up256((size_t)cmax * 4),
+               b_hist = up256((size_t)kSelPasses * num_levels * kSelBins * 4 + (size_t)num_levels * 4),
+               b_state = up256((size_t)(kSelPasses + 1) * num_levels * sizeof(SelState));
+  int rc = ensure_scratch(h, b_keys + b_box + b_sc + b_lvl + b_keep + b_cand + b_sorted + b_rank + b_hist + b_state + 512);
   if (rc != ISB_OK) return rc;
   if ((rc = ensure_nms_ws(h, cmax)) != ISB_OK) return rc;
   char* p = static_cast<char*>(h->scratch);
@@ -273,12 +372,39 @@ extern "C" int isb_rpn_filter(isb_handle* h, const float* proposals, const float
   float* cscore = (float*)p;      p += b_sc;
   int32_t* clvl = (int32_t*)p;    p += b_lvl;
   int64_t* keep = (int64_t*)p;    p += b_keep;
+  uint64_t* cand = (uint64_t*)p;  p += b_cand;
+  uint64_t* sorted = (uint64_t*)p; p += b_sorted;
+  int32_t* rank = (int32_t*)p;    p += b_rank;
+  int* hist = (int*)p;            // [passes][levels][bins] then cand_count [levels]
+  int32_t* cand_count = hist + (size_t)kSelPasses * num_levels * kSelBins;
+  p += b_hist;
+  SelState* state = (SelState*)p; p += b_state;
   int32_t* n_dev = (int32_t*)p;   // [0] candidates, [2] kept count
-  const int blocks = (n_pow2 + 255) / 256 < 8 * h->num_sms ? (n_pow2 + 255) / 256 : 8 * h->num_sms;
-  rpn_keys_kernel<<<blocks, 256, 0, s>>>(objectness, lv, n, n_pow2, keys);
-  ISB_LAUNCH_CHECK(h, "rpn_keys_kernel");
-  if ((rc = launch_sort_u64(h, keys, n_pow2, s)) != ISB_OK) return rc;
-  rpn_select_kernel<<<1, 1024, 0, s>>>(keys, n_pow2, reinterpret_cast<const float4*>(proposals), num_levels, pre_nms_top_n,
+  LevelTopK topk;
+  memset(&topk, 0, sizeof(topk));
+  int max_level = 0;
+  for (int l = 0; l < num_levels; ++l) {
+    topk.k[l] = anchors_per_level[l] < pre_nms_top_n ? anchors_per_level[l] : pre_nms_top_n;
+    if (anchors_per_level[l] > max_level) max_level = anchors_per_level[l];
+  }
+  ISB_CUDA(h, cudaMemsetAsync(hist, 0, b_hist, s));
+  int chunks = (max_level + kSelThreads * 8 - 1) / (kSelThreads * 8);
+  if (chunks > 4 * h->num_sms) chunks = 4 * h->num_sms;
+  if (chunks < 1) chunks = 1;
+  for (int pass = 0; pass <= kSelPasses; ++pass) {
+    rpn_select_pass_kernel<<<dim3(chunks, num_levels), kSelThreads, 0, s>>>(objectness, lv, topk, pass, hist, state, num_levels,
+                                                                            pre_nms_top_n, cand, cand_count);
+    ISB_LAUNCH_CHECK(h, "rpn_select_pass_kernel");
+  }
+  rpn_pack_keys_kernel<<<(n_pow2 + 255) / 256, 256, 0, s>>>(cand, lv, pre_nms_top_n, n_pow2, keys);
+  ISB_LAUNCH_CHECK(h, "rpn_pack_keys_kernel");
+  if (cmax <= kRankSortMax) {
+    if ((rc = launch_rank_sort_u64(h, keys, cmax, nullptr, rank, sorted, s)) != ISB_OK) return rc;
+  } else {
+    if ((rc = launch_sort_u64(h, keys, n_pow2, s)) != ISB_OK) return rc;
+    sorted = keys;
+  }
+  rpn_select_kernel<<<1, 1024, 0, s>>>(sorted, topk, reinterpret_cast<const float4*>(proposals), num_levels, pre_nms_top_n,
                                        (float)img_w, (float)img_h, min_size, score_thresh, cbox, cscore, clvl, n_dev);
   ISB_LAUNCH_CHECK(h, "rpn_select_kernel");
   NmsCall c;

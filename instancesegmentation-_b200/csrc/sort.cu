@@ -66,6 +66,62 @@ __global__ void __launch_bounds__(kSortThreads) sort_merge_chunks_kernel(uint64_
   for (int i = threadIdx.x; i < kSortChunk; i += kSortThreads) keys[base + i] = s[i];
 }
 
+// ---- rank sort: for up to a few ten thousand UNIQUE keys ------------------------------------------------
+// rank(i) = number of keys smaller than key i; out[rank(i)] = key i.  O(n^2) compares, but they are perfectly
+// parallel, barrier-free and need one launch each for counting and scattering: 23 M compares for the 4819 RPN
+// candidates take a few microseconds, where the bitonic network needs ~90 dependent stages.  grid (i-blocks, j-slices):
+// a CTA counts, for its 256 keys, the smaller keys inside its slice of the array (staged through shared memory)
+// and adds the partial count to rank[i].
+constexpr int kRankThreads = 256;
+
+__global__ void __launch_bounds__(kRankThreads) rank_count_kernel(const uint64_t* __restrict__ keys, int n_max,
+                                                                  const int32_t* __restrict__ n_dev, int slice,
+                                                                  int32_t* __restrict__ rank) {
+  __shared__ uint64_t tile[kRankThreads];
+  const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  const int i = blockIdx.x * kRankThreads + threadIdx.x;
+  if (blockIdx.x * kRankThreads >= n) return;  // CTA-uniform
+  const int jb = blockIdx.y * slice, je = min(n, jb + slice);
+  if (jb >= je) return;
+  const uint64_t mine = i < n ? keys[i] : 0ull;
+  int cnt = 0;
+  for (int j0 = jb; j0 < je; j0 += kRankThreads) {
+    __syncthreads();
+    const int j = j0 + threadIdx.x;
+    tile[threadIdx.x] = j < je ? keys[j] : ~0ull;  // pad: never smaller than a real key
+    __syncthreads();
+#pragma unroll 8
+    for (int t = 0; t < kRankThreads; ++t) cnt += tile[t] < mine ? 1 : 0;
+  }
+  if (i < n && cnt) atomicAdd(&rank[i], cnt);
+}
+
+__global__ void rank_scatter_kernel(const uint64_t* __restrict__ keys, int n_max, const int32_t* __restrict__ n_dev,
+                                    const int32_t* __restrict__ rank, uint64_t* __restrict__ out) {
+  const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[rank[i]] = keys[i];
+}
+
+// keys [n] unique -> out [n] ascending; rank: int32 scratch [n_max].  n is min(*n_dev, n_max) when n_dev != nullptr.
+int launch_rank_sort_u64(isb_handle* h, const uint64_t* keys, int n_max, const int32_t* n_dev, int32_t* rank, uint64_t* out,
+                         cudaStream_t s) {
+  if (n_max <= 0) return ISB_OK;
+  ISB_CUDA(h, cudaMemsetAsync(rank, 0, (size_t)n_max * sizeof(int32_t), s));
+  const int iblocks = (n_max + kRankThreads - 1) / kRankThreads;
+  int slices = (4 * h->num_sms + iblocks - 1) / iblocks;  // enough CTAs for ~4 per SM
+  if (slices > iblocks) slices = iblocks;
+  if (slices < 1) slices = 1;
+  int slice = (n_max + slices - 1) / slices;
+  slice = (slice + kRankThreads - 1) / kRankThreads * kRankThreads;
+  slices = (n_max + slice - 1) / slice;
+  rank_count_kernel<<<dim3(iblocks, slices), kRankThreads, 0, s>>>(keys, n_max, n_dev, slice, rank);
+  ISB_LAUNCH_CHECK(h, "rank_count_kernel");
+  rank_scatter_kernel<<<(n_max + 255) / 256 < 4 * h->num_sms ? (n_max + 255) / 256 : 4 * h->num_sms, 256, 0, s>>>(keys, n_max, n_dev,
+                                                                                                                 rank, out);
+  ISB_LAUNCH_CHECK(h, "rank_scatter_kernel");
+  return ISB_OK;
+}
+
 int launch_sort_u64(isb_handle* h, uint64_t* keys, int n_pow2, cudaStream_t s) {
   if (n_pow2 <= 1) return ISB_OK;
   if (n_pow2 & (n_pow2 - 1)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "sort length %d is not a power of two", n_pow2);
