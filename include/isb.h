@@ -133,6 +133,15 @@ ISB_API int isb_fast_nms(isb_handle* h, const float* box, const float* scores, c
                  float* out_box, float* out_score, int64_t* out_class, float* out_coef, int32_t* count,
                  isb_stream stream);
 
+/* utils_bbox.py:102-140 traditional_non_max_suppression(box[n,4], class_scores[n,C], coef[n,K], max_scores[n]):
+ * class = argmax over the C foreground scores, greedy per-class NMS (torchvision semantics, IoU > nms_iou
+ * suppresses, unshifted boxes) on max_scores, concatenation ordered by score, first max_det rows.
+ * Outputs sized for max_det rows; *count (device int32) receives the number of rows. */
+ISB_API int isb_traditional_nms(isb_handle* h, const float* box, const float* class_scores, const float* coef,
+                        const float* max_scores, int32_t n, int32_t num_fg_classes, int32_t num_coef, double nms_iou,
+                        int32_t max_det, float* out_box, float* out_score, int64_t* out_class, float* out_coef,
+                        int32_t* count, isb_stream stream);
+
 /* utils_bbox.py:142-152 yolact_correct_boxes(boxes[m,4], (H,W)) -> [m,4] */
 ISB_API int isb_correct_boxes(isb_handle* h, const float* boxes, int64_t m, int32_t out_h, int32_t out_w, float* out,
                       isb_stream stream);

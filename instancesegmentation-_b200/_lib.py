@@ -17,7 +17,7 @@ SYMBOLS = (
     "isb_version", "isb_create", "isb_destroy", "isb_last_error", "isb_workspace_bytes", "isb_launch_count",
     "isb_profile_begin", "isb_profile_read",
     "isb_yolact_detect", "isb_yolact_detect_host", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
-    "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_assemble",
+    "isb_traditional_nms", "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_assemble",
     "isb_box_decode", "isb_nms", "isb_batched_nms", "isb_ms_roi_align", "isb_mask_select_sigmoid", "isb_resize_boxes",
     "isb_paste_masks", "isb_rpn_filter", "isb_box_postprocess",
 )
@@ -87,6 +87,7 @@ def load():
         lib.isb_decode_boxes.argtypes = [vp, vp, vp, i64, f32, f32, vp, vp]
         lib.isb_jaccard.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp, vp]
         lib.isb_fast_nms.argtypes = [vp, vp, vp, vp, i32, i32, i32, f32, i32, i32, vp, vp, vp, vp, vp, vp]
+        lib.isb_traditional_nms.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, C.c_double, i32, vp, vp, vp, vp, vp, vp]
         lib.isb_correct_boxes.argtypes = [vp, vp, i64, i32, i32, vp, vp]
         lib.isb_crop.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
         lib.isb_mask_logits.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]

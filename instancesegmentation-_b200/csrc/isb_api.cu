@@ -14,6 +14,9 @@ int launch_correct_boxes(isb_handle*, const float*, int64_t, int, int, float*, c
 int launch_crop(isb_handle*, const float*, const float*, int, int, int, float*, cudaStream_t);
 int launch_det_layout(isb_handle*, const float*, int, int, int, int, int, DetRec*, int32_t*, cudaStream_t);
 int launch_mask_logits(isb_handle*, const float*, const float*, int64_t, int, float*, cudaStream_t);
+int launch_row_argmax(isb_handle*, const float*, int, int, int32_t*, cudaStream_t);
+int launch_trad_gather(isb_handle*, const int64_t*, const int32_t*, int, const float*, const float*, const int32_t*, const float*,
+                       float*, float*, int64_t*, float*, int32_t*, cudaStream_t);
 }  // namespace isb
 
 using namespace isb;
@@ -87,6 +90,7 @@ static void free_ws(isb_handle* h) {
   cudaFree(h->nms_keys);
   cudaFree(h->nms_keys2);
   cudaFree(h->nms_rank);
+  cudaFree(h->nms_slabel);
   cudaFree(h->nms_sbox);
   cudaFree(h->nms_order);
   cudaFree(h->nms_mask);
@@ -435,6 +439,47 @@ extern "C" int isb_fast_nms(isb_handle* h, const float* box, const float* scores
   np.out_coef = out_coef;
   np.out_count = count;
   return launch_fast_nms(h, np, s);
+}
+
+extern "C" int isb_traditional_nms(isb_handle* h, const float* box, const float* class_scores, const float* coef,
+                                   const float* max_scores, int32_t n, int32_t num_fg_classes, int32_t num_coef,
+                                   double nms_iou, int32_t max_det, float* out_box, float* out_score, int64_t* out_class,
+                                   float* out_coef, int32_t* count, isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (!count || !out_box || !out_score || !out_class || !out_coef) ISB_FAIL(h, ISB_ERR_BAD_ARG, "traditional_nms: null output");
+  if (n < 0 || num_fg_classes <= 0 || max_det <= 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "traditional_nms: bad size");
+  if (num_coef != ISB_NUM_COEF) ISB_FAIL(h, ISB_ERR_BAD_ARG, "traditional_nms: num_coef must be %d", ISB_NUM_COEF);
+  if (num_fg_classes >= (1 << kClassBits)) ISB_FAIL(h, ISB_ERR_LIMIT, "traditional_nms: classes %d >= 2^%d", num_fg_classes, kClassBits);
+  if (n >= (1 << kRowBits)) ISB_FAIL(h, ISB_ERR_LIMIT, "traditional_nms: n %d >= 2^%d", n, kRowBits);
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n == 0) {
+    ISB_CUDA(h, cudaMemsetAsync(count, 0, sizeof(int32_t), s));
+    return ISB_OK;
+  }
+  if (!box || !class_scores || !coef || !max_scores || !aligned16(box) || !aligned16(coef) || !aligned16(out_box) ||
+      !aligned16(out_coef))
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "traditional_nms: null or misaligned pointer");
+  const size_t b_lab = ((size_t)n * 4 + 255) & ~(size_t)255, b_keep = ((size_t)n * 8 + 255) & ~(size_t)255;
+  int rc = ensure_scratch(h, b_lab + b_keep + 256);
+  if (rc != ISB_OK) return rc;
+  int32_t* labels = reinterpret_cast<int32_t*>(h->scratch);
+  int64_t* keep = reinterpret_cast<int64_t*>(static_cast<char*>(h->scratch) + b_lab);
+  int32_t* kept = reinterpret_cast<int32_t*>(static_cast<char*>(h->scratch) + b_lab + b_keep);
+  if ((rc = launch_row_argmax(h, class_scores, n, num_fg_classes, labels, s)) != ISB_OK) return rc;
+  NmsCall c;
+  memset(&c, 0, sizeof(c));
+  c.boxes = reinterpret_cast<const float4*>(box);
+  c.scores = max_scores;
+  c.labels32 = labels;
+  c.n_max = n;
+  c.iou_threshold = nms_iou;
+  c.max_keep = max_det;  // the global order is by score, so the first max_det kept boxes are the final answer (:136)
+  c.keep = keep;
+  c.count = kept;
+  if ((rc = launch_nms(h, c, s)) != ISB_OK) return rc;
+  return launch_trad_gather(h, keep, kept, max_det, box, max_scores, labels, coef, out_box, out_score, out_class, out_coef,
+                            count, s);
 }
 
 extern "C" int isb_correct_boxes(isb_handle* h, const float* boxes, int64_t m, int32_t out_h, int32_t out_w, float* out,

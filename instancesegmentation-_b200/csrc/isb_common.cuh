@@ -305,6 +305,7 @@ struct isb_handle {
   uint64_t* nms_keys;      // [pow2(nms_cap)]
   uint64_t* nms_keys2;     // [nms_cap]  rank-sorted keys
   int32_t* nms_rank;       // [nms_cap]  rank scratch of the rank sort
+  int32_t* nms_slabel;     // [nms_cap]  class per sorted position (per-class NMS without offsets)
   float4* nms_sbox;        // [nms_cap]  boxes in score order (offset by class for batched NMS)
   int32_t* nms_order;      // [nms_cap]  original index per sorted position
   uint64_t* nms_mask;      // [nms_cap][ceil(nms_cap/64)] suppression bits
@@ -424,6 +425,7 @@ struct NmsCall {
   const float* scores;     // [n]
   const int64_t* idxs64;   // batched NMS categories as int64 (boxes.py:38) or nullptr
   const int32_t* idxs32;   // ... or as int32 (internal pipelines) or nullptr
+  const int32_t* labels32; // per-class NMS on the UNSHIFTED boxes (utils_bbox.py:102-140): classes < 4096, n < 2^20
   int32_t n_max;           // upper bound of n known on the host (sizes grids and workspace)
   const int32_t* n_dev;    // actual n on the device, or nullptr when n == n_max
   double iou_threshold;

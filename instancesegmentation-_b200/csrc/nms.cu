@@ -37,23 +37,30 @@ __global__ void nms_max_coord_kernel(const float4* __restrict__ boxes, int n_max
   if ((threadIdx.x & 31) == 0) atomicMin(&scalars[0], float_desc_bits(m));  // smaller desc-bits == larger float
 }
 
-__global__ void nms_keys_kernel(const float* __restrict__ scores, int n_max, const int32_t* __restrict__ n_dev,
-                                int n_pow2, uint64_t* __restrict__ keys) {
+// key = ~score | index; with `labels` (per-class NMS without coordinate offsets) the low word is
+// label << 20 | index, so equal scores order by class first -- the order of the reference's per-class concatenation.
+__global__ void nms_keys_kernel(const float* __restrict__ scores, const int32_t* __restrict__ labels, int n_max,
+                                const int32_t* __restrict__ n_dev, int n_pow2, uint64_t* __restrict__ keys) {
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pow2; i += gridDim.x * blockDim.x)
-    keys[i] = i < n ? (((uint64_t)float_desc_bits(scores[i]) << 32) | (uint32_t)i) : kPadKey;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pow2; i += gridDim.x * blockDim.x) {
+    uint32_t low = (uint32_t)i;
+    if (labels && i < n) low |= (uint32_t)labels[i] << kRowBits;
+    keys[i] = i < n ? (((uint64_t)float_desc_bits(scores[i]) << 32) | low) : kPadKey;
+  }
 }
 
 __global__ void nms_gather_kernel(const uint64_t* __restrict__ keys, const float4* __restrict__ boxes,
                                   const int64_t* __restrict__ idxs64, const int32_t* __restrict__ idxs32, int n_max,
                                   const int32_t* __restrict__ n_dev, const uint32_t* __restrict__ scalars,
-                                  float4* __restrict__ sbox, int32_t* __restrict__ order) {
+                                  const int32_t* __restrict__ labels, float4* __restrict__ sbox,
+                                  int32_t* __restrict__ order, int32_t* __restrict__ slabel) {
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   const bool batched = idxs64 || idxs32;
   float step = 0.0f;
   if (batched) step = float_from_desc_bits(scalars[0]) + 1.0f;  // boxes.py:78  (max_coordinate + 1)
   for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
-    const int i = (int)(uint32_t)keys[p];
+    const int i = labels ? (int)((uint32_t)keys[p] & (uint32_t)kRowMask) : (int)(uint32_t)keys[p];
+    if (labels) slabel[p] = labels[i];
     float4 b = boxes[i];
     if (batched) {
       const float off = (idxs64 ? (float)idxs64[i] : (float)idxs32[i]) * step;  // idxs.to(boxes) * (max + 1)
@@ -72,23 +79,26 @@ __global__ void nms_gather_kernel(const uint64_t* __restrict__ keys, const float
 // thing in the loop.
 __global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__ sbox, int n_max,
                                                       const int32_t* __restrict__ n_dev, float thr, int words,
-                                                      uint64_t* __restrict__ mask) {
+                                                      const int32_t* __restrict__ slabel, uint64_t* __restrict__ mask) {
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   const int rb = blockIdx.y, cb = blockIdx.x;
   if (rb * 64 >= n || cb * 64 >= n) return;
   __shared__ float4 cbox[64];
   __shared__ float carea[64];
+  __shared__ int clabel[64];
   const int t = threadIdx.x;
   const int cj = cb * 64 + t;
   if (cj < n) {
     cbox[t] = sbox[cj];
     carea[t] = box_area(cbox[t]);
+    clabel[t] = slabel ? slabel[cj] : 0;
   }
   __syncthreads();
   const int ri = rb * 64 + t;
   if (ri >= n) return;
   const float4 a = sbox[ri];
   const float aa = box_area(a);
+  const int alabel = slabel ? slabel[ri] : 0;  // per-class mode: only boxes of the same class interact
   const int ncol = min(64, n - cb * 64);
   const bool zero_hits = 0.0f > thr;  // a zero IoU suppresses only for a negative threshold
   uint64_t bits = 0;
@@ -101,7 +111,7 @@ __global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__
     bool hit;
     if (inter == 0.0f && uni != 0.0f && fabsf(uni) <= 3.402823466e38f) hit = zero_hits;
     else hit = inter / uni > thr;
-    if (hit) bits |= 1ull << j;
+    if (hit && clabel[j] == alabel) bits |= 1ull << j;
   }
   if (rb == cb) bits &= ~(1ull << t);  // a box does not suppress itself
   mask[(size_t)ri * words + cb] = bits;
@@ -198,10 +208,11 @@ static void free_nms_ws(isb_handle* h) {
   cudaFree(h->nms_keys);
   cudaFree(h->nms_keys2);
   cudaFree(h->nms_rank);
+  cudaFree(h->nms_slabel);
   cudaFree(h->nms_sbox);
   cudaFree(h->nms_order);
   cudaFree(h->nms_mask);
-  h->nms_keys = nullptr; h->nms_keys2 = nullptr; h->nms_rank = nullptr; h->nms_sbox = nullptr; h->nms_order = nullptr; h->nms_mask = nullptr;
+  h->nms_keys = nullptr; h->nms_keys2 = nullptr; h->nms_rank = nullptr; h->nms_slabel = nullptr; h->nms_sbox = nullptr; h->nms_order = nullptr; h->nms_mask = nullptr;
   h->nms_cap = 0;
 }
 
@@ -217,11 +228,12 @@ int ensure_nms_ws(isb_handle* h, int64_t n) {
   ISB_CUDA(h, cudaMalloc((void**)&h->nms_keys, (size_t)cap * 8));
   ISB_CUDA(h, cudaMalloc((void**)&h->nms_keys2, (size_t)cap * 8));
   ISB_CUDA(h, cudaMalloc((void**)&h->nms_rank, (size_t)cap * 4));
+  ISB_CUDA(h, cudaMalloc((void**)&h->nms_slabel, (size_t)cap * 4));
   ISB_CUDA(h, cudaMalloc((void**)&h->nms_sbox, (size_t)cap * 16));
   ISB_CUDA(h, cudaMalloc((void**)&h->nms_order, (size_t)cap * 4));
   ISB_CUDA(h, cudaMalloc((void**)&h->nms_mask, (size_t)cap * words * 8));
   h->nms_cap = cap;
-  h->ws_bytes += (size_t)cap * (40 + words * 8);
+  h->ws_bytes += (size_t)cap * (44 + words * 8);
   return ISB_OK;
 }
 
@@ -261,7 +273,7 @@ int launch_nms(isb_handle* h, const NmsCall& c, cudaStream_t s) {
     nms_max_coord_kernel<<<blocks, 256, 0, s>>>(c.boxes, n, c.n_dev, h->nms_scalars);
     ISB_LAUNCH_CHECK(h, "nms_max_coord_kernel");
   }
-  nms_keys_kernel<<<(n_pow2 + 255) / 256, 256, 0, s>>>(c.scores, n, c.n_dev, n_pow2, h->nms_keys);
+  nms_keys_kernel<<<(n_pow2 + 255) / 256, 256, 0, s>>>(c.scores, c.labels32, n, c.n_dev, n_pow2, h->nms_keys);
   ISB_LAUNCH_CHECK(h, "nms_keys_kernel");
   const uint64_t* sorted = h->nms_keys;
   if (n <= kRankSortMax) {
@@ -271,9 +283,10 @@ int launch_nms(isb_handle* h, const NmsCall& c, cudaStream_t s) {
     return rc;
   }
   nms_gather_kernel<<<blocks, 256, 0, s>>>(sorted, c.boxes, c.idxs64, c.idxs32, n, c.n_dev, h->nms_scalars,
-                                           h->nms_sbox, h->nms_order);
+                                           c.labels32, h->nms_sbox, h->nms_order, h->nms_slabel);
   ISB_LAUNCH_CHECK(h, "nms_gather_kernel");
-  nms_mask_kernel<<<dim3(words, words), 64, 0, s>>>(h->nms_sbox, n, c.n_dev, thr_f, words, h->nms_mask);
+  nms_mask_kernel<<<dim3(words, words), 64, 0, s>>>(h->nms_sbox, n, c.n_dev, thr_f, words,
+                                                    c.labels32 ? h->nms_slabel : nullptr, h->nms_mask);
   ISB_LAUNCH_CHECK(h, "nms_mask_kernel");
   const size_t smem = (size_t)words * 8;
   if (smem > 64 * 1024) ISB_FAIL(h, ISB_ERR_LIMIT, "nms scan shared memory");

@@ -82,6 +82,41 @@ __global__ void __launch_bounds__(1024) det_layout_kernel(const float4* __restri
   if (j == 0) *total_out = total;
 }
 
+// utils_bbox.py:104 torch.argmax(class_thre, dim=-1): first maximum of every row (a NaN entry wins, as in torch)
+__global__ void row_argmax_kernel(const float* __restrict__ scores, int n, int ncols, int32_t* __restrict__ labels) {
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n; r += gridDim.x * blockDim.x) {
+    const float* row = scores + (size_t)r * ncols;
+    float best = row[0];
+    int arg = 0;
+    for (int c = 1; c < ncols && best == best; ++c) {
+      const float v = row[c];
+      if (v > best || v != v) { best = v; arg = c; }
+    }
+    labels[r] = arg;
+  }
+}
+
+// utils_bbox.py:126-139: rows of the kept candidates, already in final order
+__global__ void trad_gather_kernel(const int64_t* __restrict__ keep, const int32_t* __restrict__ count, int max_det,
+                                   const float4* __restrict__ boxes, const float* __restrict__ scores,
+                                   const int32_t* __restrict__ labels, const float* __restrict__ coef,
+                                   float4* __restrict__ out_box, float* __restrict__ out_score,
+                                   int64_t* __restrict__ out_class, float* __restrict__ out_coef,
+                                   int32_t* __restrict__ out_count) {
+  const int m = min(*count, max_det);
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < m * 8; t += gridDim.x * blockDim.x) {
+    const int d = t >> 3, q = t & 7;
+    const int64_t i = keep[d];
+    reinterpret_cast<float4*>(out_coef + (size_t)d * ISB_NUM_COEF)[q] = reinterpret_cast<const float4*>(coef + i * ISB_NUM_COEF)[q];
+    if (q == 0) {
+      out_box[d] = boxes[i];
+      out_score[d] = scores[i];
+      out_class[d] = (int64_t)labels[i];
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) *out_count = m;
+}
+
 // utils_bbox.py:223 inner product: logits[pix, j] = sum_k proto[pix, k] * coef[j, k]
 __global__ void mask_logits_kernel(const float* __restrict__ proto, const float* __restrict__ coef, int64_t npix, int m,
                                    float* __restrict__ out) {
@@ -145,6 +180,20 @@ int launch_det_layout(isb_handle* h, const float* boxes, int m, int hgt, int wid
                       int32_t* total_out, cudaStream_t s) {
   det_layout_kernel<<<1, 1024, 0, s>>>(reinterpret_cast<const float4*>(boxes), m, hgt, wid, proto_h, proto_w, out, total_out);
   ISB_LAUNCH_CHECK(h, "det_layout_kernel");
+  return ISB_OK;
+}
+int launch_row_argmax(isb_handle* h, const float* scores, int n, int ncols, int32_t* labels, cudaStream_t s) {
+  row_argmax_kernel<<<grid_for(n, 128, h->num_sms), 128, 0, s>>>(scores, n, ncols, labels);
+  ISB_LAUNCH_CHECK(h, "row_argmax_kernel");
+  return ISB_OK;
+}
+int launch_trad_gather(isb_handle* h, const int64_t* keep, const int32_t* count, int max_det, const float* boxes,
+                       const float* scores, const int32_t* labels, const float* coef, float* out_box, float* out_score,
+                       int64_t* out_class, float* out_coef, int32_t* out_count, cudaStream_t s) {
+  trad_gather_kernel<<<grid_for((int64_t)max_det * 8, 256, h->num_sms), 256, 0, s>>>(
+      keep, count, max_det, reinterpret_cast<const float4*>(boxes), scores, labels, coef, reinterpret_cast<float4*>(out_box),
+      out_score, out_class, out_coef, out_count);
+  ISB_LAUNCH_CHECK(h, "trad_gather_kernel");
   return ISB_OK;
 }
 int launch_mask_logits(isb_handle* h, const float* proto, const float* coef, int64_t npix, int m, float* out,

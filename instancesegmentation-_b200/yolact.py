@@ -119,10 +119,33 @@ class BBoxUtility(object):
         m = int(count.item())  # the one 4-byte D2H a variable-length return needs
         return out_box[:m], out_score[:m], out_cls[:m], out_coef[:m]
 
+    # ------------------------------------------------------------------ utils_bbox.py:102
     def traditional_non_max_suppression(self, box_thre, class_thre, mask_thre, pred_class_max, nms_iou, max_detections):
-        # utils_bbox.py:102-140.  Off by default and broken on CUDA in the reference itself
-        # (labels are created on the CPU at :129); listed as a "next" row in SURVEY.md 8(f).
-        raise NotImplementedError("traditional_nms is outside the B200 hot path (SURVEY.md section 8f, rank 4)")
+        """Per-class greedy NMS (class = argmax of the foreground scores, score = pred_class_max), detections of all
+        classes ordered by score, first max_detections.  The reference builds its label tensor on the CPU (:129) and
+        therefore fails on CUDA inputs; here the labels stay on the device."""
+        box_thre = _cuda_f32(box_thre, "box_thre")
+        class_thre = _cuda_f32(class_thre, "class_thre")
+        mask_thre = _cuda_f32(mask_thre, "mask_thre")
+        pred_class_max = _cuda_f32(pred_class_max, "pred_class_max")
+        dev = box_thre.device
+        n, ncls = class_thre.shape
+        k = mask_thre.shape[1]
+        max_det = int(max_detections)
+        if max_det > _lib.ISB_MAX_DET_LIMIT:
+            raise ValueError(f"max_detections {max_det} > {_lib.ISB_MAX_DET_LIMIT}")
+        h = get_handle(dev.index)
+        out_box = torch.empty((max_det, 4), dtype=torch.float32, device=dev)
+        out_score = torch.empty((max_det,), dtype=torch.float32, device=dev)
+        out_cls = torch.empty((max_det,), dtype=torch.int64, device=dev)
+        out_coef = torch.empty((max_det, k), dtype=torch.float32, device=dev)
+        count = torch.zeros((1,), dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            h.check(h.lib.isb_traditional_nms(h.ptr, _ptr(box_thre), _ptr(class_thre), _ptr(mask_thre), _ptr(pred_class_max),
+                                              n, ncls, k, float(nms_iou), max_det, _ptr(out_box), _ptr(out_score),
+                                              _ptr(out_cls), _ptr(out_coef), _ptr(count), _stream(dev)))
+        m = int(count.item())
+        return out_box[:m], out_score[:m], out_cls[:m], out_coef[:m]
 
     # ------------------------------------------------------------------ utils_bbox.py:142
     def yolact_correct_boxes(self, boxes, image_shape):
@@ -216,7 +239,7 @@ class BBoxUtility(object):
     # ------------------------------------------------------------------ utils_bbox.py:170
     def decode_nms(self, outputs, anchors, confidence, nms_iou, image_shape, traditional_nms=False, max_detections=100):
         if traditional_nms:
-            raise NotImplementedError("traditional_nms=True is outside the B200 hot path (SURVEY.md section 8f)")
+            return self._decode_nms_traditional(outputs, anchors, confidence, nms_iou, image_shape, max_detections)
         # utils_bbox.py:177-180 squeeze the batch dimension: the reference handles one image.
         box, conf, coef, proto = outputs[0], outputs[1], outputs[2], outputs[3]
         box = box.reshape(-1, 4)[None]
@@ -234,3 +257,23 @@ class BBoxUtility(object):
             res = self.decode_nms_batch((box, conf, coef, proto), anchors, confidence, nms_iou, image_shape)
             m = int(res.counts[0].item())
         return res.image(0, m)
+
+    def _decode_nms_traditional(self, outputs, anchors, confidence, nms_iou, image_shape, max_detections):
+        """utils_bbox.py:170-243 with traditional_nms=True (off by default in the reference): the stage kernels chained on
+        the device; torch is used only to slice the surviving rows (:193-204)."""
+        box = _cuda_f32(outputs[0], "box").reshape(-1, 4)
+        conf = _cuda_f32(outputs[1], "conf").reshape(box.shape[0], -1)
+        coef = _cuda_f32(outputs[2], "coef").reshape(box.shape[0], -1)
+        proto = _cuda_f32(outputs[3], "proto")
+        proto = proto.reshape(tuple(proto.shape[-3:]))
+        boxes = self.decode_boxes(box, anchors)                                      # :186
+        fg = conf[:, 1:]                                                             # :193
+        cmax = fg.max(dim=1).values                                                  # :194
+        keep = cmax > confidence                                                     # :195
+        box_thre, class_thre, coef_thre = boxes[keep], fg[keep].contiguous(), coef[keep]
+        if class_thre.shape[0] == 0:                                                 # :203
+            return (None,) * 5
+        b, s, c, k = self.traditional_non_max_suppression(box_thre, class_thre, coef_thre, cmax[keep], nms_iou, max_detections)
+        b = self.yolact_correct_boxes(b, image_shape)                                # :216
+        arg, masks = self.assemble_masks(proto, k, b, image_shape)                   # :223-241
+        return b, s, c, arg, masks

@@ -126,6 +126,30 @@ def yolact_stages(name, seed):
           small=small.numpy(), up=up.numpy(), down=down.numpy())
 
 
+def yolact_traditional(name, seed):
+    """utils_bbox.py:102-140 and the traditional_nms=True branch of decode_nms (CPU only in the reference)."""
+    from . import synth
+    bu = _ref()
+    g = torch.Generator().manual_seed(seed + 7)
+    a, c, k = 500, 6, 32
+    anchors = torch.cat([torch.rand(a, 2, generator=g), torch.rand(a, 2, generator=g) * 0.3 + 0.05], 1)
+    box, conf, coef, proto = synth.yolact_heads(seed, a, num_classes=c, num_coef=k, proto_hw=(20, 24), objects=5, run=25)
+    res = bu.decode_nms((box[None], conf[None], coef[None], proto[None]), anchors, 0.05, 0.5, np.array((45, 70)),
+                        traditional_nms=True, max_detections=40)
+    # stage call on clustered boxes
+    n = 300
+    ctr = torch.rand(10, 2, generator=g)[torch.randint(0, 10, (n,), generator=g)] + torch.randn(n, 2, generator=g) * 0.02
+    wh = torch.rand(n, 2, generator=g) * 0.1 + 0.1
+    nbox = torch.cat([ctr - wh / 2, ctr + wh / 2], 1)
+    scores = torch.rand(n, 5, generator=g)
+    ncoef = torch.tanh(torch.randn(n, k, generator=g))
+    t = bu.traditional_non_max_suppression(nbox, scores, ncoef, scores.max(dim=1).values, 0.4, 50)
+    _save(name, anchors=anchors.numpy(), box=box.numpy(), conf=conf.numpy(), coef=coef.numpy(), proto=proto.numpy(),
+          image_shape=np.array((45, 70)), confidence=0.05, nms_iou=0.5, max_detections=40, **_pack_result(res),
+          t_box=nbox.numpy(), t_scores=scores.numpy(), t_coef=ncoef.numpy(), t_iou=0.4, t_max=50,
+          t_out_box=t[0].numpy(), t_out_score=t[1].numpy(), t_out_cls=t[2].numpy(), t_out_coef=t[3].numpy())
+
+
 def verseg(name, seed, n=5000, top_k=5000, max_det=1024):
     from . import synth
     bu = _ref()
@@ -156,6 +180,7 @@ def main():
     yolact_full("yolact_550_coco_sparse", 2101, 550, 81, (550, 550), 0.05, 0.5, objects=3)
     yolact_full("yolact_544_voc_1080p", 1001, 544, 21, (1080, 1920), 0.5, 0.3)
     verseg("verseg_fastnms", 5001)
+    yolact_traditional("yolact_traditional", 31)
 
 
 if __name__ == "__main__":

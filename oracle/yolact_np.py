@@ -125,6 +125,27 @@ def fast_non_max_suppression(box_thre, class_thre, mask_thre, nms_iou=0.5, top_k
     return box_nms[order2], score_nms[order2], cls_nms[order2], coef_nms[order2]
 
 
+# --------------------------------------------------------------------------- Y15
+def traditional_non_max_suppression(box_thre, class_thre, mask_thre, pred_class_max, nms_iou, max_detections):
+    """utils_bbox.py:102-140 -- class = argmax of the row, per-class torchvision nms on the row maxima, concatenation in
+    class order, stable descending sort by score, first max_detections."""
+    from .maskrcnn_np import nms
+    box_thre = np.asarray(box_thre, dtype=F32)
+    class_thre = np.asarray(class_thre, dtype=F32)
+    mask_thre = np.asarray(mask_thre, dtype=F32)
+    pred_class_max = np.asarray(pred_class_max, dtype=F32)
+    labels = np.argmax(class_thre, axis=-1)                                 # :104
+    bs, ss, cs, ms = [], [], [], []
+    for c in range(class_thre.shape[1]):                                    # :107
+        sel = np.where(labels == c)[0]
+        idx = nms(box_thre[sel], pred_class_max[sel], nms_iou)              # :123
+        bs.append(box_thre[sel][idx]); ss.append(pred_class_max[sel][idx])
+        cs.append(np.full(len(idx), c, np.int64)); ms.append(mask_thre[sel][idx])
+    b, s2, c2, m2 = np.concatenate(bs), np.concatenate(ss), np.concatenate(cs), np.concatenate(ms)
+    order = _argsort_desc_stable(s2, axis=0)[:max_detections]               # :136
+    return b[order], s2[order], c2[order], m2[order]
+
+
 # --------------------------------------------------------------------------- Y8
 def yolact_correct_boxes(boxes, image_shape):
     """utils_bbox.py:142-152 -- scale to pixels, order corners, clamp to the image.
@@ -222,8 +243,8 @@ def assemble_masks(proto, coef, boxes_px, image_shape):
 
 
 # --------------------------------------------------------------------------- Y14
-def decode_nms(outputs, anchors, confidence, nms_iou, image_shape, max_detections=100):
-    """utils_bbox.py:170-243 (traditional_nms=False branch) for one image.
+def decode_nms(outputs, anchors, confidence, nms_iou, image_shape, traditional_nms=False, max_detections=100):
+    """utils_bbox.py:170-243 for one image (Fast NMS by default, per-class greedy NMS with traditional_nms=True).
 
     outputs = (box [1,A,4] | [A,4], conf [.,A,C] softmaxed incl. background column 0,
     coef [.,A,K], proto [.,P,Q,K]).  Returns the reference's 5-tuple or five Nones.
@@ -239,9 +260,13 @@ def decode_nms(outputs, anchors, confidence, nms_iou, image_shape, max_detection
     box_thre, class_thre, coef_thre = boxes[keep], fg[keep], pred_coef[keep]  # :200-202
     if class_thre.shape[0] == 0:                                             # :203
         return None, None, None, None, None
-    box_thre, score, class_ids, coef_thre = fast_non_max_suppression(box_thre, class_thre, coef_thre, nms_iou)  # :207
-    keep2 = score > F32(confidence)                                          # :208
-    box_thre, score, class_ids, coef_thre = box_thre[keep2], score[keep2], class_ids[keep2], coef_thre[keep2]
+    if traditional_nms:                                                      # :213
+        box_thre, score, class_ids, coef_thre = traditional_non_max_suppression(
+            box_thre, class_thre, coef_thre, fg.max(axis=1)[keep], nms_iou, max_detections)
+    else:
+        box_thre, score, class_ids, coef_thre = fast_non_max_suppression(box_thre, class_thre, coef_thre, nms_iou)  # :207
+        keep2 = score > F32(confidence)                                      # :208
+        box_thre, score, class_ids, coef_thre = box_thre[keep2], score[keep2], class_ids[keep2], coef_thre[keep2]
     box_px = yolact_correct_boxes(box_thre, image_shape)                     # :216
     masks_arg, masks = assemble_masks(pred_proto, coef_thre, box_px, image_shape)
     return box_px, score, class_ids, masks_arg, masks

@@ -78,3 +78,17 @@ def test_verseg_fast_nms():
     b, s, c, k = O.fast_non_max_suppression(box, score, coef, 0.5, int(g["top_k"]), int(g["max_det"]))
     assert np.array_equal(s, g["score"]) and np.array_equal(b, g["box"]) and np.array_equal(c, g["cls"])
     assert digest(k) == str(g["coef_digest"])
+
+
+def test_traditional_nms_known_answers():
+    """utils_bbox.py:102-140 and the traditional_nms=True branch of decode_nms, pinned to the reference run on CPU."""
+    g = load_golden("yolact_traditional")
+    t = O.traditional_non_max_suppression(g["t_box"], g["t_scores"], g["t_coef"], g["t_scores"].max(axis=1),
+                                          float(g["t_iou"]), int(g["t_max"]))
+    assert np.array_equal(t[0], g["t_out_box"]) and np.array_equal(t[1], g["t_out_score"])
+    assert np.array_equal(t[2], g["t_out_cls"]) and np.array_equal(t[3], g["t_out_coef"])
+    r = O.decode_nms((g["box"], g["conf"], g["coef"], g["proto"]), g["anchors"], float(g["confidence"]), float(g["nms_iou"]),
+                     g["image_shape"], traditional_nms=True, max_detections=int(g["max_detections"]))
+    assert np.array_equal(r[1], g["scores"]) and np.array_equal(r[2], g["class_ids"])
+    assert_close_f32(r[0], g["boxes"], 1e-5, "boxes")
+    assert_masks_close(r[4], unpack_masks(g), 1e-3, "masks")

@@ -55,6 +55,22 @@ def test_fast_nms_stage(bu, tag, thr, top_k, max_det):
     assert np.array_equal(host(k), g[tag + "_coef"])
 
 
+def test_traditional_nms_stage_and_decode(bu):
+    """Y15: per-class greedy NMS (utils_bbox.py:102-140) and decode_nms(traditional_nms=True), against the reference's
+    CPU outputs: keep set, order, class ids and coefficient rows bit-exact."""
+    g = load_golden("yolact_traditional")
+    smax = g["t_scores"].max(axis=1)
+    b, s, c, k = bu.traditional_non_max_suppression(dev(g["t_box"]), dev(g["t_scores"]), dev(g["t_coef"]), dev(smax),
+                                                    float(g["t_iou"]), int(g["t_max"]))
+    assert np.array_equal(host(s), g["t_out_score"])
+    assert np.array_equal(host(c), g["t_out_cls"]) and c.dtype == torch.int64
+    assert np.array_equal(host(b), g["t_out_box"]) and np.array_equal(host(k), g["t_out_coef"])
+    res = bu.decode_nms((dev(g["box"])[None], dev(g["conf"])[None], dev(g["coef"])[None], dev(g["proto"])[None]),
+                        dev(g["anchors"]), float(g["confidence"]), float(g["nms_iou"]), g["image_shape"],
+                        traditional_nms=True, max_detections=int(g["max_detections"]))
+    _check(g, res)
+
+
 def test_correct_boxes_and_crop_bit_exact(bu):
     g = load_golden("yolact_stages")
     assert np.array_equal(host(bu.yolact_correct_boxes(dev(g["raw"]), np.array([123, 77]))), g["corrected"])
