@@ -26,6 +26,27 @@ constexpr int kNmsThreads = 1024;
 constexpr int kSmemCand = 4096;
 constexpr size_t kNmsSmem = (size_t)kSmemCand * (8 + 8 + 16);  // keys, kept keys, boxes
 
+// Coarse descending bin of a detection key's score, monotone along the key order (best scores -> bin 0): linear in
+// [0, 1] (class probabilities: ~uniform resolution where it matters), everything above 1 in bin 0, everything below 0
+// in the last bin.  Only used to pre-select a superset of the top max_det keys, so resolution affects speed, not results.
+__device__ __forceinline__ int score_bin_desc(uint64_t det_key) {
+  const float s = det_score(det_key);
+  if (!(s == s)) return (__float_as_uint(s) >> 31) ? 2047 : 0;  // -NaN sorts last, +NaN first
+  const float t = fminf(fmaxf(s * 2048.0f, 0.0f), 2047.0f);
+  return 2047 - (int)t;
+}
+
+// Warp-aggregated slot allocation: every lane of the warp calls it; lanes with `want` get consecutive slots from one
+// shared-memory atomicAdd per warp (hundreds of single-address atomics otherwise serialise for microseconds).
+__device__ __forceinline__ int warp_alloc_slot(bool want, int* counter) {
+  const unsigned bal = __ballot_sync(0xffffffffu, want);
+  const int lane = threadIdx.x & 31;
+  int base = 0;
+  if (lane == 0 && bal) base = atomicAdd(counter, __popc(bal));
+  base = __shfl_sync(0xffffffffu, base, 0);
+  return base + __popc(bal & ((1u << lane) - 1u));
+}
+
 // Compare-exchange of register-resident keys across the lanes of a warp: element index i, partner i ^ stride.
 __device__ __forceinline__ void cmpx_lane(uint64_t& v, int i, int stride, int size) {
   const uint64_t o = __shfl_xor_sync(0xffffffffu, v, stride);
@@ -110,6 +131,8 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_kept;
   __shared__ int s_scan[32];
+  __shared__ int s_cls_start[1 << kClassBits];
+  __shared__ int s_cut;
 
   const int b = blockIdx.x;
   const int tid = threadIdx.x;
@@ -145,44 +168,84 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
   // ---- 2. decode boxes of the candidates inside their class window ----------------------
   for (int i = tid; i < n; i += kNmsThreads) cbox[i] = load_box(p, b, cand_row(keys[i]));
   __syncthreads();
-
   // ---- 3. Fast NMS ----------------------------------------------------------------------
-  const bool thr_ok = 0.0f <= p.nms_iou;  // column max of a triu'd matrix is >= 0 (:80-86)
-  for (int j = tid; j < n; j += kNmsThreads) {
-    const uint64_t kj = keys[j];
-    const uint64_t cls_lo = (uint64_t)cand_class(kj) << (32 + kRowBits);
-    // first index of this class: lower_bound over the sorted keys
-    int lo = 0, hi = j;
-    while (lo < hi) {
-      int mid = (lo + hi) >> 1;
-      if (keys[mid] < cls_lo) lo = mid + 1; else hi = mid;
-    }
-    const int start = lo;
-    bool keep = thr_ok && (j - start) < p.top_k;
-    if (keep) {
-      const float4 bj = cbox[j];
-      const float aj = box_area(bj);
-      for (int i = start; i < j; ++i) {
-        const float4 bi = cbox[i];
-        // utils_bbox.py:38-47, with the division skipped when the boxes are disjoint: 0 / union is +-0 for
-        // every finite non-zero union, and thr_ok already established 0 <= nms_iou
-        const float dx = fmaxf(fminf(bi.z, bj.z) - fmaxf(bi.x, bj.x), 0.0f);
-        const float dy = fmaxf(fminf(bi.w, bj.w) - fmaxf(bi.y, bj.y), 0.0f);
-        const float inter = dx * dy;
-        const float uni = (box_area(bi) + aj) - inter;
-        if (inter == 0.0f && uni != 0.0f && fabsf(uni) <= 3.402823466e38f) continue;
-        if (!(inter / uni <= p.nms_iou)) { keep = false; break; }
-      }
-    }
-    if (keep) {
-      int slot = atomicAdd(&s_kept, 1);
-      dkeys[slot] = det_key_from_cand(kj);
-    }
+  // first sorted position of every class that occurs (the keys are class-major)
+  for (int i = tid; i < n; i += kNmsThreads) {
+    const uint32_t c = cand_class(keys[i]);
+    if (i == 0 || cand_class(keys[i - 1]) != c) s_cls_start[c] = i;
   }
   __syncthreads();
-
+  // EIGHT lanes per candidate j, striding over its higher-ranked class mates: a class with a long list does not
+  // leave one thread walking it alone while the CTA waits, and the per-candidate set-up is shared by 4 candidates
+  // per warp instruction.
+  const bool thr_ok = 0.0f <= p.nms_iou;  // column max of a triu'd matrix is >= 0 (:80-86)
+  const int sub = tid & 7;
+  const unsigned gmask = 0xffu << (tid & 24);  // the 8 lanes of this group
+  for (int j0 = 0; j0 < n; j0 += kNmsThreads / 8) {
+    const int j = j0 + (tid >> 3);
+    bool bad = true;
+    uint64_t kj = 0;
+    if (j < n) {
+      kj = keys[j];
+      const int start = s_cls_start[cand_class(kj)];
+      if (thr_ok && (j - start) < p.top_k) {
+        bad = false;
+        const float4 bj = cbox[j];
+        const float aj = box_area(bj);
+        for (int i = start + sub; i < j; i += 8) {
+          const float4 bi = cbox[i];
+          // utils_bbox.py:38-47, with the division skipped when the boxes are disjoint: 0 / union is +-0 for
+          // every finite non-zero union, and thr_ok already established 0 <= nms_iou
+          const float dx = fmaxf(fminf(bi.z, bj.z) - fmaxf(bi.x, bj.x), 0.0f);
+          const float dy = fmaxf(fminf(bi.w, bj.w) - fmaxf(bi.y, bj.y), 0.0f);
+          const float inter = dx * dy;
+          const float uni = (box_area(bi) + aj) - inter;
+          if (inter == 0.0f && uni != 0.0f && fabsf(uni) <= 3.402823466e38f) continue;
+          if (!(inter / uni <= p.nms_iou)) { bad = true; break; }
+        }
+      }
+    }
+    const unsigned any_bad = __ballot_sync(0xffffffffu, bad) & gmask;
+    const bool emit = !any_bad && sub == 0;
+    const int slot = warp_alloc_slot(emit, &s_kept);
+    if (emit) dkeys[slot] = det_key_from_cand(kj);
+  }
+  __syncthreads();
   // ---- 4. global order: score desc, class asc, row asc; keep max_det --------------------
-  const int kept = s_kept;
+  // Only the best max_det kept candidates are wanted (:94-95): histogram a coarse descending bin of the score
+  // (score_bin_desc), find the bin where the running count reaches max_det, and sort just the candidates up to that bin (a
+  // superset of the answer, typically ~1.2 x max_det instead of every kept candidate).
+  int kept = s_kept;
+  if (kept > 2 * p.max_det && kept > 128 && kept <= kSmemCand) {
+    int* s_hist = s_cls_start;  // 2048 bins (the class table is no longer needed); kClassBits >= 11
+    for (int i = tid; i < 2048; i += kNmsThreads) s_hist[i] = 0;
+    if (tid == 0) s_kept = 0;
+    __syncthreads();
+    for (int i = tid; i < kept; i += kNmsThreads) atomicAdd(&s_hist[score_bin_desc(dkeys[i])], 1);
+    __syncthreads();
+    const int h0 = s_hist[2 * tid], h1 = s_hist[2 * tid + 1];
+    int total;
+    const int excl = cta_exclusive_scan(h0 + h1, s_scan, &total);
+    // bins strictly before `cut` hold < max_det candidates in total; every bin <= cut is taken
+    if (excl < p.max_det && excl + h0 + h1 >= p.max_det) s_cut = (excl + h0 >= p.max_det) ? 2 * tid : 2 * tid + 1;
+    __syncthreads();
+    const int cut = s_cut;
+    // compact in place: a candidate moves to a slot <= its own only after every thread has read its key
+    uint64_t mine[(kSmemCand + kNmsThreads - 1) / kNmsThreads];
+#pragma unroll
+    for (int q = 0; q < (kSmemCand + kNmsThreads - 1) / kNmsThreads; ++q)
+      if (q * kNmsThreads + tid < kept) mine[q] = dkeys[q * kNmsThreads + tid];
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < (kSmemCand + kNmsThreads - 1) / kNmsThreads; ++q)
+    {
+      const bool take = q * kNmsThreads + tid < kept && score_bin_desc(mine[q]) <= cut;
+      const int slot = warp_alloc_slot(take, &s_kept);
+      if (take) dkeys[slot] = mine[q];
+    }
+    __syncthreads();
+    kept = s_kept;
+  }
   const int kp2 = max(64, next_pow2(kept));
   for (int i = kept + tid; i < kp2; i += kNmsThreads) dkeys[i] = kPadKey;
   bitonic_sort_u64(dkeys, kp2);
