@@ -58,7 +58,8 @@ constexpr int kSmapMaxBatch = 1024;
 
 __global__ void __launch_bounds__(kSmapThreads)
 sigmoid_map_kernel(MaskParams p, const DetRec* __restrict__ rec, const int32_t* __restrict__ totals,
-                   float* __restrict__ smap, int64_t s_cap) {
+                   float* __restrict__ smap, int64_t s_cap, int* __restrict__ compose_counter) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) *compose_counter = 0;  // work counter of the compose kernel that follows
   extern __shared__ __align__(16) unsigned char s_dyn[];  // DetRec s_rec[list_cap]
   __shared__ int s_cstart[kSmapMaxBatch + 1];             // first ticket of every image
   __shared__ int s_scan[32];
@@ -384,9 +385,8 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   float* smap = h->smap + (size_t)h->ws_b0 * g.s_cap;
   if (p.batch > kSmapMaxBatch) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports at most %d images per call", kSmapMaxBatch);
   int* counters = h->work_counter + h->ws_lane;
-  ISB_CUDA(h, cudaMemsetAsync(counters, 0, sizeof(int), s));
   sigmoid_map_kernel<<<h->num_sms * kSmapCtasPerSm, kSmapThreads, (size_t)g.list_cap * sizeof(DetRec), s>>>(
-      p, rec, h->smap_total + h->ws_b0, smap, g.s_cap);
+      p, rec, h->smap_total + h->ws_b0, smap, g.s_cap, counters);
   ISB_LAUNCH_CHECK(h, "sigmoid_map_kernel");
   if (h->prof_mid) ISB_CUDA(h, cudaEventRecord(h->prof_mid, s));
   const int per_sm = budget == (size_t)kCompSmemTwo ? 2 : 1;

@@ -1,0 +1,227 @@
+// Read-side microbenchmark for the YOLACT score filter (K1): how close to the read-only HBM rate does a
+// "stream 400 MB of scores once, compare, emit rare hits" pass get under different access patterns?
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/k1_read tools/k1_read.cu && /tmp/k1_read
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("%s: %s\n", #x, cudaGetErrorString(e)); return 1; } } while (0)
+
+constexpr int kRows = 19248, kCols = 81, kBatch = 64;
+constexpr uint32_t kPerImg = kRows * kCols;  // multiple of 4
+
+__global__ void fill(float* x, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint32_t c = (uint32_t)(i % kCols);
+    const uint32_t hsh = (uint32_t)(i * 2654435761u) >> 8;
+    x[i] = c == 0 ? 0.95f : ((hsh % 1500u) == 0 ? 0.2f : 0.0005f);
+  }
+}
+
+// A: plain grid-stride read
+__global__ void read_plain(const float4* __restrict__ in, int64_t nvec, uint32_t* sink) {
+  uint32_t acc = 0;
+  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
+    const float4 a = __ldcs(in + v);
+    acc ^= __float_as_uint(a.x) ^ __float_as_uint(a.y) ^ __float_as_uint(a.z) ^ __float_as_uint(a.w);
+  }
+  if (acc == 0x12345678u) *sink = acc;
+}
+
+// A4: grid-stride, 4 loads in flight
+__global__ void read_plain4(const float4* __restrict__ in, int64_t nvec, uint32_t* sink) {
+  uint32_t acc = 0;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; v + 3 * stride < nvec; v += 4 * stride) {
+    float4 a[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) a[u] = __ldcs(in + v + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) acc ^= __float_as_uint(a[u].x) ^ __float_as_uint(a[u].y) ^ __float_as_uint(a[u].z) ^ __float_as_uint(a[u].w);
+  }
+  for (; v < nvec; v += stride) {
+    const float4 a = __ldcs(in + v);
+    acc ^= __float_as_uint(a.x) ^ __float_as_uint(a.y) ^ __float_as_uint(a.z) ^ __float_as_uint(a.w);
+  }
+  if (acc == 0x12345678u) *sink = acc;
+}
+
+__device__ __forceinline__ void emit(uint32_t e, float s, int* count, uint64_t* keys, int cap, uint32_t per_img) {
+  const uint32_t b = e / per_img;
+  const uint32_t le = e - b * per_img;
+  const uint32_t row = le / kCols, c = le - row * kCols;
+  if (c == 0) return;
+  const int pos = atomicAdd(&count[b], 1);
+  if (pos < cap) keys[(size_t)b * cap + pos] = ((uint64_t)c << 52) | ((uint64_t)__float_as_uint(s) << 20) | row;
+}
+
+// MODE 0: per-image grid (P, B), K1's pattern.  MODE 1: flat grid-stride over the whole batch.
+template <int MODE, int UNROLL, bool BLANK>
+__global__ void __launch_bounds__(256) filter(const float* __restrict__ scores, float thr, int* count, uint64_t* keys, int cap) {
+  const uint32_t nvec_img = kPerImg / 4;
+  uint32_t nvec, stride, v, ebase;
+  const float4* body;
+  if (MODE == 0) {
+    body = reinterpret_cast<const float4*>(scores + (size_t)blockIdx.y * kPerImg);
+    nvec = nvec_img;
+    stride = gridDim.x * 256;
+    v = blockIdx.x * 256 + threadIdx.x;
+    ebase = blockIdx.y * kPerImg;
+  } else {
+    body = reinterpret_cast<const float4*>(scores);
+    nvec = nvec_img * kBatch;
+    stride = gridDim.x * 256;
+    v = blockIdx.x * 256 + threadIdx.x;
+    ebase = 0;
+  }
+  const uint32_t step = (4u * stride) % kCols;
+  uint32_t r = (4u * v) % kCols;
+  auto scan = [&](float4 x, uint32_t e, uint32_t rr) {
+    if (BLANK) {
+      const uint32_t k = rr == 0 ? 0u : kCols - rr;
+      if (k == 0) x.x = -1.f;
+      if (k == 1) x.y = -1.f;
+      if (k == 2) x.z = -1.f;
+      if (k == 3) x.w = -1.f;
+    }
+    if (x.x > thr || x.y > thr || x.z > thr || x.w > thr) {
+      if (x.x > thr) emit(e, x.x, count, keys, cap, kPerImg);
+      if (x.y > thr) emit(e + 1, x.y, count, keys, cap, kPerImg);
+      if (x.z > thr) emit(e + 2, x.z, count, keys, cap, kPerImg);
+      if (x.w > thr) emit(e + 3, x.w, count, keys, cap, kPerImg);
+    }
+  };
+  for (; v + (UNROLL - 1) * stride < nvec; v += UNROLL * stride) {
+    float4 x[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) x[u] = __ldcs(body + v + u * stride);
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      scan(x[u], ebase + 4 * (v + u * stride), r);
+      r += step;
+      if (r >= kCols) r -= kCols;
+    }
+  }
+  for (; v < nvec; v += stride) {
+    scan(__ldcs(body + v), ebase + 4 * v, r);
+    r += step;
+    if (r >= kCols) r -= kCols;
+  }
+}
+
+// MODE 2: contiguous chunk per CTA (each CTA walks its own contiguous range, 4 KB per iteration)
+template <int UNROLL>
+__global__ void __launch_bounds__(256) filter_chunk(const float* __restrict__ scores, float thr, int* count, uint64_t* keys, int cap) {
+  const uint32_t nvec = kPerImg / 4 * kBatch;
+  const uint32_t per_cta = (nvec + gridDim.x - 1) / gridDim.x;
+  const uint32_t v0 = blockIdx.x * per_cta, v1 = min(nvec, v0 + per_cta);
+  const float4* body = reinterpret_cast<const float4*>(scores);
+  uint32_t v = v0 + threadIdx.x;
+  const uint32_t stride = 256;
+  const uint32_t step = (4u * stride) % kCols;
+  uint32_t r = (4u * v) % kCols;
+  auto scan = [&](float4 x, uint32_t e, uint32_t rr) {
+    const uint32_t k = rr == 0 ? 0u : kCols - rr;
+    if (k == 0) x.x = -1.f;
+    if (k == 1) x.y = -1.f;
+    if (k == 2) x.z = -1.f;
+    if (k == 3) x.w = -1.f;
+    if (x.x > thr || x.y > thr || x.z > thr || x.w > thr) {
+      if (x.x > thr) emit(e, x.x, count, keys, cap, kPerImg);
+      if (x.y > thr) emit(e + 1, x.y, count, keys, cap, kPerImg);
+      if (x.z > thr) emit(e + 2, x.z, count, keys, cap, kPerImg);
+      if (x.w > thr) emit(e + 3, x.w, count, keys, cap, kPerImg);
+    }
+  };
+  for (; v + (UNROLL - 1) * stride < v1; v += UNROLL * stride) {
+    float4 x[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) x[u] = __ldcs(body + v + u * stride);
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      scan(x[u], 4 * (v + u * stride), r);
+      r += step;
+      if (r >= kCols) r -= kCols;
+    }
+  }
+  for (; v < v1; v += stride) {
+    scan(__ldcs(body + v), 4 * v, r);
+    r += step;
+    if (r >= kCols) r -= kCols;
+  }
+}
+
+template <typename F>
+static float best_ms(F f) {
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  for (int i = 0; i < 3; ++i) f();
+  float best = 1e9f;
+  for (int i = 0; i < 10; ++i) {
+    cudaEventRecord(e0);
+    f();
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms;
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (ms < best) best = ms;
+  }
+  return best;
+}
+
+int main() {
+  const int64_t n = (int64_t)kPerImg * kBatch;
+  const int64_t nbytes = n * 4;
+  float* x;
+  int* count;
+  uint64_t* keys;
+  uint32_t* sink;
+  const int cap = 16384;
+  CK(cudaMalloc(&x, nbytes));
+  CK(cudaMalloc(&count, kBatch * 4));
+  CK(cudaMalloc(&keys, (size_t)kBatch * cap * 8));
+  CK(cudaMalloc(&sink, 4));
+  fill<<<148 * 8, 256>>>(x, n);
+  CK(cudaDeviceSynchronize());
+  printf("{\n \"bytes\": %lld,\n", (long long)nbytes);
+  float ms;
+#define REPORT(name) printf(" \"%s\": {\"us\": %.1f, \"GBps\": %.1f},\n", name, ms * 1e3, nbytes / ms / 1e6)
+  for (int ps : {4, 8}) {
+    char nm[64];
+    ms = best_ms([&] { read_plain<<<148 * ps, 256>>>((const float4*)x, n / 4, sink); });
+    snprintf(nm, 64, "read_plain_x%d", ps); REPORT(nm);
+    ms = best_ms([&] { read_plain4<<<148 * ps, 256>>>((const float4*)x, n / 4, sink); });
+    snprintf(nm, 64, "read_plain4_x%d", ps); REPORT(nm);
+  }
+  for (int P : {18, 37}) {
+    char nm[64];
+    ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter<0, 4, true><<<dim3(P, kBatch), 256>>>(x, 0.05f, count, keys, cap); });
+    snprintf(nm, 64, "k1_perimg_P%d_u4_blank", P); REPORT(nm);
+    ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter<0, 4, false><<<dim3(P, kBatch), 256>>>(x, 0.05f, count, keys, cap); });
+    snprintf(nm, 64, "k1_perimg_P%d_u4_noblank", P); REPORT(nm);
+    ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter<0, 8, true><<<dim3(P, kBatch), 256>>>(x, 0.05f, count, keys, cap); });
+    snprintf(nm, 64, "k1_perimg_P%d_u8_blank", P); REPORT(nm);
+  }
+  for (int ps : {4, 8, 16}) {
+    char nm[64];
+    ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter<1, 4, true><<<148 * ps, 256>>>(x, 0.05f, count, keys, cap); });
+    snprintf(nm, 64, "k1_flat_x%d_u4", ps); REPORT(nm);
+    ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter<1, 2, true><<<148 * ps, 256>>>(x, 0.05f, count, keys, cap); });
+    snprintf(nm, 64, "k1_flat_x%d_u2", ps); REPORT(nm);
+    ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter<1, 8, true><<<148 * ps, 256>>>(x, 0.05f, count, keys, cap); });
+    snprintf(nm, 64, "k1_flat_x%d_u8", ps); REPORT(nm);
+    ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter_chunk<4><<<148 * ps, 256>>>(x, 0.05f, count, keys, cap); });
+    snprintf(nm, 64, "k1_chunk_x%d_u4", ps); REPORT(nm);
+  }
+  // thr = 2: nothing passes (pure stream + compare)
+  ms = best_ms([&] { filter<1, 4, true><<<148 * 8, 256>>>(x, 2.0f, count, keys, cap); });
+  REPORT("k1_flat_x8_u4_nohits");
+  int hc[kBatch];
+  CK(cudaMemcpy(hc, count, sizeof(hc), cudaMemcpyDeviceToHost));
+  printf(" \"hits_img0\": %d\n}\n", hc[0]);
+  CK(cudaDeviceSynchronize());
+  return 0;
+}
