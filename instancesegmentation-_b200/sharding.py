@@ -49,3 +49,53 @@ def gather_counts(local_counts, group=None, pad_to=None):
     counts = counts.to(torch.int64)
     valid = counts.clamp(min=0)
     return counts, torch.cumsum(valid, 0) - valid
+
+
+class CountExchange:
+    """The same collective for the steady state of a sharded job with equal shards, taken off the critical path.
+
+    `post(local_counts)` snapshots this step's counts (one tiny device copy on the caller's stream) and starts the
+    all-gather asynchronously: NCCL runs it on its own stream behind that copy, so it overlaps the next step's
+    score-filter kernel instead of adding its latency to every step, and nothing synchronises with the host.
+    `result()` makes the caller's stream wait for the most recent gather and returns (counts, offsets) like
+    `gather_counts`.  `depth` snapshots are kept in flight; posting the (depth+1)-th waits for the oldest.
+    """
+
+    def __init__(self, n_local, device, group=None, depth=2):
+        self.group = group
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.n_local = int(n_local)
+        self.stage = [torch.zeros((self.n_local,), dtype=torch.int32, device=device) for _ in range(depth)]
+        self.gathered = [torch.zeros((self.world * self.n_local,), dtype=torch.int32, device=device) for _ in range(depth)]
+        self.work = [None] * depth
+        self.posted = 0
+
+    def post(self, local_counts):
+        slot = self.posted % len(self.stage)
+        if self.work[slot] is not None:
+            self.work[slot].wait()  # stream-level wait on NCCL (host-blocking only on gloo)
+            self.work[slot] = None
+        self.stage[slot].copy_(local_counts)
+        if self.world > 1:
+            self.work[slot] = dist.all_gather_into_tensor(self.gathered[slot], self.stage[slot], group=self.group, async_op=True)
+        else:
+            self.gathered[slot].copy_(self.stage[slot])
+        self.posted += 1
+        return slot
+
+    def flush(self):
+        for i, w in enumerate(self.work):
+            if w is not None:
+                w.wait()
+                self.work[i] = None
+
+    def result(self):
+        if self.posted == 0:
+            raise RuntimeError("CountExchange.result() before any post()")
+        slot = (self.posted - 1) % len(self.stage)
+        if self.work[slot] is not None:
+            self.work[slot].wait()
+            self.work[slot] = None
+        counts = self.gathered[slot].to(torch.int64)
+        valid = counts.clamp(min=0)
+        return counts, torch.cumsum(valid, 0) - valid

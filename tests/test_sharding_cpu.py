@@ -66,3 +66,52 @@ def test_single_process_fallback():
     from isb.sharding import gather_counts
     c, o = gather_counts(torch.tensor([3, 0, 5], dtype=torch.int32))
     assert c.tolist() == [3, 0, 5] and o.tolist() == [0, 3, 3]
+
+
+def _xchg_worker(rank, world, port, n_local, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from isb.sharding import CountExchange
+    x = CountExchange(n_local, torch.device("cpu"), depth=2)
+    got = []
+    for step in range(5):   # more posts than slots: the oldest in-flight gather is waited for and its slot reused
+        local = (torch.arange(n_local, dtype=torch.int32) + 10 * rank + 100 * step)
+        if step == 4 and rank == 1:
+            local[0] = -1
+        x.post(local)
+        if step in (1, 4):
+            c, o = x.result()
+            got.append((c.tolist(), o.tolist()))
+    x.flush()
+    q.put((rank, got))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_count_exchange_world2():
+    world, port, n_local = 2, _free_port(), 4
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_xchg_worker, args=(r, world, port, n_local, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for step_i, step in enumerate((1, 4)):
+        expect = torch.cat([torch.arange(n_local, dtype=torch.int64) + 10 * r + 100 * step for r in range(world)])
+        if step == 4:
+            expect[n_local] = -1
+        valid = expect.clamp(min=0)
+        off = (torch.cumsum(valid, 0) - valid).tolist()
+        for rank, got in res:
+            assert got[step_i] == (expect.tolist(), off)
+
+
+def test_count_exchange_single_process():
+    from isb.sharding import CountExchange
+    x = CountExchange(3, torch.device("cpu"))
+    x.post(torch.tensor([3, 0, 5], dtype=torch.int32))
+    c, o = x.result()
+    assert c.tolist() == [3, 0, 5] and o.tolist() == [0, 3, 3]
