@@ -114,6 +114,30 @@ ISB_API int isb_yolact_detect(isb_handle* h, const isb_yolact_in* in, const isb_
 ISB_API int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out, isb_stream stream);
 
 /* ------------------------------------------------------------------------------------
+ * Detect + per-pixel CLASS MAP, for callers that draw / score a class image and never look at
+ * the per-instance masks.  Replaces decode_nms (utils_bbox.py:170-243) TOGETHER WITH the
+ * wrapper tail inst_model/yolact/yolact.py:162-170:
+ *     masks_class = masks_sigmoid * (class_ids[None, None, :] + 1)
+ *     masks_class = masks_class.reshape(-1, m)[arange(H*W), masks_arg.reshape(-1)].reshape(H, W)
+ * i.e. class_map[y, x] = class_ids[masks_arg[y, x]] + 1 where that detection's mask is set at
+ * (y, x), else 0.  bool [H,W,m] and int64 [H,W] are never written (the wrapper copies 30 MB
+ * of them to the host per image, yolact.py:162); the map is uint8 [H,W].
+ * Images without detections (counts[b] <= 0) get an all-zero map.  num_classes <= 255.
+ * ---------------------------------------------------------------------------------- */
+typedef struct {
+  float* boxes;          /* [B,max_det,4]                                               */
+  float* scores;         /* [B,max_det]                                                 */
+  int64_t* class_ids;    /* [B,max_det]                                                 */
+  uint8_t* class_map;    /* [B,H,W]                                                     */
+  int32_t* counts;       /* [B], as in isb_yolact_out                                   */
+} isb_yolact_map_out;
+
+ISB_API int isb_yolact_class_map(isb_handle* h, const isb_yolact_in* in, const isb_yolact_map_out* out, isb_stream stream);
+
+/* Host-buffer version (same pipeline as isb_yolact_detect_host; D2H is 0.3 MB instead of 32 MB per image). */
+ISB_API int isb_yolact_class_map_host(isb_handle* h, const isb_yolact_in* in, const isb_yolact_map_out* out, isb_stream stream);
+
+/* ------------------------------------------------------------------------------------
  * Stage entry points (known-answer tests call these one by one; BBoxUtility's public
  * helper methods map onto them).
  * ---------------------------------------------------------------------------------- */

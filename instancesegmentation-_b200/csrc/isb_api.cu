@@ -161,12 +161,51 @@ extern "C" int isb_create(int device, const isb_limits* limits, isb_handle** out
 }
 
 // ----------------------------------------------------------------------------------- YOLACT
-static int check_yolact(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out) {
+// Both public output structs (full masks / class map only) funnel into this one.
+struct YolactOutAll {
+  float* boxes;
+  float* scores;
+  int64_t* class_ids;
+  int64_t* masks_arg;
+  uint8_t* masks;
+  int64_t mask_slot_bytes;
+  int32_t* counts;
+  uint8_t* class_map;
+  int map_only;
+};
+
+static YolactOutAll widen(const isb_yolact_out* o) {
+  YolactOutAll a;
+  memset(&a, 0, sizeof(a));
+  if (o) {
+    a.boxes = o->boxes; a.scores = o->scores; a.class_ids = o->class_ids; a.masks_arg = o->masks_arg;
+    a.masks = o->masks; a.mask_slot_bytes = o->mask_slot_bytes; a.counts = o->counts;
+  }
+  return a;
+}
+
+static YolactOutAll widen(const isb_yolact_map_out* o) {
+  YolactOutAll a;
+  memset(&a, 0, sizeof(a));
+  if (o) {
+    a.boxes = o->boxes; a.scores = o->scores; a.class_ids = o->class_ids; a.counts = o->counts;
+    a.class_map = o->class_map;
+  }
+  a.map_only = 1;
+  return a;
+}
+
+static int check_yolact(isb_handle* h, const isb_yolact_in* in, const YolactOutAll* out, bool have_out) {
   if (!h) return ISB_ERR_BAD_ARG;
-  if (!in || !out) ISB_FAIL(h, ISB_ERR_BAD_ARG, "null in/out struct");
+  if (!in || !have_out) ISB_FAIL(h, ISB_ERR_BAD_ARG, "null in/out struct");
   if (!in->box || !in->conf || !in->coef || !in->proto || !in->anchors) ISB_FAIL(h, ISB_ERR_BAD_ARG, "null input tensor");
-  if (!out->boxes || !out->scores || !out->class_ids || !out->masks_arg || !out->masks || !out->counts)
+  if (!out->boxes || !out->scores || !out->class_ids || !out->counts) ISB_FAIL(h, ISB_ERR_BAD_ARG, "null output tensor");
+  if (out->map_only) {
+    if (!out->class_map) ISB_FAIL(h, ISB_ERR_BAD_ARG, "null class_map");
+    if (in->num_classes > 255) ISB_FAIL(h, ISB_ERR_LIMIT, "class map is uint8: at most 254 foreground classes, got %d", in->num_classes - 1);
+  } else if (!out->masks_arg || !out->masks) {
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "null output tensor");
+  }
   if (in->batch <= 0 || in->num_anchors <= 0 || in->num_classes < 2 || in->proto_h <= 0 || in->proto_w <= 0 ||
       in->out_h <= 0 || in->out_w <= 0 || in->top_k <= 0 || in->max_det <= 0)
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "non-positive dimension");
@@ -176,14 +215,14 @@ static int check_yolact(isb_handle* h, const isb_yolact_in* in, const isb_yolact
   if (in->num_classes - 1 > h->lim.max_classes) ISB_FAIL(h, ISB_ERR_LIMIT, "classes %d > max_classes %d", in->num_classes - 1, h->lim.max_classes);
   if (in->max_det > h->lim.max_det) ISB_FAIL(h, ISB_ERR_LIMIT, "max_det %d > limit %d", in->max_det, h->lim.max_det);
   if (in->top_k > h->lim.max_top_k) ISB_FAIL(h, ISB_ERR_LIMIT, "top_k %d > limit %d", in->top_k, h->lim.max_top_k);
-  if (out->mask_slot_bytes < (int64_t)in->out_h * in->out_w * in->max_det || (out->mask_slot_bytes & 15))
+  if (!out->map_only && (out->mask_slot_bytes < (int64_t)in->out_h * in->out_w * in->max_det || (out->mask_slot_bytes & 15)))
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_slot_bytes must be >= H*W*max_det and a multiple of 16");
   return ISB_OK;
 }
 
-static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out, cudaStream_t s) {
+static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const YolactOutAll* out, cudaStream_t s) {
   if (!aligned16(in->box) || !aligned16(in->coef) || !aligned16(in->proto) || !aligned16(in->anchors) ||
-      !aligned4(in->conf) || !aligned16(out->boxes) || !aligned16(out->masks))
+      !aligned4(in->conf) || !aligned16(out->boxes) || (!out->map_only && !aligned16(out->masks)))
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "box/coef/proto/anchors/boxes/masks must be 16-byte aligned, conf 4-byte aligned");
   int rc;
   cudaEvent_t* ev = (h->prof_events && h->prof_used < h->prof_cap) ? h->prof_events + (size_t)h->prof_used * 5 : nullptr;
@@ -238,6 +277,9 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const is
   mp.masks_arg = out->masks_arg;
   mp.masks = out->masks;
   mp.mask_slot_bytes = out->mask_slot_bytes;
+  mp.class_map = out->class_map;
+  mp.class_ids = out->class_ids;
+  mp.map_only = out->map_only;
   h->prof_mid = ev ? ev[3] : nullptr;  // recorded between the sigmoid-map and the compose kernel
   rc = launch_masks(h, mp, s);
   h->prof_mid = nullptr;
@@ -250,28 +292,54 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const is
 }
 
 extern "C" int isb_yolact_detect(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out, isb_stream stream) {
-  int rc = check_yolact(h, in, out);
+  const YolactOutAll all = widen(out);
+  int rc = check_yolact(h, in, &all, out != nullptr);
   if (rc != ISB_OK) return rc;
   ISB_CUDA(h, cudaSetDevice(h->device));
-  return yolact_detect_device(h, in, out, (cudaStream_t)stream);
+  return yolact_detect_device(h, in, &all, (cudaStream_t)stream);
+}
+
+extern "C" int isb_yolact_class_map(isb_handle* h, const isb_yolact_in* in, const isb_yolact_map_out* out, isb_stream stream) {
+  const YolactOutAll all = widen(out);
+  int rc = check_yolact(h, in, &all, out != nullptr);
+  if (rc != ISB_OK) return rc;
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  return yolact_detect_device(h, in, &all, (cudaStream_t)stream);
 }
 
 static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
+static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAll* out, isb_stream stream);
+
 extern "C" int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out,
                                       isb_stream stream) {
-  int rc = check_yolact(h, in, out);
+  const YolactOutAll all = widen(out);
+  int rc = check_yolact(h, in, &all, out != nullptr);
   if (rc != ISB_OK) return rc;
+  return yolact_host(h, in, &all, stream);
+}
+
+extern "C" int isb_yolact_class_map_host(isb_handle* h, const isb_yolact_in* in, const isb_yolact_map_out* out,
+                                         isb_stream stream) {
+  const YolactOutAll all = widen(out);
+  int rc = check_yolact(h, in, &all, out != nullptr);
+  if (rc != ISB_OK) return rc;
+  return yolact_host(h, in, &all, stream);
+}
+
+static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAll* out, isb_stream stream) {
+  int rc;
+  const bool map_only = out->map_only != 0;
   ISB_CUDA(h, cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
   const size_t B = in->batch, A = in->num_anchors, C = in->num_classes, K = ISB_NUM_COEF;
   const size_t HW = (size_t)in->out_h * in->out_w, D = in->max_det;
   const size_t n_box = B * A * 4 * 4, n_conf = B * A * C * 4, n_coef = B * A * K * 4,
                n_proto = B * (size_t)in->proto_h * in->proto_w * K * 4, n_anc = A * 4 * 4;
-  const size_t o_box = B * D * 16, o_score = B * D * 4, o_cls = B * D * 8, o_arg = B * HW * 8,
-               o_mask = B * (size_t)out->mask_slot_bytes, o_cnt = B * 4;
+  const size_t o_box = B * D * 16, o_score = B * D * 4, o_cls = B * D * 8, o_arg = map_only ? 0 : B * HW * 8,
+               o_mask = map_only ? 0 : B * (size_t)out->mask_slot_bytes, o_cnt = B * 4, o_map = map_only ? B * HW : 0;
   const size_t need = up256(n_box) + up256(n_conf) + up256(n_coef) + up256(n_proto) + up256(n_anc) + up256(o_box) +
-                      up256(o_score) + up256(o_cls) + up256(o_arg) + up256(o_mask) + up256(o_cnt);
+                      up256(o_score) + up256(o_cls) + up256(o_arg) + up256(o_mask) + up256(o_cnt) + up256(o_map);
   if (need > h->stage_bytes) {
     ISB_CUDA(h, cudaStreamSynchronize(s));
     cudaFree(h->stage);
@@ -283,7 +351,7 @@ extern "C" int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, co
   char* p = static_cast<char*>(h->stage);
   auto take = [&](size_t bytes) { char* r = p; p += up256(bytes); return r; };
   isb_yolact_in din = *in;
-  isb_yolact_out dout = *out;
+  YolactOutAll dout = *out;
   din.box = (const float*)take(n_box);
   din.conf = (const float*)take(n_conf);
   din.coef = (const float*)take(n_coef);
@@ -295,6 +363,7 @@ extern "C" int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, co
   dout.masks_arg = (int64_t*)take(o_arg);
   dout.masks = (uint8_t*)take(o_mask);
   dout.counts = (int32_t*)take(o_cnt);
+  dout.class_map = map_only ? (uint8_t*)take(o_map) : nullptr;
   // Sub-batch pipeline over kLanes streams: while chunk c computes and streams its masks to the host, chunk
   // c+1 is already uploading (PCIe is full duplex) -- H2D, kernels and D2H of different chunks overlap.
   constexpr int kLanes = 3;
@@ -317,7 +386,7 @@ extern "C" int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, co
     for (size_t b = b0; b < b1; ++b) {
       const int m = out->counts[b];
       if (m < 0) { overflow = true; continue; }
-      if (m == 0) continue;
+      if (m == 0 || map_only) continue;
       ISB_CUDA(h, cudaMemcpyAsync(out->masks + b * slot, dout.masks + b * slot, HW * (size_t)m, cudaMemcpyDeviceToHost,
                                   h->lane_stream[lane]));
     }
@@ -333,7 +402,7 @@ extern "C" int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, co
     ISB_CUDA(h, cudaMemcpyAsync((char*)din.coef + b0 * A * K * 4, (const char*)in->coef + b0 * A * K * 4, nb * A * K * 4, cudaMemcpyHostToDevice, st));
     ISB_CUDA(h, cudaMemcpyAsync((char*)din.proto + b0 * PP * 4, (const char*)in->proto + b0 * PP * 4, nb * PP * 4, cudaMemcpyHostToDevice, st));
     isb_yolact_in cin = din;
-    isb_yolact_out cout = dout;
+    YolactOutAll cout = dout;
     cin.batch = (int32_t)nb;
     cin.box = din.box + b0 * A * 4;
     cin.conf = din.conf + b0 * A * C;
@@ -342,9 +411,10 @@ extern "C" int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, co
     cout.boxes = dout.boxes + b0 * D * 4;
     cout.scores = dout.scores + b0 * D;
     cout.class_ids = dout.class_ids + b0 * D;
-    cout.masks_arg = dout.masks_arg + b0 * HW;
-    cout.masks = dout.masks + b0 * slot;
+    cout.masks_arg = map_only ? nullptr : dout.masks_arg + b0 * HW;
+    cout.masks = map_only ? nullptr : dout.masks + b0 * slot;
     cout.counts = dout.counts + b0;
+    cout.class_map = map_only ? dout.class_map + b0 * HW : nullptr;
     h->ws_b0 = (int32_t)b0;
     h->ws_lane = lane;
     rc = yolact_detect_device(h, &cin, &cout, st);
@@ -356,7 +426,10 @@ extern "C" int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, co
     ISB_CUDA(h, cudaMemcpyAsync(out->boxes + b0 * D * 4, cout.boxes, nb * D * 16, cudaMemcpyDeviceToHost, st));
     ISB_CUDA(h, cudaMemcpyAsync(out->scores + b0 * D, cout.scores, nb * D * 4, cudaMemcpyDeviceToHost, st));
     ISB_CUDA(h, cudaMemcpyAsync(out->class_ids + b0 * D, cout.class_ids, nb * D * 8, cudaMemcpyDeviceToHost, st));
-    ISB_CUDA(h, cudaMemcpyAsync(out->masks_arg + b0 * HW, cout.masks_arg, nb * HW * 8, cudaMemcpyDeviceToHost, st));
+    if (map_only)
+      ISB_CUDA(h, cudaMemcpyAsync(out->class_map + b0 * HW, cout.class_map, nb * HW, cudaMemcpyDeviceToHost, st));
+    else
+      ISB_CUDA(h, cudaMemcpyAsync(out->masks_arg + b0 * HW, cout.masks_arg, nb * HW * 8, cudaMemcpyDeviceToHost, st));
     if (c >= kLanes - 1) rc = finalize(c - (kLanes - 1));
   }
   for (int c = nchunks - (kLanes - 1) > 0 ? nchunks - (kLanes - 1) : 0; c < nchunks && rc == ISB_OK; ++c) rc = finalize(c);

@@ -384,6 +384,10 @@ struct MaskParams {
   int64_t* masks_arg;        // [B, H, W]
   uint8_t* masks;            // B slots
   int64_t mask_slot_bytes;
+  // optional per-pixel class map (yolact.py:167-169): class_ids[arg] + 1 where the arg-max mask is set, else 0
+  uint8_t* class_map;        // [B, H, W] or nullptr
+  const int64_t* class_ids;  // [B, det_stride], needed with class_map
+  int32_t map_only;          // 1: masks / masks_arg are not produced at all
 };
 int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s);
 // grows the sigmoid-map scratch for the handle's limits; returns floats per image in *s_cap

@@ -146,6 +146,9 @@ __device__ __forceinline__ void warp_clear(uint8_t* buf, int a, int b, int lane)
   for (int v = a16 + lane * 16; v < b16; v += 32 * 16) *reinterpret_cast<uint4*>(buf + v) = make_uint4(0, 0, 0, 0);
 }
 
+// kMasks = false is the class-map-only variant (yolact.py:162-170 needs nothing else on the host): same walk,
+// no segment images, no bulk stores, one byte per pixel out.
+template <bool kMasks>
 __global__ void __launch_bounds__(kCompThreads, 2)
 mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, const float* __restrict__ smap,
                     int* __restrict__ work_counter) {
@@ -168,7 +171,8 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
   const int HW = H * W;
 
   // ---- once per CTA: clean segment buffers, per-column bilinear taps -----------------------------
-  for (int i = tid; i < nwarps * 2 * g.buf_bytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem_raw)[i] = make_uint4(0, 0, 0, 0);
+  if (kMasks)
+    for (int i = tid; i < nwarps * 2 * g.buf_bytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem_raw)[i] = make_uint4(0, 0, 0, 0);
   for (int x = tid; x < W; x += blockDim.x) {
     int ix0, ix1;
     float l0, l1;
@@ -190,12 +194,20 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
     const int b = unit / g.units_per_img;
     const int u = unit - b * g.units_per_img;
     const int m = p.counts ? p.counts[b] : p.m_fixed;
-    if (m <= 0) continue;  // nothing to write for this image (the reference returns None)
+    if (m <= 0) {  // nothing to write for this image (the reference returns None); its class map is background
+      if (p.class_map) {
+        const int px0 = u * kUnitPx, px1 = min(px0 + kUnitPx, HW);
+        for (int q = px0 + tid; q < px1; q += blockDim.x) p.class_map[(size_t)b * HW + q] = 0;
+      }
+      continue;
+    }
     const int px0 = u * kUnitPx;
     const int px1 = min(px0 + kUnitPx, HW);
     const int ya = px0 / W, yb = (px1 - 1) / W;  // rows the unit touches
-    uint8_t* out_img = p.masks + (size_t)b * p.mask_slot_bytes;
-    int64_t* arg_img = p.masks_arg + (size_t)b * HW;
+    uint8_t* out_img = kMasks ? p.masks + (size_t)b * p.mask_slot_bytes : nullptr;
+    int64_t* arg_img = kMasks ? p.masks_arg + (size_t)b * HW : nullptr;
+    uint8_t* cmap_img = p.class_map ? p.class_map + (size_t)b * HW : nullptr;
+    const int64_t* cls_img = p.class_ids + (size_t)b * p.det_stride;
     const float* S_img = smap + (size_t)b * g.s_cap;
 
     // ---- per-row bilinear taps of the unit's rows, detections that meet those rows (ascending index) ----
@@ -242,12 +254,12 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
       const int nt = min(32, px1 - q0);
       const int par = seg_no & 1;
       uint8_t* buf = wbuf + (par ? g.buf_bytes : 0);
-      uint8_t* g0 = out_img + (int64_t)q0 * m;
-      const int shift = (int)(reinterpret_cast<uintptr_t>(g0) & 15);
-      // the bulk store issued from this buffer two segments ago must have finished reading it
-      if (lane == 0) bulk_wait_read1();
-      __syncwarp();
-      {
+      uint8_t* g0 = kMasks ? out_img + (int64_t)q0 * m : nullptr;
+      const int shift = kMasks ? (int)(reinterpret_cast<uintptr_t>(g0) & 15) : 0;
+      if (kMasks) {
+        // the bulk store issued from this buffer two segments ago must have finished reading it
+        if (lane == 0) bulk_wait_read1();
+        __syncwarp();
         const int dlo = par ? dlo1 : dlo0, dhi = par ? dhi1 : dhi0;
         if (dhi > dlo) {
           warp_clear(buf, dlo, dhi, lane);
@@ -271,7 +283,7 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
       const ColTap tb = s_xtab[x];
       const int ix0 = tb.idx & 0xffff, ix1 = ix0 + (tb.idx >> 16);
       const float lx1 = tb.l1, lx0 = 1.0f - lx1;
-      uint8_t* mypix = buf + shift + lane * m;
+      uint8_t* mypix = kMasks ? buf + shift + lane * m : nullptr;
       float best = 0.0f;
       int arg = 0;
       bool anyset = false;
@@ -293,40 +305,43 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
             const float top = lx0 * __ldg(S + r0 + ix0) + lx1 * __ldg(S + r0 + ix1);
             const float bot = lx0 * __ldg(S + r1 + ix0) + lx1 * __ldg(S + r1 + ix1);
             const float v = ly0 * top + ly1 * bot;
-            if (v > 0.5f) { mypix[r.j] = 1; anyset = true; }
+            if (kMasks && v > 0.5f) { mypix[r.j] = 1; anyset = true; }
             if (v > best) { best = v; arg = r.j; }
           }
         }
       }
-      if (active) arg_img[q0 + lane] = (int64_t)arg;
-      {  // remember what this warp dirtied
-        const unsigned sb = __ballot_sync(0xffffffffu, anyset);
-        int dlo = 0, dhi = 0;
-        if (sb) {
-          dlo = shift + (__ffs(sb) - 1) * m;
-          dhi = shift + (32 - __clz(sb)) * m;
+      if (cmap_img && active) cmap_img[q0 + lane] = best > 0.5f ? (uint8_t)(__ldg(cls_img + arg) + 1) : (uint8_t)0;
+      if (kMasks) {
+        if (active) arg_img[q0 + lane] = (int64_t)arg;
+        {  // remember what this warp dirtied
+          const unsigned sb = __ballot_sync(0xffffffffu, anyset);
+          int dlo = 0, dhi = 0;
+          if (sb) {
+            dlo = shift + (__ffs(sb) - 1) * m;
+            dhi = shift + (32 - __clz(sb)) * m;
+          }
+          if (par) { dlo1 = dlo; dhi1 = dhi; } else { dlo0 = dlo; dhi0 = dhi; }
         }
-        if (par) { dlo1 = dlo; dhi1 = dhi; } else { dlo0 = dlo; dhi0 = dhi; }
+        fence_proxy_async();  // this lane's shared-memory writes -> visible to the bulk store
+        __syncwarp();
+        // ---- the segment leaves as one bulk store (16-byte aligned interior) + < 16-byte edges ---------
+        const int nbytes = nt * m;
+        const int head = min((16 - shift) & 15, nbytes);
+        const int body = (nbytes - head) & ~15;
+        const int tail = nbytes - head - body;
+        if (lane == 0) {
+          if (body > 0) bulk_s2g(g0 + head, buf + shift + head, (uint32_t)body);
+          bulk_commit();  // one (possibly empty) group per segment keeps the wait_group arithmetic exact
+        }
+        if (lane < head) g0[lane] = buf[shift + lane];
+        if (lane >= 16 && lane - 16 < tail) g0[head + body + (lane - 16)] = buf[shift + head + body + (lane - 16)];
       }
-      fence_proxy_async();  // this lane's shared-memory writes -> visible to the bulk store
-      __syncwarp();
-      // ---- the segment leaves as one bulk store (16-byte aligned interior) + < 16-byte edges ---------
-      const int nbytes = nt * m;
-      const int head = min((16 - shift) & 15, nbytes);
-      const int body = (nbytes - head) & ~15;
-      const int tail = nbytes - head - body;
-      if (lane == 0) {
-        if (body > 0) bulk_s2g(g0 + head, buf + shift + head, (uint32_t)body);
-        bulk_commit();  // one (possibly empty) group per segment keeps the wait_group arithmetic exact
-      }
-      if (lane < head) g0[lane] = buf[shift + lane];
-      if (lane >= 16 && lane - 16 < tail) g0[head + body + (lane - 16)] = buf[shift + head + body + (lane - 16)];
       // this lane's pixel in the warp's next segment
       xq += nwarps * 32;
       while (xq >= W) { xq -= W; ++yq; }
     }
   }
-  if (lane == 0) bulk_wait_read0();  // shared memory must outlive every bulk store that reads it
+  if (kMasks && lane == 0) bulk_wait_read0();  // shared memory must outlive every bulk store that reads it
 }
 
 // ---- host side ----------------------------------------------------------------------------
@@ -334,7 +349,8 @@ static constexpr int kCompSmemTwo = 111 * 1024;   // two CTAs per SM
 static constexpr int kCompSmemOne = 200 * 1024;   // one CTA per SM (very large detection counts)
 
 int configure_masks(isb_handle* h) {
-  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
+  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
+  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
   return ISB_OK;
 }
 
@@ -365,16 +381,25 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   g.scale_x = (float)p.proto_w / (float)p.out_w;
   g.list_cap = p.m_fixed >= 0 ? (p.m_fixed > 0 ? p.m_fixed : 1) : p.det_stride;
   const size_t fixed = (((size_t)p.out_w * sizeof(ColTap) + 31) & ~(size_t)31) + (size_t)g.list_cap * sizeof(DetRec);
-  const size_t buf = ((size_t)32 * g.list_cap + 16 + 15) & ~(size_t)15;  // 32 pixels x m bytes + alignment shift
+  if (p.class_map && !p.class_ids) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask assembly: class_map needs class_ids");
+  if (p.map_only && !p.class_map) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask assembly: map_only without class_map");
+  // 32 pixels x m bytes + alignment shift; the class-map-only variant has no segment images
+  const size_t buf = p.map_only ? 0 : ((size_t)32 * g.list_cap + 16 + 15) & ~(size_t)15;
   // as many warps (each with two segment buffers) as fit: two CTAs per SM if that gives >= 8 warps, else one
   size_t budget = kCompSmemTwo;
-  int nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
-  if (nwarps < 8) {
-    budget = kCompSmemOne;
+  int nwarps = kCompWarps;
+  if (!p.map_only) {
     nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
+    if (nwarps < 8) {
+      budget = kCompSmemOne;
+      nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
+    }
+  } else if (fixed > budget) {
+    budget = kCompSmemOne;
   }
   if (nwarps > kCompWarps) nwarps = kCompWarps;
-  if (nwarps < 1) ISB_FAIL(h, ISB_ERR_LIMIT, "mask compose: %d detections x width %d exceed shared memory", g.list_cap, p.out_w);
+  if (nwarps < 1 || fixed > budget)
+    ISB_FAIL(h, ISB_ERR_LIMIT, "mask compose: %d detections x width %d exceed shared memory", g.list_cap, p.out_w);
   g.buf_bytes = (int)buf;
   const size_t smem = fixed + (size_t)nwarps * 2 * buf;
   int rc = ensure_mask_scratch(h, p.proto_h, p.proto_w, &g.s_cap);
@@ -392,7 +417,10 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   const int per_sm = budget == (size_t)kCompSmemTwo ? 2 : 1;
   int64_t grid = (int64_t)h->num_sms * per_sm;
   if (grid > total_units) grid = total_units;
-  mask_compose_kernel<<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, counters);
+  if (p.map_only)
+    mask_compose_kernel<false><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, counters);
+  else
+    mask_compose_kernel<true><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, counters);
   ISB_LAUNCH_CHECK(h, "mask_compose_kernel");
   return ISB_OK;
 }

@@ -13,7 +13,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import ISB_NUM_COEF, YolactIn, YolactOut, get_handle
+from ._lib import YolactMapOut, ISB_NUM_COEF, YolactIn, YolactOut, get_handle
 
 TOP_K = 200            # utils_bbox.py:50 default, never overridden by decode_nms (:207)
 MAX_DETECTIONS = 100   # utils_bbox.py:50 default
@@ -235,6 +235,56 @@ class BBoxUtility(object):
         with torch.cuda.device(dev):
             h.check(h.lib.isb_yolact_detect(h.ptr, C.byref(pin), C.byref(pout), _stream(dev)))
         return out
+
+    # ------------------------------------------------------------------ yolact.py:162-170
+    def decode_nms_class_map_batch(self, outputs, anchors, confidence, nms_iou, image_shape, top_k=TOP_K,
+                                   max_detections=MAX_DETECTIONS, out=None):
+        """Detect + the wrapper's per-pixel class image (inst_model/yolact/yolact.py:162-170) for a batch, without ever
+        materialising bool [H,W,m] / int64 [H,W]: returns (boxes [B,D,4], scores [B,D], class_ids [B,D] i64,
+        class_map [B,H,W] u8, counts [B] i32) on the device, nothing synchronised.
+        class_map[b,y,x] = class_ids[b, masks_arg[y,x]] + 1 where that detection's mask is set, else 0."""
+        box, conf, coef, proto = [_cuda_f32(t, n) for t, n in zip(outputs, ("box", "conf", "coef", "proto"))]
+        dev = box.device
+        anchors = _cuda_f32(anchors, "anchors").to(dev)
+        if box.dim() != 3 or conf.dim() != 3 or coef.dim() != 3 or proto.dim() != 4:
+            raise ValueError("decode_nms_class_map_batch expects [B,A,4], [B,A,C], [B,A,K], [B,Ph,Pw,K]")
+        bsz, a, c = conf.shape
+        ph, pw, k = proto.shape[1:]
+        hgt, wid = int(image_shape[0]), int(image_shape[1])
+        max_det = int(max_detections)
+        if out is None:
+            out = (torch.empty((bsz, max_det, 4), dtype=torch.float32, device=dev),
+                   torch.empty((bsz, max_det), dtype=torch.float32, device=dev),
+                   torch.empty((bsz, max_det), dtype=torch.int64, device=dev),
+                   torch.empty((bsz, hgt, wid), dtype=torch.uint8, device=dev),
+                   torch.empty((bsz,), dtype=torch.int32, device=dev))
+        h = get_handle(dev.index, max_batch=bsz, max_anchors=a, max_classes=c - 1, max_det=max_det, max_top_k=int(top_k))
+        pin = YolactIn(bsz, a, c, k, ph, pw, hgt, wid, box.data_ptr(), conf.data_ptr(), coef.data_ptr(), proto.data_ptr(),
+                       anchors.data_ptr(), float(confidence), float(nms_iou), int(top_k), max_det)
+        pout = YolactMapOut(*[t.data_ptr() for t in out])
+        with torch.cuda.device(dev):
+            h.check(h.lib.isb_yolact_class_map(h.ptr, C.byref(pin), C.byref(pout), _stream(dev)))
+        return out
+
+    def decode_nms_class_map(self, outputs, anchors, confidence, nms_iou, image_shape):
+        """One image, reference-shaped: (box_thre [m,4], class_thre [m], class_ids [m], masks_class u8 [H,W]) -- the four
+        things `YOLACT.detect_image` (yolact.py:158-170) uses after decode_nms -- or four `None`s."""
+        box, conf, coef, proto = outputs[0], outputs[1], outputs[2], outputs[3]
+        box = box.reshape(-1, 4)[None]
+        conf = conf.reshape(box.shape[1], -1)[None]
+        coef = coef.reshape(box.shape[1], -1)[None]
+        proto = proto.reshape((1,) + tuple(proto.shape[-3:]))
+        a, c = conf.shape[1], conf.shape[2]
+        res = self.decode_nms_class_map_batch((box, conf, coef, proto), anchors, confidence, nms_iou, image_shape)
+        m = int(res[4][0].item())
+        while m < 0:  # candidate buffer overflow: grow the workspace and redo
+            cap = int(get_handle(box.device.index).limits.cand_capacity)
+            get_handle(box.device.index, cand_capacity=min(cap * 4, a * (c - 1)))
+            res = self.decode_nms_class_map_batch((box, conf, coef, proto), anchors, confidence, nms_iou, image_shape)
+            m = int(res[4][0].item())
+        if m == 0:
+            return (None,) * 4
+        return res[0][0, :m], res[1][0, :m], res[2][0, :m], res[3][0]
 
     # ------------------------------------------------------------------ utils_bbox.py:170
     def decode_nms(self, outputs, anchors, confidence, nms_iou, image_shape, traditional_nms=False, max_detections=100):

@@ -270,3 +270,16 @@ def decode_nms(outputs, anchors, confidence, nms_iou, image_shape, traditional_n
     box_px = yolact_correct_boxes(box_thre, image_shape)                     # :216
     masks_arg, masks = assemble_masks(pred_proto, coef_thre, box_px, image_shape)
     return box_px, score, class_ids, masks_arg, masks
+
+
+# --------------------------------------------------------------------------- next row
+def masks_class(masks_sigmoid, class_ids, masks_arg):
+    """inst_model/yolact/yolact.py:167-169 -- the wrapper's per-pixel class image built from decode_nms' outputs:
+    every pixel takes (class id + 1) of its arg-max detection if that detection's binary mask is set there, else 0.
+    The wrapper multiplies bool [H,W,m] by (class_ids + 1) and gathers along m with masks_arg; gathering first and
+    multiplying afterwards is the same thing."""
+    masks_sigmoid = np.asarray(masks_sigmoid)
+    class_ids = np.asarray(class_ids).astype(np.int64)
+    masks_arg = np.asarray(masks_arg).astype(np.int64)
+    picked = np.take_along_axis(masks_sigmoid, masks_arg[:, :, None], axis=2)[:, :, 0]
+    return np.where(picked, class_ids[masks_arg] + 1, 0).astype(np.int64)

@@ -45,6 +45,7 @@ def test_struct_layout_matches_header(lib):
     assert ctypes.sizeof(lib.Limits) == 32
     assert ctypes.sizeof(lib.YolactIn) == 8 * 4 + 5 * 8 + 4 * 4
     assert ctypes.sizeof(lib.YolactOut) == 7 * 8
+    assert ctypes.sizeof(lib.YolactMapOut) == 5 * 8
 
 
 def test_no_cpu_fallback(lib):

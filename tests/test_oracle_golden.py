@@ -92,3 +92,19 @@ def test_traditional_nms_known_answers():
     assert np.array_equal(r[1], g["scores"]) and np.array_equal(r[2], g["class_ids"])
     assert_close_f32(r[0], g["boxes"], 1e-5, "boxes")
     assert_masks_close(r[4], unpack_masks(g), 1e-3, "masks")
+
+
+def test_masks_class_against_the_wrapper_formula():
+    """yolact.py:167-169 evaluated literally (broadcast multiply, flatten, fancy-index) on reference-generated decode_nms
+    outputs vs the oracle's gather-first formulation."""
+    from conftest import unpack_masks
+    for name in ("yolact_tiny_a", "yolact_tiny_b", "yolact_tiny_one"):
+        g = load_golden(name)
+        masks, cls, arg = unpack_masks(g), g["class_ids"], g["masks_arg"]
+        h, w, m = masks.shape
+        full = masks * (cls[None, None, :] + 1)
+        flat = full.reshape(-1, m)
+        literal = flat[np.arange(h * w), arg.reshape(-1)].reshape(h, w)
+        got = O.masks_class(masks, cls, arg)
+        assert got.shape == (h, w) and np.array_equal(got, literal)
+        assert got.max() <= cls.max() + 1 and (got[~masks.any(axis=2)] == 0).all()

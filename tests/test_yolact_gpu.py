@@ -279,3 +279,65 @@ def test_detect_host_matches_device(bu, bsz):
         assert torch.equal(hb[b, :m], ref.boxes[b, :m].cpu()) and torch.equal(hs[b, :m], ref.scores[b, :m].cpu())
         assert torch.equal(hc[b, :m], ref.class_ids[b, :m].cpu()) and torch.equal(ha[b], ref.masks_arg[b].cpu())
         assert torch.equal(hm[b, : hgt * wid * m], ref.masks_raw[b, : hgt * wid * m].cpu())
+
+
+# ------------------------------------------------------------------------------- class map
+@pytest.mark.parametrize("name", ["yolact_tiny_a", "yolact_tiny_b", "yolact_tiny_one"])
+def test_class_map_tiny_vs_golden(bu, name):
+    g = load_golden(name)
+    res = bu.decode_nms_class_map((dev(g["box"])[None], dev(g["conf"])[None], dev(g["coef"])[None], dev(g["proto"])[None]),
+                                  dev(g["anchors"]), float(g["confidence"]), float(g["nms_iou"]), g["image_shape"])
+    boxes, scores, cls, cmap = res
+    assert cmap.dtype == torch.uint8 and tuple(cmap.shape) == tuple(int(v) for v in g["image_shape"])
+    assert np.array_equal(host(scores), g["scores"]) and np.array_equal(host(cls), g["class_ids"])
+    assert_close_f32(host(boxes), g["boxes"], 1e-5, "boxes")
+    expect = O.masks_class(unpack_masks(g), g["class_ids"], g["masks_arg"])
+    assert float(np.mean(host(cmap).astype(np.int64) != expect)) <= 1e-3
+
+
+def test_class_map_none(bu):
+    g = load_golden("yolact_tiny_none")
+    res = bu.decode_nms_class_map((dev(g["box"])[None], dev(g["conf"])[None], dev(g["coef"])[None], dev(g["proto"])[None]),
+                                  dev(g["anchors"]), float(g["confidence"]), float(g["nms_iou"]), g["image_shape"])
+    assert res == (None,) * 4
+
+
+def test_class_map_batch_matches_full_outputs_and_host_entry(bu):
+    """The class map must be exactly what yolact.py:167-169 computes from this library's own decode_nms outputs, the
+    empty image gets zeros, and the host-buffer entry point returns the same bytes."""
+    import ctypes as C
+    from isb import _lib
+    a, p = synth.yolact_dims(550)
+    anchors = torch.from_numpy(O.get_anchors((550, 550))).float()
+    bsz = 4
+    box, conf, coef, proto = synth.yolact_batch(2100, bsz, a, num_classes=81, proto=p)
+    conf[2] = conf[2] * 0.0 + 0.001                        # image 2: nothing passes
+    ins = (box.cuda(), conf.cuda(), coef.cuda(), proto.cuda())
+    full = bu.decode_nms_batch(ins, anchors.cuda(), 0.05, 0.5, (550, 550))
+    boxes, scores, cls, cmap, counts = bu.decode_nms_class_map_batch(ins, anchors.cuda(), 0.05, 0.5, (550, 550))
+    assert np.array_equal(host(counts), host(full.counts)) and host(counts)[2] == 0
+    for b in range(bsz):
+        m = int(host(counts)[b])
+        if m == 0:
+            assert not host(cmap[b]).any()
+            continue
+        fb, fs, fc, farg, fmask = full.image(b, m)
+        assert torch.equal(boxes[b, :m], fb) and torch.equal(scores[b, :m], fs) and torch.equal(cls[b, :m], fc)
+        expect = O.masks_class(host(fmask), host(fc), host(farg))
+        assert np.array_equal(host(cmap[b]).astype(np.int64), expect)
+    # host-buffer entry
+    h = _lib.get_handle(0)
+    pins = [t.contiguous().pin_memory() for t in (box, conf, coef, proto)]
+    panc = anchors.pin_memory()
+    hb, hs = torch.empty((bsz, 100, 4)).pin_memory(), torch.empty((bsz, 100)).pin_memory()
+    hc = torch.empty((bsz, 100), dtype=torch.int64).pin_memory()
+    hm = torch.empty((bsz, 550, 550), dtype=torch.uint8).pin_memory()
+    hn = torch.empty((bsz,), dtype=torch.int32).pin_memory()
+    pin = _lib.YolactIn(bsz, a, 81, 32, p, p, 550, 550, pins[0].data_ptr(), pins[1].data_ptr(), pins[2].data_ptr(),
+                        pins[3].data_ptr(), panc.data_ptr(), 0.05, 0.5, 200, 100)
+    pout = _lib.YolactMapOut(hb.data_ptr(), hs.data_ptr(), hc.data_ptr(), hm.data_ptr(), hn.data_ptr())
+    h.check(h.lib.isb_yolact_class_map_host(h.ptr, C.byref(pin), C.byref(pout), None))
+    assert np.array_equal(hn.numpy(), host(counts)) and np.array_equal(hm.numpy(), host(cmap))
+    for b in range(bsz):
+        m = int(hn[b])
+        assert np.array_equal(hs[b, :m].numpy(), host(scores[b, :m])) and np.array_equal(hc[b, :m].numpy(), host(cls[b, :m]))
