@@ -239,6 +239,17 @@ ISB_API int isb_resize_boxes(isb_handle* h, const float* boxes, int64_t m, int32
 ISB_API int isb_paste_masks(isb_handle* h, const float* masks, const float* boxes, int32_t m, int32_t mask_size,
                     int32_t padding, int32_t im_h, int32_t im_w, float* out, isb_stream stream);
 
+/* Wrapper tail inst_model/Mask_RCNN/mask_rcnn.py:174-198 fused with paste_masks_in_image (transform.py:212-230):
+ * keep detections with score > confidence, paste their SxS probability masks into a (paste_h, paste_w) frame,
+ * F.interpolate(bilinear, align_corners=False) to (out_h, out_w), arg-max over the kept detections, > 0.5, and
+ *     class_map[y, x] = labels[kept[arg]] + 1 where that mask is set, else 0          (uint8 [out_h, out_w]).
+ * The [m,1,Hp,Wp] pasted floats and the [H,W,m] resized masks are never materialised.  masks_arg (int64 [H,W],
+ * index into the KEPT detections) and kept_count (int32) are optional (NULL = not written). */
+ISB_API int isb_paste_class_map(isb_handle* h, const float* masks, const float* boxes, const int64_t* labels,
+                                const float* scores, int32_t m, int32_t mask_size, int32_t padding, int32_t paste_h,
+                                int32_t paste_w, int32_t out_h, int32_t out_w, float confidence, uint8_t* class_map,
+                                int64_t* masks_arg, int32_t* kept_count, isb_stream stream);
+
 /* rpn_function.py:434-458 _get_top_n_idx + :460-529 filter_proposals, for ONE image:
  * proposals [A,4] (already decoded, rpn_function.py:624), objectness [A] logits, anchors_per_level
  * (HOST array of num_levels ints).  Per-level top pre_nms_top_n by logit, sigmoid, clip to the image,

@@ -19,7 +19,7 @@ SYMBOLS = (
     "isb_yolact_detect", "isb_yolact_detect_host", "isb_yolact_class_map", "isb_yolact_class_map_host", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
     "isb_traditional_nms", "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_assemble",
     "isb_box_decode", "isb_nms", "isb_batched_nms", "isb_ms_roi_align", "isb_mask_select_sigmoid", "isb_resize_boxes",
-    "isb_paste_masks", "isb_rpn_filter", "isb_box_postprocess",
+    "isb_paste_masks", "isb_paste_class_map", "isb_rpn_filter", "isb_box_postprocess",
 )
 
 
@@ -107,6 +107,7 @@ def load():
         lib.isb_mask_select_sigmoid.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
         lib.isb_resize_boxes.argtypes = [vp, vp, i64, i32, i32, i32, i32, vp, vp]
         lib.isb_paste_masks.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]
+        lib.isb_paste_class_map.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp, vp, vp, vp]
         lib.isb_rpn_filter.argtypes = [vp, vp, vp, C.POINTER(i32), i32, i32, i32, i32, i32, f64, f32, f32, vp, vp, vp, vp]
         lib.isb_box_postprocess.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, f32, f32, f32, f32, f64, i32,
                                             vp, vp, vp, vp, vp]

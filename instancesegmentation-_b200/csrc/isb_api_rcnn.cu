@@ -114,3 +114,25 @@ extern "C" int isb_paste_masks(isb_handle* h, const float* masks, const float* b
   ISB_CUDA(h, cudaSetDevice(h->device));
   return launch_paste_masks(h, masks, boxes, m, mask_size, padding, im_h, im_w, out, (cudaStream_t)stream);
 }
+
+namespace isb {
+int launch_paste_class_map(isb_handle* h, const float* masks, const float* boxes, const int64_t* labels, const float* scores, int m,
+                           int S, int pad, int paste_h, int paste_w, int out_h, int out_w, float confidence, uint8_t* class_map,
+                           int64_t* masks_arg, int32_t* kept_count, cudaStream_t s);
+}
+
+extern "C" int isb_paste_class_map(isb_handle* h, const float* masks, const float* boxes, const int64_t* labels,
+                                   const float* scores, int32_t m, int32_t mask_size, int32_t padding, int32_t paste_h,
+                                   int32_t paste_w, int32_t out_h, int32_t out_w, float confidence, uint8_t* class_map,
+                                   int64_t* masks_arg, int32_t* kept_count, isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (m < 0 || mask_size <= 0 || padding < 0 || paste_h <= 0 || paste_w <= 0 || out_h <= 0 || out_w <= 0)
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "paste_class_map: bad size");
+  if ((int64_t)out_h * out_w >= (1ll << 31)) ISB_FAIL(h, ISB_ERR_LIMIT, "paste_class_map: output image too large");
+  if (!class_map) ISB_FAIL(h, ISB_ERR_BAD_ARG, "paste_class_map: null class_map");
+  if (m > 0 && (!masks || !boxes || !labels || !scores || !al16(boxes)))
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "paste_class_map: null or misaligned pointer");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  return isb::launch_paste_class_map(h, masks, boxes, labels, scores, m, mask_size, padding, paste_h, paste_w, out_h, out_w,
+                                     confidence, class_map, masks_arg, kept_count, (cudaStream_t)stream);
+}

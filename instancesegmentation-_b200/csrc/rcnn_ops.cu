@@ -137,6 +137,99 @@ __global__ void __launch_bounds__(256) paste_masks_kernel(const float* __restric
 }
 
 // ------------------------------------------------------------------------------------------
+// Wrapper tail inst_model/Mask_RCNN/mask_rcnn.py:174-198 fused with the paste (transform.py:212-230): score filter,
+// paste into (paste_h, paste_w), bilinear resize to the original image size, arg-max over detections, > 0.5, class
+// image.  None of the intermediates ([m,1,Hp,Wp] floats: 118 MB at 544^2 x 100; [H,W,m] at the original size) exists:
+// a thread owns one output pixel, finds its four source taps in the pasted frame, and for each kept detection whose
+// pasted window contains a tap evaluates the paste at those taps on the fly (same arithmetic as paste_masks_kernel).
+// ------------------------------------------------------------------------------------------
+struct PasteDet {
+  int x0, y0, x1, y1;  // integer box after expand + truncation
+  float sx, sy;        // padded mask size / box size
+  int src;             // row of masks / boxes
+  int cls;             // label
+};
+
+__device__ __forceinline__ float pasted_at(const float* __restrict__ mk, const PasteDet& d, int S, int pad, int Sp, int y, int x) {
+  if (x < d.x0 || x > d.x1 || y < d.y0 || y > d.y1) return 0.0f;
+  int iy0, iy1, ix0, ix1;
+  float ly0, ly1, lx0, lx1;
+  bilinear_src(y - d.y0, d.sy, Sp, iy0, iy1, ly0, ly1);
+  bilinear_src(x - d.x0, d.sx, Sp, ix0, ix1, lx0, lx1);
+  const float top = lx0 * padded_at(mk, S, pad, iy0, ix0) + lx1 * padded_at(mk, S, pad, iy0, ix1);
+  const float bot = lx0 * padded_at(mk, S, pad, iy1, ix0) + lx1 * padded_at(mk, S, pad, iy1, ix1);
+  return ly0 * top + ly1 * bot;
+}
+
+constexpr int kPcmThreads = 256;
+
+__global__ void __launch_bounds__(kPcmThreads)
+paste_class_map_kernel(const float* __restrict__ masks, const float4* __restrict__ boxes, const int64_t* __restrict__ labels,
+                       const float* __restrict__ scores, int m, int S, int pad, int paste_h, int paste_w, int out_h, int out_w,
+                       float confidence, uint8_t* __restrict__ class_map, int64_t* __restrict__ masks_arg,
+                       int32_t* __restrict__ kept_count) {
+  extern __shared__ __align__(16) unsigned char pcm_smem[];
+  PasteDet* dets = reinterpret_cast<PasteDet*>(pcm_smem);
+  __shared__ int s_wcount[kPcmThreads / 32];
+  __shared__ int s_n;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int Sp = S + 2 * pad;
+  const float scale = (float)((double)Sp / (double)S);
+  // kept detections (score > confidence, mask_rcnn.py:174), in their original order
+  if (tid == 0) s_n = 0;
+  __syncthreads();
+  for (int base = 0; base < m; base += kPcmThreads) {
+    const int i = base + tid;
+    const bool keep = i < m && scores[i] > confidence;
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_wcount[warp] = __popc(bal);
+    __syncthreads();
+    int off = s_n, tot = 0;
+    for (int w = 0; w < kPcmThreads / 32; ++w) {
+      if (w < warp) off += s_wcount[w];
+      tot += s_wcount[w];
+    }
+    if (keep) {
+      const PasteBox pb = paste_box(boxes[i], scale);
+      PasteDet d;
+      d.x0 = pb.x0; d.y0 = pb.y0; d.x1 = pb.x1; d.y1 = pb.y1;
+      d.sx = (float)Sp / (float)max(pb.x1 - pb.x0 + 1, 1);
+      d.sy = (float)Sp / (float)max(pb.y1 - pb.y0 + 1, 1);
+      d.src = i;
+      d.cls = (int)labels[i];
+      dets[off + __popc(bal & ((1u << lane) - 1u))] = d;
+    }
+    __syncthreads();
+    if (tid == 0) s_n += tot;
+    __syncthreads();
+  }
+  const int n = s_n;
+  if (blockIdx.x == 0 && tid == 0 && kept_count) *kept_count = n;
+  const float ry = (float)paste_h / (float)out_h, rx = (float)paste_w / (float)out_w;  // F.interpolate, align_corners=False
+  const int total = out_h * out_w;
+  for (int q = blockIdx.x * kPcmThreads + tid; q < total; q += gridDim.x * kPcmThreads) {
+    const int y = q / out_w, x = q - y * out_w;
+    int iy0, iy1, ix0, ix1;
+    float ly0, ly1, lx0, lx1;
+    bilinear_src(y, ry, paste_h, iy0, iy1, ly0, ly1);
+    bilinear_src(x, rx, paste_w, ix0, ix1, lx0, lx1);
+    float best = 0.0f;
+    int arg = 0;
+    for (int k = 0; k < n; ++k) {
+      const PasteDet d = dets[k];
+      if (iy1 < d.y0 || iy0 > d.y1 || ix1 < d.x0 || ix0 > d.x1) continue;  // all four taps are zeros of the paste
+      const float* mk = masks + (int64_t)d.src * S * S;
+      const float top = lx0 * pasted_at(mk, d, S, pad, Sp, iy0, ix0) + lx1 * pasted_at(mk, d, S, pad, Sp, iy0, ix1);
+      const float bot = lx0 * pasted_at(mk, d, S, pad, Sp, iy1, ix0) + lx1 * pasted_at(mk, d, S, pad, Sp, iy1, ix1);
+      const float v = ly0 * top + ly1 * bot;
+      if (v > best) { best = v; arg = k; }
+    }
+    class_map[q] = (n > 0 && best > 0.5f) ? (uint8_t)(dets[arg].cls + 1) : (uint8_t)0;
+    if (masks_arg) masks_arg[q] = arg;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // torchvision MultiScaleRoIAlign (ctor sites faster_rcnn_framework.py:326-329, mask_rcnn.py:150;
 // call sites roi_head.py:491,540): FPN level = floor(k0 + log2(sqrt(area)/s0) + eps) clamped to
 // [k_min,k_max]; per-level roi_align(aligned=False, sampling_ratio>0); result in RoI order.
@@ -387,6 +480,20 @@ int launch_paste_masks(isb_handle* h, const float* masks, const float* boxes, in
     paste_masks_kernel<unsigned long long><<<grid_for(nvec, 256, h->num_sms, 8), 256, 0, s>>>(
         masks, reinterpret_cast<const float4*>(boxes), m, S, pad, im_h, im_w, out);
   ISB_LAUNCH_CHECK(h, "paste_masks_kernel");
+  return ISB_OK;
+}
+int launch_paste_class_map(isb_handle* h, const float* masks, const float* boxes, const int64_t* labels, const float* scores, int m,
+                           int S, int pad, int paste_h, int paste_w, int out_h, int out_w, float confidence, uint8_t* class_map,
+                           int64_t* masks_arg, int32_t* kept_count, cudaStream_t s) {
+  const size_t smem = (size_t)(m > 0 ? m : 1) * sizeof(PasteDet);
+  if (smem > 160 * 1024) ISB_FAIL(h, ISB_ERR_LIMIT, "paste_class_map: %d detections exceed shared memory", m);
+  if (smem > 48 * 1024)
+    ISB_CUDA(h, cudaFuncSetAttribute(paste_class_map_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t total = (int64_t)out_h * out_w;
+  paste_class_map_kernel<<<grid_for(total, kPcmThreads, h->num_sms, 8), kPcmThreads, smem, s>>>(
+      masks, reinterpret_cast<const float4*>(boxes), labels, scores, m, S, pad, paste_h, paste_w, out_h, out_w, confidence, class_map,
+      masks_arg, kept_count);
+  ISB_LAUNCH_CHECK(h, "paste_class_map_kernel");
   return ISB_OK;
 }
 int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, const int32_t* batch_idx, int num_rois,

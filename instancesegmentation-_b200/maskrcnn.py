@@ -225,3 +225,26 @@ def paste_masks_in_image(masks, boxes, img_shape, padding=1):
         _call(dev, lambda h: h.lib.isb_paste_masks(h.ptr, _ptr(masks), _ptr(boxes), m, s, int(padding), im_h, im_w, _ptr(out),
                                                    _stream(dev)))
     return out
+
+
+# ---------------------------------------------------------------------------- mask_rcnn.py:174-198 (wrapper tail)
+def masks_class_image(masks, boxes, labels, scores, confidence, paste_shape, image_shape, padding=1, return_arg=False):
+    """`MASK_RCNN.detect_image` tail (inst_model/Mask_RCNN/mask_rcnn.py:174-198) fused with `paste_masks_in_image`:
+    masks [m,1,S,S] probabilities, boxes [m,4] in the paste frame, labels int64 [m], scores [m]  ->  uint8 [H,W] class
+    image (labels[arg] + 1 where the arg-max kept detection's resized mask is > 0.5, else 0).  Detections with
+    score <= confidence are dropped first (:174); with nothing kept the image is all zeros (the wrapper returns the
+    input picture unchanged in that case).  `return_arg` adds masks_arg (int64 [H,W], index into the kept detections)."""
+    masks = _cuda_f32(masks, "masks")
+    dev = masks.device
+    boxes = _cuda_f32(boxes, "boxes").to(dev)
+    scores = _cuda_f32(scores, "scores").to(dev)
+    labels = labels.to(device=dev, dtype=torch.int64).contiguous()
+    m, s = masks.shape[0], masks.shape[-1]
+    ph, pw = int(paste_shape[0]), int(paste_shape[1])
+    oh, ow = int(image_shape[0]), int(image_shape[1])
+    out = torch.empty((oh, ow), dtype=torch.uint8, device=dev)
+    arg = torch.empty((oh, ow), dtype=torch.int64, device=dev) if return_arg else None
+    _call(dev, lambda h: h.lib.isb_paste_class_map(h.ptr, _ptr(masks), _ptr(boxes), _ptr(labels), _ptr(scores), m, s, int(padding),
+                                                   ph, pw, oh, ow, float(confidence), _ptr(out),
+                                                   _ptr(arg) if return_arg else None, None, _stream(dev)))
+    return (out, arg) if return_arg else out

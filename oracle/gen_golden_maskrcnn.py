@@ -136,7 +136,43 @@ def roi_full(name, seed):
           out14=out14[::10, ::16].numpy(), sum7=float(out7.double().sum()), sum14=float(out14.double().sum()))
 
 
+def class_image(name, seed, m=40, paste_hw=(272, 272), sizes=((272, 272), (360, 480), (200, 150))):
+    """Wrapper tail mask_rcnn.py:174-198.  The paste is the reference's own `transform.paste_masks_in_image`; the tail
+    lives inside `MASK_RCNN.detect_image` (not importable: its module pulls cv2 / pynvml-dependent configs), so its
+    torch / numpy statements are re-enacted here one by one on the reference's pasted masks."""
+    import torch.nn.functional as F
+    R = _ref()
+    g = torch.Generator().manual_seed(seed)
+    boxes = clustered_boxes(g, m, extent=(float(paste_hw[1]) * 0.8, float(paste_hw[0]) * 0.8), clusters=12, jitter=5.0)
+    boxes[:, :2] = boxes[:, :2].clamp(min=-8.0)
+    probs = torch.sigmoid(torch.randn(m, 1, 28, 28, generator=g) * 2.5 + 0.5)
+    # smooth the random masks a little so that they look like blobs rather than salt and pepper
+    probs = F.avg_pool2d(probs, 5, stride=1, padding=2)
+    probs = (probs - probs.amin(dim=(2, 3), keepdim=True)) / (probs.amax(dim=(2, 3), keepdim=True) - probs.amin(dim=(2, 3), keepdim=True))
+    labels = torch.randint(1, 21, (m,), generator=g)
+    scores = torch.rand(m, generator=g)
+    confidence = 0.3
+    pasted = R.transform.paste_masks_in_image(probs, boxes, paste_hw, padding=1)          # transform.py:212
+    out = {}
+    for k, (h, w) in enumerate(sizes):
+        idxs = np.greater(scores.numpy(), confidence)                                      # :174
+        classes = labels.numpy()[idxs]
+        masks = pasted.squeeze(1)[torch.from_numpy(idxs)]
+        ms = F.interpolate(masks.unsqueeze(0), (h, w), mode="bilinear", align_corners=False).squeeze(0)   # :186
+        ms = ms.permute(1, 2, 0).contiguous()
+        arg = torch.argmax(ms, dim=-1)
+        ms = ms > 0.5
+        mc = ms * (classes[None, None, :] + 1)                                             # :195
+        mc = np.reshape(mc, [-1, np.shape(ms)[-1]])
+        mc = np.reshape(mc[np.arange(np.shape(mc)[0]), np.reshape(arg, [-1])], [h, w])
+        out[f"class_map_{k}"] = np.asarray(mc).astype(np.uint8)
+        out[f"arg_{k}"] = arg.numpy().astype(np.int16)
+    _save(name, seed=seed, boxes=boxes.numpy(), probs=probs.numpy(), labels=labels.numpy(), scores=scores.numpy(),
+          confidence=np.float32(confidence), paste_hw=np.array(paste_hw), sizes=np.array(sizes), **out)
+
+
 def main():
+    class_image("maskrcnn_class_image", 4401)
     stages("maskrcnn_stages", 31)
     rpn_filter("maskrcnn_rpn_filter", 4001)
     box_post("maskrcnn_box_post", 4101)

@@ -317,3 +317,22 @@ def paste_masks_in_image(masks, boxes, img_shape, padding=1):
         if x_1 > x_0 and y_1 > y_0:
             out[i, 0, y_0:y_1, x_0:x_1] = res[(y_0 - y0b):(y_1 - y0b), (x_0 - x0b):(x_1 - x0b)]
     return out
+
+
+# --------------------------------------------------------------------------- next row
+def masks_class_image(pasted, labels, scores, confidence, image_shape):
+    """inst_model/Mask_RCNN/mask_rcnn.py:174-198 -- the wrapper's class image from the model's outputs:
+    pasted [m,1,Hp,Wp] float32 (paste_masks_in_image), labels int64 [m], scores [m].  Detections with
+    score <= confidence are dropped (:174-181), the rest are resized to image_shape (bilinear, align_corners=False,
+    :186), arg-max over detections (:188), > 0.5 (:189), class image = (label + 1) of the arg-max detection where its
+    mask is set (:195-197).  Returns (masks_class int64 [H,W], masks_arg int64 [H,W]) or (None, None)."""
+    from .yolact_np import masks_class, upsample_bilinear
+    keep = np.asarray(scores, dtype=F32) > F32(confidence)
+    if not keep.any():
+        return None, None
+    maps = np.asarray(pasted, dtype=F32)[keep][:, 0]
+    classes = np.asarray(labels).astype(np.int64)[keep]
+    up = upsample_bilinear(maps, int(image_shape[0]), int(image_shape[1]))    # [m', H, W]
+    hwm = np.ascontiguousarray(np.transpose(up, (1, 2, 0)))                   # :187
+    arg = np.argmax(hwm, axis=-1)                                             # first maximum, like torch.argmax
+    return masks_class(hwm > F32(0.5), classes, arg), arg

@@ -50,3 +50,15 @@ def test_box_postprocess():
     b2, s2, l2 = M.postprocess_detections(logits.numpy(), reg.numpy(), proposals.numpy(), tuple(g["image_shape"]))
     assert np.array_equal(l2, g["labels"])
     assert_close_f32(s2, g["scores"], 1e-5, "softmax scores")
+
+
+def test_class_image_wrapper_tail():
+    """mask_rcnn.py:174-198 (next row): oracle vs the reference's paste + the wrapper's own statements."""
+    g = load_golden("maskrcnn_class_image")
+    pasted = M.paste_masks_in_image(g["probs"], g["boxes"], tuple(int(v) for v in g["paste_hw"]))
+    for k, (h, w) in enumerate(g["sizes"]):
+        mc, arg = M.masks_class_image(pasted, g["labels"], g["scores"], float(g["confidence"]), (int(h), int(w)))
+        assert float(np.mean(mc != g[f"class_map_{k}"])) <= 1e-3
+        assert float(np.mean(arg != g[f"arg_{k}"])) <= 1e-3
+    none, _ = M.masks_class_image(pasted, g["labels"], g["scores"], 2.0, (50, 50))
+    assert none is None

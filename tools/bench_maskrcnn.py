@@ -66,6 +66,12 @@ def main():
                                           C.c_void_p(torch.cuda.current_stream().cuda_stream)))
         us = timeit(paste)
         res[f"paste_masks_100_to_{shape[0]}x{shape[1]}"] = {"us": us, "out_GBs": 100 * shape[0] * shape[1] * 4 / us / 1e3}
+    # wrapper tail fused with the paste (mask_rcnn.py:174-198): 544x544 paste frame -> class image at the original size
+    scores = torch.rand(100, device=dev)
+    b544 = boxes * (544.0 / 1333.0)
+    for shape in ((544, 544), (1080, 1920)):
+        us = timeit(lambda: R.masks_class_image(probs, b544, labels, scores, 0.5, (544, 544), shape))
+        res[f"class_image_100_544x544_to_{shape[0]}x{shape[1]}"] = {"us": us}
     print(json.dumps(res, indent=1))
 
 
