@@ -327,6 +327,34 @@ def run_gpu(args):
     assert np.array_equal(h_counts.numpy(), counts) and np.array_equal(h_map.numpy(), cm_out[3].cpu().numpy())
     cm_d2h = int(h_boxes.numel() * 4 + h_scores.numel() * 4 + h_cls.numel() * 8 + h_map.numel() + h_counts.numel() * 4)
 
+    # ---- raw-logits variant (F.softmax of nets/yolact.py:204 fused into the score filter) -- extra keys only
+    lg = synth.yolact_batch(SEED_BASE + (start % 1000), DISTINCT_IMAGES, a, num_classes=NUM_CLASSES, proto=p, return_logits=True)[1]
+    logits_d = lg.repeat((reps, 1, 1)).contiguous().to(dev)
+    lg_in = [dev_in[0], logits_d, dev_in[2], dev_in[3]]
+    for _ in range(3):
+        bu.decode_nms_batch(lg_in, anchors_d, CONFIDENCE, NMS_IOU, shape, TOP_K, MAX_DET, out=out, logits=True)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.counts.cpu().numpy(), counts)
+    handle.profile_begin(cm_steps)
+    ev0.record()
+    for _ in range(cm_steps):
+        bu.decode_nms_batch(lg_in, anchors_d, CONFIDENCE, NMS_IOU, shape, TOP_K, MAX_DET, out=out, logits=True)
+    ev1.record()
+    torch.cuda.synchronize()
+    lg_ms = ev0.elapsed_time(ev1) / cm_steps
+    lg_stage, lg_calls = handle.profile_read()
+    handle.profile_begin(0)
+    for _ in range(3):
+        torch.softmax(logits_d, dim=-1)
+    torch.cuda.synchronize()
+    ev0.record()
+    for _ in range(cm_steps):
+        torch.softmax(logits_d, dim=-1)
+    ev1.record()
+    torch.cuda.synchronize()
+    softmax_ms = ev0.elapsed_time(ev1) / cm_steps
+    del logits_d, lg_in
+
     if world > 1:
         t = torch.tensor([ms, e2e_s, cm_ms, cm_e2e_s], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -363,6 +391,11 @@ def run_gpu(args):
                                       "value": bsz * world / (cm_ms * 1e-3), "ms_per_step": cm_ms,
                                       "e2e": bsz * world / cm_e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                                       "d2h_bytes_per_step": cm_d2h, "api": "isb_yolact_class_map[_host]"},
+                "from_logits_variant": {"what": "raw class logits in, softmax (nets/yolact.py:204) fused into the score filter "
+                                                "(SURVEY 8f rank 2); not the headline",
+                                        "value": bsz / (lg_ms * 1e-3), "ms_per_step": lg_ms, "unit": UNIT + " (this rank)",
+                                        "candidates_ms": lg_stage[0] / max(lg_calls, 1),
+                                        "torch_softmax_ms_it_replaces": softmax_ms},
                 "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -91,6 +91,10 @@ typedef struct {
   float nms_iou;
   int32_t top_k;        /* reference default 200 (utils_bbox.py:50)                     */
   int32_t max_det;      /* reference default 100                                        */
+  int32_t conf_is_logits; /* 0: conf is softmaxed (the reference's input).  1: conf holds RAW class logits and
+                             the softmax of nets/yolact.py:204 (F.softmax(pred_classes, -1)) is fused into the
+                             score filter -- the [B,A,C] probabilities are never written or re-read (SURVEY 8f
+                             rank 2).  conf must then be 16-byte aligned.                              */
 } isb_yolact_in;
 
 typedef struct {

@@ -39,7 +39,7 @@ class YolactIn(C.Structure):
                 ("proto_h", C.c_int32), ("proto_w", C.c_int32), ("out_h", C.c_int32), ("out_w", C.c_int32),
                 ("box", C.c_void_p), ("conf", C.c_void_p), ("coef", C.c_void_p), ("proto", C.c_void_p),
                 ("anchors", C.c_void_p), ("confidence", C.c_float), ("nms_iou", C.c_float),
-                ("top_k", C.c_int32), ("max_det", C.c_int32)]
+                ("top_k", C.c_int32), ("max_det", C.c_int32), ("conf_is_logits", C.c_int32)]
 
 
 class YolactOut(C.Structure):

@@ -235,6 +235,8 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const Yo
   cp.use_threshold = 1;
   cp.threshold = in->confidence;
   cp.batch = in->batch;
+  cp.logits = in->conf_is_logits ? 1 : 0;
+  if (cp.logits && !aligned16(in->conf)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "conf must be 16-byte aligned when conf_is_logits is set");
   if ((rc = launch_candidates(h, cp, s)) != ISB_OK) return rc;
   if (ev) ISB_CUDA(h, cudaEventRecord(ev[1], s));
 
@@ -495,6 +497,7 @@ extern "C" int isb_fast_nms(isb_handle* h, const float* box, const float* scores
   cp.use_threshold = 0;  // the stand-alone method ranks every entry (utils_bbox.py:55-64)
   cp.threshold = 0.0f;
   cp.batch = 1;
+  cp.logits = 0;
   if ((rc = launch_candidates(h, cp, s)) != ISB_OK) return rc;
   NmsParams np;
   memset(&np, 0, sizeof(np));

@@ -349,6 +349,7 @@ struct CandParams {
   int32_t use_threshold; // 0: every entry is a candidate
   float threshold;
   int32_t batch;
+  int32_t logits;        // 1: scores are raw logits, softmax over the ncols columns is fused into the filter
 };
 int launch_candidates(isb_handle* h, const CandParams& p, cudaStream_t s);
 

@@ -127,11 +127,204 @@ candidates_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_t* __re
   }
 }
 
-int configure_candidates(isb_handle* h) { (void)h; return ISB_OK; }
+// ---------------------------------------------------------------------------------------------------------------
+// K1L -- the same filter fed with RAW class logits: softmax over the C columns (nets/yolact.py:204,
+// F.softmax(pred_classes, -1)) fused into the pass, so the conf tensor is never written and re-read.
+//
+// A row is C = 81 floats = 324 bytes: not a multiple of 16, so rows cannot be read as vectors, and a warp-per-row
+// layout spends ~45 warp instructions per row on shuffles.  Instead every WARP streams its own tiles of 16 consecutive
+// rows -- one contiguous 5 KB byte range -- into its private shared-memory buffers with one 1-D bulk (TMA) copy per
+// tile, double-buffered on the warp's two mbarriers: no CTA-wide barrier exists after start-up (a CTA-wide 128-row
+// tile version spent 39 % of its time at the tile barrier waiting for warps whose rows had candidates).  Two lanes
+// share a row (even / odd columns; the row stride of 81 words is odd, so the lanes of a warp spread over the banks).
+// Per row: max, sum of exp(x - max), and a test in logit space, x - max > log(threshold * sum) - margin, that sends
+// only real candidates to the exact expf(x - max) / sum > threshold.  Hits wait in a per-warp list and leave with one
+// reservation when the warp moves to another image (a warp's tiles are consecutive).
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float exp2f_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+constexpr int kLgRows = 16;      // rows per warp tile
+constexpr int kLgThreads = 256;  // 8 warps
+constexpr int kLgWarps = kLgThreads / 32;
+constexpr int kLgStage = 96;     // parked keys per warp
+
+struct LgWarpStage {
+  uint64_t keys[kLgStage];
+  int n;
+  int pad;
+};
+
+struct LgEmit {
+  LgWarpStage* sg;
+  int32_t* cand_count;
+  uint64_t* cand_keys;
+  int64_t cap, key_stride;
+};
+
+__device__ __forceinline__ void lg_flush(const LgEmit& e, int img, int lane) {  // whole warp, converged
+  __syncwarp();
+  const int staged = min(e.sg->n, kLgStage);
+  if (staged > 0) {
+    int gbase = 0;
+    if (lane == 0) gbase = atomicAdd(&e.cand_count[img], staged);
+    gbase = __shfl_sync(0xffffffffu, gbase, 0);
+    for (int i = lane; i < staged; i += 32)
+      if ((int64_t)gbase + i < e.cap) e.cand_keys[(size_t)img * e.key_stride + gbase + i] = e.sg->keys[i];
+  }
+  __syncwarp();
+  if (lane == 0) e.sg->n = 0;
+  __syncwarp();
+}
+
+// One row shared by a lane pair.  `row` is either the shared-memory copy (the normal case; inlined separately so the
+// loads compile to LDS) or, for the tensor's very last rows whose tail the aligned bulk copy could not cover, global.
+__device__ __forceinline__ void lg_row(const float* row, const CandParams& p, int C, int par, bool valid, int img, uint32_t grow,
+                                       const LgEmit& e) {
+  const float ninf = -__int_as_float(0x7f800000);
+  const int cf = p.col0 + ((par - p.col0) & 1);  // first foreground column of this lane's parity
+  float m0 = ninf, m1 = ninf;
+  int c = cf;
+  for (; c + 2 < C; c += 4) {
+    m0 = fmaxf(m0, row[c]);
+    m1 = fmaxf(m1, row[c + 2]);
+  }
+  if (c < C) m0 = fmaxf(m0, row[c]);
+  float mfg = fmaxf(m0, m1);
+  float mx = mfg;
+  for (int k = par; k < p.col0; k += 2) mx = fmaxf(mx, row[k]);
+  mfg = fmaxf(mfg, __shfl_xor_sync(0xffffffffu, mfg, 1));
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+  // sum of exp(x - max): ex2.approx (2 ulp) on the scaled argument.  Terms that matter to the sum have |x - max| of a few
+  // units, where this is within ~3e-7 of expf; the exact expf is kept for the candidates' own probabilities.
+  const float kLog2e = 1.4426950408889634f;
+  float s0 = 0.0f, s1 = 0.0f;
+  c = par;
+  for (; c + 2 < C; c += 4) {
+    s0 += exp2f_approx((row[c] - mx) * kLog2e);
+    s1 += exp2f_approx((row[c + 2] - mx) * kLog2e);
+  }
+  if (c < C) s0 += exp2f_approx((row[c] - mx) * kLog2e);
+  float sum = s0 + s1;
+  sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+  const float lim = p.threshold > 0.0f ? logf(p.threshold * sum) - 1e-4f : ninf;
+  if (valid && mfg - mx > lim) {  // most rows have no candidate at all
+    for (c = cf; c < C; c += 2) {
+      const float d = row[c] - mx;
+      if (!(d > lim)) continue;
+      const float pr = expf(d) / sum;
+      if (!(pr > p.threshold)) continue;
+      const uint64_t key = make_cand_key((uint32_t)(c - p.col0), pr, grow);
+      const int sp = atomicAdd(&e.sg->n, 1);
+      if (sp < kLgStage) {
+        e.sg->keys[sp] = key;
+      } else {  // list full: reserve directly (slow, rare)
+        const int pos = atomicAdd(&e.cand_count[img], 1);
+        if (pos < e.cap) e.cand_keys[(size_t)img * e.key_stride + pos] = key;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kLgThreads, 2)
+candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_t* __restrict__ cand_keys, int64_t cap,
+                         int64_t key_stride, int tiles_per_img, int64_t total_floats) {
+  extern __shared__ __align__(128) unsigned char lg_smem[];  // [warps][2] tile buffers
+  __shared__ __align__(8) uint64_t bars[kLgWarps][2];
+  __shared__ LgWarpStage stages[kLgWarps];
+  const int C = p.ncols;
+  const int tile_bytes = ((kLgRows * C * 4 + 15) & ~15) + 16;  // widened to 16-byte boundaries on both sides
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int total_tiles = p.batch * tiles_per_img;
+  const float* base = p.scores;
+  if (tid < kLgWarps) {
+    mbar_init(&bars[tid][0], 1);
+    mbar_init(&bars[tid][1], 1);
+    stages[tid].n = 0;
+  }
+  __syncthreads();
+
+  unsigned char* wbuf = lg_smem + (size_t)warp * 2 * tile_bytes;
+  LgEmit em;
+  em.sg = &stages[warp];
+  em.cand_count = cand_count;
+  em.cand_keys = cand_keys;
+  em.cap = cap;
+  em.key_stride = key_stride;
+
+  auto issue = [&](int tile, int stage) {  // lane 0 only
+    const int b = tile / tiles_per_img, t = tile - b * tiles_per_img;
+    const int r0 = t * kLgRows, nr = min(kLgRows, p.rows - r0);
+    const int64_t f0 = ((int64_t)b * p.rows + r0) * C, f1 = f0 + (int64_t)nr * C;
+    const int64_t a0 = f0 & ~(int64_t)3;                                          // floats, 16-byte boundary below
+    const int64_t a1 = min((f1 + 3) & ~(int64_t)3, total_floats & ~(int64_t)3);   // never past the tensor
+    const uint32_t bytes = (uint32_t)((a1 - a0) * 4);
+    mbar_expect_tx(&bars[warp][stage], bytes);
+    bulk_g2s(wbuf + (size_t)stage * tile_bytes, base + a0, bytes, &bars[warp][stage]);
+  };
+
+  // every warp of the grid owns a run of consecutive tiles
+  const int gw = blockIdx.x * kLgWarps + warp, nw = gridDim.x * kLgWarps;
+  const int per_warp = (total_tiles + nw - 1) / nw;
+  const int first = gw * per_warp, last = min(first + per_warp, total_tiles);
+  int cur_img = -1;
+  if (lane == 0 && first < last) issue(first, 0);
+  int it = 0;
+  for (int tile = first; tile < last; ++tile, ++it) {
+    const int stage = it & 1;
+    if (lane == 0 && tile + 1 < last) issue(tile + 1, stage ^ 1);  // released by the __syncwarp that ended the last tile
+    const int b = tile / tiles_per_img, t = tile - b * tiles_per_img;
+    if (b != cur_img) {
+      if (cur_img >= 0) lg_flush(em, cur_img, lane);
+      cur_img = b;
+    }
+    const int r0 = t * kLgRows, nr = min(kLgRows, p.rows - r0);
+    const int64_t f0 = ((int64_t)b * p.rows + r0) * C;
+    const int64_t a0 = f0 & ~(int64_t)3;
+    const int64_t a1 = min((f0 + (int64_t)nr * C + 3) & ~(int64_t)3, total_floats & ~(int64_t)3);
+    const int in_smem = (int)(a1 - f0);  // floats of this tile the bulk copy delivered (all but < 4 at the tensor's end)
+    const int par = lane & 1;
+    const bool valid = (lane >> 1) < nr;
+    const int r = valid ? (lane >> 1) : nr - 1;  // pairs past the image's last row redo it and emit nothing
+    mbar_wait(&bars[warp][stage], (it >> 1) & 1);
+    if (nr * C <= in_smem) {
+      const float* tilef = reinterpret_cast<const float*>(wbuf + (size_t)stage * tile_bytes) + (f0 - a0);
+      lg_row(tilef + r * C, p, C, par, valid, b, (uint32_t)(r0 + r), em);
+    } else {
+      lg_row(base + f0 + (int64_t)r * C, p, C, par, valid, b, (uint32_t)(r0 + r), em);
+    }
+    __syncwarp();
+    if (em.sg->n > kLgStage - 32) lg_flush(em, cur_img, lane);  // keep room so that the direct path stays rare
+  }
+  if (cur_img >= 0) lg_flush(em, cur_img, lane);
+}
+
+int configure_candidates(isb_handle* h) {
+  ISB_CUDA(h, cudaFuncSetAttribute(candidates_logits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+  return ISB_OK;
+}
 
 int launch_candidates(isb_handle* h, const CandParams& p, cudaStream_t s) {
   if ((int64_t)p.rows * p.ncols >= (1ll << 31)) ISB_FAIL(h, ISB_ERR_LIMIT, "score tensor of one image exceeds 2^31 elements");
   ISB_CUDA(h, cudaMemsetAsync(h->cand_count + h->ws_b0, 0, sizeof(int32_t) * p.batch, s));
+  if (p.logits) {
+    const int tile_bytes = ((kLgRows * p.ncols * 4 + 15) & ~15) + 16;
+    const size_t smem = (size_t)kLgWarps * 2 * tile_bytes;
+    if (smem > 100 * 1024)
+      ISB_FAIL(h, ISB_ERR_LIMIT, "detect from logits supports at most %d classes", (100 * 1024 / (2 * kLgWarps) - 32) / (kLgRows * 4));
+    if (!p.use_threshold) ISB_FAIL(h, ISB_ERR_BAD_ARG, "detect from logits needs a threshold");
+    const int tiles_per_img = (p.rows + kLgRows - 1) / kLgRows;
+    int64_t grid = (int64_t)p.batch * tiles_per_img;
+    if (grid > 2 * h->num_sms) grid = 2 * h->num_sms;
+    candidates_logits_kernel<<<(unsigned)grid, kLgThreads, smem, s>>>(
+        p, h->cand_count + h->ws_b0, h->cand_keys + (size_t)h->ws_b0 * h->cand_cap_pow2, h->lim.cand_capacity, h->cand_cap_pow2,
+        tiles_per_img, (int64_t)p.batch * p.rows * p.ncols);
+    ISB_LAUNCH_CHECK(h, "candidates_logits_kernel");
+    return ISB_OK;
+  }
   const int64_t nvec = ((int64_t)p.rows * p.ncols) / 4;
   int ctas = (int)((nvec + (int64_t)kCandThreads * kCandUnroll - 1) / ((int64_t)kCandThreads * kCandUnroll));
   // whole waves of 8 resident CTAs per SM; four waves measured best on B200 (76 us / 64 images vs 83 us for one)

@@ -205,10 +205,12 @@ class BBoxUtility(object):
 
     # ------------------------------------------------------------------ batched fused path
     def decode_nms_batch(self, outputs, anchors, confidence, nms_iou, image_shape, top_k=TOP_K,
-                         max_detections=MAX_DETECTIONS, out=None):
+                         max_detections=MAX_DETECTIONS, out=None, logits=False):
         """Fused Detect + mask assembly for a batch: outputs = (box [B,A,4], conf [B,A,C],
         coef [B,A,K], proto [B,Ph,Pw,K]) on one CUDA device.  Enqueues three kernels on the
-        current stream and returns a YolactBatchResult without synchronising."""
+        current stream and returns a YolactBatchResult without synchronising.
+        logits=True: outputs[1] holds the raw class logits of the prediction heads and the softmax of nets/yolact.py:204 is
+        fused into the score filter."""
         box, conf, coef, proto = [_cuda_f32(t, n) for t, n in zip(outputs, ("box", "conf", "coef", "proto"))]
         dev = box.device
         anchors = _cuda_f32(anchors, "anchors").to(dev)
@@ -229,7 +231,7 @@ class BBoxUtility(object):
                 torch.empty((bsz,), dtype=torch.int32, device=dev), (hgt, wid))
         h = get_handle(dev.index, max_batch=bsz, max_anchors=a, max_classes=c - 1, max_det=max_det, max_top_k=int(top_k))
         pin = YolactIn(bsz, a, c, k, ph, pw, hgt, wid, box.data_ptr(), conf.data_ptr(), coef.data_ptr(), proto.data_ptr(),
-                       anchors.data_ptr(), float(confidence), float(nms_iou), int(top_k), max_det)
+                       anchors.data_ptr(), float(confidence), float(nms_iou), int(top_k), max_det, 1 if logits else 0)
         pout = YolactOut(out.boxes.data_ptr(), out.scores.data_ptr(), out.class_ids.data_ptr(), out.masks_arg.data_ptr(),
                          out.masks_raw.data_ptr(), out.masks_raw.shape[1], out.counts.data_ptr())
         with torch.cuda.device(dev):
@@ -238,7 +240,7 @@ class BBoxUtility(object):
 
     # ------------------------------------------------------------------ yolact.py:162-170
     def decode_nms_class_map_batch(self, outputs, anchors, confidence, nms_iou, image_shape, top_k=TOP_K,
-                                   max_detections=MAX_DETECTIONS, out=None):
+                                   max_detections=MAX_DETECTIONS, out=None, logits=False):
         """Detect + the wrapper's per-pixel class image (inst_model/yolact/yolact.py:162-170) for a batch, without ever
         materialising bool [H,W,m] / int64 [H,W]: returns (boxes [B,D,4], scores [B,D], class_ids [B,D] i64,
         class_map [B,H,W] u8, counts [B] i32) on the device, nothing synchronised.
@@ -260,7 +262,7 @@ class BBoxUtility(object):
                    torch.empty((bsz,), dtype=torch.int32, device=dev))
         h = get_handle(dev.index, max_batch=bsz, max_anchors=a, max_classes=c - 1, max_det=max_det, max_top_k=int(top_k))
         pin = YolactIn(bsz, a, c, k, ph, pw, hgt, wid, box.data_ptr(), conf.data_ptr(), coef.data_ptr(), proto.data_ptr(),
-                       anchors.data_ptr(), float(confidence), float(nms_iou), int(top_k), max_det)
+                       anchors.data_ptr(), float(confidence), float(nms_iou), int(top_k), max_det, 1 if logits else 0)
         pout = YolactMapOut(*[t.data_ptr() for t in out])
         with torch.cuda.device(dev):
             h.check(h.lib.isb_yolact_class_map(h.ptr, C.byref(pin), C.byref(pout), _stream(dev)))
@@ -285,6 +287,24 @@ class BBoxUtility(object):
         if m == 0:
             return (None,) * 4
         return res[0][0, :m], res[1][0, :m], res[2][0, :m], res[3][0]
+
+    def decode_nms_from_logits(self, outputs, anchors, confidence, nms_iou, image_shape):
+        """decode_nms (utils_bbox.py:170-243) fed with the heads' RAW class logits: outputs[1] is pred_classes before
+        `F.softmax(pred_classes, -1)` (nets/yolact.py:204).  Same 5-tuple / five Nones."""
+        box, conf, coef, proto = outputs[0], outputs[1], outputs[2], outputs[3]
+        box = box.reshape(-1, 4)[None]
+        conf = conf.reshape(box.shape[1], -1)[None]
+        coef = coef.reshape(box.shape[1], -1)[None]
+        proto = proto.reshape((1,) + tuple(proto.shape[-3:]))
+        a, c = conf.shape[1], conf.shape[2]
+        res = self.decode_nms_batch((box, conf, coef, proto), anchors, confidence, nms_iou, image_shape, logits=True)
+        m = int(res.counts[0].item())
+        while m < 0:
+            cap = int(get_handle(box.device.index).limits.cand_capacity)
+            get_handle(box.device.index, cand_capacity=min(cap * 4, a * (c - 1)))
+            res = self.decode_nms_batch((box, conf, coef, proto), anchors, confidence, nms_iou, image_shape, logits=True)
+            m = int(res.counts[0].item())
+        return res.image(0, m)
 
     # ------------------------------------------------------------------ utils_bbox.py:170
     def decode_nms(self, outputs, anchors, confidence, nms_iou, image_shape, traditional_nms=False, max_detections=100):

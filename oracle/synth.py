@@ -24,9 +24,10 @@ def yolact_dims(input_size=550, num_classes=81, num_coef=32):
 
 
 def yolact_heads(seed, num_anchors, num_classes=81, num_coef=32, proto=138, objects=12, run=40,
-                 box_std=0.3, proto_hw=None):
+                 box_std=0.3, proto_hw=None, return_logits=False):
     """One image worth of head tensors (torch CPU float32):
-    box [A,4], conf [A,C] (softmaxed, column 0 = background), coef [A,K], proto [P,Q,K]."""
+    box [A,4], conf [A,C] (softmaxed, column 0 = background), coef [A,K], proto [P,Q,K].
+    return_logits=True puts the raw class logits in place of conf (same random draws)."""
     g = torch.Generator().manual_seed(int(seed))
     a, c = num_anchors, num_classes
     box = torch.randn(a, 4, generator=g) * box_std
@@ -42,7 +43,7 @@ def yolact_heads(seed, num_anchors, num_classes=81, num_coef=32, proto=138, obje
     coef = torch.tanh(torch.randn(a, num_coef, generator=g))
     ph, pw = (proto, proto) if proto_hw is None else proto_hw
     prot = torch.relu(torch.randn(ph, pw, num_coef, generator=g))
-    return box.contiguous(), conf.contiguous(), coef.contiguous(), prot.contiguous()
+    return box.contiguous(), (logits if return_logits else conf).contiguous(), coef.contiguous(), prot.contiguous()
 
 
 def yolact_batch(seed0, batch, num_anchors, **kw):

@@ -43,7 +43,7 @@ def test_every_entry_point_cites_the_reference():
 def test_struct_layout_matches_header(lib):
     # field order / sizes of the ctypes mirrors (LP64): catches drift between isb.h and _lib.py
     assert ctypes.sizeof(lib.Limits) == 32
-    assert ctypes.sizeof(lib.YolactIn) == 8 * 4 + 5 * 8 + 4 * 4
+    assert ctypes.sizeof(lib.YolactIn) == 8 * 4 + 5 * 8 + 4 * 4 + 8   # + conf_is_logits, padded to 8
     assert ctypes.sizeof(lib.YolactOut) == 7 * 8
     assert ctypes.sizeof(lib.YolactMapOut) == 5 * 8
 

@@ -341,3 +341,68 @@ def test_class_map_batch_matches_full_outputs_and_host_entry(bu):
     for b in range(bsz):
         m = int(hn[b])
         assert np.array_equal(hs[b, :m].numpy(), host(scores[b, :m])) and np.array_equal(hc[b, :m].numpy(), host(cls[b, :m]))
+
+
+# ------------------------------------------------------------------------------- detect from logits
+def _check_logits(g, res):
+    """Like _check, but the scores went through a different (fused) softmax: they agree to 2e-6 relative, not bit for bit,
+    so detections whose scores are that close (saturated scores near 1.0 are one ulp apart) may swap places.  Match the
+    detections by (class, box), require the matched scores to agree and the order to be score-descending, and compare
+    masks / arg-max through the permutation."""
+    boxes, scores, cls, arg, masks = [host(t) for t in res]
+    m = len(g["scores"])
+    assert len(scores) == m
+    perm = np.full(m, -1)
+    used = np.zeros(m, bool)
+    for i in range(m):
+        tol = 1e-5 * np.maximum(np.abs(g["boxes"][i]), 1.0)
+        cand = [j for j in range(m) if not used[j] and cls[j] == g["class_ids"][i] and (np.abs(boxes[j] - g["boxes"][i]) <= tol).all()]
+        assert cand, f"golden detection {i} has no counterpart"
+        j = min(cand, key=lambda j_: abs(j_ - i))
+        perm[i], used[j] = j, True
+    np.testing.assert_allclose(scores[perm], g["scores"], rtol=2e-6, atol=0)
+    assert (np.diff(scores) <= 0).all()
+    moved = np.nonzero(perm != np.arange(m))[0]
+    assert all(abs(scores[perm[i]] - scores[i]) <= 4e-6 * scores[i] for i in moved), "only near-ties may swap"
+    assert_masks_close(masks[:, :, perm], unpack_masks(g), 1e-3, "masks")
+    inv = np.empty(m, np.int64)
+    inv[perm] = np.arange(m)
+    assert float(np.mean(inv[arg] != g["masks_arg"])) <= 1e-3
+
+
+@pytest.mark.parametrize("name", ["yolact_550_coco", "yolact_550_coco_sparse", "yolact_544_voc_1080p"])
+def test_detect_from_logits_vs_golden(bu, name):
+    """Raw logits in, softmax (nets/yolact.py:204) fused into the score filter: same detections as the reference run on
+    softmax(logits)."""
+    g = load_golden(name)
+    size, c = int(g["input_size"]), int(g["num_classes"])
+    a, p = synth.yolact_dims(size)
+    box, logits, coef, proto = synth.yolact_heads(int(g["seed"]), a, num_classes=c, proto=p, objects=int(g["objects"]),
+                                                  return_logits=True)
+    anchors = torch.from_numpy(O.get_anchors((size, size))).float()
+    res = bu.decode_nms_from_logits((box[None].cuda(), logits[None].cuda(), coef[None].cuda(), proto[None].cuda()), anchors.cuda(),
+                                    float(g["confidence"]), float(g["nms_iou"]), g["image_shape"])
+    _check_logits(g, res)
+
+
+@pytest.mark.parametrize("a,c,bsz", [(601, 21, 5), (130, 7, 3), (19248, 81, 3)])
+def test_detect_from_logits_matches_softmax_path(bu, a, c, bsz):
+    """Odd sizes: rows that are not a multiple of the 128-row tile, images whose byte offset is not 16-byte aligned,
+    a tensor whose last floats lie past the last aligned boundary.  Candidate sets and detections must equal the
+    softmax-input path run on torch.softmax(logits)."""
+    g = torch.Generator().manual_seed(77 + a)
+    per = [synth.yolact_heads(900 + i, a, num_classes=c, proto=40, objects=4, run=20, return_logits=True) for i in range(bsz)]
+    box, logits, coef, proto = (torch.stack([p_[k] for p_ in per]).contiguous().cuda() for k in range(4))
+    anchors = torch.rand(a, 4, generator=g).mul(0.5).add(0.1).cuda()
+    conf = torch.softmax(logits, dim=-1)
+    ref = bu.decode_nms_batch((box, conf, coef, proto), anchors, 0.05, 0.5, (120, 90))
+    got = bu.decode_nms_batch((box, logits, coef, proto), anchors, 0.05, 0.5, (120, 90), logits=True)
+    assert np.array_equal(host(ref.counts), host(got.counts)) and (host(got.counts) > 0).all()
+    for b in range(bsz):
+        m = int(host(ref.counts)[b])
+        rb, rs, rc, rarg, rmask = ref.image(b, m)
+        gb, gs, gc, garg, gmask = got.image(b, m)
+        assert torch.equal(rc, gc)
+        np.testing.assert_allclose(host(gs), host(rs), rtol=2e-6, atol=0)
+        assert torch.equal(rb, gb)
+        assert float((rmask != gmask).float().mean()) <= 1e-3
