@@ -180,11 +180,15 @@ __device__ __forceinline__ void lg_flush(const LgEmit& e, int img, int lane) {  
   __syncwarp();
 }
 
-// One row shared by a lane pair.  `row` is either the shared-memory copy (the normal case; inlined separately so the
-// loads compile to LDS) or, for the tensor's very last rows whose tail the aligned bulk copy could not cover, global.
-__device__ __forceinline__ void lg_row(const float* row, const CandParams& p, int C, int par, bool valid, int img, uint32_t grow,
-                                       const LgEmit& e) {
+// One tile of <= 16 rows, a lane pair per row.  `tile` is either the shared-memory copy (the normal case; inlined
+// separately so the loads compile to LDS) or, for the tensor's very last rows whose tail the aligned bulk copy could
+// not cover, global memory.
+__device__ __forceinline__ void lg_tile(const float* tile, const CandParams& p, int C, int lane, int nr, int img, uint32_t r0,
+                                        const LgEmit& e) {
   const float ninf = -__int_as_float(0x7f800000);
+  const int par = lane & 1;
+  const bool valid = (lane >> 1) < nr;
+  const float* row = tile + (valid ? (lane >> 1) : nr - 1) * C;  // pairs past the last row redo it and flag nothing
   const int cf = p.col0 + ((par - p.col0) & 1);  // first foreground column of this lane's parity
   float m0 = ninf, m1 = ninf;
   int c = cf;
@@ -198,26 +202,37 @@ __device__ __forceinline__ void lg_row(const float* row, const CandParams& p, in
   for (int k = par; k < p.col0; k += 2) mx = fmaxf(mx, row[k]);
   mfg = fmaxf(mfg, __shfl_xor_sync(0xffffffffu, mfg, 1));
   mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
-  // sum of exp(x - max): ex2.approx (2 ulp) on the scaled argument.  Terms that matter to the sum have |x - max| of a few
-  // units, where this is within ~3e-7 of expf; the exact expf is kept for the candidates' own probabilities.
+  // sum of exp(x - max) as ex2.approx(x * log2(e) - max * log2(e)), one FFMA + one MUFU per element.  Terms that matter
+  // to the sum have |x - max| of a few units, where this is within ~3e-7 of expf; the exact expf is kept for the
+  // candidates' own probabilities.
   const float kLog2e = 1.4426950408889634f;
+  const float nm2 = -mx * kLog2e;
   float s0 = 0.0f, s1 = 0.0f;
   c = par;
   for (; c + 2 < C; c += 4) {
-    s0 += exp2f_approx((row[c] - mx) * kLog2e);
-    s1 += exp2f_approx((row[c + 2] - mx) * kLog2e);
+    s0 += exp2f_approx(fmaf(row[c], kLog2e, nm2));
+    s1 += exp2f_approx(fmaf(row[c + 2], kLog2e, nm2));
   }
-  if (c < C) s0 += exp2f_approx((row[c] - mx) * kLog2e);
+  if (c < C) s0 += exp2f_approx(fmaf(row[c], kLog2e, nm2));
   float sum = s0 + s1;
   sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+  // x - max > lim is necessary (with margin) for expf(x - max) / sum > threshold; most rows have no such column.  The
+  // flagged rows are scanned by the whole warp, 32 columns at a time.
   const float lim = p.threshold > 0.0f ? logf(p.threshold * sum) - 1e-4f : ninf;
-  if (valid && mfg - mx > lim) {  // most rows have no candidate at all
-    for (c = cf; c < C; c += 2) {
-      const float d = row[c] - mx;
-      if (!(d > lim)) continue;
-      const float pr = expf(d) / sum;
+  unsigned flagged = __ballot_sync(0xffffffffu, valid && par == 0 && mfg - mx > lim);
+  while (flagged) {
+    const int src = __ffs(flagged) - 1;
+    flagged &= flagged - 1;
+    const float rmx = __shfl_sync(0xffffffffu, mx, src);
+    const float rsum = __shfl_sync(0xffffffffu, sum, src);
+    const float rlim = __shfl_sync(0xffffffffu, lim, src);
+    const float* frow = tile + (src >> 1) * C;
+    for (int k = p.col0 + lane; k < C; k += 32) {
+      const float d = frow[k] - rmx;
+      if (!(d > rlim)) continue;
+      const float pr = expf(d) / rsum;
       if (!(pr > p.threshold)) continue;
-      const uint64_t key = make_cand_key((uint32_t)(c - p.col0), pr, grow);
+      const uint64_t key = make_cand_key((uint32_t)(k - p.col0), pr, r0 + (uint32_t)(src >> 1));
       const int sp = atomicAdd(&e.sg->n, 1);
       if (sp < kLgStage) {
         e.sg->keys[sp] = key;
@@ -255,8 +270,7 @@ candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_
   em.cap = cap;
   em.key_stride = key_stride;
 
-  auto issue = [&](int tile, int stage) {  // lane 0 only
-    const int b = tile / tiles_per_img, t = tile - b * tiles_per_img;
+  auto issue = [&](int b, int t, int stage) {  // lane 0 only; tile t of image b
     const int r0 = t * kLgRows, nr = min(kLgRows, p.rows - r0);
     const int64_t f0 = ((int64_t)b * p.rows + r0) * C, f1 = f0 + (int64_t)nr * C;
     const int64_t a0 = f0 & ~(int64_t)3;                                          // floats, 16-byte boundary below
@@ -270,13 +284,15 @@ candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_
   const int gw = blockIdx.x * kLgWarps + warp, nw = gridDim.x * kLgWarps;
   const int per_warp = (total_tiles + nw - 1) / nw;
   const int first = gw * per_warp, last = min(first + per_warp, total_tiles);
+  int b = first / tiles_per_img, t = first - b * tiles_per_img;  // (image, tile in image), advanced without divisions
   int cur_img = -1;
-  if (lane == 0 && first < last) issue(first, 0);
+  if (lane == 0 && first < last) issue(b, t, 0);
   int it = 0;
   for (int tile = first; tile < last; ++tile, ++it) {
     const int stage = it & 1;
-    if (lane == 0 && tile + 1 < last) issue(tile + 1, stage ^ 1);  // released by the __syncwarp that ended the last tile
-    const int b = tile / tiles_per_img, t = tile - b * tiles_per_img;
+    int nb = b, nt = t + 1;
+    if (nt == tiles_per_img) { nt = 0; ++nb; }
+    if (lane == 0 && tile + 1 < last) issue(nb, nt, stage ^ 1);  // released by the __syncwarp that ended the last tile
     if (b != cur_img) {
       if (cur_img >= 0) lg_flush(em, cur_img, lane);
       cur_img = b;
@@ -286,18 +302,15 @@ candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_
     const int64_t a0 = f0 & ~(int64_t)3;
     const int64_t a1 = min((f0 + (int64_t)nr * C + 3) & ~(int64_t)3, total_floats & ~(int64_t)3);
     const int in_smem = (int)(a1 - f0);  // floats of this tile the bulk copy delivered (all but < 4 at the tensor's end)
-    const int par = lane & 1;
-    const bool valid = (lane >> 1) < nr;
-    const int r = valid ? (lane >> 1) : nr - 1;  // pairs past the image's last row redo it and emit nothing
     mbar_wait(&bars[warp][stage], (it >> 1) & 1);
-    if (nr * C <= in_smem) {
-      const float* tilef = reinterpret_cast<const float*>(wbuf + (size_t)stage * tile_bytes) + (f0 - a0);
-      lg_row(tilef + r * C, p, C, par, valid, b, (uint32_t)(r0 + r), em);
-    } else {
-      lg_row(base + f0 + (int64_t)r * C, p, C, par, valid, b, (uint32_t)(r0 + r), em);
-    }
+    if (nr * C <= in_smem)
+      lg_tile(reinterpret_cast<const float*>(wbuf + (size_t)stage * tile_bytes) + (f0 - a0), p, C, lane, nr, b, (uint32_t)r0, em);
+    else
+      lg_tile(base + f0, p, C, lane, nr, b, (uint32_t)r0, em);
     __syncwarp();
     if (em.sg->n > kLgStage - 32) lg_flush(em, cur_img, lane);  // keep room so that the direct path stays rare
+    b = nb;
+    t = nt;
   }
   if (cur_img >= 0) lg_flush(em, cur_img, lane);
 }
