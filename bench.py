@@ -327,6 +327,31 @@ def run_gpu(args):
     assert np.array_equal(h_counts.numpy(), counts) and np.array_equal(h_map.numpy(), cm_out[3].cpu().numpy())
     cm_d2h = int(h_boxes.numel() * 4 + h_scores.numel() * 4 + h_cls.numel() * 8 + h_map.numel() + h_counts.numel() * 4)
 
+    # ---- COCO RLE of the batch's masks on the device (utils_map.py:33-34 without the 2 GB D2H) -- extra keys only
+    bu.decode_nms_batch(dev_in, anchors_d, CONFIDENCE, NMS_IOU, shape, TOP_K, MAX_DET, out=out)
+    rle_cap = 8 * shape[1] * MAX_DET * bsz
+    rle_out = torch.empty((rle_cap,), dtype=torch.int32, device=dev)
+    rle_cnt = torch.empty((bsz, MAX_DET), dtype=torch.int32, device=dev)
+    rle_off = torch.empty((bsz, MAX_DET), dtype=torch.int64, device=dev)
+    rle_tot = torch.empty((2,), dtype=torch.int64, device=dev)
+
+    def rle():
+        handle.check(handle.lib.isb_rle_encode(handle.ptr, out.masks_raw.data_ptr(), out.masks_raw.shape[1], out.counts.data_ptr(), -1,
+                                               MAX_DET, bsz, shape[0], shape[1], rle_out.data_ptr(), rle_cap, rle_cnt.data_ptr(),
+                                               rle_off.data_ptr(), rle_tot.data_ptr(), stream))
+    for _ in range(3):
+        rle()
+    torch.cuda.synchronize()
+    ev0.record()
+    for _ in range(10):
+        rle()
+    ev1.record()
+    torch.cuda.synchronize()
+    rle_ms = ev0.elapsed_time(ev1) / 10
+    rle_runs = int(rle_tot[1].item())
+    assert rle_runs <= rle_cap
+    del rle_out
+
     # ---- raw-logits variant (F.softmax of nets/yolact.py:204 fused into the score filter) -- extra keys only
     lg = synth.yolact_batch(SEED_BASE + (start % 1000), DISTINCT_IMAGES, a, num_classes=NUM_CLASSES, proto=p, return_logits=True)[1]
     logits_d = lg.repeat((reps, 1, 1)).contiguous().to(dev)
@@ -391,6 +416,10 @@ def run_gpu(args):
                                       "value": bsz * world / (cm_ms * 1e-3), "ms_per_step": cm_ms,
                                       "e2e": bsz * world / cm_e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                                       "d2h_bytes_per_step": cm_d2h, "api": "isb_yolact_class_map[_host]"},
+                "rle_variant": {"what": "COCO RLE (utils_map.py:33-34) of all instance masks of the step on the device "
+                                        "(SURVEY 8f rank 3); not the headline", "ms_per_step": rle_ms, "runs": rle_runs,
+                                "d2h_bytes_instead_of_masks": rle_runs * 4 + bsz * MAX_DET * 12,
+                                "mask_bytes": int(shape[0] * shape[1] * counts.sum())},
                 "from_logits_variant": {"what": "raw class logits in, softmax (nets/yolact.py:204) fused into the score filter "
                                                 "(SURVEY 8f rank 2); not the headline",
                                         "value": bsz / (lg_ms * 1e-3), "ms_per_step": lg_ms, "unit": UNIT + " (this rank)",

@@ -142,6 +142,27 @@ ISB_API int isb_yolact_class_map(isb_handle* h, const isb_yolact_in* in, const i
 ISB_API int isb_yolact_class_map_host(isb_handle* h, const isb_yolact_in* in, const isb_yolact_map_out* out, isb_stream stream);
 
 /* ------------------------------------------------------------------------------------
+ * COCO run-length encoding of the instance masks on the device.
+ * Replaces the per-instance host call inst_model/yolact/utils/utils_map.py:33-34
+ *     pycocotools.mask.encode(np.asfortranarray(segmentation.astype(np.uint8)))
+ * (driven by prep_metrics :56-62) -- third-party cocoapi maskApi.c rleEncode: column-major scan,
+ * `counts` = lengths of the alternating runs starting with a (possibly empty) run of zeros.
+ *   masks: the layout isb_yolact_detect writes (B slots, bool [H,W,m_b], m innermost);
+ *   counts: device [B] m_b (as written by detect), or NULL and m_fixed for every image;
+ *   rle_counts: flat device buffer of `capacity` uint32; detection (b, j) owns
+ *     rle_counts[run_offset[b*max_det+j] .. + run_count[b*max_det+j]);  run_count 0 = no such detection;
+ *   totals: device int64[2] = {boundaries, runs}; totals[1] > capacity means the buffer was too small
+ *     (nothing is written past it) -- call again with a larger one.
+ * ---------------------------------------------------------------------------------- */
+ISB_API int isb_rle_encode(isb_handle* h, const uint8_t* masks, int64_t mask_slot_bytes, const int32_t* counts, int32_t m_fixed,
+                           int32_t max_det, int32_t batch, int32_t hgt, int32_t wid, uint32_t* rle_counts, int64_t capacity,
+                           int32_t* run_count, int64_t* run_offset, int64_t* totals, isb_stream stream);
+
+/* HOST helper (no GPU work): the ASCII string pycocotools stores in rle['counts'] (maskApi.c rleToString) for one
+ * instance's `n` counts.  Returns the length written, -1 on bad arguments, -2 if out_cap is too small. */
+ISB_API int64_t isb_rle_to_string(const uint32_t* counts, int64_t n, char* out, int64_t out_cap);
+
+/* ------------------------------------------------------------------------------------
  * Stage entry points (known-answer tests call these one by one; BBoxUtility's public
  * helper methods map onto them).
  * ---------------------------------------------------------------------------------- */

@@ -16,7 +16,7 @@ ISB_OK, ISB_ERR_BAD_ARG, ISB_ERR_CUDA, ISB_ERR_LIMIT, ISB_ERR_OVERFLOW = 0, -1, 
 SYMBOLS = (
     "isb_version", "isb_create", "isb_destroy", "isb_last_error", "isb_workspace_bytes", "isb_launch_count",
     "isb_profile_begin", "isb_profile_read",
-    "isb_yolact_detect", "isb_yolact_detect_host", "isb_yolact_class_map", "isb_yolact_class_map_host", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
+    "isb_yolact_detect", "isb_yolact_detect_host", "isb_yolact_class_map", "isb_yolact_class_map_host", "isb_rle_encode", "isb_rle_to_string", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
     "isb_traditional_nms", "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_assemble",
     "isb_box_decode", "isb_nms", "isb_batched_nms", "isb_ms_roi_align", "isb_mask_select_sigmoid", "isb_resize_boxes",
     "isb_paste_masks", "isb_paste_class_map", "isb_rpn_filter", "isb_box_postprocess",
@@ -91,6 +91,9 @@ def load():
         lib.isb_yolact_detect_host.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactOut), vp]
         lib.isb_yolact_class_map.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactMapOut), vp]
         lib.isb_yolact_class_map_host.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactMapOut), vp]
+        lib.isb_rle_encode.argtypes = [vp, vp, i64, vp, i32, i32, i32, i32, i32, vp, i64, vp, vp, vp, vp]
+        lib.isb_rle_to_string.argtypes = [vp, i64, vp, i64]
+        lib.isb_rle_to_string.restype = i64
         lib.isb_decode_boxes.argtypes = [vp, vp, vp, i64, f32, f32, vp, vp]
         lib.isb_jaccard.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp, vp]
         lib.isb_fast_nms.argtypes = [vp, vp, vp, vp, i32, i32, i32, f32, i32, i32, vp, vp, vp, vp, vp, vp]

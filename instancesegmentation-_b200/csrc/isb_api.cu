@@ -77,6 +77,7 @@ static void free_ws(isb_handle* h) {
     if (h->lane_event[l]) cudaEventDestroy(h->lane_event[l]);
   }
   if (h->fork_event) cudaEventDestroy(h->fork_event);
+  cudaFree(h->rle_scratch);
   cudaFree(h->cand_count);
   cudaFree(h->work_counter);
   cudaFree(h->cand_keys);

@@ -281,6 +281,8 @@ struct isb_handle {
   int64_t launches;
   size_t ws_bytes;
   // workspace (device)
+  void* rle_scratch;     // run-length encoding scratch (grown on demand)
+  size_t rle_bytes;
   int32_t* cand_count;   // [max_batch]
   int32_t* work_counter; // [1] dynamic work counter of the mask kernel
   uint64_t* cand_keys;   // [max_batch][cand_cap_pow2]

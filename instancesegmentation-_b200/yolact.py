@@ -306,6 +306,51 @@ class BBoxUtility(object):
             m = int(res.counts[0].item())
         return res.image(0, m)
 
+    # ------------------------------------------------------------------ utils_map.py:33-34
+    def rle_counts(self, masks):
+        """Run lengths of every instance mask, computed on the device: masks bool/uint8 [H,W,m] (what decode_nms returns)
+        -> list of m int64 numpy arrays, each the `counts` of pycocotools' uncompressed RLE (column-major, zeros first)."""
+        if not masks.is_cuda:
+            raise RuntimeError("isb.yolact: CUDA tensors only (no CPU fallback)")
+        dev = masks.device
+        hgt, wid, m = (int(v) for v in masks.shape)
+        if m == 0:
+            return []
+        raw = masks.contiguous().view(torch.uint8)
+        h = get_handle(dev.index)
+        run_count = torch.empty((m,), dtype=torch.int32, device=dev)
+        run_off = torch.empty((m,), dtype=torch.int64, device=dev)
+        totals = torch.empty((2,), dtype=torch.int64, device=dev)
+        cap = max(4096, 8 * wid * m)  # a blob crosses a column twice; grown below if the masks are busier
+        while True:
+            out = torch.empty((cap,), dtype=torch.int32, device=dev)
+            with torch.cuda.device(dev):
+                h.check(h.lib.isb_rle_encode(h.ptr, raw.data_ptr(), raw.numel(), None, m, m, 1, hgt, wid, out.data_ptr(), cap,
+                                             run_count.data_ptr(), run_off.data_ptr(), totals.data_ptr(), _stream(dev)))
+            need = int(totals[1].item())
+            if need <= cap:
+                break
+            cap = need
+        flat = out[:need].cpu().numpy().view("uint32")
+        cnt, off = run_count.cpu().numpy(), run_off.cpu().numpy()
+        return [flat[off[j]:off[j] + cnt[j]].astype("int64") for j in range(m)]
+
+    def rle_encode(self, masks):
+        """`pycocotools.mask.encode(np.asfortranarray(masks))` (utils_map.py:34) for decode_nms' bool [H,W,m] masks without
+        copying them to the host: list of {'size': [H, W], 'counts': bytes}, one per instance."""
+        import numpy as np
+        hgt, wid = int(masks.shape[0]), int(masks.shape[1])
+        lib = get_handle(masks.device.index).lib
+        res = []
+        for cnts in self.rle_counts(masks):
+            c32 = np.ascontiguousarray(cnts.astype(np.uint32))
+            buf = C.create_string_buffer(7 * len(c32) + 8)
+            n = lib.isb_rle_to_string(c32.ctypes.data_as(C.c_void_p), len(c32), buf, len(buf))
+            if n < 0:
+                raise RuntimeError("isb_rle_to_string failed (%d)" % n)
+            res.append({"size": [hgt, wid], "counts": buf.raw[:n]})
+        return res
+
     # ------------------------------------------------------------------ utils_bbox.py:170
     def decode_nms(self, outputs, anchors, confidence, nms_iou, image_shape, traditional_nms=False, max_detections=100):
         if traditional_nms:

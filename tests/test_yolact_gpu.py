@@ -406,3 +406,66 @@ def test_detect_from_logits_matches_softmax_path(bu, a, c, bsz):
         np.testing.assert_allclose(host(gs), host(rs), rtol=2e-6, atol=0)
         assert torch.equal(rb, gb)
         assert float((rmask != gmask).float().mean()) <= 1e-3
+
+
+# ------------------------------------------------------------------------------- COCO RLE
+def test_rle_encode_vs_oracle(bu):
+    """utils_map.py:33-34 on the device: counts and strings equal the restated cocoapi algorithm, and decode back to the
+    masks (round trip) -- on real decode_nms output, on degenerate masks and on a busy random one (capacity regrowth)."""
+    from oracle import rle_np as RL
+    g = load_golden("yolact_550_coco_sparse")
+    (box, conf, coef, proto), anchors = _full_inputs(g)
+    res = bu.decode_nms((box[None].cuda(), conf[None].cuda(), coef[None].cuda(), proto[None].cuda()), anchors.cuda(),
+                        float(g["confidence"]), float(g["nms_iou"]), g["image_shape"])
+    masks = res[4]
+    hm = host(masks)
+    enc = bu.rle_encode(masks)
+    assert len(enc) == hm.shape[2]
+    for j, e in enumerate(enc):
+        assert e["size"] == [hm.shape[0], hm.shape[1]]
+        assert e["counts"] == RL.rle_to_string(RL.rle_counts(hm[:, :, j]))
+        assert np.array_equal(RL.rle_decode(RL.rle_from_string(e["counts"]), hm.shape[0], hm.shape[1]), hm[:, :, j])
+    rng = np.random.default_rng(5)
+    odd = np.zeros((37, 53, 5), bool)
+    odd[:, :, 1] = True                                  # all ones -> [0, HW]
+    odd[:, :, 2] = rng.random((37, 53)) > 0.5            # salt and pepper: ~HW/2 runs, forces the capacity to grow
+    odd[0, 0, 3] = True                                  # first pixel set -> leading zero-length run
+    odd[-1, -1, 4] = True                                # last pixel
+    got = bu.rle_counts(torch.from_numpy(odd).cuda())
+    for j in range(5):
+        assert got[j].tolist() == RL.rle_counts(odd[:, :, j]).tolist()
+    assert got[0].tolist() == [37 * 53] and got[1].tolist() == [0, 37 * 53]
+
+
+def test_rle_encode_batch_with_device_counts(bu):
+    """The batched entry point on decode_nms_batch's slots and device-side counts (ragged m per image, one empty image)."""
+    import ctypes as C
+    from isb import _lib
+    from oracle import rle_np as RL
+    a, p = synth.yolact_dims(550)
+    anchors = torch.from_numpy(O.get_anchors((550, 550))).float()
+    box, conf, coef, proto = synth.yolact_batch(2300, 3, a, num_classes=81, proto=p, objects=2)
+    conf[1] = conf[1] * 0.0 + 0.001
+    res = bu.decode_nms_batch((box.cuda(), conf.cuda(), coef.cuda(), proto.cuda()), anchors.cuda(), 0.3, 0.5, (550, 550), max_detections=40)
+    counts = host(res.counts)
+    assert counts[1] == 0 and counts[0] > 0 and counts[2] > 0
+    bsz, d, cap = 3, 40, 1 << 20
+    out = torch.empty((cap,), dtype=torch.int32, device="cuda")
+    rc = torch.empty((bsz, d), dtype=torch.int32, device="cuda")
+    ro = torch.empty((bsz, d), dtype=torch.int64, device="cuda")
+    tot = torch.empty((2,), dtype=torch.int64, device="cuda")
+    h = _lib.get_handle(0)
+    h.check(h.lib.isb_rle_encode(h.ptr, res.masks_raw.data_ptr(), res.masks_raw.shape[1], res.counts.data_ptr(), -1, d, bsz, 550, 550,
+                                 out.data_ptr(), cap, rc.data_ptr(), ro.data_ptr(), tot.data_ptr(), None))
+    torch.cuda.synchronize()
+    flat, rc, ro = host(out).view(np.uint32), host(rc), host(ro)
+    assert int(host(tot)[1]) == int(rc.sum()) <= cap
+    for b in range(bsz):
+        m = int(counts[b])
+        assert (rc[b, m:] == 0).all()
+        if m == 0:
+            continue
+        masks = host(res.image(b, m)[4])
+        for j in range(m):
+            got = flat[ro[b, j]:ro[b, j] + rc[b, j]]
+            assert got.tolist() == RL.rle_counts(masks[:, :, j]).tolist()
