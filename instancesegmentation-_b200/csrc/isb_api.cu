@@ -78,6 +78,7 @@ static void free_ws(isb_handle* h) {
   }
   if (h->fork_event) cudaEventDestroy(h->fork_event);
   cudaFree(h->rle_scratch);
+  cudaFree(h->fnms_cls);
   cudaFree(h->cand_count);
   cudaFree(h->work_counter);
   cudaFree(h->cand_keys);
@@ -515,6 +516,8 @@ extern "C" int isb_fast_nms(isb_handle* h, const float* box, const float* scores
   np.out_class = out_class;
   np.out_coef = out_coef;
   np.out_count = count;
+  // one image whose candidates do not fit the single-CTA kernel's shared memory: spread the work over the GPU
+  if ((int64_t)n * num_fg_classes > fast_nms_smem_candidates()) return launch_fast_nms_wide(h, np, n * num_fg_classes, s);
   return launch_fast_nms(h, np, s);
 }
 

@@ -281,6 +281,7 @@ struct isb_handle {
   int64_t launches;
   size_t ws_bytes;
   // workspace (device)
+  int32_t* fnms_cls;     // wide Fast NMS: class-start table + kept counter
   void* rle_scratch;     // run-length encoding scratch (grown on demand)
   size_t rle_bytes;
   int32_t* cand_count;   // [max_batch]
@@ -375,6 +376,9 @@ struct NmsParams {
   int32_t* out_count;      // [B]
 };
 int launch_fast_nms(isb_handle* h, const NmsParams& p, cudaStream_t s);
+// one image, n candidates known on the host, spread over the GPU (n > fast_nms_smem_candidates())
+int launch_fast_nms_wide(isb_handle* h, const NmsParams& p, int n, cudaStream_t s);
+int fast_nms_smem_candidates();
 
 struct MaskParams {
   int32_t batch;

@@ -123,6 +123,59 @@ __device__ __forceinline__ float4 load_box(const NmsParams& p, int b, uint32_t r
   return decode_box(pr, an, 0.1f, 0.2f);
 }
 
+// Outputs of one image (step 5 of fast_nms_kernel, shared with the wide path): boxes (rescaled / clamped when asked),
+// scores, class ids, coefficient rows, and for the mask kernels the detection records + sigmoid-map offsets.
+// Whole CTA (kNmsThreads); dkeys = sorted kept keys, m <= max_det <= kNmsThreads of them.
+__device__ __forceinline__ void fnms_emit(const NmsParams& p, int b, const uint64_t* dkeys, int m, float* __restrict__ det_coef_ws,
+                                          DetRec* __restrict__ det_rec_ws, int32_t* __restrict__ smap_total_ws, int ws_det_stride,
+                                          int* s_scan) {
+  const int tid = threadIdx.x;
+  const float wf = (float)p.out_w, hf = (float)p.out_h;
+  const float sy = (float)p.proto_h / hf, sx = (float)p.proto_w / wf;
+  for (int d0 = 0; d0 < m; d0 += kNmsThreads) {  // max_det <= 1024: one trip
+    const int d = d0 + tid;
+    DetRec rc;
+    int items = 0;
+    if (d < m) {
+      const uint64_t k = dkeys[d];
+      const uint32_t row = det_row(k);
+      float4 bx = load_box(p, b, row);
+      if (p.correct) {
+        bx = correct_box(bx, wf, hf);
+        DetBounds db;
+        crop_range(bx.x, bx.z, p.out_w, db.xlo, db.xhi);
+        crop_range(bx.y, bx.w, p.out_h, db.ylo, db.yhi);
+        int pa, pya, fw, fh;
+        det_footprint(db, sy, sx, p.proto_h, p.proto_w, pa, pya, fw, fh);
+        rc.xlo = db.xlo; rc.xhi = db.xhi; rc.ylo = db.ylo; rc.yhi = db.yhi;
+        rc.pa = (int16_t)pa; rc.pya = (int16_t)pya; rc.fw = (int16_t)fw; rc.fh = (int16_t)fh;
+        rc.j = d;
+        items = fw * fh;
+      }
+      reinterpret_cast<float4*>(p.out_box)[(size_t)b * p.max_det + d] = bx;
+      p.out_score[(size_t)b * p.max_det + d] = det_score(k);
+      p.out_class[(size_t)b * p.max_det + d] = (int64_t)det_class(k);
+    }
+    if (p.correct) {  // offsets of the detections' sigmoid maps in the per-image scratch (mask kernels)
+      int total;
+      rc.soff = cta_exclusive_scan(items, s_scan, &total);
+      if (d < m) det_rec_ws[(size_t)b * ws_det_stride + d] = rc;
+      if (tid == 0) smap_total_ws[b] = total;  // max_det <= 1024: the single trip's total is the image's
+    }
+  }
+  // coefficient rows: one warp-quarter (8 lanes x float4) per detection
+  {
+    float* dst_base = p.out_coef ? p.out_coef + (size_t)b * p.max_det * ISB_NUM_COEF
+                                 : det_coef_ws + (size_t)b * ws_det_stride * ISB_NUM_COEF;
+    for (int t = tid; t < m * 8; t += kNmsThreads) {
+      int d = t >> 3, q = t & 7;
+      const uint32_t row = det_row(dkeys[d]);
+      const float4* src = reinterpret_cast<const float4*>(p.coef + ((size_t)b * p.rows + row) * ISB_NUM_COEF);
+      reinterpret_cast<float4*>(dst_base + (size_t)d * ISB_NUM_COEF)[q] = src[q];
+    }
+  }
+}
+
 __global__ void __launch_bounds__(kNmsThreads, 1)
 fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* __restrict__ g_keys,
                 uint64_t* __restrict__ g_det, float4* __restrict__ g_box, int64_t cap, int64_t stride,
@@ -252,53 +305,133 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
   const int m = min(kept, p.max_det);
 
   // ---- 5. outputs -----------------------------------------------------------------------
-  const float wf = (float)p.out_w, hf = (float)p.out_h;
-  const float sy = (float)p.proto_h / hf, sx = (float)p.proto_w / wf;
-  for (int d0 = 0; d0 < m; d0 += kNmsThreads) {  // max_det <= 1024: one trip
-    const int d = d0 + tid;
-    DetRec rc;
-    int items = 0;
-    if (d < m) {
-      const uint64_t k = dkeys[d];
-      const uint32_t row = det_row(k);
-      float4 bx = load_box(p, b, row);
-      if (p.correct) {
-        bx = correct_box(bx, wf, hf);
-        DetBounds db;
-        crop_range(bx.x, bx.z, p.out_w, db.xlo, db.xhi);
-        crop_range(bx.y, bx.w, p.out_h, db.ylo, db.yhi);
-        int pa, pya, fw, fh;
-        det_footprint(db, sy, sx, p.proto_h, p.proto_w, pa, pya, fw, fh);
-        rc.xlo = db.xlo; rc.xhi = db.xhi; rc.ylo = db.ylo; rc.yhi = db.yhi;
-        rc.pa = (int16_t)pa; rc.pya = (int16_t)pya; rc.fw = (int16_t)fw; rc.fh = (int16_t)fh;
-        rc.j = d;
-        items = fw * fh;
-      }
-      reinterpret_cast<float4*>(p.out_box)[(size_t)b * p.max_det + d] = bx;
-      p.out_score[(size_t)b * p.max_det + d] = det_score(k);
-      p.out_class[(size_t)b * p.max_det + d] = (int64_t)det_class(k);
-    }
-    if (p.correct) {  // offsets of the detections' sigmoid maps in the per-image scratch (mask kernels)
-      int total;
-      rc.soff = cta_exclusive_scan(items, s_scan, &total);
-      if (d < m) det_rec_ws[(size_t)b * ws_det_stride + d] = rc;
-      if (tid == 0) smap_total_ws[b] = total;  // max_det <= 1024: the single trip's total is the image's
-    }
-  }
-  // coefficient rows: one warp-quarter (8 lanes x float4) per detection
-  {
-    float* dst_base = p.out_coef ? p.out_coef + (size_t)b * p.max_det * ISB_NUM_COEF
-                                 : det_coef_ws + (size_t)b * ws_det_stride * ISB_NUM_COEF;
-    for (int t = tid; t < m * 8; t += kNmsThreads) {
-      int d = t >> 3, q = t & 7;
-      const uint32_t row = det_row(dkeys[d]);
-      const float4* src = reinterpret_cast<const float4*>(p.coef + ((size_t)b * p.rows + row) * ISB_NUM_COEF);
-      reinterpret_cast<float4*>(dst_base + (size_t)d * ISB_NUM_COEF)[q] = src[q];
-    }
-  }
+  fnms_emit(p, b, dkeys, m, det_coef_ws, det_rec_ws, smap_total_ws, ws_det_stride, s_scan);
   if (tid == 0) p.out_count[b] = m;
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Wide path for ONE image with many candidates (BASELINE configs[4], VerSeg: 5000 boxes of one class, top_k 5000,
+// max_det 1024).  fast_nms_kernel gives an image to a single CTA, which for n > kSmemCand sorts in global memory and
+// walks n^2 / 2 box pairs alone (4.9 ms for n = 5000).  Here the same steps are spread over the GPU: multi-CTA bitonic
+// sort of the keys, boxes + class starts, pair tests with 32 candidates per CTA, sort of the kept keys, emit.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void fnms_fill_kernel(uint64_t* __restrict__ keys, int from, int to, int32_t* __restrict__ zero) {
+  for (int i = from + blockIdx.x * blockDim.x + threadIdx.x; i < to; i += gridDim.x * blockDim.x) keys[i] = kPadKey;
+  if (zero && blockIdx.x == 0 && threadIdx.x == 0) *zero = 0;
+}
+
+__global__ void fnms_prepare_kernel(NmsParams p, const uint64_t* __restrict__ keys, int n, float4* __restrict__ cbox,
+                                    int32_t* __restrict__ cls_start) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint64_t k = keys[i];
+    cbox[i] = load_box(p, 0, cand_row(k));
+    const uint32_t c = cand_class(k);
+    if (i == 0 || cand_class(keys[i - 1]) != c) cls_start[c] = i;
+  }
+}
+
+constexpr int kWideThreads = 256;  // 8 candidates per CTA, one warp each
+
+// utils_bbox.py:38-47 + :86 for one pair: does box i (higher ranked) suppress box j?  The division is skipped when the
+// boxes are disjoint: 0 / union is +-0 for every finite non-zero union, and the caller established 0 <= nms_iou.
+__device__ __forceinline__ bool fnms_suppresses(float4 bi, float4 bj, float aj, float thr) {
+  const float dx = fmaxf(fminf(bi.z, bj.z) - fmaxf(bi.x, bj.x), 0.0f);
+  const float dy = fmaxf(fminf(bi.w, bj.w) - fmaxf(bi.y, bj.y), 0.0f);
+  const float inter = dx * dy;
+  const float uni = (box_area(bi) + aj) - inter;
+  if (inter == 0.0f && uni != 0.0f && fabsf(uni) <= 3.402823466e38f) return false;
+  return !(inter / uni <= thr);
+}
+
+// A WARP per candidate j, four independent box loads in flight per lane: with thousands of predecessors per candidate
+// (one class, VerSeg) an 8-lane group with one load in flight spent ~100 us waiting on L2.
+__global__ void __launch_bounds__(kWideThreads)
+fnms_pairs_kernel(NmsParams p, const uint64_t* __restrict__ keys, const float4* __restrict__ cbox,
+                  const int32_t* __restrict__ cls_start, int n, uint64_t* __restrict__ dkeys, int32_t* __restrict__ kept) {
+  const int lane = threadIdx.x & 31;
+  const bool thr_ok = 0.0f <= p.nms_iou;
+  // the longest lists (highest j of a class) first: they decide when the kernel ends
+  const int j = n - 1 - (blockIdx.x * (kWideThreads / 32) + (threadIdx.x >> 5));
+  if (j < 0) return;  // warp-uniform
+  const uint64_t kj = keys[j];
+  const int start = cls_start[cand_class(kj)];
+  bool bad = !(thr_ok && (j - start) < p.top_k);
+  if (!bad) {
+    const float4 bj = cbox[j];
+    const float aj = box_area(bj);
+    for (int i0 = start; i0 < j; i0 += 128) {
+      float4 bb[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + 32 * u + lane;
+        bb[u] = cbox[i < j ? i : j];
+      }
+      bool hit = false;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) hit |= (i0 + 32 * u + lane < j) && fnms_suppresses(bb[u], bj, aj, p.nms_iou);
+      if (__any_sync(0xffffffffu, hit)) { bad = true; break; }
+    }
+  }
+  if (lane == 0 && !bad) dkeys[atomicAdd(kept, 1)] = det_key_from_cand(kj);
+}
+
+__global__ void __launch_bounds__(kNmsThreads, 1)
+fnms_emit_kernel(NmsParams p, const uint64_t* __restrict__ dkeys, const int32_t* __restrict__ kept, float* __restrict__ det_coef_ws,
+                 DetRec* __restrict__ det_rec_ws, int32_t* __restrict__ smap_total_ws, int ws_det_stride) {
+  __shared__ int s_scan[32];
+  const int m = min(*kept, p.max_det);
+  fnms_emit(p, 0, dkeys, m, det_coef_ws, det_rec_ws, smap_total_ws, ws_det_stride, s_scan);
+  if (threadIdx.x == 0) p.out_count[0] = m;
+}
+
+int launch_fast_nms_wide(isb_handle* h, const NmsParams& p, int n, cudaStream_t s) {
+  if (p.batch != 1) ISB_FAIL(h, ISB_ERR_BAD_ARG, "wide Fast NMS handles one image");
+  const size_t b0 = (size_t)h->ws_b0, cap2 = (size_t)h->cand_cap_pow2;
+  const int np2 = max(64, next_pow2(n));
+  if ((size_t)np2 > cap2) ISB_FAIL(h, ISB_ERR_LIMIT, "wide Fast NMS: %d candidates exceed the key buffer", n);
+  uint64_t* keys = h->cand_keys + b0 * cap2;
+  uint64_t* dkeys = h->det_keys + b0 * cap2;
+  float4* cbox = h->cand_box + b0 * cap2;
+  if (!h->fnms_cls) ISB_CUDA(h, cudaMalloc((void**)&h->fnms_cls, sizeof(int32_t) * ((1 << kClassBits) + 1)));
+  int32_t* cls_start = h->fnms_cls;
+  int32_t* kept = h->fnms_cls + (1 << kClassBits);
+  int rc;
+  float* coef_ws = h->det_coef + b0 * h->lim.max_det * ISB_NUM_COEF;
+  DetRec* rec_ws = h->det_rec + b0 * h->lim.max_det;
+  const int pair_grid = (n + kWideThreads / 32 - 1) / (kWideThreads / 32);
+  if (n <= kRankSortMax) {
+    // counting rank sorts (multi-CTA, two launches each); the box buffer doubles as their int32 rank scratch while it
+    // holds no boxes.  keys -> sorted in dkeys -> boxes -> kept keys back into `keys` -> sorted in dkeys -> emit.
+    int32_t* rank = reinterpret_cast<int32_t*>(cbox);
+    if ((rc = launch_rank_sort_u64(h, keys, n, nullptr, rank, dkeys, s)) != ISB_OK) return rc;
+    fnms_prepare_kernel<<<(n + 255) / 256, 256, 0, s>>>(p, dkeys, n, cbox, cls_start);
+    ISB_LAUNCH_CHECK(h, "fnms_prepare_kernel");
+    fnms_fill_kernel<<<1, 32, 0, s>>>(keys, 0, 0, kept);  // kept = 0
+    ISB_LAUNCH_CHECK(h, "fnms_fill_kernel");
+    fnms_pairs_kernel<<<pair_grid, kWideThreads, 0, s>>>(p, dkeys, cbox, cls_start, n, keys, kept);
+    ISB_LAUNCH_CHECK(h, "fnms_pairs_kernel");
+    if ((rc = launch_rank_sort_u64(h, keys, n, kept, rank, dkeys, s)) != ISB_OK) return rc;
+    fnms_emit_kernel<<<1, kNmsThreads, 0, s>>>(p, dkeys, kept, coef_ws, rec_ws, h->smap_total + b0, h->lim.max_det);
+    ISB_LAUNCH_CHECK(h, "fnms_emit_kernel");
+    return ISB_OK;
+  }
+  fnms_fill_kernel<<<8, 256, 0, s>>>(keys, n, np2, nullptr);
+  ISB_LAUNCH_CHECK(h, "fnms_fill_kernel");
+  if ((rc = launch_sort_u64(h, keys, np2, s)) != ISB_OK) return rc;
+  fnms_prepare_kernel<<<(n + 255) / 256, 256, 0, s>>>(p, keys, n, cbox, cls_start);
+  ISB_LAUNCH_CHECK(h, "fnms_prepare_kernel");
+  fnms_fill_kernel<<<(np2 + 255) / 256, 256, 0, s>>>(dkeys, 0, np2, kept);
+  ISB_LAUNCH_CHECK(h, "fnms_fill_kernel");
+  fnms_pairs_kernel<<<pair_grid, kWideThreads, 0, s>>>(p, keys, cbox, cls_start, n, dkeys, kept);
+  ISB_LAUNCH_CHECK(h, "fnms_pairs_kernel");
+  if ((rc = launch_sort_u64(h, dkeys, np2, s)) != ISB_OK) return rc;
+  fnms_emit_kernel<<<1, kNmsThreads, 0, s>>>(p, dkeys, kept, coef_ws, rec_ws, h->smap_total + b0, h->lim.max_det);
+  ISB_LAUNCH_CHECK(h, "fnms_emit_kernel");
+  return ISB_OK;
+}
+
+int fast_nms_smem_candidates() { return kSmemCand; }
 
 int configure_fast_nms(isb_handle* h) {
   ISB_CUDA(h, cudaFuncSetAttribute(fast_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kNmsSmem));

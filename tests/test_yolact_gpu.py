@@ -469,3 +469,34 @@ def test_rle_encode_batch_with_device_counts(bu):
         for j in range(m):
             got = flat[ro[b, j]:ro[b, j] + rc[b, j]]
             assert got.tolist() == RL.rle_counts(masks[:, :, j]).tolist()
+
+
+def test_assemble_masks_verseg_many_detections(bu):
+    """configs[4] shape of the problem at a size the oracle finishes quickly: ~1000 small overlapping detections (the compose
+    kernel then runs with a long detection list and few warps) on full-size prototypes."""
+    box, score, coef = synth.verseg_boxes(5003, 1024)
+    gen = torch.Generator().manual_seed(5004)
+    proto = torch.relu(torch.randn(138, 138, 32, generator=gen))
+    shape = (160, 130)
+    boxes = O.yolact_correct_boxes(box.numpy(), shape)
+    arg_ref, m_ref = O.assemble_masks(proto.numpy(), coef.numpy(), boxes, shape)
+    arg, mk = bu.assemble_masks(proto.cuda(), coef.cuda(), dev(boxes), shape)
+    assert tuple(mk.shape) == (160, 130, 1024)
+    assert_masks_close(host(mk), m_ref, 1e-3, "masks")
+    assert float(np.mean(host(arg) != arg_ref)) <= 2e-3
+
+
+@pytest.mark.parametrize("n,c,top_k,max_det", [(5000, 1, 5000, 1024), (3000, 4, 200, 100), (40000, 1, 300, 64)])
+def test_fast_nms_wide_path_vs_oracle(bu, n, c, top_k, max_det):
+    """More candidates than the single-CTA kernel holds in shared memory: the multi-CTA path (rank-sort variant up to 32768
+    keys, bitonic above) must give the oracle's detections bit for bit."""
+    g = torch.Generator().manual_seed(n + c)
+    ctr = torch.rand(n, 2, generator=g)
+    wh = torch.rand(n, 2, generator=g) * 0.05 + 0.01
+    box = torch.cat([ctr - wh / 2, ctr + wh / 2], 1).contiguous()
+    score = torch.rand(n, c, generator=g).contiguous()
+    coef = torch.tanh(torch.randn(n, 32, generator=g))
+    rb, rs, rc_, rk = O.fast_non_max_suppression(box.numpy(), score.numpy(), coef.numpy(), 0.5, top_k, max_det)
+    b, s, cls, k = bu.fast_non_max_suppression(box.cuda(), score.cuda(), coef.cuda(), 0.5, top_k, max_det)
+    assert np.array_equal(host(s), rs) and np.array_equal(host(cls), rc_)
+    assert np.array_equal(host(b), rb) and np.array_equal(host(k), rk)
