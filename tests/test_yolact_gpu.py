@@ -500,3 +500,51 @@ def test_fast_nms_wide_path_vs_oracle(bu, n, c, top_k, max_det):
     b, s, cls, k = bu.fast_non_max_suppression(box.cuda(), score.cuda(), coef.cuda(), 0.5, top_k, max_det)
     assert np.array_equal(host(s), rs) and np.array_equal(host(cls), rc_)
     assert np.array_equal(host(b), rb) and np.array_equal(host(k), rk)
+
+
+# ------------------------------------------------------------------------------- error convention
+def test_error_convention(bu):
+    """int status < 0 + isb_last_error text, nothing launched, handle usable afterwards; "no detections" is a value."""
+    import ctypes as C
+    from isb import _lib
+    h = _lib.Handle(0, max_batch=2, max_anchors=64, max_classes=4, max_det=8, max_top_k=16, cand_capacity=256)
+    try:
+        f = torch.zeros(64, device="cuda")
+        P = lambda t: C.c_void_p(t.data_ptr())
+        box, conf, coef = torch.zeros(1, 64, 4, device="cuda"), torch.zeros(1, 64, 5, device="cuda"), torch.zeros(1, 64, 32, device="cuda")
+        proto, anchors = torch.zeros(1, 8, 8, 32, device="cuda"), torch.rand(64, 4, device="cuda")
+        ob, os_, oc = torch.empty(1, 8, 4, device="cuda"), torch.empty(1, 8, device="cuda"), torch.empty(1, 8, dtype=torch.int64, device="cuda")
+        arg = torch.empty(1, 16, 16, dtype=torch.int64, device="cuda")
+        slot = 16 * 16 * 8
+        masks, cnt = torch.empty(1, slot, dtype=torch.uint8, device="cuda"), torch.full((1,), 7, dtype=torch.int32, device="cuda")
+
+        def call(**kw):
+            a = dict(batch=1, a=64, c=5, k=32, ph=8, pw=8, oh=16, ow=16, box=P(box), conf=P(conf), coef=P(coef), proto=P(proto),
+                     anchors=P(anchors), thr=0.5, iou=0.5, top_k=16, max_det=8, masks=P(masks), slot=slot)
+            a.update(kw)
+            pin = _lib.YolactIn(a["batch"], a["a"], a["c"], a["k"], a["ph"], a["pw"], a["oh"], a["ow"], a["box"], a["conf"], a["coef"],
+                                a["proto"], a["anchors"], a["thr"], a["iou"], a["top_k"], a["max_det"], 0)
+            pout = _lib.YolactOut(P(ob), P(os_), P(oc), P(arg), a["masks"], a["slot"], P(cnt))
+            return h.lib.isb_yolact_detect(h.ptr, C.byref(pin), C.byref(pout), None)
+
+        n0 = h.launch_count
+        cases = [(dict(box=None), _lib.ISB_ERR_BAD_ARG if hasattr(_lib, "ISB_ERR_BAD_ARG") else -1),      # null input
+                 (dict(k=16), -1),                                                                             # wrong coefficient count
+                 (dict(slot=slot - 16), -1),                                                                   # slot too small
+                 (dict(proto=C.c_void_p(proto.data_ptr() + 4)), -1),                                           # misaligned
+                 (dict(batch=3), -3), (dict(a=65), -3), (dict(c=6), -3), (dict(max_det=9), -3), (dict(top_k=17), -3)]
+        for kw, want in cases:
+            rc = call(**kw)
+            assert rc == want, (kw, rc)
+            assert len(h.lib.isb_last_error(h.ptr)) > 0
+        assert h.launch_count == n0, "a rejected call must not launch anything"
+        # all-zero scores: a valid call, zero detections, status OK
+        assert call() == 0
+        torch.cuda.synchronize()
+        assert int(cnt[0]) == 0
+        # stage entry points
+        assert h.lib.isb_decode_boxes(h.ptr, None, P(f), 4, 0.1, 0.2, P(f), None) == -1
+        assert h.lib.isb_fast_nms(h.ptr, P(f), P(f), P(f), 4, 1, 16, 0.5, 16, 8, P(f), P(f), P(f), P(f), P(cnt), None) == -1
+        assert h.lib.isb_nms(h.ptr, None, P(f), 4, 0.5, P(f), P(cnt), None) < 0
+    finally:
+        h.close()
