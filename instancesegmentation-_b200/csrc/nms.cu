@@ -71,9 +71,10 @@ __global__ void nms_gather_kernel(const uint64_t* __restrict__ keys, const float
   }
 }
 
-// Suppression matrix, FULL and symmetric: bit j of mask[i][j / 64] is set iff i != j and IoU(i, j) > thr, so
-// row i restricted to j < i is "who can suppress i" (what the scan needs) without a transpose.
-// grid (col_block, row_block), 64 threads: thread t owns row rb * 64 + t against the 64 boxes of the column
+// Suppression matrix, LOWER triangle (64x64 blocks with col_block <= row_block): bit j of mask[i][j / 64] is set iff
+// i != j and IoU(i, j) > thr.  The scan only ever reads row i restricted to j < i ("who can suppress i"), so the blocks
+// above the diagonal are neither computed nor launched (the words they would fill stay unwritten and unread).
+// 1-D grid over the nb (nb + 1) / 2 blocks, 64 threads: thread t owns row rb * 64 + t against the 64 boxes of the column
 // block staged in shared memory.  Disjoint pairs (the vast majority) skip the division: 0 / union is +-0 for every
 // finite non-zero union, and the slow path of the IEEE division for a zero numerator is the most expensive
 // thing in the loop.
@@ -81,8 +82,13 @@ __global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__
                                                       const int32_t* __restrict__ n_dev, float thr, int words,
                                                       const int32_t* __restrict__ slabel, uint64_t* __restrict__ mask) {
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
-  const int rb = blockIdx.y, cb = blockIdx.x;
-  if (rb * 64 >= n || cb * 64 >= n) return;
+  // linear block index -> (rb, cb), cb <= rb: rb = floor((sqrt(8 t + 1) - 1) / 2), fixed up for rounding
+  const unsigned lin = blockIdx.x;
+  int rb = (int)((sqrtf(8.0f * (float)lin + 1.0f) - 1.0f) * 0.5f);
+  while ((unsigned)(rb + 1) * (unsigned)(rb + 2) / 2 <= lin) ++rb;
+  while ((unsigned)rb * (unsigned)(rb + 1) / 2 > lin) --rb;
+  const int cb = (int)(lin - (unsigned)rb * (unsigned)(rb + 1) / 2);
+  if (rb * 64 >= n) return;
   __shared__ float4 cbox[64];
   __shared__ float carea[64];
   __shared__ int clabel[64];
@@ -285,7 +291,7 @@ int launch_nms(isb_handle* h, const NmsCall& c, cudaStream_t s) {
   nms_gather_kernel<<<blocks, 256, 0, s>>>(sorted, c.boxes, c.idxs64, c.idxs32, n, c.n_dev, h->nms_scalars,
                                            c.labels32, h->nms_sbox, h->nms_order, h->nms_slabel);
   ISB_LAUNCH_CHECK(h, "nms_gather_kernel");
-  nms_mask_kernel<<<dim3(words, words), 64, 0, s>>>(h->nms_sbox, n, c.n_dev, thr_f, words,
+  nms_mask_kernel<<<(unsigned)((int64_t)words * (words + 1) / 2), 64, 0, s>>>(h->nms_sbox, n, c.n_dev, thr_f, words,
                                                     c.labels32 ? h->nms_slabel : nullptr, h->nms_mask);
   ISB_LAUNCH_CHECK(h, "nms_mask_kernel");
   const size_t smem = (size_t)words * 8;
