@@ -203,12 +203,24 @@ __device__ __forceinline__ int cta_exclusive_scan(int v, int* s_warp /* [32] */,
   }
   if (lane == 31) s_warp[warp] = incl;
   __syncthreads();
-  int off = 0, tot = 0;
   const int nw = (blockDim.x + 31) >> 5;
-  for (int w = 0; w < nw; ++w) {
-    const int c = s_warp[w];
-    if (w < warp) off += c;
-    tot += c;
+  int off = 0, tot = 0;
+  if (nw <= 8) {  // few warps: a short loop of broadcast reads beats seven dependent shuffles
+    for (int w = 0; w < nw; ++w) {
+      const int c = s_warp[w];
+      if (w < warp) off += c;
+      tot += c;
+    }
+  } else {  // every warp scans the (<= 32) warp totals with shuffles: lane w holds warp w's total
+    const int wt = lane < nw ? s_warp[lane] : 0;
+    int winc = wt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += u;
+    }
+    tot = __shfl_sync(0xffffffffu, winc, 31);
+    off = __shfl_sync(0xffffffffu, winc - wt, warp);
   }
   __syncthreads();
   *total = tot;

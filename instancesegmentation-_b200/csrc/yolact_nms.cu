@@ -253,7 +253,7 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
           const float dy = fmaxf(fminf(bi.w, bj.w) - fmaxf(bi.y, bj.y), 0.0f);
           const float inter = dx * dy;
           const float uni = (box_area(bi) + aj) - inter;
-          if (inter == 0.0f && uni != 0.0f && fabsf(uni) <= 3.402823466e38f) continue;
+          if (inter == 0.0f && fabsf(uni) > 0.0f) continue;  // non-zero, not NaN (an infinite union gives 0 too)
           if (!(inter / uni <= p.nms_iou)) { bad = true; break; }
         }
       }
@@ -340,7 +340,7 @@ __device__ __forceinline__ bool fnms_suppresses(float4 bi, float4 bj, float aj, 
   const float dy = fmaxf(fminf(bi.w, bj.w) - fmaxf(bi.y, bj.y), 0.0f);
   const float inter = dx * dy;
   const float uni = (box_area(bi) + aj) - inter;
-  if (inter == 0.0f && uni != 0.0f && fabsf(uni) <= 3.402823466e38f) return false;
+  if (inter == 0.0f && fabsf(uni) > 0.0f) return false;  // non-zero, not NaN (an infinite union gives 0 too)
   return !(inter / uni <= thr);
 }
 

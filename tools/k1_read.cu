@@ -111,6 +111,63 @@ __global__ void __launch_bounds__(256) filter(const float* __restrict__ scores, 
   }
 }
 
+// MODE 0 with hits parked in shared memory and one reservation per CTA (what candidates_kernel does now)
+template <int UNROLL>
+__global__ void __launch_bounds__(256) filter_staged(const float* __restrict__ scores, float thr, int* count, uint64_t* keys, int cap) {
+  __shared__ uint64_t s_keys[1024];
+  __shared__ int s_n, s_base;
+  if (threadIdx.x == 0) s_n = 0;
+  __syncthreads();
+  const uint32_t nvec = kPerImg / 4;
+  const float4* body = reinterpret_cast<const float4*>(scores + (size_t)blockIdx.y * kPerImg);
+  const uint32_t stride = gridDim.x * 256;
+  uint32_t v = blockIdx.x * 256 + threadIdx.x;
+  const uint32_t step = (4u * stride) % kCols;
+  uint32_t r = (4u * v) % kCols;
+  auto hit = [&](uint32_t le, float s) {
+    const uint32_t row = le / kCols, c = le - row * kCols;
+    if (c == 0) return;
+    const int sp = atomicAdd(&s_n, 1);
+    if (sp < 1024) s_keys[sp] = ((uint64_t)c << 52) | ((uint64_t)__float_as_uint(s) << 20) | row;
+  };
+  auto scan = [&](float4 x, uint32_t e, uint32_t rr) {
+    const uint32_t k = rr == 0 ? 0u : kCols - rr;
+    if (k == 0) x.x = -1.f;
+    if (k == 1) x.y = -1.f;
+    if (k == 2) x.z = -1.f;
+    if (k == 3) x.w = -1.f;
+    if (x.x > thr || x.y > thr || x.z > thr || x.w > thr) {
+      if (x.x > thr) hit(e, x.x);
+      if (x.y > thr) hit(e + 1, x.y);
+      if (x.z > thr) hit(e + 2, x.z);
+      if (x.w > thr) hit(e + 3, x.w);
+    }
+  };
+  for (; v + (UNROLL - 1) * stride < nvec; v += UNROLL * stride) {
+    float4 x[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) x[u] = __ldcs(body + v + u * stride);
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      scan(x[u], 4 * (v + u * stride), r);
+      r += step;
+      if (r >= kCols) r -= kCols;
+    }
+  }
+  for (; v < nvec; v += stride) {
+    scan(__ldcs(body + v), 4 * v, r);
+    r += step;
+    if (r >= kCols) r -= kCols;
+  }
+  __syncthreads();
+  const int staged = min(s_n, 1024);
+  if (staged == 0) return;
+  if (threadIdx.x == 0) s_base = atomicAdd(&count[blockIdx.y], staged);
+  __syncthreads();
+  for (int i = threadIdx.x; i < staged; i += 256)
+    if (s_base + i < cap) keys[(size_t)blockIdx.y * cap + s_base + i] = s_keys[i];
+}
+
 // MODE 2: contiguous chunk per CTA (each CTA walks its own contiguous range, 4 KB per iteration)
 template <int UNROLL>
 __global__ void __launch_bounds__(256) filter_chunk(const float* __restrict__ scores, float thr, int* count, uint64_t* keys, int cap) {
@@ -205,7 +262,16 @@ int main() {
     ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter<0, 8, true><<<dim3(P, kBatch), 256>>>(x, 0.05f, count, keys, cap); });
     snprintf(nm, 64, "k1_perimg_P%d_u8_blank", P); REPORT(nm);
   }
-  for (int ps : {4, 8, 16}) {
+  for (int P : {18, 37, 74, 148}) {
+    char nm[64];
+    ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter_staged<4><<<dim3(P, kBatch), 256>>>(x, 0.05f, count, keys, cap); });
+    snprintf(nm, 64, "k1_staged_P%d_u4", P); REPORT(nm);
+    ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter_staged<8><<<dim3(P, kBatch), 256>>>(x, 0.05f, count, keys, cap); });
+    snprintf(nm, 64, "k1_staged_P%d_u8", P); REPORT(nm);
+    ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter_staged<2><<<dim3(P, kBatch), 256>>>(x, 0.05f, count, keys, cap); });
+    snprintf(nm, 64, "k1_staged_P%d_u2", P); REPORT(nm);
+  }
+  for (int ps : {8}) {
     char nm[64];
     ms = best_ms([&] { cudaMemsetAsync(count, 0, kBatch * 4); filter<1, 4, true><<<148 * ps, 256>>>(x, 0.05f, count, keys, cap); });
     snprintf(nm, 64, "k1_flat_x%d_u4", ps); REPORT(nm);
