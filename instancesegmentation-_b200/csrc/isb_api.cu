@@ -79,6 +79,9 @@ static void free_ws(isb_handle* h) {
   if (h->fork_event) cudaEventDestroy(h->fork_event);
   cudaFree(h->rle_scratch);
   cudaFree(h->fnms_cls);
+  for (int g = 0; g < 2; ++g)
+    if (h->graphs[g].exec) cudaGraphExecDestroy(h->graphs[g].exec);
+  if (h->capture_stream) cudaStreamDestroy(h->capture_stream);
   cudaFree(h->cand_count);
   cudaFree(h->work_counter);
   cudaFree(h->cand_keys);

@@ -284,6 +284,17 @@ __host__ __device__ inline int next_pow2(int v) {
 // ---------------------------------------------------------------------------------------
 // Handle
 // ---------------------------------------------------------------------------------------
+// A captured launch sequence of one multi-kernel entry point, replayed while the call's arguments (pointers included)
+// and the workspace it touches stay the same.
+struct GraphSlot {
+  unsigned char key[512];
+  int key_len;
+  unsigned char pending[512];
+  int pending_len;
+  cudaGraphExec_t exec;
+  int nodes;  // kernel launches inside the graph (for isb_launch_count)
+};
+
 struct isb_handle {
   int device;
   int num_sms;
@@ -293,6 +304,9 @@ struct isb_handle {
   int64_t launches;
   size_t ws_bytes;
   // workspace (device)
+  GraphSlot graphs[2];   // 0 = isb_rpn_filter, 1 = isb_box_postprocess
+  cudaStream_t capture_stream;
+  int graphs_off;        // set when a capture failed once: stay eager
   int32_t* fnms_cls;     // wide Fast NMS: class-start table + kept counter
   void* rle_scratch;     // run-length encoding scratch (grown on demand)
   size_t rle_bytes;

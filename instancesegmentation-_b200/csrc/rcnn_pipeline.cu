@@ -327,6 +327,78 @@ static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 using namespace isb;
 
+// ---- CUDA-graph replay of the two launch-bound chains ---------------------------------------------------------------
+// isb_rpn_filter issues ~20 small kernels and isb_box_postprocess ~13; on a B200 their sum of kernel times is about two
+// thirds of the wall time, the rest being launch gaps.  The first call with a given argument set runs eagerly (it also
+// sizes the workspace); if the next call repeats it exactly -- same pointers, sizes and workspace, the steady state of a
+// serving loop with preallocated tensors -- the sequence is captured on a private stream (nothing executes during
+// capture) and from then on replayed with one cudaGraphLaunch into the caller's stream.  Any difference falls back to
+// the eager path and restarts the cycle; ISB_NO_GRAPHS=1 disables it.
+struct KeyBuilder {
+  unsigned char buf[512];
+  int len = 0;
+  template <class T> void add(const T& v) {
+    if (len + (int)sizeof(T) <= (int)sizeof(buf)) {
+      memcpy(buf + len, &v, sizeof(T));
+      len += (int)sizeof(T);
+    } else {
+      len = (int)sizeof(buf) + 1;  // too long: never matches
+    }
+  }
+};
+
+template <class F>
+static int graph_run(isb_handle* h, int slot, const KeyBuilder& key, cudaStream_t s, F&& launch) {
+  GraphSlot& g = h->graphs[slot];
+  static const bool env_off = getenv("ISB_NO_GRAPHS") != nullptr;
+  if (env_off || h->graphs_off || key.len > (int)sizeof(g.key)) return launch(s);
+  if (g.exec && g.key_len == key.len && memcmp(g.key, key.buf, key.len) == 0) {
+    ISB_CUDA(h, cudaGraphLaunch(g.exec, s));
+    h->launches += g.nodes;
+    return ISB_OK;
+  }
+  if (g.pending_len != key.len || memcmp(g.pending, key.buf, key.len) != 0) {  // first sighting: eager
+    memcpy(g.pending, key.buf, key.len);
+    g.pending_len = key.len;
+    return launch(s);
+  }
+  // second consecutive call with these arguments: capture
+  if (!h->capture_stream) ISB_CUDA(h, cudaStreamCreateWithFlags(&h->capture_stream, cudaStreamNonBlocking));
+  if (g.exec) {
+    cudaGraphExecDestroy(g.exec);
+    g.exec = nullptr;
+  }
+  const int64_t launches0 = h->launches;
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamBeginCapture(h->capture_stream, cudaStreamCaptureModeThreadLocal);
+  int rc = ISB_ERR_CUDA;
+  if (e == cudaSuccess) {
+    rc = launch(h->capture_stream);
+    e = cudaStreamEndCapture(h->capture_stream, &graph);
+  }
+  const int nodes = (int)(h->launches - launches0);
+  h->launches = launches0;
+  if (e == cudaSuccess && rc == ISB_OK && graph) e = cudaGraphInstantiate(&g.exec, graph, 0);
+  if (graph) cudaGraphDestroy(graph);
+  if (e != cudaSuccess || rc != ISB_OK || !g.exec) {  // could not capture: stay eager from now on
+    cudaGetLastError();
+    g.exec = nullptr;
+    h->graphs_off = 1;
+    return launch(s);
+  }
+  memcpy(g.key, key.buf, key.len);
+  g.key_len = key.len;
+  g.nodes = nodes;
+  ISB_CUDA(h, cudaGraphLaunch(g.exec, s));
+  h->launches += g.nodes;
+  return ISB_OK;
+}
+
+static void key_workspace(KeyBuilder& k, const isb_handle* h) {
+  k.add(h->scratch); k.add(h->scratch_bytes); k.add(h->nms_cap); k.add(h->nms_keys); k.add(h->nms_keys2); k.add(h->nms_rank);
+  k.add(h->nms_slabel); k.add(h->nms_sbox); k.add(h->nms_order); k.add(h->nms_mask); k.add(h->nms_scalars);
+}
+
 extern "C" int isb_rpn_filter(isb_handle* h, const float* proposals, const float* objectness,
                               const int32_t* anchors_per_level, int32_t num_levels, int32_t img_h, int32_t img_w,
                               int32_t pre_nms_top_n, int32_t post_nms_top_n, double nms_thresh, float score_thresh,
@@ -366,63 +438,72 @@ extern "C" int isb_rpn_filter(isb_handle* h, const float* proposals, const float
   int rc = ensure_scratch(h, b_keys + b_box + b_sc + b_lvl + b_keep + b_cand + b_sorted + b_rank + b_hist + b_state + 512);
   if (rc != ISB_OK) return rc;
   if ((rc = ensure_nms_ws(h, cmax)) != ISB_OK) return rc;
-  char* p = static_cast<char*>(h->scratch);
-  uint64_t* keys = (uint64_t*)p;  p += b_keys;
-  float4* cbox = (float4*)p;      p += b_box;
-  float* cscore = (float*)p;      p += b_sc;
-  int32_t* clvl = (int32_t*)p;    p += b_lvl;
-  int64_t* keep = (int64_t*)p;    p += b_keep;
-  uint64_t* cand = (uint64_t*)p;  p += b_cand;
-  uint64_t* sorted = (uint64_t*)p; p += b_sorted;
-  int32_t* rank = (int32_t*)p;    p += b_rank;
-  int* hist = (int*)p;            // [passes][levels][bins] then cand_count [levels]
-  int32_t* cand_count = hist + (size_t)kSelPasses * num_levels * kSelBins;
-  p += b_hist;
-  SelState* state = (SelState*)p; p += b_state;
-  int32_t* n_dev = (int32_t*)p;   // [0] candidates, [2] kept count
-  LevelTopK topk;
-  memset(&topk, 0, sizeof(topk));
-  int max_level = 0;
-  for (int l = 0; l < num_levels; ++l) {
-    topk.k[l] = anchors_per_level[l] < pre_nms_top_n ? anchors_per_level[l] : pre_nms_top_n;
-    if (anchors_per_level[l] > max_level) max_level = anchors_per_level[l];
-  }
-  ISB_CUDA(h, cudaMemsetAsync(hist, 0, b_hist, s));
-  int chunks = (max_level + kSelThreads * 8 - 1) / (kSelThreads * 8);
-  if (chunks > 4 * h->num_sms) chunks = 4 * h->num_sms;
-  if (chunks < 1) chunks = 1;
-  for (int pass = 0; pass <= kSelPasses; ++pass) {
-    rpn_select_pass_kernel<<<dim3(chunks, num_levels), kSelThreads, 0, s>>>(objectness, lv, topk, pass, hist, state, num_levels,
-                                                                            pre_nms_top_n, cand, cand_count);
-    ISB_LAUNCH_CHECK(h, "rpn_select_pass_kernel");
-  }
-  rpn_pack_keys_kernel<<<(n_pow2 + 255) / 256, 256, 0, s>>>(cand, lv, pre_nms_top_n, n_pow2, keys);
-  ISB_LAUNCH_CHECK(h, "rpn_pack_keys_kernel");
-  if (cmax <= kRankSortMax) {
-    if ((rc = launch_rank_sort_u64(h, keys, cmax, nullptr, rank, sorted, s)) != ISB_OK) return rc;
-  } else {
-    if ((rc = launch_sort_u64(h, keys, n_pow2, s)) != ISB_OK) return rc;
-    sorted = keys;
-  }
-  rpn_select_kernel<<<1, 1024, 0, s>>>(sorted, topk, reinterpret_cast<const float4*>(proposals), num_levels, pre_nms_top_n,
-                                       (float)img_w, (float)img_h, min_size, score_thresh, cbox, cscore, clvl, n_dev);
-  ISB_LAUNCH_CHECK(h, "rpn_select_kernel");
-  NmsCall c;
-  memset(&c, 0, sizeof(c));
-  c.boxes = cbox;
-  c.scores = cscore;
-  c.idxs32 = clvl;
-  c.n_max = cmax;
-  c.n_dev = n_dev;
-  c.iou_threshold = nms_thresh;
-  c.max_keep = post_nms_top_n;
-  c.keep = keep;
-  c.count = n_dev + 2;
-  if ((rc = launch_nms(h, c, s)) != ISB_OK) return rc;
-  rpn_gather_kernel<<<8, 256, 0, s>>>(keep, n_dev + 2, cbox, cscore, post_nms_top_n, reinterpret_cast<float4*>(out_boxes),
-                                      out_scores, out_count);
-  ISB_LAUNCH_CHECK(h, "rpn_gather_kernel");
-  return ISB_OK;
+  KeyBuilder key;
+  key.add(proposals); key.add(objectness); key.add(num_levels); key.add(img_h); key.add(img_w); key.add(pre_nms_top_n);
+  key.add(post_nms_top_n); key.add(nms_thresh); key.add(score_thresh); key.add(min_size); key.add(out_boxes); key.add(out_scores);
+  key.add(out_count);
+  for (int l = 0; l < num_levels; ++l) key.add(anchors_per_level[l]);
+  key_workspace(key, h);
+  return graph_run(h, 0, key, s, [&](cudaStream_t s) -> int {
+    int rc;
+    char* p = static_cast<char*>(h->scratch);
+    uint64_t* keys = (uint64_t*)p;  p += b_keys;
+    float4* cbox = (float4*)p;      p += b_box;
+    float* cscore = (float*)p;      p += b_sc;
+    int32_t* clvl = (int32_t*)p;    p += b_lvl;
+    int64_t* keep = (int64_t*)p;    p += b_keep;
+    uint64_t* cand = (uint64_t*)p;  p += b_cand;
+    uint64_t* sorted = (uint64_t*)p; p += b_sorted;
+    int32_t* rank = (int32_t*)p;    p += b_rank;
+    int* hist = (int*)p;            // [passes][levels][bins] then cand_count [levels]
+    int32_t* cand_count = hist + (size_t)kSelPasses * num_levels * kSelBins;
+    p += b_hist;
+    SelState* state = (SelState*)p; p += b_state;
+    int32_t* n_dev = (int32_t*)p;   // [0] candidates, [2] kept count
+    LevelTopK topk;
+    memset(&topk, 0, sizeof(topk));
+    int max_level = 0;
+    for (int l = 0; l < num_levels; ++l) {
+      topk.k[l] = anchors_per_level[l] < pre_nms_top_n ? anchors_per_level[l] : pre_nms_top_n;
+      if (anchors_per_level[l] > max_level) max_level = anchors_per_level[l];
+    }
+    ISB_CUDA(h, cudaMemsetAsync(hist, 0, b_hist, s));
+    int chunks = (max_level + kSelThreads * 8 - 1) / (kSelThreads * 8);
+    if (chunks > 4 * h->num_sms) chunks = 4 * h->num_sms;
+    if (chunks < 1) chunks = 1;
+    for (int pass = 0; pass <= kSelPasses; ++pass) {
+      rpn_select_pass_kernel<<<dim3(chunks, num_levels), kSelThreads, 0, s>>>(objectness, lv, topk, pass, hist, state, num_levels,
+                                                                              pre_nms_top_n, cand, cand_count);
+      ISB_LAUNCH_CHECK(h, "rpn_select_pass_kernel");
+    }
+    rpn_pack_keys_kernel<<<(n_pow2 + 255) / 256, 256, 0, s>>>(cand, lv, pre_nms_top_n, n_pow2, keys);
+    ISB_LAUNCH_CHECK(h, "rpn_pack_keys_kernel");
+    if (cmax <= kRankSortMax) {
+      if ((rc = launch_rank_sort_u64(h, keys, cmax, nullptr, rank, sorted, s)) != ISB_OK) return rc;
+    } else {
+      if ((rc = launch_sort_u64(h, keys, n_pow2, s)) != ISB_OK) return rc;
+      sorted = keys;
+    }
+    rpn_select_kernel<<<1, 1024, 0, s>>>(sorted, topk, reinterpret_cast<const float4*>(proposals), num_levels, pre_nms_top_n,
+                                         (float)img_w, (float)img_h, min_size, score_thresh, cbox, cscore, clvl, n_dev);
+    ISB_LAUNCH_CHECK(h, "rpn_select_kernel");
+    NmsCall c;
+    memset(&c, 0, sizeof(c));
+    c.boxes = cbox;
+    c.scores = cscore;
+    c.idxs32 = clvl;
+    c.n_max = cmax;
+    c.n_dev = n_dev;
+    c.iou_threshold = nms_thresh;
+    c.max_keep = post_nms_top_n;
+    c.keep = keep;
+    c.count = n_dev + 2;
+    if ((rc = launch_nms(h, c, s)) != ISB_OK) return rc;
+    rpn_gather_kernel<<<8, 256, 0, s>>>(keep, n_dev + 2, cbox, cscore, post_nms_top_n, reinterpret_cast<float4*>(out_boxes),
+                                        out_scores, out_count);
+    ISB_LAUNCH_CHECK(h, "rpn_gather_kernel");
+    return ISB_OK;
+  });
 }
 
 extern "C" int isb_box_postprocess(isb_handle* h, const float* class_logits, const float* class_probs,
@@ -459,45 +540,53 @@ extern "C" int isb_box_postprocess(isb_handle* h, const float* class_logits, con
   int rc = ensure_scratch(h, 2 * b_cnt + b_box + 2 * b_sc + b_keep + 512);
   if (rc != ISB_OK) return rc;
   if ((rc = ensure_nms_ws(h, n_cap)) != ISB_OK) return rc;
-  char* p = static_cast<char*>(h->scratch);
-  int32_t* row_count = (int32_t*)p;   p += b_cnt;
-  int32_t* row_offset = (int32_t*)p;  p += b_cnt;
-  float4* cbox = (float4*)p;          p += b_box;
-  float* cscore = (float*)p;          p += b_sc;
-  int32_t* clabel = (int32_t*)p;      p += b_sc;
-  int64_t* keep = (int64_t*)p;        p += b_keep;
-  int32_t* n_dev = (int32_t*)p;       // [0] candidates, [1] overflow, [2] kept count
-  BoxPostParams bp;
-  bp.logits = class_probs ? nullptr : class_logits;
-  bp.probs = class_probs;
-  bp.reg = reinterpret_cast<const float4*>(box_regression);
-  bp.proposals = reinterpret_cast<const float4*>(proposals);
-  bp.R = num_rois;
-  bp.C = num_classes;
-  bp.wx = wx; bp.wy = wy; bp.ww = ww; bp.wh = wh; bp.clip = clip;
-  bp.img_w = (float)img_w; bp.img_h = (float)img_h;
-  bp.score_thresh = score_thresh;
-  const int row_blocks = (num_rois + 7) / 8;
-  boxpost_rows_kernel<0><<<row_blocks, 256, 0, s>>>(bp, row_count, nullptr, n_cap, nullptr, nullptr, nullptr);
-  ISB_LAUNCH_CHECK(h, "boxpost_rows_kernel<0>");
-  boxpost_scan_kernel<<<1, 1024, 0, s>>>(row_count, num_rois, n_cap, row_offset, n_dev);
-  ISB_LAUNCH_CHECK(h, "boxpost_scan_kernel");
-  boxpost_rows_kernel<1><<<row_blocks, 256, 0, s>>>(bp, nullptr, row_offset, n_cap, cbox, cscore, clabel);
-  ISB_LAUNCH_CHECK(h, "boxpost_rows_kernel<1>");
-  NmsCall c;
-  memset(&c, 0, sizeof(c));
-  c.boxes = cbox;
-  c.scores = cscore;
-  c.idxs32 = clabel;
-  c.n_max = n_cap;
-  c.n_dev = n_dev;
-  c.iou_threshold = nms_thresh;
-  c.max_keep = detections_per_img;
-  c.keep = keep;
-  c.count = n_dev + 2;
-  if ((rc = launch_nms(h, c, s)) != ISB_OK) return rc;
-  boxpost_gather_kernel<<<4, 256, 0, s>>>(keep, n_dev + 2, n_dev + 1, cbox, cscore, clabel, detections_per_img,
-                                          reinterpret_cast<float4*>(out_boxes), out_scores, out_labels, out_count);
-  ISB_LAUNCH_CHECK(h, "boxpost_gather_kernel");
-  return ISB_OK;
+  KeyBuilder key;
+  key.add(class_logits); key.add(class_probs); key.add(box_regression); key.add(proposals); key.add(num_rois); key.add(num_classes);
+  key.add(img_h); key.add(img_w); key.add(wx); key.add(wy); key.add(ww); key.add(wh); key.add(clip); key.add(score_thresh);
+  key.add(nms_thresh); key.add(detections_per_img); key.add(out_boxes); key.add(out_scores); key.add(out_labels); key.add(out_count);
+  key_workspace(key, h);
+  return graph_run(h, 1, key, s, [&](cudaStream_t s) -> int {
+    int rc;
+    char* p = static_cast<char*>(h->scratch);
+    int32_t* row_count = (int32_t*)p;   p += b_cnt;
+    int32_t* row_offset = (int32_t*)p;  p += b_cnt;
+    float4* cbox = (float4*)p;          p += b_box;
+    float* cscore = (float*)p;          p += b_sc;
+    int32_t* clabel = (int32_t*)p;      p += b_sc;
+    int64_t* keep = (int64_t*)p;        p += b_keep;
+    int32_t* n_dev = (int32_t*)p;       // [0] candidates, [1] overflow, [2] kept count
+    BoxPostParams bp;
+    bp.logits = class_probs ? nullptr : class_logits;
+    bp.probs = class_probs;
+    bp.reg = reinterpret_cast<const float4*>(box_regression);
+    bp.proposals = reinterpret_cast<const float4*>(proposals);
+    bp.R = num_rois;
+    bp.C = num_classes;
+    bp.wx = wx; bp.wy = wy; bp.ww = ww; bp.wh = wh; bp.clip = clip;
+    bp.img_w = (float)img_w; bp.img_h = (float)img_h;
+    bp.score_thresh = score_thresh;
+    const int row_blocks = (num_rois + 7) / 8;
+    boxpost_rows_kernel<0><<<row_blocks, 256, 0, s>>>(bp, row_count, nullptr, n_cap, nullptr, nullptr, nullptr);
+    ISB_LAUNCH_CHECK(h, "boxpost_rows_kernel<0>");
+    boxpost_scan_kernel<<<1, 1024, 0, s>>>(row_count, num_rois, n_cap, row_offset, n_dev);
+    ISB_LAUNCH_CHECK(h, "boxpost_scan_kernel");
+    boxpost_rows_kernel<1><<<row_blocks, 256, 0, s>>>(bp, nullptr, row_offset, n_cap, cbox, cscore, clabel);
+    ISB_LAUNCH_CHECK(h, "boxpost_rows_kernel<1>");
+    NmsCall c;
+    memset(&c, 0, sizeof(c));
+    c.boxes = cbox;
+    c.scores = cscore;
+    c.idxs32 = clabel;
+    c.n_max = n_cap;
+    c.n_dev = n_dev;
+    c.iou_threshold = nms_thresh;
+    c.max_keep = detections_per_img;
+    c.keep = keep;
+    c.count = n_dev + 2;
+    if ((rc = launch_nms(h, c, s)) != ISB_OK) return rc;
+    boxpost_gather_kernel<<<4, 256, 0, s>>>(keep, n_dev + 2, n_dev + 1, cbox, cscore, clabel, detections_per_img,
+                                            reinterpret_cast<float4*>(out_boxes), out_scores, out_labels, out_count);
+    ISB_LAUNCH_CHECK(h, "boxpost_gather_kernel");
+    return ISB_OK;
+  });
 }

@@ -96,17 +96,20 @@ class BoxCoder(object):
 
 # ---------------------------------------------------------------------------- rpn_function.py
 def filter_proposals(proposals, objectness, image_shape, num_anchors_per_level, pre_nms_top_n=1000, post_nms_top_n=1000,
-                     nms_thresh=0.7, score_thresh=0.0, min_size=1.0):
+                     nms_thresh=0.7, score_thresh=0.0, min_size=1.0, out=None):
     """rpn_function.py:460-529 (+ _get_top_n_idx :434) for one image: proposals [A,4] decoded boxes,
-    objectness [A] logits.  Returns (boxes [k,4], scores [k]).  Defaults: faster_rcnn_framework.py:261-270."""
+    objectness [A] logits.  Returns (boxes [k,4], scores [k]).  Defaults: faster_rcnn_framework.py:261-270.
+    `out` = (boxes [post,4] f32, scores [post] f32, count [1] i32) preallocated on the device: with the same input and
+    output tensors call after call, the library replays the whole launch sequence as one CUDA graph."""
     proposals = _cuda_f32(proposals, "proposals").reshape(-1, 4)
     dev = proposals.device
     objectness = _cuda_f32(objectness, "objectness").to(dev).reshape(-1)
     levels = (C.c_int32 * len(num_anchors_per_level))(*[int(v) for v in num_anchors_per_level])
     post = int(post_nms_top_n)
-    out_b = torch.empty((post, 4), dtype=torch.float32, device=dev)
-    out_s = torch.empty((post,), dtype=torch.float32, device=dev)
-    count = torch.zeros((1,), dtype=torch.int32, device=dev)
+    if out is None:
+        out = (torch.empty((post, 4), dtype=torch.float32, device=dev), torch.empty((post,), dtype=torch.float32, device=dev),
+               torch.zeros((1,), dtype=torch.int32, device=dev))
+    out_b, out_s, count = out
     _call(dev, lambda h: h.lib.isb_rpn_filter(h.ptr, _ptr(proposals), _ptr(objectness), levels, len(num_anchors_per_level),
                                               int(image_shape[0]), int(image_shape[1]), int(pre_nms_top_n), post,
                                               float(nms_thresh), float(score_thresh), float(min_size), _ptr(out_b),
@@ -118,9 +121,10 @@ def filter_proposals(proposals, objectness, image_shape, num_anchors_per_level, 
 # ---------------------------------------------------------------------------- roi_head.py
 def postprocess_detections(class_logits, box_regression, proposals, image_shape, weights=(10.0, 10.0, 5.0, 5.0),
                            score_thresh=0.05, nms_thresh=0.5, detections_per_img=100, bbox_xform_clip=BBOX_XFORM_CLIP,
-                           class_probs=None):
+                           class_probs=None, out=None):
     """roi_head.py:366-457 for one image.  Returns (boxes [k,4], scores [k], labels int64 [k]).
-    `class_probs` (softmaxed scores) may be given instead of logits."""
+    `class_probs` (softmaxed scores) may be given instead of logits.  `out` = preallocated (boxes [d,4] f32, scores [d] f32,
+    labels [d] i64, count [1] i32), see filter_proposals."""
     reg = _cuda_f32(box_regression, "box_regression")
     dev = reg.device
     props = _cuda_f32(proposals, "proposals").to(dev)
@@ -129,10 +133,10 @@ def postprocess_detections(class_logits, box_regression, proposals, image_shape,
     r = props.shape[0]
     c = (probs if probs is not None else logits).shape[-1]
     d = int(detections_per_img)
-    out_b = torch.empty((d, 4), dtype=torch.float32, device=dev)
-    out_s = torch.empty((d,), dtype=torch.float32, device=dev)
-    out_l = torch.empty((d,), dtype=torch.int64, device=dev)
-    count = torch.zeros((1,), dtype=torch.int32, device=dev)
+    if out is None:
+        out = (torch.empty((d, 4), dtype=torch.float32, device=dev), torch.empty((d,), dtype=torch.float32, device=dev),
+               torch.empty((d,), dtype=torch.int64, device=dev), torch.zeros((1,), dtype=torch.int32, device=dev))
+    out_b, out_s, out_l, count = out
     null = C.c_void_p(0)
     wx, wy, ww, wh = [float(w) for w in weights]
     _call(dev, lambda h: h.lib.isb_box_postprocess(h.ptr, _ptr(logits) if logits is not None else null,
