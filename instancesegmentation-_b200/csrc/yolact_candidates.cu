@@ -151,6 +151,7 @@ constexpr int kLgRows = 16;      // rows per warp tile
 constexpr int kLgThreads = 256;  // 8 warps
 constexpr int kLgWarps = kLgThreads / 32;
 constexpr int kLgStage = 96;     // parked keys per warp
+constexpr int kLgRegCols = 41;   // columns per lane kept in registers (rows of up to 82 classes: COCO's 81)
 
 struct LgWarpStage {
   uint64_t keys[kLgStage];
@@ -189,33 +190,74 @@ __device__ __forceinline__ void lg_tile(const float* tile, const CandParams& p, 
   const int par = lane & 1;
   const bool valid = (lane >> 1) < nr;
   const float* row = tile + (valid ? (lane >> 1) : nr - 1) * C;  // pairs past the last row redo it and flag nothing
-  const int cf = p.col0 + ((par - p.col0) & 1);  // first foreground column of this lane's parity
-  float m0 = ninf, m1 = ninf;
-  int c = cf;
-  for (; c + 2 < C; c += 4) {
-    m0 = fmaxf(m0, row[c]);
-    m1 = fmaxf(m1, row[c + 2]);
-  }
-  if (c < C) m0 = fmaxf(m0, row[c]);
-  float mfg = fmaxf(m0, m1);
-  float mx = mfg;
-  for (int k = par; k < p.col0; k += 2) mx = fmaxf(mx, row[k]);
-  mfg = fmaxf(mfg, __shfl_xor_sync(0xffffffffu, mfg, 1));
-  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
-  // sum of exp(x - max) as ex2.approx(x * log2(e) - max * log2(e)), one FFMA + one MUFU per element.  Terms that matter
-  // to the sum have |x - max| of a few units, where this is within ~3e-7 of expf; the exact expf is kept for the
-  // candidates' own probabilities.
   const float kLog2e = 1.4426950408889634f;
-  const float nm2 = -mx * kLog2e;
-  float s0 = 0.0f, s1 = 0.0f;
-  c = par;
-  for (; c + 2 < C; c += 4) {
-    s0 += exp2f_approx(fmaf(row[c], kLog2e, nm2));
-    s1 += exp2f_approx(fmaf(row[c + 2], kLog2e, nm2));
+  float mfg, mx, sum;
+  if (C <= 2 * kLgRegCols && p.col0 <= 1) {
+    // The lane's half of the row (columns par, par + 2, ...) is read from shared memory ONCE into registers and both
+    // passes run on them: one LDS + FMNMX, then FFMA + MUFU + FADD per element.
+    float v[kLgRegCols];
+#pragma unroll
+    for (int k = 0; k < kLgRegCols; ++k) {
+      const int c = par + 2 * k;
+      v[k] = c < C ? row[c] : ninf;
+    }
+    float m0 = ninf, m1 = ninf;
+#pragma unroll
+    for (int k = 0; k < kLgRegCols; k += 2) {
+      m0 = fmaxf(m0, v[k]);
+      if (k + 1 < kLgRegCols) m1 = fmaxf(m1, v[k + 1]);
+    }
+    mx = fmaxf(m0, m1);
+    // foreground maximum: everything but column 0 when col0 == 1 (that is element k = 0 of the even lane)
+    float mf = mx;
+    if (p.col0 == 1 && par == 0) {
+      float f0 = ninf, f1 = ninf;
+#pragma unroll
+      for (int k = 1; k < kLgRegCols; k += 2) {
+        f0 = fmaxf(f0, v[k]);
+        if (k + 1 < kLgRegCols) f1 = fmaxf(f1, v[k + 1]);
+      }
+      mf = fmaxf(f0, f1);
+    }
+    mfg = fmaxf(mf, __shfl_xor_sync(0xffffffffu, mf, 1));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+    const float nm2 = -mx * kLog2e;
+    float s0 = 0.0f, s1 = 0.0f;
+#pragma unroll
+    for (int k = 0; k < kLgRegCols; k += 2) {
+      s0 += exp2f_approx(fmaf(v[k], kLog2e, nm2));  // padding is -inf: ex2 gives 0
+      if (k + 1 < kLgRegCols) s1 += exp2f_approx(fmaf(v[k + 1], kLog2e, nm2));
+    }
+    sum = s0 + s1;
+    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+  } else {  // wider rows: two passes over shared memory
+    const int cf = p.col0 + ((par - p.col0) & 1);  // first foreground column of this lane's parity
+    float m0 = ninf, m1 = ninf;
+    int c = cf;
+    for (; c + 2 < C; c += 4) {
+      m0 = fmaxf(m0, row[c]);
+      m1 = fmaxf(m1, row[c + 2]);
+    }
+    if (c < C) m0 = fmaxf(m0, row[c]);
+    mfg = fmaxf(m0, m1);
+    mx = mfg;
+    for (int k = par; k < p.col0; k += 2) mx = fmaxf(mx, row[k]);
+    mfg = fmaxf(mfg, __shfl_xor_sync(0xffffffffu, mfg, 1));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+    // sum of exp(x - max) as ex2.approx(x * log2(e) - max * log2(e)), one FFMA + one MUFU per element.  Terms that matter
+    // to the sum have |x - max| of a few units, where this is within ~3e-7 of expf; the exact expf is kept for the
+    // candidates' own probabilities.
+    const float nm2 = -mx * kLog2e;
+    float s0 = 0.0f, s1 = 0.0f;
+    c = par;
+    for (; c + 2 < C; c += 4) {
+      s0 += exp2f_approx(fmaf(row[c], kLog2e, nm2));
+      s1 += exp2f_approx(fmaf(row[c + 2], kLog2e, nm2));
+    }
+    if (c < C) s0 += exp2f_approx(fmaf(row[c], kLog2e, nm2));
+    sum = s0 + s1;
+    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
   }
-  if (c < C) s0 += exp2f_approx(fmaf(row[c], kLog2e, nm2));
-  float sum = s0 + s1;
-  sum += __shfl_xor_sync(0xffffffffu, sum, 1);
   // x - max > lim is necessary (with margin) for expf(x - max) / sum > threshold; most rows have no such column.  The
   // flagged rows are scanned by the whole warp, 32 columns at a time.
   const float lim = p.threshold > 0.0f ? logf(p.threshold * sum) - 1e-4f : ninf;
