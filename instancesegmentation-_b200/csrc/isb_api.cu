@@ -7,6 +7,7 @@
 namespace isb {
 int configure_fast_nms(isb_handle* h);
 int configure_masks(isb_handle* h);
+int configure_rcnn_ops(isb_handle* h);
 int configure_candidates(isb_handle* h);
 int launch_decode_boxes(isb_handle*, const float*, const float*, int64_t, float, float, float*, cudaStream_t);
 int launch_jaccard(isb_handle*, const float*, const float*, int, int, int, int, float*, cudaStream_t);
@@ -159,6 +160,7 @@ extern "C" int isb_create(int device, const isb_limits* limits, isb_handle** out
   if ((rc = configure_candidates(h)) != ISB_OK) return rc;
   if ((rc = configure_fast_nms(h)) != ISB_OK) return rc;
   if ((rc = configure_masks(h)) != ISB_OK) return rc;
+  if ((rc = configure_rcnn_ops(h)) != ISB_OK) return rc;
   if ((rc = configure_nms(h)) != ISB_OK) return rc;
   if ((rc = configure_mask_gemm_tc(h)) != ISB_OK) return rc;
   h->err[0] = 0;

@@ -49,10 +49,9 @@ __global__ void resize_boxes_kernel(const float4* __restrict__ in, int64_t m, fl
 
 // ------------------------------------------------------------------------------------------
 // transform.py:212-230  paste_masks_in_image (+ expand_masks :171, expand_boxes :145,
-// paste_mask_in_image :182).  Output float32 [m,1,H,W] written exactly once with 16-byte stores:
-// HBM-write-bound (427 MB at m=100, 800x1333).  A thread produces 4 consecutive output floats; each
-// one is either 0 (outside the integer box) or a bilinear sample of the zero-padded SxS mask
-// resized to the box (aten align_corners=False arithmetic), read through L1.
+// paste_mask_in_image :182).  Output float32 [m,1,H,W] written exactly once: HBM-write-bound (427 MB at
+// m=100, 800x1333).  Each element is either 0 (outside the integer box) or a bilinear sample of the
+// zero-padded SxS mask resized to the box (aten align_corners=False arithmetic), read through L1.
 // ------------------------------------------------------------------------------------------
 struct PasteBox { int x0, y0, x1, y1; };
 
@@ -75,65 +74,132 @@ __device__ __forceinline__ float padded_at(const float* __restrict__ mk, int S, 
   return (yy >= 0 && yy < S && xx >= 0 && xx < S) ? __ldg(mk + yy * S + xx) : 0.0f;
 }
 
-// IDX = uint32_t whenever m*H*W < 2^32 (always, for real image sizes): the flat element index -> (mask, row, col)
-// arithmetic is then 32-bit; the 64-bit instantiation exists for completeness.
-template <typename IDX>
-__global__ void __launch_bounds__(256) paste_masks_kernel(const float* __restrict__ masks, const float4* __restrict__ boxes,
-                                                          int m, int S, int pad, int im_h, int im_w,
-                                                          float* __restrict__ out) {
-  const IDX plane = (IDX)im_h * (IDX)im_w;
-  const IDX total = (IDX)m * plane;
-  const IDX nvec = (total + 3) >> 2;
+// One pasted value: bilinear sample of the zero-padded mask resized to the integer box (transform.py:182-209).
+struct PasteWin {
+  PasteBox pb;
+  float sx, sy;
+  const float* mk;
+};
+__device__ __forceinline__ PasteWin paste_win(const float* __restrict__ masks, const float4* __restrict__ boxes, int i, int S,
+                                              int Sp, float scale) {
+  PasteWin w;
+  w.pb = paste_box(__ldg(boxes + i), scale);
+  w.sx = (float)Sp / (float)max(w.pb.x1 - w.pb.x0 + 1, 1);
+  w.sy = (float)Sp / (float)max(w.pb.y1 - w.pb.y0 + 1, 1);
+  w.mk = masks + (int64_t)i * S * S;
+  return w;
+}
+__device__ __forceinline__ float paste_sample(const PasteWin& w, int S, int pad, int Sp, int y, int x) {
+  int iy0, iy1, ix0, ix1;
+  float ly0, ly1, lx0, lx1;
+  bilinear_src(y - w.pb.y0, w.sy, Sp, iy0, iy1, ly0, ly1);
+  bilinear_src(x - w.pb.x0, w.sx, Sp, ix0, ix1, lx0, lx1);
+  const float top = lx0 * padded_at(w.mk, S, pad, iy0, ix0) + lx1 * padded_at(w.mk, S, pad, iy0, ix1);
+  const float bot = lx0 * padded_at(w.mk, S, pad, iy1, ix0) + lx1 * padded_at(w.mk, S, pad, iy1, ix1);
+  return ly0 * top + ly1 * bot;
+}
+
+// The output is one flat stream of m*H*W floats cut into 4 KB chunks; chunk c belongs to warp (c mod #warps), so
+// neighbouring chunks (the rows of one box) spread over the whole grid.  A chunk whose rows miss its mask's box -- most
+// of them -- leaves as ONE bulk asynchronous store from a shared all-zero buffer (cp.async.bulk.global.shared::cta, SASS
+// UBLKCP): one lane issues it and no SM instruction touches the data.  Any other chunk is composed in one of the warp's
+// two private shared-memory buffers -- cleared with 16-byte stores, then only the columns inside the box are sampled,
+// row piece by row piece: the row's bilinear taps are warp-uniform, the two padded source rows sit in registers (one
+// column per lane) and the four taps of a pixel are warp shuffles -- and leaves the same way; the warp only waits
+// (wait_group.read) before it overwrites a buffer.  No CTA barrier after the prologue.
+constexpr int kPasteChunk = 1024;  // floats per bulk store
+constexpr int kPasteWarps = 16;
+constexpr size_t kPasteSmem = (size_t)(1 + 2 * kPasteWarps) * kPasteChunk * sizeof(float);
+
+template <int N>
+__device__ __forceinline__ void bulk_wait_read_n() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+
+__global__ void __launch_bounds__(kPasteWarps * 32, 1)
+paste_masks_bulk_kernel(const float* __restrict__ masks, const float4* __restrict__ boxes, int m, int S, int pad, int im_h,
+                        int im_w, float* __restrict__ out) {
+  extern __shared__ __align__(128) float s_paste[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* s_zero = s_paste;
+  float* s_buf = s_paste + kPasteChunk + (size_t)warp * 2 * kPasteChunk;
+  for (int t = threadIdx.x; t < kPasteChunk; t += blockDim.x) s_zero[t] = 0.0f;
+  fence_proxy_async();
+  __syncthreads();
+  const unsigned long long plane = (unsigned long long)im_h * im_w, total = (unsigned long long)m * plane;
+  const unsigned long long nchunks = (total + kPasteChunk - 1) / kPasteChunk;
   const int Sp = S + 2 * pad;
   const float scale = (float)((double)Sp / (double)S);  // transform.py:178, cast to the tensor dtype at :156
-  for (IDX v = (IDX)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (IDX)gridDim.x * blockDim.x) {
-    const IDX e0 = v << 2;
-    int i = (int)(e0 / plane);
-    const IDX pix = e0 - (IDX)i * plane;
-    int y = (int)(pix / (IDX)im_w), x = (int)(pix - (IDX)y * (IDX)im_w);
-    // fast path: the 4 elements lie in one row of one mask and entirely outside its box -> one zero store
-    PasteBox pb = paste_box(__ldg(boxes + i), scale);
-    if (x + 3 < im_w && e0 + 3 < total && (y < pb.y0 || y > pb.y1 || x + 3 < pb.x0 || x > pb.x1)) {
-      __stcs(reinterpret_cast<float4*>(out) + v, make_float4(0.f, 0.f, 0.f, 0.f));
-      continue;
-    }
-    float vals[4];
-    int cur = i;
-    int w = max(pb.x1 - pb.x0 + 1, 1), hgt = max(pb.y1 - pb.y0 + 1, 1);
-    float sx = (float)Sp / (float)w, sy = (float)Sp / (float)hgt;
+  int flip = 0;
+  for (unsigned long long c = (unsigned long long)blockIdx.x * kPasteWarps + warp; c < nchunks;
+       c += (unsigned long long)gridDim.x * kPasteWarps) {
+    const unsigned long long e0 = c * kPasteChunk;
+    const int n = (int)min((unsigned long long)kPasteChunk, total - e0);
+    const int nvec = n & ~3;
+    // walk the row pieces of the chunk (warp-uniform): (mask ii, row y, columns [x, x + len))
+    int ii = (int)(e0 / plane);
+    const unsigned long long pix0 = e0 - (unsigned long long)ii * plane;
+    int y = (int)(pix0 / (unsigned)im_w), x = (int)(pix0 - (unsigned long long)y * im_w);
+    PasteWin w = paste_win(masks, boxes, ii, S, Sp, scale);
+    float* buf = nullptr;
+    for (int off = 0; off < n;) {
+      const int len = min(im_w - x, n - off);
+      // transform.py:202-208: the pasted window is [max(x0,0), min(x1+1, W)) x [max(y0,0), min(y1+1, H))
+      const int lo = max(x, w.pb.x0), hi = min(x + len - 1, w.pb.x1);
+      if (y >= w.pb.y0 && y <= w.pb.y1 && lo <= hi) {
+        if (!buf) {  // first piece of the chunk that meets its box: take a buffer and clear it
+          buf = s_buf + flip * kPasteChunk;
+          flip ^= 1;
+          if (lane == 0) bulk_wait_read1();
+          __syncwarp();
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      float r = 0.0f;
-      if (e0 + k < total) {
-        if (i != cur) {
-          pb = paste_box(__ldg(boxes + i), scale);
-          w = max(pb.x1 - pb.x0 + 1, 1);
-          hgt = max(pb.y1 - pb.y0 + 1, 1);
-          sx = (float)Sp / (float)w;
-          sy = (float)Sp / (float)hgt;
-          cur = i;
+          for (int k = 0; k < kPasteChunk / 128; ++k)
+            reinterpret_cast<float4*>(buf)[lane + 32 * k] = make_float4(0.f, 0.f, 0.f, 0.f);
+          __syncwarp();
         }
-        // transform.py:202-208: the pasted window is [max(x0,0), min(x1+1, W)) x [max(y0,0), min(y1+1, H))
-        if (x >= pb.x0 && x <= pb.x1 && y >= pb.y0 && y <= pb.y1) {
-          int iy0, iy1, ix0, ix1;
-          float ly0, ly1, lx0, lx1;
-          bilinear_src(y - pb.y0, sy, Sp, iy0, iy1, ly0, ly1);
-          bilinear_src(x - pb.x0, sx, Sp, ix0, ix1, lx0, lx1);
-          const float* mk = masks + (int64_t)i * S * S;
-          const float top = lx0 * padded_at(mk, S, pad, iy0, ix0) + lx1 * padded_at(mk, S, pad, iy0, ix1);
-          const float bot = lx0 * padded_at(mk, S, pad, iy1, ix0) + lx1 * padded_at(mk, S, pad, iy1, ix1);
-          r = ly0 * top + ly1 * bot;
+        int iy0, iy1;
+        float ly0, ly1;
+        bilinear_src(y - w.pb.y0, w.sy, Sp, iy0, iy1, ly0, ly1);
+        float* dst = buf + off - x;  // dst[column]
+        if (Sp <= 32) {
+          // lane l keeps column l of the two padded source rows; the four taps of a pixel are shuffles
+          const float p0 = lane < Sp ? padded_at(w.mk, S, pad, iy0, lane) : 0.0f;
+          const float p1 = lane < Sp ? padded_at(w.mk, S, pad, iy1, lane) : 0.0f;
+          for (int xb = lo; xb <= hi; xb += 32) {
+            const int xx = xb + lane;
+            int ix0, ix1;
+            float lx0, lx1;
+            bilinear_src(xx - w.pb.x0, w.sx, Sp, ix0, ix1, lx0, lx1);
+            const float top = lx0 * __shfl_sync(0xffffffffu, p0, ix0) + lx1 * __shfl_sync(0xffffffffu, p0, ix1);
+            const float bot = lx0 * __shfl_sync(0xffffffffu, p1, ix0) + lx1 * __shfl_sync(0xffffffffu, p1, ix1);
+            if (xx <= hi) dst[xx] = ly0 * top + ly1 * bot;
+          }
+        } else {
+          for (int xx = lo + lane; xx <= hi; xx += 32) dst[xx] = paste_sample(w, S, pad, Sp, y, xx);
         }
-        if (++x == im_w) { x = 0; if (++y == im_h) { y = 0; ++i; } }
       }
-      vals[k] = r;
+      off += len;
+      x = 0;
+      if (++y == im_h) {
+        y = 0;
+        if (++ii < m) w = paste_win(masks, boxes, ii, S, Sp, scale);
+      }
     }
-    if (e0 + 3 < total) {
-      __stcs(reinterpret_cast<float4*>(out) + v, make_float4(vals[0], vals[1], vals[2], vals[3]));
-    } else {
-      for (int k = 0; k < 4 && e0 + k < total; ++k) out[e0 + k] = vals[k];
+    const float* src = s_zero;
+    if (buf) {
+      fence_proxy_async();
+      __syncwarp();
+      src = buf;
+    } else if (lane == 0) {
+      bulk_wait_read_n<6>();
     }
+    if (lane == 0 && nvec > 0) {
+      bulk_s2g(out + e0, src, (uint32_t)nvec * sizeof(float));
+      bulk_commit();
+    }
+    if (lane < n - nvec) out[e0 + nvec + lane] = src[nvec + lane];  // < 4 trailing floats of the whole output
   }
+  if (lane == 0) bulk_wait0();
 }
 
 // ------------------------------------------------------------------------------------------
@@ -470,16 +536,19 @@ int launch_resize_boxes(isb_handle* h, const float* in, int64_t m, float rw, flo
   ISB_LAUNCH_CHECK(h, "resize_boxes_kernel");
   return ISB_OK;
 }
+int configure_rcnn_ops(isb_handle* h) {  // once per handle (isb_create), on the handle's device
+  ISB_CUDA(h, cudaFuncSetAttribute(paste_masks_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPasteSmem));
+  return ISB_OK;
+}
 int launch_paste_masks(isb_handle* h, const float* masks, const float* boxes, int m, int S, int pad, int im_h, int im_w,
                        float* out, cudaStream_t s) {
-  const int64_t total = (int64_t)m * im_h * im_w, nvec = (total + 3) / 4;
-  if (total + 4 < (1ll << 32))
-    paste_masks_kernel<uint32_t><<<grid_for(nvec, 256, h->num_sms, 8), 256, 0, s>>>(masks, reinterpret_cast<const float4*>(boxes),
-                                                                                    m, S, pad, im_h, im_w, out);
-  else
-    paste_masks_kernel<unsigned long long><<<grid_for(nvec, 256, h->num_sms, 8), 256, 0, s>>>(
-        masks, reinterpret_cast<const float4*>(boxes), m, S, pad, im_h, im_w, out);
-  ISB_LAUNCH_CHECK(h, "paste_masks_kernel");
+  const int64_t total = (int64_t)m * im_h * im_w;  // `out` is 16-byte aligned (checked by isb_paste_masks)
+  if (total <= 0) return ISB_OK;
+  const int64_t nchunks = (total + kPasteChunk - 1) / kPasteChunk;
+  const int grid = (int)min((int64_t)h->num_sms, (nchunks + kPasteWarps - 1) / kPasteWarps);
+  paste_masks_bulk_kernel<<<grid, kPasteWarps * 32, kPasteSmem, s>>>(masks, reinterpret_cast<const float4*>(boxes), m, S, pad, im_h,
+                                                                    im_w, out);
+  ISB_LAUNCH_CHECK(h, "paste_masks_bulk_kernel");
   return ISB_OK;
 }
 int launch_paste_class_map(isb_handle* h, const float* masks, const float* boxes, const int64_t* labels, const float* scores, int m,
