@@ -318,7 +318,8 @@ __device__ __forceinline__ AxisSample axis_sample(float v, int size) {
 
 constexpr int kRoiThreads = 256;
 constexpr int kRoiAxisMax = 128;      // out * sampling_ratio per axis
-constexpr int kRoiBufFloats = 4096;   // one staging buffer (16 KB); two of them + one offset table per CTA
+constexpr int kRoiTileFloats = 8 * 1024;   // tap tiles of one pass of channels + the pass's output staging (32 KB; swept 6-18 K)
+constexpr int kRoiMaxEntries = 1024;       // (bin, sample) table entries the launcher will size shared memory for (32 KB)
 
 __device__ __forceinline__ void cp_async4(uint32_t dst_smem, const void* src_gmem) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_smem), "l"(src_gmem) : "memory");
@@ -359,25 +360,32 @@ __device__ void build_tap_list(const AxisSample* __restrict__ smp, int n, int* _
 
 // grid (RoI, channel group).  The CTA works out the RoI's FPN level and its (y, x) sample tables once, then the
 // lists of DISTINCT feature rows and columns those samples touch (at most 2 * out * sampling_ratio each, whatever
-// the RoI's size or aspect ratio) and a table of their global offsets.  Channel chunk by channel chunk the
-// ny x nx tap tile is gathered into shared memory with asynchronous copies (cp.async, double-buffered: chunk
-// k+1 is in flight while chunk k is reduced) -- one table look-up and one copy per element, no per-row
-// arithmetic -- and every output bin takes its 2 x 2 samples x 4 taps from shared memory.  The features are
-// NCHW, so a direct per-output gather costs one L1 wavefront per lane (the one-thread-per-output kernel this
-// replaces was L1-wavefront bound).  TMA tensor tiles are not usable in general here: the row pitch of an FPN
-// level need not be a multiple of 16 bytes (42 floats at the coarsest level of an 800 x 1344 input).
+// the RoI's size or aspect ratio) and, per (bin, sample), the four tap positions inside a channel tile and their
+// weights.  The group's channels go through shared memory in passes of up to 32: the ny x nx tap tile of every
+// channel of the pass is gathered with asynchronous copies (cp.async, coalesced along the feature rows; a thread owns
+// a tap and copies it for all channels of the pass), stored channel by channel with an ODD pitch.  In the reduction
+// a lane is a CHANNEL and a warp walks output bins: tap positions and weights are warp-uniform (two broadcast
+// 16-byte reads per sample), the 16 taps of a bin are 16 conflict-free shared-memory reads (lane stride = the odd
+// pitch), and there is no per-lane index arithmetic.  The first version,
+// lane = output element, spent 136 M warp instructions and 36 M shared-memory wavefronts (13 M of them bank
+// conflicts) on 1000 RoIs (ncu); this one needs about a quarter of both.  Results are staged [channel][bin] in shared
+// memory and leave as one contiguous, coalesced run per pass (the channels of a RoI are adjacent in [K,C,oh,ow]),
+// while the next pass's gather is already in flight.  TMA tensor tiles are not usable in general here: the row
+// pitch of an FPN level need not be a multiple of 16 bytes (42 floats at the coarsest level of an 800 x 1344 input).
 // SR > 0: sampling ratio known at compile time (the reference always passes 2); SR == 0: run-time value.
 template <int SR>
-__global__ void __launch_bounds__(kRoiThreads) ms_roi_align_kernel(RoiLevels L, const float4* __restrict__ boxes,
+__global__ void __launch_bounds__(kRoiThreads, 4) ms_roi_align_kernel(RoiLevels L, const float4* __restrict__ boxes,
                                                                    const int32_t* __restrict__ batch_idx, int channels,
-                                                                   int oh, int ow, int sr_rt, int cpc, float* __restrict__ out) {
+                                                                   int oh, int ow, int sr_rt, int cpc, int tile_floats, int table_cap,
+                                                                      float* __restrict__ out) {
   const int sr = SR > 0 ? SR : sr_rt;
-  extern __shared__ __align__(16) float s_buf[];  // [2][kRoiBufFloats] tiles | [kRoiBufFloats] int offsets
+  extern __shared__ __align__(16) float s_buf[];  // [kRoiTileFloats] tiles + output staging | (bin, sample) table
   __shared__ AxisSample ys[kRoiAxisMax], xs[kRoiAxisMax];
   __shared__ TapSample tys[kRoiAxisMax], txs[kRoiAxisMax];
   __shared__ int ylist[2 * kRoiAxisMax], xlist[2 * kRoiAxisMax];
   __shared__ int s_level, s_ny, s_nx;
-  int* s_goff = reinterpret_cast<int*>(s_buf + 2 * kRoiBufFloats);
+  int4* s_off = reinterpret_cast<int4*>(s_buf + tile_floats);          // tap offsets of a sample inside a channel tile
+  float4* s_wt = reinterpret_cast<float4*>(s_off + table_cap);         // its four bilinear weights
   const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int cbase = blockIdx.y * cpc, cend = min(channels, cbase + cpc);
   const float4 b = boxes[r];
@@ -412,7 +420,8 @@ __global__ void __launch_bounds__(kRoiThreads) ms_roi_align_kernel(RoiLevels L, 
   if (tid == 32) build_tap_list(xs, nx, xlist, &s_nx, txs);
   __syncthreads();
   const int nyl = s_ny, nxl = s_nx, plane = nyl * nxl;
-  const float count = (float)max(sr * sr, 1);
+  const int nsmp = sr * sr, entries = oh * ow * nsmp;
+  const float count = SR > 0 ? (float)(SR * SR) : (float)max(nsmp, 1);
   const int bins = oh * ow;
   const int img = batch_idx ? batch_idx[r] : 0;
   const float* fbase = L.feat[lvl] + (size_t)img * channels * fh * fw;
@@ -421,7 +430,8 @@ __global__ void __launch_bounds__(kRoiThreads) ms_roi_align_kernel(RoiLevels L, 
     for (int o = cbase * bins + tid; o < cend * bins; o += kRoiThreads) obase[o] = 0.0f;
     return;
   }
-  if (plane > kRoiBufFloats || nyl > 255 || nxl > 255) {  // very large out * sampling_ratio: direct gather
+  const int pitch = plane | 1;
+  if (entries > table_cap || nyl > 255 || nxl > 255 || pitch + bins > tile_floats) {  // very large out * sampling_ratio: direct gather
     for (int o = cbase * bins + tid; o < cend * bins; o += kRoiThreads) {
       const int c = o / bins, bin = o - c * bins;
       const int ph = bin / ow, pw = bin - ph * ow;
@@ -445,63 +455,74 @@ __global__ void __launch_bounds__(kRoiThreads) ms_roi_align_kernel(RoiLevels L, 
     }
     return;
   }
-  for (int i = tid; i < plane; i += kRoiThreads) {
-    const int yi = i / nxl, xi = i - yi * nxl;
-    s_goff[i] = ylist[yi] * fw + xlist[xi];
+  // (bin, sample) table: where the sample's four taps sit inside a channel tile and their weights w1..w4
+  // (roi_align's hy*hx, hy*lx, ly*hx, ly*lx).  A sample outside the map contributes 0 in the reference; here it
+  // gets four zero weights on tap 0, which is the same for finite features.
+  for (int e = tid; e < entries; e += kRoiThreads) {
+    const int bin = e / nsmp, k = e - bin * nsmp, iy = k / sr, ix = k - iy * sr;
+    const int ph = bin / ow, pw = bin - ph * ow;
+    const TapSample sy = tys[ph * sr + iy], sx = txs[pw * sr + ix];
+    int4 o = make_int4(0, 0, 0, 0);
+    float4 wq = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!((sy.idx | sx.idx) >> 16)) {
+      const float syl = sy.l, syh = 1.0f - syl, sxl = sx.l, sxh = 1.0f - sxl;
+      const int rlo = (sy.idx & 0xff) * nxl, rhi = ((sy.idx >> 8) & 0xff) * nxl;
+      const int xlo = sx.idx & 0xff, xhi = (sx.idx >> 8) & 0xff;
+      o = make_int4(rlo + xlo, rlo + xhi, rhi + xlo, rhi + xhi);
+      wq = make_float4(syh * sxh, syh * sxl, syl * sxh, syl * sxl);
+    }
+    s_off[e] = o;
+    s_wt[e] = wq;
   }
-  __syncthreads();
-  const int cg = min(kRoiBufFloats / plane, cend - cbase);
+  // channels per pass: the largest power of two <= 32 whose tiles and outputs fit
+  int cg = 32;
+  while (cg > 1 && cg * (pitch + bins) > tile_floats) cg >>= 1;
+  float* otile = s_buf + cg * pitch;
   const uint32_t sbase = smem_u32(s_buf);
-  const int nchunks = (cend - cbase + cg - 1) / cg;
-  // chunk k: channels [cbase + k * cg, ...) gathered into buffer k & 1, a warp per channel
-#define ROI_STAGE(K)                                                                     \
+  const int ch = lane & (cg - 1);                                  // lane -> (channel of the pass, bin slot)
+  const int slots = kRoiThreads / cg, slot = tid / cg;             // bin slots of the CTA (8 when cg == 32)
+  const float* tc = s_buf + ch * pitch;
+  const size_t fhw = (size_t)fh * fw;
+  // a thread owns taps tid, tid + 256, ... of the tile and copies them for every channel of the pass: the tap's global
+  // offset is worked out once, then it is one cp.async and two pointer bumps per element
+#define ROI_STAGE(C0)                                                                    \
   do {                                                                                   \
-    const int c0_ = cbase + (K) * cg, nc_ = min(cg, cend - c0_);                         \
-    const uint32_t dst_ = sbase + (((K) & 1) * kRoiBufFloats) * 4u;                      \
-    for (int c = warp; c < nc_; c += kRoiThreads / 32) {                                 \
-      const float* src_ = fbase + (size_t)(c0_ + c) * fh * fw;                           \
-      const uint32_t d_ = dst_ + (uint32_t)(c * plane) * 4u;                             \
-      for (int i = lane; i < plane; i += 32) cp_async4(d_ + 4u * i, src_ + s_goff[i]);   \
+    const int nc_ = min(cg, cend - (C0));                                                \
+    const float* src0_ = fbase + (size_t)(C0) * fhw;                                     \
+    for (int i = tid; i < plane; i += kRoiThreads) {                                     \
+      const int yi = i / nxl, xi = i - yi * nxl;                                         \
+      const float* src_ = src0_ + (ylist[yi] * fw + xlist[xi]);                          \
+      uint32_t d_ = sbase + 4u * i;                                                      \
+      _Pragma("unroll 4") for (int c = 0; c < nc_; ++c) {                                \
+        cp_async4(d_, src_);                                                             \
+        src_ += fhw;                                                                     \
+        d_ += 4u * pitch;                                                                \
+      }                                                                                  \
     }                                                                                    \
     cp_async_commit();                                                                   \
   } while (0)
-  ROI_STAGE(0);
-  for (int k = 0; k < nchunks; ++k) {
-    const int c0 = cbase + k * cg, nc = min(cg, cend - c0);
-    if (k + 1 < nchunks) {
-      ROI_STAGE(k + 1);
-      cp_async_wait1();
-    } else {
-      cp_async_wait0();
-    }
-    __syncthreads();
-    const float* tile = s_buf + (k & 1) * kRoiBufFloats;
-    for (int o = tid; o < nc * bins; o += kRoiThreads) {
-      const int c = o / bins, bin = o - c * bins;
-      const int ph = bin / ow, pw = bin - ph * ow;
-      const int pbase = c * plane;
-      float acc = 0.0f;
+  ROI_STAGE(cbase);
+  for (int c0 = cbase; c0 < cend; c0 += cg) {
+    const int nc = min(cg, cend - c0);
+    cp_async_wait0();
+    __syncthreads();  // tiles of this pass (and, the first time, the sample table) complete; otile is free again
+    if (ch < nc) {
+      for (int bin = slot; bin < bins; bin += slots) {
+        float acc = 0.0f;
+        const int e0 = bin * nsmp;
 #pragma unroll
-      for (int iy = 0; iy < (SR > 0 ? SR : sr); ++iy) {
-        const TapSample sy = tys[ph * sr + iy];
-        const float syl = sy.l, syh = 1.0f - syl;
-        const int rlo = pbase + (sy.idx & 0xff) * nxl, rhi = pbase + ((sy.idx >> 8) & 0xff) * nxl;
-#pragma unroll
-        for (int ix = 0; ix < (SR > 0 ? SR : sr); ++ix) {
-          const TapSample sx = txs[pw * sr + ix];
-          float val = 0.0f;
-          if (!((sy.idx | sx.idx) >> 16)) {
-            const float sxl = sx.l, sxh = 1.0f - sxl;
-            const int xlo = sx.idx & 0xff, xhi = (sx.idx >> 8) & 0xff;
-            const float w1 = syh * sxh, w2 = syh * sxl, w3 = syl * sxh, w4 = syl * sxl;
-            val = ((w1 * tile[rlo + xlo] + w2 * tile[rlo + xhi]) + w3 * tile[rhi + xlo]) + w4 * tile[rhi + xhi];
-          }
-          acc += val;
+        for (int k = 0; k < (SR > 0 ? SR * SR : nsmp); ++k) {
+          const int4 o = s_off[e0 + k];
+          const float4 wq = s_wt[e0 + k];
+          acc += ((wq.x * tc[o.x] + wq.y * tc[o.y]) + wq.z * tc[o.z]) + wq.w * tc[o.w];
         }
+        otile[ch * bins + bin] = acc / count;
       }
-      obase[(size_t)c0 * bins + o] = acc / count;
     }
-    __syncthreads();  // buffer (k & 1) is free for chunk k + 2
+    __syncthreads();  // tiles consumed, outputs staged
+    if (c0 + cg < cend) ROI_STAGE(c0 + cg);
+    float* dst = obase + (size_t)c0 * bins;
+    for (int o = tid; o < nc * bins; o += kRoiThreads) dst[o] = otile[o];
   }
 #undef ROI_STAGE
 }
@@ -568,25 +589,30 @@ int launch_paste_class_map(isb_handle* h, const float* masks, const float* boxes
 int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, const int32_t* batch_idx, int num_rois,
                         int channels, int oh, int ow, int sr, float* out, cudaStream_t s) {
   if (!h->roi_configured) {
-    ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)(3 * kRoiBufFloats * sizeof(float))));
-    ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)(3 * kRoiBufFloats * sizeof(float))));
+    const int max_smem = (int)(kRoiTileFloats * sizeof(float) + (size_t)kRoiMaxEntries * 32);
+    ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
     h->roi_configured = 1;
   }
-  // channel groups per RoI: enough CTAs to fill the GPU about a dozen times over, at least 8 channels each
+  // shared memory: the tile budget + a (bin, sample) table of exactly this call's size (more entries than the cap: the
+  // kernel's direct-gather path, no table)
+  const int tile_floats = kRoiTileFloats;
+  int table_cap = oh * ow * sr * sr;
+  if (table_cap > kRoiMaxEntries) table_cap = 0;
+  const size_t smem = (size_t)tile_floats * sizeof(float) + (size_t)table_cap * 32;
+  // channel groups per RoI: enough CTAs to fill the GPU about a dozen times over, whole passes of 32 channels each
   int groups = (12 * h->num_sms + num_rois - 1) / num_rois;
-  if (groups > (channels + 7) / 8) groups = (channels + 7) / 8;
+  if (groups > (channels + 31) / 32) groups = (channels + 31) / 32;
   if (groups < 1) groups = 1;
   int cpc = (channels + groups - 1) / groups;
-  cpc = (cpc + 7) & ~7;
+  cpc = (cpc + 31) & ~31;
   groups = (channels + cpc - 1) / cpc;
   if (sr == 2)
-    ms_roi_align_kernel<2><<<dim3(num_rois, groups), kRoiThreads, 3 * kRoiBufFloats * sizeof(float), s>>>(
-        L, reinterpret_cast<const float4*>(boxes), batch_idx, channels, oh, ow, sr, cpc, out);
+    ms_roi_align_kernel<2><<<dim3(num_rois, groups), kRoiThreads, smem, s>>>(
+        L, reinterpret_cast<const float4*>(boxes), batch_idx, channels, oh, ow, sr, cpc, tile_floats, table_cap, out);
   else
-    ms_roi_align_kernel<0><<<dim3(num_rois, groups), kRoiThreads, 3 * kRoiBufFloats * sizeof(float), s>>>(
-        L, reinterpret_cast<const float4*>(boxes), batch_idx, channels, oh, ow, sr, cpc, out);
+    ms_roi_align_kernel<0><<<dim3(num_rois, groups), kRoiThreads, smem, s>>>(
+        L, reinterpret_cast<const float4*>(boxes), batch_idx, channels, oh, ow, sr, cpc, tile_floats, table_cap, out);
   ISB_LAUNCH_CHECK(h, "ms_roi_align_kernel");
   return ISB_OK;
 }
