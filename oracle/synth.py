@@ -162,3 +162,21 @@ def box_head_outputs(seed, n=1000, num_classes=21, image_hw=(800, 1333), hot=60)
     logits[rows, cls] += torch.rand(hot * 4, generator=g) * 6.0 + 2.0
     reg = torch.randn(n, 4 * num_classes, generator=g) * torch.tensor([1.0, 1.0, 0.5, 0.5]).repeat(num_classes)
     return proposals, logits.contiguous(), reg.contiguous()
+
+
+def picture(seed, h, w):
+    """Seeded photo-like uint8 [h, w, 3] picture: linear colour ramps, a few hard-edged rectangles and integer noise.
+    Only integer draws from numpy's RandomState and exact integer arithmetic, so the GPU box re-draws the same
+    bytes whatever its CPU / libm.  Input of the pre-processing row."""
+    rs = np.random.RandomState(int(seed))
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.int64)
+    img = np.zeros((h, w, 3), np.int64)
+    for c in range(3):
+        ay, ax, base = rs.randint(-200, 201), rs.randint(-200, 201), rs.randint(60, 196)
+        img[..., c] = base + (ay * yy) // max(h, 1) + (ax * xx) // max(w, 1)
+    for _ in range(12):
+        y0, x0 = rs.randint(0, max(h, 2)), rs.randint(0, max(w, 2))
+        y1, x1 = y0 + rs.randint(1, max(h // 3, 2)), x0 + rs.randint(1, max(w // 3, 2))
+        img[y0:y1, x0:x1] = rs.randint(0, 256, 3)
+    img += rs.randint(-8, 9, img.shape)
+    return np.clip(img, 0, 255).astype(np.uint8)
