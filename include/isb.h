@@ -142,6 +142,21 @@ ISB_API int isb_yolact_class_map(isb_handle* h, const isb_yolact_in* in, const i
 ISB_API int isb_yolact_class_map_host(isb_handle* h, const isb_yolact_in* in, const isb_yolact_map_out* out, isb_stream stream);
 
 /* ------------------------------------------------------------------------------------
+ * Wrapper pre-processing, for a batch of same-sized pictures.
+ * Replaces inst_model/yolact/yolact.py:137-148 and inst_model/Mask_RCNN/mask_rcnn.py:140-148:
+ *     resize_image(image, (W_in, H_in))          utils/utils.py:19-22, PIL Image.resize(.., Image.BICUBIC)
+ *     preprocess_input(np.array(.., float32))    utils/utils.py:32-36, (x - mean) / std in float64
+ *     transpose(2, 0, 1)[None] -> FloatTensor    yolact.py:145-148
+ * The resize follows Pillow's 8-bit fixed-point resampling (libImaging/Resample.c) bit for bit.
+ *   images:  device uint8 [B, in_h, in_w, 3] (RGB, HWC);
+ *   mean, std: 3 doubles each (utils.py:33-34: 123.68, 116.78, 103.94 / 58.40, 57.12, 57.38);
+ *   resized: device uint8 [B, out_h, out_w, 3] = the PIL image resize_image returns, or NULL;
+ *   input:   device float32 [B, 3, out_h, out_w] = the tensor the wrapper feeds the network, or NULL.
+ * ---------------------------------------------------------------------------------- */
+ISB_API int isb_preprocess(isb_handle* h, const uint8_t* images, int32_t batch, int32_t in_h, int32_t in_w, int32_t out_h,
+                   int32_t out_w, const double* mean, const double* std, uint8_t* resized, float* input, isb_stream stream);
+
+/* ------------------------------------------------------------------------------------
  * COCO run-length encoding of the instance masks on the device.
  * Replaces the per-instance host call inst_model/yolact/utils/utils_map.py:33-34
  *     pycocotools.mask.encode(np.asfortranarray(segmentation.astype(np.uint8)))

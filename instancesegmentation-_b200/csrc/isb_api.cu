@@ -8,6 +8,7 @@ namespace isb {
 int configure_fast_nms(isb_handle* h);
 int configure_masks(isb_handle* h);
 int configure_rcnn_ops(isb_handle* h);
+void destroy_preprocess(isb_handle* h);
 int configure_candidates(isb_handle* h);
 int launch_decode_boxes(isb_handle*, const float*, const float*, int64_t, float, float, float*, cudaStream_t);
 int launch_jaccard(isb_handle*, const float*, const float*, int, int, int, int, float*, cudaStream_t);
@@ -107,6 +108,7 @@ static void free_ws(isb_handle* h) {
 extern "C" void isb_destroy(isb_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
+  destroy_preprocess(h);
   free_ws(h);
   delete h;
 }

@@ -343,6 +343,7 @@ struct isb_handle {
   void* scratch;
   size_t scratch_bytes;
   int roi_configured;      // ms_roi_align_kernel's dynamic shared memory limit has been raised
+  void* prep;              // pre-processing state (preprocess.cu): coefficient tables, intermediate image, value table
   // optional per-stage event ring (isb_profile_begin / isb_profile_read)
   cudaEvent_t* prof_events;  // [prof_cap][5]
   cudaEvent_t prof_mid;      // set while a profiled call is inside launch_masks

@@ -1,0 +1,87 @@
+"""GPU parity of the pre-processing row (isb_preprocess behind isb.preprocess): Pillow's 8-bit bicubic resize and the
+wrappers' normalisation, bit-exact against the Pillow / reference-generated goldens and the numpy oracle."""
+import hashlib
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+from oracle import preprocess_np as P
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def pre():
+    from isb import preprocess
+    return preprocess
+
+
+def _sha(a):
+    return hashlib.sha1(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def test_small_cases_bit_exact(pre):
+    g = load_golden("preprocess")
+    for i in range(int(g["num_small"])):
+        img, resized, net_in = g[f"s{i}_in"], g[f"s{i}_resized"], g[f"s{i}_input"]
+        shape = resized.shape[:2]
+        out, res = pre.image_to_input(img, shape, return_resized=True)
+        assert out.shape == (1, 3) + shape and out.dtype == torch.float32 and out.is_cuda
+        assert np.array_equal(res[0].cpu().numpy(), resized), f"case {i}: {img.shape} -> {resized.shape}"
+        assert np.array_equal(out.cpu().numpy(), net_in)
+        pil = pre.resize_image(img, (shape[1], shape[0]))
+        assert pil.size == (shape[1], shape[0]) and np.array_equal(np.array(pil), resized)
+        assert np.array_equal(pre.preprocess_input(resized).cpu().numpy(), net_in)
+
+
+@pytest.mark.parametrize("tag", ["full544", "full550", "up"])
+def test_full_size_bit_exact(pre, tag):
+    g = load_golden("preprocess")
+    h, w = [int(v) for v in g[f"{tag}_hw"]]
+    shape = tuple(int(v) for v in g[f"{tag}_shape"])
+    img = synth.picture(int(g[f"{tag}_seed"]), h, w)
+    assert _sha(img) == str(g[f"{tag}_in_sha"])
+    out, res = pre.image_to_input(img, shape, return_resized=True)
+    res, out = res[0].cpu().numpy(), out.cpu().numpy()
+    assert np.array_equal(res[::9, ::7], g[f"{tag}_resized_sub"])
+    assert _sha(res) == str(g[f"{tag}_resized_sha"])
+    assert np.array_equal(out[:, :, ::9, ::7], g[f"{tag}_input_sub"])
+    assert _sha(out) == str(g[f"{tag}_input_sha"])
+
+
+def test_batch_and_other_sizes_vs_oracle(pre):
+    """A batch of pictures in one call, strong reductions (many taps), one unchanged axis, a single-pixel source and
+    other mean / std values, against the numpy oracle."""
+    rng = np.random.RandomState(11)
+    for (h, w), (oh, ow), b in [((120, 90), (17, 23), 3), ((64, 200), (64, 31), 2), ((77, 50), (20, 50), 2), ((1, 1), (9, 5), 1),
+                               ((300, 500), (31, 29), 2), ((40, 30), (128, 97), 4)]:
+        imgs = rng.randint(0, 256, (b, h, w, 3), dtype=np.uint8)
+        mean, std = (100.0, 110.5, 90.25), (50.0, 60.5, 70.125)
+        out, res = pre.image_to_input(imgs, (oh, ow), mean=mean, std=std, return_resized=True)
+        assert out.shape == (b, 3, oh, ow) and res.shape == (b, oh, ow, 3)
+        for i in range(b):
+            ref = P.resize_u8(imgs[i], ow, oh)
+            assert np.array_equal(res[i].cpu().numpy(), ref), f"{(h, w)} -> {(oh, ow)} image {i}"
+            assert np.array_equal(out[i:i + 1].cpu().numpy(), P.normalize_chw(ref, mean, std))
+
+
+def test_value_table_follows_mean_std(pre):
+    img = synth.picture(5, 40, 60)
+    a = pre.image_to_input(img, (20, 30)).cpu().numpy()
+    b = pre.image_to_input(img, (20, 30), mean=(0.0, 0.0, 0.0), std=(1.0, 1.0, 1.0)).cpu().numpy()
+    c = pre.image_to_input(img, (20, 30)).cpu().numpy()
+    assert np.array_equal(a, c) and np.array_equal(a, P.image_to_input(img, (20, 30)))
+    assert np.array_equal(b[0], np.transpose(P.resize_u8(img, 30, 20), (2, 0, 1)).astype(np.float32))
+
+
+def test_error_convention(pre):
+    from isb._lib import IsbError
+    with pytest.raises((IsbError, ValueError, TypeError)):
+        pre.image_to_input(np.zeros((4, 4, 4), np.uint8), (2, 2))
+    with pytest.raises(IsbError):
+        pre.image_to_input(np.zeros((4, 4, 3), np.uint8), (2, 2), std=(1.0, 0.0, 1.0))
+    with pytest.raises(IsbError):
+        pre.image_to_input(np.zeros((2, 4000, 3), np.uint8), (2, 100))      # 40:1 reduction: more taps than staged
