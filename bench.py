@@ -380,6 +380,21 @@ def run_gpu(args):
     softmax_ms = ev0.elapsed_time(ev1) / cm_steps
     del logits_d, lg_in
 
+    # ---- pre-processing variant (PIL bicubic resize + normalisation of yolact.py:137-148) -- extra keys only
+    from isb import preprocess as pre
+    pics = torch.randint(0, 256, (bsz, 1080, 1920, 3), dtype=torch.uint8, device=dev)
+    for _ in range(3):
+        pre.image_to_input(pics, shape)
+    torch.cuda.synchronize()
+    ev0.record()
+    for _ in range(cm_steps):
+        pre.image_to_input(pics, shape)
+    ev1.record()
+    torch.cuda.synchronize()
+    pre_ms = ev0.elapsed_time(ev1) / cm_steps
+    pre_bytes = bsz * (1080 * 1920 * 3 + shape[0] * shape[1] * 12)
+    del pics
+
     if world > 1:
         t = torch.tensor([ms, e2e_s, cm_ms, cm_e2e_s], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -425,6 +440,10 @@ def run_gpu(args):
                                         "value": bsz / (lg_ms * 1e-3), "ms_per_step": lg_ms, "unit": UNIT + " (this rank)",
                                         "candidates_ms": lg_stage[0] / max(lg_calls, 1),
                                         "torch_softmax_ms_it_replaces": softmax_ms},
+                "preprocess_variant": {"what": "wrapper pre-processing on the device (SURVEY 8f rank 4): 1080x1920 uint8 pictures "
+                                               "-> Pillow-exact bicubic resize -> normalised float32 CHW network input; "
+                                               "not the headline", "value": bsz / (pre_ms * 1e-3), "unit": "pictures/s (this rank)",
+                                       "ms_per_step": pre_ms, "algorithmic_GBs": pre_bytes / (pre_ms * 1e-3) / 1e9},
                 "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -19,7 +19,6 @@ namespace isb {
 
 constexpr int kPrecisionBits = 32 - 8 - 2;
 constexpr int kPrepThreads = 128;
-constexpr int kPrepMaxTaps = 64;  // taps per output sample the horizontal kernel stages (reductions up to ~15:1)
 
 struct AxisTable {
   int in_size, out_size, ksize;
@@ -195,7 +194,6 @@ int launch_preprocess(isb_handle* h, const uint8_t* images, int batch, int in_h,
     tx = &txv;
   }
   if ((rc = get_axis(h, st, in_h, out_h, &tyv)) != ISB_OK) return rc;  // unchanged height: unit coefficients, same bytes
-  if (tx && tx->ksize > kPrepMaxTaps) ISB_FAIL(h, ISB_ERR_LIMIT, "preprocess: horizontal reduction %d -> %d needs %d taps (max %d)", in_w, out_w, tx->ksize, kPrepMaxTaps);
   if (input) {
     bool same = st->lut_valid;
     for (int c = 0; c < 3 && same; ++c) same = st->mean[c] == mean[c] && st->stdv[c] == stdv[c];
@@ -224,6 +222,7 @@ int launch_preprocess(isb_handle* h, const uint8_t* images, int batch, int in_h,
     // shared memory: the input columns one block of outputs can touch
     const double scale = (double)in_w / (double)out_w;
     const size_t smem = (size_t)((int)ceil(kPrepThreads * scale) + tx->ksize + 2) * 3;
+    if (smem > 48 * 1024) ISB_FAIL(h, ISB_ERR_LIMIT, "preprocess: horizontal reduction %d -> %d is too strong for the staged row span", in_w, out_w);
     prep_horizontal_kernel<<<dim3((out_w + kPrepThreads - 1) / kPrepThreads, in_h, batch), kPrepThreads, smem, s>>>(
         images, in_h, in_w, out_w, tx->ksize, tx->d_bounds, tx->d_coef, st->temp);
     ISB_LAUNCH_CHECK(h, "prep_horizontal_kernel");

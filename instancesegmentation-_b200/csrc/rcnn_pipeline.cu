@@ -16,7 +16,9 @@ struct LevelTopK { int k[8]; };  // min(pre_nms_top_n, level size)
 // Every anchor has a unique 52-bit rank key  ~logit (32 bits, smaller = better) | anchor index (20 bits), i.e.
 // score descending with ties by ascending index.  The k-th smallest key of each level is found digit by digit
 // (11, 11, 11, 11, 8 bits): pass p histograms the digit of the anchors that match the prefix chosen so far; the
-// next launch resolves that histogram (every CTA redundantly, 2048 bins) before it filters.  The objectness
+// next launch resolves that histogram (every CTA redundantly, 2048 bins) before it filters.  As soon as the chosen bin
+// holds exactly the keys still wanted -- after the third digit at the latest when the logits are distinct, at once
+// for a level with no more than k anchors -- the level is done and the remaining passes return immediately.  The objectness
 // map (1 MB, L2-resident) is read six times; nothing is sorted until the exactly k survivors per level are
 // known, so the full sort of 2^19 keys this replaces shrinks to one of 8192.
 constexpr int kSelBins = 2048;
@@ -25,7 +27,7 @@ constexpr int kSelThreads = 256;
 __device__ __constant__ int kSelShift[kSelPasses] = {41, 30, 19, 8, 0};
 __device__ __constant__ int kSelBits[kSelPasses] = {11, 11, 11, 11, 8};
 
-struct SelState { unsigned long long prefix; int k_rem; int pad; };
+struct SelState { unsigned long long prefix; int k_rem; int done; };  // done: the chosen bin is taken whole, later digits are moot
 
 __device__ __forceinline__ uint64_t rpn_rank_key(float logit, uint32_t index) {
   return ((uint64_t)float_desc_bits(logit) << kRowBits) | index;
@@ -33,8 +35,15 @@ __device__ __forceinline__ uint64_t rpn_rank_key(float logit, uint32_t index) {
 
 // Resolve the histogram of pass `p` (p >= 0) given the state before it: pick the digit whose cumulative count
 // reaches k_rem.  Called by all threads of a 256-thread CTA; the result is returned to every thread.
-__device__ SelState sel_resolve(SelState st, const int* __restrict__ hist, int p, int* s_scan /* [32] */, int* s_res /* [2] */) {
+__device__ SelState sel_resolve(SelState st, const int* __restrict__ hist, int p, int* s_scan /* [32] */, int* s_res /* [3] */) {
   const int tid = threadIdx.x;
+  if (st.done) {  // every key under the prefix is selected: the k-th key is the largest one under it
+    SelState out;
+    out.prefix = (st.prefix << kSelBits[p]) | (unsigned long long)((1 << kSelBits[p]) - 1);
+    out.k_rem = st.k_rem;
+    out.done = 1;
+    return out;
+  }
   int v[kSelBins / kSelThreads];
   int sum = 0;
 #pragma unroll
@@ -42,20 +51,21 @@ __device__ SelState sel_resolve(SelState st, const int* __restrict__ hist, int p
   int total;
   int excl = cta_exclusive_scan(sum, s_scan, &total);
   if (excl < st.k_rem && st.k_rem <= excl + sum) {  // exactly one thread
-    int b = 0;
+    int b = 0, vb = 0;
 #pragma unroll
     for (int i = 0; i < kSelBins / kSelThreads; ++i) {
-      if (excl + v[i] >= st.k_rem) { b = i; break; }
+      if (excl + v[i] >= st.k_rem) { b = i; vb = v[i]; break; }
       excl += v[i];
     }
     s_res[0] = tid * (kSelBins / kSelThreads) + b;
     s_res[1] = st.k_rem - excl;
+    s_res[2] = vb == st.k_rem - excl;  // the bin holds exactly the keys still wanted (always true once keys are unique)
   }
   __syncthreads();
   SelState out;
   out.prefix = (st.prefix << kSelBits[p]) | (unsigned long long)s_res[0];
   out.k_rem = s_res[1];
-  out.pad = 0;
+  out.done = s_res[2];
   __syncthreads();
   return out;
 }
@@ -69,19 +79,20 @@ __global__ void __launch_bounds__(kSelThreads) rpn_select_pass_kernel(const floa
                                                                       int32_t* __restrict__ cand_count) {
   __shared__ int s_hist[kSelBins];
   __shared__ int s_scan[32];
-  __shared__ int s_res[2];
+  __shared__ int s_res[3];
   const int l = blockIdx.y, tid = threadIdx.x;
   const int begin = lv.start[l], end = lv.start[l + 1];
   if (begin >= end) return;
   // state[p] = prefix / remaining rank after the histogram of pass p - 1 has been resolved (written by launch p)
   SelState st;
-  st.prefix = 0; st.k_rem = topk.k[l]; st.pad = 0;
+  st.prefix = 0; st.k_rem = topk.k[l]; st.done = 0;
   if (pass > 0) {
     if (pass > 1) st = state[(size_t)(pass - 1) * num_levels + l];
     st = sel_resolve(st, hist + ((size_t)(pass - 1) * num_levels + l) * kSelBins, pass - 1, s_scan, s_res);
     if (blockIdx.x == 0 && tid == 0) state[(size_t)pass * num_levels + l] = st;
   }
   if (pass < kSelPasses) {
+    if (st.done) return;  // nothing left to decide for this level: no histogram (the next launch fills the prefix with ones)
     for (int i = tid; i < kSelBins; i += kSelThreads) s_hist[i] = 0;
     __syncthreads();
     const int shift = kSelShift[pass], mask = (1 << kSelBits[pass]) - 1;

@@ -84,4 +84,4 @@ def test_error_convention(pre):
     with pytest.raises(IsbError):
         pre.image_to_input(np.zeros((4, 4, 3), np.uint8), (2, 2), std=(1.0, 0.0, 1.0))
     with pytest.raises(IsbError):
-        pre.image_to_input(np.zeros((2, 4000, 3), np.uint8), (2, 100))      # 40:1 reduction: more taps than staged
+        pre.image_to_input(np.zeros((2, 60000, 3), np.uint8), (2, 100))     # 600:1 reduction: row span beyond shared memory
