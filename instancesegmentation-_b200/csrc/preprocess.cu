@@ -24,6 +24,8 @@ struct AxisTable {
   int in_size, out_size, ksize;
   int32_t* d_bounds;  // [out][2]  first tap, tap count
   int32_t* d_coef;    // [ksize][out]  (transposed: consecutive outputs are adjacent)
+  int groups;         // ceil(ksize / 4)
+  uint32_t* d_pack;   // [groups][3][out]: byte slices 0..2 of the coefficients of taps 4g..4g+3, one byte per tap (dp4a operand)
 };
 
 struct PrepState {
@@ -76,6 +78,20 @@ static int build_axis(isb_handle* h, int in_size, int out_size, AxisTable* t) {
   t->in_size = in_size;
   t->out_size = out_size;
   t->ksize = ksize;
+  // coefficient k = k2 * 65536 + k1 * 256 + k0 with k0, k1 unsigned bytes and k2 a signed byte (|k| < 2^23): the
+  // horizontal pass forms sum(pixel * k) as three 4-way byte dot products per group of four taps
+  const int groups = (ksize + 3) / 4;
+  std::vector<uint32_t> pack((size_t)groups * 3 * out_size, 0u);
+  for (int xx = 0; xx < out_size; ++xx)
+    for (int x = 0; x < ksize; ++x) {
+      const int32_t k = coef[(size_t)x * out_size + xx];
+      if (k >= (1 << 23) || k < -(1 << 23)) ISB_FAIL(h, ISB_ERR_LIMIT, "preprocess: coefficient out of the 24-bit range");
+      const uint32_t slice[3] = {(uint32_t)k & 0xffu, ((uint32_t)k >> 8) & 0xffu, ((uint32_t)(k >> 16)) & 0xffu};
+      for (int j = 0; j < 3; ++j) pack[((size_t)(x >> 2) * 3 + j) * out_size + xx] |= slice[j] << (8 * (x & 3));
+    }
+  t->groups = groups;
+  ISB_CUDA(h, cudaMalloc((void**)&t->d_pack, pack.size() * sizeof(uint32_t)));
+  ISB_CUDA(h, cudaMemcpy(t->d_pack, pack.data(), pack.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
   ISB_CUDA(h, cudaMalloc((void**)&t->d_bounds, bounds.size() * sizeof(int32_t)));
   ISB_CUDA(h, cudaMalloc((void**)&t->d_coef, coef.size() * sizeof(int32_t)));
   ISB_CUDA(h, cudaMemcpy(t->d_bounds, bounds.data(), bounds.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
@@ -101,68 +117,184 @@ __device__ __forceinline__ uint8_t clip8(int acc) {
   return (uint8_t)min(max(v, 0), 255);
 }
 
-// Horizontal pass (ImagingResampleHorizontal_8bpc): grid (column blocks, rows, images), thread = output column.
-// The row bytes a block needs (the taps of its first to its last column) are staged in shared memory with coalesced
-// loads; the coefficient table is transposed so that neighbouring columns read neighbouring words.
-__global__ void __launch_bounds__(kPrepThreads)
-prep_horizontal_kernel(const uint8_t* __restrict__ src, int in_h, int in_w, int out_w, int ksize,
-                       const int32_t* __restrict__ bounds, const int32_t* __restrict__ coef, uint8_t* __restrict__ dst) {
-  extern __shared__ uint8_t s_row[];
-  const int xx0 = blockIdx.x * kPrepThreads, xx1 = min(xx0 + kPrepThreads, out_w) - 1;
-  const int y = blockIdx.y, b = blockIdx.z;
-  const int span0 = bounds[2 * xx0], span1 = bounds[2 * xx1] + bounds[2 * xx1 + 1];  // [span0, span1) input columns
-  const uint8_t* row = src + ((size_t)b * in_h + y) * (size_t)in_w * 3;
-  for (int i = threadIdx.x; i < (span1 - span0) * 3; i += kPrepThreads) s_row[i] = row[(size_t)span0 * 3 + i];
-  __syncthreads();
-  const int xx = xx0 + threadIdx.x;
-  if (xx >= out_w) return;
-  const int xmin = bounds[2 * xx], xmax = bounds[2 * xx + 1];
-  int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
-  const uint8_t* p = s_row + (xmin - span0) * 3;
-  for (int x = 0; x < xmax; ++x) {
-    const int k = coef[(size_t)x * out_w + xx];
-    a0 += (int)p[3 * x] * k;
-    a1 += (int)p[3 * x + 1] * k;
-    a2 += (int)p[3 * x + 2] * k;
-  }
-  uint8_t* o = dst + (((size_t)b * in_h + y) * out_w + xx) * 3;
-  o[0] = clip8(a0);
-  o[1] = clip8(a1);
-  o[2] = clip8(a2);
+// Horizontal pass (ImagingResampleHorizontal_8bpc): grid (blocks of 128 output columns, groups of kPrepRows rows,
+// pictures), thread = output column.  Row after row, the input pixels the block's columns can touch -- the taps of its
+// first to its last column -- are staged in one of two shared-memory buffers (the next row is in flight while this one
+// is reduced: one barrier per row), DE-INTERLEAVED into one byte plane per channel.  A staging thread owns 4 pixels =
+// 12 bytes: aligned 32-bit loads, funnel shifts for the row's byte misalignment, six byte permutes, one 32-bit store
+// per plane.  In a plane the taps of a column are consecutive bytes, so a thread reads them as aligned words, realigns
+// them with funnel shifts and multiplies four taps at a time with dp4a: the coefficient k is split on the host into
+// k0 + 256 k1 + 65536 k2 (unsigned, unsigned, signed bytes), one packed word per slice and group of four taps, held in
+// registers for all rows of the block; sum(pixel * k) = s0 + 256 s1 + 65536 s2 exactly.  No per-byte extraction, and
+// neighbouring columns start ~scale bytes apart in a plane, so a warp's loads fall into at most 32 consecutive words
+// (no bank conflicts; the interleaved layout cost 100 M conflict wavefronts of 185 M, ncu).  The result goes to an
+// intermediate 8-bit image whose row pitch is a multiple of 16 bytes, so that the vertical pass can read it with
+// aligned 32-bit loads whatever the output width.  NG = groups of four taps (template: coefficients in registers);
+// NG = 0: any tap count, coefficients re-read through L1.
+constexpr int kPrepRows = 16;
+constexpr int kPrepMaxGroups = 6;  // register-resident coefficients up to 24 taps (reductions up to 5.5 : 1)
+
+__device__ __forceinline__ uint32_t load_word_guarded(const uint8_t* p, const uint8_t* lo, const uint8_t* hi) {
+  if (p >= lo && p + 4 <= hi) return __ldg(reinterpret_cast<const uint32_t*>(p));
+  uint32_t w = 0;  // a word straddling the end of the caller's buffer: byte by byte
+  for (int k = 0; k < 4; ++k)
+    if (p + k >= lo && p + k < hi) w |= (uint32_t)p[k] << (8 * k);
+  return w;
 }
 
-// Vertical pass (ImagingResampleVertical_8bpc) + normalisation + HWC -> CHW: grid (column blocks, rows, images),
-// thread = output column; the row's taps and coefficients are block-uniform.
+__device__ __forceinline__ int dp4a_uu(uint32_t a, uint32_t b, int c) {
+  int d;
+  asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {  // a: unsigned bytes, b: signed bytes
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+
+template <int NG>
 __global__ void __launch_bounds__(kPrepThreads)
-prep_vertical_kernel(const uint8_t* __restrict__ src, int in_h, int out_h, int out_w, int ksize,
+prep_horizontal_kernel(const uint8_t* __restrict__ src, size_t src_bytes, int in_h, int in_w, int out_w, int groups, int plane_cap,
+                       const int32_t* __restrict__ bounds, const uint32_t* __restrict__ pack, uint8_t* __restrict__ dst, int tpitch) {
+  extern __shared__ __align__(16) uint32_t s_planes[];  // [2 buffers][3 planes][plane_cap / 4 words]
+  const int tid = threadIdx.x;
+  const int xx0 = blockIdx.x * kPrepThreads, xx1 = min(xx0 + kPrepThreads, out_w) - 1, xx = xx0 + tid;
+  const int xc = min(xx, out_w - 1);  // threads past the last column compute a duplicate and do not store
+  const int y0 = blockIdx.y * kPrepRows, y1 = min(y0 + kPrepRows, in_h), b = blockIdx.z;
+  const int span0 = bounds[2 * xx0], span1 = bounds[2 * xx1] + bounds[2 * xx1 + 1];  // input columns [span0, span1)
+  const int units = (span1 - span0 + 3) >> 2;  // groups of 4 pixels
+  const int pw = plane_cap >> 2;               // words per plane
+  const int o = bounds[2 * xc] - span0;        // first tap of this column inside the planes
+  const int wi = o >> 2, sh = (o & 3) * 8;
+  uint32_t K[NG > 0 ? NG : 1][3];
+  if (NG > 0) {
+#pragma unroll
+    for (int g = 0; g < NG; ++g)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) K[g][j] = g < groups ? pack[((size_t)g * 3 + j) * out_w + xc] : 0u;
+  }
+  const uint8_t* src_end = src + src_bytes;
+  auto stage = [&](int y, uint32_t* buf) {
+    const uint8_t* row = src + (((size_t)b * in_h + y) * (size_t)in_w + span0) * 3;
+    const int rsh = (int)(reinterpret_cast<uintptr_t>(row) & 3) * 8;  // 12 bytes per unit: the same for every unit of the row
+    const uint8_t* arow = row - (rsh >> 3);
+    const bool inside = arow >= src && arow + (size_t)units * 12 + 4 <= src_end;  // block-uniform
+    for (int u = tid; u < units; u += kPrepThreads) {
+      const uint8_t* p = arow + u * 12;
+      uint32_t w0, w1, w2, w3;
+      if (inside) {
+        const uint32_t* q = reinterpret_cast<const uint32_t*>(p);
+        w0 = __ldg(q); w1 = __ldg(q + 1); w2 = __ldg(q + 2); w3 = __ldg(q + 3);
+      } else {
+        w0 = load_word_guarded(p, src, src_end); w1 = load_word_guarded(p + 4, src, src_end);
+        w2 = load_word_guarded(p + 8, src, src_end); w3 = load_word_guarded(p + 12, src, src_end);
+      }
+      // f0 = [r0 g0 b0 r1]  f1 = [g1 b1 r2 g2]  f2 = [b2 r3 g3 b3]
+      const uint32_t f0 = __funnelshift_r(w0, w1, rsh), f1 = __funnelshift_r(w1, w2, rsh), f2 = __funnelshift_r(w2, w3, rsh);
+      buf[u] = __byte_perm(__byte_perm(f0, f1, 0x0630), f2, 0x5210);
+      buf[pw + u] = __byte_perm(__byte_perm(f0, f1, 0x0741), f2, 0x6210);
+      buf[2 * pw + u] = __byte_perm(__byte_perm(f0, f1, 0x0052), f2, 0x7410);
+    }
+  };
+  stage(y0, s_planes);
+  for (int y = y0; y < y1; ++y) {
+    const uint32_t* buf = s_planes + ((y - y0) & 1) * 3 * pw + wi;
+    __syncthreads();  // row y staged; the other buffer is free again
+    if (y + 1 < y1) stage(y + 1, s_planes + ((y + 1 - y0) & 1) * 3 * pw);
+    int res[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const uint32_t* pl = buf + c * pw;
+      int s0 = 0, s1 = 0, s2 = 0;
+      uint32_t prev = pl[0];
+      if (NG > 0) {
+#pragma unroll
+        for (int g = 0; g < NG; ++g) {
+          const uint32_t next = pl[g + 1];
+          const uint32_t f = __funnelshift_r(prev, next, sh);
+          s0 = dp4a_uu(f, K[g][0], s0);
+          s1 = dp4a_uu(f, K[g][1], s1);
+          s2 = dp4a_us(f, K[g][2], s2);
+          prev = next;
+        }
+      } else {
+        for (int g = 0; g < groups; ++g) {
+          const uint32_t next = pl[g + 1];
+          const uint32_t f = __funnelshift_r(prev, next, sh);
+          const uint32_t* kp = pack + (size_t)g * 3 * out_w + xc;
+          s0 = dp4a_uu(f, __ldg(kp), s0);
+          s1 = dp4a_uu(f, __ldg(kp + out_w), s1);
+          s2 = dp4a_us(f, __ldg(kp + 2 * out_w), s2);
+          prev = next;
+        }
+      }
+      // modulo 2^32 like Resample.c's int accumulator: the slices may wrap, the total does not
+      res[c] = (int)((1u << (kPrecisionBits - 1)) + (uint32_t)s0 + ((uint32_t)s1 << 8) + ((uint32_t)s2 << 16));
+    }
+    if (xx < out_w) {
+      uint8_t* op = dst + ((size_t)b * in_h + y) * (size_t)tpitch + (size_t)xx * 3;
+      op[0] = clip8(res[0]);
+      op[1] = clip8(res[1]);
+      op[2] = clip8(res[2]);
+    }
+  }
+}
+
+// Vertical pass (ImagingResampleVertical_8bpc) + normalisation + HWC -> CHW: grid (blocks of 128 output pixels,
+// groups of kPrepRows output rows, pictures).  The pass is independent per byte of a row, so a thread reduces FOUR
+// adjacent bytes: one aligned 32-bit load per tap row (block-uniform taps and coefficients), four multiply-adds.  The
+// clipped bytes go to shared memory; then a thread per pixel picks its three channels, looks the float values up and
+// writes one coalesced run per channel plane (plus the optional 8-bit picture).
+constexpr int kPrepVWords = kPrepThreads * 3 / 4;  // 96 words = 384 bytes = 128 pixels per block
+
+__global__ void __launch_bounds__(kPrepThreads)
+prep_vertical_kernel(const uint8_t* __restrict__ src, int tpitch, int in_h, int out_h, int out_w,
                      const int32_t* __restrict__ bounds, const int32_t* __restrict__ coef, const float* __restrict__ lut,
                      uint8_t* __restrict__ resized, float* __restrict__ input) {
-  const int xx = blockIdx.x * kPrepThreads + threadIdx.x;
-  const int yy = blockIdx.y, b = blockIdx.z;
-  if (xx >= out_w) return;
-  const int ymin = bounds[2 * yy], ymax = bounds[2 * yy + 1];
-  int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
-  const uint8_t* p = src + (((size_t)b * in_h + ymin) * out_w + xx) * 3;
-  for (int y = 0; y < ymax; ++y) {
-    const int k = coef[(size_t)y * out_h + yy];
-    a0 += (int)p[0] * k;
-    a1 += (int)p[1] * k;
-    a2 += (int)p[2] * k;
-    p += (size_t)out_w * 3;
-  }
-  const uint8_t v0 = clip8(a0), v1 = clip8(a1), v2 = clip8(a2);
-  if (resized) {
-    uint8_t* o = resized + (((size_t)b * out_h + yy) * out_w + xx) * 3;
-    o[0] = v0;
-    o[1] = v1;
-    o[2] = v2;
-  }
-  if (input) {
-    const size_t plane = (size_t)out_h * out_w;
-    float* o = input + (size_t)b * 3 * plane + (size_t)yy * out_w + xx;
-    o[0] = __ldg(lut + v0);
-    o[plane] = __ldg(lut + 256 + v1);
-    o[2 * plane] = __ldg(lut + 512 + v2);
+  __shared__ uint32_t s_out[2][kPrepVWords];
+  const int tid = threadIdx.x, b = blockIdx.z;
+  const int px0 = blockIdx.x * kPrepThreads;  // first pixel of the block
+  const int word = blockIdx.x * kPrepVWords + tid;
+  const bool reducer = tid < kPrepVWords && word * 4 < tpitch;
+  const int yy0 = blockIdx.y * kPrepRows, yy1 = min(yy0 + kPrepRows, out_h);
+  const size_t plane = (size_t)out_h * out_w;
+  for (int yy = yy0; yy < yy1; ++yy) {
+    uint32_t* so = s_out[(yy - yy0) & 1];
+    if (reducer) {
+      const int ymin = __ldg(bounds + 2 * yy), ymax = __ldg(bounds + 2 * yy + 1);
+      int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0, a3 = a0;
+      const uint32_t* p = reinterpret_cast<const uint32_t*>(src + ((size_t)b * in_h + ymin) * (size_t)tpitch) + word;
+#pragma unroll 3
+      for (int y = 0; y < ymax; ++y) {
+        const int k = __ldg(coef + (size_t)y * out_h + yy);
+        const uint32_t w = __ldg(p);
+        a0 += (int)(w & 0xffu) * k;
+        a1 += (int)((w >> 8) & 0xffu) * k;
+        a2 += (int)((w >> 16) & 0xffu) * k;
+        a3 += (int)(w >> 24) * k;
+        p += tpitch >> 2;
+      }
+      so[tid] = (uint32_t)clip8(a0) | ((uint32_t)clip8(a1) << 8) | ((uint32_t)clip8(a2) << 16) | ((uint32_t)clip8(a3) << 24);
+    }
+    __syncthreads();  // one barrier per row: the buffer written two rows ago was read before the previous barrier
+    const int xx = px0 + tid;
+    if (xx < out_w) {
+      const uint8_t* sb = reinterpret_cast<const uint8_t*>(so) + tid * 3;
+      const uint8_t v0 = sb[0], v1 = sb[1], v2 = sb[2];
+      if (resized) {
+        uint8_t* o = resized + (((size_t)b * out_h + yy) * out_w + xx) * 3;
+        o[0] = v0;
+        o[1] = v1;
+        o[2] = v2;
+      }
+      if (input) {
+        float* o = input + (size_t)b * 3 * plane + (size_t)yy * out_w + xx;
+        o[0] = __ldg(lut + v0);
+        o[plane] = __ldg(lut + 256 + v1);
+        o[2 * plane] = __ldg(lut + 512 + v2);
+      }
+    }
   }
 }
 
@@ -172,6 +304,7 @@ void destroy_preprocess(isb_handle* h) {
   for (AxisTable& t : st->tables) {
     cudaFree(t.d_bounds);
     cudaFree(t.d_coef);
+    cudaFree(t.d_pack);
   }
   cudaFree(st->temp);
   cudaFree(st->d_lut);
@@ -187,13 +320,11 @@ int launch_preprocess(isb_handle* h, const uint8_t* images, int batch, int in_h,
   }
   PrepState* st = static_cast<PrepState*>(h->prep);
   int rc;
-  AxisTable txv, tyv;
-  const AxisTable *tx = nullptr, *ty = &tyv;
-  if (in_w != out_w) {  // Resample.c skips an unchanged axis
-    if ((rc = get_axis(h, st, in_w, out_w, &txv)) != ISB_OK) return rc;
-    tx = &txv;
-  }
-  if ((rc = get_axis(h, st, in_h, out_h, &tyv)) != ISB_OK) return rc;  // unchanged height: unit coefficients, same bytes
+  AxisTable tx, ty;
+  // Resample.c skips an axis whose size does not change; the unit coefficients computed for it give the same bytes,
+  // so both passes always run and the vertical pass always reads the aligned intermediate image.
+  if ((rc = get_axis(h, st, in_w, out_w, &tx)) != ISB_OK) return rc;
+  if ((rc = get_axis(h, st, in_h, out_h, &ty)) != ISB_OK) return rc;
   if (input) {
     bool same = st->lut_valid;
     for (int c = 0; c < 3 && same; ++c) same = st->mean[c] == mean[c] && st->stdv[c] == stdv[c];
@@ -208,28 +339,47 @@ int launch_preprocess(isb_handle* h, const uint8_t* images, int batch, int in_h,
       st->lut_valid = true;
     }
   }
-  const uint8_t* vsrc = images;
-  if (tx) {
-    const size_t need = (size_t)batch * in_h * out_w * 3;
-    if (need > st->temp_bytes) {
-      ISB_CUDA(h, cudaStreamSynchronize(s));
-      cudaFree(st->temp);
-      st->temp = nullptr;
-      st->temp_bytes = 0;
-      ISB_CUDA(h, cudaMalloc((void**)&st->temp, need));
-      st->temp_bytes = need;
-    }
-    // shared memory: the input columns one block of outputs can touch
-    const double scale = (double)in_w / (double)out_w;
-    const size_t smem = (size_t)((int)ceil(kPrepThreads * scale) + tx->ksize + 2) * 3;
-    if (smem > 48 * 1024) ISB_FAIL(h, ISB_ERR_LIMIT, "preprocess: horizontal reduction %d -> %d is too strong for the staged row span", in_w, out_w);
-    prep_horizontal_kernel<<<dim3((out_w + kPrepThreads - 1) / kPrepThreads, in_h, batch), kPrepThreads, smem, s>>>(
-        images, in_h, in_w, out_w, tx->ksize, tx->d_bounds, tx->d_coef, st->temp);
-    ISB_LAUNCH_CHECK(h, "prep_horizontal_kernel");
-    vsrc = st->temp;
+  const int tpitch = (out_w * 3 + 15) & ~15;
+  const size_t need = (size_t)batch * in_h * tpitch;
+  if (need > st->temp_bytes) {
+    ISB_CUDA(h, cudaStreamSynchronize(s));
+    cudaFree(st->temp);
+    st->temp = nullptr;
+    st->temp_bytes = 0;
+    ISB_CUDA(h, cudaMalloc((void**)&st->temp, need));
+    ISB_CUDA(h, cudaMemset(st->temp, 0, need));  // the pitch padding is read (and discarded) by the vertical pass
+    st->temp_bytes = need;
   }
-  prep_vertical_kernel<<<dim3((out_w + kPrepThreads - 1) / kPrepThreads, out_h, batch), kPrepThreads, 0, s>>>(
-      vsrc, in_h, out_h, out_w, ty->ksize, ty->d_bounds, ty->d_coef, st->d_lut, resized, input);
+  // shared memory of the horizontal pass: two buffers of three byte planes for the input pixels one block of output
+  // columns can touch, plus the words a column reads past its last tap
+  const double scale = (double)in_w / (double)out_w;
+  const int groups = tx.groups, ng = groups <= kPrepMaxGroups ? groups : 0;
+  const int plane_cap = (((int)ceil(kPrepThreads * scale) + tx.ksize + 2 + 4 * (ng > 0 ? ng : groups) + 8 + 3) & ~3);
+  const size_t smem = 2 * 3 * (size_t)plane_cap;
+  if (smem > 96 * 1024) ISB_FAIL(h, ISB_ERR_LIMIT, "preprocess: horizontal reduction %d -> %d is too strong for the staged row span", in_w, out_w);
+  const int colblocks = (out_w + kPrepThreads - 1) / kPrepThreads;
+  const dim3 hgrid(colblocks, (in_h + kPrepRows - 1) / kPrepRows, batch);
+  const size_t src_bytes = (size_t)batch * in_h * in_w * 3;
+#define ISB_PREP_H(NGV)                                                                                                      \
+  do {                                                                                                                       \
+    if (smem > 48 * 1024)                                                                                                    \
+      ISB_CUDA(h, cudaFuncSetAttribute(prep_horizontal_kernel<NGV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); \
+    prep_horizontal_kernel<NGV><<<hgrid, kPrepThreads, smem, s>>>(images, src_bytes, in_h, in_w, out_w, groups, plane_cap,    \
+                                                                  tx.d_bounds, tx.d_pack, st->temp, tpitch);                 \
+  } while (0)
+  switch (ng) {
+    case 1: ISB_PREP_H(1); break;
+    case 2: ISB_PREP_H(2); break;
+    case 3: ISB_PREP_H(3); break;
+    case 4: ISB_PREP_H(4); break;
+    case 5: ISB_PREP_H(5); break;
+    case 6: ISB_PREP_H(6); break;
+    default: ISB_PREP_H(0); break;
+  }
+#undef ISB_PREP_H
+  ISB_LAUNCH_CHECK(h, "prep_horizontal_kernel");
+  prep_vertical_kernel<<<dim3(colblocks, (out_h + kPrepRows - 1) / kPrepRows, batch), kPrepThreads, 0, s>>>(
+      st->temp, tpitch, in_h, out_h, out_w, ty.d_bounds, ty.d_coef, st->d_lut, resized, input);
   ISB_LAUNCH_CHECK(h, "prep_vertical_kernel");
   return ISB_OK;
 }
@@ -241,7 +391,7 @@ extern "C" int isb_preprocess(isb_handle* h, const uint8_t* images, int32_t batc
                               isb_stream stream) {
   if (!h) return ISB_ERR_BAD_ARG;
   if (batch < 0 || in_h <= 0 || in_w <= 0 || out_h <= 0 || out_w <= 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "preprocess: bad size");
-  if (batch > 65535 || in_h > 65535 || out_h > 65535) ISB_FAIL(h, ISB_ERR_LIMIT, "preprocess: batch / height above 65535");
+  if (batch > 65535 || in_h > 65535 * 16 || out_h > 65535 * 16) ISB_FAIL(h, ISB_ERR_LIMIT, "preprocess: batch / height too large");
   if (batch == 0) return ISB_OK;
   if (!images || (!resized && !input)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "preprocess: null pointer");
   if (input && (!mean || !std)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "preprocess: mean / std required for the float output");
