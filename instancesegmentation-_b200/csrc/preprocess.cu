@@ -175,11 +175,16 @@ prep_horizontal_kernel(const uint8_t* __restrict__ src, size_t src_bytes, int in
       for (int j = 0; j < 3; ++j) K[g][j] = g < groups ? pack[((size_t)g * 3 + j) * out_w + xc] : 0u;
   }
   const uint8_t* src_end = src + src_bytes;
+  // everything about a row's address that does not depend on the row is worked out once: rows are in_w * 3 bytes apart
+  const uint8_t* row0 = src + (((size_t)b * in_h + y0) * (size_t)in_w + span0) * 3;
+  const unsigned row_step = (unsigned)in_w * 3u;
+  const uint8_t* last = row0 + (size_t)(y1 - 1 - y0) * row_step;
+  // block-uniform: every 32-bit load of every row of the block (aligned down, plus one word of slack) is inside the buffer
+  const bool inside = row0 >= src + 3 && last + (size_t)units * 12 + 8 <= src_end;
   auto stage = [&](int y, uint32_t* buf) {
-    const uint8_t* row = src + (((size_t)b * in_h + y) * (size_t)in_w + span0) * 3;
+    const uint8_t* row = row0 + (size_t)(unsigned)(y - y0) * row_step;
     const int rsh = (int)(reinterpret_cast<uintptr_t>(row) & 3) * 8;  // 12 bytes per unit: the same for every unit of the row
     const uint8_t* arow = row - (rsh >> 3);
-    const bool inside = arow >= src && arow + (size_t)units * 12 + 4 <= src_end;  // block-uniform
     for (int u = tid; u < units; u += kPrepThreads) {
       const uint8_t* p = arow + u * 12;
       uint32_t w0, w1, w2, w3;
@@ -197,6 +202,7 @@ prep_horizontal_kernel(const uint8_t* __restrict__ src, size_t src_bytes, int in
       buf[2 * pw + u] = __byte_perm(__byte_perm(f0, f1, 0x0052), f2, 0x7410);
     }
   };
+  uint8_t* orow = dst + ((size_t)b * in_h + y0) * (size_t)tpitch + (size_t)xc * 3;
   stage(y0, s_planes);
   for (int y = y0; y < y1; ++y) {
     const uint32_t* buf = s_planes + ((y - y0) & 1) * 3 * pw + wi;
@@ -233,11 +239,11 @@ prep_horizontal_kernel(const uint8_t* __restrict__ src, size_t src_bytes, int in
       res[c] = (int)((1u << (kPrecisionBits - 1)) + (uint32_t)s0 + ((uint32_t)s1 << 8) + ((uint32_t)s2 << 16));
     }
     if (xx < out_w) {
-      uint8_t* op = dst + ((size_t)b * in_h + y) * (size_t)tpitch + (size_t)xx * 3;
-      op[0] = clip8(res[0]);
-      op[1] = clip8(res[1]);
-      op[2] = clip8(res[2]);
+      orow[0] = clip8(res[0]);
+      orow[1] = clip8(res[1]);
+      orow[2] = clip8(res[2]);
     }
+    orow += tpitch;
   }
 }
 
@@ -259,12 +265,16 @@ prep_vertical_kernel(const uint8_t* __restrict__ src, int tpitch, int in_h, int 
   const bool reducer = tid < kPrepVWords && word * 4 < tpitch;
   const int yy0 = blockIdx.y * kPrepRows, yy1 = min(yy0 + kPrepRows, out_h);
   const size_t plane = (size_t)out_h * out_w;
+  const int xx = px0 + tid, xs = min(xx, out_w - 1);
+  const uint32_t* img = reinterpret_cast<const uint32_t*>(src + (size_t)b * in_h * (size_t)tpitch) + word;
+  uint8_t* rrow = resized ? resized + (((size_t)b * out_h + yy0) * out_w + xs) * 3 : nullptr;
+  float* irow = input ? input + (size_t)b * 3 * plane + (size_t)yy0 * out_w + xs : nullptr;
   for (int yy = yy0; yy < yy1; ++yy) {
     uint32_t* so = s_out[(yy - yy0) & 1];
     if (reducer) {
       const int ymin = __ldg(bounds + 2 * yy), ymax = __ldg(bounds + 2 * yy + 1);
       int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0, a3 = a0;
-      const uint32_t* p = reinterpret_cast<const uint32_t*>(src + ((size_t)b * in_h + ymin) * (size_t)tpitch) + word;
+      const uint32_t* p = img + (size_t)(unsigned)ymin * (unsigned)(tpitch >> 2);
 #pragma unroll 3
       for (int y = 0; y < ymax; ++y) {
         const int k = __ldg(coef + (size_t)y * out_h + yy);
@@ -278,21 +288,20 @@ prep_vertical_kernel(const uint8_t* __restrict__ src, int tpitch, int in_h, int 
       so[tid] = (uint32_t)clip8(a0) | ((uint32_t)clip8(a1) << 8) | ((uint32_t)clip8(a2) << 16) | ((uint32_t)clip8(a3) << 24);
     }
     __syncthreads();  // one barrier per row: the buffer written two rows ago was read before the previous barrier
-    const int xx = px0 + tid;
     if (xx < out_w) {
       const uint8_t* sb = reinterpret_cast<const uint8_t*>(so) + tid * 3;
       const uint8_t v0 = sb[0], v1 = sb[1], v2 = sb[2];
       if (resized) {
-        uint8_t* o = resized + (((size_t)b * out_h + yy) * out_w + xx) * 3;
-        o[0] = v0;
-        o[1] = v1;
-        o[2] = v2;
+        rrow[0] = v0;
+        rrow[1] = v1;
+        rrow[2] = v2;
+        rrow += (size_t)out_w * 3;
       }
       if (input) {
-        float* o = input + (size_t)b * 3 * plane + (size_t)yy * out_w + xx;
-        o[0] = __ldg(lut + v0);
-        o[plane] = __ldg(lut + 256 + v1);
-        o[2 * plane] = __ldg(lut + 512 + v2);
+        irow[0] = __ldg(lut + v0);
+        irow[plane] = __ldg(lut + 256 + v1);
+        irow[2 * plane] = __ldg(lut + 512 + v2);
+        irow += out_w;
       }
     }
   }
