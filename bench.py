@@ -209,7 +209,14 @@ def run_gpu(args):
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    json_fd = None
     if world > 1:
+        # NCCL writes its version banner to the process's stdout (fd 1) when NCCL_DEBUG is set on the box; stdout must
+        # carry exactly ONE JSON line, so everything else that lands on fd 1 goes to stderr and the line is written to
+        # a saved copy of the original descriptor
+        sys.stdout.flush()
+        json_fd = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
 
     a, p = synth.yolact_dims(INPUT_SIZE)
@@ -445,7 +452,10 @@ def run_gpu(args):
                                                "not the headline", "value": bsz / (pre_ms * 1e-3), "unit": "pictures/s (this rank)",
                                        "ms_per_step": pre_ms, "algorithmic_GBs": pre_bytes / (pre_ms * 1e-3) / 1e9},
                 "cpu_baseline": cpu}
-        print(json.dumps(line), flush=True)
+        if json_fd is None:
+            print(json.dumps(line), flush=True)
+        else:
+            os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 
