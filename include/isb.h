@@ -279,6 +279,16 @@ ISB_API int isb_resize_boxes(isb_handle* h, const float* boxes, int64_t m, int32
 ISB_API int isb_paste_masks(isb_handle* h, const float* masks, const float* boxes, int32_t m, int32_t mask_size,
                     int32_t padding, int32_t im_h, int32_t im_w, float* out, isb_stream stream);
 
+/* GeneralizedRCNNTransform.forward for inference, one image (transform.py:436-459): normalize :264-270, resize
+ * :284-315 (F.interpolate bilinear, align_corners=False, to the size the host computed with the reference's rule,
+ * transform.py:88-110) and the image's slot of batch_images :352-386 in one pass.
+ *   image: device float32 [3, in_h, in_w];  mean, std: 3 floats each (host);
+ *   canvas: device float32 [3, canvas_h, canvas_w], this image's slot of the batch: the resized image at the top-left,
+ *   zeros elsewhere (every element is written). */
+ISB_API int isb_rcnn_transform(isb_handle* h, const float* image, int32_t in_h, int32_t in_w, int32_t out_h, int32_t out_w,
+                       const float* mean, const float* std, float* canvas, int32_t canvas_h, int32_t canvas_w,
+                       isb_stream stream);
+
 /* Wrapper tail inst_model/Mask_RCNN/mask_rcnn.py:174-198 fused with paste_masks_in_image (transform.py:212-230):
  * keep detections with score > confidence, paste their SxS probability masks into a (paste_h, paste_w) frame,
  * F.interpolate(bilinear, align_corners=False) to (out_h, out_w), arg-max over the kept detections, > 0.5, and

@@ -20,6 +20,7 @@ SYMBOLS = (
     "isb_traditional_nms", "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_assemble",
     "isb_box_decode", "isb_nms", "isb_batched_nms", "isb_ms_roi_align", "isb_mask_select_sigmoid", "isb_resize_boxes",
     "isb_paste_masks", "isb_paste_class_map", "isb_rpn_filter", "isb_box_postprocess", "isb_preprocess",
+    "isb_rcnn_transform",
 )
 
 
@@ -114,6 +115,7 @@ def load():
         lib.isb_rpn_filter.argtypes = [vp, vp, vp, C.POINTER(i32), i32, i32, i32, i32, i32, f64, f32, f32, vp, vp, vp, vp]
         lib.isb_box_postprocess.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, f32, f32, f32, f32, f64, i32,
                                             vp, vp, vp, vp, vp]
+        lib.isb_rcnn_transform.argtypes = [vp, vp, i32, i32, i32, i32, C.POINTER(f32), C.POINTER(f32), vp, i32, i32, vp]
         lib.isb_preprocess.argtypes = [vp, vp, i32, i32, i32, i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double), vp, vp, vp]
         for name in SYMBOLS:
             fn = getattr(lib, name)

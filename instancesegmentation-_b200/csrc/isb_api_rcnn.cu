@@ -136,3 +136,20 @@ extern "C" int isb_paste_class_map(isb_handle* h, const float* masks, const floa
   return isb::launch_paste_class_map(h, masks, boxes, labels, scores, m, mask_size, padding, paste_h, paste_w, out_h, out_w,
                                      confidence, class_map, masks_arg, kept_count, (cudaStream_t)stream);
 }
+
+namespace isb {
+int launch_rcnn_transform(isb_handle* h, const float* img, int in_h, int in_w, int out_h, int out_w, const float mean[3],
+                          const float stdv[3], float* canvas, int can_h, int can_w, cudaStream_t s);
+}
+
+extern "C" int isb_rcnn_transform(isb_handle* h, const float* image, int32_t in_h, int32_t in_w, int32_t out_h, int32_t out_w,
+                                  const float* mean, const float* std, float* canvas, int32_t canvas_h, int32_t canvas_w,
+                                  isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (in_h <= 0 || in_w <= 0 || out_h <= 0 || out_w <= 0 || canvas_h < out_h || canvas_w < out_w)
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "rcnn_transform: bad size (the canvas must hold the resized image)");
+  if (canvas_h > 65535) ISB_FAIL(h, ISB_ERR_LIMIT, "rcnn_transform: canvas higher than 65535 rows");
+  if (!image || !mean || !std || !canvas) ISB_FAIL(h, ISB_ERR_BAD_ARG, "rcnn_transform: null pointer");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  return isb::launch_rcnn_transform(h, image, in_h, in_w, out_h, out_w, mean, std, canvas, canvas_h, canvas_w, (cudaStream_t)stream);
+}

@@ -125,9 +125,11 @@ __device__ __forceinline__ void crop_range(float v1, float v2, int size, int& lo
 __device__ __forceinline__ float sigmoidf_ref(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 // Bilinear source index / weight, aten area_pixel_compute_source_index +
-// guard_index_and_lambda with align_corners=False (reached from utils_bbox.py:228).
+// guard_index_and_lambda with align_corners=False (reached from utils_bbox.py:228).  The source coordinate is ONE
+// fused multiply-add, as in torch's own binaries (vectorised CPU kernel and CUDA kernel alike): with two roundings it
+// is off by an ulp of ~in_size, i.e. the weights by up to 1e-4 on a 1000-pixel axis (oracle/yolact_np.py).
 __device__ __forceinline__ void bilinear_src(int dst, float scale, int in_size, int& i0, int& i1, float& l0, float& l1) {
-  float src = scale * ((float)dst + 0.5f) - 0.5f;
+  float src = fmaf(scale, (float)dst + 0.5f, -0.5f);
   if (src < 0.0f) src = 0.0f;
   int f = (int)floorf(src);
   i0 = f < in_size - 1 ? f : in_size - 1;

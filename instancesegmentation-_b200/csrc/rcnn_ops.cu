@@ -527,6 +527,34 @@ __global__ void __launch_bounds__(kRoiThreads, 4) ms_roi_align_kernel(RoiLevels 
 #undef ROI_STAGE
 }
 
+// ------------------------------------------------------------------------------------------
+// GeneralizedRCNNTransform for inference, one image (transform.py:436-459): normalize (:264-270, float32
+// (v - mean) / std), resize (:284-315 -> F.interpolate bilinear, align_corners=False, output size given) and the
+// image's slot of batch_images (:352-386: zero canvas, image at the top-left) in one pass: a thread per canvas
+// pixel of a channel plane reads its four taps, normalises each (the reference interpolates normalised values) and
+// writes the pixel, or writes 0 outside the resized image.  out = h0*(w0*p00 + w1*p01) + h1*(w0*p10 + w1*p11).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+rcnn_transform_kernel(const float* __restrict__ img, int in_h, int in_w, int out_h, int out_w, float m0, float m1, float m2,
+                      float s0, float s1, float s2, float* __restrict__ canvas, int can_h, int can_w) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, c = blockIdx.z;
+  if (x >= can_w) return;
+  float r = 0.0f;
+  if (y < out_h && x < out_w) {
+    const float mean = c == 0 ? m0 : (c == 1 ? m1 : m2), sd = c == 0 ? s0 : (c == 1 ? s1 : s2);
+    const float ry = (float)in_h / (float)out_h, rx = (float)in_w / (float)out_w;
+    int iy0, iy1, ix0, ix1;
+    float ly0, ly1, lx0, lx1;
+    bilinear_src(y, ry, in_h, iy0, iy1, ly0, ly1);
+    bilinear_src(x, rx, in_w, ix0, ix1, lx0, lx1);
+    const float* pl = img + (size_t)c * in_h * in_w;
+    const float p00 = (__ldg(pl + (size_t)iy0 * in_w + ix0) - mean) / sd, p01 = (__ldg(pl + (size_t)iy0 * in_w + ix1) - mean) / sd;
+    const float p10 = (__ldg(pl + (size_t)iy1 * in_w + ix0) - mean) / sd, p11 = (__ldg(pl + (size_t)iy1 * in_w + ix1) - mean) / sd;
+    r = ly0 * (lx0 * p00 + lx1 * p01) + ly1 * (lx0 * p10 + lx1 * p11);
+  }
+  canvas[((size_t)c * can_h + y) * can_w + x] = r;
+}
+
 // ---------------------------------------------------------------------------- launchers
 static inline unsigned grid_for(int64_t n, int threads, int num_sms, int per_sm = 16) {
   int64_t g = (n + threads - 1) / threads;
@@ -584,6 +612,13 @@ int launch_paste_class_map(isb_handle* h, const float* masks, const float* boxes
       masks, reinterpret_cast<const float4*>(boxes), labels, scores, m, S, pad, paste_h, paste_w, out_h, out_w, confidence, class_map,
       masks_arg, kept_count);
   ISB_LAUNCH_CHECK(h, "paste_class_map_kernel");
+  return ISB_OK;
+}
+int launch_rcnn_transform(isb_handle* h, const float* img, int in_h, int in_w, int out_h, int out_w, const float mean[3],
+                          const float stdv[3], float* canvas, int can_h, int can_w, cudaStream_t s) {
+  rcnn_transform_kernel<<<dim3((can_w + 255) / 256, can_h, 3), 256, 0, s>>>(img, in_h, in_w, out_h, out_w, mean[0], mean[1], mean[2],
+                                                                            stdv[0], stdv[1], stdv[2], canvas, can_h, can_w);
+  ISB_LAUNCH_CHECK(h, "rcnn_transform_kernel");
   return ISB_OK;
 }
 int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, const int32_t* batch_idx, int num_rois,

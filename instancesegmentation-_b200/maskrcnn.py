@@ -252,3 +252,39 @@ def masks_class_image(masks, boxes, labels, scores, confidence, paste_shape, ima
                                                    ph, pw, oh, ow, float(confidence), _ptr(out),
                                                    _ptr(arg) if return_arg else None, None, _stream(dev)))
     return (out, arg) if return_arg else out
+
+
+# ---------------------------------------------------------------------------- transform.py:232-459 (pre-processing)
+def transform_output_size(h, w, min_size, max_size):
+    """Size `GeneralizedRCNNTransform.resize` produces for an [.., h, w] image (transform.py:88-110): the scale is
+    min(min_size / min(h, w), max_size / max(h, w)) evaluated the way torch evaluates `float / float32 tensor`
+    (reciprocal, then a float32 product), and F.interpolate(recompute_scale_factor=True) takes int(size * scale)."""
+    f32 = np.float32
+    lo, hi = f32(min(h, w)), f32(max(h, w))
+    scale = float(min((f32(1) / lo) * f32(min_size), (f32(1) / hi) * f32(max_size)))
+    return int(h * scale), int(w * scale)
+
+
+def rcnn_transform(images, min_size, max_size, image_mean, image_std, size_divisible=32):
+    """`GeneralizedRCNNTransform.forward` for inference (transform.py:436-459): images = list of float32 [3,H,W] CUDA
+    tensors -> (batch float32 [B,3,Hp,Wp], [(h_i, w_i)]): normalize, bilinear resize to the reference's size rule, zero
+    canvas padded to a multiple of `size_divisible`, one fused kernel per image writing straight into the batch."""
+    if isinstance(min_size, (list, tuple)):
+        min_size = min_size[-1]                                    # transform.py:299: testing uses the largest scale
+    imgs = [_cuda_f32(im, "image") for im in images]
+    for im in imgs:
+        if im.dim() != 3 or im.shape[0] != 3:
+            raise ValueError(f"images is expected to be a list of 3d tensors of shape [3, H, W], got {tuple(im.shape)}")
+    dev = imgs[0].device
+    sizes = [transform_output_size(im.shape[1], im.shape[2], float(min_size), float(max_size)) for im in imgs]
+    stride = float(size_divisible)
+    hp = int(math.ceil(float(max(s[0] for s in sizes)) / stride) * stride)     # transform.py:372-376
+    wp = int(math.ceil(float(max(s[1] for s in sizes)) / stride) * stride)
+    batch = torch.empty((len(imgs), 3, hp, wp), dtype=torch.float32, device=dev)
+    m3 = (C.c_float * 3)(*[float(v) for v in image_mean])
+    s3 = (C.c_float * 3)(*[float(v) for v in image_std])
+    for i, (im, (oh, ow)) in enumerate(zip(imgs, sizes)):
+        im = im.to(dev)
+        _call(dev, lambda h, im=im, oh=oh, ow=ow, i=i: h.lib.isb_rcnn_transform(
+            h.ptr, _ptr(im), im.shape[1], im.shape[2], oh, ow, m3, s3, C.c_void_p(batch[i].data_ptr()), hp, wp, _stream(dev)))
+    return batch, sizes

@@ -10,6 +10,7 @@ What is rebound:
   ...network_files.transform.paste_masks_in_image / resize_boxes -> isb.maskrcnn.*      (transform.py:410,415)
   ...network_files.roi_head.maskrcnn_inference              -> isb.maskrcnn.maskrcnn_inference (roi_head.py:555)
   torchvision MultiScaleRoIAlign instances of a built model -> isb.maskrcnn.MultiScaleRoIAlign (swap_roi_pools)
+  model.transform.forward (GeneralizedRCNNTransform)         -> isb.maskrcnn.rcnn_transform (swap_transform)
 """
 from __future__ import annotations
 
@@ -75,3 +76,23 @@ def swap_roi_pools(model):
             setattr(heads, name, new)
             swapped.append(name)
     return swapped
+
+
+def swap_transform(model):
+    """Route `model.transform.forward` (GeneralizedRCNNTransform, transform.py:436-459) through the fused CUDA
+    normalize + resize + batch kernel for inference (targets pass through untouched; training keeps the original)."""
+    t = getattr(model, "transform", None)
+    if t is None or getattr(t, "_isb_swapped", False):
+        return False
+    image_list = importlib.import_module(type(t).__module__.rsplit(".", 1)[0] + ".image_list")
+    original = t.forward
+
+    def forward(images, targets=None):
+        if targets is not None or getattr(t, "train_mode", None):
+            return original(images, targets)
+        batch, sizes = maskrcnn.rcnn_transform(list(images), t.min_size, t.max_size, t.image_mean, t.image_std, t.size_divisible)
+        return image_list.ImageList(batch, sizes), targets
+
+    t.forward = forward
+    t._isb_swapped = True
+    return True

@@ -171,7 +171,53 @@ def class_image(name, seed, m=40, paste_hw=(272, 272), sizes=((272, 272), (360, 
           confidence=np.float32(confidence), paste_hw=np.array(paste_hw), sizes=np.array(sizes), **out)
 
 
+IMAGENET_MEAN, IMAGENET_STD = [0.485, 0.456, 0.406], [0.229, 0.224, 0.225]   # faster_rcnn_framework.py:255-258
+
+
+def transform_golden(name, seed):
+    """GeneralizedRCNNTransform.forward (transform.py:436-459) of the reference on seeded pictures: two small batches with
+    their inputs, the wrapper's case (544 x 544 -> min 800 / max 1333) as a sub-sampled output, and the output size of
+    400 random shapes (the size rule is host logic)."""
+    R = _ref()
+    out = dict(seed=seed, mean=np.array(IMAGENET_MEAN), std=np.array(IMAGENET_STD))
+    g = torch.Generator().manual_seed(seed)
+    for tag, mn, mx, shapes in (("a", 160, 200, [(97, 211), (150, 90), (33, 35)]), ("b", 48, 64, [(60, 80), (50, 45)])):
+        t = R.transform.GeneralizedRCNNTransform(mn, mx, IMAGENET_MEAN, IMAGENET_STD, train_mode=False)
+        imgs = [torch.rand(3, h, w, generator=g) for h, w in shapes]
+        with torch.no_grad():
+            il, _ = t(imgs)
+        out[f"{tag}_min_max"] = np.array([mn, mx])
+        out[f"{tag}_n"] = len(imgs)
+        for i, im in enumerate(imgs):
+            out[f"{tag}_in{i}"] = im.numpy()
+        out[f"{tag}_shape"] = np.array(il.tensors.shape)
+        out[f"{tag}_batch"] = il.tensors.numpy() if tag == "b" else il.tensors.numpy()[:, :, ::3, ::3]   # a: sub-sampled
+        out[f"{tag}_sizes"] = np.array([tuple(s) for s in il.image_sizes])
+    t = R.transform.GeneralizedRCNNTransform(800, 1333, IMAGENET_MEAN, IMAGENET_STD, train_mode=False)
+    gf = torch.Generator().manual_seed(seed + 1)
+    img = torch.rand(3, 544, 544, generator=gf)
+    with torch.no_grad():
+        il, _ = t([img])
+    out["full_hw"] = np.array([544, 544])
+    out["full_digest_in"] = digest(img.numpy())
+    out["full_sizes"] = np.array([tuple(s) for s in il.image_sizes])
+    out["full_shape"] = np.array(il.tensors.shape)
+    out["full_sub"] = il.tensors.numpy()[:, :, ::13, ::11]
+    out["full_sum"] = float(il.tensors.double().sum())
+    rs = np.random.RandomState(seed)
+    hw = np.stack([rs.randint(20, 1400, 400), rs.randint(20, 2000, 400)], 1)
+    got = []
+    for h, w in hw:
+        with torch.no_grad():
+            il, _ = t([torch.zeros(3, int(h), int(w))])
+        got.append(tuple(il.image_sizes[0]))
+    out["rule_hw"] = hw
+    out["rule_sizes"] = np.array(got)
+    _save(name, **out)
+
+
 def main():
+    transform_golden("maskrcnn_transform", 4501)
     class_image("maskrcnn_class_image", 4401)
     stages("maskrcnn_stages", 31)
     rpn_filter("maskrcnn_rpn_filter", 4001)

@@ -336,3 +336,38 @@ def masks_class_image(pasted, labels, scores, confidence, image_shape):
     hwm = np.ascontiguousarray(np.transpose(up, (1, 2, 0)))                   # :187
     arg = np.argmax(hwm, axis=-1)                                             # first maximum, like torch.argmax
     return masks_class(hwm > F32(0.5), classes, arg), arg
+
+
+# --------------------------------------------------------------------------- next row
+def transform_output_size(h, w, min_size, max_size):
+    """transform.py:88-97 + F.interpolate(scale_factor=..., recompute_scale_factor=True): `self_min_size / min_size`
+    is python-float / float32-tensor, which torch evaluates as reciprocal(tensor) * float in float32
+    (Tensor.__rtruediv__); the scale is the float32 minimum of the two ratios taken to a Python float (.item()), and the
+    output size is int(size * scale) per axis in double (torch/nn/functional.py interpolate)."""
+    lo, hi = F32(min(h, w)), F32(max(h, w))
+    scale = float(min((F32(1) / lo) * F32(min_size), (F32(1) / hi) * F32(max_size)))
+    return int(h * scale), int(w * scale)
+
+
+def rcnn_transform(images, min_size, max_size, image_mean, image_std, size_divisible=32):
+    """GeneralizedRCNNTransform.forward for inference (transform.py:436-459): per image normalize (:264-270, float32),
+    resize (:284-315 -> _resize_image_and_masks :72-110, bilinear, align_corners=False, sizes recomputed), then
+    batch_images (:352-386): zero canvas [B, 3, ceil(maxH / 32) * 32, ceil(maxW / 32) * 32], images at the top-left.
+    images: list of float32 [3, H, W].  Returns (batch float32 [B,3,Hp,Wp], [(h_i, w_i)])."""
+    import math
+    from .yolact_np import upsample_bilinear
+    mean = np.asarray(image_mean, dtype=F32)[:, None, None]
+    std = np.asarray(image_std, dtype=F32)[:, None, None]
+    resized, sizes = [], []
+    for img in images:
+        x = (np.asarray(img, dtype=F32) - mean) / std
+        oh, ow = transform_output_size(x.shape[1], x.shape[2], min_size, max_size)
+        resized.append(upsample_bilinear(x, oh, ow))
+        sizes.append((oh, ow))
+    stride = float(size_divisible)
+    hp = int(math.ceil(float(max(s[0] for s in sizes)) / stride) * stride)
+    wp = int(math.ceil(float(max(s[1] for s in sizes)) / stride) * stride)
+    batch = np.zeros((len(images), 3, hp, wp), F32)
+    for i, r in enumerate(resized):
+        batch[i, :, : r.shape[1], : r.shape[2]] = r
+    return batch, sizes

@@ -183,10 +183,15 @@ def _linear_index_weights(in_size, out_size):
     (torch 2.11 ATen/native/UpSample.h; reached from utils_bbox.py:228.)  All in float32:
     scale = in/out; src = scale*(dst+0.5)-0.5 clamped at 0; i0 = min(floor(src), in-1);
     lambda1 = clamp(src - i0, 0, 1); lambda0 = 1 - lambda1; i1 = i0 + (i0 < in-1).
+    The product and the subtraction of `src` are ONE fused multiply-add in torch's binaries (the vectorised CPU kernel
+    and the CUDA kernel are both compiled with contraction on): with separate roundings the index is off by an ulp of
+    ~in_size, i.e. the weights by up to 1e-4 on a 1000-pixel axis (measured: 1.5e-4 max output error at 1080 -> 749,
+    5e-7 with the fused form).  The fused operation is emulated exactly in float64 (the product of two float32 is
+    exact there) with one rounding to float32.
     """
     scale = F32(in_size) / F32(out_size)
     dst = np.arange(out_size, dtype=F32)
-    src = scale * (dst + F32(0.5)) - F32(0.5)
+    src = (np.float64(scale) * (dst + F32(0.5)).astype(np.float64) - 0.5).astype(F32)
     src = np.where(src < 0, F32(0), src).astype(F32)
     i0 = np.minimum(np.floor(src).astype(np.int64), in_size - 1)
     lam1 = np.minimum(np.maximum(src - i0.astype(F32), F32(0)), F32(1)).astype(F32)

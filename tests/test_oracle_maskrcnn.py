@@ -62,3 +62,27 @@ def test_class_image_wrapper_tail():
         assert float(np.mean(arg != g[f"arg_{k}"])) <= 1e-3
     none, _ = M.masks_class_image(pasted, g["labels"], g["scores"], 2.0, (50, 50))
     assert none is None
+
+
+def test_rcnn_transform_vs_reference_golden():
+    """GeneralizedRCNNTransform.forward (transform.py:436-459): normalize + bilinear resize + batch padding, and the
+    output-size rule on 400 random shapes (exact), against outputs of the reference itself."""
+    g = load_golden("maskrcnn_transform")
+    mean, std = g["mean"], g["std"]
+    for tag in ("a", "b"):
+        mn, mx = [int(v) for v in g[f"{tag}_min_max"]]
+        imgs = [g[f"{tag}_in{i}"] for i in range(int(g[f"{tag}_n"]))]
+        batch, sizes = M.rcnn_transform(imgs, mn, mx, mean, std)
+        assert batch.shape == tuple(g[f"{tag}_shape"]) and [tuple(s) for s in g[f"{tag}_sizes"]] == sizes
+        got = batch if tag == "b" else batch[:, :, ::3, ::3]
+        assert_close_f32(got, g[f"{tag}_batch"], 1e-5, f"transform {tag}")
+        assert np.array_equal(got == 0, g[f"{tag}_batch"] == 0)
+    for (h, w), want in zip(g["rule_hw"], g["rule_sizes"]):
+        assert M.transform_output_size(int(h), int(w), 800, 1333) == tuple(want), (h, w)
+
+
+def test_product_size_rule_matches_reference_golden():
+    from isb import maskrcnn as R
+    g = load_golden("maskrcnn_transform")
+    for (h, w), want in zip(g["rule_hw"], g["rule_sizes"]):
+        assert R.transform_output_size(int(h), int(w), 800, 1333) == tuple(want), (h, w)

@@ -36,3 +36,37 @@ def test_swap_roi_pools():
     assert isb.patch.swap_roi_pools(model) == ["box_roi_pool", "mask_roi_pool"]
     assert isinstance(heads.box_roi_pool, maskrcnn.MultiScaleRoIAlign) and heads.mask_roi_pool.output_size == (14, 14)
     assert isinstance(heads.box_roi_pool, torchvision.ops.MultiScaleRoIAlign)   # reference isinstance checks still pass
+
+
+def test_swap_transform_routes_inference_only(monkeypatch):
+    """swap_transform: training calls and calls with targets keep the reference's forward; inference goes to
+    isb.maskrcnn.rcnn_transform and comes back as the reference package's ImageList."""
+    import sys
+    import isb.patch
+    from isb import maskrcnn
+    pkg = types.ModuleType("fakeref")
+    tmod, imod = types.ModuleType("fakeref.transform"), types.ModuleType("fakeref.image_list")
+
+    class ImageList:
+        def __init__(self, tensors, image_sizes):
+            self.tensors, self.image_sizes = tensors, image_sizes
+
+    class Transform:
+        min_size, max_size, image_mean, image_std, size_divisible, train_mode = (800,), 1333, [0.5] * 3, [0.2] * 3, 32, False
+
+        def forward(self, images, targets=None):
+            return "original", targets
+    Transform.__module__ = "fakeref.transform"
+    imod.ImageList = ImageList
+    for name, mod in (("fakeref", pkg), ("fakeref.transform", tmod), ("fakeref.image_list", imod)):
+        monkeypatch.setitem(sys.modules, name, mod)
+    calls = []
+    monkeypatch.setattr(maskrcnn, "rcnn_transform", lambda images, *a: (calls.append(a) or ("batch", [(1, 2)])))
+    model = types.SimpleNamespace(transform=Transform())
+    assert isb.patch.swap_transform(model) and not isb.patch.swap_transform(model)
+    out, tg = model.transform.forward(["img"])
+    assert isinstance(out, ImageList) and out.tensors == "batch" and out.image_sizes == [(1, 2)] and tg is None
+    assert calls == [((800,), 1333, [0.5] * 3, [0.2] * 3, 32)]
+    assert model.transform.forward(["img"], targets=[{}])[0] == "original"
+    model.transform.train_mode = True
+    assert model.transform.forward(["img"])[0] == "original"
