@@ -66,6 +66,12 @@ def main():
                                           C.c_void_p(torch.cuda.current_stream().cuda_stream)))
         us = timeit(paste)
         res[f"paste_masks_100_to_{shape[0]}x{shape[1]}"] = {"us": us, "out_GBs": 100 * shape[0] * shape[1] * 4 / us / 1e3}
+    # GeneralizedRCNNTransform.forward (transform.py:436-459): the wrapper's 544 x 544 tensor -> 800 x 800, and a 1080p picture
+    for hw in ((544, 544), (1080, 1920)):
+        img = torch.rand(3, *hw, device=dev)
+        us = timeit(lambda: R.rcnn_transform([img], 800, 1333, [0.485, 0.456, 0.406], [0.229, 0.224, 0.225]))
+        oh, ow = R.transform_output_size(hw[0], hw[1], 800.0, 1333.0)
+        res[f"rcnn_transform_{hw[0]}x{hw[1]}_to_{oh}x{ow}"] = {"us": us, "GBs": (3 * hw[0] * hw[1] + 3 * ((oh + 31) // 32 * 32) * ((ow + 31) // 32 * 32)) * 4 / us / 1e3}
     # wrapper tail fused with the paste (mask_rcnn.py:174-198): 544x544 paste frame -> class image at the original size
     scores = torch.rand(100, device=dev)
     b544 = boxes * (544.0 / 1333.0)
