@@ -61,6 +61,7 @@ __global__ void nms_gather_kernel(const uint64_t* __restrict__ keys, const float
   for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
     const int i = labels ? (int)((uint32_t)keys[p] & (uint32_t)kRowMask) : (int)(uint32_t)keys[p];
     if (labels) slabel[p] = labels[i];
+    else if (idxs32) slabel[p] = idxs32[i];  // level / class of the offset trick: lets the mask kernel skip cross-group pairs
     float4 b = boxes[i];
     if (batched) {
       const float off = (idxs64 ? (float)idxs64[i] : (float)idxs32[i]) * step;  // idxs.to(boxes) * (max + 1)
@@ -80,7 +81,8 @@ __global__ void nms_gather_kernel(const uint64_t* __restrict__ keys, const float
 // thing in the loop.
 __global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__ sbox, int n_max,
                                                       const int32_t* __restrict__ n_dev, float thr, int words,
-                                                      const int32_t* __restrict__ slabel, uint64_t* __restrict__ mask) {
+                                                      const int32_t* __restrict__ slabel, int offset_groups,
+                                                      uint64_t* __restrict__ mask) {
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   // linear block index -> (rb, cb), cb <= rb: rb = floor((sqrt(8 t + 1) - 1) / 2), fixed up for rounding
   const unsigned lin = blockIdx.x;
@@ -109,6 +111,14 @@ __global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__
   const bool zero_hits = 0.0f > thr;  // a zero IoU suppresses only for a negative threshold
   uint64_t bits = 0;
   for (int j = 0; j < ncol; ++j) {
+    // boxes of different groups never overlap: per-class mode says so, and under the coordinate-offset trick
+    // (boxes.py:70-82) their shifted copies are disjoint, so the IoU is exactly 0 -- no arithmetic needed.  (The
+    // shortcut is only taken for the int32 group ids of the fused RPN pipeline, whose boxes are clipped to the image
+    // first; with negative coordinates shifted groups CAN touch, and the int64 path of batched_nms computes every pair.)
+    if (clabel[j] != alabel) {
+      if (offset_groups && zero_hits) bits |= 1ull << j;
+      continue;
+    }
     const float4 c = cbox[j];
     const float w = fmaxf(0.0f, fminf(a.z, c.z) - fmaxf(a.x, c.x));
     const float hgt = fmaxf(0.0f, fminf(a.w, c.w) - fmaxf(a.y, c.y));
@@ -117,7 +127,7 @@ __global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__
     bool hit;
     if (inter == 0.0f && uni != 0.0f && fabsf(uni) <= 3.402823466e38f) hit = zero_hits;
     else hit = inter / uni > thr;
-    if (hit && clabel[j] == alabel) bits |= 1ull << j;
+    if (hit) bits |= 1ull << j;
   }
   if (rb == cb) bits &= ~(1ull << t);  // a box does not suppress itself
   mask[(size_t)ri * words + cb] = bits;
@@ -292,7 +302,7 @@ int launch_nms(isb_handle* h, const NmsCall& c, cudaStream_t s) {
                                            c.labels32, h->nms_sbox, h->nms_order, h->nms_slabel);
   ISB_LAUNCH_CHECK(h, "nms_gather_kernel");
   nms_mask_kernel<<<(unsigned)((int64_t)words * (words + 1) / 2), 64, 0, s>>>(h->nms_sbox, n, c.n_dev, thr_f, words,
-                                                    c.labels32 ? h->nms_slabel : nullptr, h->nms_mask);
+                                                    (c.labels32 || c.idxs32) ? h->nms_slabel : nullptr, c.labels32 ? 0 : 1, h->nms_mask);
   ISB_LAUNCH_CHECK(h, "nms_mask_kernel");
   const size_t smem = (size_t)words * 8;
   if (smem > 64 * 1024) ISB_FAIL(h, ISB_ERR_LIMIT, "nms scan shared memory");

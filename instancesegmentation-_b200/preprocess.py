@@ -21,10 +21,13 @@ STD = (58.40, 57.12, 57.38)      # utils/utils.py:34
 
 def _as_u8_batch(images, device):
     """PIL image / uint8 ndarray / uint8 tensor, [H,W,3] or [B,H,W,3] -> (cuda uint8 [B,H,W,3], was_single)."""
+    def rgb(im):  # utils/utils.py:9-14 cvtColor: anything that is not an RGB picture is converted by PIL
+        return im.convert("RGB") if hasattr(im, "convert") and getattr(im, "mode", "RGB") != "RGB" else im
     if isinstance(images, (list, tuple)):
-        images = np.stack([np.asarray(im, dtype=np.uint8) for im in images])
+        images = np.stack([np.asarray(rgb(im), dtype=np.uint8) for im in images])
+    images = rgb(images)
     if not torch.is_tensor(images):
-        images = torch.from_numpy(np.ascontiguousarray(np.asarray(images, dtype=np.uint8)))
+        images = torch.from_numpy(np.array(images, dtype=np.uint8, order="C"))   # a writable copy (PIL buffers are read-only)
     if images.dtype != torch.uint8:
         raise TypeError(f"pictures must be uint8, got {images.dtype}")
     single = images.dim() == 3

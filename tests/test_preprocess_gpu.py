@@ -68,6 +68,18 @@ def test_batch_and_other_sizes_vs_oracle(pre):
             assert np.array_equal(out[i:i + 1].cpu().numpy(), P.normalize_chw(ref, mean, std))
 
 
+def test_pil_inputs_and_grey_pictures(pre):
+    """PIL pictures go in as they are; a picture that is not RGB is converted first like utils.py:9-14 cvtColor."""
+    Image = pytest.importorskip("PIL.Image")
+    grey = Image.fromarray(synth.picture(9, 50, 70)[:, :, 0])
+    rgb = np.array(grey.convert("RGB"))
+    out, res = pre.image_to_input(grey, (24, 32), return_resized=True)
+    assert np.array_equal(res[0].cpu().numpy(), P.resize_u8(rgb, 32, 24))
+    assert np.array_equal(out.cpu().numpy(), P.image_to_input(rgb, (24, 32)))
+    pil = Image.fromarray(synth.picture(10, 40, 60))
+    assert np.array_equal(np.array(pre.resize_image(pil, (30, 20))), np.array(pil.resize((30, 20), Image.BICUBIC)))
+
+
 def test_value_table_follows_mean_std(pre):
     img = synth.picture(5, 40, 60)
     a = pre.image_to_input(img, (20, 30)).cpu().numpy()
