@@ -150,54 +150,68 @@ __device__ __forceinline__ float4 clip_box(float4 b, float wf, float hf) {
   return b;
 }
 
-// Single CTA: walk the levels' top-k in order, clip, drop small / low-score boxes, compact in order.
+// Single CTA: the levels' top-k in order (the sorted keys are level-major), clip, drop small / low-score boxes, compact
+// in order.  A thread owns a run of consecutive candidates (at most kSelPerThread = ceil(total / 1024)): all its key and
+// proposal loads are issued before anything depends on them, and ONE exclusive scan of the per-thread counts places
+// every survivor -- two dependent global round trips and one scan instead of one of each per level.
+constexpr int kSelPerThread = 8;  // 8 * 1024 candidates: 8 levels of pre_nms_top_n 1000; more falls back to a loop of passes
+
 __global__ void __launch_bounds__(1024) rpn_select_kernel(const uint64_t* __restrict__ keys, LevelTopK topk,
                                                           const float4* __restrict__ proposals, int num_levels,
                                                           int pre_top_n, float img_w, float img_h, float min_size,
                                                           float score_thresh, float4* __restrict__ cbox,
                                                           float* __restrict__ cscore, int32_t* __restrict__ clvl,
                                                           int32_t* __restrict__ n_out) {
-  __shared__ int s_wcount[32];
-  __shared__ int s_base;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_base = 0;
-  __syncthreads();
-  int start = 0;
-  for (int l = 0; l < num_levels; start += topk.k[l], ++l) {  // the sorted keys hold exactly topk.k[l] entries per level
-    const int k = topk.k[l];
-    for (int r0 = 0; r0 < k; r0 += 1024) {
-      const int r = r0 + tid;
-      bool ok = false;
-      float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
-      float sc = 0.f;
-      if (r < k) {
-        const uint64_t key = keys[start + r];
-        b = clip_box(proposals[cand_row(key)], img_w, img_h);                       // :509
-        sc = sigmoidf_ref(float_from_desc_bits(cand_score_bits(key)));              // :502
-        ok = (b.z - b.x >= min_size) && (b.w - b.y >= min_size) && (sc >= score_thresh);  // :512, :517
-      }
-      const unsigned bal = __ballot_sync(0xffffffffu, ok);
-      if (lane == 0) s_wcount[warp] = __popc(bal);
-      __syncthreads();
-      int off = s_base, tot = 0;
+  __shared__ int s_scan[32];
+  const int tid = threadIdx.x;
+  int lvl_end[8];
+  int total = 0;
 #pragma unroll
-      for (int w = 0; w < 32; ++w) {
-        const int c = s_wcount[w];
-        if (w < warp) off += c;
-        tot += c;
-      }
-      if (ok) {
-        const int slot = off + __popc(bal & ((1u << lane) - 1u));
-        cbox[slot] = b;
-        cscore[slot] = sc;
-        clvl[slot] = l;
-      }
-      __syncthreads();
-      if (tid == 0) s_base += tot;
-      __syncthreads();
-    }
+  for (int l = 0; l < 8; ++l) {
+    if (l < num_levels) total += topk.k[l];
+    lvl_end[l] = total;  // candidates [lvl_end[l-1], lvl_end[l]) belong to level l
   }
-  if (tid == 0) *n_out = s_base;
+  int base = 0;
+  for (int p0 = 0; p0 < total; p0 += kSelPerThread * 1024) {  // one pass unless there are more than 8192 candidates
+    const int n = min(total - p0, kSelPerThread * 1024);
+    const int per = (n + 1023) / 1024;
+    const int i0 = p0 + tid * per, i1 = min(i0 + per, p0 + n);
+    uint64_t key[kSelPerThread];
+    float4 bx[kSelPerThread];
+#pragma unroll
+    for (int q = 0; q < kSelPerThread; ++q)
+      if (i0 + q < i1) key[q] = keys[i0 + q];
+#pragma unroll
+    for (int q = 0; q < kSelPerThread; ++q)
+      if (i0 + q < i1) bx[q] = proposals[cand_row(key[q])];
+    float sc[kSelPerThread];
+    unsigned okmask = 0;
+    int cnt = 0;
+#pragma unroll
+    for (int q = 0; q < kSelPerThread; ++q)
+      if (i0 + q < i1) {
+        bx[q] = clip_box(bx[q], img_w, img_h);                                                  // :509
+        sc[q] = sigmoidf_ref(float_from_desc_bits(cand_score_bits(key[q])));                    // :502
+        if ((bx[q].z - bx[q].x >= min_size) && (bx[q].w - bx[q].y >= min_size) && (sc[q] >= score_thresh)) {  // :512, :517
+          okmask |= 1u << q;
+          ++cnt;
+        }
+      }
+    int pass_total;
+    int slot = base + cta_exclusive_scan(cnt, s_scan, &pass_total);
+#pragma unroll
+    for (int q = 0; q < kSelPerThread; ++q)
+      if ((okmask >> q) & 1u) {
+        int l = 0;
+        while (l < 7 && i0 + q >= lvl_end[l]) ++l;
+        cbox[slot] = bx[q];
+        cscore[slot] = sc[q];
+        clvl[slot] = l;
+        ++slot;
+      }
+    base += pass_total;
+  }
+  if (tid == 0) *n_out = base;
 }
 
 __global__ void rpn_gather_kernel(const int64_t* __restrict__ keep, const int32_t* __restrict__ count,
