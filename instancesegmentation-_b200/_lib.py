@@ -206,5 +206,24 @@ def get_handle(device, **needs):
     return cur
 
 
+class _NoGuard:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
+
+
+_NO_GUARD = _NoGuard()
+
+
+def on_device(dev):
+    """`torch.cuda.device(dev)` only when `dev` is not already current: the library selects its handle's device itself,
+    the guard exists to put the caller's current device back, and entering / leaving it costs microseconds that show
+    on every small call."""
+    import torch
+    return _NO_GUARD if torch.cuda.current_device() == dev.index else torch.cuda.device(dev)
+
+
 def total_launches():
     return sum(h.launch_count for h in _handles.values())

@@ -26,7 +26,7 @@ BBOX_XFORM_CLIP = math.log(1000.0 / 16)  # det_utils.py:146
 
 def _call(dev, fn):
     h = get_handle(dev.index)
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         h.check(fn(h))
 
 

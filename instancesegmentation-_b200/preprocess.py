@@ -13,6 +13,7 @@ import ctypes as C
 import numpy as np
 import torch
 
+from . import _lib
 from ._lib import get_handle
 
 MEAN = (123.68, 116.78, 103.94)   # utils/utils.py:33
@@ -49,7 +50,7 @@ def _run(images, out_h, out_w, want_resized, want_input, mean, std):
     net_in = torch.empty((b, 3, out_h, out_w), dtype=torch.float32, device=dev) if want_input else None
     m3, s3 = (C.c_double * 3)(*[float(v) for v in mean]), (C.c_double * 3)(*[float(v) for v in std])
     h = get_handle(dev.index)
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         h.check(h.lib.isb_preprocess(h.ptr, C.c_void_p(images.data_ptr()), b, in_h, in_w, out_h, out_w, m3, s3,
                                      C.c_void_p(resized.data_ptr()) if want_resized else None,
                                      C.c_void_p(net_in.data_ptr()) if want_input else None,

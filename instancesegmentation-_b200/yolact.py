@@ -74,7 +74,7 @@ class BBoxUtility(object):
         dev = pred_box.device
         out = torch.empty_like(pred_box)
         h = get_handle(dev.index)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             h.check(h.lib.isb_decode_boxes(h.ptr, _ptr(pred_box), _ptr(anchors), pred_box.shape[0], float(variances[0]),
                                            float(variances[1]), _ptr(out), _stream(dev)))
         return out
@@ -90,7 +90,7 @@ class BBoxUtility(object):
         dev = box_a.device
         out = torch.empty((n, na, nb), dtype=torch.float32, device=dev)
         h = get_handle(dev.index)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             h.check(h.lib.isb_jaccard(h.ptr, _ptr(box_a), _ptr(box_b), n, na, nb, int(bool(iscrowd)), _ptr(out), _stream(dev)))
         return out if use_batch else out.squeeze(0)
 
@@ -112,7 +112,7 @@ class BBoxUtility(object):
         out_cls = torch.empty((max_det,), dtype=torch.int64, device=dev)
         out_coef = torch.empty((max_det, k), dtype=torch.float32, device=dev)
         count = torch.zeros((1,), dtype=torch.int32, device=dev)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             h.check(h.lib.isb_fast_nms(h.ptr, _ptr(box_thre), _ptr(class_thre), _ptr(mask_thre), n, ncls, k, float(nms_iou),
                                        top_k, max_det, _ptr(out_box), _ptr(out_score), _ptr(out_cls), _ptr(out_coef),
                                        _ptr(count), _stream(dev)))
@@ -140,7 +140,7 @@ class BBoxUtility(object):
         out_cls = torch.empty((max_det,), dtype=torch.int64, device=dev)
         out_coef = torch.empty((max_det, k), dtype=torch.float32, device=dev)
         count = torch.zeros((1,), dtype=torch.int32, device=dev)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             h.check(h.lib.isb_traditional_nms(h.ptr, _ptr(box_thre), _ptr(class_thre), _ptr(mask_thre), _ptr(pred_class_max),
                                               n, ncls, k, float(nms_iou), max_det, _ptr(out_box), _ptr(out_score),
                                               _ptr(out_cls), _ptr(out_coef), _ptr(count), _stream(dev)))
@@ -154,7 +154,7 @@ class BBoxUtility(object):
         hgt, wid = int(image_shape[0]), int(image_shape[1])
         out = torch.empty_like(boxes)
         h = get_handle(dev.index)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             h.check(h.lib.isb_correct_boxes(h.ptr, _ptr(boxes), boxes.shape[0], hgt, wid, _ptr(out), _stream(dev)))
         return out
 
@@ -166,7 +166,7 @@ class BBoxUtility(object):
         dev = masks.device
         out = torch.empty_like(masks)
         h = get_handle(dev.index)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             h.check(h.lib.isb_crop(h.ptr, _ptr(masks), _ptr(boxes), hgt, wid, m, _ptr(out), _stream(dev)))
         return out
 
@@ -179,7 +179,7 @@ class BBoxUtility(object):
         m = coef.shape[0]
         out = torch.empty((ph, pw, m), dtype=torch.float32, device=proto.device)
         h = get_handle(proto.device.index)
-        with torch.cuda.device(proto.device):
+        with _lib.on_device(proto.device):
             h.check(h.lib.isb_mask_logits(h.ptr, _ptr(proto), _ptr(coef), ph, pw, m, _ptr(out), _stream(proto.device)))
         return out
 
@@ -198,7 +198,7 @@ class BBoxUtility(object):
         masks = torch.empty((max(nbytes, 16),), dtype=torch.uint8, device=dev)
         arg = torch.empty((hgt, wid), dtype=torch.int64, device=dev)
         h = get_handle(dev.index, max_det=max(m, 1))
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             h.check(h.lib.isb_mask_assemble(h.ptr, _ptr(proto), _ptr(coef), _ptr(boxes), ph, pw, m, hgt, wid, _ptr(arg),
                                             _ptr(masks), _stream(dev)))
         return arg, masks[: hgt * wid * m].view(hgt, wid, m).view(torch.bool)
@@ -234,7 +234,7 @@ class BBoxUtility(object):
                        anchors.data_ptr(), float(confidence), float(nms_iou), int(top_k), max_det, 1 if logits else 0)
         pout = YolactOut(out.boxes.data_ptr(), out.scores.data_ptr(), out.class_ids.data_ptr(), out.masks_arg.data_ptr(),
                          out.masks_raw.data_ptr(), out.masks_raw.shape[1], out.counts.data_ptr())
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             h.check(h.lib.isb_yolact_detect(h.ptr, C.byref(pin), C.byref(pout), _stream(dev)))
         return out
 
@@ -264,7 +264,7 @@ class BBoxUtility(object):
         pin = YolactIn(bsz, a, c, k, ph, pw, hgt, wid, box.data_ptr(), conf.data_ptr(), coef.data_ptr(), proto.data_ptr(),
                        anchors.data_ptr(), float(confidence), float(nms_iou), int(top_k), max_det, 1 if logits else 0)
         pout = YolactMapOut(*[t.data_ptr() for t in out])
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             h.check(h.lib.isb_yolact_class_map(h.ptr, C.byref(pin), C.byref(pout), _stream(dev)))
         return out
 
@@ -324,7 +324,7 @@ class BBoxUtility(object):
         cap = max(4096, 8 * wid * m)  # a blob crosses a column twice; grown below if the masks are busier
         while True:
             out = torch.empty((cap,), dtype=torch.int32, device=dev)
-            with torch.cuda.device(dev):
+            with _lib.on_device(dev):
                 h.check(h.lib.isb_rle_encode(h.ptr, raw.data_ptr(), raw.numel(), None, m, m, 1, hgt, wid, out.data_ptr(), cap,
                                              run_count.data_ptr(), run_off.data_ptr(), totals.data_ptr(), _stream(dev)))
             need = int(totals[1].item())
