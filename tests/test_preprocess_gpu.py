@@ -80,6 +80,24 @@ def test_pil_inputs_and_grey_pictures(pre):
     assert np.array_equal(np.array(pre.resize_image(pil, (30, 20))), np.array(pil.resize((30, 20), Image.BICUBIC)))
 
 
+@pytest.mark.parametrize("offset", [1, 2, 3, 5])
+def test_unaligned_picture_pointer(pre, offset):
+    """The staging loads are 32-bit and aligned down: a picture buffer that starts at an odd byte address (a view into a
+    larger allocation) takes the guarded loads at both ends of the buffer and a non-zero funnel shift on every row."""
+    rng = np.random.RandomState(40 + offset)
+    b, h, w = 2, 37, 53
+    imgs = rng.randint(0, 256, (b, h, w, 3), dtype=np.uint8)
+    flat = torch.zeros(offset + imgs.size, dtype=torch.uint8, device="cuda")
+    flat[offset:] = torch.from_numpy(imgs.reshape(-1)).cuda()
+    view = flat[offset:].view(b, h, w, 3)
+    assert view.data_ptr() % 4 == offset % 4 and view.is_contiguous()
+    out, res = pre.image_to_input(view, (19, 23), return_resized=True)
+    for i in range(b):
+        ref = P.resize_u8(imgs[i], 23, 19)
+        assert np.array_equal(res[i].cpu().numpy(), ref)
+        assert np.array_equal(out[i:i + 1].cpu().numpy(), P.normalize_chw(ref))
+
+
 def test_value_table_follows_mean_std(pre):
     img = synth.picture(5, 40, 60)
     a = pre.image_to_input(img, (20, 30)).cpu().numpy()
