@@ -98,6 +98,25 @@ def test_unaligned_picture_pointer(pre, offset):
         assert np.array_equal(out[i:i + 1].cpu().numpy(), P.normalize_chw(ref))
 
 
+def test_benchmark_size_batch_properties(pre):
+    """Eight 1080 x 1920 pictures to the 550 x 550 network input in one call: every picture of the batch equals the
+    same picture processed alone (pictures are independent, the intermediate image is per picture), two of them equal
+    the numpy oracle bit for bit, and a second call gives the same bytes (no state carried between calls)."""
+    pics = np.stack([synth.picture(300 + i, 1080, 1920) for i in range(8)])
+    dev_pics = torch.from_numpy(pics).cuda()
+    out, res = pre.image_to_input(dev_pics, (550, 550), return_resized=True)
+    assert out.shape == (8, 3, 550, 550) and res.shape == (8, 550, 550, 3)
+    for i in (0, 3, 7):
+        o1, r1 = pre.image_to_input(dev_pics[i], (550, 550), return_resized=True)
+        assert torch.equal(o1[0], out[i]) and torch.equal(r1[0], res[i])
+    for i in (1, 6):
+        ref = P.resize_u8(pics[i], 550, 550)
+        assert np.array_equal(res[i].cpu().numpy(), ref)
+        assert np.array_equal(out[i:i + 1].cpu().numpy(), P.normalize_chw(ref))
+    out2 = pre.image_to_input(dev_pics, (550, 550))
+    assert torch.equal(out, out2)
+
+
 def test_value_table_follows_mean_std(pre):
     img = synth.picture(5, 40, 60)
     a = pre.image_to_input(img, (20, 30)).cpu().numpy()
