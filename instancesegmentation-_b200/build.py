@@ -8,7 +8,7 @@ LIB = os.path.join(PKG, "libisb.so")
 
 
 def build(verbose=False):
-    cmd = ["make", "-C", CSRC, f"OUT={LIB}"]
+    cmd = ["make", "-j", str(os.cpu_count() or 4), "-C", CSRC, f"OUT={LIB}"]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or res.returncode != 0:
         print(res.stdout)

@@ -290,6 +290,7 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const Yo
   mp.mask_slot_bytes = out->mask_slot_bytes;
   mp.class_map = out->class_map;
   mp.class_ids = out->class_ids;
+  mp.class_stride = in->max_det;  // fnms_emit wrote the caller's [B, in->max_det] array
   mp.map_only = out->map_only;
   h->prof_mid = ev ? ev[3] : nullptr;  // recorded between the sigmoid-map and the compose kernel
   rc = launch_masks(h, mp, s);

@@ -30,6 +30,7 @@ __host__ __device__ inline uint32_t float_desc_bits(float f) {
 #else
   memcpy(&u, &f, 4);
 #endif
+  if ((u & 0x7fffffffu) > 0x7f800000u) u = 0x7fc00000u;  // any NaN ranks first, before +inf, as in torch.sort(descending=True)
   u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);  // ascending orderable
   return ~u;
 }
@@ -422,7 +423,8 @@ struct MaskParams {
   int64_t mask_slot_bytes;
   // optional per-pixel class map (yolact.py:167-169): class_ids[arg] + 1 where the arg-max mask is set, else 0
   uint8_t* class_map;        // [B, H, W] or nullptr
-  const int64_t* class_ids;  // [B, det_stride], needed with class_map
+  const int64_t* class_ids;  // [B, class_stride], needed with class_map
+  int32_t class_stride;      // rows between images in class_ids (the CALLER's array: in->max_det, not the workspace stride)
   int32_t map_only;          // 1: masks / masks_arg are not produced at all
 };
 int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s);

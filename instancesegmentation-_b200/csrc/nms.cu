@@ -24,16 +24,19 @@ namespace isb {
 
 constexpr int kScanThreads = 1024;
 
+// boxes.max() of boxes.py:78 propagates NaN (torch.max); fmaxf would drop it
+__device__ __forceinline__ float nan_max(float a, float b) { return (a != a || b != b) ? __int_as_float(0x7fc00000) : fmaxf(a, b); }
+
 __global__ void nms_max_coord_kernel(const float4* __restrict__ boxes, int n_max, const int32_t* __restrict__ n_dev,
                                      uint32_t* __restrict__ scalars) {
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   float m = -INFINITY;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const float4 b = boxes[i];
-    m = fmaxf(fmaxf(m, fmaxf(b.x, b.y)), fmaxf(b.z, b.w));
+    m = nan_max(nan_max(m, nan_max(b.x, b.y)), nan_max(b.z, b.w));
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  for (int o = 16; o > 0; o >>= 1) m = nan_max(m, __shfl_xor_sync(0xffffffffu, m, o));
   if ((threadIdx.x & 31) == 0) atomicMin(&scalars[0], float_desc_bits(m));  // smaller desc-bits == larger float
 }
 
@@ -119,9 +122,15 @@ __global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__
       if (offset_groups && zero_hits) bits |= 1ull << j;
       continue;
     }
+    // torchvision's CPU kernel (the reference's path, boxes.py:35): std::max(i, j) = (i < j) ? j : i and
+    // std::min(i, j) = (j < i) ? j : i with i = the higher-ranked box (the COLUMN box c here), j = the row box a --
+    // this decides what a NaN coordinate does; max(0, d) = (0 < d) ? d : 0 turns a NaN extent into 0.
     const float4 c = cbox[j];
-    const float w = fmaxf(0.0f, fminf(a.z, c.z) - fmaxf(a.x, c.x));
-    const float hgt = fmaxf(0.0f, fminf(a.w, c.w) - fmaxf(a.y, c.y));
+    const float xx1 = (c.x < a.x) ? a.x : c.x, yy1 = (c.y < a.y) ? a.y : c.y;
+    const float xx2 = (a.z < c.z) ? a.z : c.z, yy2 = (a.w < c.w) ? a.w : c.w;
+    const float dw = xx2 - xx1, dh = yy2 - yy1;
+    const float w = (0.0f < dw) ? dw : 0.0f;
+    const float hgt = (0.0f < dh) ? dh : 0.0f;
     const float inter = w * hgt;
     const float uni = (aa + carea[j]) - inter;
     bool hit;

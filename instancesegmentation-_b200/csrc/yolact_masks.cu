@@ -207,7 +207,7 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
     uint8_t* out_img = kMasks ? p.masks + (size_t)b * p.mask_slot_bytes : nullptr;
     int64_t* arg_img = kMasks ? p.masks_arg + (size_t)b * HW : nullptr;
     uint8_t* cmap_img = p.class_map ? p.class_map + (size_t)b * HW : nullptr;
-    const int64_t* cls_img = p.class_ids + (size_t)b * p.det_stride;
+    const int64_t* cls_img = p.class_ids + (size_t)b * p.class_stride;
     const float* S_img = smap + (size_t)b * g.s_cap;
 
     // ---- per-row bilinear taps of the unit's rows, detections that meet those rows (ascending index) ----

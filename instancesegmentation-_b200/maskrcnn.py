@@ -1,12 +1,23 @@
 """Drop-ins for the Mask R-CNN post-processing functions of the reference
-(inst_model/Mask_RCNN/net/network_files/...): same names, argument order and return types; the work
-is done by libisb.so on the tensors' CUDA device and current stream.
+(inst_model/Mask_RCNN/net/network_files/...); the work is done by libisb.so on the tensors' CUDA device and
+current stream.
 
+Module-level functions with the reference's names, argument order and return types (rebound by isb.patch):
     nms, batched_nms                  boxes.py:7, :38
-    decode_single                     det_utils.py:224  (BoxCoder.decode_single)
     MultiScaleRoIAlign                torchvision module constructed at faster_rcnn_framework.py:326, mask_rcnn.py:150
     maskrcnn_inference                roi_head.py:59
     resize_boxes, paste_masks_in_image  transform.py:462, :212
+
+METHOD drop-ins: same `(self, ...)` signatures as the reference's methods, reading the same attributes of `self`;
+isb.patch binds them onto the reference's classes, so a patched reference model reaches the fused kernels
+without any edit of the reference tree:
+    BoxCoder.decode_single            det_utils.py:224   -> boxcoder_decode_single    (isb_box_decode)
+    RegionProposalNetwork.filter_proposals  rpn_function.py:460 -> rpn_filter_proposals (isb_rpn_filter per image)
+    RoIHeads.postprocess_detections   roi_head.py:366    -> roiheads_postprocess_detections (isb_box_postprocess)
+    GeneralizedRCNNTransform.postprocess  transform.py:388 -> transform_postprocess   (isb_resize_boxes + isb_paste_masks)
+
+Functional forms with explicit parameters (one image, used by the stage tests and benches):
+    decode_single, filter_proposals, postprocess_detections
 """
 from __future__ import annotations
 
@@ -148,6 +159,93 @@ def postprocess_detections(class_logits, box_regression, proposals, image_shape,
     if k < 0:
         raise RuntimeError("postprocess_detections: class_probs rows exceed the candidate bound (do they sum to 1?)")
     return out_b[:k], out_s[:k], out_l[:k]
+
+
+# ---------------------------------------------------------------------------- method drop-ins
+def boxcoder_decode_single(self, rel_codes, boxes):
+    """`BoxCoder.decode_single(self, rel_codes, boxes)` (det_utils.py:224-267): reads `self.weights` and
+    `self.bbox_xform_clip` like the reference; rel_codes [N,4k], boxes [N,4] -> [N,4k]."""
+    return decode_single(rel_codes, boxes.to(rel_codes.dtype), self.weights, self.bbox_xform_clip)
+
+
+def rpn_filter_proposals(self, proposals, objectness, image_shapes, num_anchors_per_level):
+    """`RegionProposalNetwork.filter_proposals(self, proposals, objectness, image_shapes, num_anchors_per_level)`
+    (rpn_function.py:460-529, with `_get_top_n_idx` :434-458 folded in): proposals [N,A,4] decoded boxes, objectness
+    [N*A,1] or [N,A] logits -> (List[Tensor [k_i,4]], List[Tensor [k_i]]).  Reads `self.pre_nms_top_n()`,
+    `self.post_nms_top_n()`, `self.nms_thresh`, `self.score_thresh`, `self.min_size` exactly as the reference does.
+    One fused launch sequence per image into padded [N,post,..] buffers, then ONE 4N-byte read of the counts for the
+    variable-length views the reference's return type needs (the reference synchronises several times per image)."""
+    num_images = proposals.shape[0]
+    proposals = _cuda_f32(proposals.detach(), "proposals").reshape(num_images, -1, 4)
+    dev = proposals.device
+    objectness = _cuda_f32(objectness.detach(), "objectness").to(dev).reshape(num_images, -1)      # :475-476
+    post, pre = int(self.post_nms_top_n()), int(self.pre_nms_top_n())
+    nlev = len(num_anchors_per_level)
+    levels = (C.c_int32 * nlev)(*[int(v) for v in num_anchors_per_level])
+    out_b = torch.empty((num_images, post, 4), dtype=torch.float32, device=dev)
+    out_s = torch.empty((num_images, post), dtype=torch.float32, device=dev)
+    counts = torch.zeros((num_images,), dtype=torch.int32, device=dev)
+    h = get_handle(dev.index)
+    with _lib.on_device(dev):
+        for i in range(num_images):
+            shp = image_shapes[i]
+            h.check(h.lib.isb_rpn_filter(h.ptr, _ptr(proposals[i]), _ptr(objectness[i]), levels, nlev, int(shp[0]), int(shp[1]),
+                                         pre, post, float(self.nms_thresh), float(self.score_thresh), float(self.min_size),
+                                         _ptr(out_b[i]), _ptr(out_s[i]), C.c_void_p(counts[i:].data_ptr()), _stream(dev)))
+    ks = counts.tolist()
+    return [out_b[i, :k] for i, k in enumerate(ks)], [out_s[i, :k] for i, k in enumerate(ks)]
+
+
+def roiheads_postprocess_detections(self, class_logits, box_regression, proposals, image_shapes):
+    """`RoIHeads.postprocess_detections(self, class_logits, box_regression, proposals, image_shapes)`
+    (roi_head.py:366-457): class_logits [sum R_i, C], box_regression [sum R_i, 4C], proposals List[[R_i,4]] ->
+    (List[boxes [k_i,4]], List[scores [k_i]], List[labels int64 [k_i]]).  Reads `self.box_coder.weights`,
+    `self.box_coder.bbox_xform_clip`, `self.score_thresh`, `self.nms_thresh`, `self.detection_per_img`.
+    Decode, softmax, clip, filters, per-class NMS and top-k are one fused sequence per image; one read of the counts."""
+    logits = _cuda_f32(class_logits.detach(), "class_logits")
+    dev = logits.device
+    reg = _cuda_f32(box_regression.detach(), "box_regression").to(dev)
+    num_classes = logits.shape[-1]
+    per_image = [int(p.shape[0]) for p in proposals]
+    n_img, d = len(per_image), int(self.detection_per_img)
+    wx, wy, ww, wh = [float(w) for w in self.box_coder.weights]
+    clip = float(self.box_coder.bbox_xform_clip)
+    out_b = torch.empty((n_img, d, 4), dtype=torch.float32, device=dev)
+    out_s = torch.empty((n_img, d), dtype=torch.float32, device=dev)
+    out_l = torch.empty((n_img, d), dtype=torch.int64, device=dev)
+    counts = torch.zeros((max(n_img, 1),), dtype=torch.int32, device=dev)
+    h = get_handle(dev.index)
+    null = C.c_void_p(0)
+    row = 0
+    with _lib.on_device(dev):
+        for i, r in enumerate(per_image):
+            props = _cuda_f32(proposals[i].detach(), "proposals").to(dev)
+            shp = image_shapes[i]
+            if r > 0:
+                h.check(h.lib.isb_box_postprocess(h.ptr, _ptr(logits[row:row + r]), null, _ptr(reg[row:row + r]), _ptr(props), r,
+                                                  num_classes, int(shp[0]), int(shp[1]), wx, wy, ww, wh, clip,
+                                                  float(self.score_thresh), float(self.nms_thresh), d, _ptr(out_b[i]),
+                                                  _ptr(out_s[i]), _ptr(out_l[i]), C.c_void_p(counts[i:].data_ptr()), _stream(dev)))
+            row += r
+    ks = counts[:n_img].tolist()
+    if any(k < 0 for k in ks):
+        raise RuntimeError("postprocess_detections: candidate bound exceeded")
+    return ([out_b[i, :k] for i, k in enumerate(ks)], [out_s[i, :k] for i, k in enumerate(ks)],
+            [out_l[i, :k] for i, k in enumerate(ks)])
+
+
+def transform_postprocess(self, result, image_shapes, original_image_sizes):
+    """`GeneralizedRCNNTransform.postprocess(self, result, image_shapes, original_image_sizes)` (transform.py:388-418):
+    per image, boxes back to the original frame (resize_boxes :462) and the 28x28 mask probabilities pasted into
+    [m,1,H,W] (paste_masks_in_image :212).  Training mode returns `result` untouched (:404-405)."""
+    if getattr(self, "train_mode", None):
+        return result
+    for i, (pred, im_s, o_im_s) in enumerate(zip(result, image_shapes, original_image_sizes)):
+        boxes = resize_boxes(pred["boxes"], im_s, o_im_s)                                 # :410
+        result[i]["boxes"] = boxes
+        if "masks" in pred:
+            result[i]["masks"] = paste_masks_in_image(pred["masks"], boxes, o_im_s)       # :415
+    return result
 
 
 # ---------------------------------------------------------------------------- MultiScaleRoIAlign

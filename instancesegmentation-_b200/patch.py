@@ -9,6 +9,11 @@ What is rebound:
   ...network_files.boxes.nms / batched_nms                  -> isb.maskrcnn.*           (rpn_function.py:521, roi_head.py:446)
   ...network_files.transform.paste_masks_in_image / resize_boxes -> isb.maskrcnn.*      (transform.py:410,415)
   ...network_files.roi_head.maskrcnn_inference              -> isb.maskrcnn.maskrcnn_inference (roi_head.py:555)
+  METHODS, bound onto the reference's classes (same `(self, ...)` signatures, same attributes of self read):
+  ...det_utils.BoxCoder.decode_single                       -> isb.maskrcnn.boxcoder_decode_single      (det_utils.py:224)
+  ...rpn_function.RegionProposalNetwork.filter_proposals    -> isb.maskrcnn.rpn_filter_proposals        (rpn_function.py:460)
+  ...roi_head.RoIHeads.postprocess_detections               -> isb.maskrcnn.roiheads_postprocess_detections (roi_head.py:366)
+  ...transform.GeneralizedRCNNTransform.postprocess         -> isb.maskrcnn.transform_postprocess       (transform.py:388)
   torchvision MultiScaleRoIAlign instances of a built model -> isb.maskrcnn.MultiScaleRoIAlign (swap_roi_pools)
   model.transform.forward (GeneralizedRCNNTransform)         -> isb.maskrcnn.rcnn_transform (swap_transform)
 """
@@ -25,7 +30,25 @@ _REBIND = [
     ("inst_model.Mask_RCNN.net.network_files.transform", "paste_masks_in_image", lambda: maskrcnn.paste_masks_in_image),
     ("inst_model.Mask_RCNN.net.network_files.transform", "resize_boxes", lambda: maskrcnn.resize_boxes),
     ("inst_model.Mask_RCNN.net.network_files.roi_head", "maskrcnn_inference", lambda: maskrcnn.maskrcnn_inference),
+    # methods: "Class.method" is resolved inside the module and set on the class, so every instance -- built before or
+    # after install() -- dispatches to the drop-in
+    ("inst_model.Mask_RCNN.net.network_files.det_utils", "BoxCoder.decode_single", lambda: maskrcnn.boxcoder_decode_single),
+    ("inst_model.Mask_RCNN.net.network_files.rpn_function", "RegionProposalNetwork.filter_proposals",
+     lambda: maskrcnn.rpn_filter_proposals),
+    ("inst_model.Mask_RCNN.net.network_files.roi_head", "RoIHeads.postprocess_detections",
+     lambda: maskrcnn.roiheads_postprocess_detections),
+    ("inst_model.Mask_RCNN.net.network_files.transform", "GeneralizedRCNNTransform.postprocess",
+     lambda: maskrcnn.transform_postprocess),
 ]
+
+
+def _owner(mod, attr):
+    """("Class.method") -> (class object, "method"); ("name") -> (module, "name")."""
+    owner = mod
+    parts = attr.split(".")
+    for part in parts[:-1]:
+        owner = getattr(owner, part)
+    return owner, parts[-1]
 
 
 def install(only=None, strict=False):
@@ -34,7 +57,7 @@ def install(only=None, strict=False):
     `strict`."""
     done = []
     for mod_name, attr, getter in _REBIND:
-        if only is not None and attr not in only:
+        if only is not None and attr not in only and attr.split(".")[-1] not in only:
             continue
         try:
             mod = importlib.import_module(mod_name)
@@ -44,8 +67,9 @@ def install(only=None, strict=False):
             continue
         if not hasattr(mod, "_isb_original"):
             mod._isb_original = {}
-        mod._isb_original.setdefault(attr, getattr(mod, attr))
-        setattr(mod, attr, getter())
+        owner, name = _owner(mod, attr)
+        mod._isb_original.setdefault(attr, owner.__dict__[name] if isinstance(owner, type) else getattr(owner, name))
+        setattr(owner, name, getter())
         done.append((mod_name, attr))
     return done
 
@@ -58,7 +82,8 @@ def uninstall():
             continue
         orig = getattr(mod, "_isb_original", {})
         if attr in orig:
-            setattr(mod, attr, orig.pop(attr))
+            owner, name = _owner(mod, attr)
+            setattr(owner, name, orig.pop(attr))
 
 
 def swap_roi_pools(model):

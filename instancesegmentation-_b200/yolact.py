@@ -54,7 +54,10 @@ class YolactBatchResult:
         """Reference-shaped 5-tuple for image b (reads counts[b] from the device if m is None)."""
         if m is None:
             m = int(self.counts[b].item())
-        if m <= 0:
+        if m < 0:
+            raise _lib.IsbError(_lib.ISB_ERR_OVERFLOW, f"image {b}: candidate buffer overflow (counts = -1): raise "
+                                "cand_capacity (isb._lib.get_handle(device, cand_capacity=...)) and run the batch again")
+        if m == 0:
             return (None,) * 5
         h, w = self.out_hw
         masks = self.masks_raw[b, : h * w * m].view(h, w, m).view(torch.bool)

@@ -216,7 +216,126 @@ def transform_golden(name, seed):
     _save(name, **out)
 
 
+def chain(name, seed, num_classes=21, image_shape=(800, 1333), original_size=(600, 1000)):
+    """The whole inference post-processing chain of the reference at configs[3] size, run by the reference's OWN objects:
+    BoxCoder.decode (rpn_function.py:624) -> RegionProposalNetwork.filter_proposals (:460) -> RoIHeads.forward
+    (roi_head.py:459-557: box_roi_pool 7x7, postprocess_detections, mask_roi_pool 14x14, maskrcnn_inference) ->
+    GeneralizedRCNNTransform.postprocess (transform.py:388-418).  The network layers in between (box head, predictors,
+    mask head) are the deterministic stand-ins of oracle/synth.py; everything else is reference / torchvision code."""
+    from torchvision.ops import MultiScaleRoIAlign
+    from . import synth
+    R = _ref()
+    feats, anchors, deltas, logits, per_level = synth.chain_inputs(seed)
+    coder = R.det_utils.BoxCoder((1.0, 1.0, 1.0, 1.0))
+    proposals = coder.decode(deltas, [anchors]).view(1, -1, 4)                       # rpn_function.py:624-625
+    rpn = R.rpn.RegionProposalNetwork(None, None, 0.7, 0.3, 256, 0.5, dict(training=2000, testing=1000),
+                                      dict(training=2000, testing=1000), 0.7, train_mode=False)
+    boxes, scores = rpn.filter_proposals(proposals, logits[None], [image_shape], per_level)
+    heads = R.roi_head.RoIHeads(MultiScaleRoIAlign(["0", "1", "2", "3"], 7, 2), synth.ChainBoxHead(),
+                                synth.ChainBoxPredictor(num_classes), 0.5, 0.5, 512, 0.25, None, 0.05, 0.5, 100,
+                                mask_roi_pool=MultiScaleRoIAlign(["0", "1", "2", "3"], 14, 2), mask_head=torch.nn.Identity(),
+                                mask_predictor=synth.ChainMaskPredictor(num_classes), train_mode=False)
+    fd = OrderedDict((str(i), f) for i, f in enumerate(feats))
+    with torch.no_grad():
+        det, _ = heads(fd, boxes, [image_shape])
+    masks28 = det[0]["masks"].clone()
+    boxes_net = det[0]["boxes"].clone()
+    tf = R.transform.GeneralizedRCNNTransform(800, 1333, IMAGENET_MEAN, IMAGENET_STD, train_mode=False)
+    out = tf.postprocess(det, [image_shape], [original_size])[0]
+    pasted = out["masks"]
+    nz = pasted != 0
+    _save(name, seed=seed, num_classes=num_classes, image_shape=np.array(image_shape), original_size=np.array(original_size),
+          input_digest=digest(*[f.numpy() for f in feats], anchors.numpy(), deltas.numpy(), logits.numpy()),
+          rpn_boxes=boxes[0].numpy(), rpn_scores=scores[0].numpy(),
+          det_boxes_net=boxes_net.numpy(), det_scores=out["scores"].numpy(), det_labels=out["labels"].numpy(),
+          masks28=masks28.numpy(), det_boxes=out["boxes"].numpy(),
+          pasted_sub=pasted[:, :, ::5, ::7].numpy(), pasted_sum=pasted.double().sum(dim=(1, 2, 3)).numpy(),
+          pasted_nonzero=nz.sum(dim=(1, 2, 3)).numpy(),
+          pasted_rows=np.packbits(nz.any(dim=3).numpy()), pasted_cols=np.packbits(nz.any(dim=2).numpy()))
+
+
+def paste_full(name, seed, m=100, image_shape=(800, 1333)):
+    """paste_masks_in_image (transform.py:212-230) at configs[3] size: 100 masks into (800, 1333) = 426.6 MB of float32.
+    Stored: a sub-sampled copy, per-mask float64 sums, the exact zero pattern as row / column occupancy and counts."""
+    R = _ref()
+    g = torch.Generator().manual_seed(seed)
+    boxes = clustered_boxes(g, m, extent=(1250.0, 760.0), clusters=30, jitter=9.0)
+    boxes[0] = torch.tensor([-20.5, -11.0, 300.2, 410.0])
+    boxes[1] = torch.tensor([1200.0, 700.0, 1400.0, 830.5])
+    boxes[2] = torch.tensor([0.0, 0.0, 1333.0, 800.0])
+    boxes[3] = torch.tensor([640.3, 400.2, 640.9, 400.6])
+    probs = torch.rand(m, 1, 28, 28, generator=g)
+    pasted = R.transform.paste_masks_in_image(probs, boxes, image_shape)
+    nz = pasted != 0
+    _save(name, seed=seed, image_shape=np.array(image_shape), boxes=boxes.numpy(), probs=probs.numpy(),
+          sub=pasted[:, :, ::7, ::9].numpy(), sums=pasted.double().sum(dim=(1, 2, 3)).numpy(),
+          nonzero=nz.sum(dim=(1, 2, 3)).numpy(), rows=np.packbits(nz.any(dim=3).numpy()), cols=np.packbits(nz.any(dim=2).numpy()),
+          full2=pasted[[0, 57], 0].numpy())
+
+
+def nan_inf(name, seed):
+    """NaN / +-inf boxes and scores through the reference's own Fast NMS (utils_bbox.py:27-99: torch.min / max / clamp and
+    the column max propagate NaN, so a NaN IoU suppresses) and through boxes.nms / batched_nms (boxes.py:7-83 ->
+    torchvision's CPU kernel, std::max / std::min and `ovr > thr`, where a NaN IoU does NOT suppress)."""
+    from .gen_golden import _ref as _yolact_ref
+    R = _ref()
+    bu = _yolact_ref()
+    g = torch.Generator().manual_seed(seed)
+    nan, inf = float("nan"), float("inf")
+    # ---- Fast NMS: 3 classes x 64 boxes, clustered so that plenty of pairs overlap
+    n, c = 64, 3
+    box = clustered_boxes(g, n, extent=(1.0, 1.0), clusters=6, jitter=0.01)
+    box = torch.cat([box[:, :2].clamp(0, 1), box[:, :2].clamp(0, 1) + (torch.rand(n, 2, generator=g) * 0.2 + 0.05)], 1)
+    sc = torch.rand(n, c, generator=g)
+    coef = torch.tanh(torch.randn(n, 32, generator=g))
+    box[3, 0] = nan                      # NaN corner: NaN area -> suppresses every lower-ranked box of each class it is in
+    box[9] = torch.tensor([0.2, 0.2, inf, 0.6])        # infinite width: IoU 0 with everything
+    box[17] = torch.tensor([-inf, 0.1, inf, 0.9])      # infinite both ways
+    box[25] = torch.tensor([inf, 0.3, inf, 0.5])       # inf - inf = NaN area
+    box[31] = torch.tensor([0.4, 0.4, 0.4, inf])       # zero width x infinite height: 0 * inf = NaN intersection
+    sc[40, 0] = inf
+    sc[41, 1] = -inf
+    sc[42, 2] = nan                      # torch.sort(descending=True) ranks NaN first
+    sc[3, 0] = 0.99                      # the NaN box near the top of class 0 ...
+    sc[3, 1] = 0.0001                    # ... and at the bottom of class 1
+    out = dict(seed=seed, f_box=box.numpy(), f_scores=sc.numpy(), f_coef=coef.numpy())
+    for tag, thr, top_k, max_det in (("a", 0.5, 200, 100), ("b", 0.3, 20, 15)):
+        b, s, cl, k = bu.fast_non_max_suppression(box, sc, coef, thr, top_k, max_det)
+        out.update({f"f{tag}_box": b.numpy(), f"f{tag}_score": s.numpy(), f"f{tag}_cls": cl.numpy(), f"f{tag}_coef": k.numpy(),
+                    f"f{tag}_params": np.array([thr, top_k, max_det])})
+    out["f_iou"] = bu.jaccard(box[:12], box[:36]).numpy()
+    # ---- torchvision-style greedy NMS
+    m = 90
+    nb = clustered_boxes(g, m, extent=(300.0, 200.0), clusters=8, jitter=3.0)
+    ns = torch.rand(m, generator=g)
+    idx = torch.randint(0, 3, (m,), generator=g)
+    nb[5, 2] = nan
+    nb[11, 1] = nan
+    nb[20] = torch.tensor([10.0, 10.0, inf, 80.0])
+    nb[33] = torch.tensor([-inf, -inf, inf, inf])
+    nb[47] = torch.tensor([inf, 5.0, inf, 50.0])
+    ns[60] = inf
+    ns[61] = -inf
+    ns[62] = nan
+    ns[5] = 0.97
+    out.update(n_boxes=nb.numpy(), n_scores=ns.numpy(), n_idxs=idx.numpy(),
+               n_keep=R.boxes.nms(nb, ns, 0.5).numpy(), n_keep_b=R.boxes.batched_nms(nb, ns, idx, 0.5).numpy())
+    # finite boxes, non-finite scores only (batched_nms' max coordinate stays finite)
+    fb = clustered_boxes(g, m, extent=(300.0, 200.0), clusters=8, jitter=3.0)
+    out.update(n2_boxes=fb.numpy(), n2_keep=R.boxes.nms(fb, ns, 0.5).numpy(), n2_keep_b=R.boxes.batched_nms(fb, ns, idx, 0.5).numpy())
+    # one infinite coordinate: boxes.py:78 max_coordinate = inf -> offsets inf / NaN
+    ib = fb.clone()
+    ib[7, 2] = inf
+    fs = torch.rand(m, generator=g)
+    out.update(n3_boxes=ib.numpy(), n3_scores=fs.numpy(), n3_keep=R.boxes.nms(ib, fs, 0.5).numpy(),
+               n3_keep_b=R.boxes.batched_nms(ib, fs, idx, 0.5).numpy())
+    _save(name, **out)
+
+
 def main():
+    nan_inf("nan_inf_cases", 4801)
+    chain("maskrcnn_chain", 4601)
+    paste_full("maskrcnn_paste_full", 4701)
     transform_golden("maskrcnn_transform", 4501)
     class_image("maskrcnn_class_image", 4401)
     stages("maskrcnn_stages", 31)

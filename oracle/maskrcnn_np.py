@@ -22,7 +22,8 @@ BBOX_XFORM_CLIP = math.log(1000.0 / 16)   # det_utils.py:146
 
 
 def _desc_stable(x):
-    return np.argsort(-np.asarray(x), kind="stable")
+    from .yolact_np import _argsort_desc_stable
+    return _argsort_desc_stable(np.asarray(x), axis=0)    # NaN first, like torch.sort(descending=True)
 
 
 # --------------------------------------------------------------------------- M1
@@ -71,6 +72,9 @@ def nms(boxes, scores, iou_threshold):
     Greedy: visit boxes by stable-descending score; a visited, unsuppressed box suppresses every later
     box whose IoU with it is > threshold.  IoU = inter / ((area_i + area_j) - inter) in float32 with
     inter = max(0, xx2-xx1) * max(0, yy2-yy1); the comparison is against the threshold as a double.
+    max / min are the C++ std::max(a, b) = (a < b) ? b : a and std::min(a, b) = (b < a) ? b : a with a = the visited
+    (higher-ranked) box, which fixes what a NaN coordinate does; `ovr > thr` is false for a NaN overlap, so NaN never
+    suppresses here (the opposite of Fast NMS).
     Returns kept indices (int64) in decreasing score order.
     """
     b = np.asarray(boxes, dtype=F32)
@@ -90,9 +94,15 @@ def nms(boxes, scores, iou_threshold):
             continue
         keep.append(i)
         rest = order[pos + 1:]
-        w = np.maximum(F32(0), np.minimum(x2[i], x2[rest]) - np.maximum(x1[i], x1[rest]))
-        h = np.maximum(F32(0), np.minimum(y2[i], y2[rest]) - np.maximum(y1[i], y1[rest]))
-        inter = w * h
+        with np.errstate(invalid="ignore"):
+            xx1 = np.where(x1[i] < x1[rest], x1[rest], x1[i])
+            yy1 = np.where(y1[i] < y1[rest], y1[rest], y1[i])
+            xx2 = np.where(x2[rest] < x2[i], x2[rest], x2[i])
+            yy2 = np.where(y2[rest] < y2[i], y2[rest], y2[i])
+            dw, dh = xx2 - xx1, yy2 - yy1
+            w = np.where(F32(0) < dw, dw, F32(0))
+            h = np.where(F32(0) < dh, dh, F32(0))
+            inter = w * h
         with np.errstate(divide="ignore", invalid="ignore"):
             ovr = inter / ((areas[i] + areas[rest]) - inter)
         suppressed[rest[ovr.astype(np.float64) > thr]] = True
@@ -104,9 +114,11 @@ def batched_nms(boxes, scores, idxs, iou_threshold):
     b = np.asarray(boxes, dtype=F32)
     if b.size == 0:
         return np.zeros((0,), np.int64)
-    max_coordinate = b.max()
-    offsets = np.asarray(idxs).astype(F32) * (max_coordinate + F32(1))
-    return nms(b + offsets[:, None], scores, iou_threshold)
+    max_coordinate = b.max()                                   # propagates NaN like torch's boxes.max()
+    with np.errstate(invalid="ignore", over="ignore"):
+        offsets = np.asarray(idxs).astype(F32) * (max_coordinate + F32(1))
+        shifted = b + offsets[:, None]
+    return nms(shifted, scores, iou_threshold)
 
 
 # --------------------------------------------------------------------------- M2, M3

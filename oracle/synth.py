@@ -180,3 +180,47 @@ def picture(seed, h, w):
         img[y0:y1, x0:x1] = rs.randint(0, 256, 3)
     img += rs.randint(-8, 9, img.shape)
     return np.clip(img, 0, 255).astype(np.uint8)
+
+
+# --------------------------------------------------------------------------- Mask R-CNN chain test
+class ChainBoxHead(torch.nn.Module):
+    """Stand-in for TwoMLPHead (faster_rcnn_framework.py:203): spatial mean of the 7x7 RoI features in float64, so the
+    result does not depend on the device's summation order beyond one final rounding.  [R,256,7,7] -> [R,256]."""
+
+    def forward(self, x):
+        return x.double().mean(dim=(2, 3)).float()
+
+
+class ChainBoxPredictor(torch.nn.Module):
+    """Stand-in for FastRCNNPredictor (faster_rcnn_framework.py:226): element-wise maps of selected channels -- no
+    matmul, so CPU and GPU agree to the last bit given equal inputs.  -> (class_logits [R,C], box_regression [R,4C])."""
+
+    def __init__(self, num_classes):
+        super().__init__()
+        self.c = int(num_classes)
+
+    def forward(self, x):
+        c = self.c
+        logits = x[:, :c] * 14.0
+        logits = torch.cat([logits[:, :1] + 2.0, logits[:, 1:]], 1)
+        reg = x[:, c:5 * c] * torch.tensor([6.0, 6.0, 3.0, 3.0], device=x.device).repeat(c)
+        return logits.contiguous(), reg.contiguous()
+
+
+class ChainMaskPredictor(torch.nn.Module):
+    """Stand-in for MaskRCNNHeads + MaskRCNNPredictor (mask_rcnn.py:62-105): nearest 2x up-sampling of the first C
+    channels of the 14x14 RoI features, scaled.  [m,256,14,14] -> [m,C,28,28]."""
+
+    def __init__(self, num_classes):
+        super().__init__()
+        self.c = int(num_classes)
+
+    def forward(self, x):
+        return (x[:, :self.c].repeat_interleave(2, dim=2).repeat_interleave(2, dim=3) * 3.0).contiguous()
+
+
+def chain_inputs(seed, image_hw=(800, 1344)):
+    """Inputs of the chained Mask R-CNN test at configs[3] size: FPN features, RPN anchors / deltas / logits."""
+    feats = fpn_features(seed, 256, image_hw)
+    anchors, deltas, logits, per_level = rpn_heads(seed + 1, image_hw)
+    return feats, anchors, deltas, logits, per_level

@@ -91,8 +91,17 @@ def jaccard(box_a, box_b):
 
 
 def _argsort_desc_stable(x, axis=-1):
-    """Descending sort order with ties kept in ascending index order."""
-    return np.argsort(-x, axis=axis, kind="stable")
+    """Descending sort order with ties kept in ascending index order; NaN ranks before everything else, +inf included,
+    as in torch.sort(descending=True)."""
+    x = np.asarray(x)
+    nan = np.isnan(x)
+    if not nan.any():
+        return np.argsort(-x, axis=axis, kind="stable")
+    xm, nm = np.moveaxis(x, axis, -1), np.moveaxis(nan, axis, -1)
+    out = np.empty(xm.shape, np.int64)
+    for i in np.ndindex(xm.shape[:-1]):
+        out[i] = np.lexsort((np.where(nm[i], 0, -xm[i]), ~nm[i]))     # primary key: NaN first; then value descending
+    return np.moveaxis(out, -1, axis)
 
 
 # --------------------------------------------------------------------------- Y4-Y6

@@ -52,3 +52,18 @@ def assert_masks_close(actual, expected, frac=1e-3, what=""):
 @pytest.fixture(scope="session")
 def golden():
     return load_golden
+
+
+def check_pasted(pasted, g, prefix, sub_step, tol=1e-5, what="paste"):
+    """Compare a full pasted-mask tensor [m,1,H,W] (numpy) with a golden that stores a sub-sampled copy, per-mask float64
+    sums, the exact zero pattern (row / column occupancy + non-zero counts)."""
+    sy, sx = sub_step
+    key = lambda k: g[(prefix + k) if prefix else k]
+    assert_close_f32(pasted[:, :, ::sy, ::sx], key("sub"), tol, what + " sub-sample")
+    nz = pasted != 0
+    assert np.array_equal(nz.sum(axis=(1, 2, 3)), key("nonzero")), what + ": non-zero counts"
+    assert np.array_equal(np.packbits(nz.any(axis=3)), key("rows")), what + ": occupied rows"
+    assert np.array_equal(np.packbits(nz.any(axis=2)), key("cols")), what + ": occupied columns"
+    sums = pasted.astype(np.float64).sum(axis=(1, 2, 3))
+    ref = key("sum" if prefix else "sums")
+    assert np.all(np.abs(sums - ref) <= 1e-5 * np.maximum(np.abs(ref), 1.0)), what + ": per-mask sums"

@@ -108,3 +108,23 @@ def test_masks_class_against_the_wrapper_formula():
         got = O.masks_class(masks, cls, arg)
         assert got.shape == (h, w) and np.array_equal(got, literal)
         assert got.max() <= cls.max() + 1 and (got[~masks.any(axis=2)] == 0).all()
+
+
+def test_nan_inf_cases():
+    """NaN / +-inf boxes and scores, oracle against the reference's own Fast NMS (a NaN IoU
+    suppresses: torch.min / max / clamp / max(dim) propagate NaN) and torchvision-backed nms / batched_nms (std::max /
+    std::min, `ovr > thr`: a NaN IoU does not suppress)."""
+    from oracle import maskrcnn_np as M
+    g = load_golden("nan_inf_cases")
+    assert np.array_equal(O.jaccard(g["f_box"][:12], g["f_box"][:36]), g["f_iou"], equal_nan=True)
+    for tag in ("a", "b"):
+        thr, top_k, max_det = g[f"f{tag}_params"]
+        b, s, c, k = O.fast_non_max_suppression(g["f_box"], g["f_scores"], g["f_coef"], float(thr), int(top_k), int(max_det))
+        assert np.array_equal(s, g[f"f{tag}_score"], equal_nan=True) and np.array_equal(c, g[f"f{tag}_cls"])
+        assert np.array_equal(b, g[f"f{tag}_box"], equal_nan=True) and np.array_equal(k, g[f"f{tag}_coef"])
+    assert np.array_equal(M.nms(g["n_boxes"], g["n_scores"], 0.5), g["n_keep"])
+    assert np.array_equal(M.batched_nms(g["n_boxes"], g["n_scores"], g["n_idxs"], 0.5), g["n_keep_b"])
+    assert np.array_equal(M.nms(g["n2_boxes"], g["n_scores"], 0.5), g["n2_keep"])
+    assert np.array_equal(M.batched_nms(g["n2_boxes"], g["n_scores"], g["n_idxs"], 0.5), g["n2_keep_b"])
+    assert np.array_equal(M.nms(g["n3_boxes"], g["n3_scores"], 0.5), g["n3_keep"])
+    assert np.array_equal(M.batched_nms(g["n3_boxes"], g["n3_scores"], g["n_idxs"], 0.5), g["n3_keep_b"])

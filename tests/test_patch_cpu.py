@@ -70,3 +70,78 @@ def test_swap_transform_routes_inference_only(monkeypatch):
     assert model.transform.forward(["img"], targets=[{}])[0] == "original"
     model.transform.train_mode = True
     assert model.transform.forward(["img"])[0] == "original"
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree only exists in the build container")
+def test_method_dropins_bind_with_reference_signatures():
+    """the fused Mask R-CNN stages must be reachable from an UNEDITED reference model.  Build the
+    reference's own RegionProposalNetwork / RoIHeads / BoxCoder / GeneralizedRCNNTransform objects, install the patch and
+    check that the bound methods are ours and carry the reference methods' exact parameter lists."""
+    import inspect
+    sys.dont_write_bytecode = True
+    if REF not in sys.path:
+        sys.path.insert(0, REF)
+    import isb.patch
+    from isb import maskrcnn
+    from inst_model.Mask_RCNN.net.network_files import det_utils, roi_head, rpn_function, transform
+    isb.patch.uninstall()
+    ref_sigs = {
+        "decode_single": inspect.signature(det_utils.BoxCoder.decode_single),
+        "filter_proposals": inspect.signature(rpn_function.RegionProposalNetwork.filter_proposals),
+        "postprocess_detections": inspect.signature(roi_head.RoIHeads.postprocess_detections),
+        "postprocess": inspect.signature(transform.GeneralizedRCNNTransform.postprocess),
+    }
+    # instances built BEFORE install() must be patched too (the methods are set on the classes)
+    rpn = rpn_function.RegionProposalNetwork(anchor_generator=None, head=None, fg_iou_thresh=0.7, bg_iou_thresh=0.3,
+                                             batch_size_per_image=256, positive_fraction=0.5,
+                                             pre_nms_top_n=dict(training=2000, testing=1000),
+                                             post_nms_top_n=dict(training=2000, testing=1000), nms_thresh=0.7)
+    heads = roi_head.RoIHeads(None, None, None, 0.5, 0.5, 512, 0.25, None, 0.05, 0.5, 100)
+    coder = det_utils.BoxCoder((10.0, 10.0, 5.0, 5.0))
+    tfm = transform.GeneralizedRCNNTransform(800, 1333, [0.485, 0.456, 0.406], [0.229, 0.224, 0.225])
+    try:
+        done = {a for _, a in isb.patch.install()}
+        assert {"BoxCoder.decode_single", "RegionProposalNetwork.filter_proposals", "RoIHeads.postprocess_detections",
+                "GeneralizedRCNNTransform.postprocess"} <= done
+        pairs = [(coder.decode_single, maskrcnn.boxcoder_decode_single, "decode_single"),
+                 (rpn.filter_proposals, maskrcnn.rpn_filter_proposals, "filter_proposals"),
+                 (heads.postprocess_detections, maskrcnn.roiheads_postprocess_detections, "postprocess_detections"),
+                 (tfm.postprocess, maskrcnn.transform_postprocess, "postprocess")]
+        for bound, ours, name in pairs:
+            assert bound.__func__ is ours, name
+            assert inspect.signature(ours) == ref_sigs[name], (name, inspect.signature(ours), ref_sigs[name])
+        # the drop-ins read exactly these attributes of the reference objects
+        assert rpn.pre_nms_top_n() == 1000 and rpn.post_nms_top_n() == 1000 and rpn.nms_thresh == 0.7
+        assert rpn.score_thresh == 0.0 and rpn.min_size == 1.0
+        assert heads.box_coder.weights == (10.0, 10.0, 5.0, 5.0) and heads.detection_per_img == 100
+        assert heads.score_thresh == 0.05 and heads.nms_thresh == 0.5 and heads.box_coder.bbox_xform_clip > 4.13
+        # no CPU fallback: CPU tensors raise instead of silently running the reference
+        import torch
+        with pytest.raises(RuntimeError):
+            coder.decode_single(torch.zeros(2, 4), torch.zeros(2, 4))
+    finally:
+        isb.patch.uninstall()
+    assert rpn_function.RegionProposalNetwork.filter_proposals.__module__.endswith("rpn_function")
+    assert det_utils.BoxCoder.decode_single.__module__.endswith("det_utils")
+
+
+def test_integration_md_structs_match_the_binding():
+    """INTEGRATION.md shows the ctypes structs a maintainer would copy: they must have the layout of isb/_lib.py (and so of
+    include/isb.h) -- a stale struct makes the library read past the caller's memory."""
+    import ctypes as C
+    import re
+    from isb import _lib
+    text = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "INTEGRATION.md")).read()
+    blocks = re.findall(r"class (\w+)\(C\.Structure\):\n\s+_fields_ = \[(.*?)\][ \t]*(?:#[^\n]*)?\n", text, flags=re.S)
+    seen = {}
+    for name, body in blocks:
+        body = re.sub(r"#.*", "", body)
+        fields = re.findall(r'\("(\w+)",\s*C\.(\w+)\)', body)
+        doc = type(name, (C.Structure,), {"_fields_": [(f, getattr(C, t)) for f, t in fields]})
+        seen[name] = doc
+        ours = getattr(_lib, name)
+        assert C.sizeof(doc) == C.sizeof(ours), (name, C.sizeof(doc), C.sizeof(ours))
+        assert [f for f, _ in doc._fields_] == [f for f, _ in ours._fields_], name
+        for f, _ in doc._fields_:
+            assert getattr(doc, f).offset == getattr(ours, f).offset, (name, f)
+    assert {"Limits", "YolactIn", "YolactOut"} <= set(seen)
