@@ -117,6 +117,20 @@ ISB_API int isb_yolact_detect(isb_handle* h, const isb_yolact_in* in, const isb_
  * reports as `e2e`.  Returns ISB_ERR_OVERFLOW if any counts[b] is -1. */
 ISB_API int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, const isb_yolact_out* out, isb_stream stream);
 
+/* How isb_yolact_detect_host delivers bool [H,W,m] to the host.  97 % of those bytes are zeros and one byte per bit is
+ * the reference's format (utils_bbox.py:241), so the call is bound by the device-to-host link; the device therefore ALSO
+ * writes every image's masks one bit per element, and two consumers drain the batch concurrently: the copy engine moves
+ * images densely (as before), and `threads` host worker threads take other images as packed bits (an eighth of the PCIe
+ * bytes) and expand them into the caller's buffer with non-temporal stores.  Which image goes which way is decided at
+ * run time by whichever consumer is free, so the split follows the box (link rate, cores, memory bandwidth).  The
+ * caller's contract does not change: every byte of out->masks[b][0 .. H*W*m_b) is written, identical to the device path.
+ *   threads < 0: default = CPUs of this process / LOCAL_WORLD_SIZE - 1 (ISB_HOST_THREADS overrides);  0: copy engine only. */
+ISB_API int isb_set_host_threads(isb_handle* h, int32_t threads);
+
+/* Counters of the last *_host call: stats[0] images delivered by the copy engine, [1] images expanded by host threads,
+ * [2] device-to-host bytes copied, [3] host-to-device bytes copied, [4] worker threads used, [5..7] reserved (0). */
+ISB_API int isb_host_stats(const isb_handle* h, int64_t stats[8]);
+
 /* ------------------------------------------------------------------------------------
  * Detect + per-pixel CLASS MAP, for callers that draw / score a class image and never look at
  * the per-instance masks.  Replaces decode_nms (utils_bbox.py:170-243) TOGETHER WITH the

@@ -16,7 +16,7 @@ ISB_OK, ISB_ERR_BAD_ARG, ISB_ERR_CUDA, ISB_ERR_LIMIT, ISB_ERR_OVERFLOW = 0, -1, 
 SYMBOLS = (
     "isb_version", "isb_create", "isb_destroy", "isb_last_error", "isb_workspace_bytes", "isb_launch_count",
     "isb_profile_begin", "isb_profile_read",
-    "isb_yolact_detect", "isb_yolact_detect_host", "isb_yolact_class_map", "isb_yolact_class_map_host", "isb_rle_encode", "isb_rle_to_string", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
+    "isb_yolact_detect", "isb_yolact_detect_host", "isb_set_host_threads", "isb_host_stats", "isb_yolact_class_map", "isb_yolact_class_map_host", "isb_rle_encode", "isb_rle_to_string", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
     "isb_traditional_nms", "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_assemble",
     "isb_box_decode", "isb_nms", "isb_batched_nms", "isb_ms_roi_align", "isb_mask_select_sigmoid", "isb_resize_boxes",
     "isb_paste_masks", "isb_paste_class_map", "isb_rpn_filter", "isb_box_postprocess", "isb_preprocess",
@@ -90,6 +90,8 @@ def load():
         lib.isb_profile_read.argtypes = [vp, C.POINTER(C.c_double * 4), C.POINTER(i32)]
         lib.isb_yolact_detect.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactOut), vp]
         lib.isb_yolact_detect_host.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactOut), vp]
+        lib.isb_set_host_threads.argtypes = [vp, i32]
+        lib.isb_host_stats.argtypes = [vp, C.POINTER(i64 * 8)]
         lib.isb_yolact_class_map.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactMapOut), vp]
         lib.isb_yolact_class_map_host.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactMapOut), vp]
         lib.isb_rle_encode.argtypes = [vp, vp, i64, vp, i32, i32, i32, i32, i32, vp, i64, vp, vp, vp, vp]
@@ -169,6 +171,16 @@ class Handle:
         n = C.c_int32()
         self.check(self.lib.isb_profile_read(self.ptr, C.byref(ms), C.byref(n)))
         return [ms[0], ms[1], ms[2], ms[3]], int(n.value)
+
+    def set_host_threads(self, threads):
+        """Worker threads of the *_host entry points (-1 default, 0 = copy engine only); see include/isb.h."""
+        self.check(self.lib.isb_set_host_threads(self.ptr, int(threads)))
+
+    def host_stats(self):
+        st = (C.c_int64 * 8)()
+        self.check(self.lib.isb_host_stats(self.ptr, C.byref(st)))
+        return dict(images_copy_engine=int(st[0]), images_host_threads=int(st[1]), d2h_bytes=int(st[2]), h2d_bytes=int(st[3]),
+                    host_threads=int(st[4]))
 
     def close(self):
         if getattr(self, "_h", None) is not None:

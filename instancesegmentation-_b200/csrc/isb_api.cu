@@ -1,7 +1,11 @@
 // C-ABI entry points of libisb.so (see include/isb.h): argument validation, workspace
 // management and kernel sequencing.  No torch, no exceptions, plain pointers and sizes.
+#include <deque>
 #include <new>
+#include <thread>
+#include <vector>
 
+#include "host_expand.h"
 #include "isb_common.cuh"
 
 namespace isb {
@@ -72,8 +76,11 @@ extern "C" int isb_profile_read(isb_handle* h, double stage_ms[4], int32_t* call
   return ISB_OK;
 }
 
+static void destroy_host_pipe(isb_handle* h);
+
 static void free_ws(isb_handle* h) {
   free_profile(h);
+  destroy_host_pipe(h);
   for (int l = 0; l < 3; ++l) {
     if (h->lane_stream[l]) cudaStreamDestroy(h->lane_stream[l]);
     if (h->lane_event[l]) cudaEventDestroy(h->lane_event[l]);
@@ -121,6 +128,7 @@ extern "C" int isb_create(int device, const isb_limits* limits, isb_handle** out
   memset(h, 0, sizeof(*h));
   *out = h;  // returned even on failure so that isb_last_error() can be read; caller destroys it
   h->device = device;
+  h->host_threads = -1;
   isb_limits L;
   memset(&L, 0, sizeof(L));
   if (limits) L = *limits;
@@ -181,6 +189,8 @@ struct YolactOutAll {
   int32_t* counts;
   uint8_t* class_map;
   int map_only;
+  uint8_t* packed;            // host pipeline only: bit-packed copy of the masks (device), or nullptr
+  int64_t packed_slot_bytes;
 };
 
 static YolactOutAll widen(const isb_yolact_out* o) {
@@ -281,6 +291,7 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const Yo
   mp.counts = out->counts;
   mp.m_fixed = -1;
   mp.det_stride = h->lim.max_det;
+  mp.m_cap = in->max_det;
   mp.proto_h = in->proto_h;
   mp.proto_w = in->proto_w;
   mp.out_h = in->out_h;
@@ -292,6 +303,8 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const Yo
   mp.class_ids = out->class_ids;
   mp.class_stride = in->max_det;  // fnms_emit wrote the caller's [B, in->max_det] array
   mp.map_only = out->map_only;
+  mp.packed = out->packed;
+  mp.packed_slot_bytes = out->packed_slot_bytes;
   h->prof_mid = ev ? ev[3] : nullptr;  // recorded between the sigmoid-map and the compose kernel
   rc = launch_masks(h, mp, s);
   h->prof_mid = nullptr;
@@ -339,6 +352,96 @@ extern "C" int isb_yolact_class_map_host(isb_handle* h, const isb_yolact_in* in,
   return yolact_host(h, in, &all, stream);
 }
 
+// Host delivery state of the *_host entry points (created on first use, owned by the handle).
+struct HostPipe {
+  static constexpr int kDenseSlots = 2;   // dense copies in flight on the copy engine
+  static constexpr int kPackedSlots = 4;  // images being copied as bits / expanded by the worker pool
+  isb::HostPool* pool = nullptr;
+  int pool_threads = 0;
+  uint8_t* land = nullptr;  // pinned landing buffer of the packed bits
+  size_t land_bytes = 0;
+  cudaStream_t dense_stream = nullptr, packed_stream = nullptr;
+  std::vector<cudaEvent_t> chunk_events;
+  cudaEvent_t dense_ev[kDenseSlots] = {};
+  int dense_img[kDenseSlots];
+  struct PackedSlot {
+    cudaEvent_t ev = nullptr;
+    int img = -1;
+    int state = 0;  // 0 free, 1 bits on their way to the landing buffer, 2 being expanded
+    isb::ExpandJob job;
+  } packed[kPackedSlots];
+};
+
+static void destroy_host_pipe(isb_handle* h) {
+  HostPipe* hp = static_cast<HostPipe*>(h->host_pipe);
+  if (!hp) return;
+  if (hp->pool) isb::host_pool_destroy(hp->pool);
+  if (hp->land) cudaFreeHost(hp->land);
+  if (hp->dense_stream) cudaStreamDestroy(hp->dense_stream);
+  if (hp->packed_stream) cudaStreamDestroy(hp->packed_stream);
+  for (cudaEvent_t e : hp->chunk_events) cudaEventDestroy(e);
+  for (int i = 0; i < HostPipe::kDenseSlots; ++i)
+    if (hp->dense_ev[i]) cudaEventDestroy(hp->dense_ev[i]);
+  for (int i = 0; i < HostPipe::kPackedSlots; ++i)
+    if (hp->packed[i].ev) cudaEventDestroy(hp->packed[i].ev);
+  delete hp;
+  h->host_pipe = nullptr;
+}
+
+extern "C" int isb_set_host_threads(isb_handle* h, int32_t threads) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (threads > 256) ISB_FAIL(h, ISB_ERR_BAD_ARG, "set_host_threads: at most 256 threads");
+  h->host_threads = threads < 0 ? -1 : threads;
+  return ISB_OK;
+}
+
+extern "C" int isb_host_stats(const isb_handle* h, int64_t stats[8]) {
+  if (!h || !stats) return ISB_ERR_BAD_ARG;
+  memcpy(stats, h->host_stats, sizeof(h->host_stats));
+  return ISB_OK;
+}
+
+static int get_host_pipe(isb_handle* h, int nchunks, size_t land_bytes, HostPipe** out) {
+  HostPipe* hp = static_cast<HostPipe*>(h->host_pipe);
+  if (!hp) {
+    hp = new (std::nothrow) HostPipe();
+    if (!hp) ISB_FAIL(h, ISB_ERR_CUDA, "host pipeline: out of host memory");
+    h->host_pipe = hp;
+    ISB_CUDA(h, cudaStreamCreateWithFlags(&hp->dense_stream, cudaStreamNonBlocking));
+    ISB_CUDA(h, cudaStreamCreateWithFlags(&hp->packed_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < HostPipe::kDenseSlots; ++i) ISB_CUDA(h, cudaEventCreateWithFlags(&hp->dense_ev[i], cudaEventDisableTiming));
+    for (int i = 0; i < HostPipe::kPackedSlots; ++i) ISB_CUDA(h, cudaEventCreateWithFlags(&hp->packed[i].ev, cudaEventDisableTiming));
+  }
+  const int want = h->host_threads < 0 ? isb::host_default_threads() : h->host_threads;
+  if (want != hp->pool_threads) {
+    if (hp->pool) isb::host_pool_destroy(hp->pool);
+    hp->pool = want > 0 ? isb::host_pool_create(want) : nullptr;
+    hp->pool_threads = want;
+  }
+  while ((int)hp->chunk_events.size() < nchunks) {
+    cudaEvent_t e;
+    ISB_CUDA(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    hp->chunk_events.push_back(e);
+  }
+  if (hp->pool && land_bytes > hp->land_bytes) {
+    if (hp->land) cudaFreeHost(hp->land);
+    hp->land = nullptr;
+    hp->land_bytes = 0;
+    ISB_CUDA(h, cudaHostAlloc((void**)&hp->land, land_bytes, cudaHostAllocDefault));
+    hp->land_bytes = land_bytes;
+  }
+  *out = hp;
+  return ISB_OK;
+}
+
+// cudaEventQuery as a tri-state: 1 done, 0 not yet, < 0 error (message set)
+static int event_done(isb_handle* h, cudaEvent_t e) {
+  const cudaError_t r = cudaEventQuery(e);
+  if (r == cudaSuccess) return 1;
+  if (r == cudaErrorNotReady) return 0;
+  ISB_FAIL(h, ISB_ERR_CUDA, "cudaEventQuery: %s", cudaGetErrorString(r));
+}
+
 static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAll* out, isb_stream stream) {
   int rc;
   const bool map_only = out->map_only != 0;
@@ -346,12 +449,23 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
   cudaStream_t s = (cudaStream_t)stream;
   const size_t B = in->batch, A = in->num_anchors, C = in->num_classes, K = ISB_NUM_COEF;
   const size_t HW = (size_t)in->out_h * in->out_w, D = in->max_det;
+  // Sub-batch pipeline over kLanes streams: while chunk c computes and its results travel to the host, chunk c+1 is
+  // already uploading (PCIe is full duplex) -- H2D, kernels and D2H of different chunks overlap.
+  constexpr int kLanes = 3;
+  const int chunk = (int)(B >= 24 ? 8 : (B + kLanes - 1) / kLanes);
+  const int nchunks = (int)((B + chunk - 1) / chunk);
+  // packed transport: one slot per image, 64-byte multiple, 16 bytes of slack for the expansion's look-ahead word
+  const size_t pslot = map_only ? 0 : ((4 * ((HW * D + 31) / 32) + 16 + 63) & ~(size_t)63);
+  HostPipe* hp = nullptr;
+  if ((rc = get_host_pipe(h, nchunks, B * pslot, &hp)) != ISB_OK) return rc;
+  const bool use_pool = !map_only && hp->pool != nullptr;
   const size_t n_box = B * A * 4 * 4, n_conf = B * A * C * 4, n_coef = B * A * K * 4,
                n_proto = B * (size_t)in->proto_h * in->proto_w * K * 4, n_anc = A * 4 * 4;
   const size_t o_box = B * D * 16, o_score = B * D * 4, o_cls = B * D * 8, o_arg = map_only ? 0 : B * HW * 8,
-               o_mask = map_only ? 0 : B * (size_t)out->mask_slot_bytes, o_cnt = B * 4, o_map = map_only ? B * HW : 0;
+               o_mask = map_only ? 0 : B * (size_t)out->mask_slot_bytes, o_cnt = B * 4, o_map = map_only ? B * HW : 0,
+               o_pack = use_pool ? B * pslot : 0;
   const size_t need = up256(n_box) + up256(n_conf) + up256(n_coef) + up256(n_proto) + up256(n_anc) + up256(o_box) +
-                      up256(o_score) + up256(o_cls) + up256(o_arg) + up256(o_mask) + up256(o_cnt) + up256(o_map);
+                      up256(o_score) + up256(o_cls) + up256(o_arg) + up256(o_mask) + up256(o_cnt) + up256(o_map) + up256(o_pack);
   if (need > h->stage_bytes) {
     ISB_CUDA(h, cudaStreamSynchronize(s));
     cudaFree(h->stage);
@@ -376,35 +490,25 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
   dout.masks = (uint8_t*)take(o_mask);
   dout.counts = (int32_t*)take(o_cnt);
   dout.class_map = map_only ? (uint8_t*)take(o_map) : nullptr;
-  // Sub-batch pipeline over kLanes streams: while chunk c computes and streams its masks to the host, chunk
-  // c+1 is already uploading (PCIe is full duplex) -- H2D, kernels and D2H of different chunks overlap.
-  constexpr int kLanes = 3;
+  dout.packed = use_pool ? (uint8_t*)take(o_pack) : nullptr;
+  dout.packed_slot_bytes = (int64_t)pslot;
   for (int l = 0; l < kLanes; ++l) {
     if (!h->lane_stream[l]) ISB_CUDA(h, cudaStreamCreateWithFlags(&h->lane_stream[l], cudaStreamNonBlocking));
     if (!h->lane_event[l]) ISB_CUDA(h, cudaEventCreateWithFlags(&h->lane_event[l], cudaEventDisableTiming));
   }
   if (!h->fork_event) ISB_CUDA(h, cudaEventCreateWithFlags(&h->fork_event, cudaEventDisableTiming));
+  int64_t d2h_bytes = 0, h2d_bytes = 0, n_dense = 0, n_pool = 0;
   ISB_CUDA(h, cudaMemcpyAsync((void*)din.anchors, in->anchors, n_anc, cudaMemcpyHostToDevice, s));
+  h2d_bytes += (int64_t)n_anc;
   ISB_CUDA(h, cudaEventRecord(h->fork_event, s));
   for (int l = 0; l < kLanes; ++l) ISB_CUDA(h, cudaStreamWaitEvent(h->lane_stream[l], h->fork_event, 0));
-  const int chunk = (int)(B >= 24 ? 8 : (B + kLanes - 1) / kLanes);
-  const int nchunks = (int)((B + chunk - 1) / chunk);
+  ISB_CUDA(h, cudaStreamWaitEvent(hp->dense_stream, h->fork_event, 0));
+  ISB_CUDA(h, cudaStreamWaitEvent(hp->packed_stream, h->fork_event, 0));
   const size_t slot = (size_t)out->mask_slot_bytes, PP = (size_t)in->proto_h * in->proto_w * K;
-  bool overflow = false;
-  auto finalize = [&](int c) -> int {  // chunk c's counts are on the host: size and enqueue its mask copies
-    const int lane = c % kLanes;
-    ISB_CUDA(h, cudaEventSynchronize(h->lane_event[lane]));
-    const size_t b0 = (size_t)c * chunk, b1 = b0 + chunk < B ? b0 + chunk : B;
-    for (size_t b = b0; b < b1; ++b) {
-      const int m = out->counts[b];
-      if (m < 0) { overflow = true; continue; }
-      if (m == 0 || map_only) continue;
-      ISB_CUDA(h, cudaMemcpyAsync(out->masks + b * slot, dout.masks + b * slot, HW * (size_t)m, cudaMemcpyDeviceToHost,
-                                  h->lane_stream[lane]));
-    }
-    return ISB_OK;
-  };
+  // ---- 1. enqueue every chunk: inputs up, kernels, counts + per-detection records + arg-max (or class map) down ---------
   rc = ISB_OK;
+  h->ws_images = (int32_t)B;  // the per-image workspace is addressed by absolute image index (ws_b0)
+  int issued = 0;
   for (int c = 0; c < nchunks && rc == ISB_OK; ++c) {
     const int lane = c % kLanes;
     cudaStream_t st = h->lane_stream[lane];
@@ -413,6 +517,7 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
     ISB_CUDA(h, cudaMemcpyAsync((char*)din.conf + b0 * A * C * 4, (const char*)in->conf + b0 * A * C * 4, nb * A * C * 4, cudaMemcpyHostToDevice, st));
     ISB_CUDA(h, cudaMemcpyAsync((char*)din.coef + b0 * A * K * 4, (const char*)in->coef + b0 * A * K * 4, nb * A * K * 4, cudaMemcpyHostToDevice, st));
     ISB_CUDA(h, cudaMemcpyAsync((char*)din.proto + b0 * PP * 4, (const char*)in->proto + b0 * PP * 4, nb * PP * 4, cudaMemcpyHostToDevice, st));
+    h2d_bytes += (int64_t)(nb * (A * 16 + A * C * 4 + A * K * 4 + PP * 4));
     isb_yolact_in cin = din;
     YolactOutAll cout = dout;
     cin.batch = (int32_t)nb;
@@ -427,6 +532,7 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
     cout.masks = map_only ? nullptr : dout.masks + b0 * slot;
     cout.counts = dout.counts + b0;
     cout.class_map = map_only ? dout.class_map + b0 * HW : nullptr;
+    cout.packed = use_pool ? dout.packed + b0 * pslot : nullptr;
     h->ws_b0 = (int32_t)b0;
     h->ws_lane = lane;
     rc = yolact_detect_device(h, &cin, &cout, st);
@@ -434,7 +540,8 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
     h->ws_lane = 0;
     if (rc != ISB_OK) break;
     ISB_CUDA(h, cudaMemcpyAsync(out->counts + b0, cout.counts, nb * 4, cudaMemcpyDeviceToHost, st));
-    ISB_CUDA(h, cudaEventRecord(h->lane_event[lane], st));
+    ISB_CUDA(h, cudaEventRecord(hp->chunk_events[c], st));
+    issued = c + 1;
     ISB_CUDA(h, cudaMemcpyAsync(out->boxes + b0 * D * 4, cout.boxes, nb * D * 16, cudaMemcpyDeviceToHost, st));
     ISB_CUDA(h, cudaMemcpyAsync(out->scores + b0 * D, cout.scores, nb * D * 4, cudaMemcpyDeviceToHost, st));
     ISB_CUDA(h, cudaMemcpyAsync(out->class_ids + b0 * D, cout.class_ids, nb * D * 8, cudaMemcpyDeviceToHost, st));
@@ -442,14 +549,115 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
       ISB_CUDA(h, cudaMemcpyAsync(out->class_map + b0 * HW, cout.class_map, nb * HW, cudaMemcpyDeviceToHost, st));
     else
       ISB_CUDA(h, cudaMemcpyAsync(out->masks_arg + b0 * HW, cout.masks_arg, nb * HW * 8, cudaMemcpyDeviceToHost, st));
-    if (c >= kLanes - 1) rc = finalize(c - (kLanes - 1));
+    d2h_bytes += (int64_t)(nb * (4 + D * 28 + (map_only ? HW : HW * 8)));
   }
-  for (int c = nchunks - (kLanes - 1) > 0 ? nchunks - (kLanes - 1) : 0; c < nchunks && rc == ISB_OK; ++c) rc = finalize(c);
+  h->ws_images = 0;
+  // ---- 2. deliver the masks: two consumers drain the images whose counts have arrived ------------------------------
+  //   copy engine: dense bool [H,W,m] straight into the caller's buffer (newest ready image first);
+  //   host threads: the image's packed bits into the landing buffer, then expanded into the caller's buffer (oldest first).
+  // Whichever has a free slot takes the next image, so the split follows the measured rates of this box.
+  bool overflow = false;
+  if (!map_only && rc == ISB_OK) {
+    std::deque<int> ready;
+    int next_chunk = 0, busy = 0;
+    for (int i = 0; i < HostPipe::kDenseSlots; ++i) hp->dense_img[i] = -1;
+    for (int i = 0; i < HostPipe::kPackedSlots; ++i) { hp->packed[i].state = 0; hp->packed[i].img = -1; }
+    while (rc == ISB_OK && (next_chunk < issued || !ready.empty() || busy > 0)) {
+      bool progress = false;
+      if (next_chunk < issued) {
+        const int d = event_done(h, hp->chunk_events[next_chunk]);
+        if (d < 0) { rc = d; break; }
+        if (d) {
+          const size_t b0 = (size_t)next_chunk * chunk, b1 = b0 + chunk < B ? b0 + chunk : B;
+          for (size_t b = b0; b < b1; ++b) {
+            const int m = out->counts[b];
+            if (m < 0) overflow = true;
+            if (m > 0) ready.push_back((int)b);
+          }
+          ++next_chunk;
+          progress = true;
+        }
+      }
+      for (int i = 0; i < HostPipe::kDenseSlots && rc == ISB_OK; ++i) {
+        if (hp->dense_img[i] >= 0) {
+          const int d = event_done(h, hp->dense_ev[i]);
+          if (d < 0) { rc = d; break; }
+          if (d) { hp->dense_img[i] = -1; --busy; progress = true; }
+        }
+        if (hp->dense_img[i] < 0 && !ready.empty()) {
+          const int b = ready.back();
+          ready.pop_back();
+          const size_t bytes = HW * (size_t)out->counts[b];
+          const cudaError_t e = cudaMemcpyAsync(out->masks + (size_t)b * slot, dout.masks + (size_t)b * slot, bytes,
+                                                cudaMemcpyDeviceToHost, hp->dense_stream);
+          if (e != cudaSuccess || cudaEventRecord(hp->dense_ev[i], hp->dense_stream) != cudaSuccess) {
+            snprintf(h->err, sizeof(h->err), "host delivery (dense copy): %s", cudaGetErrorString(cudaGetLastError()));
+            rc = ISB_ERR_CUDA;
+            break;
+          }
+          hp->dense_img[i] = b;
+          ++busy; ++n_dense;
+          d2h_bytes += (int64_t)bytes;
+          progress = true;
+        }
+      }
+      for (int i = 0; use_pool && i < HostPipe::kPackedSlots && rc == ISB_OK; ++i) {
+        HostPipe::PackedSlot& ps = hp->packed[i];
+        if (ps.state == 1) {
+          const int d = event_done(h, ps.ev);
+          if (d < 0) { rc = d; break; }
+          if (d) {
+            ps.job.src = reinterpret_cast<const uint64_t*>(hp->land + (size_t)ps.img * pslot);
+            ps.job.dst = out->masks + (size_t)ps.img * slot;
+            ps.job.out_bytes = HW * (size_t)out->counts[ps.img];
+            isb::host_pool_submit(hp->pool, &ps.job);
+            ps.state = 2;
+            progress = true;
+          }
+        } else if (ps.state == 2 && ps.job.done()) {
+          ps.state = 0;
+          --busy;
+          progress = true;
+        }
+        if (ps.state == 0 && !ready.empty()) {
+          const int b = ready.front();
+          ready.pop_front();
+          const size_t bytes = 4 * ((HW * (size_t)out->counts[b] + 31) / 32);
+          const cudaError_t e = cudaMemcpyAsync(hp->land + (size_t)b * pslot, dout.packed + (size_t)b * pslot, bytes,
+                                                cudaMemcpyDeviceToHost, hp->packed_stream);
+          if (e != cudaSuccess || cudaEventRecord(ps.ev, hp->packed_stream) != cudaSuccess) {
+            snprintf(h->err, sizeof(h->err), "host delivery (packed copy): %s", cudaGetErrorString(cudaGetLastError()));
+            rc = ISB_ERR_CUDA;
+            break;
+          }
+          ps.img = b;
+          ps.state = 1;
+          ++busy; ++n_pool;
+          d2h_bytes += (int64_t)bytes;
+          progress = true;
+        }
+      }
+      if (!progress) std::this_thread::yield();
+    }
+    // on an error: wait for whatever is still running before the caller's buffers can be released
+    if (rc != ISB_OK) {
+      cudaStreamSynchronize(hp->dense_stream);
+      cudaStreamSynchronize(hp->packed_stream);
+      for (int i = 0; use_pool && i < HostPipe::kPackedSlots; ++i)
+        while (hp->packed[i].state == 2 && !hp->packed[i].job.done()) std::this_thread::yield();
+    }
+  } else if (rc == ISB_OK) {
+    // class map: nothing variable-length to deliver; only the overflow flag needs the counts
+    for (int c = 0; c < issued; ++c) ISB_CUDA(h, cudaEventSynchronize(hp->chunk_events[c]));
+    for (size_t b = 0; b < B; ++b) overflow |= out->counts[b] < 0;
+  }
   for (int l = 0; l < kLanes; ++l) {  // join (also on the error path, so the lanes are idle when we return)
     cudaEventRecord(h->lane_event[l], h->lane_stream[l]);
     cudaStreamWaitEvent(s, h->lane_event[l], 0);
   }
   ISB_CUDA(h, cudaStreamSynchronize(s));
+  h->host_stats[0] = n_dense; h->host_stats[1] = n_pool; h->host_stats[2] = d2h_bytes; h->host_stats[3] = h2d_bytes;
+  h->host_stats[4] = use_pool ? hp->pool_threads : 0;
   if (rc != ISB_OK) return rc;
   if (overflow) ISB_FAIL(h, ISB_ERR_OVERFLOW, "candidate buffer overflow: raise isb_limits.cand_capacity (now %lld)", (long long)h->lim.cand_capacity);
   return ISB_OK;

@@ -329,9 +329,13 @@ struct isb_handle {
   // sub-batch pipelining (isb_yolact_detect_host): image offset into the per-image workspace arrays and
   // the lane whose work counter / stream the next launches use
   int32_t ws_b0, ws_lane;
+  int32_t ws_images;       // images the per-image workspace must hold while a sub-batch pipeline runs (0: the call's batch)
   cudaStream_t lane_stream[3];
   cudaEvent_t lane_event[3];
   cudaEvent_t fork_event;
+  void* host_pipe;         // HostPipe (isb_api.cu): worker pool, pinned landing buffer, copy streams / events of the host delivery
+  int32_t host_threads;    // isb_set_host_threads: -1 = default (host_default_threads()), 0 = copy engine only
+  int64_t host_stats[8];   // last *_host call: images by copy engine, images by host threads, D2H bytes, H2D bytes, ...
   // Mask R-CNN side: NMS workspace, grown on demand (ensure_nms_ws)
   int64_t nms_cap;         // boxes the arrays below hold
   uint64_t* nms_keys;      // [pow2(nms_cap)]
@@ -417,6 +421,8 @@ struct MaskParams {
   const int32_t* counts;     // [B]   device; or nullptr when m_fixed >= 0
   int32_t m_fixed;
   int32_t det_stride;        // rows between images in coef / bounds
+  int32_t m_cap;             // upper bound of the detections per image in THIS call (sizes shared memory and the sigmoid-map
+                             // scratch); 0 = det_stride
   int32_t proto_h, proto_w, out_h, out_w;
   int64_t* masks_arg;        // [B, H, W]
   uint8_t* masks;            // B slots
@@ -426,10 +432,15 @@ struct MaskParams {
   const int64_t* class_ids;  // [B, class_stride], needed with class_map
   int32_t class_stride;      // rows between images in class_ids (the CALLER's array: in->max_det, not the workspace stride)
   int32_t map_only;          // 1: masks / masks_arg are not produced at all
+  // optional bit-packed copy of the masks (transport format of the *_host path): slot b holds the image's H*W*m_b
+  // mask bits, bit i = element i of the dense [H,W,m_b] stream, in little-endian 32-bit words
+  uint8_t* packed;           // B slots of packed_slot_bytes, or nullptr
+  int64_t packed_slot_bytes; // >= 4 * ceil(H*W*max_det / 32), multiple of 16
+  int32_t skip_dense;        // 1 with `packed`: the dense masks are not written (masks may be nullptr); masks_arg still is
 };
 int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s);
-// grows the sigmoid-map scratch for the handle's limits; returns floats per image in *s_cap
-int ensure_mask_scratch(isb_handle* h, int proto_h, int proto_w, int64_t* s_cap);
+// grows the sigmoid-map scratch for `images` images of at most m_cap detections; returns floats per image in *s_cap
+int ensure_mask_scratch(isb_handle* h, int proto_h, int proto_w, int m_cap, int64_t images, int64_t* s_cap);
 
 struct RoiLevels {
   const float* feat[8];

@@ -528,6 +528,170 @@ __global__ void __launch_bounds__(kRoiThreads, 4) ms_roi_align_kernel(RoiLevels 
 }
 
 // ------------------------------------------------------------------------------------------
+// MultiScaleRoIAlign, register / shuffle formulation (the common case: out * sampling_ratio <= 32 per axis, i.e. the
+// reference's 7 x 7 and 14 x 14 poolers with sampling_ratio 2).
+//
+// The staged kernel above spends its time in the shared-memory pipe (22 M wavefronts per 1000 RoIs: 4-byte cp.async
+// writes of the gather, tap and table reads) behind CTA barriers.  Here nothing is staged.  roi_align is separable:
+//     bin(ph, pw) = 1/count * sum_{iy, ix} (hy*v[ylo] + ly*v[yhi]) (x-interpolated)
+// so a warp takes one channel at a time with LANE = DISTINCT FEATURE COLUMN the RoI touches (at most 2 * out * sr
+// of them, in one or two registers per lane): for an output row ph it loads the 2 * sr feature rows its samples need
+// straight from global memory (one coalesced <= 128-byte load per row and lane register; rows shared by neighbouring
+// samples hit L1), blends them with the y weights into one register T per lane, and then the lanes switch roles --
+// lane = x sample (pw, ix) -- and fetch their two taps of T with two shuffles, weight them, add the sr samples of a bin
+// with shuffles, and store the bin.  Per (RoI, channel) that is ~2 * out * sr loads and ~20 instructions per output
+// row, no shared-memory traffic beyond one broadcast 16-byte read per sample row, and no barrier after the prologue.
+// Arithmetic: y blend first, then x, with fused multiply-adds -- a different association than torchvision's
+// w1*v1 + w2*v2 + w3*v3 + w4*v4 (well inside the 1e-5 bar; RoIAlign is not an index-producing stage).
+// ------------------------------------------------------------------------------------------
+constexpr int kRoiRowThreads = 256;
+constexpr int kRoiRowWarps = kRoiRowThreads / 32;
+
+struct RowSample { int lo, hi; float h, l; };  // feature-row OFFSETS (row * fw) of a y sample's two taps and their weights
+
+template <int SR>
+__global__ void __launch_bounds__(kRoiRowThreads) ms_roi_align_rows_kernel(RoiLevels L, const float4* __restrict__ boxes,
+                                                                        const int32_t* __restrict__ batch_idx, int channels,
+                                                                        int oh, int ow, int sr_rt, int cpc,
+                                                                        float* __restrict__ out) {
+  const int sr = SR > 0 ? SR : sr_rt;
+  __shared__ RowSample s_y[32];
+  __shared__ int s_xlist[64];          // distinct feature columns, ascending
+  __shared__ int s_xpos[32];           // per x sample: position of its lo tap | hi tap << 8 in s_xlist
+  __shared__ float s_xl[32];           // per x sample: weight of the hi tap (lx); < 0 marks a sample outside the map
+  __shared__ int s_nx;
+  const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const float4 b = boxes[r];
+  int lvl = 0;
+  if (L.num_levels > 1) {  // LevelMapper (poolers.py:73-84), every thread: a handful of instructions
+    const float s = sqrtf((b.z - b.x) * (b.w - b.y));
+    float t = floorf(L.canonical_level + log2f(s / L.canonical_scale) + L.eps);
+    t = fminf(fmaxf(t, (float)L.k_min), (float)L.k_max);
+    lvl = (int)(long long)t - L.k_min;
+  }
+  const int fh = L.h[lvl], fw = L.w[lvl];
+  const float ss = L.scale[lvl];
+  const float start_w = b.x * ss, start_h = b.y * ss, end_w = b.z * ss, end_h = b.w * ss;
+  const float roi_w = fmaxf(end_w - start_w, 1.0f), roi_h = fmaxf(end_h - start_h, 1.0f);
+  const float bin_h = roi_h / (float)oh, bin_w = roi_w / (float)ow;
+  const int ny = oh * sr, nx = ow * sr;
+  if (warp == 0 && lane < ny) {
+    const int ph = lane / sr, iy = lane - ph * sr;
+    const AxisSample a = axis_sample(start_h + (float)ph * bin_h + (((float)iy + 0.5f) * bin_h) / (float)sr, fh);
+    RowSample rs;
+    rs.lo = a.bad ? 0 : a.lo * fw;
+    rs.hi = a.bad ? 0 : a.hi * fw;
+    rs.h = a.bad ? 0.0f : a.h;
+    rs.l = a.bad ? 0.0f : a.l;
+    s_y[lane] = rs;
+  }
+  if (warp == 1) {
+    // x samples are monotone along the axis and a sample's hi tap is its lo tap or the next column, so a tap is new
+    // iff it exceeds the previous valid sample's hi tap: positions in the distinct list come from one warp prefix sum
+    AxisSample a;
+    a.bad = 1; a.lo = a.hi = 0; a.l = a.h = 0.0f;
+    if (lane < nx) {
+      const int pw = lane / sr, ix = lane - pw * sr;
+      a = axis_sample(start_w + (float)pw * bin_w + (((float)ix + 0.5f) * bin_w) / (float)sr, fw);
+    }
+    const bool ok = !a.bad;
+    const unsigned okmask = __ballot_sync(0xffffffffu, ok);
+    const int prev_hi = __shfl_up_sync(0xffffffffu, a.hi, 1);
+    const bool first = ok && !((okmask >> (lane > 0 ? lane - 1 : 0)) & 1u) ? true : (ok && lane == 0);
+    // (valid samples are one contiguous run: the ones outside the map sit at the two ends)
+    const bool new_lo = ok && (first || a.lo > prev_hi);
+    const bool new_hi = ok && a.hi > a.lo && (first || a.hi > prev_hi);
+    const int add = (new_lo ? 1 : 0) + (new_hi ? 1 : 0);
+    int incl = add;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += u;
+    }
+    const int base = incl - add;
+    int pos_lo = 0, pos_hi = 0;
+    if (ok) {
+      pos_lo = new_lo ? base : (a.lo == prev_hi ? base - 1 : base - 2);
+      pos_hi = a.hi == a.lo ? pos_lo : (new_hi ? base + (new_lo ? 1 : 0) : base - 1);
+      if (new_lo) s_xlist[base] = a.lo;
+      if (new_hi) s_xlist[base + (new_lo ? 1 : 0)] = a.hi;
+    }
+    if (lane < 32) {
+      s_xpos[lane] = pos_lo | (pos_hi << 8);
+      s_xl[lane] = ok ? a.l : -1.0f;
+    }
+    if (lane == 31) s_nx = incl;
+  }
+  __syncthreads();
+  const int nxl = s_nx;
+  // lane as a feature column (two registers cover up to 64 distinct columns)
+  const int col0 = lane < nxl ? s_xlist[lane] : 0;
+  const int col1 = lane + 32 < nxl ? s_xlist[lane + 32] : 0;
+  const bool wide = nxl > 32;
+  // lane as an x sample
+  const int xp = s_xpos[lane];
+  const int plo = xp & 0xff, phi = (xp >> 8) & 0xff;
+  const float xl_raw = s_xl[lane];
+  const float lx = (lane < nx && xl_raw >= 0.0f) ? xl_raw : 0.0f;
+  const float hx = (lane < nx && xl_raw >= 0.0f) ? 1.0f - xl_raw : 0.0f;
+  const int my_pw = lane / sr;
+  const bool bin_lane = lane < nx && lane - my_pw * sr == 0;
+  const float inv_count = 1.0f / (float)(sr * sr);
+  const int bins = oh * ow;
+  const int img = batch_idx ? batch_idx[r] : 0;
+  const size_t fhw = (size_t)fh * fw;
+  const float* fbase = L.feat[lvl] + (size_t)img * channels * fhw;
+  float* obase = out + (size_t)r * channels * bins;
+  const int cbase = blockIdx.y * cpc, cend = min(channels, cbase + cpc);
+  for (int c = cbase + warp; c < cend; c += kRoiRowWarps) {
+    const float* pl = fbase + (size_t)c * fhw;
+    float* oc = obase + (size_t)c * bins;
+#pragma unroll 2
+    for (int ph = 0; ph < oh; ++ph) {
+      float t0 = 0.0f, t1 = 0.0f;
+#pragma unroll
+      for (int iy = 0; iy < (SR > 0 ? SR : 1); ++iy) {
+        const RowSample rs = s_y[ph * sr + iy];
+        const float a = __ldg(pl + rs.lo + col0), bb = __ldg(pl + rs.hi + col0);
+        t0 = fmaf(rs.h, a, t0);
+        t0 = fmaf(rs.l, bb, t0);
+        if (wide) {
+          const float a1 = __ldg(pl + rs.lo + col1), b1 = __ldg(pl + rs.hi + col1);
+          t1 = fmaf(rs.h, a1, t1);
+          t1 = fmaf(rs.l, b1, t1);
+        }
+      }
+      if (SR == 0) {
+        for (int iy = 1; iy < sr; ++iy) {
+          const RowSample rs = s_y[ph * sr + iy];
+          t0 = fmaf(rs.h, __ldg(pl + rs.lo + col0), t0);
+          t0 = fmaf(rs.l, __ldg(pl + rs.hi + col0), t0);
+          if (wide) {
+            t1 = fmaf(rs.h, __ldg(pl + rs.lo + col1), t1);
+            t1 = fmaf(rs.l, __ldg(pl + rs.hi + col1), t1);
+          }
+        }
+      }
+      // roles switch: lane = x sample; its two taps of T come from the lanes that own those columns
+      float vlo = __shfl_sync(0xffffffffu, t0, plo & 31), vhi = __shfl_sync(0xffffffffu, t0, phi & 31);
+      if (wide) {
+        const float wlo = __shfl_sync(0xffffffffu, t1, plo & 31), whi = __shfl_sync(0xffffffffu, t1, phi & 31);
+        if (plo >= 32) vlo = wlo;
+        if (phi >= 32) vhi = whi;
+      }
+      float v = fmaf(hx, vlo, lx * vhi);
+      if (SR == 2) {
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+      } else {
+        const float own = v;
+        for (int k = 1; k < sr; ++k) v += __shfl_down_sync(0xffffffffu, own, k);
+      }
+      if (bin_lane) oc[ph * ow + my_pw] = v * inv_count;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // GeneralizedRCNNTransform for inference, one image (transform.py:436-459): normalize (:264-270, float32
 // (v - mean) / std), resize (:284-315 -> F.interpolate bilinear, align_corners=False, output size given) and the
 // image's slot of batch_images (:352-386: zero canvas, image at the top-left) in one pass: a thread per canvas
@@ -629,6 +793,25 @@ int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, c
     ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
     h->roi_configured = 1;
   }
+  if (oh * sr <= 32 && ow * sr <= 32) {
+    // register / shuffle kernel: a CTA = (RoI, group of channels), a warp walks the group's channels.  Enough CTAs for
+    // ~2 waves of 8 resident CTAs per SM; at least one channel per warp and pass.
+    int groups = (16 * h->num_sms + num_rois - 1) / num_rois;
+    if (groups > (channels + kRoiRowWarps - 1) / kRoiRowWarps) groups = (channels + kRoiRowWarps - 1) / kRoiRowWarps;
+    if (groups < 1) groups = 1;
+    int cpc = (channels + groups - 1) / groups;
+    cpc = (cpc + kRoiRowWarps - 1) / kRoiRowWarps * kRoiRowWarps;
+    groups = (channels + cpc - 1) / cpc;
+    if (sr == 2)
+      ms_roi_align_rows_kernel<2><<<dim3(num_rois, groups), kRoiRowThreads, 0, s>>>(
+          L, reinterpret_cast<const float4*>(boxes), batch_idx, channels, oh, ow, sr, cpc, out);
+    else
+      ms_roi_align_rows_kernel<0><<<dim3(num_rois, groups), kRoiRowThreads, 0, s>>>(
+          L, reinterpret_cast<const float4*>(boxes), batch_idx, channels, oh, ow, sr, cpc, out);
+    ISB_LAUNCH_CHECK(h, "ms_roi_align_rows_kernel");
+    return ISB_OK;
+  }
+  // larger out * sampling_ratio: the staged kernel.
   // shared memory: the tile budget + a (bin, sample) table of exactly this call's size (more entries than the cap: the
   // kernel's direct-gather path, no table)
   const int tile_floats = kRoiTileFloats;

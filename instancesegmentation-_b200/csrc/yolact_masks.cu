@@ -33,6 +33,7 @@ constexpr int kUnitPx = 4096;         // pixels per work unit (128 segments of 3
 constexpr int kYTabRows = 64;         // rows of a unit with tabulated bilinear taps (more: computed directly)
 constexpr int kSmapThreads = 256;
 constexpr int kSmapCtasPerSm = 4;     // persistent CTAs of the sigmoid-map kernel
+constexpr int kSecondCounter = 16;    // work counter of a second compose launch (dense + packed), ints after the first
 
 struct CompGeom {
   int units_per_img;
@@ -59,7 +60,10 @@ constexpr int kSmapMaxBatch = 1024;
 __global__ void __launch_bounds__(kSmapThreads)
 sigmoid_map_kernel(MaskParams p, const DetRec* __restrict__ rec, const int32_t* __restrict__ totals,
                    float* __restrict__ smap, int64_t s_cap, int* __restrict__ compose_counter) {
-  if (blockIdx.x == 0 && threadIdx.x == 0) *compose_counter = 0;  // work counter of the compose kernel that follows
+  if (blockIdx.x == 0 && threadIdx.x == 0) {  // work counters of the compose kernel(s) that follow
+    compose_counter[0] = 0;
+    compose_counter[kSecondCounter] = 0;
+  }
   extern __shared__ __align__(16) unsigned char s_dyn[];  // DetRec s_rec[list_cap]
   __shared__ int s_cstart[kSmapMaxBatch + 1];             // first ticket of every image
   __shared__ int s_scan[32];
@@ -146,12 +150,22 @@ __device__ __forceinline__ void warp_clear(uint8_t* buf, int a, int b, int lane)
   for (int v = a16 + lane * 16; v < b16; v += 32 * 16) *reinterpret_cast<uint4*>(buf + v) = make_uint4(0, 0, 0, 0);
 }
 
-// kMasks = false is the class-map-only variant (yolact.py:162-170 needs nothing else on the host): same walk,
+// kMode = kCompMap is the class-map-only variant (yolact.py:162-170 needs nothing else on the host): same walk,
 // no segment images, no bulk stores, one byte per pixel out.
-template <bool kMasks>
+// kMode = kCompPacked writes the SAME bool [H,W,m] stream one BIT per element instead of one byte (bit i of the image's
+// packed stream = byte i of the dense stream, little-endian within 32-bit words) plus the dense int64 arg-max: the
+// transport format of isb_yolact_detect_host, which expands it into the caller's host buffer on host threads -- an
+// eighth of the bytes cross PCIe.  A 32-pixel segment is exactly m 32-bit words (32 * m bits, word-aligned because
+// segments start at multiples of 32 pixels): lanes OR their bits into the warp's m-word buffer, which then leaves as
+// plain coalesced stores.
+enum { kCompMap = 0, kCompDense = 1, kCompPacked = 2 };
+
+template <int kMode>
 __global__ void __launch_bounds__(kCompThreads, 2)
 mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, const float* __restrict__ smap,
                     int* __restrict__ work_counter) {
+  constexpr bool kMasks = kMode == kCompDense;
+  constexpr bool kPacked = kMode == kCompPacked;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ int s_unit;
   __shared__ int s_wcount[kCompWarps];
@@ -171,7 +185,7 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
   const int HW = H * W;
 
   // ---- once per CTA: clean segment buffers, per-column bilinear taps -----------------------------
-  if (kMasks)
+  if (kMasks)  // (the packed variant clears its m words per segment)
     for (int i = tid; i < nwarps * 2 * g.buf_bytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem_raw)[i] = make_uint4(0, 0, 0, 0);
   for (int x = tid; x < W; x += blockDim.x) {
     int ix0, ix1;
@@ -205,7 +219,8 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
     const int px1 = min(px0 + kUnitPx, HW);
     const int ya = px0 / W, yb = (px1 - 1) / W;  // rows the unit touches
     uint8_t* out_img = kMasks ? p.masks + (size_t)b * p.mask_slot_bytes : nullptr;
-    int64_t* arg_img = kMasks ? p.masks_arg + (size_t)b * HW : nullptr;
+    uint32_t* pk_img = kPacked ? reinterpret_cast<uint32_t*>(p.packed + (size_t)b * p.packed_slot_bytes) : nullptr;
+    int64_t* arg_img = (kMasks || kPacked) ? p.masks_arg + (size_t)b * HW : nullptr;
     uint8_t* cmap_img = p.class_map ? p.class_map + (size_t)b * HW : nullptr;
     const int64_t* cls_img = p.class_ids + (size_t)b * p.class_stride;
     const float* S_img = smap + (size_t)b * g.s_cap;
@@ -266,6 +281,12 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
           __syncwarp();
         }
       }
+      uint32_t* wbits = reinterpret_cast<uint32_t*>(wbuf);  // packed mode: the warp's m words
+      if (kPacked) {
+        __syncwarp();  // every lane has stored the previous segment's words
+        for (int w = lane; w < m; w += 32) wbits[w] = 0u;
+        __syncwarp();
+      }
       const bool active = lane < nt;
       const int y = yq, x = xq;
       const int wy0 = __shfl_sync(0xffffffffu, y, 0), wy1 = __shfl_sync(0xffffffffu, y, nt - 1);
@@ -306,6 +327,10 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
             const float bot = lx0 * __ldg(S + r1 + ix0) + lx1 * __ldg(S + r1 + ix1);
             const float v = ly0 * top + ly1 * bot;
             if (kMasks && v > 0.5f) { mypix[r.j] = 1; anyset = true; }
+            if (kPacked && v > 0.5f) {
+              const int bit = lane * m + r.j;
+              atomicOr(&wbits[bit >> 5], 1u << (bit & 31));
+            }
             if (v > best) { best = v; arg = r.j; }
           }
         }
@@ -336,6 +361,13 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
         if (lane < head) g0[lane] = buf[shift + lane];
         if (lane >= 16 && lane - 16 < tail) g0[head + body + (lane - 16)] = buf[shift + head + body + (lane - 16)];
       }
+      if (kPacked) {
+        if (active && p.skip_dense) arg_img[q0 + lane] = (int64_t)arg;  // (a dense pass before this one wrote it already)
+        __syncwarp();  // all bits of the segment are in shared memory
+        const int nwords = (nt * m + 31) >> 5;  // nt < 32 only in the image's last segment: the tail word is zero-padded
+        uint32_t* gw = pk_img + (size_t)(q0 >> 5) * m;
+        for (int w = lane; w < nwords; w += 32) gw[w] = wbits[w];
+      }
       // this lane's pixel in the warp's next segment
       xq += nwarps * 32;
       while (xq >= W) { xq -= W; ++yq; }
@@ -349,8 +381,9 @@ static constexpr int kCompSmemTwo = 111 * 1024;   // two CTAs per SM
 static constexpr int kCompSmemOne = 200 * 1024;   // one CTA per SM (very large detection counts)
 
 int configure_masks(isb_handle* h) {
-  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
-  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
+  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<kCompDense>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
+  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<kCompMap>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
+  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<kCompPacked>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
   return ISB_OK;
 }
 
@@ -365,9 +398,11 @@ static int ensure_smap(isb_handle* h, size_t floats) {
   return ISB_OK;
 }
 
-int ensure_mask_scratch(isb_handle* h, int proto_h, int proto_w, int64_t* s_cap) {
-  *s_cap = (int64_t)h->lim.max_det * proto_h * proto_w;  // worst case: every box covers the whole image
-  return ensure_smap(h, (size_t)h->lim.max_batch * (size_t)*s_cap);
+int ensure_mask_scratch(isb_handle* h, int proto_h, int proto_w, int m_cap, int64_t images, int64_t* s_cap) {
+  // worst case per image: every box covers the whole prototype map.  Sized by the CALL (its detection bound and image
+  // count), not by the handle's limits: 7.6 MB per image at m = 100, 138 x 138.
+  *s_cap = (int64_t)m_cap * proto_h * proto_w;
+  return ensure_smap(h, (size_t)images * (size_t)*s_cap);
 }
 
 int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
@@ -379,30 +414,14 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   g.units_per_img = (int)((hw + kUnitPx - 1) / kUnitPx);
   g.scale_y = (float)p.proto_h / (float)p.out_h;
   g.scale_x = (float)p.proto_w / (float)p.out_w;
-  g.list_cap = p.m_fixed >= 0 ? (p.m_fixed > 0 ? p.m_fixed : 1) : p.det_stride;
+  g.list_cap = p.m_fixed >= 0 ? (p.m_fixed > 0 ? p.m_fixed : 1) : (p.m_cap > 0 ? p.m_cap : p.det_stride);
   const size_t fixed = (((size_t)p.out_w * sizeof(ColTap) + 31) & ~(size_t)31) + (size_t)g.list_cap * sizeof(DetRec);
   if (p.class_map && !p.class_ids) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask assembly: class_map needs class_ids");
   if (p.map_only && !p.class_map) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask assembly: map_only without class_map");
-  // 32 pixels x m bytes + alignment shift; the class-map-only variant has no segment images
-  const size_t buf = p.map_only ? 0 : ((size_t)32 * g.list_cap + 16 + 15) & ~(size_t)15;
-  // as many warps (each with two segment buffers) as fit: two CTAs per SM if that gives >= 8 warps, else one
-  size_t budget = kCompSmemTwo;
-  int nwarps = kCompWarps;
-  if (!p.map_only) {
-    nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
-    if (nwarps < 8) {
-      budget = kCompSmemOne;
-      nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
-    }
-  } else if (fixed > budget) {
-    budget = kCompSmemOne;
-  }
-  if (nwarps > kCompWarps) nwarps = kCompWarps;
-  if (nwarps < 1 || fixed > budget)
-    ISB_FAIL(h, ISB_ERR_LIMIT, "mask compose: %d detections x width %d exceed shared memory", g.list_cap, p.out_w);
-  g.buf_bytes = (int)buf;
-  const size_t smem = fixed + (size_t)nwarps * 2 * buf;
-  int rc = ensure_mask_scratch(h, p.proto_h, p.proto_w, &g.s_cap);
+  if (p.packed && (p.packed_slot_bytes < 4 * ((hw * g.list_cap + 31) / 32) || (p.packed_slot_bytes & 15)))
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask assembly: packed_slot_bytes must be >= 4*ceil(H*W*max_det/32) and a multiple of 16");
+  const int64_t ws_images = h->ws_images > h->ws_b0 + p.batch ? h->ws_images : h->ws_b0 + p.batch;
+  int rc = ensure_mask_scratch(h, p.proto_h, p.proto_w, g.list_cap, ws_images, &g.s_cap);
   if (rc != ISB_OK) return rc;
   const int64_t total_units = (int64_t)p.batch * g.units_per_img;
   if (total_units == 0) return ISB_OK;
@@ -414,14 +433,46 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
       p, rec, h->smap_total + h->ws_b0, smap, g.s_cap, counters);
   ISB_LAUNCH_CHECK(h, "sigmoid_map_kernel");
   if (h->prof_mid) ISB_CUDA(h, cudaEventRecord(h->prof_mid, s));
-  const int per_sm = budget == (size_t)kCompSmemTwo ? 2 : 1;
-  int64_t grid = (int64_t)h->num_sms * per_sm;
-  if (grid > total_units) grid = total_units;
-  if (p.map_only)
-    mask_compose_kernel<false><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, counters);
-  else
-    mask_compose_kernel<true><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, counters);
-  ISB_LAUNCH_CHECK(h, "mask_compose_kernel");
+  // one compose launch per output format: class map only | dense bytes | packed bits (dense + packed when both are asked for)
+  const int modes[2] = {p.map_only ? kCompMap : ((p.packed && p.skip_dense) ? kCompPacked : kCompDense),
+                        (!p.map_only && p.packed && !p.skip_dense) ? kCompPacked : -1};
+  for (int pass = 0; pass < 2; ++pass) {
+    const int mode = modes[pass];
+    if (mode < 0) break;
+    // per-warp staging: dense = two segment images of 32 pixels x m bytes (+ alignment shift); packed = m words (split
+    // over the two "buffers"); the class-map-only variant has none
+    size_t buf = 0;
+    if (mode == kCompDense) buf = ((size_t)32 * g.list_cap + 16 + 15) & ~(size_t)15;
+    if (mode == kCompPacked) buf = ((size_t)2 * g.list_cap + 15) & ~(size_t)15;
+    // as many warps as fit: two CTAs per SM if that gives >= 8 warps, else one
+    size_t budget = kCompSmemTwo;
+    int nwarps = kCompWarps;
+    if (mode != kCompMap) {
+      nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
+      if (nwarps < 8) {
+        budget = kCompSmemOne;
+        nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
+      }
+    } else if (fixed > budget) {
+      budget = kCompSmemOne;
+    }
+    if (nwarps > kCompWarps) nwarps = kCompWarps;
+    if (nwarps < 1 || fixed > budget)
+      ISB_FAIL(h, ISB_ERR_LIMIT, "mask compose: %d detections x width %d exceed shared memory", g.list_cap, p.out_w);
+    g.buf_bytes = (int)buf;
+    const size_t smem = fixed + (size_t)nwarps * 2 * buf;
+    const int per_sm = budget == (size_t)kCompSmemTwo ? 2 : 1;
+    int64_t grid = (int64_t)h->num_sms * per_sm;
+    if (grid > total_units) grid = total_units;
+    int* ctr = counters + (pass ? kSecondCounter : 0);
+    if (mode == kCompMap)
+      mask_compose_kernel<kCompMap><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
+    else if (mode == kCompDense)
+      mask_compose_kernel<kCompDense><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
+    else
+      mask_compose_kernel<kCompPacked><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
+    ISB_LAUNCH_CHECK(h, "mask_compose_kernel");
+  }
   return ISB_OK;
 }
 

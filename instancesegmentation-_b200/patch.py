@@ -6,6 +6,7 @@
 
 What is rebound:
   inst_model.yolact.yolact.BBoxUtility                      -> isb.yolact.BBoxUtility   (yolact.py:81,158,240,272)
+  inst_model.yolact.yolact.get_anchors, ...utils.anchors.get_anchors -> isb.anchors.get_anchors (yolact.py:81, anchors.py:39)
   ...network_files.boxes.nms / batched_nms                  -> isb.maskrcnn.*           (rpn_function.py:521, roi_head.py:446)
   ...network_files.transform.paste_masks_in_image / resize_boxes -> isb.maskrcnn.*      (transform.py:410,415)
   ...network_files.roi_head.maskrcnn_inference              -> isb.maskrcnn.maskrcnn_inference (roi_head.py:555)
@@ -21,10 +22,12 @@ from __future__ import annotations
 
 import importlib
 
-from . import maskrcnn, yolact
+from . import anchors, maskrcnn, yolact
 
 _REBIND = [
     ("inst_model.yolact.yolact", "BBoxUtility", lambda: yolact.BBoxUtility),
+    ("inst_model.yolact.yolact", "get_anchors", lambda: anchors.get_anchors),          # yolact.py:14,81
+    ("inst_model.yolact.utils.anchors", "get_anchors", lambda: anchors.get_anchors),   # anchors.py:39
     ("inst_model.Mask_RCNN.net.network_files.boxes", "nms", lambda: maskrcnn.nms),
     ("inst_model.Mask_RCNN.net.network_files.boxes", "batched_nms", lambda: maskrcnn.batched_nms),
     ("inst_model.Mask_RCNN.net.network_files.transform", "paste_masks_in_image", lambda: maskrcnn.paste_masks_in_image),

@@ -128,3 +128,23 @@ def test_nan_inf_cases():
     assert np.array_equal(M.batched_nms(g["n2_boxes"], g["n_scores"], g["n_idxs"], 0.5), g["n2_keep_b"])
     assert np.array_equal(M.nms(g["n3_boxes"], g["n3_scores"], 0.5), g["n3_keep"])
     assert np.array_equal(M.batched_nms(g["n3_boxes"], g["n3_scores"], g["n_idxs"], 0.5), g["n3_keep_b"])
+
+
+def test_product_anchors_equal_oracle_and_reference():
+    """Y1: isb.anchors.get_anchors (the product's prior table, vectorised) is bit-equal to the oracle's restatement of
+    anchors.py:7-48 (itself pinned to the reference) and, in the build container, to the reference's own function."""
+    import os
+    import sys
+    from isb import anchors as A
+    for shape in ((550, 550), (544, 544), (300, 420)):
+        ours = A.get_anchors(list(shape))
+        assert ours.dtype == np.float64 and np.array_equal(ours, O.get_anchors(shape))
+    assert A.get_anchors().shape == (19248, 4) and A.proto_size((550, 550)) == (138, 138) and A.proto_size((544, 544)) == (136, 136)
+    if os.path.isdir("/root/reference"):
+        sys.dont_write_bytecode = True
+        if "/root/reference" not in sys.path:
+            sys.path.insert(0, "/root/reference")
+        from inst_model.yolact.utils.anchors import get_anchors as ref
+        for shape in ([550, 550], [544, 544], [320, 480]):
+            assert np.array_equal(A.get_anchors(shape), ref(shape))
+        assert np.array_equal(A.get_anchors([550, 550], [16, 32, 64, 128, 256]), ref([550, 550], [16, 32, 64, 128, 256]))

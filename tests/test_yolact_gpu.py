@@ -645,3 +645,59 @@ def test_batch_result_overflow_raises(bu, monkeypatch):
     for hd in _lib._handles.values():
         hd.close()
     _lib._handles.clear()
+
+
+@pytest.mark.parametrize("threads", [0, 3, -1])
+def test_detect_host_full_size_matches_device(bu, threads):
+    """isb_yolact_detect_host at the benchmark's image size (550 x 550, up to 100 detections) with the
+    hybrid delivery -- dense copies by the copy engine and bit-packed copies expanded by host threads, split at run time --
+    must leave the caller's host buffers byte-identical to the device path: every mask byte, every image, whichever way
+    it travelled.  threads = 0 is the copy engine alone, 3 a small pool, -1 the default."""
+    import ctypes as C
+    from isb import _lib
+    from isb import anchors as A
+    anchors = torch.from_numpy(A.get_anchors([550, 550])).float()
+    a, p = anchors.shape[0], 138
+    bsz, d, hgt, wid = 11, 100, 550, 550
+    box, conf, coef, proto = synth.yolact_batch(2600, bsz, a, num_classes=81, proto=p)
+    conf[4] = conf[4] * 0.0 + 0.001                      # an image without detections in the middle of a chunk
+    conf[7, :, 1:] *= (torch.rand(a, 1) < 0.02)           # an image with few detections (ragged m)
+    ref = bu.decode_nms_batch((box.cuda(), conf.cuda(), coef.cuda(), proto.cuda()), anchors.cuda(), 0.05, 0.5, (hgt, wid))
+    torch.cuda.synchronize()
+    counts = ref.counts.cpu()
+    assert int(counts[4]) == 0 and 0 < int(counts[7]) < 100 and int(counts[0]) == 100
+    slot = (hgt * wid * d + 15) // 16 * 16
+    pin = [t.contiguous().pin_memory() for t in (box, conf, coef, proto, anchors)]
+    hb, hs = torch.zeros((bsz, d, 4)).pin_memory(), torch.zeros((bsz, d)).pin_memory()
+    hc = torch.zeros((bsz, d), dtype=torch.int64).pin_memory()
+    ha = torch.zeros((bsz, hgt, wid), dtype=torch.int64).pin_memory()
+    hm = torch.full((bsz, slot), 7, dtype=torch.uint8).pin_memory()      # poisoned: every byte must be overwritten
+    hn = torch.zeros((bsz,), dtype=torch.int32).pin_memory()
+    h = _lib.get_handle(0, max_batch=bsz, max_anchors=a, max_classes=80)
+    h.set_host_threads(threads)
+    try:
+        yin = _lib.YolactIn(bsz, a, 81, 32, p, p, hgt, wid, pin[0].data_ptr(), pin[1].data_ptr(), pin[2].data_ptr(),
+                            pin[3].data_ptr(), pin[4].data_ptr(), 0.05, 0.5, 200, d, 0)
+        yout = _lib.YolactOut(hb.data_ptr(), hs.data_ptr(), hc.data_ptr(), ha.data_ptr(), hm.data_ptr(), slot, hn.data_ptr())
+        for rep in range(2):                                              # second call: recycled slots / events / jobs
+            hm.fill_(7)
+            h.check(h.lib.isb_yolact_detect_host(h.ptr, C.byref(yin), C.byref(yout), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+            assert torch.equal(hn, counts)
+            for b in range(bsz):
+                m = int(counts[b])
+                if m == 0:
+                    continue
+                assert torch.equal(hb[b, :m], ref.boxes[b, :m].cpu()) and torch.equal(hs[b, :m], ref.scores[b, :m].cpu())
+                assert torch.equal(hc[b, :m], ref.class_ids[b, :m].cpu()) and torch.equal(ha[b], ref.masks_arg[b].cpu())
+                assert torch.equal(hm[b, : hgt * wid * m], ref.masks_raw[b, : hgt * wid * m].cpu()), f"masks of image {b} (call {rep})"
+                assert bool((hm[b, hgt * wid * m:] == 7).all()), "bytes past H*W*m of a slot must not be touched"
+            st = h.host_stats()
+            assert st["images_copy_engine"] + st["images_host_threads"] == int((counts > 0).sum())
+            if threads == 0:
+                assert st["images_host_threads"] == 0 and st["host_threads"] == 0
+            if threads == 3:
+                assert st["host_threads"] == 3
+            dense_bytes = hgt * wid * int(counts.sum())
+            assert st["d2h_bytes"] <= dense_bytes + bsz * (4 + d * 28 + hgt * wid * 8)
+    finally:
+        h.set_host_threads(-1)
