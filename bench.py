@@ -95,6 +95,7 @@ def workload_config(n_gpus):
             "batch_per_gpu": BATCH_PER_GPU, "global_batch": BATCH_PER_GPU * n_gpus, "anchors": 19248, "classes": NUM_CLASSES,
             "protos": "138x138x32", "out_hw": [INPUT_SIZE, INPUT_SIZE], "confidence": CONFIDENCE, "nms_iou": NMS_IOU,
             "top_k": TOP_K, "max_det": MAX_DET, "objects_per_image": 12, "parallelism": f"per-image shard x{n_gpus}",
+            "count_exchange": "none (1 GPU)" if n_gpus == 1 else "see run",
             "l2": "inputs (733 MB) and outputs (2.1 GB) per step exceed the 126 MB L2; no flush needed"}
 
 
@@ -300,7 +301,12 @@ def run_gpu(args):
                             torch.empty((bsz, slot), dtype=torch.uint8, device=dev),
                             torch.empty((bsz,), dtype=torch.int32, device=dev), shape)
 
-    xchg = sharding.CountExchange(bsz, dev) if world > 1 else None
+    xchg = None
+    if world > 1:
+        # the path's one exchange (per-image detection counts): fused into the NMS kernel as NVLink peer stores when the
+        # ranks can map each other's memory (isb_counts_*), else one NCCL all-gather per step posted off the critical path
+        _lib.get_handle(local_rank, max_batch=bsz, max_anchors=a, max_classes=NUM_CLASSES - 1, max_det=MAX_DET, max_top_k=TOP_K)
+        xchg = sharding.open_count_exchange(bsz, dev, prefer_fused=not args.nccl_counts)
 
     def step():
         bu.decode_nms_batch(dev_in, anchors_d, CONFIDENCE, NMS_IOU, shape, TOP_K, MAX_DET, out=out)
@@ -339,6 +345,8 @@ def run_gpu(args):
         all_counts, all_offsets = xchg.result()
         assert all_counts.numel() == bsz * world and bool((all_counts[rank * bsz:(rank + 1) * bsz].cpu() == out.counts.cpu()).all())
         assert int(all_offsets[-1]) + int(all_counts[-1]) == int(all_counts.sum())
+        if getattr(xchg, "fused", False):
+            assert int(xchg.status.item()) == 0, "fused count exchange: a peer's counts did not arrive"
 
     # ---- end to end through the host-buffer C ABI entry (pinned host memory) -----------------
     import ctypes as C
@@ -538,7 +546,11 @@ def run_gpu(args):
         tr = ncu_traffic()
         line = {"metric": METRIC, "value": n_img / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(world),
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {**workload_config(world),
+                           "count_exchange": "none (1 GPU)" if xchg is None else
+                           ("fused into fast_nms_kernel: NVLink peer stores into every rank's ring (isb_counts_*), no collective launch"
+                            if getattr(xchg, "fused", False) else "NCCL all_gather_into_tensor of int32 counts, posted asynchronously")},
                 "clocks": sampler.summary(),
                 "e2e": {"value": bsz * world / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "steps": e2e_steps, "api": "isb_yolact_detect_host (pinned host buffers in, pinned host bool [H,W,m] out)",
@@ -816,6 +828,8 @@ def main():
     ap.add_argument("--impl", default="isb", choices=["isb", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-variants", action="store_true", help="skip the configs[3] / configs[4] extra keys")
+    ap.add_argument("--nccl-counts", action="store_true", help="multi-GPU: use the NCCL all-gather for the count exchange "
+                                                               "instead of the fused NVLink peer stores")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -132,6 +132,31 @@ ISB_API int isb_set_host_threads(isb_handle* h, int32_t threads);
 ISB_API int isb_host_stats(const isb_handle* h, int64_t stats[8]);
 
 /* ------------------------------------------------------------------------------------
+ * Multi-GPU: the path's one exchange -- every rank learns every image's detection count (the reference has
+ * no multi-GPU inference path: utils_bbox.py:177-180 handles one image) -- fused into isb_yolact_detect over NVLink peer
+ * memory instead of a collective launched after it.
+ *   isb_counts_export  allocates this rank's ring [depth][world * n_local] of 64-bit words and returns its 64-byte CUDA IPC
+ *                      handle; the caller exchanges the handles of all ranks (any side channel, once);
+ *   isb_counts_attach  maps every peer's ring (handles = world x 64 bytes, rank-major).  From then on every
+ *                      isb_yolact_detect call with batch == n_local advances the epoch and its NMS kernel stores
+ *                      epoch << 32 | count of each of its images into slot (epoch mod depth) of EVERY rank's ring -- no
+ *                      extra launch, no collective, no cross-rank stream dependency;
+ *   isb_counts_wait    enqueues a one-CTA kernel that waits (bounded by timeout_ms, default 2000) until all world * n_local
+ *                      words of `epoch` (-1 = this rank's latest) have arrived, then writes counts int32 [world * n_local]
+ *                      (rank-major, -1 = candidate overflow) and, if not NULL, offsets int64 = exclusive scan of
+ *                      max(count, 0).  *status (device int32, may be NULL): 0 ok, 1 timed out, 2 the slot was overwritten
+ *                      by a newer epoch (a rank ran more than `depth` calls ahead of this read);
+ *   isb_counts_epoch   epoch of this rank's latest publishing call;  isb_counts_detach unmaps and frees.
+ * All ranks must issue the same sequence of publishing calls.
+ * ---------------------------------------------------------------------------------- */
+ISB_API int isb_counts_export(isb_handle* h, int32_t n_local, int32_t world, int32_t depth, unsigned char handle_out[64]);
+ISB_API int isb_counts_attach(isb_handle* h, int32_t rank, const unsigned char* handles);
+ISB_API int isb_counts_wait(isb_handle* h, int64_t epoch, int32_t* counts, int64_t* offsets, int32_t* status,
+                            int32_t timeout_ms, isb_stream stream);
+ISB_API int64_t isb_counts_epoch(const isb_handle* h);
+ISB_API int isb_counts_detach(isb_handle* h);
+
+/* ------------------------------------------------------------------------------------
  * Detect + per-pixel CLASS MAP, for callers that draw / score a class image and never look at
  * the per-instance masks.  Replaces decode_nms (utils_bbox.py:170-243) TOGETHER WITH the
  * wrapper tail inst_model/yolact/yolact.py:162-170:
@@ -231,6 +256,13 @@ ISB_API int isb_crop(isb_handle* h, const float* masks, const float* boxes, int3
 /* utils_bbox.py:223 inner product only: proto[Ph,Pw,K] @ coef[m,K]^T -> logits [Ph,Pw,m] */
 ISB_API int isb_mask_logits(isb_handle* h, const float* proto, const float* coef, int32_t proto_h, int32_t proto_w, int32_t m,
                     float* out, isb_stream stream);
+
+/* utils_bbox.py:223 for a BATCH of pictures in one persistent launch on the tensor cores: proto [B,Ph,Pw,K], coef [B,m,K]
+ * (m <= 128) -> out [B,Ph,Pw,m] = proto @ coef^T, or sigmoid of it (apply_sigmoid != 0: the whole of :223).  tcgen05.mma
+ * kind::tf32 with every fp32 operand split exactly into three tf32 parts (six partial products, fp32 accumulation in tensor
+ * memory: the result meets the 1e-5 bar), prototype tiles fetched by bulk TMA two deep, one bulk store per 128-pixel tile. */
+ISB_API int isb_mask_logits_batch(isb_handle* h, const float* proto, const float* coef, int32_t batch, int32_t proto_h,
+                                  int32_t proto_w, int32_t m, int32_t apply_sigmoid, float* out, isb_stream stream);
 
 /* utils_bbox.py:223-241 for one image with m known on the host:
  * sigmoid(proto@coef^T) -> bilinear to (H,W) -> crop by boxes_px -> argmax, >0.5.

@@ -16,8 +16,9 @@ ISB_OK, ISB_ERR_BAD_ARG, ISB_ERR_CUDA, ISB_ERR_LIMIT, ISB_ERR_OVERFLOW = 0, -1, 
 SYMBOLS = (
     "isb_version", "isb_create", "isb_destroy", "isb_last_error", "isb_workspace_bytes", "isb_launch_count",
     "isb_profile_begin", "isb_profile_read",
-    "isb_yolact_detect", "isb_yolact_detect_host", "isb_set_host_threads", "isb_host_stats", "isb_yolact_class_map", "isb_yolact_class_map_host", "isb_rle_encode", "isb_rle_to_string", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
-    "isb_traditional_nms", "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_assemble",
+    "isb_yolact_detect", "isb_yolact_detect_host", "isb_set_host_threads", "isb_host_stats",
+    "isb_counts_export", "isb_counts_attach", "isb_counts_wait", "isb_counts_epoch", "isb_counts_detach", "isb_yolact_class_map", "isb_yolact_class_map_host", "isb_rle_encode", "isb_rle_to_string", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
+    "isb_traditional_nms", "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_logits_batch", "isb_mask_assemble",
     "isb_box_decode", "isb_nms", "isb_batched_nms", "isb_ms_roi_align", "isb_mask_select_sigmoid", "isb_resize_boxes",
     "isb_paste_masks", "isb_paste_class_map", "isb_rpn_filter", "isb_box_postprocess", "isb_preprocess",
     "isb_rcnn_transform",
@@ -90,6 +91,12 @@ def load():
         lib.isb_profile_read.argtypes = [vp, C.POINTER(C.c_double * 4), C.POINTER(i32)]
         lib.isb_yolact_detect.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactOut), vp]
         lib.isb_yolact_detect_host.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactOut), vp]
+        lib.isb_counts_export.argtypes = [vp, i32, i32, i32, C.c_char_p]
+        lib.isb_counts_attach.argtypes = [vp, i32, C.c_char_p]
+        lib.isb_counts_wait.argtypes = [vp, i64, vp, vp, vp, i32, vp]
+        lib.isb_counts_epoch.argtypes = [vp]
+        lib.isb_counts_epoch.restype = i64
+        lib.isb_counts_detach.argtypes = [vp]
         lib.isb_set_host_threads.argtypes = [vp, i32]
         lib.isb_host_stats.argtypes = [vp, C.POINTER(i64 * 8)]
         lib.isb_yolact_class_map.argtypes = [vp, C.POINTER(YolactIn), C.POINTER(YolactMapOut), vp]
@@ -104,6 +111,7 @@ def load():
         lib.isb_correct_boxes.argtypes = [vp, vp, i64, i32, i32, vp, vp]
         lib.isb_crop.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
         lib.isb_mask_logits.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
+        lib.isb_mask_logits_batch.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]
         lib.isb_mask_assemble.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp]
         f64 = C.c_double
         lib.isb_box_decode.argtypes = [vp, vp, vp, i64, i32, f32, f32, f32, f32, f32, vp, vp]
@@ -121,7 +129,8 @@ def load():
         lib.isb_preprocess.argtypes = [vp, vp, i32, i32, i32, i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double), vp, vp, vp]
         for name in SYMBOLS:
             fn = getattr(lib, name)
-            if name not in ("isb_destroy", "isb_last_error", "isb_workspace_bytes", "isb_launch_count", "isb_version"):
+            if name not in ("isb_destroy", "isb_last_error", "isb_workspace_bytes", "isb_launch_count", "isb_version",
+                            "isb_counts_epoch", "isb_rle_to_string"):
                 fn.restype = C.c_int
         _lib = lib
         return lib

@@ -77,10 +77,12 @@ extern "C" int isb_profile_read(isb_handle* h, double stage_ms[4], int32_t* call
 }
 
 static void destroy_host_pipe(isb_handle* h);
+static void cx_release(isb_handle* h);
 
 static void free_ws(isb_handle* h) {
   free_profile(h);
   destroy_host_pipe(h);
+  cx_release(h);
   for (int l = 0; l < 3; ++l) {
     if (h->lane_stream[l]) cudaStreamDestroy(h->lane_stream[l]);
     if (h->lane_event[l]) cudaEventDestroy(h->lane_event[l]);
@@ -280,6 +282,14 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const Yo
   np.out_class = out->class_ids;
   np.out_coef = nullptr;  // coefficients of kept detections go to the workspace
   np.out_count = out->counts;
+  if (h->cx_attached && in->batch == h->cx_local && h->ws_b0 == 0 && h->ws_images == 0) {  // (not from inside the *_host sub-batch pipeline)
+    // fused count exchange: this call's counts also go to slot (epoch mod depth) of every rank's ring
+    h->cx_epoch += 1;
+    np.n_peers = h->cx_world;
+    for (int r = 0; r < h->cx_world; ++r) np.peer_ring[r] = h->cx_peer[r];
+    np.peer_index0 = (int32_t)((h->cx_epoch % (uint32_t)h->cx_depth) * (uint32_t)(h->cx_world * h->cx_local) + h->cx_rank * h->cx_local);
+    np.peer_epoch = h->cx_epoch;
+  }
   if ((rc = launch_fast_nms(h, np, s)) != ISB_OK) return rc;
   if (ev) ISB_CUDA(h, cudaEventRecord(ev[2], s));
 
@@ -663,6 +673,92 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
   return ISB_OK;
 }
 
+// ----------------------------------------------------------------------------------- fused count exchange
+static void cx_release(isb_handle* h) {
+  for (int r = 0; r < 8; ++r) {
+    if (h->cx_peer[r] && r != h->cx_rank && h->cx_attached) cudaIpcCloseMemHandle(h->cx_peer[r]);
+    h->cx_peer[r] = nullptr;
+  }
+  cudaFree(h->cx_ring);
+  cudaFree(h->cx_status);
+  h->cx_ring = nullptr;
+  h->cx_status = nullptr;
+  h->cx_attached = 0;
+  h->cx_world = h->cx_local = h->cx_depth = 0;
+}
+
+extern "C" int isb_counts_export(isb_handle* h, int32_t n_local, int32_t world, int32_t depth, unsigned char handle_out[64]) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (!handle_out || n_local <= 0 || world < 1 || world > 8 || depth < 2 || depth > 64)
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "counts_export: need n_local > 0, 1 <= world <= 8, 2 <= depth <= 64");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handles are 64 bytes");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_CUDA(h, cudaDeviceSynchronize());
+  cx_release(h);
+  const size_t words = (size_t)depth * world * n_local;
+  ISB_CUDA(h, cudaMalloc((void**)&h->cx_ring, words * sizeof(unsigned long long)));
+  ISB_CUDA(h, cudaMemset(h->cx_ring, 0, words * sizeof(unsigned long long)));  // epoch 0 = nothing published yet
+  ISB_CUDA(h, cudaMalloc((void**)&h->cx_status, sizeof(int32_t)));
+  ISB_CUDA(h, cudaDeviceSynchronize());
+  cudaIpcMemHandle_t ipc;
+  ISB_CUDA(h, cudaIpcGetMemHandle(&ipc, h->cx_ring));
+  memcpy(handle_out, &ipc, 64);
+  h->cx_world = world;
+  h->cx_local = n_local;
+  h->cx_depth = depth;
+  h->cx_epoch = 0;
+  return ISB_OK;
+}
+
+extern "C" int isb_counts_attach(isb_handle* h, int32_t rank, const unsigned char* handles) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (!h->cx_ring) ISB_FAIL(h, ISB_ERR_BAD_ARG, "counts_attach: call isb_counts_export first");
+  if (!handles || rank < 0 || rank >= h->cx_world) ISB_FAIL(h, ISB_ERR_BAD_ARG, "counts_attach: bad rank or null handles");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  h->cx_rank = rank;
+  for (int r = 0; r < h->cx_world; ++r) {
+    if (r == rank) { h->cx_peer[r] = h->cx_ring; continue; }
+    cudaIpcMemHandle_t ipc;
+    memcpy(&ipc, handles + (size_t)r * 64, 64);
+    void* ptr = nullptr;
+    const cudaError_t e = cudaIpcOpenMemHandle(&ptr, ipc, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      for (int q = 0; q < r; ++q)
+        if (q != rank && h->cx_peer[q]) { cudaIpcCloseMemHandle(h->cx_peer[q]); h->cx_peer[q] = nullptr; }
+      ISB_FAIL(h, ISB_ERR_CUDA, "counts_attach: cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e));
+    }
+    h->cx_peer[r] = static_cast<unsigned long long*>(ptr);
+  }
+  h->cx_attached = 1;
+  return ISB_OK;
+}
+
+extern "C" int isb_counts_detach(isb_handle* h) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_CUDA(h, cudaDeviceSynchronize());
+  cx_release(h);
+  return ISB_OK;
+}
+
+extern "C" int64_t isb_counts_epoch(const isb_handle* h) { return h ? (int64_t)h->cx_epoch : -1; }
+
+extern "C" int isb_counts_wait(isb_handle* h, int64_t epoch, int32_t* counts, int64_t* offsets, int32_t* status,
+                               int32_t timeout_ms, isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (!h->cx_attached) ISB_FAIL(h, ISB_ERR_BAD_ARG, "counts_wait: no count exchange attached");
+  if (!counts) ISB_FAIL(h, ISB_ERR_BAD_ARG, "counts_wait: null counts");
+  if (epoch < 0) epoch = h->cx_epoch;
+  if (epoch == 0 || epoch > (int64_t)h->cx_epoch) ISB_FAIL(h, ISB_ERR_BAD_ARG, "counts_wait: epoch %lld has not been published by this rank", (long long)epoch);
+  if ((int64_t)h->cx_epoch - epoch >= h->cx_depth) ISB_FAIL(h, ISB_ERR_LIMIT, "counts_wait: epoch %lld left the ring (depth %d)", (long long)epoch, h->cx_depth);
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  const int n = h->cx_world * h->cx_local;
+  const unsigned long long* slot = h->cx_ring + (size_t)((uint32_t)epoch % (uint32_t)h->cx_depth) * n;
+  if (timeout_ms <= 0) timeout_ms = 2000;
+  return launch_counts_wait(h, slot, n, (unsigned)epoch, counts, offsets, status ? status : h->cx_status,
+                            (long long)timeout_ms * 1000000ll, (cudaStream_t)stream);
+}
+
 // ----------------------------------------------------------------------------------- stages
 extern "C" int isb_decode_boxes(isb_handle* h, const float* pred, const float* anchors, int64_t n, float var0, float var1,
                                 float* out, isb_stream stream) {
@@ -806,6 +902,23 @@ extern "C" int isb_mask_logits(isb_handle* h, const float* proto, const float* c
   if (!proto || !coef || !out || !aligned16(proto) || !aligned16(coef)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_logits: null or misaligned pointer");
   ISB_CUDA(h, cudaSetDevice(h->device));
   return launch_mask_logits_tc(h, proto, coef, (int64_t)proto_h * proto_w, m, out, (cudaStream_t)stream);
+}
+
+extern "C" int isb_mask_logits_batch(isb_handle* h, const float* proto, const float* coef, int32_t batch, int32_t proto_h,
+                                     int32_t proto_w, int32_t m, int32_t apply_sigmoid, float* out, isb_stream stream) {
+  if (!h) return ISB_ERR_BAD_ARG;
+  if (batch < 0 || proto_h < 0 || proto_w < 0 || m < 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_logits_batch: negative size");
+  if ((int64_t)batch * proto_h * proto_w * m == 0) return ISB_OK;
+  if (m > kTcBatchMaxDet) ISB_FAIL(h, ISB_ERR_LIMIT, "mask_logits_batch: m %d > %d (use isb_mask_logits per picture)", m, kTcBatchMaxDet);
+  if ((int64_t)proto_h * proto_w >= (1ll << 31)) ISB_FAIL(h, ISB_ERR_LIMIT, "mask_logits_batch: prototype map too large");
+  if (!proto || !coef || !out || !aligned16(proto) || !aligned16(coef) || !aligned16(out))
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_logits_batch: null or misaligned pointer");
+  ISB_CUDA(h, cudaSetDevice(h->device));
+  TcBatchArgs a;
+  memset(&a, 0, sizeof(a));
+  a.proto = proto; a.coef = coef; a.coef_rows = m; a.counts = nullptr; a.m_fixed = m; a.batch = batch;
+  a.npix = proto_h * proto_w; a.proto_w = proto_w; a.mode = apply_sigmoid ? 1 : 0; a.out = out;
+  return launch_mask_logits_batch(h, a, (cudaStream_t)stream);
 }
 
 extern "C" int isb_mask_assemble(isb_handle* h, const float* proto, const float* coef, const float* boxes_px,

@@ -333,6 +333,12 @@ struct isb_handle {
   cudaStream_t lane_stream[3];
   cudaEvent_t lane_event[3];
   cudaEvent_t fork_event;
+  // fused count exchange (isb_counts_*): this rank's ring, the peers' mappings of theirs
+  unsigned long long* cx_ring;        // [cx_depth][cx_world * cx_local] on this device (cudaMalloc, exported through CUDA IPC)
+  unsigned long long* cx_peer[8];     // ring of rank r as mapped into this process (cx_peer[cx_rank] == cx_ring)
+  int32_t cx_world, cx_rank, cx_local, cx_depth, cx_attached;
+  uint32_t cx_epoch;                  // epoch of the last isb_yolact_detect call that published counts
+  int32_t* cx_status;                 // device word the wait kernel reports into
   void* host_pipe;         // HostPipe (isb_api.cu): worker pool, pinned landing buffer, copy streams / events of the host delivery
   int32_t host_threads;    // isb_set_host_threads: -1 = default (host_default_threads()), 0 = copy engine only
   int64_t host_stats[8];   // last *_host call: images by copy engine, images by host threads, D2H bytes, H2D bytes, ...
@@ -408,6 +414,12 @@ struct NmsParams {
   int64_t* out_class;      // [B, max_det]
   float* out_coef;         // [B, max_det, K]
   int32_t* out_count;      // [B]
+  // fused count exchange (counts_exchange.cu): with n_peers > 0 the kernel also stores epoch << 32 | count of image b into
+  // peer_ring[r][peer_index0 + b] for every rank r (peer-mapped device memory)
+  unsigned long long* peer_ring[8];
+  int32_t n_peers;
+  int32_t peer_index0;
+  uint32_t peer_epoch;
 };
 int launch_fast_nms(isb_handle* h, const NmsParams& p, cudaStream_t s);
 // one image, n candidates known on the host, spread over the GPU (n > fast_nms_smem_candidates())
@@ -464,7 +476,17 @@ int configure_nms(isb_handle* h);
 int configure_mask_gemm_tc(isb_handle* h);
 int launch_mask_logits_tc(isb_handle* h, const float* proto, const float* coef, int64_t npix, int m, float* out,
                           cudaStream_t s);
+// batched tcgen05 product (mask_gemm_tc.cu): mode 0 logits, 1 sigmoid -> dense out [B, npix, m]; mode 2 sigmoid scattered
+// into the packed footprint maps (rec / smap / s_cap), m read per image from counts
+struct TcBatchArgs {
+  const float* proto; const float* coef; int64_t coef_rows; const int32_t* counts; int32_t m_fixed;
+  int32_t batch, npix, proto_w, mode; float* out; const DetRec* rec; int32_t rec_stride; float* smap; int64_t s_cap;
+};
+int launch_mask_logits_batch(isb_handle* h, const TcBatchArgs& a, cudaStream_t s);
+constexpr int kTcBatchMaxDet = 128;
 
+int launch_counts_wait(isb_handle* h, const unsigned long long* slot, int n, unsigned epoch, int32_t* counts, int64_t* offsets,
+                       int32_t* status, long long timeout_ns, cudaStream_t s);
 int launch_sort_u64(isb_handle* h, uint64_t* keys, int n_pow2, cudaStream_t s);
 int launch_rank_sort_u64(isb_handle* h, const uint64_t* keys, int n_max, const int32_t* n_dev, int32_t* rank, uint64_t* out,
                          cudaStream_t s);

@@ -23,6 +23,8 @@
 //       zero except for the bytes their owner warp set, which it clears again after the store has
 //       read the buffer.
 // Bound: HBM write bandwidth (302 500*m + 2 420 000 bytes per image at 550^2).
+#include <stdlib.h>
+
 #include "isb_common.cuh"
 
 namespace isb {
@@ -37,6 +39,9 @@ constexpr int kSecondCounter = 16;    // work counter of a second compose launch
 
 struct CompGeom {
   int units_per_img;
+  int unit_px;         // pixels per work unit (<= kUnitPx; smaller when the call has few pixels in total, so every SM gets work)
+  int seg_px;          // pixels per warp segment (32; 16 / 8 / 4 when m is so large that 32-pixel segment images would leave
+                       // room for only a couple of warps per SM -- BASELINE configs[4], m = 1024)
   float scale_y, scale_x;
   int list_cap;        // detections per image upper bound
   int buf_bytes;       // bytes of one warp's segment buffer (multiple of 16), two per warp
@@ -137,6 +142,13 @@ sigmoid_map_kernel(MaskParams p, const DetRec* __restrict__ rec, const int32_t* 
   }
 }
 
+__global__ void reset_counters_kernel(int* __restrict__ compose_counter) {
+  if (threadIdx.x == 0) {
+    compose_counter[0] = 0;
+    compose_counter[kSecondCounter] = 0;
+  }
+}
+
 // ---- K3b -----------------------------------------------------------------------------------
 // zero buf[a, b) with one warp: 16-byte interior, byte edges (never touches a byte outside [a, b))
 __device__ __forceinline__ void warp_clear(uint8_t* buf, int a, int b, int lane) {
@@ -210,13 +222,14 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
     const int m = p.counts ? p.counts[b] : p.m_fixed;
     if (m <= 0) {  // nothing to write for this image (the reference returns None); its class map is background
       if (p.class_map) {
-        const int px0 = u * kUnitPx, px1 = min(px0 + kUnitPx, HW);
+        const int px0 = u * g.unit_px, px1 = min(px0 + g.unit_px, HW);
         for (int q = px0 + tid; q < px1; q += blockDim.x) p.class_map[(size_t)b * HW + q] = 0;
       }
       continue;
     }
-    const int px0 = u * kUnitPx;
-    const int px1 = min(px0 + kUnitPx, HW);
+    const int px0 = u * g.unit_px;
+    const int px1 = min(px0 + g.unit_px, HW);
+    const int segpx = g.seg_px;
     const int ya = px0 / W, yb = (px1 - 1) / W;  // rows the unit touches
     uint8_t* out_img = kMasks ? p.masks + (size_t)b * p.mask_slot_bytes : nullptr;
     uint32_t* pk_img = kPacked ? reinterpret_cast<uint32_t*>(p.packed + (size_t)b * p.packed_slot_bytes) : nullptr;
@@ -263,10 +276,10 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
     const int nlist = s_nlist;
 
     // ---- segments of 32 pixels: every warp runs its own, independently of the other warps ---------------
-    int xq = (px0 - ya * W) + warp * 32 + lane, yq = ya;  // this lane's pixel in the warp's first segment
+    int xq = (px0 - ya * W) + warp * segpx + lane, yq = ya;  // this lane's pixel in the warp's first segment
     while (xq >= W) { xq -= W; ++yq; }
-    for (int q0 = px0 + warp * 32; q0 < px1; q0 += nwarps * 32, ++seg_no) {
-      const int nt = min(32, px1 - q0);
+    for (int q0 = px0 + warp * segpx; q0 < px1; q0 += nwarps * segpx, ++seg_no) {
+      const int nt = min(segpx, px1 - q0);
       const int par = seg_no & 1;
       uint8_t* buf = wbuf + (par ? g.buf_bytes : 0);
       uint8_t* g0 = kMasks ? out_img + (int64_t)q0 * m : nullptr;
@@ -369,7 +382,7 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
         for (int w = lane; w < nwords; w += 32) gw[w] = wbits[w];
       }
       // this lane's pixel in the warp's next segment
-      xq += nwarps * 32;
+      xq += nwarps * segpx;
       while (xq >= W) { xq -= W; ++yq; }
     }
   }
@@ -411,7 +424,12 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   if (p.det_stride > h->lim.max_det) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly: %d detections > max_det %d", p.det_stride, h->lim.max_det);
   CompGeom g;
   const int64_t hw = (int64_t)p.out_h * p.out_w;
-  g.units_per_img = (int)((hw + kUnitPx - 1) / kUnitPx);
+  // work units: kUnitPx pixels, halved while the call has fewer than ~4 units per resident CTA (one image with very many
+  // detections -- configs[4] -- would otherwise keep half the SMs idle: 74 units for 148 CTAs)
+  g.unit_px = kUnitPx;
+  while (g.unit_px > 512 && (int64_t)p.batch * ((hw + g.unit_px - 1) / g.unit_px) < 8ll * h->num_sms) g.unit_px >>= 1;
+  g.units_per_img = (int)((hw + g.unit_px - 1) / g.unit_px);
+  g.seg_px = 32;
   g.scale_y = (float)p.proto_h / (float)p.out_h;
   g.scale_x = (float)p.proto_w / (float)p.out_w;
   g.list_cap = p.m_fixed >= 0 ? (p.m_fixed > 0 ? p.m_fixed : 1) : (p.m_cap > 0 ? p.m_cap : p.det_stride);
@@ -429,9 +447,21 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   float* smap = h->smap + (size_t)h->ws_b0 * g.s_cap;
   if (p.batch > kSmapMaxBatch) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports at most %d images per call", kSmapMaxBatch);
   int* counters = h->work_counter + h->ws_lane;
-  sigmoid_map_kernel<<<h->num_sms * kSmapCtasPerSm, kSmapThreads, (size_t)g.list_cap * sizeof(DetRec), s>>>(
-      p, rec, h->smap_total + h->ws_b0, smap, g.s_cap, counters);
-  ISB_LAUNCH_CHECK(h, "sigmoid_map_kernel");
+  static const bool tc_smap = getenv("ISB_TC_SMAP") != nullptr;  // tensor-core product instead of K3a (measurement switch)
+  if (tc_smap && g.list_cap <= kTcBatchMaxDet) {
+    reset_counters_kernel<<<1, 32, 0, s>>>(counters);
+    ISB_LAUNCH_CHECK(h, "reset_counters_kernel");
+    TcBatchArgs a;
+    memset(&a, 0, sizeof(a));
+    a.proto = p.proto; a.coef = p.coef; a.coef_rows = p.det_stride; a.counts = p.counts; a.m_fixed = p.m_fixed;
+    a.batch = p.batch; a.npix = p.proto_h * p.proto_w; a.proto_w = p.proto_w; a.mode = 2;
+    a.rec = rec; a.rec_stride = p.det_stride; a.smap = smap; a.s_cap = g.s_cap;
+    if ((rc = launch_mask_logits_batch(h, a, s)) != ISB_OK) return rc;
+  } else {
+    sigmoid_map_kernel<<<h->num_sms * kSmapCtasPerSm, kSmapThreads, (size_t)g.list_cap * sizeof(DetRec), s>>>(
+        p, rec, h->smap_total + h->ws_b0, smap, g.s_cap, counters);
+    ISB_LAUNCH_CHECK(h, "sigmoid_map_kernel");
+  }
   if (h->prof_mid) ISB_CUDA(h, cudaEventRecord(h->prof_mid, s));
   // one compose launch per output format: class map only | dense bytes | packed bits (dense + packed when both are asked for)
   const int modes[2] = {p.map_only ? kCompMap : ((p.packed && p.skip_dense) ? kCompPacked : kCompDense),
@@ -442,12 +472,24 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
     // per-warp staging: dense = two segment images of 32 pixels x m bytes (+ alignment shift); packed = m words (split
     // over the two "buffers"); the class-map-only variant has none
     size_t buf = 0;
-    if (mode == kCompDense) buf = ((size_t)32 * g.list_cap + 16 + 15) & ~(size_t)15;
-    if (mode == kCompPacked) buf = ((size_t)2 * g.list_cap + 15) & ~(size_t)15;
-    // as many warps as fit: two CTAs per SM if that gives >= 8 warps, else one
     size_t budget = kCompSmemTwo;
     int nwarps = kCompWarps;
-    if (mode != kCompMap) {
+    g.seg_px = 32;
+    if (mode == kCompPacked) buf = ((size_t)2 * g.list_cap + 15) & ~(size_t)15;
+    if (mode == kCompDense) {
+      // as many warps as fit: two CTAs per SM if that gives >= 8 warps, else one; if even that leaves fewer than 8
+      // warps, shorter segments (the segment image is seg_px x m bytes)
+      for (int seg = 32; seg >= 4; seg >>= 1) {
+        g.seg_px = seg;
+        buf = ((size_t)seg * g.list_cap + 16 + 15) & ~(size_t)15;
+        budget = kCompSmemTwo;
+        nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
+        if (nwarps >= 8) break;
+        budget = kCompSmemOne;
+        nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
+        if (nwarps >= 8) break;
+      }
+    } else if (mode == kCompPacked) {
       nwarps = fixed < budget ? (int)((budget - fixed) / (2 * buf)) : 0;
       if (nwarps < 8) {
         budget = kCompSmemOne;

@@ -176,6 +176,20 @@ __device__ __forceinline__ void fnms_emit(const NmsParams& p, int b, const uint6
   }
 }
 
+// counts[b] = m, and -- multi-GPU jobs with the fused count exchange attached -- the same count into the current ring slot of
+// every rank over NVLink: one self-validating 64-bit word (epoch << 32 | count) per image and peer, written by the
+// CTA's first thread.  Called by the whole CTA.
+__device__ __forceinline__ void publish_count(const NmsParams& p, int b, int m) {
+  if (threadIdx.x == 0) {
+    p.out_count[b] = m;
+    const unsigned long long w = ((unsigned long long)p.peer_epoch << 32) | (unsigned)m;
+#pragma unroll
+    for (int r = 0; r < 8; ++r)  // static indices: the pointer table stays in the kernel's parameter bank
+      if (r < p.n_peers)
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.peer_ring[r] + p.peer_index0 + b), "l"(w) : "memory");
+  }
+}
+
 __global__ void __launch_bounds__(kNmsThreads, 1)
 fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* __restrict__ g_keys,
                 uint64_t* __restrict__ g_det, float4* __restrict__ g_box, int64_t cap, int64_t stride,
@@ -191,12 +205,12 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
   const int tid = threadIdx.x;
   const int64_t total = cand_count[b];
   if (total > cap) {  // candidate buffer overflowed: report, never guess
-    if (tid == 0) p.out_count[b] = -1;
+    publish_count(p, b, -1);
     return;
   }
   const int n = (int)total;
   if (n == 0) {
-    if (tid == 0) p.out_count[b] = 0;
+    publish_count(p, b, 0);
     return;
   }
   const int np2 = max(64, next_pow2(n));
@@ -306,7 +320,7 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
 
   // ---- 5. outputs -----------------------------------------------------------------------
   fnms_emit(p, b, dkeys, m, det_coef_ws, det_rec_ws, smap_total_ws, ws_det_stride, s_scan);
-  if (tid == 0) p.out_count[b] = m;
+  publish_count(p, b, m);
 }
 
 

@@ -186,6 +186,22 @@ class BBoxUtility(object):
             h.check(h.lib.isb_mask_logits(h.ptr, _ptr(proto), _ptr(coef), ph, pw, m, _ptr(out), _stream(proto.device)))
         return out
 
+    def mask_logits_batch(self, pred_proto, mask_coef, sigmoid=False):
+        """utils_bbox.py:223 for a batch in one launch on the tensor cores: proto [B,Ph,Pw,K], coef [B,m,K] (m <= 128) ->
+        [B,Ph,Pw,m] = proto @ coef^T (sigmoid=True: torch.sigmoid of it, the whole of :223)."""
+        proto = _cuda_f32(pred_proto, "pred_proto")
+        coef = _cuda_f32(mask_coef, "mask_coef").to(proto.device)
+        b, ph, pw, k = proto.shape
+        m = coef.shape[1]
+        if k != ISB_NUM_COEF or coef.shape[0] != b or coef.shape[2] != k:
+            raise ValueError("mask_logits_batch expects proto [B,Ph,Pw,32] and coef [B,m,32]")
+        out = torch.empty((b, ph, pw, m), dtype=torch.float32, device=proto.device)
+        h = get_handle(proto.device.index)
+        with _lib.on_device(proto.device):
+            h.check(h.lib.isb_mask_logits_batch(h.ptr, _ptr(proto), _ptr(coef), b, ph, pw, m, 1 if sigmoid else 0, _ptr(out),
+                                                _stream(proto.device)))
+        return out
+
     def assemble_masks(self, pred_proto, mask_coef, boxes_px, image_shape):
         """utils_bbox.py:223-241 for given detections: returns (masks_arg i64 [H,W], masks bool [H,W,m])."""
         proto = _cuda_f32(pred_proto, "pred_proto")

@@ -115,3 +115,14 @@ def test_count_exchange_single_process():
     x.post(torch.tensor([3, 0, 5], dtype=torch.int32))
     c, o = x.result()
     assert c.tolist() == [3, 0, 5] and o.tolist() == [0, 3, 3]
+
+
+def test_open_count_exchange_falls_back_without_cuda():
+    """open_count_exchange picks the fused NVLink version only for CUDA devices of an initialised multi-rank group; anywhere
+    else it is the all-gather class (single process here: world 1, CPU tensors)."""
+    from isb.sharding import CountExchange, open_count_exchange
+    x = open_count_exchange(4, torch.device("cpu"))
+    assert isinstance(x, CountExchange) and not getattr(x, "fused", False)
+    x.post(torch.tensor([3, 0, -1, 5], dtype=torch.int32))
+    counts, offsets = x.result()
+    assert counts.tolist() == [3, 0, -1, 5] and offsets.tolist() == [0, 3, 3, 3]

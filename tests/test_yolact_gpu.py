@@ -701,3 +701,75 @@ def test_detect_host_full_size_matches_device(bu, threads):
             assert st["d2h_bytes"] <= dense_bytes + bsz * (4 + d * 28 + hgt * wid * 8)
     finally:
         h.set_host_threads(-1)
+
+
+def test_fused_count_exchange_single_rank(bu):
+    """isb_counts_* (the multi-GPU count exchange fused into fast_nms_kernel as peer stores) with world = 1: the rank's own
+    ring is its only peer.  Every publishing detect call advances the epoch; the wait kernel returns the counts and their
+    exclusive scan; an epoch that left the ring is refused; the wait is bounded when a word never arrives."""
+    import ctypes as C
+    from isb import _lib
+    g = load_golden("yolact_tiny_a")
+    bsz = 3
+    ins = tuple(dev(g[k])[None].repeat((bsz,) + (1,) * g[k].ndim).contiguous() for k in ("box", "conf", "coef", "proto"))
+    ins[1][1] *= 0.0                                   # image 1: no detections
+    anchors = dev(g["anchors"])
+    h = _lib.get_handle(0, max_batch=bsz, max_anchors=g["conf"].shape[0], max_classes=g["conf"].shape[1] - 1)
+    mine = C.create_string_buffer(64)
+    h.check(h.lib.isb_counts_export(h.ptr, bsz, 1, 2, mine))
+    h.check(h.lib.isb_counts_attach(h.ptr, 0, mine.raw))
+    try:
+        counts = torch.full((bsz,), -7, dtype=torch.int32, device="cuda")
+        offsets = torch.zeros((bsz,), dtype=torch.int64, device="cuda")
+        status = torch.full((1,), -1, dtype=torch.int32, device="cuda")
+        P = lambda t: C.c_void_p(t.data_ptr())
+        for call in range(1, 4):
+            res = bu.decode_nms_batch(ins, anchors, float(g["confidence"]), float(g["nms_iou"]), g["image_shape"])
+            assert int(h.lib.isb_counts_epoch(h.ptr)) == call
+            h.check(h.lib.isb_counts_wait(h.ptr, -1, P(counts), P(offsets), P(status), 500, None))
+            torch.cuda.synchronize()
+            assert int(status[0]) == 0 and torch.equal(counts, res.counts)
+            c = res.counts.cpu().to(torch.int64).clamp(min=0)
+            assert torch.equal(offsets.cpu(), torch.cumsum(c, 0) - c) and int(counts[1]) == 0 and int(counts[0]) > 0
+        # a batch of another size does not publish
+        bu.decode_nms_batch(tuple(t[:2] for t in ins), anchors, float(g["confidence"]), float(g["nms_iou"]), g["image_shape"])
+        assert int(h.lib.isb_counts_epoch(h.ptr)) == 3
+        assert h.lib.isb_counts_wait(h.ptr, 1, P(counts), P(offsets), P(status), 500, None) == _lib.ISB_ERR_LIMIT   # depth 2
+        assert h.lib.isb_counts_wait(h.ptr, 9, P(counts), P(offsets), P(status), 500, None) == _lib.ISB_ERR_BAD_ARG
+    finally:
+        h.check(h.lib.isb_counts_detach(h.ptr))
+    assert h.lib.isb_counts_wait(h.ptr, -1, P(counts), P(offsets), P(status), 500, None) == _lib.ISB_ERR_BAD_ARG
+
+
+@pytest.mark.parametrize("m,bsz", [(100, 5), (37, 2), (128, 1), (8, 3)])
+def test_mask_logits_batch_tensor_cores(bu, m, bsz):
+    """isb_mask_logits_batch (batched tcgen05 + TMEM kernel, bulk-TMA prototype tiles): within 1e-5 of the float64 product
+    for every picture, including the partial last tile (138 * 138 = 148 * 128 + 100 pixels), a detection count that is not
+    a multiple of 4 or 16, and the sigmoid epilogue (utils_bbox.py:223)."""
+    gen = torch.Generator().manual_seed(30 + m)
+    proto = torch.relu(torch.randn(bsz, 138, 138, 32, generator=gen))
+    coef = torch.tanh(torch.randn(bsz, m, 32, generator=gen))
+    ref = torch.matmul(proto.double(), coef.double().transpose(1, 2)[:, None])
+    out = bu.mask_logits_batch(proto.cuda(), coef.cuda())
+    assert tuple(out.shape) == (bsz, 138, 138, m)
+    assert_close_f32(host(out), ref.numpy(), 1e-5, "batched mask logits")
+    sg = bu.mask_logits_batch(proto.cuda(), coef.cuda(), sigmoid=True)
+    assert_close_f32(host(sg), torch.sigmoid(ref).numpy(), 1e-5, "batched sigmoid(mask logits)")
+    # the per-picture stage kernel agrees
+    one = bu.mask_logits(proto[0].cuda(), coef[0].cuda())
+    assert_close_f32(host(one), ref[0].numpy(), 1e-5, "single-picture mask logits")
+
+
+def test_tensor_core_sigmoid_maps_on_the_fused_path():
+    """ISB_TC_SMAP=1 swaps K3a (FFMA, footprints only) for the batched tcgen05 product scattering into the same packed
+    footprint maps: the fused path must still reproduce the reference goldens (run in a child process: the switch is read
+    once per process)."""
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, ISB_TC_SMAP="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_yolact_gpu.py"), "-q", "-x", "-m", "gpu", "-k",
+                        "test_full_size_end_to_end or test_batch_equals_single_and_oracle or test_tiny_end_to_end"],
+                       env=env, cwd=root, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]

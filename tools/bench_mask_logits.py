@@ -36,10 +36,17 @@ def main():
     us_blas = timeit(lambda: [p.reshape(-1, 32) @ c.t() for p, c in zip(protos, coefs)])
     pb, cb = torch.stack(protos).reshape(b, -1, 32), torch.stack(coefs).transpose(1, 2).contiguous()
     us_bmm = timeit(lambda: torch.bmm(pb, cb))
+    pstack, cstack = torch.stack(protos), torch.stack(coefs)
+    us_tc_batch = timeit(lambda: bu.mask_logits_batch(pstack, cstack))
+    us_tc_batch_sig = timeit(lambda: bu.mask_logits_batch(pstack, cstack, sigmoid=True))
+    err = float((bu.mask_logits_batch(pstack, cstack).double() - torch.bmm(pb.double(), cb.double()).reshape(b, 138, 138, m)).abs().max())
     out_bytes = b * 138 * 138 * m * 4
     in_bytes = b * (138 * 138 * 32 + m * 32) * 4
     print(json.dumps({"pictures": b, "detections": m, "output_MB": out_bytes / 1e6, "input_MB": in_bytes / 1e6,
                       "isb_mask_logits_tcgen05_us": us_tc, "cublas_sgemm_loop_us": us_blas, "cublas_bmm_us": us_bmm,
+                      "isb_mask_logits_batch_tcgen05_us": us_tc_batch, "isb_mask_logits_batch_sigmoid_us": us_tc_batch_sig,
+                      "batch_max_abs_err_vs_fp64": err,
+                      "batch_out_GBs": out_bytes / us_tc_batch / 1e3,
                       "hbm_floor_us_at_6538GBs": (out_bytes + in_bytes) / 6538.3e3,
                       "note": "K3a (sigmoid maps on the box footprints only) takes ~38 us for the same 64 pictures inside the step"},
                      indent=1))
