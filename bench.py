@@ -317,7 +317,6 @@ def run_gpu(args):
         step()
     torch.cuda.synchronize()
     handle = _lib.get_handle(local_rank)
-    handle.profile_begin(args.steps)
     sampler = ClockSampler("GPU-" + str(torch.cuda.get_device_properties(dev).uuid))
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if world > 1:
@@ -337,6 +336,13 @@ def run_gpu(args):
         dist.barrier()
     launches = handle.launch_count - launches0
     ms = ev0.elapsed_time(ev1)
+    # per-stage device times (the roofline kernel's duration): a second, untimed pass with the library's event ring armed --
+    # profiled calls run the four kernels back to back on one stream (the timed pass above overlaps the two halves' K1 / K2 / K3a)
+    prof_steps = max(5, min(args.steps, 50))
+    handle.profile_begin(prof_steps)
+    for _ in range(prof_steps):
+        bu.decode_nms_batch(dev_in, anchors_d, CONFIDENCE, NMS_IOU, shape, TOP_K, MAX_DET, out=out)
+    torch.cuda.synchronize()
     stage_ms, calls = handle.profile_read()
     handle.profile_begin(0)
     counts = out.counts.cpu().numpy()
@@ -347,6 +353,9 @@ def run_gpu(args):
         assert int(all_offsets[-1]) + int(all_counts[-1]) == int(all_counts.sum())
         if getattr(xchg, "fused", False):
             assert int(xchg.status.item()) == 0, "fused count exchange: a peer's counts did not arrive"
+            ref_counts, ref_offsets = sharding.gather_counts(out.counts, pad_to=bsz)   # outside the timed region: NCCL as the checker
+            assert torch.equal(ref_counts.cpu(), all_counts.cpu()) and torch.equal(ref_offsets.cpu(), all_offsets.cpu()), \
+                "fused count exchange disagrees with the NCCL all-gather"
 
     # ---- end to end through the host-buffer C ABI entry (pinned host memory) -----------------
     import ctypes as C

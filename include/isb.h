@@ -124,7 +124,7 @@ ISB_API int isb_yolact_detect_host(isb_handle* h, const isb_yolact_in* in, const
  * bytes) and expand them into the caller's buffer with non-temporal stores.  Which image goes which way is decided at
  * run time by whichever consumer is free, so the split follows the box (link rate, cores, memory bandwidth).  The
  * caller's contract does not change: every byte of out->masks[b][0 .. H*W*m_b) is written, identical to the device path.
- *   threads < 0: default = CPUs of this process / LOCAL_WORLD_SIZE - 1 (ISB_HOST_THREADS overrides);  0: copy engine only. */
+ *   threads < 0: default = min(8, CPUs of this process / LOCAL_WORLD_SIZE - 1) (ISB_HOST_THREADS overrides);  0: copy engine only. */
 ISB_API int isb_set_host_threads(isb_handle* h, int32_t threads);
 
 /* Counters of the last *_host call: stats[0] images delivered by the copy engine, [1] images expanded by host threads,

@@ -79,6 +79,14 @@ __attribute__((target("avx512f,avx512bw"))) void expand_lines_avx512(const uint6
   _mm_sfence();
 }
 
+// experiment: regular (write-allocate) 64-byte stores instead of non-temporal ones
+__attribute__((target("avx512f,avx512bw"))) void expand_lines_avx512_cached(const uint64_t* src, size_t bit0, uint8_t* dst, size_t n) {
+  const __m512i one = _mm512_set1_epi8(1);
+  for (size_t i = 0; i < n; i += 64)
+    _mm512_store_si512(reinterpret_cast<__m512i*>(dst + i), _mm512_maskz_mov_epi8((__mmask64)bits64(src, bit0 + i), one));
+}
+void expand_lines_dry(const uint64_t*, size_t, uint8_t*, size_t) {}  // experiment: no stores at all
+
 using LinesFn = void (*)(const uint64_t*, size_t, uint8_t*, size_t);
 
 struct Isa {
@@ -92,6 +100,8 @@ Isa pick_isa() {
   const bool a512 = __builtin_cpu_supports("avx512bw") && __builtin_cpu_supports("avx512f");
   const bool a2 = __builtin_cpu_supports("avx2");
   if (force && !strcmp(force, "scalar")) return {expand_lines_scalar, "scalar"};
+  if (force && !strcmp(force, "dry")) return {expand_lines_dry, "dry (experiment: nothing written)"};
+  if (force && !strcmp(force, "cached") && a512) return {expand_lines_avx512_cached, "avx512bw, cached stores (experiment)"};
   if (force && !strcmp(force, "avx2") && a2) return {expand_lines_avx2, "avx2"};
   if (a512) return {expand_lines_avx512, "avx512bw"};
   if (a2) return {expand_lines_avx2, "avx2"};
@@ -206,7 +216,9 @@ int host_default_threads() {
   int ranks = 1;
   if (const char* e = getenv("LOCAL_WORLD_SIZE")) ranks = atoi(e) > 0 ? atoi(e) : 1;
   n = n / ranks - 1;
-  if (n > 32) n = 32;
+  // more workers than ~8 write faster than the host's memory system can absorb next to the upload's DMA reads: measured on
+  // the 16-vCPU B200 box (profiles/r02_host_delivery.json): 22.8 ms per 64 images with 8 workers, 24.9 ms with 15
+  if (n > 8) n = 8;
   return n < 1 ? 1 : n;
 }
 

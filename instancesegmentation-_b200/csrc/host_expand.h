@@ -35,7 +35,8 @@ void host_pool_submit(HostPool* p, ExpandJob* job);
 // Expand on the calling thread (tests, tiny inputs).
 void host_expand_serial(const uint64_t* src, uint8_t* dst, size_t out_bytes);
 // Default worker count: CPUs this process may run on (sched_getaffinity), divided by LOCAL_WORLD_SIZE when a launcher
-// set it (one process per GPU shares the host), minus one for the thread that drives the copies; ISB_HOST_THREADS overrides.
+// set it (one process per GPU shares the host), minus one for the thread that drives the copies, at most 8 (measured optimum);
+// ISB_HOST_THREADS overrides.
 int host_default_threads();
 
 }  // namespace isb

@@ -1,5 +1,6 @@
 // C-ABI entry points of libisb.so (see include/isb.h): argument validation, workspace
 // management and kernel sequencing.  No torch, no exceptions, plain pointers and sizes.
+#include <chrono>
 #include <deque>
 #include <new>
 #include <thread>
@@ -241,33 +242,76 @@ static int check_yolact(isb_handle* h, const isb_yolact_in* in, const YolactOutA
   return ISB_OK;
 }
 
-static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const YolactOutAll* out, cudaStream_t s) {
-  if (!aligned16(in->box) || !aligned16(in->coef) || !aligned16(in->proto) || !aligned16(in->anchors) ||
-      !aligned4(in->conf) || !aligned16(out->boxes) || (!out->map_only && !aligned16(out->masks)))
-    ISB_FAIL(h, ISB_ERR_BAD_ARG, "box/coef/proto/anchors/boxes/masks must be 16-byte aligned, conf 4-byte aligned");
-  int rc;
-  cudaEvent_t* ev = (h->prof_events && h->prof_used < h->prof_cap) ? h->prof_events + (size_t)h->prof_used * 5 : nullptr;
-  if (ev) ISB_CUDA(h, cudaEventRecord(ev[0], s));
+// One image range [b0, b0 + nb) of a call through K1 (score filter), K2 (sort + Fast NMS) and K3a (sigmoid maps) on stream
+// `st`; the workspace is addressed by absolute image index (base + b0).
+struct DetectRange {
+  isb_handle* h;
+  const isb_yolact_in* in;
+  const YolactOutAll* out;
+  int base;          // h->ws_b0 of the call (host pipeline: the sub-batch's first image)
+  bool publish;      // fused count exchange: this call's counts also go to every rank's ring
+  cudaEvent_t* ev;   // profiling events of a sequential call, or nullptr
+};
+
+static MaskParams mask_params(const DetectRange& d, int b0, int nb) {
+  const isb_yolact_in* in = d.in;
+  const YolactOutAll* out = d.out;
+  const size_t HW = (size_t)in->out_h * in->out_w;
+  MaskParams mp;
+  memset(&mp, 0, sizeof(mp));
+  mp.batch = nb;
+  mp.proto = in->proto + (size_t)b0 * in->proto_h * in->proto_w * ISB_NUM_COEF;
+  mp.coef = d.h->det_coef + (size_t)(d.base + b0) * d.h->lim.max_det * ISB_NUM_COEF;
+  mp.counts = out->counts + b0;
+  mp.m_fixed = -1;
+  mp.det_stride = d.h->lim.max_det;
+  mp.m_cap = in->max_det;
+  mp.proto_h = in->proto_h;
+  mp.proto_w = in->proto_w;
+  mp.out_h = in->out_h;
+  mp.out_w = in->out_w;
+  mp.masks_arg = out->masks_arg ? out->masks_arg + (size_t)b0 * HW : nullptr;
+  mp.masks = out->masks ? out->masks + (size_t)b0 * out->mask_slot_bytes : nullptr;
+  mp.mask_slot_bytes = out->mask_slot_bytes;
+  mp.class_map = out->class_map ? out->class_map + (size_t)b0 * HW : nullptr;
+  mp.class_ids = out->class_ids + (size_t)b0 * in->max_det;
+  mp.class_stride = in->max_det;  // fnms_emit wrote the caller's [B, in->max_det] array
+  mp.map_only = out->map_only;
+  mp.packed = out->packed ? out->packed + (size_t)b0 * out->packed_slot_bytes : nullptr;
+  mp.packed_slot_bytes = out->packed_slot_bytes;
+  return mp;
+}
+
+static int detect_k1(const DetectRange& d, int b0, int nb, cudaStream_t st) {
+  isb_handle* h = d.h;
+  const isb_yolact_in* in = d.in;
   CandParams cp;
-  cp.scores = in->conf;
+  cp.scores = in->conf + (size_t)b0 * in->num_anchors * in->num_classes;
   cp.rows = in->num_anchors;
   cp.ncols = in->num_classes;
   cp.col0 = 1;  // utils_bbox.py:193 drops the background column
   cp.use_threshold = 1;
   cp.threshold = in->confidence;
-  cp.batch = in->batch;
+  cp.batch = nb;
   cp.logits = in->conf_is_logits ? 1 : 0;
-  if (cp.logits && !aligned16(in->conf)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "conf must be 16-byte aligned when conf_is_logits is set");
-  if ((rc = launch_candidates(h, cp, s)) != ISB_OK) return rc;
-  if (ev) ISB_CUDA(h, cudaEventRecord(ev[1], s));
+  if (cp.logits && !aligned16(cp.scores)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "conf must be 16-byte aligned when conf_is_logits is set");
+  h->ws_b0 = d.base + b0;
+  const int rc = launch_candidates(h, cp, st);
+  h->ws_b0 = d.base;
+  return rc;
+}
 
+static int detect_k2_k3a(const DetectRange& d, int b0, int nb, cudaStream_t st) {
+  isb_handle* h = d.h;
+  const isb_yolact_in* in = d.in;
+  const YolactOutAll* out = d.out;
   NmsParams np;
   memset(&np, 0, sizeof(np));
-  np.batch = in->batch;
-  np.pred_box = reinterpret_cast<const float4*>(in->box);
+  np.batch = nb;
+  np.pred_box = reinterpret_cast<const float4*>(in->box) + (size_t)b0 * in->num_anchors;
   np.anchors = reinterpret_cast<const float4*>(in->anchors);
   np.boxes = nullptr;
-  np.coef = in->coef;
+  np.coef = in->coef + (size_t)b0 * in->num_anchors * ISB_NUM_COEF;
   np.rows = in->num_anchors;
   np.nms_iou = in->nms_iou;
   np.top_k = in->top_k;
@@ -277,47 +321,60 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const Yo
   np.out_w = in->out_w;
   np.proto_h = in->proto_h;
   np.proto_w = in->proto_w;
-  np.out_box = out->boxes;
-  np.out_score = out->scores;
-  np.out_class = out->class_ids;
+  np.out_box = out->boxes + (size_t)b0 * in->max_det * 4;
+  np.out_score = out->scores + (size_t)b0 * in->max_det;
+  np.out_class = out->class_ids + (size_t)b0 * in->max_det;
   np.out_coef = nullptr;  // coefficients of kept detections go to the workspace
-  np.out_count = out->counts;
-  if (h->cx_attached && in->batch == h->cx_local && h->ws_b0 == 0 && h->ws_images == 0) {  // (not from inside the *_host sub-batch pipeline)
-    // fused count exchange: this call's counts also go to slot (epoch mod depth) of every rank's ring
-    h->cx_epoch += 1;
+  np.out_count = out->counts + b0;
+  if (d.publish) {
     np.n_peers = h->cx_world;
     for (int r = 0; r < h->cx_world; ++r) np.peer_ring[r] = h->cx_peer[r];
-    np.peer_index0 = (int32_t)((h->cx_epoch % (uint32_t)h->cx_depth) * (uint32_t)(h->cx_world * h->cx_local) + h->cx_rank * h->cx_local);
+    np.peer_index0 = (int32_t)((h->cx_epoch % (uint32_t)h->cx_depth) * (uint32_t)(h->cx_world * h->cx_local) + h->cx_rank * h->cx_local + b0);
     np.peer_epoch = h->cx_epoch;
   }
-  if ((rc = launch_fast_nms(h, np, s)) != ISB_OK) return rc;
-  if (ev) ISB_CUDA(h, cudaEventRecord(ev[2], s));
+  h->ws_b0 = d.base + b0;
+  int rc = launch_fast_nms(h, np, st);
+  if (rc == ISB_OK) {
+    if (d.ev) {
+      const cudaError_t e = cudaEventRecord(d.ev[2], st);
+      if (e != cudaSuccess) { h->ws_b0 = d.base; ISB_FAIL(h, ISB_ERR_CUDA, "cudaEventRecord: %s", cudaGetErrorString(e)); }
+    }
+    const MaskParams mp = mask_params(d, b0, nb);
+    rc = launch_masks(h, mp, st, 1);
+  }
+  h->ws_b0 = d.base;
+  return rc;
+}
 
-  MaskParams mp;
-  memset(&mp, 0, sizeof(mp));
-  mp.batch = in->batch;
-  mp.proto = in->proto;
-  mp.coef = h->det_coef + (size_t)h->ws_b0 * h->lim.max_det * ISB_NUM_COEF;
-  mp.counts = out->counts;
-  mp.m_fixed = -1;
-  mp.det_stride = h->lim.max_det;
-  mp.m_cap = in->max_det;
-  mp.proto_h = in->proto_h;
-  mp.proto_w = in->proto_w;
-  mp.out_h = in->out_h;
-  mp.out_w = in->out_w;
-  mp.masks_arg = out->masks_arg;
-  mp.masks = out->masks;
-  mp.mask_slot_bytes = out->mask_slot_bytes;
-  mp.class_map = out->class_map;
-  mp.class_ids = out->class_ids;
-  mp.class_stride = in->max_det;  // fnms_emit wrote the caller's [B, in->max_det] array
-  mp.map_only = out->map_only;
-  mp.packed = out->packed;
-  mp.packed_slot_bytes = out->packed_slot_bytes;
+static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const YolactOutAll* out, cudaStream_t s) {
+  if (!aligned16(in->box) || !aligned16(in->coef) || !aligned16(in->proto) || !aligned16(in->anchors) ||
+      !aligned4(in->conf) || !aligned16(out->boxes) || (!out->map_only && !aligned16(out->masks)))
+    ISB_FAIL(h, ISB_ERR_BAD_ARG, "box/coef/proto/anchors/boxes/masks must be 16-byte aligned, conf 4-byte aligned");
+  int rc;
+  cudaEvent_t* ev = (h->prof_events && h->prof_used < h->prof_cap) ? h->prof_events + (size_t)h->prof_used * 5 : nullptr;
+  DetectRange d;
+  d.h = h; d.in = in; d.out = out; d.base = h->ws_b0; d.ev = ev;
+  d.publish = h->cx_attached && in->batch == h->cx_local && !h->in_host_pipe;
+  if (d.publish) h->cx_epoch += 1;
+  const int B = in->batch;
+  // the sigmoid-map scratch must hold the whole call before any range is launched (no reallocation under running kernels)
+  const int32_t ws_images_saved = h->ws_images;
+  if (h->ws_images < d.base + B) h->ws_images = d.base + B;
+  // The four kernels run back to back on the caller's stream.  (Measured and rejected in round 2: running the first half's
+  // K2 + K3a on a second stream under the second half's K1 -- K2 is latency-bound, ~37 us whatever the image count, so every
+  // extra K2 launch that is not fully hidden costs more than the overlap saves: 0.4765 ms with the two-half overlap against
+  // 0.4669 ms for the plain sequence, profiles/r02_split_overlap.json.)
+  if (ev) ISB_CUDA(h, cudaEventRecord(ev[0], s));
+  rc = detect_k1(d, 0, B, s);
+  if (rc == ISB_OK && ev) ISB_CUDA(h, cudaEventRecord(ev[1], s));
   h->prof_mid = ev ? ev[3] : nullptr;  // recorded between the sigmoid-map and the compose kernel
-  rc = launch_masks(h, mp, s);
+  if (rc == ISB_OK) rc = detect_k2_k3a(d, 0, B, s);
   h->prof_mid = nullptr;
+  if (rc == ISB_OK) {
+    const MaskParams mp = mask_params(d, 0, B);
+    rc = launch_masks(h, mp, s, 2);
+  }
+  h->ws_images = ws_images_saved;
   if (rc != ISB_OK) return rc;
   if (ev) {
     ISB_CUDA(h, cudaEventRecord(ev[4], s));
@@ -363,17 +420,32 @@ extern "C" int isb_yolact_class_map_host(isb_handle* h, const isb_yolact_in* in,
 }
 
 // Host delivery state of the *_host entry points (created on first use, owned by the handle).
+//
+// Streams by ROLE, so that no transfer ever waits behind one of another kind:
+//   up     host -> device only (one stream: two alternating ones were slower): every chunk's inputs, enqueued back to back at call start (the upload never stalls);
+//   comp   kernels only: chunk c waits for upload event c, records kernel event c;
+//   cnt    the counts and per-detection records of a chunk (a few KB): what tells the host which images are ready;
+//   fast   the packed mask bits of the images the host threads take (3.8 MB per image);
+//   dense  bulk device -> host traffic in pieces of kPieceBytes with at most kDensePieces outstanding: the arg-max maps
+//          and the dense masks of the images the copy engine takes -- so the other two streams' copies interleave with it
+//          on the device-to-host link instead of queueing behind 30 MB.
+// Every device-to-host copy is issued by the host only once its source is READY: nothing blocked ever sits in a copy queue.
+// (Round 1 and the first version of this pipeline put a chunk's upload, kernels and downloads on one of three lane
+// streams: the next upload of a lane sat behind that lane's mask downloads, and the small copies shared hardware queues
+// with blocked work -- measured: packed copies issued at 1.7 ms completed at 25.8 ms, chunks 5-7 became ready at 25 ms.)
 struct HostPipe {
-  static constexpr int kDenseSlots = 2;   // dense copies in flight on the copy engine
-  static constexpr int kPackedSlots = 4;  // images being copied as bits / expanded by the worker pool
+  static constexpr int kDensePieces = 2;       // dense pieces in flight
+  static constexpr size_t kPieceBytes = 4u << 20;
+  static constexpr int kPackedSlots = 6;       // images being copied as bits / expanded by the worker pool
   isb::HostPool* pool = nullptr;
   int pool_threads = 0;
   uint8_t* land = nullptr;  // pinned landing buffer of the packed bits
   size_t land_bytes = 0;
-  cudaStream_t dense_stream = nullptr, packed_stream = nullptr;
-  std::vector<cudaEvent_t> chunk_events;
-  cudaEvent_t dense_ev[kDenseSlots] = {};
-  int dense_img[kDenseSlots];
+  cudaStream_t up = nullptr, comp = nullptr, cnt = nullptr, fast = nullptr, dense = nullptr;
+  std::vector<cudaEvent_t> up_ev, k_ev, cnt_ev;  // per chunk: inputs uploaded, kernels done, counts on the host
+  cudaEvent_t piece_ev[kDensePieces] = {};
+  bool piece_busy[kDensePieces] = {};
+  cudaEvent_t join_ev = nullptr;
   struct PackedSlot {
     cudaEvent_t ev = nullptr;
     int img = -1;
@@ -387,11 +459,13 @@ static void destroy_host_pipe(isb_handle* h) {
   if (!hp) return;
   if (hp->pool) isb::host_pool_destroy(hp->pool);
   if (hp->land) cudaFreeHost(hp->land);
-  if (hp->dense_stream) cudaStreamDestroy(hp->dense_stream);
-  if (hp->packed_stream) cudaStreamDestroy(hp->packed_stream);
-  for (cudaEvent_t e : hp->chunk_events) cudaEventDestroy(e);
-  for (int i = 0; i < HostPipe::kDenseSlots; ++i)
-    if (hp->dense_ev[i]) cudaEventDestroy(hp->dense_ev[i]);
+  for (cudaStream_t st : {hp->up, hp->comp, hp->cnt, hp->fast, hp->dense})
+    if (st) cudaStreamDestroy(st);
+  for (auto* v : {&hp->up_ev, &hp->k_ev, &hp->cnt_ev})
+    for (cudaEvent_t e : *v) cudaEventDestroy(e);
+  for (int i = 0; i < HostPipe::kDensePieces; ++i)
+    if (hp->piece_ev[i]) cudaEventDestroy(hp->piece_ev[i]);
+  if (hp->join_ev) cudaEventDestroy(hp->join_ev);
   for (int i = 0; i < HostPipe::kPackedSlots; ++i)
     if (hp->packed[i].ev) cudaEventDestroy(hp->packed[i].ev);
   delete hp;
@@ -417,10 +491,10 @@ static int get_host_pipe(isb_handle* h, int nchunks, size_t land_bytes, HostPipe
     hp = new (std::nothrow) HostPipe();
     if (!hp) ISB_FAIL(h, ISB_ERR_CUDA, "host pipeline: out of host memory");
     h->host_pipe = hp;
-    ISB_CUDA(h, cudaStreamCreateWithFlags(&hp->dense_stream, cudaStreamNonBlocking));
-    ISB_CUDA(h, cudaStreamCreateWithFlags(&hp->packed_stream, cudaStreamNonBlocking));
-    for (int i = 0; i < HostPipe::kDenseSlots; ++i) ISB_CUDA(h, cudaEventCreateWithFlags(&hp->dense_ev[i], cudaEventDisableTiming));
+    for (cudaStream_t* st : {&hp->up, &hp->comp, &hp->cnt, &hp->fast, &hp->dense}) ISB_CUDA(h, cudaStreamCreateWithFlags(st, cudaStreamNonBlocking));
+    for (int i = 0; i < HostPipe::kDensePieces; ++i) ISB_CUDA(h, cudaEventCreateWithFlags(&hp->piece_ev[i], cudaEventDisableTiming));
     for (int i = 0; i < HostPipe::kPackedSlots; ++i) ISB_CUDA(h, cudaEventCreateWithFlags(&hp->packed[i].ev, cudaEventDisableTiming));
+    ISB_CUDA(h, cudaEventCreateWithFlags(&hp->join_ev, cudaEventDisableTiming));
   }
   const int want = h->host_threads < 0 ? isb::host_default_threads() : h->host_threads;
   if (want != hp->pool_threads) {
@@ -428,11 +502,12 @@ static int get_host_pipe(isb_handle* h, int nchunks, size_t land_bytes, HostPipe
     hp->pool = want > 0 ? isb::host_pool_create(want) : nullptr;
     hp->pool_threads = want;
   }
-  while ((int)hp->chunk_events.size() < nchunks) {
-    cudaEvent_t e;
-    ISB_CUDA(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    hp->chunk_events.push_back(e);
-  }
+  for (auto* v : {&hp->up_ev, &hp->k_ev, &hp->cnt_ev})
+    while ((int)v->size() < nchunks) {
+      cudaEvent_t e;
+      ISB_CUDA(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      v->push_back(e);
+    }
   if (hp->pool && land_bytes > hp->land_bytes) {
     if (hp->land) cudaFreeHost(hp->land);
     hp->land = nullptr;
@@ -459,15 +534,16 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
   cudaStream_t s = (cudaStream_t)stream;
   const size_t B = in->batch, A = in->num_anchors, C = in->num_classes, K = ISB_NUM_COEF;
   const size_t HW = (size_t)in->out_h * in->out_w, D = in->max_det;
-  // Sub-batch pipeline over kLanes streams: while chunk c computes and its results travel to the host, chunk c+1 is
-  // already uploading (PCIe is full duplex) -- H2D, kernels and D2H of different chunks overlap.
-  constexpr int kLanes = 3;
-  const int chunk = (int)(B >= 24 ? 8 : (B + kLanes - 1) / kLanes);
+  // sub-batches: small enough that the pipeline fills quickly (the first masks leave after one chunk's upload) and
+  // drains quickly (the last chunk's delivery is all that remains once the upload ends)
+  const int chunk = (int)(B >= 32 ? 4 : (B >= 8 ? 2 : 1));
   const int nchunks = (int)((B + chunk - 1) / chunk);
   // packed transport: one slot per image, 64-byte multiple, 16 bytes of slack for the expansion's look-ahead word
   const size_t pslot = map_only ? 0 : ((4 * ((HW * D + 31) / 32) + 16 + 63) & ~(size_t)63);
   HostPipe* hp = nullptr;
-  if ((rc = get_host_pipe(h, nchunks, B * pslot, &hp)) != ISB_OK) return rc;
+  // the landing buffer has one slot per in-flight packed image (not per image of the batch): a few MB that are written by the
+  // copy engine and read by the worker threads straight away, i.e. out of the last-level cache rather than DRAM
+  if ((rc = get_host_pipe(h, nchunks, (size_t)HostPipe::kPackedSlots * pslot, &hp)) != ISB_OK) return rc;
   const bool use_pool = !map_only && hp->pool != nullptr;
   const size_t n_box = B * A * 4 * 4, n_conf = B * A * C * 4, n_coef = B * A * K * 4,
                n_proto = B * (size_t)in->proto_h * in->proto_w * K * 4, n_anc = A * 4 * 4;
@@ -502,32 +578,34 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
   dout.class_map = map_only ? (uint8_t*)take(o_map) : nullptr;
   dout.packed = use_pool ? (uint8_t*)take(o_pack) : nullptr;
   dout.packed_slot_bytes = (int64_t)pslot;
-  for (int l = 0; l < kLanes; ++l) {
-    if (!h->lane_stream[l]) ISB_CUDA(h, cudaStreamCreateWithFlags(&h->lane_stream[l], cudaStreamNonBlocking));
-    if (!h->lane_event[l]) ISB_CUDA(h, cudaEventCreateWithFlags(&h->lane_event[l], cudaEventDisableTiming));
-  }
   if (!h->fork_event) ISB_CUDA(h, cudaEventCreateWithFlags(&h->fork_event, cudaEventDisableTiming));
   int64_t d2h_bytes = 0, h2d_bytes = 0, n_dense = 0, n_pool = 0;
-  ISB_CUDA(h, cudaMemcpyAsync((void*)din.anchors, in->anchors, n_anc, cudaMemcpyHostToDevice, s));
-  h2d_bytes += (int64_t)n_anc;
   ISB_CUDA(h, cudaEventRecord(h->fork_event, s));
-  for (int l = 0; l < kLanes; ++l) ISB_CUDA(h, cudaStreamWaitEvent(h->lane_stream[l], h->fork_event, 0));
-  ISB_CUDA(h, cudaStreamWaitEvent(hp->dense_stream, h->fork_event, 0));
-  ISB_CUDA(h, cudaStreamWaitEvent(hp->packed_stream, h->fork_event, 0));
+  for (cudaStream_t st : {hp->up, hp->comp, hp->cnt, hp->fast, hp->dense}) ISB_CUDA(h, cudaStreamWaitEvent(st, h->fork_event, 0));
   const size_t slot = (size_t)out->mask_slot_bytes, PP = (size_t)in->proto_h * in->proto_w * K;
-  // ---- 1. enqueue every chunk: inputs up, kernels, counts + per-detection records + arg-max (or class map) down ---------
+  static const bool trace = getenv("ISB_HOST_TRACE") != nullptr;  // per-image delivery timeline on stderr
+  const auto t_call = std::chrono::steady_clock::now();
+  auto now_us = [&]() { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_call).count(); };
+  struct TraceRec { int img; char path; double t_ready, t_issue, t_copied, t_done; };
+  std::vector<TraceRec> tr;
+  if (trace) tr.resize(B, TraceRec{-1, '-', 0, 0, 0, 0});
+  // ---- 1. enqueue every chunk's upload (stream `up`) and kernels (stream `comp`) ------------------------------------
+  ISB_CUDA(h, cudaMemcpyAsync((void*)din.anchors, in->anchors, n_anc, cudaMemcpyHostToDevice, hp->up));
+  h2d_bytes += (int64_t)n_anc;
   rc = ISB_OK;
   h->ws_images = (int32_t)B;  // the per-image workspace is addressed by absolute image index (ws_b0)
+  h->in_host_pipe = 1;
   int issued = 0;
   for (int c = 0; c < nchunks && rc == ISB_OK; ++c) {
-    const int lane = c % kLanes;
-    cudaStream_t st = h->lane_stream[lane];
     const size_t b0 = (size_t)c * chunk, nb = (b0 + chunk < B ? b0 + chunk : B) - b0;
-    ISB_CUDA(h, cudaMemcpyAsync((char*)din.box + b0 * A * 16, (const char*)in->box + b0 * A * 16, nb * A * 16, cudaMemcpyHostToDevice, st));
-    ISB_CUDA(h, cudaMemcpyAsync((char*)din.conf + b0 * A * C * 4, (const char*)in->conf + b0 * A * C * 4, nb * A * C * 4, cudaMemcpyHostToDevice, st));
-    ISB_CUDA(h, cudaMemcpyAsync((char*)din.coef + b0 * A * K * 4, (const char*)in->coef + b0 * A * K * 4, nb * A * K * 4, cudaMemcpyHostToDevice, st));
-    ISB_CUDA(h, cudaMemcpyAsync((char*)din.proto + b0 * PP * 4, (const char*)in->proto + b0 * PP * 4, nb * PP * 4, cudaMemcpyHostToDevice, st));
+    cudaStream_t upc = hp->up;  // (two alternating upload streams were measured: 26.9 ms against 24.2 ms for one)
+    ISB_CUDA(h, cudaMemcpyAsync((char*)din.box + b0 * A * 16, (const char*)in->box + b0 * A * 16, nb * A * 16, cudaMemcpyHostToDevice, upc));
+    ISB_CUDA(h, cudaMemcpyAsync((char*)din.conf + b0 * A * C * 4, (const char*)in->conf + b0 * A * C * 4, nb * A * C * 4, cudaMemcpyHostToDevice, upc));
+    ISB_CUDA(h, cudaMemcpyAsync((char*)din.coef + b0 * A * K * 4, (const char*)in->coef + b0 * A * K * 4, nb * A * K * 4, cudaMemcpyHostToDevice, upc));
+    ISB_CUDA(h, cudaMemcpyAsync((char*)din.proto + b0 * PP * 4, (const char*)in->proto + b0 * PP * 4, nb * PP * 4, cudaMemcpyHostToDevice, upc));
+    ISB_CUDA(h, cudaEventRecord(hp->up_ev[c], upc));
     h2d_bytes += (int64_t)(nb * (A * 16 + A * C * 4 + A * K * 4 + PP * 4));
+    ISB_CUDA(h, cudaStreamWaitEvent(hp->comp, hp->up_ev[c], 0));
     isb_yolact_in cin = din;
     YolactOutAll cout = dout;
     cin.batch = (int32_t)nb;
@@ -544,87 +622,139 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
     cout.class_map = map_only ? dout.class_map + b0 * HW : nullptr;
     cout.packed = use_pool ? dout.packed + b0 * pslot : nullptr;
     h->ws_b0 = (int32_t)b0;
-    h->ws_lane = lane;
-    rc = yolact_detect_device(h, &cin, &cout, st);
+    rc = yolact_detect_device(h, &cin, &cout, hp->comp);
     h->ws_b0 = 0;
-    h->ws_lane = 0;
     if (rc != ISB_OK) break;
-    ISB_CUDA(h, cudaMemcpyAsync(out->counts + b0, cout.counts, nb * 4, cudaMemcpyDeviceToHost, st));
-    ISB_CUDA(h, cudaEventRecord(hp->chunk_events[c], st));
+    ISB_CUDA(h, cudaEventRecord(hp->k_ev[c], hp->comp));
     issued = c + 1;
-    ISB_CUDA(h, cudaMemcpyAsync(out->boxes + b0 * D * 4, cout.boxes, nb * D * 16, cudaMemcpyDeviceToHost, st));
-    ISB_CUDA(h, cudaMemcpyAsync(out->scores + b0 * D, cout.scores, nb * D * 4, cudaMemcpyDeviceToHost, st));
-    ISB_CUDA(h, cudaMemcpyAsync(out->class_ids + b0 * D, cout.class_ids, nb * D * 8, cudaMemcpyDeviceToHost, st));
-    if (map_only)
-      ISB_CUDA(h, cudaMemcpyAsync(out->class_map + b0 * HW, cout.class_map, nb * HW, cudaMemcpyDeviceToHost, st));
-    else
-      ISB_CUDA(h, cudaMemcpyAsync(out->masks_arg + b0 * HW, cout.masks_arg, nb * HW * 8, cudaMemcpyDeviceToHost, st));
-    d2h_bytes += (int64_t)(nb * (4 + D * 28 + (map_only ? HW : HW * 8)));
   }
   h->ws_images = 0;
-  // ---- 2. deliver the masks: two consumers drain the images whose counts have arrived ------------------------------
-  //   copy engine: dense bool [H,W,m] straight into the caller's buffer (newest ready image first);
-  //   host threads: the image's packed bits into the landing buffer, then expanded into the caller's buffer (oldest first).
-  // Whichever has a free slot takes the next image, so the split follows the measured rates of this box.
+  h->in_host_pipe = 0;
+  const double t_enqueued = now_us();
+  // ---- 2. results down, as they become ready.  The host issues every device-to-host copy itself, only once its source
+  // is complete, so the copy queues never hold blocked work:
+  //   kernels of chunk c done  -> counts, records, arg-max (or class map) of the chunk on `fast`;
+  //   counts of chunk c here   -> its images join the ready list, which two consumers drain:
+  //       copy engine: dense bool [H,W,m] in pieces of kPieceBytes on `dense` (newest ready image first);
+  //       host threads: the image's packed bits on `fast` into the landing buffer, then expanded into the caller's
+  //       buffer (oldest ready image first).
+  // Whichever consumer has a free slot takes the next image, so the split follows the measured rates of this box.
   bool overflow = false;
-  if (!map_only && rc == ISB_OK) {
+  if (rc == ISB_OK) {
     std::deque<int> ready;
-    int next_chunk = 0, busy = 0;
-    for (int i = 0; i < HostPipe::kDenseSlots; ++i) hp->dense_img[i] = -1;
+    struct BulkJob { char* dst; const char* src; size_t bytes; };
+    std::deque<BulkJob> bulk;   // arg-max / class maps waiting for the piece-wise copier (taken before any new dense image)
+    int next_k = 0, next_cnt = 0, busy = 0;
+    int cur_img = -1;           // image the copy engine is working through (-2: a bulk job)
+    char* cur_dst = nullptr;
+    const char* cur_src = nullptr;
+    size_t cur_off = 0, cur_bytes = 0;
+    for (int i = 0; i < HostPipe::kDensePieces; ++i) hp->piece_busy[i] = false;
     for (int i = 0; i < HostPipe::kPackedSlots; ++i) { hp->packed[i].state = 0; hp->packed[i].img = -1; }
-    while (rc == ISB_OK && (next_chunk < issued || !ready.empty() || busy > 0)) {
+    static const int env_slots = getenv("ISB_HOST_POOL_SLOTS") ? atoi(getenv("ISB_HOST_POOL_SLOTS")) : 0;  // tuning knob
+    const int pool_slots = env_slots > 0 && env_slots < HostPipe::kPackedSlots ? env_slots : HostPipe::kPackedSlots;
+    auto cuda_fail = [&](const char* what) {
+      snprintf(h->err, sizeof(h->err), "host delivery (%s): %s", what, cudaGetErrorString(cudaGetLastError()));
+      rc = ISB_ERR_CUDA;
+    };
+    std::vector<double> t_up(trace ? issued : 0, 0.0), t_kd(trace ? issued : 0, 0.0), t_cnt(trace ? issued : 0, 0.0);
+    int next_up = 0;
+    while (rc == ISB_OK && (next_cnt < issued || !ready.empty() || !bulk.empty() || cur_img != -1 || busy > 0)) {
       bool progress = false;
-      if (next_chunk < issued) {
-        const int d = event_done(h, hp->chunk_events[next_chunk]);
+      if (trace && next_up < issued && cudaEventQuery(hp->up_ev[next_up]) == cudaSuccess) t_up[next_up++] = now_us();
+      if (next_k < issued) {
+        const int d = event_done(h, hp->k_ev[next_k]);
         if (d < 0) { rc = d; break; }
         if (d) {
-          const size_t b0 = (size_t)next_chunk * chunk, b1 = b0 + chunk < B ? b0 + chunk : B;
+          const size_t b0 = (size_t)next_k * chunk, nb = (b0 + chunk < B ? b0 + chunk : B) - b0;
+          bool ok = cudaMemcpyAsync(out->counts + b0, dout.counts + b0, nb * 4, cudaMemcpyDeviceToHost, hp->cnt) == cudaSuccess;
+          ok = ok && cudaEventRecord(hp->cnt_ev[next_k], hp->cnt) == cudaSuccess;
+          ok = ok && cudaMemcpyAsync(out->boxes + b0 * D * 4, dout.boxes + b0 * D * 4, nb * D * 16, cudaMemcpyDeviceToHost, hp->cnt) == cudaSuccess;
+          ok = ok && cudaMemcpyAsync(out->scores + b0 * D, dout.scores + b0 * D, nb * D * 4, cudaMemcpyDeviceToHost, hp->cnt) == cudaSuccess;
+          ok = ok && cudaMemcpyAsync(out->class_ids + b0 * D, dout.class_ids + b0 * D, nb * D * 8, cudaMemcpyDeviceToHost, hp->cnt) == cudaSuccess;
+          // the chunk's arg-max maps (or class maps) are bulk traffic: queued for the piece-wise copier below
+          if (map_only) bulk.push_back(BulkJob{(char*)(out->class_map + b0 * HW), (const char*)(dout.class_map + b0 * HW), nb * HW});
+          else bulk.push_back(BulkJob{(char*)(out->masks_arg + b0 * HW), (const char*)(dout.masks_arg + b0 * HW), nb * HW * 8});
+          if (!ok) { cuda_fail("result copies"); break; }
+          d2h_bytes += (int64_t)(nb * (4 + D * 28));
+          if (trace) t_kd[next_k] = now_us();
+          ++next_k;
+          progress = true;
+        }
+      }
+      if (next_cnt < next_k) {
+        const int d = event_done(h, hp->cnt_ev[next_cnt]);
+        if (d < 0) { rc = d; break; }
+        if (d) {
+          const size_t b0 = (size_t)next_cnt * chunk, b1 = b0 + chunk < B ? b0 + chunk : B;
           for (size_t b = b0; b < b1; ++b) {
             const int m = out->counts[b];
             if (m < 0) overflow = true;
-            if (m > 0) ready.push_back((int)b);
+            if (m > 0 && !map_only) ready.push_back((int)b);
+            if (trace) { tr[b].img = (int)b; tr[b].t_ready = now_us(); }
           }
-          ++next_chunk;
+          if (trace) t_cnt[next_cnt] = now_us();
+          ++next_cnt;
           progress = true;
         }
       }
-      for (int i = 0; i < HostPipe::kDenseSlots && rc == ISB_OK; ++i) {
-        if (hp->dense_img[i] >= 0) {
-          const int d = event_done(h, hp->dense_ev[i]);
+      // ---- copy engine: dense pieces ---------------------------------------------------------------------------------
+      for (int i = 0; i < HostPipe::kDensePieces && rc == ISB_OK; ++i) {
+        if (hp->piece_busy[i]) {
+          const int d = event_done(h, hp->piece_ev[i]);
           if (d < 0) { rc = d; break; }
-          if (d) { hp->dense_img[i] = -1; --busy; progress = true; }
+          if (d) { hp->piece_busy[i] = false; --busy; progress = true; }
         }
-        if (hp->dense_img[i] < 0 && !ready.empty()) {
-          const int b = ready.back();
-          ready.pop_back();
-          const size_t bytes = HW * (size_t)out->counts[b];
-          const cudaError_t e = cudaMemcpyAsync(out->masks + (size_t)b * slot, dout.masks + (size_t)b * slot, bytes,
-                                                cudaMemcpyDeviceToHost, hp->dense_stream);
-          if (e != cudaSuccess || cudaEventRecord(hp->dense_ev[i], hp->dense_stream) != cudaSuccess) {
-            snprintf(h->err, sizeof(h->err), "host delivery (dense copy): %s", cudaGetErrorString(cudaGetLastError()));
-            rc = ISB_ERR_CUDA;
-            break;
+        if (!hp->piece_busy[i]) {
+          if (cur_img == -1 && !bulk.empty()) {
+            const BulkJob j = bulk.front();
+            bulk.pop_front();
+            cur_img = -2;
+            cur_dst = j.dst; cur_src = j.src; cur_off = 0; cur_bytes = j.bytes;
           }
-          hp->dense_img[i] = b;
-          ++busy; ++n_dense;
-          d2h_bytes += (int64_t)bytes;
-          progress = true;
+          if (cur_img == -1 && !ready.empty()) {
+            cur_img = ready.back();
+            ready.pop_back();
+            cur_dst = (char*)out->masks + (size_t)cur_img * slot;
+            cur_src = (const char*)dout.masks + (size_t)cur_img * slot;
+            cur_off = 0;
+            cur_bytes = HW * (size_t)out->counts[cur_img];
+            ++n_dense;
+            if (trace) { tr[cur_img].path = 'D'; tr[cur_img].t_issue = now_us(); }
+          }
+          if (cur_img != -1) {
+            const size_t nbytes = cur_bytes - cur_off < HostPipe::kPieceBytes ? cur_bytes - cur_off : HostPipe::kPieceBytes;
+            if (cudaMemcpyAsync(cur_dst + cur_off, cur_src + cur_off, nbytes, cudaMemcpyDeviceToHost, hp->dense) != cudaSuccess ||
+                cudaEventRecord(hp->piece_ev[i], hp->dense) != cudaSuccess) { cuda_fail("bulk copy"); break; }
+            hp->piece_busy[i] = true;
+            ++busy;
+            d2h_bytes += (int64_t)nbytes;
+            cur_off += nbytes;
+            if (cur_off >= cur_bytes) {
+              if (trace && cur_img >= 0) tr[cur_img].t_done = now_us();  // (last piece issued)
+              cur_img = -1;
+            }
+            progress = true;
+          }
         }
       }
-      for (int i = 0; use_pool && i < HostPipe::kPackedSlots && rc == ISB_OK; ++i) {
+      // ---- host threads: packed bits, then expansion --------------------------------------------------------------------
+      for (int i = 0; use_pool && i < pool_slots && rc == ISB_OK; ++i) {
         HostPipe::PackedSlot& ps = hp->packed[i];
         if (ps.state == 1) {
           const int d = event_done(h, ps.ev);
           if (d < 0) { rc = d; break; }
           if (d) {
-            ps.job.src = reinterpret_cast<const uint64_t*>(hp->land + (size_t)ps.img * pslot);
+            ps.job.src = reinterpret_cast<const uint64_t*>(hp->land + (size_t)i * pslot);
             ps.job.dst = out->masks + (size_t)ps.img * slot;
             ps.job.out_bytes = HW * (size_t)out->counts[ps.img];
             isb::host_pool_submit(hp->pool, &ps.job);
+            if (trace) tr[ps.img].t_copied = now_us();
             ps.state = 2;
             progress = true;
           }
         } else if (ps.state == 2 && ps.job.done()) {
+          if (trace) tr[ps.img].t_done = now_us();
           ps.state = 0;
           --busy;
           progress = true;
@@ -633,15 +763,11 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
           const int b = ready.front();
           ready.pop_front();
           const size_t bytes = 4 * ((HW * (size_t)out->counts[b] + 31) / 32);
-          const cudaError_t e = cudaMemcpyAsync(hp->land + (size_t)b * pslot, dout.packed + (size_t)b * pslot, bytes,
-                                                cudaMemcpyDeviceToHost, hp->packed_stream);
-          if (e != cudaSuccess || cudaEventRecord(ps.ev, hp->packed_stream) != cudaSuccess) {
-            snprintf(h->err, sizeof(h->err), "host delivery (packed copy): %s", cudaGetErrorString(cudaGetLastError()));
-            rc = ISB_ERR_CUDA;
-            break;
-          }
+          if (cudaMemcpyAsync(hp->land + (size_t)i * pslot, dout.packed + (size_t)b * pslot, bytes, cudaMemcpyDeviceToHost, hp->fast) != cudaSuccess ||
+              cudaEventRecord(ps.ev, hp->fast) != cudaSuccess) { cuda_fail("packed copy"); break; }
           ps.img = b;
           ps.state = 1;
+          if (trace) { tr[b].path = 'P'; tr[b].t_issue = now_us(); }
           ++busy; ++n_pool;
           d2h_bytes += (int64_t)bytes;
           progress = true;
@@ -649,23 +775,29 @@ static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAl
       }
       if (!progress) std::this_thread::yield();
     }
-    // on an error: wait for whatever is still running before the caller's buffers can be released
-    if (rc != ISB_OK) {
-      cudaStreamSynchronize(hp->dense_stream);
-      cudaStreamSynchronize(hp->packed_stream);
+    if (trace)
+      for (int c = 0; c < issued; ++c)
+        fprintf(stderr, "[isb host] chunk %2d uploaded %7.0f kernels done %7.0f counts here %7.0f\n", c, t_up[c], t_kd[c], t_cnt[c]);
+    if (rc != ISB_OK)  // wait for whatever is still running before the caller's buffers can be released
       for (int i = 0; use_pool && i < HostPipe::kPackedSlots; ++i)
         while (hp->packed[i].state == 2 && !hp->packed[i].job.done()) std::this_thread::yield();
+  }
+  // join (also on the error path, so nothing of this call is in flight when we return)
+  for (cudaStream_t st : {hp->up, hp->comp, hp->cnt, hp->fast, hp->dense}) {
+    const cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess && rc == ISB_OK) {
+      snprintf(h->err, sizeof(h->err), "host delivery (join): %s", cudaGetErrorString(e));
+      rc = ISB_ERR_CUDA;
     }
-  } else if (rc == ISB_OK) {
-    // class map: nothing variable-length to deliver; only the overflow flag needs the counts
-    for (int c = 0; c < issued; ++c) ISB_CUDA(h, cudaEventSynchronize(hp->chunk_events[c]));
-    for (size_t b = 0; b < B; ++b) overflow |= out->counts[b] < 0;
   }
-  for (int l = 0; l < kLanes; ++l) {  // join (also on the error path, so the lanes are idle when we return)
-    cudaEventRecord(h->lane_event[l], h->lane_stream[l]);
-    cudaStreamWaitEvent(s, h->lane_event[l], 0);
+  if (trace) {
+    fprintf(stderr, "[isb host] B=%zu chunks=%d enqueued at %.0f us, total %.0f us, dense %lld, pool %lld (threads %d)\n", B, nchunks,
+            t_enqueued, now_us(), (long long)n_dense, (long long)n_pool, use_pool ? hp->pool_threads : 0);
+    for (size_t b = 0; b < tr.size(); ++b)
+      if (tr[b].img >= 0)
+        fprintf(stderr, "[isb host] img %2zu %c ready %7.0f issue %7.0f copied %7.0f done %7.0f\n", b, tr[b].path, tr[b].t_ready,
+                tr[b].t_issue, tr[b].t_copied, tr[b].t_done);
   }
-  ISB_CUDA(h, cudaStreamSynchronize(s));
   h->host_stats[0] = n_dense; h->host_stats[1] = n_pool; h->host_stats[2] = d2h_bytes; h->host_stats[3] = h2d_bytes;
   h->host_stats[4] = use_pool ? hp->pool_threads : 0;
   if (rc != ISB_OK) return rc;

@@ -330,6 +330,7 @@ struct isb_handle {
   // the lane whose work counter / stream the next launches use
   int32_t ws_b0, ws_lane;
   int32_t ws_images;       // images the per-image workspace must hold while a sub-batch pipeline runs (0: the call's batch)
+  int32_t in_host_pipe;    // set while isb_*_host drives sub-batches through the device entry
   cudaStream_t lane_stream[3];
   cudaEvent_t lane_event[3];
   cudaEvent_t fork_event;
@@ -450,7 +451,8 @@ struct MaskParams {
   int64_t packed_slot_bytes; // >= 4 * ceil(H*W*max_det / 32), multiple of 16
   int32_t skip_dense;        // 1 with `packed`: the dense masks are not written (masks may be nullptr); masks_arg still is
 };
-int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s);
+// which: bit 0 = sigmoid maps (K3a), bit 1 = compose (K3b); the two may be launched for different image ranges / streams
+int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s, int which = 3);
 // grows the sigmoid-map scratch for `images` images of at most m_cap detections; returns floats per image in *s_cap
 int ensure_mask_scratch(isb_handle* h, int proto_h, int proto_w, int m_cap, int64_t images, int64_t* s_cap);
 

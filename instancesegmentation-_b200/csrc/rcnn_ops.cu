@@ -1,5 +1,7 @@
 // Mask R-CNN element-wise / gather kernels: BoxCoder.decode_single, maskrcnn_inference,
 // resize_boxes, paste_masks_in_image and (Multi-scale) RoIAlign.
+#include <stdlib.h>
+
 #include "isb_common.cuh"
 
 namespace isb {
@@ -549,8 +551,29 @@ constexpr int kRoiRowWarps = kRoiRowThreads / 32;
 
 struct RowSample { int lo, hi; float h, l; };  // feature-row OFFSETS (row * fw) of a y sample's two taps and their weights
 
+// x phase of one output row: lane = x sample; its two taps of T come from the lanes that own those columns
 template <int SR>
-__global__ void __launch_bounds__(kRoiRowThreads) ms_roi_align_rows_kernel(RoiLevels L, const float4* __restrict__ boxes,
+__device__ __forceinline__ float roi_row_x_phase(float t0, float t1, bool wide, int plo, int phi, float hx, float lx, int sr) {
+  float vlo = __shfl_sync(0xffffffffu, t0, plo & 31), vhi = __shfl_sync(0xffffffffu, t0, phi & 31);
+  if (wide) {
+    const float wlo = __shfl_sync(0xffffffffu, t1, plo & 31), whi = __shfl_sync(0xffffffffu, t1, phi & 31);
+    if (plo >= 32) vlo = wlo;
+    if (phi >= 32) vhi = whi;
+  }
+  float v = fmaf(hx, vlo, lx * vhi);
+  if (SR == 2) {
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+  } else {
+    const float own = v;
+    for (int k = 1; k < sr; ++k) v += __shfl_down_sync(0xffffffffu, own, k);
+  }
+  return v;
+}
+
+// OH > 0 (with SR > 0): output height known at compile time -- all 2 * OH * SR row loads of a channel are issued before
+// anything depends on them (one memory round trip per channel instead of one per output row).
+template <int SR, int OH>
+__global__ void __launch_bounds__(kRoiRowThreads, 2) ms_roi_align_rows_kernel(RoiLevels L, const float4* __restrict__ boxes,
                                                                         const int32_t* __restrict__ batch_idx, int channels,
                                                                         int oh, int ow, int sr_rt, int cpc,
                                                                         float* __restrict__ out) {
@@ -625,8 +648,9 @@ __global__ void __launch_bounds__(kRoiRowThreads) ms_roi_align_rows_kernel(RoiLe
   __syncthreads();
   const int nxl = s_nx;
   // lane as a feature column (two registers cover up to 64 distinct columns)
-  const int col0 = lane < nxl ? s_xlist[lane] : 0;
-  const int col1 = lane + 32 < nxl ? s_xlist[lane + 32] : 0;
+  // lanes past the last distinct column repeat it (a load of column 0 would pull an unrelated sector into every request)
+  const int col0 = nxl > 0 ? s_xlist[min(lane, nxl - 1)] : 0;
+  const int col1 = nxl > 32 ? s_xlist[min(lane + 32, nxl - 1)] : col0;
   const bool wide = nxl > 32;
   // lane as an x sample
   const int xp = s_xpos[lane];
@@ -646,6 +670,76 @@ __global__ void __launch_bounds__(kRoiRowThreads) ms_roi_align_rows_kernel(RoiLe
   for (int c = cbase + warp; c < cend; c += kRoiRowWarps) {
     const float* pl = fbase + (size_t)c * fhw;
     float* oc = obase + (size_t)c * bins;
+    if constexpr (OH > 0 && SR > 0) {
+      // output rows in chunks of CH, TWO channels per pass: 4 * CH * SR independent row loads in flight per lane (the
+      // kernel is bound by memory latency x sequential passes per warp, not by bytes: more loads per pass, fewer passes),
+      // then the chunk's y blend and x phase.  The chunk loop is not unrolled, so a 14-row pooler needs no more registers
+      // than a 7-row one; the sample table is re-read from shared memory (broadcast) instead of living in registers.
+      constexpr int CH = OH % 7 == 0 ? 7 : OH;
+      constexpr int NYC = CH * SR;
+      const bool two = c + kRoiRowWarps < cend;            // second channel of the pass (warp-uniform)
+      const float* pl2 = two ? pl + (size_t)kRoiRowWarps * fhw : pl;
+#pragma unroll 1
+      for (int ph0 = 0; ph0 < OH; ph0 += CH) {
+        const RowSample* sy = s_y + ph0 * SR;
+#pragma unroll 1
+        for (int half = 0; half < (wide ? 2 : 1); ++half) {
+          const int col = half ? col1 : col0;
+          float va[2 * NYC], vb[2 * NYC];
+#pragma unroll
+          for (int q = 0; q < NYC; ++q) {
+            const int lo = sy[q].lo + col, hi = sy[q].hi + col;
+            va[2 * q] = __ldg(pl + lo);
+            va[2 * q + 1] = __ldg(pl + hi);
+            vb[2 * q] = __ldg(pl2 + lo);
+            vb[2 * q + 1] = __ldg(pl2 + hi);
+          }
+          // y blend; with `wide` the x phase needs both column halves of a row: the first half's rows are parked in
+          // shared-memory-free fashion by running the x phase per half and adding (the x weights select by position)
+#pragma unroll
+          for (int ph = 0; ph < CH; ++ph) {
+            float ta = 0.0f, tb = 0.0f;
+#pragma unroll
+            for (int iy = 0; iy < SR; ++iy) {
+              const float wh = sy[ph * SR + iy].h, wl = sy[ph * SR + iy].l;
+              ta = fmaf(wh, va[2 * (ph * SR + iy)], ta);
+              ta = fmaf(wl, va[2 * (ph * SR + iy) + 1], ta);
+              tb = fmaf(wh, vb[2 * (ph * SR + iy)], tb);
+              tb = fmaf(wl, vb[2 * (ph * SR + iy) + 1], tb);
+            }
+            // x phase restricted to the taps that live in this column half
+            const bool lo_here = (plo >= 32) == (half == 1), hi_here = (phi >= 32) == (half == 1);
+            const float alo = __shfl_sync(0xffffffffu, ta, plo & 31), ahi = __shfl_sync(0xffffffffu, ta, phi & 31);
+            const float blo = __shfl_sync(0xffffffffu, tb, plo & 31), bhi = __shfl_sync(0xffffffffu, tb, phi & 31);
+            float xa = (lo_here ? hx * alo : 0.0f) + (hi_here ? lx * ahi : 0.0f);
+            float xb = (lo_here ? hx * blo : 0.0f) + (hi_here ? lx * bhi : 0.0f);
+            if (SR == 2) {
+              xa += __shfl_xor_sync(0xffffffffu, xa, 1);
+              xb += __shfl_xor_sync(0xffffffffu, xb, 1);
+            } else {
+              const float oa = xa, ob = xb;
+              for (int k = 1; k < sr; ++k) {
+                xa += __shfl_down_sync(0xffffffffu, oa, k);
+                xb += __shfl_down_sync(0xffffffffu, ob, k);
+              }
+            }
+            if (bin_lane) {
+              float* o1 = oc + (ph0 + ph) * ow + my_pw;
+              float* o2 = o1 + (size_t)kRoiRowWarps * bins;
+              if (half == 0) {
+                *o1 = xa * inv_count;
+                if (two) *o2 = xb * inv_count;
+              } else {  // second column half of a wide RoI: add to what the first half stored
+                *o1 += xa * inv_count;
+                if (two) *o2 += xb * inv_count;
+              }
+            }
+          }
+        }
+      }
+      c += kRoiRowWarps;  // the pass covered channels c and c + kRoiRowWarps
+      continue;
+    }
 #pragma unroll 2
     for (int ph = 0; ph < oh; ++ph) {
       float t0 = 0.0f, t1 = 0.0f;
@@ -672,20 +766,7 @@ __global__ void __launch_bounds__(kRoiRowThreads) ms_roi_align_rows_kernel(RoiLe
           }
         }
       }
-      // roles switch: lane = x sample; its two taps of T come from the lanes that own those columns
-      float vlo = __shfl_sync(0xffffffffu, t0, plo & 31), vhi = __shfl_sync(0xffffffffu, t0, phi & 31);
-      if (wide) {
-        const float wlo = __shfl_sync(0xffffffffu, t1, plo & 31), whi = __shfl_sync(0xffffffffu, t1, phi & 31);
-        if (plo >= 32) vlo = wlo;
-        if (phi >= 32) vhi = whi;
-      }
-      float v = fmaf(hx, vlo, lx * vhi);
-      if (SR == 2) {
-        v += __shfl_xor_sync(0xffffffffu, v, 1);
-      } else {
-        const float own = v;
-        for (int k = 1; k < sr; ++k) v += __shfl_down_sync(0xffffffffu, own, k);
-      }
+      const float v = roi_row_x_phase<SR>(t0, t1, wide, plo, phi, hx, lx, sr);
       if (bin_lane) oc[ph * ow + my_pw] = v * inv_count;
     }
   }
@@ -793,21 +874,25 @@ int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, c
     ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
     h->roi_configured = 1;
   }
-  if (oh * sr <= 32 && ow * sr <= 32) {
+  static const bool force_staged = getenv("ISB_ROI_STAGED") != nullptr;  // A/B switch: the round-1 staged kernel
+  if (oh * sr <= 32 && ow * sr <= 32 && !force_staged) {
     // register / shuffle kernel: a CTA = (RoI, group of channels), a warp walks the group's channels.  Enough CTAs for
     // ~2 waves of 8 resident CTAs per SM; at least one channel per warp and pass.
     int groups = (16 * h->num_sms + num_rois - 1) / num_rois;
     if (groups > (channels + kRoiRowWarps - 1) / kRoiRowWarps) groups = (channels + kRoiRowWarps - 1) / kRoiRowWarps;
     if (groups < 1) groups = 1;
     int cpc = (channels + groups - 1) / groups;
-    cpc = (cpc + kRoiRowWarps - 1) / kRoiRowWarps * kRoiRowWarps;
+    cpc = (cpc + 2 * kRoiRowWarps - 1) / (2 * kRoiRowWarps) * (2 * kRoiRowWarps);  // a warp takes channels in pairs
     groups = (channels + cpc - 1) / cpc;
-    if (sr == 2)
-      ms_roi_align_rows_kernel<2><<<dim3(num_rois, groups), kRoiRowThreads, 0, s>>>(
-          L, reinterpret_cast<const float4*>(boxes), batch_idx, channels, oh, ow, sr, cpc, out);
+    const float4* b4 = reinterpret_cast<const float4*>(boxes);
+    if (sr == 2 && oh == 7)        // box head pooler (faster_rcnn_framework.py:326)
+      ms_roi_align_rows_kernel<2, 7><<<dim3(num_rois, groups), kRoiRowThreads, 0, s>>>(L, b4, batch_idx, channels, oh, ow, sr, cpc, out);
+    else if (sr == 2 && oh == 14)  // mask head pooler (mask_rcnn.py:150)
+      ms_roi_align_rows_kernel<2, 14><<<dim3(num_rois, groups), kRoiRowThreads, 0, s>>>(L, b4, batch_idx, channels, oh, ow, sr, cpc, out);
+    else if (sr == 2)
+      ms_roi_align_rows_kernel<2, 0><<<dim3(num_rois, groups), kRoiRowThreads, 0, s>>>(L, b4, batch_idx, channels, oh, ow, sr, cpc, out);
     else
-      ms_roi_align_rows_kernel<0><<<dim3(num_rois, groups), kRoiRowThreads, 0, s>>>(
-          L, reinterpret_cast<const float4*>(boxes), batch_idx, channels, oh, ow, sr, cpc, out);
+      ms_roi_align_rows_kernel<0, 0><<<dim3(num_rois, groups), kRoiRowThreads, 0, s>>>(L, b4, batch_idx, channels, oh, ow, sr, cpc, out);
     ISB_LAUNCH_CHECK(h, "ms_roi_align_rows_kernel");
     return ISB_OK;
   }

@@ -418,7 +418,7 @@ int ensure_mask_scratch(isb_handle* h, int proto_h, int proto_w, int m_cap, int6
   return ensure_smap(h, (size_t)images * (size_t)*s_cap);
 }
 
-int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
+int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s, int which) {
   if (p.proto_w >= 32768 || p.proto_h >= 32768) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports prototype sides < 32768");
   if ((int64_t)p.out_h * p.out_w >= (1ll << 31) / 8) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly: output image too large");
   if (p.det_stride > h->lim.max_det) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly: %d detections > max_det %d", p.det_stride, h->lim.max_det);
@@ -448,7 +448,9 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
   if (p.batch > kSmapMaxBatch) ISB_FAIL(h, ISB_ERR_LIMIT, "mask assembly supports at most %d images per call", kSmapMaxBatch);
   int* counters = h->work_counter + h->ws_lane;
   static const bool tc_smap = getenv("ISB_TC_SMAP") != nullptr;  // tensor-core product instead of K3a (measurement switch)
-  if (tc_smap && g.list_cap <= kTcBatchMaxDet) {
+  if (!(which & 1)) {
+    // compose only: the sigmoid maps were launched separately
+  } else if (tc_smap && g.list_cap <= kTcBatchMaxDet) {
     reset_counters_kernel<<<1, 32, 0, s>>>(counters);
     ISB_LAUNCH_CHECK(h, "reset_counters_kernel");
     TcBatchArgs a;
@@ -463,6 +465,7 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s) {
     ISB_LAUNCH_CHECK(h, "sigmoid_map_kernel");
   }
   if (h->prof_mid) ISB_CUDA(h, cudaEventRecord(h->prof_mid, s));
+  if (!(which & 2)) return ISB_OK;
   // one compose launch per output format: class map only | dense bytes | packed bits (dense + packed when both are asked for)
   const int modes[2] = {p.map_only ? kCompMap : ((p.packed && p.skip_dense) ? kCompPacked : kCompDense),
                         (!p.map_only && p.packed && !p.skip_dense) ? kCompPacked : -1};

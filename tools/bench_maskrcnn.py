@@ -39,6 +39,7 @@ def main():
     res["rpn_filter_268569_to_1000"] = {"us": us}
     feats = OrderedDict((str(i), f.to(dev)) for i, f in enumerate(synth.fpn_features(4201, 256)))
     rois = synth.roi_boxes(4202, 1000).to(dev)
+    res["roi_kernel"] = "staged (round 1, ISB_ROI_STAGED)" if os.environ.get("ISB_ROI_STAGED") else "register / shuffle rows kernel"
     p7, p14 = R.MultiScaleRoIAlign(["0", "1", "2", "3"], 7, 2), R.MultiScaleRoIAlign(["0", "1", "2", "3"], 14, 2)
     us = timeit(lambda: p7(feats, [rois], [(800, 1333)]))
     res["ms_roi_align_7x7_x1000"] = {"us": us, "out_GBs": 1000 * 256 * 49 * 4 / us / 1e3}
