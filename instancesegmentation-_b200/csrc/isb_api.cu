@@ -49,7 +49,7 @@ static void free_profile(isb_handle* h) {
 extern "C" int isb_profile_begin(isb_handle* h, int32_t max_calls) {
   if (!h) return ISB_ERR_BAD_ARG;
   if (max_calls < 0 || max_calls > (1 << 16)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "profile_begin: bad max_calls");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   free_profile(h);
   if (max_calls == 0) return ISB_OK;
   h->prof_events = new (std::nothrow) cudaEvent_t[(size_t)max_calls * 5];
@@ -65,7 +65,7 @@ extern "C" int isb_profile_read(isb_handle* h, double stage_ms[4], int32_t* call
   stage_ms[0] = stage_ms[1] = stage_ms[2] = stage_ms[3] = 0.0;
   *calls = h->prof_used;
   if (h->prof_used == 0) return ISB_OK;
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   ISB_CUDA(h, cudaEventSynchronize(h->prof_events[(size_t)(h->prof_used - 1) * 5 + 4]));
   for (int c = 0; c < h->prof_used; ++c)
     for (int st = 0; st < 4; ++st) {
@@ -117,7 +117,8 @@ static void free_ws(isb_handle* h) {
 
 extern "C" void isb_destroy(isb_handle* h) {
   if (!h) return;
-  cudaSetDevice(h->device);
+  IsbDeviceGuard guard;
+  guard.set(h->device);
   destroy_preprocess(h);
   free_ws(h);
   delete h;
@@ -147,7 +148,8 @@ extern "C" int isb_create(int device, const isb_limits* limits, isb_handle** out
   if (L.cand_capacity > (1ll << 30)) ISB_FAIL(h, ISB_ERR_LIMIT, "cand_capacity too large");
   h->lim = L;
   h->cand_cap_pow2 = next_pow2((int)L.cand_capacity) < 64 ? 64 : next_pow2((int)L.cand_capacity);
-  ISB_CUDA(h, cudaSetDevice(device));
+  IsbDeviceGuard guard;
+  ISB_CUDA(h, guard.set(device));
   cudaDeviceProp prop;
   ISB_CUDA(h, cudaGetDeviceProperties(&prop, device));
   if (prop.major != 10) ISB_FAIL(h, ISB_ERR_CUDA, "libisb is built for sm_100a only; device %d is sm_%d%d", device, prop.major, prop.minor);
@@ -387,7 +389,7 @@ extern "C" int isb_yolact_detect(isb_handle* h, const isb_yolact_in* in, const i
   const YolactOutAll all = widen(out);
   int rc = check_yolact(h, in, &all, out != nullptr);
   if (rc != ISB_OK) return rc;
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return yolact_detect_device(h, in, &all, (cudaStream_t)stream);
 }
 
@@ -395,7 +397,7 @@ extern "C" int isb_yolact_class_map(isb_handle* h, const isb_yolact_in* in, cons
   const YolactOutAll all = widen(out);
   int rc = check_yolact(h, in, &all, out != nullptr);
   if (rc != ISB_OK) return rc;
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return yolact_detect_device(h, in, &all, (cudaStream_t)stream);
 }
 
@@ -530,7 +532,7 @@ static int event_done(isb_handle* h, cudaEvent_t e) {
 static int yolact_host(isb_handle* h, const isb_yolact_in* in, const YolactOutAll* out, isb_stream stream) {
   int rc;
   const bool map_only = out->map_only != 0;
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
   const size_t B = in->batch, A = in->num_anchors, C = in->num_classes, K = ISB_NUM_COEF;
   const size_t HW = (size_t)in->out_h * in->out_w, D = in->max_det;
@@ -824,7 +826,7 @@ extern "C" int isb_counts_export(isb_handle* h, int32_t n_local, int32_t world, 
   if (!handle_out || n_local <= 0 || world < 1 || world > 8 || depth < 2 || depth > 64)
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "counts_export: need n_local > 0, 1 <= world <= 8, 2 <= depth <= 64");
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handles are 64 bytes");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   ISB_CUDA(h, cudaDeviceSynchronize());
   cx_release(h);
   const size_t words = (size_t)depth * world * n_local;
@@ -846,7 +848,7 @@ extern "C" int isb_counts_attach(isb_handle* h, int32_t rank, const unsigned cha
   if (!h) return ISB_ERR_BAD_ARG;
   if (!h->cx_ring) ISB_FAIL(h, ISB_ERR_BAD_ARG, "counts_attach: call isb_counts_export first");
   if (!handles || rank < 0 || rank >= h->cx_world) ISB_FAIL(h, ISB_ERR_BAD_ARG, "counts_attach: bad rank or null handles");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   h->cx_rank = rank;
   for (int r = 0; r < h->cx_world; ++r) {
     if (r == rank) { h->cx_peer[r] = h->cx_ring; continue; }
@@ -867,7 +869,7 @@ extern "C" int isb_counts_attach(isb_handle* h, int32_t rank, const unsigned cha
 
 extern "C" int isb_counts_detach(isb_handle* h) {
   if (!h) return ISB_ERR_BAD_ARG;
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   ISB_CUDA(h, cudaDeviceSynchronize());
   cx_release(h);
   return ISB_OK;
@@ -883,7 +885,7 @@ extern "C" int isb_counts_wait(isb_handle* h, int64_t epoch, int32_t* counts, in
   if (epoch < 0) epoch = h->cx_epoch;
   if (epoch == 0 || epoch > (int64_t)h->cx_epoch) ISB_FAIL(h, ISB_ERR_BAD_ARG, "counts_wait: epoch %lld has not been published by this rank", (long long)epoch);
   if ((int64_t)h->cx_epoch - epoch >= h->cx_depth) ISB_FAIL(h, ISB_ERR_LIMIT, "counts_wait: epoch %lld left the ring (depth %d)", (long long)epoch, h->cx_depth);
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   const int n = h->cx_world * h->cx_local;
   const unsigned long long* slot = h->cx_ring + (size_t)((uint32_t)epoch % (uint32_t)h->cx_depth) * n;
   if (timeout_ms <= 0) timeout_ms = 2000;
@@ -898,7 +900,7 @@ extern "C" int isb_decode_boxes(isb_handle* h, const float* pred, const float* a
   if (n < 0 || !out || (n > 0 && (!pred || !anchors))) ISB_FAIL(h, ISB_ERR_BAD_ARG, "decode_boxes: bad argument");
   if (!aligned16(pred) || !aligned16(anchors) || !aligned16(out)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "decode_boxes: pointers must be 16-byte aligned");
   if (n == 0) return ISB_OK;
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return launch_decode_boxes(h, pred, anchors, n, var0, var1, out, (cudaStream_t)stream);
 }
 
@@ -908,7 +910,7 @@ extern "C" int isb_jaccard(isb_handle* h, const float* a, const float* b, int32_
   if (batch < 0 || na < 0 || nb < 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "jaccard: negative size");
   if ((int64_t)batch * na * nb == 0) return ISB_OK;
   if (!a || !b || !out || !aligned16(a) || !aligned16(b)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "jaccard: null or misaligned pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return launch_jaccard(h, a, b, batch, na, nb, iscrowd, out, (cudaStream_t)stream);
 }
 
@@ -920,7 +922,7 @@ extern "C" int isb_fast_nms(isb_handle* h, const float* box, const float* scores
   if (!count || !out_box || !out_score || !out_class || !out_coef) ISB_FAIL(h, ISB_ERR_BAD_ARG, "fast_nms: null output");
   if (n < 0 || num_fg_classes <= 0 || top_k <= 0 || max_det <= 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "fast_nms: bad size");
   if (num_coef != ISB_NUM_COEF) ISB_FAIL(h, ISB_ERR_BAD_ARG, "fast_nms: num_coef must be %d", ISB_NUM_COEF);
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
   if (n == 0) {
     ISB_CUDA(h, cudaMemsetAsync(count, 0, sizeof(int32_t), s));
@@ -975,7 +977,7 @@ extern "C" int isb_traditional_nms(isb_handle* h, const float* box, const float*
   if (num_coef != ISB_NUM_COEF) ISB_FAIL(h, ISB_ERR_BAD_ARG, "traditional_nms: num_coef must be %d", ISB_NUM_COEF);
   if (num_fg_classes >= (1 << kClassBits)) ISB_FAIL(h, ISB_ERR_LIMIT, "traditional_nms: classes %d >= 2^%d", num_fg_classes, kClassBits);
   if (n >= (1 << kRowBits)) ISB_FAIL(h, ISB_ERR_LIMIT, "traditional_nms: n %d >= 2^%d", n, kRowBits);
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
   if (n == 0) {
     ISB_CUDA(h, cudaMemsetAsync(count, 0, sizeof(int32_t), s));
@@ -1012,7 +1014,7 @@ extern "C" int isb_correct_boxes(isb_handle* h, const float* boxes, int64_t m, i
   if (m < 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "correct_boxes: negative m");
   if (m == 0) return ISB_OK;
   if (!boxes || !out || !aligned16(boxes) || !aligned16(out)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "correct_boxes: null or misaligned pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return launch_correct_boxes(h, boxes, m, out_h, out_w, out, (cudaStream_t)stream);
 }
 
@@ -1022,7 +1024,7 @@ extern "C" int isb_crop(isb_handle* h, const float* masks, const float* boxes, i
   if (hgt < 0 || wid < 0 || m < 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "crop: negative size");
   if ((int64_t)hgt * wid * m == 0) return ISB_OK;
   if (!masks || !boxes || !out || !aligned16(boxes)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "crop: null or misaligned pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return launch_crop(h, masks, boxes, hgt, wid, m, out, (cudaStream_t)stream);
 }
 
@@ -1032,7 +1034,7 @@ extern "C" int isb_mask_logits(isb_handle* h, const float* proto, const float* c
   if (proto_h < 0 || proto_w < 0 || m < 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_logits: negative size");
   if ((int64_t)proto_h * proto_w * m == 0) return ISB_OK;
   if (!proto || !coef || !out || !aligned16(proto) || !aligned16(coef)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_logits: null or misaligned pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return launch_mask_logits_tc(h, proto, coef, (int64_t)proto_h * proto_w, m, out, (cudaStream_t)stream);
 }
 
@@ -1045,7 +1047,7 @@ extern "C" int isb_mask_logits_batch(isb_handle* h, const float* proto, const fl
   if ((int64_t)proto_h * proto_w >= (1ll << 31)) ISB_FAIL(h, ISB_ERR_LIMIT, "mask_logits_batch: prototype map too large");
   if (!proto || !coef || !out || !aligned16(proto) || !aligned16(coef) || !aligned16(out))
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_logits_batch: null or misaligned pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   TcBatchArgs a;
   memset(&a, 0, sizeof(a));
   a.proto = proto; a.coef = coef; a.coef_rows = m; a.counts = nullptr; a.m_fixed = m; a.batch = batch;
@@ -1063,7 +1065,7 @@ extern "C" int isb_mask_assemble(isb_handle* h, const float* proto, const float*
   if (!proto || !coef || !boxes_px || !masks_arg || !masks || !aligned16(proto) || !aligned16(coef) ||
       !aligned16(boxes_px) || !aligned16(masks))
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_assemble: null or misaligned pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
   int rc = launch_det_layout(h, boxes_px, m, out_h, out_w, proto_h, proto_w, h->det_rec, h->smap_total, s);
   if (rc != ISB_OK) return rc;

@@ -12,7 +12,7 @@ extern "C" int isb_box_decode(isb_handle* h, const float* rel_codes, const float
   if (n == 0) return ISB_OK;
   if (!rel_codes || !boxes || !out || !al16(rel_codes) || !al16(boxes) || !al16(out))
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "box_decode: null or misaligned pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   const float w[4] = {wx, wy, ww, wh};
   return launch_box_decode(h, rel_codes, boxes, n, k, w, clip, out, (cudaStream_t)stream);
 }
@@ -21,7 +21,7 @@ static int nms_common(isb_handle* h, const float* boxes, const float* scores, co
                       double thr, int64_t* keep, int32_t* count, isb_stream stream, const char* what) {
   if (!h) return ISB_ERR_BAD_ARG;
   if (n < 0 || !count) ISB_FAIL(h, ISB_ERR_BAD_ARG, "%s: bad size or null count", what);
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
   if (n == 0) {  // boxes.py:66-67: empty input -> empty int64 result
     ISB_CUDA(h, cudaMemsetAsync(count, 0, sizeof(int32_t), s));
@@ -78,7 +78,7 @@ extern "C" int isb_ms_roi_align(isb_handle* h, const isb_roi_align_cfg* cfg, con
   L.canonical_scale = (float)cfg->canonical_scale;
   L.canonical_level = (float)cfg->canonical_level;
   L.eps = 1e-6f;
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return launch_ms_roi_align(h, L, boxes, batch_idx, num_rois, cfg->channels, cfg->out_h, cfg->out_w, cfg->sampling_ratio,
                              out, (cudaStream_t)stream);
 }
@@ -89,7 +89,7 @@ extern "C" int isb_mask_select_sigmoid(isb_handle* h, const float* logits, const
   if (m < 0 || num_classes <= 0 || mask_size <= 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_select_sigmoid: bad size");
   if (m == 0) return ISB_OK;
   if (!logits || !labels || !out) ISB_FAIL(h, ISB_ERR_BAD_ARG, "mask_select_sigmoid: null pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return launch_mask_select_sigmoid(h, logits, labels, m, num_classes, mask_size * mask_size, out, (cudaStream_t)stream);
 }
 
@@ -99,7 +99,7 @@ extern "C" int isb_resize_boxes(isb_handle* h, const float* boxes, int64_t m, in
   if (m < 0 || orig_h <= 0 || orig_w <= 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "resize_boxes: bad size");
   if (m == 0) return ISB_OK;
   if (!boxes || !out || !al16(boxes) || !al16(out)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "resize_boxes: null or misaligned pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   // transform.py:471-475: float32(new) / float32(orig) per axis
   const float rh = (float)new_h / (float)orig_h, rw = (float)new_w / (float)orig_w;
   return launch_resize_boxes(h, boxes, m, rw, rh, out, (cudaStream_t)stream);
@@ -111,7 +111,7 @@ extern "C" int isb_paste_masks(isb_handle* h, const float* masks, const float* b
   if (m < 0 || mask_size <= 0 || padding < 0 || im_h <= 0 || im_w <= 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "paste_masks: bad size");
   if (m == 0) return ISB_OK;
   if (!masks || !boxes || !out || !al16(boxes) || !al16(out)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "paste_masks: null or misaligned pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return launch_paste_masks(h, masks, boxes, m, mask_size, padding, im_h, im_w, out, (cudaStream_t)stream);
 }
 
@@ -132,7 +132,7 @@ extern "C" int isb_paste_class_map(isb_handle* h, const float* masks, const floa
   if (!class_map) ISB_FAIL(h, ISB_ERR_BAD_ARG, "paste_class_map: null class_map");
   if (m > 0 && (!masks || !boxes || !labels || !scores || !al16(boxes)))
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "paste_class_map: null or misaligned pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return isb::launch_paste_class_map(h, masks, boxes, labels, scores, m, mask_size, padding, paste_h, paste_w, out_h, out_w,
                                      confidence, class_map, masks_arg, kept_count, (cudaStream_t)stream);
 }
@@ -150,6 +150,6 @@ extern "C" int isb_rcnn_transform(isb_handle* h, const float* image, int32_t in_
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "rcnn_transform: bad size (the canvas must hold the resized image)");
   if (canvas_h > 65535) ISB_FAIL(h, ISB_ERR_LIMIT, "rcnn_transform: canvas higher than 65535 rows");
   if (!image || !mean || !std || !canvas) ISB_FAIL(h, ISB_ERR_BAD_ARG, "rcnn_transform: null pointer");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return isb::launch_rcnn_transform(h, image, in_h, in_w, out_h, out_w, mean, std, canvas, canvas_h, canvas_w, (cudaStream_t)stream);
 }

@@ -376,6 +376,27 @@ struct isb_handle {
     if (e_ != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
   } while (0)
 
+// Makes the handle's device current for the rest of the calling scope and puts the caller's device back on the way out:
+// an entry point must not leave the runtime's current device changed behind a caller that drives several GPUs from one process.
+struct IsbDeviceGuard {
+  int prev = -1;
+  bool changed = false;
+  cudaError_t set(int dev) {
+    cudaError_t e = cudaGetDevice(&prev);
+    if (e != cudaSuccess) return e;
+    if (prev == dev) return cudaSuccess;
+    e = cudaSetDevice(dev);
+    changed = e == cudaSuccess;
+    return e;
+  }
+  ~IsbDeviceGuard() {
+    if (changed) cudaSetDevice(prev);
+  }
+};
+#define ISB_SET_DEVICE(h)    \
+  IsbDeviceGuard dev_guard_; \
+  ISB_CUDA(h, dev_guard_.set((h)->device))
+
 #define ISB_LAUNCH_CHECK(h, name)                                                                 \
   do {                                                                                            \
     cudaError_t e_ = cudaGetLastError();                                                          \

@@ -407,6 +407,6 @@ extern "C" int isb_preprocess(isb_handle* h, const uint8_t* images, int32_t batc
   if (input)
     for (int c = 0; c < 3; ++c)
       if (!(std[c] != 0.0)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "preprocess: std[%d] is zero or NaN", c);
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return isb::launch_preprocess(h, images, batch, in_h, in_w, out_h, out_w, mean, std, resized, input, (cudaStream_t)stream);
 }

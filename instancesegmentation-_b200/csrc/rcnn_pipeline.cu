@@ -447,7 +447,7 @@ extern "C" int isb_rpn_filter(isb_handle* h, const float* proposals, const float
   }
   lv.start[num_levels] = (int)total;
   if (total > (1 << kRowBits)) ISB_FAIL(h, ISB_ERR_LIMIT, "rpn_filter: %lld anchors > 2^%d", (long long)total, kRowBits);
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
   if (total == 0) {
     ISB_CUDA(h, cudaMemsetAsync(out_count, 0, sizeof(int32_t), s));
@@ -545,7 +545,7 @@ extern "C" int isb_box_postprocess(isb_handle* h, const float* class_logits, con
   if ((reinterpret_cast<uintptr_t>(box_regression) & 15) || (reinterpret_cast<uintptr_t>(proposals) & 15) ||
       (reinterpret_cast<uintptr_t>(out_boxes) & 15))
     ISB_FAIL(h, ISB_ERR_BAD_ARG, "box_postprocess: box_regression / proposals / out_boxes must be 16-byte aligned");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
   if (num_rois == 0) {
     ISB_CUDA(h, cudaMemsetAsync(out_count, 0, sizeof(int32_t), s));

@@ -286,7 +286,7 @@ extern "C" int isb_rle_encode(isb_handle* h, const uint8_t* masks, int64_t mask_
   if ((int64_t)hgt * wid >= (1ll << 32)) ISB_FAIL(h, ISB_ERR_LIMIT, "rle_encode: image too large");
   if ((int64_t)wid * max_det >= (1ll << 31) || (int64_t)batch * max_det >= (1ll << 31)) ISB_FAIL(h, ISB_ERR_LIMIT, "rle_encode: too many columns");
   if (batch > 1 && mask_slot_bytes < (int64_t)hgt * wid * max_det) ISB_FAIL(h, ISB_ERR_BAD_ARG, "rle_encode: mask_slot_bytes too small");
-  ISB_CUDA(h, cudaSetDevice(h->device));
+  ISB_SET_DEVICE(h);
   return isb::launch_rle(h, masks, mask_slot_bytes, counts, m_fixed, max_det, batch, hgt, wid, rle_counts, capacity, run_count,
                          run_offset, totals, (cudaStream_t)stream);
 }

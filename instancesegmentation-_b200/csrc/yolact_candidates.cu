@@ -349,6 +349,8 @@ candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_
       lg_tile(reinterpret_cast<const float*>(wbuf + (size_t)stage * tile_bytes) + (f0 - a0), p, C, lane, nr, b, (uint32_t)r0, em);
     else
       lg_tile(base + f0, p, C, lane, nr, b, (uint32_t)r0, em);
+    // the generic-proxy reads of this stage must be ordered before the async-proxy write that refills it (WAR across proxies)
+    fence_proxy_async();
     __syncwarp();
     if (em.sg->n > kLgStage - 32) lg_flush(em, cur_img, lane);  // keep room so that the direct path stays rare
     b = nb;

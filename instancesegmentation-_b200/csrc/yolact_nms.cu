@@ -178,7 +178,8 @@ __device__ __forceinline__ void fnms_emit(const NmsParams& p, int b, const uint6
 
 // counts[b] = m, and -- multi-GPU jobs with the fused count exchange attached -- the same count into the current ring slot of
 // every rank over NVLink: one self-validating 64-bit word (epoch << 32 | count) per image and peer, written by the
-// CTA's first thread.  Called by the whole CTA.
+// CTA's first thread.  Called by the whole CTA.  The word is the whole message (nothing else has to be visible before it),
+// so the stores are relaxed: eight release stores at system scope would each wait for the CTA's earlier writes to drain.
 __device__ __forceinline__ void publish_count(const NmsParams& p, int b, int m) {
   if (threadIdx.x == 0) {
     p.out_count[b] = m;
@@ -186,7 +187,7 @@ __device__ __forceinline__ void publish_count(const NmsParams& p, int b, int m) 
 #pragma unroll
     for (int r = 0; r < 8; ++r)  // static indices: the pointer table stays in the kernel's parameter bank
       if (r < p.n_peers)
-        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.peer_ring[r] + p.peer_index0 + b), "l"(w) : "memory");
+        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.peer_ring[r] + p.peer_index0 + b), "l"(w) : "memory");
   }
 }
 

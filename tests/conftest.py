@@ -67,3 +67,40 @@ def check_pasted(pasted, g, prefix, sub_step, tol=1e-5, what="paste"):
     sums = pasted.astype(np.float64).sum(axis=(1, 2, 3))
     ref = key("sum" if prefix else "sums")
     assert np.all(np.abs(sums - ref) <= 1e-5 * np.maximum(np.abs(ref), 1.0)), what + ": per-mask sums"
+
+
+# ------------------------------------------------------------------ guard bands (stand-in for compute-sanitizer on this pool)
+BAND = 4096
+BAND_BYTE = 0xA5
+
+
+class BandedAllocator:
+    """Drop-in for the `torch` name inside an isb module: `empty()` hands out views into buffers that carry BAND bytes of a
+    known pattern before and after the payload, so that a kernel writing outside its output is caught by `check()`."""
+
+    def __init__(self):
+        import torch
+        self._torch = torch
+        self.raws = []
+
+    def __getattr__(self, name):
+        return getattr(self._torch, name)
+
+    def empty(self, *shape, dtype=None, device=None, **kw):
+        torch = self._torch
+        if len(shape) == 1 and isinstance(shape[0], (tuple, list, torch.Size)):
+            shape = tuple(shape[0])
+        dtype = dtype or torch.float32
+        if device is None or torch.device(device).type != "cuda":
+            return torch.empty(shape, dtype=dtype, device=device, **kw)
+        n = int(np.prod(shape, dtype=np.int64)) * torch.empty((), dtype=dtype).element_size()
+        pad = (n + 15) // 16 * 16
+        raw = torch.full((BAND + pad + BAND,), BAND_BYTE, dtype=torch.uint8, device=device)
+        self.raws.append((raw, pad))
+        return raw[BAND:BAND + n].view(dtype).view(shape)
+
+    def check(self):
+        assert self.raws, "no banded allocation was made"
+        for i, (raw, pad) in enumerate(self.raws):
+            assert bool((raw[:BAND] == BAND_BYTE).all()), f"allocation {i}: bytes BEFORE the output were overwritten"
+            assert bool((raw[BAND + pad:] == BAND_BYTE).all()), f"allocation {i}: bytes AFTER the output were overwritten"

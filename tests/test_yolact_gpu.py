@@ -773,3 +773,41 @@ def test_tensor_core_sigmoid_maps_on_the_fused_path():
                         "test_full_size_end_to_end or test_batch_equals_single_and_oracle or test_tiny_end_to_end"],
                        env=env, cwd=root, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+# ------------------------------------------------------------------ memory-safety stand-in (compute-sanitizer is closed on this pool)
+def test_guard_bands_and_repeatability(bu):
+    """Every output of the fused call sits between 4 KB bands of a known byte: none may change (out-of-bounds writes), and two
+    runs into differently poisoned buffers must agree bit for bit (reads of uninitialised memory, races)."""
+    from conftest import BandedAllocator
+    from isb.yolact import YolactBatchResult
+    a, p = synth.yolact_dims(550)
+    anchors = torch.from_numpy(O.get_anchors((550, 550))).float().cuda()
+    bsz, max_det, hgt, wid = 5, 100, 550, 550
+    box, conf, coef, proto = synth.yolact_batch(2100, bsz, a, num_classes=81, proto=p)
+    conf[2] = conf[2] * 0.0 + 0.001                      # an empty image in the middle of the batch
+    outs = [t.cuda() for t in (box, conf, coef, proto)]
+    slot = (hgt * wid * max_det + 15) // 16 * 16
+    runs = []
+    for poison in (0x00, 0xFF):
+        alloc = BandedAllocator()
+        d = "cuda"
+        res = YolactBatchResult(alloc.empty((bsz, max_det, 4), dtype=torch.float32, device=d),
+                                alloc.empty((bsz, max_det), dtype=torch.float32, device=d),
+                                alloc.empty((bsz, max_det), dtype=torch.int64, device=d),
+                                alloc.empty((bsz, hgt, wid), dtype=torch.int64, device=d),
+                                alloc.empty((bsz, slot), dtype=torch.uint8, device=d),
+                                alloc.empty((bsz,), dtype=torch.int32, device=d), (hgt, wid))
+        for t in (res.boxes, res.scores, res.class_ids, res.masks_arg, res.masks_raw, res.counts):
+            t.view(torch.uint8).fill_(poison)
+        bu.decode_nms_batch(outs, anchors, 0.05, 0.5, (hgt, wid), out=res)
+        torch.cuda.synchronize()
+        alloc.check()
+        runs.append(res)
+    c0, c1 = host(runs[0].counts), host(runs[1].counts)
+    assert np.array_equal(c0, c1) and c0[2] == 0 and (c0[[0, 1, 3, 4]] > 0).all()
+    for b in range(bsz):
+        if c0[b] == 0:
+            continue
+        for x, y in zip(runs[0].image(b, int(c0[b])), runs[1].image(b, int(c1[b]))):
+            assert torch.equal(x, y), f"image {b}: two runs differ"
