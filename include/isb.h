@@ -291,6 +291,21 @@ ISB_API int isb_nms(isb_handle* h, const float* boxes, const float* scores, int3
 ISB_API int isb_batched_nms(isb_handle* h, const float* boxes, const float* scores, const int64_t* idxs, int32_t n,
                     double iou_threshold, int64_t* keep, int32_t* count, isb_stream stream);
 
+/* isb_nms without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that may not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, outputs and results as isb_nms, but no handle: the scratch of the pipeline (sort keys, ranks, boxes in score
+ * order, the suppression bit matrix) is a file-scope `static __device__` array of 2 260 992 bytes that every GPU which
+ * loads the library holds until the process exits.  Runs on the CURRENT device and on `stream`; calls no cudaMalloc,
+ * cudaFree or other allocating routine (the first call on a device looks the array's address up once with
+ * cudaGetSymbolAddress -- make that first call outside a graph capture).
+ *   n > ISB_NMS_STATIC_MAX  ->  ISB_ERR_LIMIT (use isb_nms, whose workspace grows).
+ *   All calls on one GPU share the array, which keeps the previous call's contents (a call clears what it needs at zero
+ *   on `stream`); calls that OVERLAP on the GPU -- different streams, different host threads -- race on it.
+ * `err` (may be NULL) receives the error text, at most err_len bytes including the terminator. */
+#define ISB_NMS_STATIC_MAX 4096
+ISB_API int isb_nms_static(const float* boxes, const float* scores, int32_t n, double iou_threshold, int64_t* keep,
+                           int32_t* count, isb_stream stream, char* err, int32_t err_len);
+
 /* torchvision MultiScaleRoIAlign.forward (constructed at faster_rcnn_framework.py:326-329 and
  * mask_rcnn.py:150, called at roi_head.py:491,540). */
 typedef struct {

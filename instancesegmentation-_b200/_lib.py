@@ -10,6 +10,7 @@ LIB_PATH = os.path.join(PKG, "libisb.so")
 
 ISB_NUM_COEF = 32
 ISB_MAX_DET_LIMIT = 1024
+ISB_NMS_STATIC_MAX = 4096  # boxes per isb_nms_static call (fixed device scratch)
 ISB_OK, ISB_ERR_BAD_ARG, ISB_ERR_CUDA, ISB_ERR_LIMIT, ISB_ERR_OVERFLOW = 0, -1, -2, -3, -4
 
 # every exported symbol of include/isb.h (tests check the library exports exactly these)
@@ -19,7 +20,7 @@ SYMBOLS = (
     "isb_yolact_detect", "isb_yolact_detect_host", "isb_set_host_threads", "isb_host_stats",
     "isb_counts_export", "isb_counts_attach", "isb_counts_wait", "isb_counts_epoch", "isb_counts_detach", "isb_yolact_class_map", "isb_yolact_class_map_host", "isb_rle_encode", "isb_rle_to_string", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
     "isb_traditional_nms", "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_logits_batch", "isb_mask_assemble",
-    "isb_box_decode", "isb_nms", "isb_batched_nms", "isb_ms_roi_align", "isb_mask_select_sigmoid", "isb_resize_boxes",
+    "isb_box_decode", "isb_nms", "isb_nms_static", "isb_batched_nms", "isb_ms_roi_align", "isb_mask_select_sigmoid", "isb_resize_boxes",
     "isb_paste_masks", "isb_paste_class_map", "isb_rpn_filter", "isb_box_postprocess", "isb_preprocess",
     "isb_rcnn_transform",
 )
@@ -117,6 +118,7 @@ def load():
         lib.isb_box_decode.argtypes = [vp, vp, vp, i64, i32, f32, f32, f32, f32, f32, vp, vp]
         lib.isb_nms.argtypes = [vp, vp, vp, i32, f64, vp, vp, vp]
         lib.isb_batched_nms.argtypes = [vp, vp, vp, vp, i32, f64, vp, vp, vp]
+        lib.isb_nms_static.argtypes = [vp, vp, i32, f64, vp, vp, vp, C.c_char_p, i32]  # no handle: fixed device scratch
         lib.isb_ms_roi_align.argtypes = [vp, C.POINTER(RoiAlignCfg), vp, vp, i32, vp, vp]
         lib.isb_mask_select_sigmoid.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
         lib.isb_resize_boxes.argtypes = [vp, vp, i64, i32, i32, i32, i32, vp, vp]

@@ -17,6 +17,10 @@
 //   serially from shared memory, kept rows OR-ed into the removed bitmap in parallel) ->
 //   ordered compaction of the kept indices.
 #include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
 
 #include "isb_common.cuh"
 
@@ -321,3 +325,128 @@ int launch_nms(isb_handle* h, const NmsCall& c, cudaStream_t s) {
 }
 
 }  // namespace isb
+
+// ------------------------------------------------------------------------------------------------------------------
+// isb_nms_static: the same greedy NMS for callers that may not allocate (CUDA graph capture, serving loops, harnesses
+// that forbid cudaMalloc).  No counterpart in the reference.
+//
+// Every scratch array of the pipeline above (sort keys, rank, boxes in score order, original indices, the suppression
+// bit matrix) lives in ONE file-scope device array of a fixed, modest size; each GPU that loads libisb.so holds it
+// until the process exits.  The array is shared by every call on that GPU and keeps the last call's contents: what
+// must start at zero (the rank counters) is cleared on the caller's stream, everything else a call reads it has
+// written first (keys incl. padding, order, boxes, the lower-triangle mask words).  Calls that overlap on the GPU
+// (two streams, two threads) race on it.
+namespace isb {
+namespace {
+
+constexpr int kStaticNmsMax = ISB_NMS_STATIC_MAX;              // boxes per call
+constexpr int kStaticWords = kStaticNmsMax / 64;               // mask words per row at the maximum
+constexpr size_t kStOffKeys = 0;                                                     // u64 [max]  (max is a power of two)
+constexpr size_t kStOffKeys2 = kStOffKeys + (size_t)kStaticNmsMax * 8;               // u64 [max]
+constexpr size_t kStOffBox = kStOffKeys2 + (size_t)kStaticNmsMax * 8;                // float4 [max]
+constexpr size_t kStOffRank = kStOffBox + (size_t)kStaticNmsMax * 16;                // i32 [max]
+constexpr size_t kStOffOrder = kStOffRank + (size_t)kStaticNmsMax * 4;               // i32 [max]
+constexpr size_t kStOffMask = kStOffOrder + (size_t)kStaticNmsMax * 4;               // u64 [max][max / 64]
+constexpr size_t kStaticNmsBytes = kStOffMask + (size_t)kStaticNmsMax * kStaticWords * 8;  // 2 260 992 bytes at 4096
+static_assert((kStaticNmsMax & (kStaticNmsMax - 1)) == 0 && kStaticNmsMax <= kRankSortMax, "power of two within the rank sort");
+static_assert(kStOffMask % 256 == 0, "every sub-array stays 256-byte aligned");
+
+// In HOST code this name is only a stand-in for the symbol: its device address comes from cudaGetSymbolAddress.
+static __device__ __align__(256) unsigned char g_nms_static_scratch[kStaticNmsBytes];
+
+constexpr int kStaticMaxDevices = 64;
+struct StaticNmsDevice {
+  std::once_flag once;
+  cudaError_t status = cudaErrorUnknown;
+  unsigned char* base = nullptr;  // device address of g_nms_static_scratch on this GPU
+  int num_sms = 0;
+};
+StaticNmsDevice g_static_dev[kStaticMaxDevices];
+
+// once per device, with that device current
+void static_nms_setup(StaticNmsDevice* d, int device) {
+  void* p = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(&p, g_nms_static_scratch);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&d->num_sms, cudaDevAttrMultiProcessorCount, device);
+  d->base = static_cast<unsigned char*>(p);
+  d->status = e;
+}
+
+int static_fail(char* err, int32_t err_len, int code, const char* msg) {
+  if (err && err_len > 0) snprintf(err, (size_t)err_len, "%s", msg);
+  return code;
+}
+
+}  // namespace
+}  // namespace isb
+
+extern "C" int isb_nms_static(const float* boxes, const float* scores, int32_t n, double iou_threshold, int64_t* keep,
+                              int32_t* count, isb_stream stream, char* err, int32_t err_len) {
+  using namespace isb;
+  char msg[256];
+  if (err && err_len > 0) err[0] = 0;
+  if (n < 0 || !count) return static_fail(err, err_len, ISB_ERR_BAD_ARG, "nms_static: negative n or null count");
+  if (n > kStaticNmsMax) {
+    snprintf(msg, sizeof(msg), "nms_static: %d boxes exceed the fixed scratch of ISB_NMS_STATIC_MAX = %d boxes (use isb_nms)", n,
+             kStaticNmsMax);
+    return static_fail(err, err_len, ISB_ERR_LIMIT, msg);
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  int device = -1;
+  cudaError_t e = cudaGetDevice(&device);
+  if (e != cudaSuccess || device < 0 || device >= kStaticMaxDevices) {
+    snprintf(msg, sizeof(msg), "nms_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), device);
+    return static_fail(err, err_len, ISB_ERR_CUDA, msg);
+  }
+  StaticNmsDevice* d = &g_static_dev[device];
+  std::call_once(d->once, static_nms_setup, d, device);
+  if (d->status != cudaSuccess || !d->base) {
+    snprintf(msg, sizeof(msg), "nms_static: cudaGetSymbolAddress(scratch) on device %d: %s", device, cudaGetErrorString(d->status));
+    return static_fail(err, err_len, ISB_ERR_CUDA, msg);
+  }
+  if (n == 0) {  // boxes.py:66-67: empty input -> empty result
+    e = cudaMemsetAsync(count, 0, sizeof(int32_t), s);
+    if (e != cudaSuccess) return static_fail(err, err_len, ISB_ERR_CUDA, cudaGetErrorString(e));
+    return ISB_OK;
+  }
+  if (!boxes || !scores || !keep || (reinterpret_cast<uintptr_t>(boxes) & 15))
+    return static_fail(err, err_len, ISB_ERR_BAD_ARG, "nms_static: null or misaligned pointer");
+
+  uint64_t* keys = reinterpret_cast<uint64_t*>(d->base + kStOffKeys);
+  uint64_t* keys2 = reinterpret_cast<uint64_t*>(d->base + kStOffKeys2);
+  float4* sbox = reinterpret_cast<float4*>(d->base + kStOffBox);
+  int32_t* rank = reinterpret_cast<int32_t*>(d->base + kStOffRank);
+  int32_t* order = reinterpret_cast<int32_t*>(d->base + kStOffOrder);
+  uint64_t* mask = reinterpret_cast<uint64_t*>(d->base + kStOffMask);
+
+  // launch geometry and error text of the shared launchers come from a handle: a plain stack object stands in (no workspace)
+  isb_handle ctx;
+  memset(&ctx, 0, sizeof(ctx));
+  ctx.device = device;
+  ctx.num_sms = d->num_sms;
+  const int n_pow2 = next_pow2(n);
+  const int words = (n + 63) / 64;
+  float thr_f = (float)iou_threshold;  // largest float <= the double threshold, as in launch_nms
+  if ((double)thr_f > iou_threshold) thr_f = nextafterf(thr_f, -INFINITY);
+  const int blocks = (n + 255) / 256 < 4 * d->num_sms ? (n + 255) / 256 : 4 * d->num_sms;
+  int rc = ISB_OK;
+  const char* where = "";
+  do {
+    nms_keys_kernel<<<(n_pow2 + 255) / 256, 256, 0, s>>>(scores, nullptr, n, nullptr, n_pow2, keys);
+    if ((e = cudaGetLastError()) != cudaSuccess) { where = "nms_keys_kernel"; break; }
+    if ((rc = launch_rank_sort_u64(&ctx, keys, n, nullptr, rank, keys2, s)) != ISB_OK) break;  // clears rank[0..n) first
+    nms_gather_kernel<<<blocks, 256, 0, s>>>(keys2, reinterpret_cast<const float4*>(boxes), nullptr, nullptr, n, nullptr, nullptr,
+                                             nullptr, sbox, order, nullptr);
+    if ((e = cudaGetLastError()) != cudaSuccess) { where = "nms_gather_kernel"; break; }
+    nms_mask_kernel<<<(unsigned)((int64_t)words * (words + 1) / 2), 64, 0, s>>>(sbox, n, nullptr, thr_f, words, nullptr, 1, mask);
+    if ((e = cudaGetLastError()) != cudaSuccess) { where = "nms_mask_kernel"; break; }
+    nms_scan_kernel<<<1, kScanThreads, (size_t)words * 8, s>>>(mask, order, n, nullptr, words, 0, keep, count);
+    if ((e = cudaGetLastError()) != cudaSuccess) { where = "nms_scan_kernel"; break; }
+  } while (0);
+  if (rc != ISB_OK) return static_fail(err, err_len, rc, ctx.err);
+  if (e != cudaSuccess) {
+    snprintf(msg, sizeof(msg), "nms_static: launch %s: %s", where, cudaGetErrorString(e));
+    return static_fail(err, err_len, ISB_ERR_CUDA, msg);
+  }
+  return ISB_OK;
+}

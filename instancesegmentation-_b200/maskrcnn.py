@@ -54,6 +54,27 @@ def nms(boxes, scores, iou_threshold):
     return keep[: int(count.item())]
 
 
+def nms_static(boxes, scores, iou_threshold, keep, count):
+    """`nms` for callers that may not allocate (no counterpart in the reference):
+    float32 CUDA `boxes` [n,4] / `scores` [n], n <= ISB_NMS_STATIC_MAX, and PREALLOCATED outputs `keep`
+    (int64 [>= n]) and `count` (int32 [1]) on the same device.  Enqueues `isb_nms_static` on the current stream: no handle,
+    no torch or CUDA allocation, nothing synchronised -- the kept indices are keep[:count].  Every call on a GPU shares one
+    fixed scratch array, so calls that overlap on the GPU race."""
+    dev, n = boxes.device, boxes.shape[0]
+    for t, dt, name in ((boxes, torch.float32, "boxes"), (scores, torch.float32, "scores"), (keep, torch.int64, "keep"),
+                        (count, torch.int32, "count")):
+        if not (t.is_cuda and t.device == dev and t.dtype == dt and t.is_contiguous()):
+            raise ValueError(f"nms_static: {name} must be a contiguous {dt} tensor on {dev} (nothing is converted or copied)")
+    if keep.numel() < n or count.numel() < 1:
+        raise ValueError("nms_static: keep needs n elements and count one")
+    err = C.create_string_buffer(256)
+    with _lib.on_device(dev):
+        rc = _lib.load().isb_nms_static(_ptr(boxes), _ptr(scores), n, float(iou_threshold), _ptr(keep), _ptr(count), _stream(dev),
+                                        err, len(err))
+    if rc != 0:
+        raise _lib.IsbError(rc, err.value.decode())
+
+
 def batched_nms(boxes, scores, idxs, iou_threshold):
     """boxes.py:38-83: NMS per category via the reference's float32 coordinate-offset trick."""
     boxes = _cuda_f32(boxes, "boxes")
