@@ -357,6 +357,7 @@ struct isb_handle {
   void* scratch;
   size_t scratch_bytes;
   int roi_configured;      // ms_roi_align_kernel's dynamic shared memory limit has been raised
+  int fused_grid[2];       // CTAs of the one-launch rpn_filter / box_postprocess kernels (0: not asked yet, -1: unavailable)
   void* prep;              // pre-processing state (preprocess.cu): coefficient tables, intermediate image, value table
   // optional per-stage event ring (isb_profile_begin / isb_profile_read)
   cudaEvent_t* prof_events;  // [prof_cap][5]

@@ -23,13 +23,11 @@
 #include <mutex>
 
 #include "isb_common.cuh"
+#include "nms_pair.cuh"
 
 namespace isb {
 
 constexpr int kScanThreads = 1024;
-
-// boxes.max() of boxes.py:78 propagates NaN (torch.max); fmaxf would drop it
-__device__ __forceinline__ float nan_max(float a, float b) { return (a != a || b != b) ? __int_as_float(0x7fc00000) : fmaxf(a, b); }
 
 __global__ void nms_max_coord_kernel(const float4* __restrict__ boxes, int n_max, const int32_t* __restrict__ n_dev,
                                      uint32_t* __restrict__ scalars) {
@@ -126,20 +124,8 @@ __global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__
       if (offset_groups && zero_hits) bits |= 1ull << j;
       continue;
     }
-    // torchvision's CPU kernel (the reference's path, boxes.py:35): std::max(i, j) = (i < j) ? j : i and
-    // std::min(i, j) = (j < i) ? j : i with i = the higher-ranked box (the COLUMN box c here), j = the row box a --
-    // this decides what a NaN coordinate does; max(0, d) = (0 < d) ? d : 0 turns a NaN extent into 0.
-    const float4 c = cbox[j];
-    const float xx1 = (c.x < a.x) ? a.x : c.x, yy1 = (c.y < a.y) ? a.y : c.y;
-    const float xx2 = (a.z < c.z) ? a.z : c.z, yy2 = (a.w < c.w) ? a.w : c.w;
-    const float dw = xx2 - xx1, dh = yy2 - yy1;
-    const float w = (0.0f < dw) ? dw : 0.0f;
-    const float hgt = (0.0f < dh) ? dh : 0.0f;
-    const float inter = w * hgt;
-    const float uni = (aa + carea[j]) - inter;
-    bool hit;
-    if (inter == 0.0f && uni != 0.0f && fabsf(uni) <= 3.402823466e38f) hit = zero_hits;
-    else hit = inter / uni > thr;
+    // torchvision's CPU kernel semantics (NaN handling, division skipped for disjoint pairs): nms_pair.cuh
+    const bool hit = nms_pair_hit(a, aa, cbox[j], carea[j], thr, zero_hits);
     if (hit) bits |= 1ull << j;
   }
   if (rb == cb) bits &= ~(1ull << t);  // a box does not suppress itself

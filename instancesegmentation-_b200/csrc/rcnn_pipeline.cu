@@ -6,6 +6,7 @@
 #include <math.h>
 
 #include "isb_common.cuh"
+#include "nms_pair.cuh"
 
 namespace isb {
 
@@ -350,7 +351,54 @@ static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 }  // namespace isb
 
+#include "rcnn_fused.cuh"
+
 using namespace isb;
+
+// ---- host side of the one-launch kernels (rcnn_fused.cuh) --------------------------------------------------------------
+// Grid of the cooperative launch: every CTA must be resident at once, one 1024-thread CTA per SM.
+template <class K>
+static int fused_grid(isb_handle* h, int which, K kernel) {
+  if (h->fused_grid[which] == 0) {
+    const bool env_chain = getenv("ISB_RCNN_CHAIN") != nullptr;  // read once per handle: tests create a fresh one to get the chain
+    int per_sm = 0, coop = 0;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFuSmemBytes);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kFuThreads, kFuSmemBytes);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device);
+    if (e != cudaSuccess) cudaGetLastError();
+    h->fused_grid[which] = (e == cudaSuccess && per_sm >= 1 && coop && !env_chain) ? h->num_sms : -1;
+  }
+  return h->fused_grid[which];
+}
+
+// carve the fused workspace out of the scratch: [zero block | extra_zero | arrays]; returns the bytes needed
+static size_t fused_layout(char* base, int groups, size_t extra_zero, FusedWs* ws, char** extra, size_t* zero_bytes) {
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += up256(bytes); return p; };
+  char* z = take(2 * 4 + (size_t)kFuMaxGroups * 4 + 2 * 4);
+  char* x = take(extra_zero);
+  const size_t zb = off;
+  const size_t gc = (size_t)groups * kFuCap;
+  char* lkey = take(gc * 8); char* lbox = take(gc * 16); char* sbox = take(gc * 16); char* sscore = take(gc * 4);
+  char* spos = take(gc * 4); char* mask = take(gc * kFuWords * 8); char* kkey = take(gc * 8); char* kref = take(gc * 4);
+  if (base) {
+    ws->bar = (unsigned*)z;
+    ws->gcount = (int32_t*)(z + 8);
+    ws->gmax = (uint32_t*)(z + 8 + kFuMaxGroups * 4);
+    ws->kept_total = (int32_t*)(z + 8 + kFuMaxGroups * 4 + 4);
+    ws->lkey = (uint64_t*)lkey; ws->lbox = (float4*)lbox; ws->sbox = (float4*)sbox; ws->sscore = (float*)sscore;
+    ws->spos = (uint32_t*)spos; ws->mask = (uint64_t*)mask; ws->kept_key = (uint64_t*)kkey; ws->kept_ref = (uint32_t*)kref;
+    *extra = x;
+    *zero_bytes = zb;
+  }
+  return off;
+}
+
+static float nms_threshold_f32(double thr) {  // largest float <= the double threshold: (double)iou > thr  <=>  iou > thr_f
+  float t = (float)thr;
+  if ((double)t > thr) t = nextafterf(t, -INFINITY);
+  return t;
+}
 
 // ---- CUDA-graph replay of the two launch-bound chains ---------------------------------------------------------------
 // isb_rpn_filter issues ~20 small kernels and isb_box_postprocess ~13; on a B200 their sum of kernel times is about two
@@ -452,6 +500,46 @@ extern "C" int isb_rpn_filter(isb_handle* h, const float* proposals, const float
   if (total == 0) {
     ISB_CUDA(h, cudaMemsetAsync(out_count, 0, sizeof(int32_t), s));
     return ISB_OK;
+  }
+  if (pre_nms_top_n <= kFuCap && nms_thresh >= 0.0) {
+    const int grid = fused_grid(h, 0, rpn_filter_fused_kernel);
+    if (grid >= num_levels) {
+      const size_t b_hist = (size_t)kSelPasses * num_levels * kSelBins * 4;
+      int rc = ensure_scratch(h, fused_layout(nullptr, num_levels, b_hist, nullptr, nullptr, nullptr));
+      if (rc != ISB_OK) return rc;
+      RpnFusedParams fp;
+      memset(&fp, 0, sizeof(fp));
+      char* hist = nullptr;
+      size_t zero_bytes = 0;
+      fused_layout(static_cast<char*>(h->scratch), num_levels, b_hist, &fp.ws, &hist, &zero_bytes);
+      fp.objectness = objectness;
+      fp.proposals = reinterpret_cast<const float4*>(proposals);
+      fp.lv = lv;
+      fp.num_levels = num_levels;
+      fp.pre_top_n = pre_nms_top_n;
+      fp.post_top_n = post_nms_top_n;
+      fp.img_w = (float)img_w; fp.img_h = (float)img_h;
+      fp.min_size = min_size; fp.score_thresh = score_thresh;
+      fp.thr = nms_threshold_f32(nms_thresh);
+      fp.hist = reinterpret_cast<int*>(hist);
+      fp.out_boxes = reinterpret_cast<float4*>(out_boxes); fp.out_scores = out_scores; fp.out_count = out_count;
+      // CTAs per level in the select passes, in proportion to the level's anchors (every non-empty level gets one)
+      int given = 0, largest = 0;
+      int nx[8];
+      for (int l = 0; l < num_levels; ++l) {
+        fp.topk.k[l] = anchors_per_level[l] < pre_nms_top_n ? anchors_per_level[l] : pre_nms_top_n;
+        nx[l] = anchors_per_level[l] > 0 ? (int)((int64_t)(grid - num_levels) * anchors_per_level[l] / total) + 1 : 0;
+        given += nx[l];
+        if (anchors_per_level[l] > anchors_per_level[largest]) largest = l;
+      }
+      nx[largest] += grid - given;  // the rounding remainder goes to the largest level
+      for (int l = 0; l < num_levels; ++l) fp.cta_begin[l + 1] = fp.cta_begin[l] + nx[l];
+      ISB_CUDA(h, cudaMemsetAsync(h->scratch, 0, zero_bytes, s));
+      void* args[] = {&fp};
+      ISB_CUDA(h, cudaLaunchCooperativeKernel((void*)rpn_filter_fused_kernel, dim3(grid), dim3(kFuThreads), args, kFuSmemBytes, s));
+      h->launches++;
+      return ISB_OK;
+    }
   }
   const int cmax = (int)cand_max, n_pow2 = next_pow2(cmax);
   const size_t b_keys = up256((size_t)n_pow2 * 8), b_box = up256((size_t)cmax * 16), b_sc = up256((size_t)cmax * 4),
@@ -556,6 +644,37 @@ extern "C" int isb_box_postprocess(isb_handle* h, const float* class_logits, con
   if (score_thresh > 0.0f) {
     const int lim = (int)floorf(1.0f / score_thresh);
     if (lim < per_row) per_row = lim > 1 ? lim : 1;
+  }
+  if (num_rois <= kFuCap && num_classes - 1 <= kFuMaxGroups && (int64_t)num_rois * num_classes < (1 << 20) && nms_thresh >= 0.0) {
+    const int grid = fused_grid(h, 1, boxpost_fused_kernel);
+    if (grid > 0) {
+      const int groups = num_classes - 1;
+      int rc = ensure_scratch(h, fused_layout(nullptr, groups, 0, nullptr, nullptr, nullptr));
+      if (rc != ISB_OK) return rc;
+      BoxFusedParams fp;
+      memset(&fp, 0, sizeof(fp));
+      char* unused = nullptr;
+      size_t zero_bytes = 0;
+      fused_layout(static_cast<char*>(h->scratch), groups, 0, &fp.ws, &unused, &zero_bytes);
+      fp.bp.logits = class_probs ? nullptr : class_logits;
+      fp.bp.probs = class_probs;
+      fp.bp.reg = reinterpret_cast<const float4*>(box_regression);
+      fp.bp.proposals = reinterpret_cast<const float4*>(proposals);
+      fp.bp.R = num_rois;
+      fp.bp.C = num_classes;
+      fp.bp.wx = wx; fp.bp.wy = wy; fp.bp.ww = ww; fp.bp.wh = wh; fp.bp.clip = clip;
+      fp.bp.img_w = (float)img_w; fp.bp.img_h = (float)img_h;
+      fp.bp.score_thresh = score_thresh;
+      fp.thr = nms_threshold_f32(nms_thresh);
+      fp.max_keep = detections_per_img;
+      fp.out_boxes = reinterpret_cast<float4*>(out_boxes); fp.out_scores = out_scores; fp.out_labels = out_labels;
+      fp.out_count = out_count;
+      ISB_CUDA(h, cudaMemsetAsync(h->scratch, 0, zero_bytes, s));
+      void* args[] = {&fp};
+      ISB_CUDA(h, cudaLaunchCooperativeKernel((void*)boxpost_fused_kernel, dim3(grid), dim3(kFuThreads), args, kFuSmemBytes, s));
+      h->launches++;
+      return ISB_OK;
+    }
   }
   const int64_t cap64 = (int64_t)num_rois * per_row;
   if (cap64 > (1 << 17)) ISB_FAIL(h, ISB_ERR_LIMIT, "box_postprocess: up to %lld candidates exceed the NMS limit", (long long)cap64);

@@ -37,6 +37,28 @@ def main():
     proposals = R.decode_single(deltas, anchors)
     us = timeit(lambda: R.filter_proposals(proposals, logits, (800, 1333), per_level))
     res["rpn_filter_268569_to_1000"] = {"us": us}
+    # the C entry points alone (preallocated outputs, no count read-back): device time of the call itself
+    import ctypes as C
+    from isb._lib import get_handle
+    h = get_handle(0)
+    vp = lambda t: C.c_void_p(t.data_ptr())
+    stream = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    ob, osc, ocnt = torch.empty(1000, 4, device=dev), torch.empty(1000, device=dev), torch.zeros(1, dtype=torch.int32, device=dev)
+    lv = (C.c_int32 * len(per_level))(*[int(v) for v in per_level])
+    objf = logits.reshape(-1).contiguous()
+
+    def rpn_c():
+        h.check(h.lib.isb_rpn_filter(h.ptr, vp(proposals), vp(objf), lv, len(per_level), 800, 1333, 1000, 1000, 0.7, 0.0, 1.0, vp(ob),
+                                     vp(osc), vp(ocnt), stream()))
+    res["isb_rpn_filter_device_only"] = {"us": timeit(rpn_c), "kept": int(ocnt.item()),
+                                         "path": "chain" if os.environ.get("ISB_RCNN_CHAIN") else "one cooperative launch"}
+    props, lg, reg = [t.to(dev) for t in synth.box_head_outputs(4101, 1000, 21)]
+    db, ds, dl = torch.empty(100, 4, device=dev), torch.empty(100, device=dev), torch.empty(100, dtype=torch.int64, device=dev)
+
+    def box_c():
+        h.check(h.lib.isb_box_postprocess(h.ptr, vp(lg), C.c_void_p(0), vp(reg), vp(props), 1000, 21, 800, 1333, 10.0, 10.0, 5.0, 5.0,
+                                          R.BBOX_XFORM_CLIP, 0.05, 0.5, 100, vp(db), vp(ds), vp(dl), vp(ocnt), stream()))
+    res["isb_box_postprocess_device_only_1000x21"] = {"us": timeit(box_c), "kept": int(ocnt.item())}
     feats = OrderedDict((str(i), f.to(dev)) for i, f in enumerate(synth.fpn_features(4201, 256)))
     rois = synth.roi_boxes(4202, 1000).to(dev)
     res["roi_kernel"] = "staged (round 1, ISB_ROI_STAGED)" if os.environ.get("ISB_ROI_STAGED") else "register / shuffle rows kernel"
