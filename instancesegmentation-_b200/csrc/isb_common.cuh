@@ -90,6 +90,15 @@ __device__ __forceinline__ float4 decode_box(float4 p, float4 a, float var0, flo
   return make_float4(x1, y1, w + x1, h + y1);
 }
 
+// IEEE fp32 division the compiler may not speculate.  A plain `a / b` behind a branch is if-converted and hoisted above the
+// test that was meant to skip it, and its slow path (taken for a ZERO numerator -- every disjoint box pair) then runs for
+// every pair: 45 of the 80 instructions per pair in the NMS loops (ncu, round 2).
+__device__ __forceinline__ float div_rn_guarded(float a, float b) {
+  float q;
+  asm volatile("div.rn.f32 %0, %1, %2;" : "=f"(q) : "f"(a), "f"(b));
+  return q;
+}
+
 __device__ __forceinline__ float box_area(float4 b) { return (b.z - b.x) * (b.w - b.y); }
 
 __device__ __forceinline__ float iou_pair(float4 a, float area_a, float4 b, float area_b) {
@@ -277,9 +286,13 @@ __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.pr
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 __host__ __device__ inline int next_pow2(int v) {
+#ifdef __CUDA_ARCH__
+  return v <= 1 ? 1 : 1 << (32 - __clz(v - 1));
+#else
   int p = 1;
   while (p < v) p <<= 1;
   return p;
+#endif
 }
 
 }  // namespace isb

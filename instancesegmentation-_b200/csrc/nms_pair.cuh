@@ -23,7 +23,7 @@ __device__ __forceinline__ bool nms_pair_hit(const float4 a, const float area_a,
   const float inter = w * hgt;
   const float uni = (area_a + area_c) - inter;
   if (inter == 0.0f && uni != 0.0f && fabsf(uni) <= 3.402823466e38f) return zero_hits;
-  return inter / uni > thr;
+  return div_rn_guarded(inter, uni) > thr;
 }
 
 }  // namespace isb

@@ -191,6 +191,17 @@ __device__ __forceinline__ void publish_count(const NmsParams& p, int b, int m) 
   }
 }
 
+// utils_bbox.py:38-47 + :86 for one pair: does box i (higher ranked) suppress box j?  The division is skipped when the
+// boxes are disjoint: 0 / union is +-0 for every finite non-zero union, and the caller established 0 <= nms_iou.
+__device__ __forceinline__ bool fnms_suppresses(float4 bi, float4 bj, float aj, float thr) {
+  const float dx = fmaxf(fminf(bi.z, bj.z) - fmaxf(bi.x, bj.x), 0.0f);
+  const float dy = fmaxf(fminf(bi.w, bj.w) - fmaxf(bi.y, bj.y), 0.0f);
+  const float inter = dx * dy;
+  const float uni = (box_area(bi) + aj) - inter;
+  if (inter == 0.0f && fabsf(uni) > 0.0f) return false;  // non-zero, not NaN (an infinite union gives 0 too)
+  return !(div_rn_guarded(inter, uni) <= thr);
+}
+
 __global__ void __launch_bounds__(kNmsThreads, 1)
 fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* __restrict__ g_keys,
                 uint64_t* __restrict__ g_det, float4* __restrict__ g_box, int64_t cap, int64_t stride,
@@ -201,6 +212,7 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
   __shared__ int s_scan[32];
   __shared__ int s_cls_start[1 << kClassBits];
   __shared__ int s_cut;
+  __shared__ __align__(16) uint8_t s_sup[kSmemCand];  // sort-free walk: candidate is suppressed / outside its class window
 
   const int b = blockIdx.x;
   const int tid = threadIdx.x;
@@ -221,62 +233,144 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
   float4* cbox = in_smem ? reinterpret_cast<float4*>(smem_raw + 2 * kSmemCand * sizeof(uint64_t))
                          : g_box + (size_t)b * stride;
 
-  // ---- 1. sort candidates -------------------------------------------------------------
-  {
-    const uint64_t* src = g_keys + (size_t)b * stride;
-    if (in_smem) {
-      for (int i = tid; i < np2; i += kNmsThreads) keys[i] = i < n ? src[i] : kPadKey;
-    } else {
-      for (int i = n + tid; i < np2; i += kNmsThreads) keys[i] = kPadKey;
-    }
-    if (tid == 0) s_kept = 0;
-  }
-  bitonic_sort_u64(keys, np2);
-
-  // ---- 2. decode boxes of the candidates inside their class window ----------------------
-  for (int i = tid; i < n; i += kNmsThreads) cbox[i] = load_box(p, b, cand_row(keys[i]));
-  __syncthreads();
-  // ---- 3. Fast NMS ----------------------------------------------------------------------
-  // first sorted position of every class that occurs (the keys are class-major)
-  for (int i = tid; i < n; i += kNmsThreads) {
-    const uint32_t c = cand_class(keys[i]);
-    if (i == 0 || cand_class(keys[i - 1]) != c) s_cls_start[c] = i;
-  }
-  __syncthreads();
-  // EIGHT lanes per candidate j, striding over its higher-ranked class mates: a class with a long list does not
-  // leave one thread walking it alone while the CTA waits, and the per-candidate set-up is shared by 4 candidates
-  // per warp instruction.
+  // ---- 1-3. class lists, boxes, Fast NMS ---------------------------------------------------
   const bool thr_ok = 0.0f <= p.nms_iou;  // column max of a triu'd matrix is >= 0 (:80-86)
   const int sub = tid & 7;
   const unsigned gmask = 0xffu << (tid & 24);  // the 8 lanes of this group
-  for (int j0 = 0; j0 < n; j0 += kNmsThreads / 8) {
-    const int j = j0 + (tid >> 3);
-    bool bad = true;
-    uint64_t kj = 0;
-    if (j < n) {
-      kj = keys[j];
-      const int start = s_cls_start[cand_class(kj)];
-      if (thr_ok && (j - start) < p.top_k) {
-        bad = false;
-        const float4 bj = cbox[j];
-        const float aj = box_area(bj);
-        for (int i = start + sub; i < j; i += 8) {
-          const float4 bi = cbox[i];
-          // utils_bbox.py:38-47, with the division skipped when the boxes are disjoint: 0 / union is +-0 for
-          // every finite non-zero union, and thr_ok already established 0 <= nms_iou
-          const float dx = fmaxf(fminf(bi.z, bj.z) - fmaxf(bi.x, bj.x), 0.0f);
-          const float dy = fmaxf(fminf(bi.w, bj.w) - fmaxf(bi.y, bj.y), 0.0f);
-          const float inter = dx * dy;
-          const float uni = (box_area(bi) + aj) - inter;
-          if (inter == 0.0f && fabsf(uni) > 0.0f) continue;  // non-zero, not NaN (an infinite union gives 0 too)
-          if (!(inter / uni <= p.nms_iou)) { bad = true; break; }
+  if (tid == 0) { s_kept = 0; s_cut = 0; }
+  bool done = false;  // CTA-uniform
+  if (in_smem) {
+    // No sort at all when the class lists are short (the usual case: ~1000 candidates over dozens of classes): a counting
+    // sort BY CLASS only (shared-memory histogram, scan, scatter), then every candidate walks its class mates once and
+    // both counts the ones that rank before it (its place in the class's sorted list, :61-64) and tests them as
+    // suppressors (:75-86).  That is sum(class size^2) / 8 steps of an 8-lane group -- a few thousand warp instructions
+    // where the bitonic network + class table + triangular walk spend ~60 k.  The order inside a class never has to be
+    // materialised: kept candidates are re-sorted by score below anyway.  Images whose classes are too long for the
+    // quadratic walk (one class with thousands of candidates) take the bitonic sort.
+    // pointers derived straight from the shared array, so that the walks below compile to LDS / STS (the generic
+    // `keys` / `cbox` of the spill path make every access a generic load with its address arithmetic)
+    uint64_t* const skeys = reinterpret_cast<uint64_t*>(smem_raw);
+    uint64_t* const raw = skeys + kSmemCand;  // raw keys first live in the second buffer
+    float4* const sbox = reinterpret_cast<float4*>(smem_raw + 2 * kSmemCand * sizeof(uint64_t));
+    const uint64_t* src = g_keys + (size_t)b * stride;
+    for (int i = tid; i < n; i += kNmsThreads) raw[i] = src[i];
+    for (int c = tid; c < (1 << kClassBits); c += kNmsThreads) s_cls_start[c] = 0;
+    for (int i = tid; i < (n + 3) / 4; i += kNmsThreads) reinterpret_cast<uint32_t*>(s_sup)[i] = 0u;
+    __syncthreads();
+    for (int i = tid; i < n; i += kNmsThreads) atomicAdd(&s_cls_start[cand_class(raw[i])], 1);
+    __syncthreads();
+    constexpr int kPer = (1 << kClassBits) / kNmsThreads;
+    int cnt[kPer], sum = 0, sq = 0;
+#pragma unroll
+    for (int q = 0; q < kPer; ++q) {
+      cnt[q] = s_cls_start[tid * kPer + q];
+      sum += cnt[q];
+      sq += cnt[q] * cnt[q];
+    }
+    sq = __reduce_add_sync(0xffffffffu, sq);
+    if ((tid & 31) == 0 && sq) atomicAdd(&s_cut, sq);
+    int tot;
+    int run = cta_exclusive_scan(sum, s_scan, &tot);  // barriers inside: s_cut is complete afterwards
+#pragma unroll
+    for (int q = 0; q < kPer; ++q) {
+      s_cls_start[tid * kPer + q] = run;
+      run += cnt[q];
+    }
+    __syncthreads();
+    if (s_cut <= 64 * np2) {
+      for (int i = tid; i < n; i += kNmsThreads) {
+        const uint64_t k = raw[i];
+        const int pos = atomicAdd(&s_cls_start[cand_class(k)], 1);  // afterwards s_cls_start[c] = END of class c
+        skeys[pos] = k;
+        sbox[pos] = load_box(p, b, cand_row(k));
+      }
+      __syncthreads();
+      // A list no longer than top_k lies wholly inside the window (:63-64), so ranks are not needed and every unordered
+      // pair is looked at ONCE (i before j in the list's arbitrary order): whichever of the two ranks lower is flagged when
+      // they overlap too much -- a suppressed box still suppresses (Fast NMS), so nothing stops early.  Longer lists walk
+      // all mates of j, count the ones that rank before it and flag j alone.
+      for (int j0 = 0; j0 < n; j0 += kNmsThreads / 8) {
+        const int j = j0 + (tid >> 3);
+        bool bad = false;
+        if (j < n) {
+          const uint64_t kj = skeys[j];
+          const uint32_t c = cand_class(kj);
+          const int lo = c ? s_cls_start[c - 1] : 0, hi = s_cls_start[c];
+          const float4 bj = sbox[j];
+          const float aj = box_area(bj);
+          if (hi - lo <= p.top_k) {
+#pragma unroll 1
+            for (int i = lo + sub; i < j; i += 8) {
+              const float4 bi = sbox[i];
+              if (fnms_suppresses(bi, bj, aj, p.nms_iou)) {  // symmetric in the two boxes
+                if (skeys[i] < kj) bad = true; else s_sup[i] = 1;
+              }
+            }
+          } else {
+            int before = 0;
+#pragma unroll 1
+            for (int i = lo + sub; i < hi; i += 8) {
+              const bool higher = skeys[i] < kj;  // i ranks before j (score desc, row asc); false for i == j
+              before += higher;
+              if (higher && fnms_suppresses(sbox[i], bj, aj, p.nms_iou)) bad = true;
+            }
+            before += __shfl_xor_sync(gmask, before, 1);
+            before += __shfl_xor_sync(gmask, before, 2);
+            before += __shfl_xor_sync(gmask, before, 4);
+            if (before >= p.top_k) bad = true;
+          }
+          if (bad) s_sup[j] = 1;
         }
       }
+      __syncthreads();
+      for (int j0 = 0; j0 < n; j0 += kNmsThreads) {
+        const int j = j0 + tid;
+        const bool emit = thr_ok && j < n && !s_sup[j];
+        const int slot = warp_alloc_slot(emit, &s_kept);
+        if (emit) raw[slot] = det_key_from_cand(skeys[j]);  // the raw keys are no longer needed (raw == dkeys)
+      }
+      done = true;
+    } else {
+      for (int i = tid; i < np2; i += kNmsThreads) keys[i] = i < n ? raw[i] : kPadKey;
+      bitonic_sort_u64(keys, np2);
     }
-    const unsigned any_bad = __ballot_sync(0xffffffffu, bad) & gmask;
-    const bool emit = !any_bad && sub == 0;
-    const int slot = warp_alloc_slot(emit, &s_kept);
-    if (emit) dkeys[slot] = det_key_from_cand(kj);
+  } else {
+    for (int i = n + tid; i < np2; i += kNmsThreads) keys[i] = kPadKey;
+    bitonic_sort_u64(keys, np2);
+  }
+  if (!done) {
+    // sorted keys (class asc, score desc, row asc): boxes, first position of every class, triangular walk
+    for (int i = tid; i < n; i += kNmsThreads) cbox[i] = load_box(p, b, cand_row(keys[i]));
+    __syncthreads();
+    for (int i = tid; i < n; i += kNmsThreads) {
+      const uint32_t c = cand_class(keys[i]);
+      if (i == 0 || cand_class(keys[i - 1]) != c) s_cls_start[c] = i;
+    }
+    __syncthreads();
+    // EIGHT lanes per candidate j, striding over its higher-ranked class mates: a class with a long list does not
+    // leave one thread walking it alone while the CTA waits, and the per-candidate set-up is shared by 4 candidates
+    // per warp instruction.
+    for (int j0 = 0; j0 < n; j0 += kNmsThreads / 8) {
+      const int j = j0 + (tid >> 3);
+      bool bad = true;
+      uint64_t kj = 0;
+      if (j < n) {
+        kj = keys[j];
+        const int start = s_cls_start[cand_class(kj)];
+        if (thr_ok && (j - start) < p.top_k) {
+          bad = false;
+          const float4 bj = cbox[j];
+          const float aj = box_area(bj);
+          for (int i = start + sub; i < j; i += 8) {
+            if (fnms_suppresses(cbox[i], bj, aj, p.nms_iou)) { bad = true; break; }
+          }
+        }
+      }
+      const unsigned any_bad = __ballot_sync(0xffffffffu, bad) & gmask;
+      const bool emit = !any_bad && sub == 0;
+      const int slot = warp_alloc_slot(emit, &s_kept);
+      if (emit) dkeys[slot] = det_key_from_cand(kj);
+    }
   }
   __syncthreads();
   // ---- 4. global order: score desc, class asc, row asc; keep max_det --------------------
@@ -347,17 +441,6 @@ __global__ void fnms_prepare_kernel(NmsParams p, const uint64_t* __restrict__ ke
 }
 
 constexpr int kWideThreads = 256;  // 8 candidates per CTA, one warp each
-
-// utils_bbox.py:38-47 + :86 for one pair: does box i (higher ranked) suppress box j?  The division is skipped when the
-// boxes are disjoint: 0 / union is +-0 for every finite non-zero union, and the caller established 0 <= nms_iou.
-__device__ __forceinline__ bool fnms_suppresses(float4 bi, float4 bj, float aj, float thr) {
-  const float dx = fmaxf(fminf(bi.z, bj.z) - fmaxf(bi.x, bj.x), 0.0f);
-  const float dy = fmaxf(fminf(bi.w, bj.w) - fmaxf(bi.y, bj.y), 0.0f);
-  const float inter = dx * dy;
-  const float uni = (box_area(bi) + aj) - inter;
-  if (inter == 0.0f && fabsf(uni) > 0.0f) return false;  // non-zero, not NaN (an infinite union gives 0 too)
-  return !(inter / uni <= thr);
-}
 
 // A WARP per candidate j, four independent box loads in flight per lane: with thousands of predecessors per candidate
 // (one class, VerSeg) an 8-lane group with one load in flight spent ~100 us waiting on L2.

@@ -512,6 +512,25 @@ def test_fast_nms_wide_path_vs_oracle(bu, n, c, top_k, max_det):
     assert np.array_equal(host(b), rb) and np.array_equal(host(k), rk)
 
 
+@pytest.mark.parametrize("n,c,top_k,max_det,path", [(40, 80, 200, 100, "rank"), (60, 30, 20, 50, "rank, lists longer than top_k"),
+                                                     (1000, 4, 200, 100, "bitonic"), (300, 10, 50, 20, "bitonic"),
+                                                     (4096, 1, 100, 100, "bitonic, full buffer"), (7, 3, 200, 100, "tiny")])
+def test_fast_nms_single_cta_sort_paths_vs_oracle(bu, n, c, top_k, max_det, path):
+    """Inside one CTA the class-major order comes either from a counting sort by class + in-class ranking (many short
+    lists) or from the bitonic network (few long lists); both, with lists shorter and longer than top_k and heavily
+    overlapping boxes, must give the oracle's detections bit for bit."""
+    g = torch.Generator().manual_seed(7 * n + c)
+    ctr = torch.rand(n, 2, generator=g)
+    wh = torch.rand(n, 2, generator=g) * 0.2 + 0.1
+    box = torch.cat([ctr - wh / 2, ctr + wh / 2], 1).contiguous()
+    score = torch.rand(n, c, generator=g).contiguous()
+    coef = torch.tanh(torch.randn(n, 32, generator=g))
+    rb, rs, rc_, rk = O.fast_non_max_suppression(box.numpy(), score.numpy(), coef.numpy(), 0.5, top_k, max_det)
+    b, s, cls, k = bu.fast_non_max_suppression(box.cuda(), score.cuda(), coef.cuda(), 0.5, top_k, max_det)
+    assert np.array_equal(host(s), rs) and np.array_equal(host(cls), rc_), path
+    assert np.array_equal(host(b), rb) and np.array_equal(host(k), rk), path
+
+
 # ------------------------------------------------------------------------------- error convention (SURVEY 8b)
 def test_error_convention(bu):
     """int status < 0 + isb_last_error text, nothing launched, handle usable afterwards; "no detections" is a value."""
