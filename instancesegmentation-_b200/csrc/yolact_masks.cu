@@ -172,8 +172,12 @@ __device__ __forceinline__ void warp_clear(uint8_t* buf, int a, int b, int lane)
 // plain coalesced stores.
 enum { kCompMap = 0, kCompDense = 1, kCompPacked = 2 };
 
-template <int kMode>
-__global__ void __launch_bounds__(kCompThreads, 2)
+// kBig: the one-CTA-per-SM configuration of very large detection counts (BASELINE configs[4]: m = 1024, 8-pixel segments,
+// ~10 warps per SM).  With so few warps the kernel is bound by its serial memory round trips, so this instantiation may
+// use 128 registers and (a) loads the records of up to four list-building rounds before the first barrier instead of one
+// round trip + three barriers per round, (b) keeps the sigmoid-map taps of TWO covering detections in flight per lane.
+template <int kMode, bool kBig>
+__global__ void __launch_bounds__(kCompThreads, kBig ? 1 : 2)
 mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, const float* __restrict__ smap,
                     int* __restrict__ work_counter) {
   constexpr bool kMasks = kMode == kCompDense;
@@ -211,12 +215,15 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
   int dlo0 = 0, dhi0 = 0, dlo1 = 0, dhi1 = 0;  // this warp's dirty byte range in each of its buffers
   unsigned seg_no = 0;
 
+  int next_unit = 0;  // kBig: the ticket of the following unit is fetched while this one is processed (units are short there)
+  if (kBig && tid == 0) next_unit = atomicAdd(work_counter, 1);
   while (true) {
     __syncthreads();  // everyone is done with the previous unit's list (and s_unit)
-    if (tid == 0) s_unit = atomicAdd(work_counter, 1);
+    if (tid == 0) s_unit = kBig ? next_unit : atomicAdd(work_counter, 1);
     __syncthreads();
     const int unit = s_unit;
     if (unit >= total_units) break;
+    if (kBig && tid == 0) next_unit = atomicAdd(work_counter, 1);
     const int b = unit / g.units_per_img;
     const int u = unit - b * g.units_per_img;
     const int m = p.counts ? p.counts[b] : p.m_fixed;
@@ -251,6 +258,52 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
     }
     if (tid == 0) s_nlist = 0;
     __syncthreads();
+    if constexpr (kBig) {
+      // four rounds per sweep: all record loads of the sweep are in flight together, one count exchange for the four
+      for (int base = 0; base < m; base += 4 * blockDim.x) {
+        int4 bb[4];
+        unsigned bal[4];
+        bool hit[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int j = base + q * blockDim.x + tid;
+          bb[q] = make_int4(0, 0, 0, 0);
+          if (j < m) bb[q] = __ldg(reinterpret_cast<const int4*>(&rec[(size_t)b * p.det_stride + j]));  // xlo, xhi, ylo, yhi
+        }
+        int packed = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int j = base + q * blockDim.x + tid;
+          hit[q] = j < m && bb[q].z <= yb && bb[q].w > ya && bb[q].x < bb[q].y;
+          bal[q] = __ballot_sync(0xffffffffu, hit[q]);
+          packed |= __popc(bal[q]) << (8 * q);  // <= 32 per round and warp
+        }
+        if (lane == 0) s_wcount[warp] = packed;
+        __syncthreads();
+        int before[4] = {0, 0, 0, 0}, tot[4] = {0, 0, 0, 0};
+        for (int w = 0; w < nwarps; ++w) {
+          const int c = s_wcount[w];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int cq = (c >> (8 * q)) & 0xff;
+            if (w < warp) before[q] += cq;
+            tot[q] += cq;
+          }
+        }
+        int off = s_nlist;  // ascending detection index: round-major, then warp, then lane
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (hit[q]) {
+            const int j = base + q * blockDim.x + tid;
+            s_det[off + before[q] + __popc(bal[q] & ((1u << lane) - 1u))] = rec[(size_t)b * p.det_stride + j];
+          }
+          off += tot[q];
+        }
+        __syncthreads();
+        if (tid == 0) s_nlist = off;
+        __syncthreads();
+      }
+    } else {
     for (int base = 0; base < m; base += blockDim.x) {
       const int j = base + tid;
       bool hit = false;
@@ -272,6 +325,7 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
       __syncthreads();
       if (tid == 0) s_nlist += tot;
       __syncthreads();
+    }
     }
     const int nlist = s_nlist;
 
@@ -328,6 +382,38 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
           hit = bb.z <= wy1 && bb.w > wy0 && bb.x < wxb && bb.y > wxa;
         }
         unsigned bal = __ballot_sync(0xffffffffu, hit);
+        if constexpr (kBig) {
+          // two listed detections per step: eight sigmoid-map taps in flight per lane instead of four
+          auto taps = [&](const DetRec& r, float& p00, float& p01, float& p10, float& p11) {
+            const float* S = S_img + r.soff;
+            const int fw = r.fw;
+            const int r0 = (iy0 - r.pya) * fw - r.pa, r1 = (iy1 - r.pya) * fw - r.pa;
+            p00 = __ldg(S + r0 + ix0); p01 = __ldg(S + r0 + ix1);
+            p10 = __ldg(S + r1 + ix0); p11 = __ldg(S + r1 + ix1);
+          };
+          auto take = [&](int jdet, float p00, float p01, float p10, float p11) {
+            const float top = lx0 * p00 + lx1 * p01;
+            const float bot = lx0 * p10 + lx1 * p11;
+            const float v = ly0 * top + ly1 * bot;
+            if (kMasks && v > 0.5f) { mypix[jdet] = 1; anyset = true; }
+            if (v > best) { best = v; arg = jdet; }
+          };
+          while (bal) {
+            const int k = __ffs(bal) - 1;
+            bal &= bal - 1;
+            const bool two = bal != 0u;  // warp-uniform
+            const int k2 = two ? __ffs(bal) - 1 : k;
+            if (two) bal &= bal - 1;
+            const DetRec r = s_det[base + k], r2 = s_det[base + k2];
+            const bool in0 = active && y >= r.ylo && y < r.yhi && x >= r.xlo && x < r.xhi;
+            const bool in1 = two && active && y >= r2.ylo && y < r2.yhi && x >= r2.xlo && x < r2.xhi;
+            float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f, b00 = 0.f, b01 = 0.f, b10 = 0.f, b11 = 0.f;
+            if (in0) taps(r, a00, a01, a10, a11);
+            if (in1) taps(r2, b00, b01, b10, b11);
+            if (in0) take(r.j, a00, a01, a10, a11);
+            if (in1) take(r2.j, b00, b01, b10, b11);  // ascending index: first max wins
+          }
+        } else {
         while (bal) {
           const int k = __ffs(bal) - 1;
           bal &= bal - 1;
@@ -346,6 +432,7 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
             }
             if (v > best) { best = v; arg = r.j; }
           }
+        }
         }
       }
       if (cmap_img && active) cmap_img[q0 + lane] = best > 0.5f ? (uint8_t)(__ldg(cls_img + arg) + 1) : (uint8_t)0;
@@ -391,12 +478,13 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
 
 // ---- host side ----------------------------------------------------------------------------
 static constexpr int kCompSmemTwo = 111 * 1024;   // two CTAs per SM
-static constexpr int kCompSmemOne = 200 * 1024;   // one CTA per SM (very large detection counts)
+static constexpr int kCompSmemOne = 224 * 1024;   // one CTA per SM (very large detection counts)
 
 int configure_masks(isb_handle* h) {
-  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<kCompDense>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
-  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<kCompMap>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
-  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<kCompPacked>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
+  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<kCompDense, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
+  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<kCompDense, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
+  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<kCompMap, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
+  ISB_CUDA(h, cudaFuncSetAttribute(mask_compose_kernel<kCompPacked, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCompSmemOne));
   return ISB_OK;
 }
 
@@ -511,11 +599,13 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s, int which) 
     if (grid > total_units) grid = total_units;
     int* ctr = counters + (pass ? kSecondCounter : 0);
     if (mode == kCompMap)
-      mask_compose_kernel<kCompMap><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
+      mask_compose_kernel<kCompMap, false><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
+    else if (mode == kCompDense && per_sm == 1)  // very large detection counts: the latency-oriented instantiation
+      mask_compose_kernel<kCompDense, true><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
     else if (mode == kCompDense)
-      mask_compose_kernel<kCompDense><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
+      mask_compose_kernel<kCompDense, false><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
     else
-      mask_compose_kernel<kCompPacked><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
+      mask_compose_kernel<kCompPacked, false><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
     ISB_LAUNCH_CHECK(h, "mask_compose_kernel");
   }
   return ISB_OK;
