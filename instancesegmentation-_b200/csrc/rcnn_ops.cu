@@ -2,6 +2,8 @@
 // resize_boxes, paste_masks_in_image and (Multi-scale) RoIAlign.
 #include <stdlib.h>
 
+#include <cuda.h>
+#include <mutex>
 #include "isb_common.cuh"
 
 namespace isb {
@@ -573,10 +575,9 @@ __device__ __forceinline__ float roi_row_x_phase(float t0, float t1, bool wide, 
 // OH > 0 (with SR > 0): output height known at compile time -- all 2 * OH * SR row loads of a channel are issued before
 // anything depends on them (one memory round trip per channel instead of one per output row).
 template <int SR, int OH>
-__global__ void __launch_bounds__(kRoiRowThreads, 2) ms_roi_align_rows_kernel(RoiLevels L, const float4* __restrict__ boxes,
-                                                                        const int32_t* __restrict__ batch_idx, int channels,
-                                                                        int oh, int ow, int sr_rt, int cpc,
-                                                                        float* __restrict__ out) {
+__device__ __forceinline__ void roi_rows_body(const RoiLevels& L, const float4* __restrict__ boxes,
+                                              const int32_t* __restrict__ batch_idx, int channels, int oh, int ow, int sr_rt,
+                                              int cpc, float* __restrict__ out) {
   const int sr = SR > 0 ? SR : sr_rt;
   __shared__ RowSample s_y[32];
   __shared__ int s_xlist[64];          // distinct feature columns, ascending
@@ -772,6 +773,181 @@ __global__ void __launch_bounds__(kRoiRowThreads, 2) ms_roi_align_rows_kernel(Ro
   }
 }
 
+template <int SR, int OH>
+__global__ void __launch_bounds__(kRoiRowThreads, 2) ms_roi_align_rows_kernel(RoiLevels L, const float4* __restrict__ boxes,
+                                                                        const int32_t* __restrict__ batch_idx, int channels,
+                                                                        int oh, int ow, int sr_rt, int cpc,
+                                                                        float* __restrict__ out) {
+  roi_rows_body<SR, OH>(L, boxes, batch_idx, channels, oh, ow, sr_rt, cpc, out);
+}
+
+// ------------------------------------------------------------------------------------------
+// TMA-staged RoIAlign (sampling ratio 2, 7 x 7 and 14 x 14 poolers).  What a RoI needs of one channel is a WINDOW of its
+// FPN level -- the rows and columns between its first and last bilinear tap, at most ~30 x 30 because the LevelMapper
+// picks the level on which the RoI is 14-28 feature pixels across.  Here that window arrives as ONE tensor-tile TMA
+// load per (RoI, channel) (cp.async.bulk.tensor.3d, SASS UTMALDG): a tensor map per level and per box shape
+// (8/16/24/32 columns x 8/16/24/32 rows x 1 channel, starting at a 16-byte-aligned column; the smallest shape that
+// covers the window is used, so small RoIs
+// do not drag 4 KB tiles through the L2), zero-filled outside the map.  Every WARP runs its own three-deep ring of
+// tiles on its own mbarriers (no CTA barrier after the prologue): lane 0 issues the loads of the warp's next channels
+// while the warp reduces the current one out of shared memory with the arithmetic of the rows kernel above (lane =
+// window column for the y blend, lane = x sample for the x phase; identical bits).  No load instruction, address
+// arithmetic or scoreboard wait for global memory is left in the SM's instruction stream: ~125 instead of ~290 warp
+// instructions per (RoI, channel).  RoIs whose window does not fit 32 x 32 (elongated boxes) and levels whose row pitch
+// is not a multiple of 16 bytes (42 floats at the coarsest level of an 800 x 1344 image) take roi_rows_body.
+// ------------------------------------------------------------------------------------------
+constexpr int kTmaStages = 3;      // ring size in tiles of the largest shape
+constexpr int kTmaMaxStages = 8;   // ring depth for small tiles
+constexpr int kTmaTileBytes = 32 * 32 * 4;
+constexpr int kTmaLevels = 4;
+
+struct RoiTmaMaps {
+  CUtensorMap m[kTmaLevels][16];  // [level][(rows / 8 - 1) * 4 + (cols / 8 - 1)]
+  int ok[8];                      // level usable (pitch and base 16-byte aligned, map encoded)
+};
+
+__device__ __forceinline__ void tma_load_3d(void* dst_smem, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+          smem_u32(dst_smem)),
+      "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+      : "memory");
+}
+
+template <int OH>
+__global__ void __launch_bounds__(kRoiRowThreads, 2)
+ms_roi_align_tma_kernel(const __grid_constant__ RoiTmaMaps M, RoiLevels L, const float4* __restrict__ boxes,
+                        const int32_t* __restrict__ batch_idx, int channels, int cpc, float* __restrict__ out) {
+  constexpr int SR = 2, NS = OH * SR;  // samples per axis (14 or 28)
+  extern __shared__ __align__(128) unsigned char tma_smem[];  // [warps][stages][4 KB]
+  __shared__ __align__(8) uint64_t bars[kRoiRowWarps][kTmaMaxStages];
+  __shared__ int s_ylo[32], s_yhi[32], s_xlo[32], s_xhi[32];  // absolute tap rows / columns
+  __shared__ float s_yh[32], s_yl[32], s_xl[32];              // weights (0 for samples outside the map); s_xl < 0: outside
+  __shared__ int s_win[4];                                    // first / last tap column, first / last tap row
+  const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const float4 b = boxes[r];
+  int lvl = 0;
+  if (L.num_levels > 1) {  // LevelMapper (poolers.py:73-84)
+    const float s = sqrtf((b.z - b.x) * (b.w - b.y));
+    float t = floorf(L.canonical_level + log2f(s / L.canonical_scale) + L.eps);
+    t = fminf(fmaxf(t, (float)L.k_min), (float)L.k_max);
+    lvl = (int)(long long)t - L.k_min;
+  }
+  const int fh = L.h[lvl], fw = L.w[lvl];
+  const float ss = L.scale[lvl];
+  const float start_w = b.x * ss, start_h = b.y * ss, end_w = b.z * ss, end_h = b.w * ss;
+  const float roi_w = fmaxf(end_w - start_w, 1.0f), roi_h = fmaxf(end_h - start_h, 1.0f);
+  const float bin_h = roi_h / (float)OH, bin_w = roi_w / (float)OH;
+  if (tid < kRoiRowWarps * kTmaMaxStages) mbar_init(&bars[tid / kTmaMaxStages][tid % kTmaMaxStages], 1);
+  if (warp < 2) {  // warp 0: y samples, warp 1: x samples
+    const bool isx = warp == 1;
+    AxisSample a;
+    a.bad = 1; a.lo = a.hi = 0; a.l = a.h = 0.0f;
+    if (lane < NS) {
+      const int pq = lane / SR, iq = lane - pq * SR;
+      a = isx ? axis_sample(start_w + (float)pq * bin_w + (((float)iq + 0.5f) * bin_w) / (float)SR, fw)
+              : axis_sample(start_h + (float)pq * bin_h + (((float)iq + 0.5f) * bin_h) / (float)SR, fh);
+    }
+    const int first = __reduce_min_sync(0xffffffffu, a.bad ? 0x7fffffff : a.lo);
+    const int last = __reduce_max_sync(0xffffffffu, a.bad ? -1 : a.hi);
+    if (isx) {
+      s_xlo[lane] = a.bad ? 0 : a.lo;
+      s_xhi[lane] = a.bad ? 0 : a.hi;
+      s_xl[lane] = a.bad ? -1.0f : a.l;
+      if (lane == 0) { s_win[0] = first; s_win[1] = last; }
+    } else {
+      s_ylo[lane] = a.bad ? 0 : a.lo;
+      s_yhi[lane] = a.bad ? 0 : a.hi;
+      s_yh[lane] = a.bad ? 0.0f : a.h;
+      s_yl[lane] = a.bad ? 0.0f : a.l;
+      if (lane == 0) { s_win[2] = first; s_win[3] = last; }
+    }
+  }
+  __syncthreads();
+  // the innermost tile coordinate must be a multiple of 16 bytes (an unaligned one faults with "illegal instruction":
+  // tools/tma_probe2.cu): the window starts at the 4-column boundary at or below the first tap
+  const int x0 = s_win[0] & ~3, x1 = s_win[1], y0 = s_win[2], y1 = s_win[3];
+  const int spanx = x1 - x0 + 1, spany = y1 - y0 + 1;
+  const bool fits = lvl < kTmaLevels && M.ok[lvl] && x1 >= x0 && y1 >= y0 && spanx <= 32 && spany <= 32;
+  if (!fits) {  // CTA-uniform
+    roi_rows_body<SR, OH>(L, boxes, batch_idx, channels, OH, OH, SR, cpc, out);
+    return;
+  }
+  const int bw = (spanx + 7) & ~7, bh = (spany + 7) & ~7;
+  const CUtensorMap* map = &M.m[lvl][((bh >> 3) - 1) * 4 + ((bw >> 3) - 1)];
+  const uint32_t tile_bytes = (uint32_t)(bw * bh * 4);
+  // lane as a window column (y blend) and as an x sample (x phase)
+  const int lc = min(lane, bw - 1);
+  const int plo = (lane < NS ? s_xlo[lane] - x0 : 0) & 31, phi = (lane < NS ? s_xhi[lane] - x0 : 0) & 31;
+  const float xl_raw = lane < NS ? s_xl[lane] : -1.0f;
+  const float lx = xl_raw >= 0.0f ? xl_raw : 0.0f;
+  const float hx = xl_raw >= 0.0f ? 1.0f - xl_raw : 0.0f;
+  const int my_pw = lane / SR;
+  const bool bin_lane = lane < NS && lane - my_pw * SR == 0;
+  const float inv_count = 1.0f / (float)(SR * SR);
+  constexpr int bins = OH * OH;
+  const int img = batch_idx ? batch_idx[r] : 0;
+  float* obase = out + (size_t)r * channels * bins;
+  const int cbase = blockIdx.y * cpc, cend = min(channels, cbase + cpc);
+  const int nk = cbase + warp < cend ? (cend - cbase - warp + kRoiRowWarps - 1) / kRoiRowWarps : 0;  // this warp's channels
+  // the warp's 12 KB ring holds as many tiles as fit (3 of the largest shape, up to 8 of the small ones): the deeper the
+  // ring, the more load latency the warp rides out
+  unsigned char* wbuf = tma_smem + (size_t)warp * kTmaStages * kTmaTileBytes;
+  uint64_t* wbar = bars[warp];
+  const int slot = (int)((tile_bytes + 127u) & ~127u);
+  const int nst = min(kTmaMaxStages, (kTmaStages * kTmaTileBytes) / slot);
+  auto issue = [&](int k, int st) {  // lane 0: channel k of this warp -> stage st
+    mbar_expect_tx(&wbar[st], tile_bytes);
+    tma_load_3d(wbuf + (size_t)st * slot, map, x0, y0, img * channels + cbase + warp + k * kRoiRowWarps, &wbar[st]);
+  };
+  if (lane == 0)
+    for (int k = 0; k < nst - 1 && k < nk; ++k) issue(k, k);
+  // y taps as float offsets inside the tile, with their weights
+  int ylo[OH == 7 ? NS : 1], yhi[OH == 7 ? NS : 1];
+  float wh[OH == 7 ? NS : 1], wl[OH == 7 ? NS : 1];
+  if constexpr (OH == 7) {
+#pragma unroll
+    for (int q = 0; q < NS; ++q) {
+      ylo[q] = (s_ylo[q] - y0) * bw;
+      yhi[q] = (s_yhi[q] - y0) * bw;
+      wh[q] = s_yh[q];
+      wl[q] = s_yl[q];
+    }
+  }
+  int st = 0, fill = nst - 1;  // stage of channel k, stage the next load goes to (the one iteration k - 1 released)
+  uint32_t par = 0;
+  for (int k = 0; k < nk; ++k) {
+    if (lane == 0 && k + nst - 1 < nk) issue(k + nst - 1, fill);
+    if (++fill == nst) fill = 0;
+    mbar_wait(&wbar[st], par);
+    const float* T = reinterpret_cast<const float*>(wbuf + (size_t)st * slot) + lc;
+    float* oc = obase + (size_t)(cbase + warp + k * kRoiRowWarps) * bins;
+#pragma unroll
+    for (int ph = 0; ph < OH; ++ph) {
+      float ta = 0.0f;
+#pragma unroll
+      for (int iy = 0; iy < SR; ++iy) {
+        const int q = ph * SR + iy;
+        float vlo, vhi, h_, l_;
+        if constexpr (OH == 7) {
+          vlo = T[ylo[q]]; vhi = T[yhi[q]]; h_ = wh[q]; l_ = wl[q];
+        } else {
+          vlo = T[(s_ylo[q] - y0) * bw]; vhi = T[(s_yhi[q] - y0) * bw]; h_ = s_yh[q]; l_ = s_yl[q];
+        }
+        ta = fmaf(h_, vlo, ta);
+        ta = fmaf(l_, vhi, ta);
+      }
+      const float alo = __shfl_sync(0xffffffffu, ta, plo), ahi = __shfl_sync(0xffffffffu, ta, phi);
+      float xa = hx * alo + lx * ahi;
+      xa += __shfl_xor_sync(0xffffffffu, xa, 1);
+      if (bin_lane) oc[ph * OH + my_pw] = xa * inv_count;
+    }
+    fence_proxy_async();  // this stage's generic-proxy reads before the async-proxy refill (WAR across proxies)
+    __syncwarp();
+    if (++st == nst) { st = 0; par ^= 1u; }
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // GeneralizedRCNNTransform for inference, one image (transform.py:436-459): normalize (:264-270, float32
 // (v - mean) / std), resize (:284-315 -> F.interpolate bilinear, align_corners=False, output size given) and the
@@ -866,9 +1042,73 @@ int launch_rcnn_transform(isb_handle* h, const float* img, int in_h, int in_w, i
   ISB_LAUNCH_CHECK(h, "rcnn_transform_kernel");
   return ISB_OK;
 }
+// Tensor maps of the TMA RoIAlign: one per level and box shape, encoded on the host (cuTensorMapEncodeTiled through the
+// runtime's driver entry point: libisb.so does not link libcuda) and kept per device for as long as the feature maps stay
+// where they are -- the steady state of a loop over preallocated tensors.  nullptr: no usable level / no driver entry
+// point (the caller then runs the rows kernel).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+struct RoiTmaCache {
+  RoiTmaMaps maps;
+  const float* feat[kTmaLevels];
+  int h[kTmaLevels], w[kTmaLevels], levels, channels, valid, any;
+};
+static const RoiTmaMaps* roi_tma_maps(isb_handle* h, const RoiLevels& L, int channels) {
+  static std::mutex mu;
+  static RoiTmaCache cache[64];
+  static EncodeTiledFn encode = nullptr;
+  static bool looked = false;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!looked) {
+    looked = true;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      encode = reinterpret_cast<EncodeTiledFn>(fn);
+    cudaGetLastError();
+  }
+  if (!encode || h->device < 0 || h->device >= 64) return nullptr;
+  RoiTmaCache& c = cache[h->device];
+  const int nl = L.num_levels < kTmaLevels ? L.num_levels : kTmaLevels;
+  bool same = c.valid && c.levels == nl && c.channels == channels;
+  for (int l = 0; same && l < nl; ++l) same = c.feat[l] == L.feat[l] && c.h[l] == L.h[l] && c.w[l] == L.w[l];
+  if (same) return c.any ? &c.maps : nullptr;
+  memset(&c, 0, sizeof(c));
+  c.levels = nl;
+  c.channels = channels;
+  for (int l = 0; l < nl; ++l) {
+    c.feat[l] = L.feat[l];
+    c.h[l] = L.h[l];
+    c.w[l] = L.w[l];
+    if ((L.w[l] & 3) || (reinterpret_cast<uintptr_t>(L.feat[l]) & 15) || L.w[l] < 1 || L.h[l] < 1) continue;
+    // [planes = images x channels][rows][columns]; the plane count is only an out-of-bounds limit (the image count is not
+    // an argument of the call: any plane the kernel names exists)
+    const cuuint64_t dims[3] = {(cuuint64_t)L.w[l], (cuuint64_t)L.h[l], (cuuint64_t)channels * 65536ull};
+    const cuuint64_t strides[2] = {(cuuint64_t)L.w[l] * 4ull, (cuuint64_t)L.w[l] * (cuuint64_t)L.h[l] * 4ull};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    bool ok = true;
+    for (int by = 0; ok && by < 4; ++by)
+      for (int bx = 0; ok && bx < 4; ++bx) {
+        const cuuint32_t box[3] = {(cuuint32_t)(8 * (bx + 1)), (cuuint32_t)(8 * (by + 1)), 1};
+        ok = encode(&c.maps.m[l][by * 4 + bx], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(L.feat[l]), dims, strides, box,
+                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+      }
+    c.maps.ok[l] = ok ? 1 : 0;
+    c.any |= c.maps.ok[l];
+  }
+  c.valid = 1;
+  return c.any ? &c.maps : nullptr;
+}
+
 int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, const int32_t* batch_idx, int num_rois,
                         int channels, int oh, int ow, int sr, float* out, cudaStream_t s) {
   if (!h->roi_configured) {
+    ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_tma_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     kRoiRowWarps * kTmaStages * kTmaTileBytes));
+    ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_tma_kernel<14>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     kRoiRowWarps * kTmaStages * kTmaTileBytes));
     const int max_smem = (int)(kRoiTileFloats * sizeof(float) + (size_t)kRoiMaxEntries * 32);
     ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
     ISB_CUDA(h, cudaFuncSetAttribute(ms_roi_align_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
@@ -885,6 +1125,19 @@ int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, c
     cpc = (cpc + 2 * kRoiRowWarps - 1) / (2 * kRoiRowWarps) * (2 * kRoiRowWarps);  // a warp takes channels in pairs
     groups = (channels + cpc - 1) / cpc;
     const float4* b4 = reinterpret_cast<const float4*>(boxes);
+    static const bool no_tma = getenv("ISB_ROI_NO_TMA") != nullptr;  // A/B switch: the register / shuffle rows kernel alone
+    if (sr == 2 && oh == ow && (oh == 7 || oh == 14) && !no_tma) {
+      const RoiTmaMaps* maps = roi_tma_maps(h, L, channels);
+      if (maps) {
+        const size_t smem = (size_t)kRoiRowWarps * kTmaStages * kTmaTileBytes;
+        if (oh == 7)
+          ms_roi_align_tma_kernel<7><<<dim3(num_rois, groups), kRoiRowThreads, smem, s>>>(*maps, L, b4, batch_idx, channels, cpc, out);
+        else
+          ms_roi_align_tma_kernel<14><<<dim3(num_rois, groups), kRoiRowThreads, smem, s>>>(*maps, L, b4, batch_idx, channels, cpc, out);
+        ISB_LAUNCH_CHECK(h, "ms_roi_align_tma_kernel");
+        return ISB_OK;
+      }
+    }
     if (sr == 2 && oh == 7)        // box head pooler (faster_rcnn_framework.py:326)
       ms_roi_align_rows_kernel<2, 7><<<dim3(num_rois, groups), kRoiRowThreads, 0, s>>>(L, b4, batch_idx, channels, oh, ow, sr, cpc, out);
     else if (sr == 2 && oh == 14)  // mask head pooler (mask_rcnn.py:150)
