@@ -184,8 +184,13 @@ __device__ __forceinline__ void lg_flush(const LgEmit& e, int img, int lane) {  
 // One tile of <= 16 rows, a lane pair per row.  `tile` is either the shared-memory copy (the normal case; inlined
 // separately so the loads compile to LDS) or, for the tensor's very last rows whose tail the aligned bulk copy could
 // not cover, global memory.
-__device__ __forceinline__ void lg_tile(const float* tile, const CandParams& p, int C, int lane, int nr, int img, uint32_t r0,
+// CT > 0: the class count as a compile-time constant (COCO's 81 and VOC's 21 columns are instantiated): the bounds test and
+// select on every element of the register-resident half row fold away (ncu, round 2: 594 warp instructions per tile with a
+// run-time count, where the arithmetic needs about 205).
+template <int CT>
+__device__ __forceinline__ void lg_tile(const float* tile, const CandParams& p, int C_rt, int lane, int nr, int img, uint32_t r0,
                                         const LgEmit& e) {
+  const int C = CT > 0 ? CT : C_rt;
   const float ninf = -__int_as_float(0x7f800000);
   const int par = lane & 1;
   const bool valid = (lane >> 1) < nr;
@@ -286,13 +291,14 @@ __device__ __forceinline__ void lg_tile(const float* tile, const CandParams& p, 
   }
 }
 
+template <int CT>
 __global__ void __launch_bounds__(kLgThreads, 2)
 candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_t* __restrict__ cand_keys, int64_t cap,
                          int64_t key_stride, int tiles_per_img, int64_t total_floats) {
   extern __shared__ __align__(128) unsigned char lg_smem[];  // [warps][2] tile buffers
   __shared__ __align__(8) uint64_t bars[kLgWarps][2];
   __shared__ LgWarpStage stages[kLgWarps];
-  const int C = p.ncols;
+  const int C = CT > 0 ? CT : p.ncols;
   const int tile_bytes = ((kLgRows * C * 4 + 15) & ~15) + 16;  // widened to 16-byte boundaries on both sides
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int total_tiles = p.batch * tiles_per_img;
@@ -346,9 +352,9 @@ candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_
     const int in_smem = (int)(a1 - f0);  // floats of this tile the bulk copy delivered (all but < 4 at the tensor's end)
     mbar_wait(&bars[warp][stage], (it >> 1) & 1);
     if (nr * C <= in_smem)
-      lg_tile(reinterpret_cast<const float*>(wbuf + (size_t)stage * tile_bytes) + (f0 - a0), p, C, lane, nr, b, (uint32_t)r0, em);
+      lg_tile<CT>(reinterpret_cast<const float*>(wbuf + (size_t)stage * tile_bytes) + (f0 - a0), p, C, lane, nr, b, (uint32_t)r0, em);
     else
-      lg_tile(base + f0, p, C, lane, nr, b, (uint32_t)r0, em);
+      lg_tile<CT>(base + f0, p, C, lane, nr, b, (uint32_t)r0, em);
     // the generic-proxy reads of this stage must be ordered before the async-proxy write that refills it (WAR across proxies)
     fence_proxy_async();
     __syncwarp();
@@ -360,7 +366,9 @@ candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_
 }
 
 int configure_candidates(isb_handle* h) {
-  ISB_CUDA(h, cudaFuncSetAttribute(candidates_logits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+  ISB_CUDA(h, cudaFuncSetAttribute(candidates_logits_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+  ISB_CUDA(h, cudaFuncSetAttribute(candidates_logits_kernel<81>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+  ISB_CUDA(h, cudaFuncSetAttribute(candidates_logits_kernel<21>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
   return ISB_OK;
 }
 
@@ -376,7 +384,8 @@ int launch_candidates(isb_handle* h, const CandParams& p, cudaStream_t s) {
     const int tiles_per_img = (p.rows + kLgRows - 1) / kLgRows;
     int64_t grid = (int64_t)p.batch * tiles_per_img;
     if (grid > 2 * h->num_sms) grid = 2 * h->num_sms;
-    candidates_logits_kernel<<<(unsigned)grid, kLgThreads, smem, s>>>(
+    auto kern = p.ncols == 81 ? candidates_logits_kernel<81> : (p.ncols == 21 ? candidates_logits_kernel<21> : candidates_logits_kernel<0>);
+    kern<<<(unsigned)grid, kLgThreads, smem, s>>>(
         p, h->cand_count + h->ws_b0, h->cand_keys + (size_t)h->ws_b0 * h->cand_cap_pow2, h->lim.cand_capacity, h->cand_cap_pow2,
         tiles_per_img, (int64_t)p.batch * p.rows * p.ncols);
     ISB_LAUNCH_CHECK(h, "candidates_logits_kernel");
