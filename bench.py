@@ -558,7 +558,7 @@ def run_gpu(args):
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {**workload_config(world),
                            "count_exchange": "none (1 GPU)" if xchg is None else
-                           ("fused into fast_nms_kernel: NVLink peer stores into every rank's ring (isb_counts_*), no collective launch"
+                           ("fused into the step's own kernels: NVLink peer stores of every image's count into every rank's ring (isb_counts_*), no collective launch"
                             if getattr(xchg, "fused", False) else "NCCL all_gather_into_tensor of int32 counts, posted asynchronously")},
                 "clocks": sampler.summary(),
                 "e2e": {"value": bsz * world / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

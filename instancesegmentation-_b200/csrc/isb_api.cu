@@ -328,7 +328,10 @@ static int detect_k2_k3a(const DetectRange& d, int b0, int nb, cudaStream_t st) 
   np.out_class = out->class_ids + (size_t)b0 * in->max_det;
   np.out_coef = nullptr;  // coefficients of kept detections go to the workspace
   np.out_count = out->counts + b0;
-  if (d.publish) {
+  // the counts reach the peers from the sigmoid-map kernel that follows (MaskParams); from this kernel only when the
+  // measurement switch replaces that kernel
+  const bool publish_here = d.publish && masks_tc_smap_forced();
+  if (publish_here) {
     np.n_peers = h->cx_world;
     for (int r = 0; r < h->cx_world; ++r) np.peer_ring[r] = h->cx_peer[r];
     np.peer_index0 = (int32_t)((h->cx_epoch % (uint32_t)h->cx_depth) * (uint32_t)(h->cx_world * h->cx_local) + h->cx_rank * h->cx_local + b0);
@@ -341,7 +344,13 @@ static int detect_k2_k3a(const DetectRange& d, int b0, int nb, cudaStream_t st) 
       const cudaError_t e = cudaEventRecord(d.ev[2], st);
       if (e != cudaSuccess) { h->ws_b0 = d.base; ISB_FAIL(h, ISB_ERR_CUDA, "cudaEventRecord: %s", cudaGetErrorString(e)); }
     }
-    const MaskParams mp = mask_params(d, b0, nb);
+    MaskParams mp = mask_params(d, b0, nb);
+    if (d.publish && !publish_here) {
+      mp.n_peers = h->cx_world;
+      for (int r = 0; r < h->cx_world; ++r) mp.peer_ring[r] = h->cx_peer[r];
+      mp.peer_index0 = (int32_t)((h->cx_epoch % (uint32_t)h->cx_depth) * (uint32_t)(h->cx_world * h->cx_local) + h->cx_rank * h->cx_local + b0);
+      mp.peer_epoch = h->cx_epoch;
+    }
     rc = launch_masks(h, mp, st, 1);
   }
   h->ws_b0 = d.base;

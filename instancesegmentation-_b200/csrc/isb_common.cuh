@@ -168,16 +168,18 @@ __device__ __forceinline__ void det_footprint(const DetBounds& bd, float sy, flo
 // Eight elements of sigmoid maps, computed by 8 cooperating lanes (q = lane & 7): element i of the group is
 // S = sigmoid(proto_vec_i . coef_vec_i) (utils_bbox.py:223 restricted to the prototype pixels a crop box can
 // reach).  Every lane passes the 128-byte prototype / coefficient vectors of ITS element (pp, cf); for each of
-// the 8 elements the pointers are broadcast and lane q loads channels 4q..4q+3, so a vector is read as one
+// the 8 elements the vector indices are broadcast and lane q loads channels 4q..4q+3, so a vector is read as one
 // coalesced line.  The 8 x 8 partial sums are then transpose-reduced with a fixed xor butterfly (4, 2, 1):
 // lane q returns the complete dot product of element q -- same summation order everywhere this is used.
-__device__ __forceinline__ float smap_dot8(const float4* pp, const float4* cf, int q) {
+// The vectors are named by their index in units of 128 bytes (prototype pixel / coefficient row of the image): one
+// 32-bit shuffle each instead of a 64-bit pointer (two).
+__device__ __forceinline__ float smap_dot8(const float4* proto_img, const float4* coef_img, int pix, int det, int q) {
   float part[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int src = (threadIdx.x & 24) | i;
-    const float4* pi = reinterpret_cast<const float4*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(pp), src));
-    const float4* ci = reinterpret_cast<const float4*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(cf), src));
+    const float4* pi = proto_img + (size_t)__shfl_sync(0xffffffffu, pix, src) * (ISB_NUM_COEF / 4);
+    const float4* ci = coef_img + (size_t)__shfl_sync(0xffffffffu, det, src) * (ISB_NUM_COEF / 4);
     const float4 a = __ldg(pi + q), c = __ldg(ci + q);
     float acc = a.x * c.x;
     acc = fmaf(a.y, c.y, acc);
@@ -485,9 +487,17 @@ struct MaskParams {
   uint8_t* packed;           // B slots of packed_slot_bytes, or nullptr
   int64_t packed_slot_bytes; // >= 4 * ceil(H*W*max_det / 32), multiple of 16
   int32_t skip_dense;        // 1 with `packed`: the dense masks are not written (masks may be nullptr); masks_arg still is
+  // fused count exchange, deferred from the NMS kernel (NmsParams below): the sigmoid-map kernel stores epoch << 32 | count
+  // of every image into peer_ring[r][peer_index0 + b] at its START, so the NVLink stores drain under its own 38 us instead
+  // of holding up the end of the NMS kernel (a kernel is not complete before its remote stores are: +4 us at 8 GPUs)
+  unsigned long long* peer_ring[8];
+  int32_t n_peers;
+  int32_t peer_index0;
+  uint32_t peer_epoch;
 };
 // which: bit 0 = sigmoid maps (K3a), bit 1 = compose (K3b); the two may be launched for different image ranges / streams
 int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s, int which = 3);
+bool masks_tc_smap_forced();  // ISB_TC_SMAP measurement switch: the sigmoid maps come from the tensor-core kernel
 // grows the sigmoid-map scratch for `images` images of at most m_cap detections; returns floats per image in *s_cap
 int ensure_mask_scratch(isb_handle* h, int proto_h, int proto_w, int m_cap, int64_t images, int64_t* s_cap);
 

@@ -69,6 +69,15 @@ sigmoid_map_kernel(MaskParams p, const DetRec* __restrict__ rec, const int32_t* 
     compose_counter[0] = 0;
     compose_counter[kSecondCounter] = 0;
   }
+  if (p.n_peers > 0 && blockIdx.x == gridDim.x - 1) {  // multi-GPU: every image's count into every rank's ring (see MaskParams)
+    for (int b = threadIdx.x; b < p.batch; b += kSmapThreads) {
+      const unsigned long long w = ((unsigned long long)p.peer_epoch << 32) | (unsigned)p.counts[b];
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        if (r < p.n_peers)
+          asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.peer_ring[r] + p.peer_index0 + b), "l"(w) : "memory");
+    }
+  }
   extern __shared__ __align__(16) unsigned char s_dyn[];  // DetRec s_rec[list_cap]
   __shared__ int s_cstart[kSmapMaxBatch + 1];             // first ticket of every image
   __shared__ int s_scan[32];
@@ -133,10 +142,12 @@ sigmoid_map_kernel(MaskParams p, const DetRec* __restrict__ rec, const int32_t* 
         r = s_rec[l];
       }
       const int f = tt - r.soff, fw = r.fw;
-      const int fy = f / fw, fx = f - fy * fw;
-      const float4* pp = reinterpret_cast<const float4*>(proto_img + ((size_t)(r.pya + fy) * p.proto_w + (r.pa + fx)) * ISB_NUM_COEF);
-      const float4* cf = reinterpret_cast<const float4*>(coef_img + (size_t)l * ISB_NUM_COEF);
-      const float v = sigmoidf_ref(smap_dot8(pp, cf, q));
+      // f / fw without the integer division (~20 instructions): float estimate + one correction step, exact for any f
+      int fy = __float2int_rz(((float)f + 0.5f) * __frcp_rn((float)fw));
+      int fx = f - fy * fw;
+      if (fx < 0) { --fy; fx += fw; } else if (fx >= fw) { ++fy; fx -= fw; }
+      const float v = sigmoidf_ref(smap_dot8(reinterpret_cast<const float4*>(proto_img), reinterpret_cast<const float4*>(coef_img),
+                                             (r.pya + fy) * p.proto_w + (r.pa + fx), l, q));
       if (on) S[t] = v;
     }
   }
@@ -504,6 +515,11 @@ int ensure_mask_scratch(isb_handle* h, int proto_h, int proto_w, int m_cap, int6
   // count), not by the handle's limits: 7.6 MB per image at m = 100, 138 x 138.
   *s_cap = (int64_t)m_cap * proto_h * proto_w;
   return ensure_smap(h, (size_t)images * (size_t)*s_cap);
+}
+
+bool masks_tc_smap_forced() {
+  static const bool v = getenv("ISB_TC_SMAP") != nullptr;
+  return v;
 }
 
 int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s, int which) {
