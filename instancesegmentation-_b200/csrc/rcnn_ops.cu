@@ -796,8 +796,7 @@ __global__ void __launch_bounds__(kRoiRowThreads, 2) ms_roi_align_rows_kernel(Ro
 // instructions per (RoI, channel).  RoIs whose window does not fit 32 x 32 (elongated boxes) and levels whose row pitch
 // is not a multiple of 16 bytes (42 floats at the coarsest level of an 800 x 1344 image) take roi_rows_body.
 // ------------------------------------------------------------------------------------------
-constexpr int kTmaStages = 3;      // ring size in tiles of the largest shape
-constexpr int kTmaMaxStages = 8;   // ring depth for small tiles
+constexpr int kTmaStages = 3;
 constexpr int kTmaTileBytes = 32 * 32 * 4;
 constexpr int kTmaLevels = 4;
 
@@ -805,6 +804,11 @@ struct RoiTmaMaps {
   CUtensorMap m[kTmaLevels][16];  // [level][(rows / 8 - 1) * 4 + (cols / 8 - 1)]
   int ok[8];                      // level usable (pitch and base 16-byte aligned, map encoded)
 };
+
+// Planes (channels) per tile.  Several planes per request -- as many as fit a 4 KB ring slot, up to 8 for 8 x 8 windows --
+// were measured and change nothing (97.6 vs 95.6 us for 1000 small RoIs; 14 x 14: 69 vs 54 us, the plane offset costs
+// three address instructions per tap): the copy unit's request rate is not what bounds the kernel, so one plane it is.
+__host__ __device__ constexpr int roi_tma_planes(int, int) { return 1; }
 
 __device__ __forceinline__ void tma_load_3d(void* dst_smem, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
   asm volatile(
@@ -820,7 +824,8 @@ ms_roi_align_tma_kernel(const __grid_constant__ RoiTmaMaps M, RoiLevels L, const
                         const int32_t* __restrict__ batch_idx, int channels, int cpc, float* __restrict__ out) {
   constexpr int SR = 2, NS = OH * SR;  // samples per axis (14 or 28)
   extern __shared__ __align__(128) unsigned char tma_smem[];  // [warps][stages][4 KB]
-  __shared__ __align__(8) uint64_t bars[kRoiRowWarps][kTmaMaxStages];
+  __shared__ __align__(8) uint64_t bars[kRoiRowWarps][kTmaStages];   // tile landed (TMA transaction bytes)
+  __shared__ __align__(8) uint64_t empty[kRoiRowWarps][kTmaStages];  // tile consumed (all 32 lanes arrived)
   __shared__ int s_ylo[32], s_yhi[32], s_xlo[32], s_xhi[32];  // absolute tap rows / columns
   __shared__ float s_yh[32], s_yl[32], s_xl[32];              // weights (0 for samples outside the map); s_xl < 0: outside
   __shared__ int s_win[4];                                    // first / last tap column, first / last tap row
@@ -838,7 +843,10 @@ ms_roi_align_tma_kernel(const __grid_constant__ RoiTmaMaps M, RoiLevels L, const
   const float start_w = b.x * ss, start_h = b.y * ss, end_w = b.z * ss, end_h = b.w * ss;
   const float roi_w = fmaxf(end_w - start_w, 1.0f), roi_h = fmaxf(end_h - start_h, 1.0f);
   const float bin_h = roi_h / (float)OH, bin_w = roi_w / (float)OH;
-  if (tid < kRoiRowWarps * kTmaMaxStages) mbar_init(&bars[tid / kTmaMaxStages][tid % kTmaMaxStages], 1);
+  if (tid < kRoiRowWarps * kTmaStages) {
+    mbar_init(&bars[tid / kTmaStages][tid % kTmaStages], 1);
+    mbar_init(&empty[tid / kTmaStages][tid % kTmaStages], 32);
+  }
   if (warp < 2) {  // warp 0: y samples, warp 1: x samples
     const bool isx = warp == 1;
     AxisSample a;
@@ -874,8 +882,14 @@ ms_roi_align_tma_kernel(const __grid_constant__ RoiTmaMaps M, RoiLevels L, const
     return;
   }
   const int bw = (spanx + 7) & ~7, bh = (spany + 7) & ~7;
+  constexpr int bc = roi_tma_planes(0, 0);  // planes per tile (see roi_tma_planes)
+  if (channels < bc) {  // (a tile must not name planes past the image's last channel)
+    roi_rows_body<SR, OH>(L, boxes, batch_idx, channels, OH, OH, SR, cpc, out);
+    return;
+  }
   const CUtensorMap* map = &M.m[lvl][((bh >> 3) - 1) * 4 + ((bw >> 3) - 1)];
-  const uint32_t tile_bytes = (uint32_t)(bw * bh * 4);
+  const int plane = bw * bh;  // floats
+  const uint32_t tile_bytes = (uint32_t)(plane * 4 * bc);
   // lane as a window column (y blend) and as an x sample (x phase)
   const int lc = min(lane, bw - 1);
   const int plo = (lane < NS ? s_xlo[lane] - x0 : 0) & 31, phi = (lane < NS ? s_xhi[lane] - x0 : 0) & 31;
@@ -889,62 +903,87 @@ ms_roi_align_tma_kernel(const __grid_constant__ RoiTmaMaps M, RoiLevels L, const
   const int img = batch_idx ? batch_idx[r] : 0;
   float* obase = out + (size_t)r * channels * bins;
   const int cbase = blockIdx.y * cpc, cend = min(channels, cbase + cpc);
-  const int nk = cbase + warp < cend ? (cend - cbase - warp + kRoiRowWarps - 1) / kRoiRowWarps : 0;  // this warp's channels
-  // the warp's 12 KB ring holds as many tiles as fit (3 of the largest shape, up to 8 of the small ones): the deeper the
-  // ring, the more load latency the warp rides out
+  // this warp's tiles: blocks of bc channels, block index warp, warp + 8, ...
+  const int nblk = (cend - cbase + bc - 1) / bc;
+  const int nk = warp < nblk ? (nblk - warp + kRoiRowWarps - 1) / kRoiRowWarps : 0;
+  // the warp's ring: kTmaStages slots of 4 KB.  The tile loop is unrolled by the ring depth, so a tap's shared-memory
+  // address is a per-RoI register plus an IMMEDIATE stage offset (plus the plane offset inside a multi-channel tile)
   unsigned char* wbuf = tma_smem + (size_t)warp * kTmaStages * kTmaTileBytes;
   uint64_t* wbar = bars[warp];
-  const int slot = (int)((tile_bytes + 127u) & ~127u);
-  const int nst = min(kTmaMaxStages, (kTmaStages * kTmaTileBytes) / slot);
-  auto issue = [&](int k, int st) {  // lane 0: channel k of this warp -> stage st
+  uint64_t* wempty = empty[warp];
+  auto first_plane = [&](int k) {  // first channel of tile k, pulled back so that the tile ends inside the image's planes
+    return min(cbase + (warp + k * kRoiRowWarps) * bc, channels - bc);
+  };
+  auto issue = [&](int k, int st) {  // lane 0: tile k of this warp -> stage st
     mbar_expect_tx(&wbar[st], tile_bytes);
-    tma_load_3d(wbuf + (size_t)st * slot, map, x0, y0, img * channels + cbase + warp + k * kRoiRowWarps, &wbar[st]);
+    tma_load_3d(wbuf + (size_t)st * kTmaTileBytes, map, x0, y0, img * channels + first_plane(k), &wbar[st]);
   };
   if (lane == 0)
-    for (int k = 0; k < nst - 1 && k < nk; ++k) issue(k, k);
-  // y taps as float offsets inside the tile, with their weights
-  int ylo[OH == 7 ? NS : 1], yhi[OH == 7 ? NS : 1];
+    for (int k = 0; k < kTmaStages - 1 && k < nk; ++k) issue(k, k);
+  // y taps: addresses of this lane's column in stage 0, plane 0, with their weights; the x weights carry 1 / count (a power of two)
+  const float* T0 = reinterpret_cast<const float*>(wbuf) + lc;
+  const float* alo_p[OH == 7 ? NS : 1];
+  const float* ahi_p[OH == 7 ? NS : 1];
   float wh[OH == 7 ? NS : 1], wl[OH == 7 ? NS : 1];
   if constexpr (OH == 7) {
 #pragma unroll
     for (int q = 0; q < NS; ++q) {
-      ylo[q] = (s_ylo[q] - y0) * bw;
-      yhi[q] = (s_yhi[q] - y0) * bw;
+      alo_p[q] = T0 + (s_ylo[q] - y0) * bw;
+      ahi_p[q] = T0 + (s_yhi[q] - y0) * bw;
       wh[q] = s_yh[q];
       wl[q] = s_yl[q];
     }
   }
-  int st = 0, fill = nst - 1;  // stage of channel k, stage the next load goes to (the one iteration k - 1 released)
+  const float hxc = hx * inv_count, lxc = lx * inv_count;
   uint32_t par = 0;
-  for (int k = 0; k < nk; ++k) {
-    if (lane == 0 && k + nst - 1 < nk) issue(k + nst - 1, fill);
-    if (++fill == nst) fill = 0;
-    mbar_wait(&wbar[st], par);
-    const float* T = reinterpret_cast<const float*>(wbuf + (size_t)st * slot) + lc;
-    float* oc = obase + (size_t)(cbase + warp + k * kRoiRowWarps) * bins;
+  for (int k0 = 0; k0 < nk; k0 += kTmaStages) {
 #pragma unroll
-    for (int ph = 0; ph < OH; ++ph) {
-      float ta = 0.0f;
-#pragma unroll
-      for (int iy = 0; iy < SR; ++iy) {
-        const int q = ph * SR + iy;
-        float vlo, vhi, h_, l_;
-        if constexpr (OH == 7) {
-          vlo = T[ylo[q]]; vhi = T[yhi[q]]; h_ = wh[q]; l_ = wl[q];
-        } else {
-          vlo = T[(s_ylo[q] - y0) * bw]; vhi = T[(s_yhi[q] - y0) * bw]; h_ = s_yh[q]; l_ = s_yl[q];
+    for (int st = 0; st < kTmaStages; ++st) {
+      const int k = k0 + st;
+      if (k < nk) {  // warp-uniform
+        // the load kTmaStages - 1 tiles ahead goes into the stage the previous tile released: its 32 lanes arrived on the
+        // stage's "empty" barrier after their last read -- the release / acquire pair orders those generic-proxy reads
+        // before the async-proxy refill (no fence.proxy.async, which lowers to MEMBAR.ALL.CTA and waits for the stores)
+        if (lane == 0 && k + kTmaStages - 1 < nk) {
+          const int s2 = (st + kTmaStages - 1) % kTmaStages;
+          if (st == 0) { if (k0 > 0) mbar_wait(&wempty[s2], par ^ 1u); } else mbar_wait(&wempty[s2], par);
+          issue(k + kTmaStages - 1, s2);
         }
-        ta = fmaf(h_, vlo, ta);
-        ta = fmaf(l_, vhi, ta);
+        mbar_wait(&wbar[st], par);
+        constexpr int kStageFloats = kTmaTileBytes / 4;
+        const int c_first = first_plane(k);                                  // plane 0 of the tile
+        const int c_lo = cbase + (warp + k * kRoiRowWarps) * bc;              // channels this tile is responsible for
+        const int c_hi = min(c_lo + bc, cend);
+#pragma unroll 1
+        for (int c = c_lo; c < c_hi; ++c) {
+          const int poff = (c - c_first) * plane;
+          float* oc = obase + (size_t)c * bins;
+#pragma unroll
+          for (int ph = 0; ph < OH; ++ph) {
+            float ta = 0.0f;
+#pragma unroll
+            for (int iy = 0; iy < SR; ++iy) {
+              const int q = ph * SR + iy;
+              float vlo, vhi, h_, l_;
+              if constexpr (OH == 7) {
+                vlo = (alo_p[q] + poff)[st * kStageFloats]; vhi = (ahi_p[q] + poff)[st * kStageFloats]; h_ = wh[q]; l_ = wl[q];
+              } else {
+                vlo = T0[st * kStageFloats + poff + (s_ylo[q] - y0) * bw]; vhi = T0[st * kStageFloats + poff + (s_yhi[q] - y0) * bw];
+                h_ = s_yh[q]; l_ = s_yl[q];
+              }
+              ta = fmaf(h_, vlo, ta);
+              ta = fmaf(l_, vhi, ta);
+            }
+            const float alo = __shfl_sync(0xffffffffu, ta, plo), ahi = __shfl_sync(0xffffffffu, ta, phi);
+            float xa = fmaf(hxc, alo, lxc * ahi);
+            xa += __shfl_xor_sync(0xffffffffu, xa, 1);
+            if (bin_lane) oc[ph * OH + my_pw] = xa;
+          }
+        }
+        mbar_arrive(&wempty[st]);  // this lane's reads of the stage are done (release)
       }
-      const float alo = __shfl_sync(0xffffffffu, ta, plo), ahi = __shfl_sync(0xffffffffu, ta, phi);
-      float xa = hx * alo + lx * ahi;
-      xa += __shfl_xor_sync(0xffffffffu, xa, 1);
-      if (bin_lane) oc[ph * OH + my_pw] = xa * inv_count;
     }
-    fence_proxy_async();  // this stage's generic-proxy reads before the async-proxy refill (WAR across proxies)
-    __syncwarp();
-    if (++st == nst) { st = 0; par ^= 1u; }
+    par ^= 1u;
   }
 }
 
@@ -1090,7 +1129,7 @@ static const RoiTmaMaps* roi_tma_maps(isb_handle* h, const RoiLevels& L, int cha
     bool ok = true;
     for (int by = 0; ok && by < 4; ++by)
       for (int bx = 0; ok && bx < 4; ++bx) {
-        const cuuint32_t box[3] = {(cuuint32_t)(8 * (bx + 1)), (cuuint32_t)(8 * (by + 1)), 1};
+        const cuuint32_t box[3] = {(cuuint32_t)(8 * (bx + 1)), (cuuint32_t)(8 * (by + 1)), (cuuint32_t)roi_tma_planes(8 * (bx + 1), 8 * (by + 1))};
         ok = encode(&c.maps.m[l][by * 4 + bx], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(L.feat[l]), dims, strides, box,
                     estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -1118,6 +1157,7 @@ int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, c
   if (oh * sr <= 32 && ow * sr <= 32 && !force_staged) {
     // register / shuffle kernel: a CTA = (RoI, group of channels), a warp walks the group's channels.  Enough CTAs for
     // ~2 waves of 8 resident CTAs per SM; at least one channel per warp and pass.
+    // (swept for the TMA kernel at 1000 RoIs: one group of 256 channels per RoI 113 us, two or three groups 96 us)
     int groups = (16 * h->num_sms + num_rois - 1) / num_rois;
     if (groups > (channels + kRoiRowWarps - 1) / kRoiRowWarps) groups = (channels + kRoiRowWarps - 1) / kRoiRowWarps;
     if (groups < 1) groups = 1;
@@ -1126,7 +1166,12 @@ int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, c
     groups = (channels + cpc - 1) / cpc;
     const float4* b4 = reinterpret_cast<const float4*>(boxes);
     static const bool no_tma = getenv("ISB_ROI_NO_TMA") != nullptr;  // A/B switch: the register / shuffle rows kernel alone
-    if (sr == 2 && oh == ow && (oh == 7 || oh == 14) && !no_tma) {
+    // the 7 x 7 box-head pooler: faster than the rows kernel on every box population measured (101 / 104 / 122 us against
+    // 123 / 124 / 127, tools/bench_roi_shapes.py).  The 14 x 14 mask-head pooler stays on the rows kernel unless
+    // ISB_ROI_TMA14 is set: its 28-sample table does not fit in registers next to the tile pointers and is re-read from
+    // shared memory per tap (54 us against 47.5 us for 100 RoIs; 33.5 against 36.3 on the chain bench's detections).
+    static const bool tma14 = getenv("ISB_ROI_TMA14") != nullptr;
+    if (sr == 2 && oh == ow && (oh == 7 || (oh == 14 && tma14)) && !no_tma) {
       const RoiTmaMaps* maps = roi_tma_maps(h, L, channels);
       if (maps) {
         const size_t smem = (size_t)kRoiRowWarps * kTmaStages * kTmaTileBytes;
