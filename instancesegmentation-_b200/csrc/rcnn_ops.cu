@@ -1093,7 +1093,8 @@ struct RoiTmaCache {
   const float* feat[kTmaLevels];
   int h[kTmaLevels], w[kTmaLevels], levels, channels, valid, any;
 };
-static const RoiTmaMaps* roi_tma_maps(isb_handle* h, const RoiLevels& L, int channels) {
+// Copies the maps into *out under the cache lock (another thread's call on the same device may re-encode the entry).
+static bool roi_tma_maps(isb_handle* h, const RoiLevels& L, int channels, RoiTmaMaps* out) {
   static std::mutex mu;
   static RoiTmaCache cache[64];
   static EncodeTiledFn encode = nullptr;
@@ -1107,12 +1108,15 @@ static const RoiTmaMaps* roi_tma_maps(isb_handle* h, const RoiLevels& L, int cha
       encode = reinterpret_cast<EncodeTiledFn>(fn);
     cudaGetLastError();
   }
-  if (!encode || h->device < 0 || h->device >= 64) return nullptr;
+  if (!encode || h->device < 0 || h->device >= 64) return false;
   RoiTmaCache& c = cache[h->device];
   const int nl = L.num_levels < kTmaLevels ? L.num_levels : kTmaLevels;
   bool same = c.valid && c.levels == nl && c.channels == channels;
   for (int l = 0; same && l < nl; ++l) same = c.feat[l] == L.feat[l] && c.h[l] == L.h[l] && c.w[l] == L.w[l];
-  if (same) return c.any ? &c.maps : nullptr;
+  if (same) {
+    if (c.any) *out = c.maps;
+    return c.any != 0;
+  }
   memset(&c, 0, sizeof(c));
   c.levels = nl;
   c.channels = channels;
@@ -1138,7 +1142,8 @@ static const RoiTmaMaps* roi_tma_maps(isb_handle* h, const RoiLevels& L, int cha
     c.any |= c.maps.ok[l];
   }
   c.valid = 1;
-  return c.any ? &c.maps : nullptr;
+  if (c.any) *out = c.maps;
+  return c.any != 0;
 }
 
 int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, const int32_t* batch_idx, int num_rois,
@@ -1172,8 +1177,9 @@ int launch_ms_roi_align(isb_handle* h, const RoiLevels& L, const float* boxes, c
     // shared memory per tap (54 us against 47.5 us for 100 RoIs; 33.5 against 36.3 on the chain bench's detections).
     static const bool tma14 = getenv("ISB_ROI_TMA14") != nullptr;
     if (sr == 2 && oh == ow && (oh == 7 || (oh == 14 && tma14)) && !no_tma) {
-      const RoiTmaMaps* maps = roi_tma_maps(h, L, channels);
-      if (maps) {
+      RoiTmaMaps maps_copy;
+      const RoiTmaMaps* maps = &maps_copy;
+      if (roi_tma_maps(h, L, channels, &maps_copy)) {
         const size_t smem = (size_t)kRoiRowWarps * kTmaStages * kTmaTileBytes;
         if (oh == 7)
           ms_roi_align_tma_kernel<7><<<dim3(num_rois, groups), kRoiRowThreads, smem, s>>>(*maps, L, b4, batch_idx, channels, cpc, out);
