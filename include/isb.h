@@ -383,6 +383,16 @@ ISB_API int isb_box_postprocess(isb_handle* h, const float* class_logits, const 
                         int32_t detections_per_img, float* out_boxes, float* out_scores, int64_t* out_labels,
                         int32_t* out_count, isb_stream stream);
 
+/* isb_box_postprocess for a pipeline that never reads a count on the host (roi_head.py:366-457 on the PADDED proposals of
+ * one image): the rows are [max_rois, ...] as isb_rpn_filter leaves them (post_nms_top_n rows, valid ones first), and
+ * *num_rois_dev (device memory, e.g. isb_rpn_filter's out_count) says how many are valid; rows past it are ignored.
+ * Results are identical to isb_box_postprocess(num_rois = *num_rois_dev). */
+ISB_API int isb_box_postprocess_rows(isb_handle* h, const float* class_logits, const float* class_probs, const float* box_regression,
+                             const float* proposals, int32_t max_rois, const int32_t* num_rois_dev, int32_t num_classes,
+                             int32_t img_h, int32_t img_w, float wx, float wy, float ww, float wh, float clip,
+                             float score_thresh, double nms_thresh, int32_t detections_per_img, float* out_boxes,
+                             float* out_scores, int64_t* out_labels, int32_t* out_count, isb_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -21,7 +21,7 @@ SYMBOLS = (
     "isb_counts_export", "isb_counts_attach", "isb_counts_wait", "isb_counts_epoch", "isb_counts_detach", "isb_yolact_class_map", "isb_yolact_class_map_host", "isb_rle_encode", "isb_rle_to_string", "isb_decode_boxes", "isb_jaccard", "isb_fast_nms",
     "isb_traditional_nms", "isb_correct_boxes", "isb_crop", "isb_mask_logits", "isb_mask_logits_batch", "isb_mask_assemble",
     "isb_box_decode", "isb_nms", "isb_nms_static", "isb_batched_nms", "isb_ms_roi_align", "isb_mask_select_sigmoid", "isb_resize_boxes",
-    "isb_paste_masks", "isb_paste_class_map", "isb_rpn_filter", "isb_box_postprocess", "isb_preprocess",
+    "isb_paste_masks", "isb_paste_class_map", "isb_rpn_filter", "isb_box_postprocess", "isb_box_postprocess_rows", "isb_preprocess",
     "isb_rcnn_transform",
 )
 
@@ -127,6 +127,8 @@ def load():
         lib.isb_rpn_filter.argtypes = [vp, vp, vp, C.POINTER(i32), i32, i32, i32, i32, i32, f64, f32, f32, vp, vp, vp, vp]
         lib.isb_box_postprocess.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, f32, f32, f32, f32, f64, i32,
                                             vp, vp, vp, vp, vp]
+        lib.isb_box_postprocess_rows.argtypes = [vp, vp, vp, vp, vp, i32, vp, i32, i32, i32, f32, f32, f32, f32, f32, f32, f64, i32,
+                                                 vp, vp, vp, vp, vp]
         lib.isb_rcnn_transform.argtypes = [vp, vp, i32, i32, i32, i32, C.POINTER(f32), C.POINTER(f32), vp, i32, i32, vp]
         lib.isb_preprocess.argtypes = [vp, vp, i32, i32, i32, i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double), vp, vp, vp]
         for name in SYMBOLS:

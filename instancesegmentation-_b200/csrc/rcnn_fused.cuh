@@ -426,7 +426,8 @@ __global__ void __launch_bounds__(kFuThreads, 1) boxpost_fused_kernel(const BoxF
 
   // ---- P0: a warp per proposal row: softmax (:401), decode (:398), clip (:404), score / size filters (:437-442);
   //          every survivor joins its class's list with the key (score, row * C + class) -- at most one per row and class ----
-  for (int r = blockIdx.x * kFuWarps + (tid >> 5); r < p.R; r += nblocks * kFuWarps) {
+  const int rows = boxpost_rows(p);
+  for (int r = blockIdx.x * kFuWarps + (tid >> 5); r < rows; r += nblocks * kFuWarps) {
     float mx = -INFINITY, sum = 0.0f;
     if (!p.probs) {
       for (int c = lane; c < p.C; c += 32) mx = fmaxf(mx, p.logits[(size_t)r * p.C + c]);

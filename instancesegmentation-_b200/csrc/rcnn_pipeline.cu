@@ -246,7 +246,14 @@ struct BoxPostParams {
   const float4* proposals;  // [R]
   int R, C;
   float wx, wy, ww, wh, clip, img_w, img_h, score_thresh;
+  const int32_t* R_dev;  // optional: number of valid rows (<= R) in device memory; rows past it are ignored
 };
+
+__device__ __forceinline__ int boxpost_rows(const BoxPostParams& p) {
+  if (!p.R_dev) return p.R;
+  const int r = *p.R_dev;
+  return r < 0 ? 0 : (r < p.R ? r : p.R);
+}
 
 // pass 0: count candidates per row (row_count); pass 1: write them at row_offset in class order.
 template <int PASS>
@@ -257,6 +264,10 @@ __global__ void __launch_bounds__(256) boxpost_rows_kernel(BoxPostParams p, int3
   const int lane = threadIdx.x & 31;
   const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (r >= p.R) return;
+  if (r >= boxpost_rows(p)) {  // padded rows of a sync-free pipeline: no candidates
+    if (!PASS && lane == 0) row_count[r] = 0;
+    return;
+  }
   float mx = -INFINITY, sum = 0.0f;
   if (!p.probs) {
     for (int c = lane; c < p.C; c += 32) mx = fmaxf(mx, p.logits[(size_t)r * p.C + c]);
@@ -619,12 +630,12 @@ extern "C" int isb_rpn_filter(isb_handle* h, const float* proposals, const float
   });
 }
 
-extern "C" int isb_box_postprocess(isb_handle* h, const float* class_logits, const float* class_probs,
-                                   const float* box_regression, const float* proposals, int32_t num_rois,
-                                   int32_t num_classes, int32_t img_h, int32_t img_w, float wx, float wy, float ww,
-                                   float wh, float clip, float score_thresh, double nms_thresh, int32_t detections_per_img,
-                                   float* out_boxes, float* out_scores, int64_t* out_labels, int32_t* out_count,
-                                   isb_stream stream) {
+static int box_postprocess_impl(isb_handle* h, const float* class_logits, const float* class_probs,
+                                const float* box_regression, const float* proposals, int32_t num_rois,
+                                const int32_t* num_rois_dev, int32_t num_classes, int32_t img_h, int32_t img_w, float wx,
+                                float wy, float ww, float wh, float clip, float score_thresh, double nms_thresh,
+                                int32_t detections_per_img, float* out_boxes, float* out_scores, int64_t* out_labels,
+                                int32_t* out_count, isb_stream stream) {
   if (!h) return ISB_ERR_BAD_ARG;
   if ((!class_logits && !class_probs) || !box_regression || !proposals || !out_boxes || !out_scores || !out_labels ||
       !out_count)
@@ -661,6 +672,7 @@ extern "C" int isb_box_postprocess(isb_handle* h, const float* class_logits, con
       fp.bp.reg = reinterpret_cast<const float4*>(box_regression);
       fp.bp.proposals = reinterpret_cast<const float4*>(proposals);
       fp.bp.R = num_rois;
+      fp.bp.R_dev = num_rois_dev;
       fp.bp.C = num_classes;
       fp.bp.wx = wx; fp.bp.wy = wy; fp.bp.ww = ww; fp.bp.wh = wh; fp.bp.clip = clip;
       fp.bp.img_w = (float)img_w; fp.bp.img_h = (float)img_h;
@@ -685,7 +697,8 @@ extern "C" int isb_box_postprocess(isb_handle* h, const float* class_logits, con
   if (rc != ISB_OK) return rc;
   if ((rc = ensure_nms_ws(h, n_cap)) != ISB_OK) return rc;
   KeyBuilder key;
-  key.add(class_logits); key.add(class_probs); key.add(box_regression); key.add(proposals); key.add(num_rois); key.add(num_classes);
+  key.add(class_logits); key.add(class_probs); key.add(box_regression); key.add(proposals); key.add(num_rois); key.add(num_rois_dev);
+  key.add(num_classes);
   key.add(img_h); key.add(img_w); key.add(wx); key.add(wy); key.add(ww); key.add(wh); key.add(clip); key.add(score_thresh);
   key.add(nms_thresh); key.add(detections_per_img); key.add(out_boxes); key.add(out_scores); key.add(out_labels); key.add(out_count);
   key_workspace(key, h);
@@ -705,6 +718,7 @@ extern "C" int isb_box_postprocess(isb_handle* h, const float* class_logits, con
     bp.reg = reinterpret_cast<const float4*>(box_regression);
     bp.proposals = reinterpret_cast<const float4*>(proposals);
     bp.R = num_rois;
+    bp.R_dev = num_rois_dev;
     bp.C = num_classes;
     bp.wx = wx; bp.wy = wy; bp.ww = ww; bp.wh = wh; bp.clip = clip;
     bp.img_w = (float)img_w; bp.img_h = (float)img_h;
@@ -733,4 +747,27 @@ extern "C" int isb_box_postprocess(isb_handle* h, const float* class_logits, con
     ISB_LAUNCH_CHECK(h, "boxpost_gather_kernel");
     return ISB_OK;
   });
+}
+
+extern "C" int isb_box_postprocess(isb_handle* h, const float* class_logits, const float* class_probs,
+                                   const float* box_regression, const float* proposals, int32_t num_rois,
+                                   int32_t num_classes, int32_t img_h, int32_t img_w, float wx, float wy, float ww,
+                                   float wh, float clip, float score_thresh, double nms_thresh, int32_t detections_per_img,
+                                   float* out_boxes, float* out_scores, int64_t* out_labels, int32_t* out_count,
+                                   isb_stream stream) {
+  return box_postprocess_impl(h, class_logits, class_probs, box_regression, proposals, num_rois, nullptr, num_classes, img_h, img_w,
+                              wx, wy, ww, wh, clip, score_thresh, nms_thresh, detections_per_img, out_boxes, out_scores, out_labels,
+                              out_count, stream);
+}
+
+extern "C" int isb_box_postprocess_rows(isb_handle* h, const float* class_logits, const float* class_probs,
+                                        const float* box_regression, const float* proposals, int32_t max_rois,
+                                        const int32_t* num_rois_dev, int32_t num_classes, int32_t img_h, int32_t img_w,
+                                        float wx, float wy, float ww, float wh, float clip, float score_thresh,
+                                        double nms_thresh, int32_t detections_per_img, float* out_boxes, float* out_scores,
+                                        int64_t* out_labels, int32_t* out_count, isb_stream stream) {
+  if (h && !num_rois_dev) ISB_FAIL(h, ISB_ERR_BAD_ARG, "box_postprocess_rows: num_rois_dev is null");
+  return box_postprocess_impl(h, class_logits, class_probs, box_regression, proposals, max_rois, num_rois_dev, num_classes, img_h,
+                              img_w, wx, wy, ww, wh, clip, score_thresh, nms_thresh, detections_per_img, out_boxes, out_scores,
+                              out_labels, out_count, stream);
 }

@@ -255,6 +255,69 @@ def roiheads_postprocess_detections(self, class_logits, box_regression, proposal
             [out_l[i, :k] for i, k in enumerate(ks)])
 
 
+# ---------------------------------------------------------------------------- sync-free (padded) forms
+# The reference's return types are lists of variable-length tensors, so the drop-ins above must read the counts on the
+# host once per stage.  A pipeline that keeps everything padded never has to: proposals stay [N, post_nms_top_n, 4] with
+# the valid rows first and ZERO rows after them (RoIAlign of a zero box is harmless), detections [N, detections_per_img, ..],
+# and the counts stay on the device -- `isb_box_postprocess_rows` takes the number of valid proposal rows from device memory.
+# No counterpart in the reference (its stages are separated by Python lists); results are the list forms' results, padded.
+def rpn_filter_proposals_padded(proposals, objectness, image_shapes, num_anchors_per_level, pre_nms_top_n=1000,
+                                post_nms_top_n=1000, nms_thresh=0.7, score_thresh=0.0, min_size=1.0):
+    """`filter_proposals` (rpn_function.py:460-529) without a host read: proposals [N,A,4], objectness [N,A] ->
+    (boxes float32 [N,post,4] zero-padded, scores [N,post], counts int32 [N]) on the device."""
+    num_images = proposals.shape[0]
+    proposals = _cuda_f32(proposals.detach(), "proposals").reshape(num_images, -1, 4)
+    dev = proposals.device
+    objectness = _cuda_f32(objectness.detach(), "objectness").to(dev).reshape(num_images, -1)
+    post, pre = int(post_nms_top_n), int(pre_nms_top_n)
+    nlev = len(num_anchors_per_level)
+    levels = (C.c_int32 * nlev)(*[int(v) for v in num_anchors_per_level])
+    out_b = torch.zeros((num_images, post, 4), dtype=torch.float32, device=dev)
+    out_s = torch.zeros((num_images, post), dtype=torch.float32, device=dev)
+    counts = torch.zeros((num_images,), dtype=torch.int32, device=dev)
+    h = get_handle(dev.index)
+    with _lib.on_device(dev):
+        for i in range(num_images):
+            shp = image_shapes[i]
+            h.check(h.lib.isb_rpn_filter(h.ptr, _ptr(proposals[i]), _ptr(objectness[i]), levels, nlev, int(shp[0]), int(shp[1]),
+                                         pre, post, float(nms_thresh), float(score_thresh), float(min_size),
+                                         _ptr(out_b[i]), _ptr(out_s[i]), C.c_void_p(counts[i:].data_ptr()), _stream(dev)))
+    return out_b, out_s, counts
+
+
+def postprocess_detections_padded(class_logits, box_regression, proposals, proposal_counts, image_shapes,
+                                  weights=(10.0, 10.0, 5.0, 5.0), bbox_xform_clip=BBOX_XFORM_CLIP, score_thresh=0.05,
+                                  nms_thresh=0.5, detections_per_img=100):
+    """`postprocess_detections` (roi_head.py:366-457) without a host read: class_logits [N*R,C], box_regression [N*R,4C],
+    proposals [N,R,4] padded, proposal_counts int32 [N] on the device (rows past a count are ignored) ->
+    (boxes [N,D,4] zero-padded, scores [N,D], labels int64 [N,D], counts int32 [N])."""
+    props = _cuda_f32(proposals.detach(), "proposals")
+    dev = props.device
+    n_img, r = int(props.shape[0]), int(props.shape[1])
+    logits = _cuda_f32(class_logits.detach(), "class_logits").to(dev)
+    reg = _cuda_f32(box_regression.detach(), "box_regression").to(dev)
+    num_classes = logits.shape[-1]
+    if logits.shape[0] != n_img * r or proposal_counts.dtype != torch.int32 or not proposal_counts.is_cuda:
+        raise ValueError("postprocess_detections_padded: class_logits must have N*R rows, proposal_counts must be CUDA int32")
+    d = int(detections_per_img)
+    wx, wy, ww, wh = [float(w) for w in weights]
+    out_b = torch.zeros((n_img, d, 4), dtype=torch.float32, device=dev)
+    out_s = torch.zeros((n_img, d), dtype=torch.float32, device=dev)
+    out_l = torch.zeros((n_img, d), dtype=torch.int64, device=dev)
+    counts = torch.zeros((n_img,), dtype=torch.int32, device=dev)
+    h = get_handle(dev.index)
+    null = C.c_void_p(0)
+    with _lib.on_device(dev):
+        for i in range(n_img):
+            shp = image_shapes[i]
+            h.check(h.lib.isb_box_postprocess_rows(h.ptr, _ptr(logits[i * r:(i + 1) * r]), null, _ptr(reg[i * r:(i + 1) * r]),
+                                                   _ptr(props[i]), r, C.c_void_p(proposal_counts[i:].data_ptr()), num_classes,
+                                                   int(shp[0]), int(shp[1]), wx, wy, ww, wh, float(bbox_xform_clip),
+                                                   float(score_thresh), float(nms_thresh), d, _ptr(out_b[i]), _ptr(out_s[i]),
+                                                   _ptr(out_l[i]), C.c_void_p(counts[i:].data_ptr()), _stream(dev)))
+    return out_b, out_s, out_l, counts
+
+
 def transform_postprocess(self, result, image_shapes, original_image_sizes):
     """`GeneralizedRCNNTransform.postprocess(self, result, image_shapes, original_image_sizes)` (transform.py:388-418):
     per image, boxes back to the original frame (resize_boxes :462) and the 28x28 mask probabilities pasted into

@@ -1,4 +1,9 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout -s KILL 300 python -m pytest tests/test_maskrcnn_gpu.py -m gpu -q -x -k "roi_align and not rows_kernel" 2>&1 | tail -2
-timeout -s KILL 300 python tools/bench_roi_shapes.py 2> gpurun_out/q_rs.err | tr -d '\n '; echo
+timeout -s KILL 600 python bench.py --no-cpu-baseline > gpurun_out/q_bench.json 2> gpurun_out/q_bench.err; echo "bench rc=$?"; tail -3 gpurun_out/q_bench.err
+python - <<'PY'
+import json
+d=json.loads(open("gpurun_out/q_bench.json").read().strip().splitlines()[-1])
+mv=d["maskrcnn_variant"]
+print({k[:28]: round(v["us"],1) for k,v in mv["stages"].items()}, mv["total_us"], mv["sync_free_pipeline"])
+PY
