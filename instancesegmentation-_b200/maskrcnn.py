@@ -353,7 +353,8 @@ class MultiScaleRoIAlign(torchvision.ops.MultiScaleRoIAlign):
             self.scales = [_infer_scale(f.shape[-2], max_h) for f in feats]
             self._k_min = int(-np.log2(np.float32(self.scales[0])))
             self._k_max = int(-np.log2(np.float32(self.scales[-1])))
-        concat = _cuda_f32(torch.cat(boxes, dim=0), "boxes").to(dev)
+        # (one image: no copy of the boxes; torch.cat of a single tensor still launches a kernel)
+        concat = _cuda_f32(boxes[0] if len(boxes) == 1 else torch.cat(boxes, dim=0), "boxes").to(dev)
         k = concat.shape[0]
         batch_idx = None
         if len(boxes) > 1:
@@ -361,15 +362,22 @@ class MultiScaleRoIAlign(torchvision.ops.MultiScaleRoIAlign):
         c = feats[0].shape[1]
         oh, ow = self.output_size
         out = torch.empty((k, c, oh, ow), dtype=torch.float32, device=dev)
-        cfg = RoiAlignCfg()
-        cfg.num_levels = len(feats)
-        for i, f in enumerate(feats):
-            cfg.feat[i] = f.data_ptr()
-            cfg.feat_h[i], cfg.feat_w[i] = f.shape[-2], f.shape[-1]
-            cfg.scale[i] = self.scales[i]
-        cfg.k_min, cfg.k_max = self._k_min, self._k_max
-        cfg.canonical_scale, cfg.canonical_level = int(self.canonical_scale), int(self.canonical_level)
-        cfg.channels, cfg.out_h, cfg.out_w, cfg.sampling_ratio = c, oh, ow, int(self.sampling_ratio)
+        # the C struct is rebuilt only when the feature maps moved or changed shape (steady state of a loop: never)
+        sig = tuple((f.data_ptr(), f.shape[-2], f.shape[-1]) for f in feats) + (c, oh, ow)
+        cached = getattr(self, "_isb_cfg", None)
+        if cached is not None and cached[0] == sig:
+            cfg = cached[1]
+        else:
+            cfg = RoiAlignCfg()
+            cfg.num_levels = len(feats)
+            for i, f in enumerate(feats):
+                cfg.feat[i] = f.data_ptr()
+                cfg.feat_h[i], cfg.feat_w[i] = f.shape[-2], f.shape[-1]
+                cfg.scale[i] = self.scales[i]
+            cfg.k_min, cfg.k_max = self._k_min, self._k_max
+            cfg.canonical_scale, cfg.canonical_level = int(self.canonical_scale), int(self.canonical_level)
+            cfg.channels, cfg.out_h, cfg.out_w, cfg.sampling_ratio = c, oh, ow, int(self.sampling_ratio)
+            self._isb_cfg = (sig, cfg)
         bptr = _ptr(batch_idx) if batch_idx is not None else C.c_void_p(0)
         _call(dev, lambda h: h.lib.isb_ms_roi_align(h.ptr, C.byref(cfg), _ptr(concat), bptr, k, _ptr(out), _stream(dev)))
         return out
@@ -381,7 +389,7 @@ def maskrcnn_inference(x, labels):
     x = _cuda_f32(x, "mask logits")
     dev = x.device
     boxes_per_image = [label.shape[0] for label in labels]
-    lab = torch.cat(labels).to(device=dev, dtype=torch.int64).contiguous()
+    lab = (labels[0] if len(labels) == 1 else torch.cat(labels)).to(device=dev, dtype=torch.int64).contiguous()
     m, c, s = x.shape[0], x.shape[1], x.shape[-1]
     out = torch.empty((m, 1, s, s), dtype=torch.float32, device=dev)
     _call(dev, lambda h: h.lib.isb_mask_select_sigmoid(h.ptr, _ptr(x), _ptr(lab), m, c, s, _ptr(out), _stream(dev)))
