@@ -80,6 +80,20 @@ def test_verseg_fast_nms():
     assert digest(k) == str(g["coef_digest"])
 
 
+@pytest.mark.parametrize("case", range(6))
+def test_fast_nms_list_structures(case):
+    """Many short class lists, lists longer than top_k, a few long lists, a full 4096-candidate buffer, a handful of
+    candidates: the reference's own fast_non_max_suppression outputs (oracle/gen_golden_fnms.py) pin the oracle."""
+    from oracle.gen_golden_fnms import fnms_case_inputs
+    g = load_golden("fnms_lists")
+    n, c, top_k, max_det = [int(v) for v in g[f"c{case}_params"]]
+    box, score, coef = [t.numpy() for t in fnms_case_inputs(n, c)]
+    assert digest(box, score, coef) == str(g[f"c{case}_digest"])
+    b, s, cl, k = O.fast_non_max_suppression(box, score, coef, 0.5, top_k, max_det)
+    assert np.array_equal(s, g[f"c{case}_score"]) and np.array_equal(cl, g[f"c{case}_cls"])
+    assert np.array_equal(b, g[f"c{case}_box"]) and np.array_equal(k, g[f"c{case}_coef"])
+
+
 def test_traditional_nms_known_answers():
     """utils_bbox.py:102-140 and the traditional_nms=True branch of decode_nms, pinned to the reference run on CPU."""
     g = load_golden("yolact_traditional")

@@ -199,6 +199,21 @@ def test_verseg_fast_nms(bu):
     assert np.array_equal(host(s), g["score"]) and np.array_equal(host(b), g["box"]) and np.array_equal(host(c), g["cls"])
 
 
+@pytest.mark.parametrize("case", range(6))
+def test_fast_nms_list_structures_vs_reference_golden(bu, case):
+    """The single-CTA Fast NMS kernel on the list structures it treats differently (sort-free class walk, rank counting for
+    lists longer than top_k, bitonic fallback, full buffer) against the REFERENCE's outputs (oracle/gen_golden_fnms.py)."""
+    from oracle.gen_golden import digest
+    from oracle.gen_golden_fnms import fnms_case_inputs
+    g = load_golden("fnms_lists")
+    n, c, top_k, max_det = [int(v) for v in g[f"c{case}_params"]]
+    box, score, coef = fnms_case_inputs(n, c)
+    assert digest(box.numpy(), score.numpy(), coef.numpy()) == str(g[f"c{case}_digest"]), "seeded inputs differ from the golden's"
+    b, s, cl, k = bu.fast_non_max_suppression(box.cuda(), score.cuda(), coef.cuda(), 0.5, top_k, max_det)
+    assert np.array_equal(host(s), g[f"c{case}_score"]) and np.array_equal(host(cl), g[f"c{case}_cls"])
+    assert np.array_equal(host(b), g[f"c{case}_box"]) and np.array_equal(host(k), g[f"c{case}_coef"])
+
+
 def test_candidate_overflow_grows_workspace(bu, monkeypatch):
     # confidence 0 makes every (anchor, class) entry a candidate: 600*5 = 3000 per image, more than
     # the 1024 the workspace is created with here -> counts = -1 -> the shim grows it and reruns
