@@ -351,7 +351,9 @@ static int detect_k2_k3a(const DetectRange& d, int b0, int nb, cudaStream_t st) 
       mp.peer_index0 = (int32_t)((h->cx_epoch % (uint32_t)h->cx_depth) * (uint32_t)(h->cx_world * h->cx_local) + h->cx_rank * h->cx_local + b0);
       mp.peer_epoch = h->cx_epoch;
     }
+    h->smap_follows_nms = d.ev ? 0 : 1;  // (a profiled call records an event in between)
     rc = launch_masks(h, mp, st, 1);
+    h->smap_follows_nms = 0;
   }
   h->ws_b0 = d.base;
   return rc;
@@ -383,7 +385,9 @@ static int yolact_detect_device(isb_handle* h, const isb_yolact_in* in, const Yo
   h->prof_mid = nullptr;
   if (rc == ISB_OK) {
     const MaskParams mp = mask_params(d, 0, B);
+    h->compose_follows_smap = ev ? 0 : 1;  // (a profiled call records an event in between)
     rc = launch_masks(h, mp, s, 2);
+    h->compose_follows_smap = 0;
   }
   h->ws_images = ws_images_saved;
   if (rc != ISB_OK) return rc;

@@ -65,6 +65,10 @@ constexpr int kSmapMaxBatch = 1024;
 __global__ void __launch_bounds__(kSmapThreads)
 sigmoid_map_kernel(MaskParams p, const DetRec* __restrict__ rec, const int32_t* __restrict__ totals,
                    float* __restrict__ smap, int64_t s_cap, int* __restrict__ compose_counter) {
+  // programmatic dependent launch: the compose kernel that follows may be scheduled as this kernel's CTAs drain and run its
+  // prologue (shared-memory clears, column tap table); it waits (griddepcontrol.wait) before it touches anything written here
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");  // (launched as fast_nms_kernel's programmatic dependent in the fused path)
   if (blockIdx.x == 0 && threadIdx.x == 0) {  // work counters of the compose kernel(s) that follow
     compose_counter[0] = 0;
     compose_counter[kSecondCounter] = 0;
@@ -225,6 +229,8 @@ mask_compose_kernel(MaskParams p, CompGeom g, const DetRec* __restrict__ rec, co
   }
   int dlo0 = 0, dhi0 = 0, dlo1 = 0, dhi1 = 0;  // this warp's dirty byte range in each of its buffers
   unsigned seg_no = 0;
+  // everything above is independent of the kernels before this one; counts, records, sigmoid maps and the work counter are not
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 
   int next_unit = 0;  // kBig: the ticket of the following unit is fetched while this one is processed (units are short there)
   if (kBig && tid == 0) next_unit = atomicAdd(work_counter, 1);
@@ -564,8 +570,22 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s, int which) 
     a.rec = rec; a.rec_stride = p.det_stride; a.smap = smap; a.s_cap = g.s_cap;
     if ((rc = launch_mask_logits_batch(h, a, s)) != ISB_OK) return rc;
   } else {
-    sigmoid_map_kernel<<<h->num_sms * kSmapCtasPerSm, kSmapThreads, (size_t)g.list_cap * sizeof(DetRec), s>>>(
-        p, rec, h->smap_total + h->ws_b0, smap, g.s_cap, counters);
+    cudaLaunchConfig_t lc;
+    memset(&lc, 0, sizeof(lc));
+    lc.gridDim = dim3((unsigned)(h->num_sms * kSmapCtasPerSm));
+    lc.blockDim = dim3(kSmapThreads);
+    lc.dynamicSmemBytes = (size_t)g.list_cap * sizeof(DetRec);
+    lc.stream = s;
+    cudaLaunchAttribute attr;
+    memset(&attr, 0, sizeof(attr));
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    static const bool no_pdl = getenv("ISB_NO_PDL") != nullptr;
+    lc.attrs = &attr;
+    lc.numAttrs = (h->smap_follows_nms && !no_pdl) ? 1 : 0;
+    const cudaError_t le = cudaLaunchKernelEx(&lc, sigmoid_map_kernel, p, (const DetRec*)rec, (const int32_t*)(h->smap_total + h->ws_b0),
+                                              smap, g.s_cap, counters);
+    if (le != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "sigmoid_map_kernel launch: %s", cudaGetErrorString(le));
     ISB_LAUNCH_CHECK(h, "sigmoid_map_kernel");
   }
   if (h->prof_mid) ISB_CUDA(h, cudaEventRecord(h->prof_mid, s));
@@ -614,14 +634,29 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s, int which) 
     int64_t grid = (int64_t)h->num_sms * per_sm;
     if (grid > total_units) grid = total_units;
     int* ctr = counters + (pass ? kSecondCounter : 0);
+    cudaLaunchConfig_t lc;
+    memset(&lc, 0, sizeof(lc));
+    lc.gridDim = dim3((unsigned)grid);
+    lc.blockDim = dim3((unsigned)(nwarps * 32));
+    lc.dynamicSmemBytes = smem;
+    lc.stream = s;
+    cudaLaunchAttribute attr;
+    memset(&attr, 0, sizeof(attr));
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    static const bool no_pdl = getenv("ISB_NO_PDL") != nullptr;
+    lc.attrs = &attr;
+    lc.numAttrs = (pass == 0 && h->compose_follows_smap && !no_pdl) ? 1 : 0;  // only right behind the sigmoid-map kernel of this call
+    cudaError_t le;
     if (mode == kCompMap)
-      mask_compose_kernel<kCompMap, false><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
+      le = cudaLaunchKernelEx(&lc, mask_compose_kernel<kCompMap, false>, p, g, (const DetRec*)rec, (const float*)smap, ctr);
     else if (mode == kCompDense && per_sm == 1)  // very large detection counts: the latency-oriented instantiation
-      mask_compose_kernel<kCompDense, true><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
+      le = cudaLaunchKernelEx(&lc, mask_compose_kernel<kCompDense, true>, p, g, (const DetRec*)rec, (const float*)smap, ctr);
     else if (mode == kCompDense)
-      mask_compose_kernel<kCompDense, false><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
+      le = cudaLaunchKernelEx(&lc, mask_compose_kernel<kCompDense, false>, p, g, (const DetRec*)rec, (const float*)smap, ctr);
     else
-      mask_compose_kernel<kCompPacked, false><<<(unsigned)grid, nwarps * 32, smem, s>>>(p, g, rec, smap, ctr);
+      le = cudaLaunchKernelEx(&lc, mask_compose_kernel<kCompPacked, false>, p, g, (const DetRec*)rec, (const float*)smap, ctr);
+    if (le != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "mask_compose_kernel launch: %s", cudaGetErrorString(le));
     ISB_LAUNCH_CHECK(h, "mask_compose_kernel");
   }
   return ISB_OK;

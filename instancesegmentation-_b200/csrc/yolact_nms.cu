@@ -214,6 +214,8 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
   __shared__ int s_cut;
   __shared__ __align__(16) uint8_t s_sup[kSmemCand];  // sort-free walk: candidate is suppressed / outside its class window
 
+  // the sigmoid-map kernel behind this one may be scheduled onto the idle SMs now (it waits before reading anything)
+  asm volatile("griddepcontrol.launch_dependents;");
   const int b = blockIdx.x;
   const int tid = threadIdx.x;
   const int64_t total = cand_count[b];
