@@ -338,7 +338,9 @@ static int detect_k2_k3a(const DetectRange& d, int b0, int nb, cudaStream_t st) 
     np.peer_epoch = h->cx_epoch;
   }
   h->ws_b0 = d.base + b0;
+  h->nms_follows_cand = d.ev ? 0 : 1;  // (a profiled call records an event in between)
   int rc = launch_fast_nms(h, np, st);
+  h->nms_follows_cand = 0;
   if (rc == ISB_OK) {
     if (d.ev) {
       const cudaError_t e = cudaEventRecord(d.ev[2], st);

@@ -380,6 +380,7 @@ struct isb_handle {
   // optional per-stage event ring (isb_profile_begin / isb_profile_read)
   cudaEvent_t* prof_events;  // [prof_cap][5]
   cudaEvent_t prof_mid;      // set while a profiled call is inside launch_masks
+  int nms_follows_cand;      // fast_nms_kernel right behind candidates_kernel on the stream (fused path): programmatic dependent
   int smap_follows_nms;      // same for the sigmoid-map kernel right behind fast_nms_kernel
   int compose_follows_smap;  // set by the fused path around its compose launch: the sigmoid-map kernel of the same call is the
                              // stream's previous operation, so the compose kernel may be launched as its programmatic dependent

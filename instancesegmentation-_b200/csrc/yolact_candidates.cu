@@ -52,6 +52,7 @@ __device__ __forceinline__ void cand_emit(const CandParams& p, int b, uint32_t e
 __global__ void __launch_bounds__(kCandThreads)
 candidates_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_t* __restrict__ cand_keys, int64_t cap,
                   int64_t key_stride) {
+  asm volatile("griddepcontrol.launch_dependents;");  // fast_nms_kernel may be queued behind this grid's last wave
   __shared__ CandStage st;
   if (threadIdx.x == 0) st.n = 0;
   __syncthreads();

@@ -216,6 +216,7 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
 
   // the sigmoid-map kernel behind this one may be scheduled onto the idle SMs now (it waits before reading anything)
   asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");  // (launched as candidates_kernel's programmatic dependent in the fused path)
   const int b = blockIdx.x;
   const int tid = threadIdx.x;
   const int64_t total = cand_count[b];
@@ -540,11 +541,25 @@ int configure_fast_nms(isb_handle* h) {
 
 int launch_fast_nms(isb_handle* h, const NmsParams& p, cudaStream_t s) {
   const size_t b0 = (size_t)h->ws_b0, cap2 = (size_t)h->cand_cap_pow2;
-  fast_nms_kernel<<<p.batch, kNmsThreads, kNmsSmem, s>>>(
-      p, h->cand_count + b0, h->cand_keys + b0 * cap2, h->det_keys + b0 * cap2, h->cand_box + b0 * cap2,
-      h->lim.cand_capacity, h->cand_cap_pow2, h->det_coef + b0 * h->lim.max_det * ISB_NUM_COEF,
-      h->det_rec + b0 * h->lim.max_det, h->smap_total + b0, h->lim.max_det);
-  ISB_LAUNCH_CHECK(h, "fast_nms_kernel");
+  cudaLaunchConfig_t lc;
+  memset(&lc, 0, sizeof(lc));
+  lc.gridDim = dim3((unsigned)p.batch);
+  lc.blockDim = dim3(kNmsThreads);
+  lc.dynamicSmemBytes = kNmsSmem;
+  lc.stream = s;
+  cudaLaunchAttribute attr;
+  memset(&attr, 0, sizeof(attr));
+  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr.val.programmaticStreamSerializationAllowed = 1;
+  static const bool no_pdl = getenv("ISB_NO_PDL") != nullptr;
+  lc.attrs = &attr;
+  lc.numAttrs = (h->nms_follows_cand && !no_pdl) ? 1 : 0;
+  const cudaError_t le = cudaLaunchKernelEx(
+      &lc, fast_nms_kernel, p, (const int32_t*)(h->cand_count + b0), h->cand_keys + b0 * cap2, h->det_keys + b0 * cap2,
+      h->cand_box + b0 * cap2, (int64_t)h->lim.cand_capacity, (int64_t)h->cand_cap_pow2,
+      h->det_coef + b0 * h->lim.max_det * ISB_NUM_COEF, h->det_rec + b0 * h->lim.max_det, h->smap_total + b0, (int)h->lim.max_det);
+  if (le != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "fast_nms_kernel launch: %s", cudaGetErrorString(le));
+  h->launches++;
   return ISB_OK;
 }
 
