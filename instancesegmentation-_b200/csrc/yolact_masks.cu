@@ -646,7 +646,9 @@ int launch_masks(isb_handle* h, const MaskParams& p, cudaStream_t s, int which) 
     attr.val.programmaticStreamSerializationAllowed = 1;
     static const bool no_pdl = getenv("ISB_NO_PDL") != nullptr;
     lc.attrs = &attr;
-    lc.numAttrs = (pass == 0 && h->compose_follows_smap && !no_pdl) ? 1 : 0;  // only right behind the sigmoid-map kernel of this call
+    // only right behind the sigmoid-map kernel of this call (the fused path says so; isb_mask_assemble launches both here)
+    const bool behind_smap = h->compose_follows_smap || ((which & 3) == 3 && !h->prof_mid && !(tc_smap && g.list_cap <= kTcBatchMaxDet));
+    lc.numAttrs = (pass == 0 && behind_smap && !no_pdl) ? 1 : 0;
     cudaError_t le;
     if (mode == kCompMap)
       le = cudaLaunchKernelEx(&lc, mask_compose_kernel<kCompMap, false>, p, g, (const DetRec*)rec, (const float*)smap, ctr);
