@@ -296,6 +296,7 @@ template <int CT>
 __global__ void __launch_bounds__(kLgThreads, 2)
 candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_t* __restrict__ cand_keys, int64_t cap,
                          int64_t key_stride, int tiles_per_img, int64_t total_floats) {
+  asm volatile("griddepcontrol.launch_dependents;");  // fast_nms_kernel may be queued behind this grid (fused path)
   extern __shared__ __align__(128) unsigned char lg_smem[];  // [warps][2] tile buffers
   __shared__ __align__(8) uint64_t bars[kLgWarps][2];
   __shared__ LgWarpStage stages[kLgWarps];
