@@ -1,5 +1,6 @@
 // Internal shared declarations for libisb.so (not part of the public ABI).
 #pragma once
+#include <stdlib.h>
 
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -290,6 +291,15 @@ __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// Programmatic dependent launch inside ONE entry point: a kernel that calls pdl_enter() first thing may be launched with
+// launch_chained(..., chained = true) right behind another kernel of the same call -- it is scheduled while its predecessor
+// drains and starts the moment that one has completed (griddepcontrol.wait), which hides the launch latency between
+// short kernels.  Launched normally, pdl_enter() does nothing.
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 __host__ __device__ inline int next_pow2(int v) {
 #ifdef __CUDA_ARCH__
   return v <= 1 ? 1 : 1 << (32 - __clz(v - 1));
@@ -299,6 +309,27 @@ __host__ __device__ inline int next_pow2(int v) {
   return p;
 #endif
 }
+
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chained(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool chained,
+                                  Args... args) {
+  static const bool no_pdl = getenv("ISB_NO_PDL") != nullptr;
+  cudaLaunchConfig_t lc;
+  memset(&lc, 0, sizeof(lc));
+  lc.gridDim = grid;
+  lc.blockDim = block;
+  lc.dynamicSmemBytes = smem;
+  lc.stream = s;
+  cudaLaunchAttribute attr;
+  memset(&attr, 0, sizeof(attr));
+  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr.val.programmaticStreamSerializationAllowed = 1;
+  lc.attrs = &attr;
+  lc.numAttrs = (chained && !no_pdl) ? 1 : 0;
+  return cudaLaunchKernelEx(&lc, kernel, static_cast<KArgs>(args)...);
+}
+#endif
 
 }  // namespace isb
 

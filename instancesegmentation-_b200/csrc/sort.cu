@@ -78,6 +78,7 @@ __global__ void __launch_bounds__(kRankThreads) rank_count_kernel(const uint64_t
                                                                   const int32_t* __restrict__ n_dev, int slice,
                                                                   int32_t* __restrict__ rank) {
   __shared__ uint64_t tile[kRankThreads];
+  pdl_enter();
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   const int i = blockIdx.x * kRankThreads + threadIdx.x;
   if (blockIdx.x * kRankThreads >= n) return;  // CTA-uniform
@@ -98,6 +99,7 @@ __global__ void __launch_bounds__(kRankThreads) rank_count_kernel(const uint64_t
 
 __global__ void rank_scatter_kernel(const uint64_t* __restrict__ keys, int n_max, const int32_t* __restrict__ n_dev,
                                     const int32_t* __restrict__ rank, uint64_t* __restrict__ out) {
+  pdl_enter();
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[rank[i]] = keys[i];
 }
@@ -116,9 +118,11 @@ int launch_rank_sort_u64(isb_handle* h, const uint64_t* keys, int n_max, const i
   slices = (n_max + slice - 1) / slice;
   rank_count_kernel<<<dim3(iblocks, slices), kRankThreads, 0, s>>>(keys, n_max, n_dev, slice, rank);
   ISB_LAUNCH_CHECK(h, "rank_count_kernel");
-  rank_scatter_kernel<<<(n_max + 255) / 256 < 4 * h->num_sms ? (n_max + 255) / 256 : 4 * h->num_sms, 256, 0, s>>>(keys, n_max, n_dev,
-                                                                                                                 rank, out);
-  ISB_LAUNCH_CHECK(h, "rank_scatter_kernel");
+  const int sblocks = (n_max + 255) / 256 < 4 * h->num_sms ? (n_max + 255) / 256 : 4 * h->num_sms;
+  const cudaError_t le = launch_chained(rank_scatter_kernel, dim3(sblocks), dim3(256), 0, s, true, keys, n_max, n_dev,
+                                        (const int32_t*)rank, out);  // right behind rank_count_kernel
+  if (le != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "launch rank_scatter_kernel: %s", cudaGetErrorString(le));
+  h->launches++;
   return ISB_OK;
 }
 

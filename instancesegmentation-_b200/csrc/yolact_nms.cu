@@ -429,12 +429,14 @@ fast_nms_kernel(NmsParams p, const int32_t* __restrict__ cand_count, uint64_t* _
 // sort of the keys, boxes + class starts, pair tests with 32 candidates per CTA, sort of the kept keys, emit.
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void fnms_fill_kernel(uint64_t* __restrict__ keys, int from, int to, int32_t* __restrict__ zero) {
+  pdl_enter();
   for (int i = from + blockIdx.x * blockDim.x + threadIdx.x; i < to; i += gridDim.x * blockDim.x) keys[i] = kPadKey;
   if (zero && blockIdx.x == 0 && threadIdx.x == 0) *zero = 0;
 }
 
 __global__ void fnms_prepare_kernel(NmsParams p, const uint64_t* __restrict__ keys, int n, float4* __restrict__ cbox,
                                     int32_t* __restrict__ cls_start) {
+  pdl_enter();
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const uint64_t k = keys[i];
     cbox[i] = load_box(p, 0, cand_row(k));
@@ -450,6 +452,7 @@ constexpr int kWideThreads = 256;  // 8 candidates per CTA, one warp each
 __global__ void __launch_bounds__(kWideThreads)
 fnms_pairs_kernel(NmsParams p, const uint64_t* __restrict__ keys, const float4* __restrict__ cbox,
                   const int32_t* __restrict__ cls_start, int n, uint64_t* __restrict__ dkeys, int32_t* __restrict__ kept) {
+  pdl_enter();
   const int lane = threadIdx.x & 31;
   const bool thr_ok = 0.0f <= p.nms_iou;
   // the longest lists (highest j of a class) first: they decide when the kernel ends
@@ -481,6 +484,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1)
 fnms_emit_kernel(NmsParams p, const uint64_t* __restrict__ dkeys, const int32_t* __restrict__ kept, float* __restrict__ det_coef_ws,
                  DetRec* __restrict__ det_rec_ws, int32_t* __restrict__ smap_total_ws, int ws_det_stride) {
   __shared__ int s_scan[32];
+  pdl_enter();
   const int m = min(*kept, p.max_det);
   fnms_emit(p, 0, dkeys, m, det_coef_ws, det_rec_ws, smap_total_ws, ws_det_stride, s_scan);
   if (threadIdx.x == 0) p.out_count[0] = m;
@@ -506,15 +510,22 @@ int launch_fast_nms_wide(isb_handle* h, const NmsParams& p, int n, cudaStream_t 
     // holds no boxes.  keys -> sorted in dkeys -> boxes -> kept keys back into `keys` -> sorted in dkeys -> emit.
     int32_t* rank = reinterpret_cast<int32_t*>(cbox);
     if ((rc = launch_rank_sort_u64(h, keys, n, nullptr, rank, dkeys, s)) != ISB_OK) return rc;
-    fnms_prepare_kernel<<<(n + 255) / 256, 256, 0, s>>>(p, dkeys, n, cbox, cls_start);
-    ISB_LAUNCH_CHECK(h, "fnms_prepare_kernel");
-    fnms_fill_kernel<<<1, 32, 0, s>>>(keys, 0, 0, kept);  // kept = 0
-    ISB_LAUNCH_CHECK(h, "fnms_fill_kernel");
-    fnms_pairs_kernel<<<pair_grid, kWideThreads, 0, s>>>(p, dkeys, cbox, cls_start, n, keys, kept);
-    ISB_LAUNCH_CHECK(h, "fnms_pairs_kernel");
+    // every kernel from here on is launched as the programmatic dependent of the one before it (pdl_enter): the chain is
+    // eight short kernels, and the launch latency between them was a sixth of its 76 us
+    cudaError_t le;
+    le = launch_chained(fnms_prepare_kernel, dim3((n + 255) / 256), dim3(256), 0, s, true, p, (const uint64_t*)dkeys, n, cbox, cls_start);
+    if (le != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "launch fnms_prepare_kernel: %s", cudaGetErrorString(le));
+    le = launch_chained(fnms_fill_kernel, dim3(1), dim3(32), 0, s, true, keys, 0, 0, kept);  // kept = 0
+    if (le != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "launch fnms_fill_kernel: %s", cudaGetErrorString(le));
+    le = launch_chained(fnms_pairs_kernel, dim3(pair_grid), dim3(kWideThreads), 0, s, true, p, (const uint64_t*)dkeys,
+                        (const float4*)cbox, (const int32_t*)cls_start, n, keys, kept);
+    if (le != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "launch fnms_pairs_kernel: %s", cudaGetErrorString(le));
+    h->launches += 3;
     if ((rc = launch_rank_sort_u64(h, keys, n, kept, rank, dkeys, s)) != ISB_OK) return rc;
-    fnms_emit_kernel<<<1, kNmsThreads, 0, s>>>(p, dkeys, kept, coef_ws, rec_ws, h->smap_total + b0, h->lim.max_det);
-    ISB_LAUNCH_CHECK(h, "fnms_emit_kernel");
+    le = launch_chained(fnms_emit_kernel, dim3(1), dim3(kNmsThreads), 0, s, true, p, (const uint64_t*)dkeys, (const int32_t*)kept,
+                        coef_ws, rec_ws, h->smap_total + b0, (int)h->lim.max_det);
+    if (le != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "launch fnms_emit_kernel: %s", cudaGetErrorString(le));
+    h->launches++;
     return ISB_OK;
   }
   fnms_fill_kernel<<<8, 256, 0, s>>>(keys, n, np2, nullptr);
