@@ -574,7 +574,7 @@ int launch_counts_wait(isb_handle* h, const unsigned long long* slot, int n, uns
                        int32_t* status, long long timeout_ns, cudaStream_t s);
 int launch_sort_u64(isb_handle* h, uint64_t* keys, int n_pow2, cudaStream_t s);
 int launch_rank_sort_u64(isb_handle* h, const uint64_t* keys, int n_max, const int32_t* n_dev, int32_t* rank, uint64_t* out,
-                         cudaStream_t s);
+                         cudaStream_t s, bool rank_is_zero = false);
 constexpr int kRankSortMax = 32768;  // above this the O(n^2) rank sort loses to the bitonic network
 int ensure_nms_ws(isb_handle* h, int64_t n);
 int ensure_scratch(isb_handle* h, size_t bytes);

@@ -46,6 +46,7 @@ __global__ void nms_max_coord_kernel(const float4* __restrict__ boxes, int n_max
 // label << 20 | index, so equal scores order by class first -- the order of the reference's per-class concatenation.
 __global__ void nms_keys_kernel(const float* __restrict__ scores, const int32_t* __restrict__ labels, int n_max,
                                 const int32_t* __restrict__ n_dev, int n_pow2, uint64_t* __restrict__ keys) {
+  pdl_enter();
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pow2; i += gridDim.x * blockDim.x) {
     uint32_t low = (uint32_t)i;
@@ -59,6 +60,7 @@ __global__ void nms_gather_kernel(const uint64_t* __restrict__ keys, const float
                                   const int32_t* __restrict__ n_dev, const uint32_t* __restrict__ scalars,
                                   const int32_t* __restrict__ labels, float4* __restrict__ sbox,
                                   int32_t* __restrict__ order, int32_t* __restrict__ slabel) {
+  pdl_enter();
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   const bool batched = idxs64 || idxs32;
   float step = 0.0f;
@@ -88,6 +90,7 @@ __global__ void __launch_bounds__(64) nms_mask_kernel(const float4* __restrict__
                                                       const int32_t* __restrict__ n_dev, float thr, int words,
                                                       const int32_t* __restrict__ slabel, int offset_groups,
                                                       uint64_t* __restrict__ mask) {
+  pdl_enter();
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   // linear block index -> (rb, cb), cb <= rb: rb = floor((sqrt(8 t + 1) - 1) / 2), fixed up for rounding
   const unsigned lin = blockIdx.x;
@@ -145,6 +148,7 @@ __global__ void __launch_bounds__(kScanThreads) nms_scan_kernel(const uint64_t* 
                                                                 const int32_t* __restrict__ order, int n_max,
                                                                 const int32_t* __restrict__ n_dev, int words, int max_keep,
                                                                 int64_t* __restrict__ keep, int32_t* __restrict__ count) {
+  pdl_enter();
   extern __shared__ uint64_t s_kept[];            // [words] kept bitmap over all boxes (score order)
   __shared__ uint32_t s_cur[kScanThreads / 32];   // this round's keep bits of the chunk, one ballot per warp
   __shared__ int s_warp_cnt[kScanThreads / 32];
@@ -283,30 +287,44 @@ int launch_nms(isb_handle* h, const NmsCall& c, cudaStream_t s) {
   if ((double)thr_f > c.iou_threshold) thr_f = nextafterf(thr_f, -INFINITY);
   const bool batched = c.idxs64 || c.idxs32;
   const int blocks = (n + 255) / 256 < 4 * h->num_sms ? (n + 255) / 256 : 4 * h->num_sms;
+  // The memsets go first, so that the five to seven kernels behind them are adjacent on the stream and each can be the
+  // programmatic dependent of the one before (pdl_enter / launch_chained): they are short, and the launch latency between
+  // them was a large part of the call.
+  const bool rank_sort = n <= kRankSortMax;
+  if (rank_sort) ISB_CUDA(h, cudaMemsetAsync(h->nms_rank, 0, (size_t)n * sizeof(int32_t), s));
+  cudaError_t le;
+#define ISB_CHAINED(name, call)                                                                      \
+  do {                                                                                               \
+    le = (call);                                                                                     \
+    if (le != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "launch %s: %s", name, cudaGetErrorString(le)); \
+    h->launches++;                                                                                   \
+  } while (0)
   if (batched) {
     ISB_CUDA(h, cudaMemsetAsync(h->nms_scalars, 0xff, sizeof(uint32_t), s));
     nms_max_coord_kernel<<<blocks, 256, 0, s>>>(c.boxes, n, c.n_dev, h->nms_scalars);
     ISB_LAUNCH_CHECK(h, "nms_max_coord_kernel");
   }
-  nms_keys_kernel<<<(n_pow2 + 255) / 256, 256, 0, s>>>(c.scores, c.labels32, n, c.n_dev, n_pow2, h->nms_keys);
-  ISB_LAUNCH_CHECK(h, "nms_keys_kernel");
+  ISB_CHAINED("nms_keys_kernel", launch_chained(nms_keys_kernel, dim3((n_pow2 + 255) / 256), dim3(256), 0, s, batched, c.scores,
+                                                c.labels32, n, c.n_dev, n_pow2, h->nms_keys));
   const uint64_t* sorted = h->nms_keys;
-  if (n <= kRankSortMax) {
-    if ((rc = launch_rank_sort_u64(h, h->nms_keys, n, c.n_dev, h->nms_rank, h->nms_keys2, s)) != ISB_OK) return rc;
+  if (rank_sort) {
+    if ((rc = launch_rank_sort_u64(h, h->nms_keys, n, c.n_dev, h->nms_rank, h->nms_keys2, s, true)) != ISB_OK) return rc;
     sorted = h->nms_keys2;
   } else if ((rc = launch_sort_u64(h, h->nms_keys, n_pow2, s)) != ISB_OK) {
     return rc;
   }
-  nms_gather_kernel<<<blocks, 256, 0, s>>>(sorted, c.boxes, c.idxs64, c.idxs32, n, c.n_dev, h->nms_scalars,
-                                           c.labels32, h->nms_sbox, h->nms_order, h->nms_slabel);
-  ISB_LAUNCH_CHECK(h, "nms_gather_kernel");
-  nms_mask_kernel<<<(unsigned)((int64_t)words * (words + 1) / 2), 64, 0, s>>>(h->nms_sbox, n, c.n_dev, thr_f, words,
-                                                    (c.labels32 || c.idxs32) ? h->nms_slabel : nullptr, c.labels32 ? 0 : 1, h->nms_mask);
-  ISB_LAUNCH_CHECK(h, "nms_mask_kernel");
+  ISB_CHAINED("nms_gather_kernel", launch_chained(nms_gather_kernel, dim3(blocks), dim3(256), 0, s, rank_sort, sorted, c.boxes, c.idxs64,
+                                                  c.idxs32, n, c.n_dev, (const uint32_t*)h->nms_scalars, c.labels32, h->nms_sbox,
+                                                  h->nms_order, h->nms_slabel));
+  ISB_CHAINED("nms_mask_kernel",
+              launch_chained(nms_mask_kernel, dim3((unsigned)((int64_t)words * (words + 1) / 2)), dim3(64), 0, s, true,
+                             (const float4*)h->nms_sbox, n, c.n_dev, thr_f, words,
+                             (const int32_t*)((c.labels32 || c.idxs32) ? h->nms_slabel : nullptr), c.labels32 ? 0 : 1, h->nms_mask));
   const size_t smem = (size_t)words * 8;
   if (smem > 64 * 1024) ISB_FAIL(h, ISB_ERR_LIMIT, "nms scan shared memory");
-  nms_scan_kernel<<<1, kScanThreads, smem, s>>>(h->nms_mask, h->nms_order, n, c.n_dev, words, c.max_keep, c.keep, c.count);
-  ISB_LAUNCH_CHECK(h, "nms_scan_kernel");
+  ISB_CHAINED("nms_scan_kernel", launch_chained(nms_scan_kernel, dim3(1), dim3(kScanThreads), smem, s, true, (const uint64_t*)h->nms_mask,
+                                                (const int32_t*)h->nms_order, n, c.n_dev, words, c.max_keep, c.keep, c.count));
+#undef ISB_CHAINED
   return ISB_OK;
 }
 

@@ -106,9 +106,11 @@ __global__ void rank_scatter_kernel(const uint64_t* __restrict__ keys, int n_max
 
 // keys [n] unique -> out [n] ascending; rank: int32 scratch [n_max].  n is min(*n_dev, n_max) when n_dev != nullptr.
 int launch_rank_sort_u64(isb_handle* h, const uint64_t* keys, int n_max, const int32_t* n_dev, int32_t* rank, uint64_t* out,
-                         cudaStream_t s) {
+                         cudaStream_t s, bool rank_is_zero) {
   if (n_max <= 0) return ISB_OK;
-  ISB_CUDA(h, cudaMemsetAsync(rank, 0, (size_t)n_max * sizeof(int32_t), s));
+  // rank_is_zero: the caller cleared rank[0 .. n_max) earlier on the stream and a kernel of the same call is the stream's last
+  // operation, so the count kernel joins the caller's programmatic-dependent chain instead of following a memset node
+  if (!rank_is_zero) ISB_CUDA(h, cudaMemsetAsync(rank, 0, (size_t)n_max * sizeof(int32_t), s));
   const int iblocks = (n_max + kRankThreads - 1) / kRankThreads;
   int slices = (4 * h->num_sms + iblocks - 1) / iblocks;  // enough CTAs for ~4 per SM
   if (slices > iblocks) slices = iblocks;
@@ -116,8 +118,10 @@ int launch_rank_sort_u64(isb_handle* h, const uint64_t* keys, int n_max, const i
   int slice = (n_max + slices - 1) / slices;
   slice = (slice + kRankThreads - 1) / kRankThreads * kRankThreads;
   slices = (n_max + slice - 1) / slice;
-  rank_count_kernel<<<dim3(iblocks, slices), kRankThreads, 0, s>>>(keys, n_max, n_dev, slice, rank);
-  ISB_LAUNCH_CHECK(h, "rank_count_kernel");
+  const cudaError_t lc = launch_chained(rank_count_kernel, dim3(iblocks, slices), dim3(kRankThreads), 0, s, rank_is_zero, keys, n_max,
+                                        n_dev, slice, rank);
+  if (lc != cudaSuccess) ISB_FAIL(h, ISB_ERR_CUDA, "launch rank_count_kernel: %s", cudaGetErrorString(lc));
+  h->launches++;
   const int sblocks = (n_max + 255) / 256 < 4 * h->num_sms ? (n_max + 255) / 256 : 4 * h->num_sms;
   const cudaError_t le = launch_chained(rank_scatter_kernel, dim3(sblocks), dim3(256), 0, s, true, keys, n_max, n_dev,
                                         (const int32_t*)rank, out);  // right behind rank_count_kernel
