@@ -24,7 +24,7 @@ struct AxisTable {
   int in_size, out_size, ksize;
   int32_t* d_bounds;  // [out][2]  first tap, tap count
   int32_t* d_coef;    // [ksize][out]  (transposed: consecutive outputs are adjacent)
-  int groups;         // ceil(ksize / 4)
+  int groups;         // ceil(longest tap run / 4)
   uint32_t* d_pack;   // [groups][3][out]: byte slices 0..2 of the coefficients of taps 4g..4g+3, one byte per tap (dp4a operand)
 };
 
@@ -80,10 +80,13 @@ static int build_axis(isb_handle* h, int in_size, int out_size, AxisTable* t) {
   t->ksize = ksize;
   // coefficient k = k2 * 65536 + k1 * 256 + k0 with k0, k1 unsigned bytes and k2 a signed byte (|k| < 2^23): the
   // horizontal pass forms sum(pixel * k) as three 4-way byte dot products per group of four taps
-  const int groups = (ksize + 3) / 4;
+  // groups of four taps: from the longest tap run that occurs, not from ksize (1920 -> 544: ksize 17, 15 taps at most)
+  int max_taps = 1;
+  for (int xx = 0; xx < out_size; ++xx) max_taps = std::max(max_taps, bounds[2 * xx + 1]);
+  const int groups = (max_taps + 3) / 4;
   std::vector<uint32_t> pack((size_t)groups * 3 * out_size, 0u);
   for (int xx = 0; xx < out_size; ++xx)
-    for (int x = 0; x < ksize; ++x) {
+    for (int x = 0; x < bounds[2 * xx + 1]; ++x) {
       const int32_t k = coef[(size_t)x * out_size + xx];
       if (k >= (1 << 23) || k < -(1 << 23)) ISB_FAIL(h, ISB_ERR_LIMIT, "preprocess: coefficient out of the 24-bit range");
       const uint32_t slice[3] = {(uint32_t)k & 0xffu, ((uint32_t)k >> 8) & 0xffu, ((uint32_t)(k >> 16)) & 0xffu};
@@ -153,13 +156,13 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {  // a: u
   return d;
 }
 
-template <int NG>
-__global__ void __launch_bounds__(kPrepThreads)
+template <int NG, int T>
+__global__ void __launch_bounds__(T)
 prep_horizontal_kernel(const uint8_t* __restrict__ src, size_t src_bytes, int in_h, int in_w, int out_w, int groups, int plane_cap,
                        const int32_t* __restrict__ bounds, const uint32_t* __restrict__ pack, uint8_t* __restrict__ dst, int tpitch) {
   extern __shared__ __align__(16) uint32_t s_planes[];  // [2 buffers][3 planes][plane_cap / 4 words]
   const int tid = threadIdx.x;
-  const int xx0 = blockIdx.x * kPrepThreads, xx1 = min(xx0 + kPrepThreads, out_w) - 1, xx = xx0 + tid;
+  const int xx0 = blockIdx.x * T, xx1 = min(xx0 + T, out_w) - 1, xx = xx0 + tid;
   const int xc = min(xx, out_w - 1);  // threads past the last column compute a duplicate and do not store
   const int y0 = blockIdx.y * kPrepRows, y1 = min(y0 + kPrepRows, in_h), b = blockIdx.z;
   const int span0 = bounds[2 * xx0], span1 = bounds[2 * xx1] + bounds[2 * xx1 + 1];  // input columns [span0, span1)
@@ -181,38 +184,60 @@ prep_horizontal_kernel(const uint8_t* __restrict__ src, size_t src_bytes, int in
   const uint8_t* last = row0 + (size_t)(y1 - 1 - y0) * row_step;
   // block-uniform: every 32-bit load of every row of the block (aligned down, plus one word of slack) is inside the buffer
   const bool inside = row0 >= src + 3 && last + (size_t)units * 12 + 8 <= src_end;
-  auto stage = [&](int y, uint32_t* buf) {
-    const uint8_t* row = row0 + (size_t)(unsigned)(y - y0) * row_step;
-    const int rsh = (int)(reinterpret_cast<uintptr_t>(row) & 3) * 8;  // 12 bytes per unit: the same for every unit of the row
-    const uint8_t* arow = row - (rsh >> 3);
-    for (int u = tid; u < units; u += kPrepThreads) {
-      const uint8_t* p = arow + u * 12;
-      uint32_t w0, w1, w2, w3;
-      if (inside) {
-        const uint32_t* q = reinterpret_cast<const uint32_t*>(p);
-        w0 = __ldg(q); w1 = __ldg(q + 1); w2 = __ldg(q + 2); w3 = __ldg(q + 3);
-      } else {
-        w0 = load_word_guarded(p, src, src_end); w1 = load_word_guarded(p + 4, src, src_end);
-        w2 = load_word_guarded(p + 8, src, src_end); w3 = load_word_guarded(p + 12, src, src_end);
-      }
-      // f0 = [r0 g0 b0 r1]  f1 = [g1 b1 r2 g2]  f2 = [b2 r3 g3 b3]
-      const uint32_t f0 = __funnelshift_r(w0, w1, rsh), f1 = __funnelshift_r(w1, w2, rsh), f2 = __funnelshift_r(w2, w3, rsh);
-      buf[u] = __byte_perm(__byte_perm(f0, f1, 0x0630), f2, 0x5210);
-      buf[pw + u] = __byte_perm(__byte_perm(f0, f1, 0x0741), f2, 0x6210);
-      buf[2 * pw + u] = __byte_perm(__byte_perm(f0, f1, 0x0052), f2, 0x7410);
+  // this thread's first unit (4 pixels = 12 bytes) of the row to stage next; one pointer add per row instead of a fresh
+  // (picture, row, column) address, and the shared-memory addresses of both buffers are fixed registers (the first
+  // version spent 75 of its 180 warp instructions per row on staging, most of them address arithmetic)
+  const uint8_t* up = row0 + (size_t)tid * 12;
+  struct Unit { uint32_t w0, w1, w2, w3; int rsh; };
+  auto fetch = [&](const uint8_t* p, Unit& r) {
+    if (inside) {
+      const uint32_t* q = reinterpret_cast<const uint32_t*>(p);
+      r.w0 = __ldg(q); r.w1 = __ldg(q + 1); r.w2 = __ldg(q + 2); r.w3 = __ldg(q + 3);
+    } else {
+      r.w0 = load_word_guarded(p, src, src_end); r.w1 = load_word_guarded(p + 4, src, src_end);
+      r.w2 = load_word_guarded(p + 8, src, src_end); r.w3 = load_word_guarded(p + 12, src, src_end);
     }
   };
+  auto park = [&](const Unit& r, uint32_t* slot) {
+    // f0 = [r0 g0 b0 r1]  f1 = [g1 b1 r2 g2]  f2 = [b2 r3 g3 b3]
+    const uint32_t f0 = __funnelshift_r(r.w0, r.w1, r.rsh), f1 = __funnelshift_r(r.w1, r.w2, r.rsh),
+                   f2 = __funnelshift_r(r.w2, r.w3, r.rsh);
+    slot[0] = __byte_perm(__byte_perm(f0, f1, 0x0630), f2, 0x5210);
+    slot[pw] = __byte_perm(__byte_perm(f0, f1, 0x0741), f2, 0x6210);
+    slot[2 * pw] = __byte_perm(__byte_perm(f0, f1, 0x0052), f2, 0x7410);
+  };
+  const bool has_unit = tid < units, more_units = units > T;  // the second is block-uniform and false up to 4 : 1
+  // A row is staged in two halves around the reduction of the row before it: the loads are issued first (stage_fetch),
+  // their permutes and shared-memory stores come after the reduction (stage_park), so the global-memory latency is
+  // covered by the thread's own ~90 instructions instead of by other warps only.
+  Unit pend;
+  pend.w0 = pend.w1 = pend.w2 = pend.w3 = 0u; pend.rsh = 0;
+  auto stage_fetch = [&]() {
+    pend.rsh = (int)(reinterpret_cast<uintptr_t>(up) & 3) * 8;  // T * 12 bytes per step: the same for every unit of the row
+    if (has_unit) fetch(up - (pend.rsh >> 3), pend);
+  };
+  auto stage_park = [&](uint32_t* slot) {  // slot = this thread's word of the buffer's first plane
+    if (has_unit) park(pend, slot);
+    if (more_units) {
+      const uint8_t* p = up - (pend.rsh >> 3);
+#pragma unroll 1
+      for (int u = tid + T; u < units; u += T) {
+        Unit r;
+        r.rsh = pend.rsh;
+        fetch(p + (size_t)(u - tid) * 12, r);
+        park(r, slot + (u - tid));
+      }
+    }
+    up += row_step;
+  };
   uint8_t* orow = dst + ((size_t)b * in_h + y0) * (size_t)tpitch + (size_t)xc * 3;
-  stage(y0, s_planes);
-  for (int y = y0; y < y1; ++y) {
-    const uint32_t* buf = s_planes + ((y - y0) & 1) * 3 * pw + wi;
-    __syncthreads();  // row y staged; the other buffer is free again
-    if (y + 1 < y1) stage(y + 1, s_planes + ((y + 1 - y0) & 1) * 3 * pw);
+  const bool store = xx < out_w;
+  auto reduce_row = [&](const uint32_t* buf) {  // buf = first word of this column's taps in the first plane
     int res[3];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
       const uint32_t* pl = buf + c * pw;
-      int s0 = 0, s1 = 0, s2 = 0;
+      int s0 = 1 << (kPrecisionBits - 1), s1 = 0, s2 = 0;  // the rounding term rides in the low slice
       uint32_t prev = pl[0];
       if (NG > 0) {
 #pragma unroll
@@ -236,14 +261,100 @@ prep_horizontal_kernel(const uint8_t* __restrict__ src, size_t src_bytes, int in
         }
       }
       // modulo 2^32 like Resample.c's int accumulator: the slices may wrap, the total does not
-      res[c] = (int)((1u << (kPrecisionBits - 1)) + (uint32_t)s0 + ((uint32_t)s1 << 8) + ((uint32_t)s2 << 16));
+      res[c] = (int)((uint32_t)s0 + ((uint32_t)s1 << 8) + ((uint32_t)s2 << 16));
     }
-    if (xx < out_w) {
+    if (store) {
       orow[0] = clip8(res[0]);
       orow[1] = clip8(res[1]);
       orow[2] = clip8(res[2]);
     }
     orow += tpitch;
+  };
+  // two rows per trip so that the buffer a row is staged into / reduced from is known at compile time
+  uint32_t* const slot0 = s_planes + tid;
+  uint32_t* const slot1 = slot0 + 3 * pw;
+  const uint32_t* const taps0 = s_planes + wi;
+  const uint32_t* const taps1 = taps0 + 3 * pw;
+  // ---- asynchronous staging (every block whose 16-byte chunks lie inside the caller's buffer) --------------------------
+  // ncu on the register-staged loop: the first dp4a of every row waited ~35 % of the kernel on a long scoreboard although
+  // its operands come from shared memory -- the row's global loads and its tap loads share scoreboard counters, so
+  // issuing the loads early did not hide their latency.  LDGSTS has no register scoreboard: the raw bytes of row y + 4 go
+  // from global to a 4-slot shared-memory ring in 16-byte chunks (one per thread), completion is a cp.async group wait
+  // three rows later, and the de-interleaving into planes reads the ring.
+  const int raw_cap = (plane_cap * 3 + 48 + 15) & ~15;  // bytes per ring slot (launch_preprocess sizes the same)
+  uint8_t* const ring = reinterpret_cast<uint8_t*>(s_planes) + ((6 * plane_cap + 15) & ~15);
+  const uint8_t* const first16 = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(row0) & ~(uintptr_t)15);
+  const bool inside16 = inside && first16 >= src &&
+                        reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(last) & ~(uintptr_t)15) + raw_cap <= src_end;
+  if (inside16) {
+    const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
+    const uint8_t* rowp = row0;  // row whose copy is issued next
+    int issued = 0;              // rows issued so far
+    const int nrows = y1 - y0;
+    auto issue = [&]() {         // one commit group per call, empty past the last row
+      if (issued < nrows) {
+        const uintptr_t a16 = reinterpret_cast<uintptr_t>(rowp) & ~(uintptr_t)15;
+        const int d = (int)(reinterpret_cast<uintptr_t>(rowp) - a16);
+        const int chunks = (d + units * 12 + 4 + 15) >> 4;
+        const uint32_t dst = ring_s + (uint32_t)(issued & 3) * (uint32_t)raw_cap;
+#pragma unroll 1
+        for (int c = tid; c < chunks; c += T)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * c), "l"(a16 + 16u * (unsigned)c) : "memory");
+        rowp += row_step;
+      }
+      ++issued;
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    const uint8_t* parkp = row0;  // row parked next
+    int parked = 0;
+    auto park_raw = [&](uint32_t* slot) {
+      const int d = (int)(reinterpret_cast<uintptr_t>(parkp) & 15);
+      const uint8_t* raw = ring + (parked & 3) * raw_cap;
+      Unit r;
+      r.rsh = (d & 3) * 8;
+#pragma unroll 1
+      for (int u = tid; u < units; u += T) {
+        const uint32_t* q = reinterpret_cast<const uint32_t*>(raw + ((d + 12 * u) & ~3));
+        r.w0 = q[0]; r.w1 = q[1]; r.w2 = q[2]; r.w3 = q[3];
+        park(r, slot + (u - tid));
+      }
+      parkp += row_step;
+      ++parked;
+    };
+    issue(); issue(); issue(); issue();
+    asm volatile("cp.async.wait_group 3;" ::: "memory");
+    __syncthreads();
+    park_raw(slot0);  // row y0
+    asm volatile("cp.async.wait_group 2;" ::: "memory");
+    for (int y = y0; y < y1; y += 2) {
+      __syncthreads();  // row y in planes 0, raw row y + 1 landed; ring slot of raw row y is free
+      issue();          // raw row y + 4
+      if (y + 1 < y1) park_raw(slot1);
+      reduce_row(taps0);
+      if (y + 1 >= y1) break;
+      asm volatile("cp.async.wait_group 2;" ::: "memory");
+      __syncthreads();
+      issue();
+      if (y + 2 < y1) park_raw(slot0);
+      reduce_row(taps1);
+      asm volatile("cp.async.wait_group 2;" ::: "memory");
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    return;
+  }
+  // ---- first / last block of the whole batch: register staging with guarded loads ----------------------------------
+  stage_fetch();
+  stage_park(slot0);
+  for (int y = y0; y < y1; y += 2) {
+    __syncthreads();  // row y staged; the other buffer is free again
+    if (y + 1 < y1) stage_fetch();
+    reduce_row(taps0);
+    if (y + 1 >= y1) break;
+    stage_park(slot1);
+    __syncthreads();
+    if (y + 2 < y1) stage_fetch();
+    reduce_row(taps1);
+    if (y + 2 < y1) stage_park(slot0);
   }
 }
 
@@ -363,18 +474,29 @@ int launch_preprocess(isb_handle* h, const uint8_t* images, int batch, int in_h,
   // columns can touch, plus the words a column reads past its last tap
   const double scale = (double)in_w / (double)out_w;
   const int groups = tx.groups, ng = groups <= kPrepMaxGroups ? groups : 0;
-  const int plane_cap = (((int)ceil(kPrepThreads * scale) + tx.ksize + 2 + 4 * (ng > 0 ? ng : groups) + 8 + 3) & ~3);
-  const size_t smem = 2 * 3 * (size_t)plane_cap;
+  // columns per block = threads per block: 128 or 192, whichever leaves fewer idle threads in the last block of a row
+  // (550 columns: 5 x 128 = 640 slots against 3 x 192 = 576)
+  const int waste128 = (out_w + 127) / 128 * 128 - out_w, waste192 = (out_w + 191) / 192 * 192 - out_w;
+  const int ht = (waste192 < waste128 && !getenv("ISB_PREP_T128")) ? 192 : 128;
+  const int plane_cap = (((int)ceil(ht * scale) + tx.ksize + 2 + 4 * (ng > 0 ? ng : groups) + 8 + 3) & ~3);
+  // two plane buffers + the 4-slot ring of raw rows (same formula as in the kernel)
+  const size_t smem = (((size_t)6 * plane_cap + 15) & ~(size_t)15) + 4 * (size_t)((plane_cap * 3 + 48 + 15) & ~15);
   if (smem > 96 * 1024) ISB_FAIL(h, ISB_ERR_LIMIT, "preprocess: horizontal reduction %d -> %d is too strong for the staged row span", in_w, out_w);
-  const int colblocks = (out_w + kPrepThreads - 1) / kPrepThreads;
-  const dim3 hgrid(colblocks, (in_h + kPrepRows - 1) / kPrepRows, batch);
+  const dim3 hgrid((out_w + ht - 1) / ht, (in_h + kPrepRows - 1) / kPrepRows, batch);
   const size_t src_bytes = (size_t)batch * in_h * in_w * 3;
-#define ISB_PREP_H(NGV)                                                                                                      \
-  do {                                                                                                                       \
-    if (smem > 48 * 1024)                                                                                                    \
-      ISB_CUDA(h, cudaFuncSetAttribute(prep_horizontal_kernel<NGV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); \
-    prep_horizontal_kernel<NGV><<<hgrid, kPrepThreads, smem, s>>>(images, src_bytes, in_h, in_w, out_w, groups, plane_cap,    \
-                                                                  tx.d_bounds, tx.d_pack, st->temp, tpitch);                 \
+#define ISB_PREP_HT(NGV, TV)                                                                                                       \
+  do {                                                                                                                             \
+    if (smem > 48 * 1024)                                                                                                          \
+      ISB_CUDA(h, cudaFuncSetAttribute(prep_horizontal_kernel<NGV, TV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); \
+    prep_horizontal_kernel<NGV, TV><<<hgrid, TV, smem, s>>>(images, src_bytes, in_h, in_w, out_w, groups, plane_cap, tx.d_bounds,  \
+                                                            tx.d_pack, st->temp, tpitch);                                          \
+  } while (0)
+#define ISB_PREP_H(NGV)          \
+  do {                           \
+    if (ht == 192)               \
+      ISB_PREP_HT(NGV, 192);     \
+    else                         \
+      ISB_PREP_HT(NGV, 128);     \
   } while (0)
   switch (ng) {
     case 1: ISB_PREP_H(1); break;
@@ -386,7 +508,9 @@ int launch_preprocess(isb_handle* h, const uint8_t* images, int batch, int in_h,
     default: ISB_PREP_H(0); break;
   }
 #undef ISB_PREP_H
+#undef ISB_PREP_HT
   ISB_LAUNCH_CHECK(h, "prep_horizontal_kernel");
+  const int colblocks = (out_w + kPrepThreads - 1) / kPrepThreads;
   prep_vertical_kernel<<<dim3(colblocks, (out_h + kPrepRows - 1) / kPrepRows, batch), kPrepThreads, 0, s>>>(
       st->temp, tpitch, in_h, out_h, out_w, ty.d_bounds, ty.d_coef, st->d_lut, resized, input);
   ISB_LAUNCH_CHECK(h, "prep_vertical_kernel");
