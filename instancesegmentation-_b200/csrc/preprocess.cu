@@ -287,39 +287,54 @@ prep_horizontal_kernel(const uint8_t* __restrict__ src, size_t src_bytes, int in
   const bool inside16 = inside && first16 >= src &&
                         reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(last) & ~(uintptr_t)15) + raw_cap <= src_end;
   if (inside16) {
-    const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
-    const uint8_t* rowp = row0;  // row whose copy is issued next
-    int issued = 0;              // rows issued so far
-    const int nrows = y1 - y0;
-    auto issue = [&]() {         // one commit group per call, empty past the last row
-      if (issued < nrows) {
-        const uintptr_t a16 = reinterpret_cast<uintptr_t>(rowp) & ~(uintptr_t)15;
-        const int d = (int)(reinterpret_cast<uintptr_t>(rowp) - a16);
-        const int chunks = (d + units * 12 + 4 + 15) >> 4;
-        const uint32_t dst = ring_s + (uint32_t)(issued & 3) * (uint32_t)raw_cap;
+    // running per-thread state instead of per-row address arithmetic: the byte address of this thread's 16-byte chunk
+    // before alignment (its low four bits are the row's misalignment d), the ring offsets of the slot written / read next
+    const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring) + 16u * tid;
+    const uint32_t ring_bytes = 4u * (uint32_t)raw_cap;
+    uintptr_t g = reinterpret_cast<uintptr_t>(row0) + 16u * tid;
+    uint32_t ioff = 0, poff = 0;
+    int to_issue = y1 - y0;  // rows not yet issued
+    const int ubytes = units * 12 + 4 + 15;
+    const bool more_chunks = ((15 + ubytes) >> 4) > T;  // block-uniform, false up to ~5 : 1
+    auto issue = [&]() {  // one commit group per call, empty past the last row
+      if (to_issue > 0) {
+        const int chunks = (int)(((uint32_t)g & 15u) + ubytes) >> 4;
+        if (tid < chunks) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring_s + ioff), "l"(g & ~(uintptr_t)15) : "memory");
+        if (more_chunks) {
 #pragma unroll 1
-        for (int c = tid; c < chunks; c += T)
-          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * c), "l"(a16 + 16u * (unsigned)c) : "memory");
-        rowp += row_step;
+          for (int c = tid + T; c < chunks; c += T)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring_s + ioff + 16u * (c - tid)),
+                         "l"((g & ~(uintptr_t)15) + 16u * (unsigned)(c - tid)) : "memory");
+        }
+        g += row_step;
+        ioff += (uint32_t)raw_cap;
+        if (ioff == ring_bytes) ioff = 0;
       }
-      ++issued;
+      --to_issue;
       asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    const uint8_t* parkp = row0;  // row parked next
-    int parked = 0;
+    uint32_t pd = (uint32_t)(reinterpret_cast<uintptr_t>(row0) & 15);  // misalignment of the row parked next
+    const uint32_t u12 = 12u * tid;
     auto park_raw = [&](uint32_t* slot) {
-      const int d = (int)(reinterpret_cast<uintptr_t>(parkp) & 15);
-      const uint8_t* raw = ring + (parked & 3) * raw_cap;
       Unit r;
-      r.rsh = (d & 3) * 8;
-#pragma unroll 1
-      for (int u = tid; u < units; u += T) {
-        const uint32_t* q = reinterpret_cast<const uint32_t*>(raw + ((d + 12 * u) & ~3));
+      r.rsh = (int)(pd & 3u) * 8;
+      const uint8_t* raw = ring + poff;
+      if (has_unit) {
+        const uint32_t* q = reinterpret_cast<const uint32_t*>(raw + ((pd + u12) & ~3u));
         r.w0 = q[0]; r.w1 = q[1]; r.w2 = q[2]; r.w3 = q[3];
-        park(r, slot + (u - tid));
+        park(r, slot);
       }
-      parkp += row_step;
-      ++parked;
+      if (more_units) {
+#pragma unroll 1
+        for (int u = tid + T; u < units; u += T) {
+          const uint32_t* q = reinterpret_cast<const uint32_t*>(raw + ((pd + 12u * u) & ~3u));
+          r.w0 = q[0]; r.w1 = q[1]; r.w2 = q[2]; r.w3 = q[3];
+          park(r, slot + (u - tid));
+        }
+      }
+      pd = (pd + row_step) & 15u;
+      poff += (uint32_t)raw_cap;
+      if (poff == ring_bytes) poff = 0;
     };
     issue(); issue(); issue(); issue();
     asm volatile("cp.async.wait_group 3;" ::: "memory");
@@ -358,61 +373,91 @@ prep_horizontal_kernel(const uint8_t* __restrict__ src, size_t src_bytes, int in
   }
 }
 
-// Vertical pass (ImagingResampleVertical_8bpc) + normalisation + HWC -> CHW: grid (blocks of 128 output pixels,
-// groups of kPrepRows output rows, pictures).  The pass is independent per byte of a row, so a thread reduces FOUR
-// adjacent bytes: one aligned 32-bit load per tap row (block-uniform taps and coefficients), four multiply-adds.  The
-// clipped bytes go to shared memory; then a thread per pixel picks its three channels, looks the float values up and
-// writes one coalesced run per channel plane (plus the optional 8-bit picture).
-constexpr int kPrepVWords = kPrepThreads * 3 / 4;  // 96 words = 384 bytes = 128 pixels per block
+// Vertical pass (ImagingResampleVertical_8bpc) + normalisation + HWC -> CHW: grid (column blocks, groups of kPrepVRows
+// output rows, pictures), 256 threads.  The pass is independent per byte of a row, so a thread reduces EIGHT adjacent
+// bytes: one aligned 64-bit load per tap row (block-uniform taps and coefficient), eight byte extractions (PRMT) and
+// eight multiply-adds -- per byte 2.6 instructions per tap instead of 4 with four bytes per thread (ncu, round 2: the
+// pass ran at 76 % of the issue slots with 215 warp instructions per 128 bytes of a row).  A block covers `ppb` byte
+// octets (a multiple of 3, so that its byte range starts and ends on a pixel boundary; 207 for a 550-pixel row: one
+// block, 6.5 of its 7 reducing warps busy).  The clipped bytes go to shared memory; then a thread per pixel picks its
+// three channels, looks the float values up and writes one coalesced run per channel plane (plus the optional 8-bit
+// picture).
+constexpr int kPrepVThreads = 256;
+constexpr int kPrepVRows = 8;
+constexpr int kPrepVMaxOctets = 222;  // <= 7 warps reduce; 222 * 8 / 3 = 592 pixels
+constexpr int kPrepVMaxTaps = 32;
 
-__global__ void __launch_bounds__(kPrepThreads)
-prep_vertical_kernel(const uint8_t* __restrict__ src, int tpitch, int in_h, int out_h, int out_w,
+__global__ void __launch_bounds__(kPrepVThreads)
+prep_vertical_kernel(const uint8_t* __restrict__ src, int tpitch, int in_h, int out_h, int out_w, int ppb, int ksize,
                      const int32_t* __restrict__ bounds, const int32_t* __restrict__ coef, const float* __restrict__ lut,
                      uint8_t* __restrict__ resized, float* __restrict__ input) {
-  __shared__ uint32_t s_out[2][kPrepVWords];
+  __shared__ uint2 s_out[2][kPrepVMaxOctets];
+  __shared__ int32_t s_coef[kPrepVRows][kPrepVMaxTaps];  // the block's coefficients: one LDS with an immediate offset per tap
   const int tid = threadIdx.x, b = blockIdx.z;
-  const int px0 = blockIdx.x * kPrepThreads;  // first pixel of the block
-  const int word = blockIdx.x * kPrepVWords + tid;
-  const bool reducer = tid < kPrepVWords && word * 4 < tpitch;
-  const int yy0 = blockIdx.y * kPrepRows, yy1 = min(yy0 + kPrepRows, out_h);
+  const int npx = (ppb * 8) / 3;        // pixels per block
+  const int px0 = blockIdx.x * npx;     // first pixel of the block
+  const int octet = blockIdx.x * ppb + tid;
+  const bool reducer = tid < ppb && octet * 8 < tpitch;  // tpitch is a multiple of 16
+  const int yy0 = blockIdx.y * kPrepVRows, yy1 = min(yy0 + kPrepVRows, out_h);
   const size_t plane = (size_t)out_h * out_w;
-  const int xx = px0 + tid, xs = min(xx, out_w - 1);
-  const uint32_t* img = reinterpret_cast<const uint32_t*>(src + (size_t)b * in_h * (size_t)tpitch) + word;
-  uint8_t* rrow = resized ? resized + (((size_t)b * out_h + yy0) * out_w + xs) * 3 : nullptr;
-  float* irow = input ? input + (size_t)b * 3 * plane + (size_t)yy0 * out_w + xs : nullptr;
+  const uint2* img = reinterpret_cast<const uint2*>(src + (size_t)b * in_h * (size_t)tpitch) + octet;
+  const unsigned pitch8 = (unsigned)(tpitch >> 3);
+  const bool staged = ksize <= kPrepVMaxTaps;  // block-uniform; longer tap runs (reductions beyond 7.5 : 1) read the table
+  if (staged) {
+    for (int i = tid; i < (yy1 - yy0) * ksize; i += kPrepVThreads) {
+      const int r = i / ksize, y = i - r * ksize;
+      s_coef[r][y] = __ldg(coef + (size_t)y * out_h + yy0 + r);
+    }
+    __syncthreads();
+  }
   for (int yy = yy0; yy < yy1; ++yy) {
-    uint32_t* so = s_out[(yy - yy0) & 1];
+    uint2* so = s_out[(yy - yy0) & 1];
     if (reducer) {
       const int ymin = __ldg(bounds + 2 * yy), ymax = __ldg(bounds + 2 * yy + 1);
-      int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0, a3 = a0;
-      const uint32_t* p = img + (size_t)(unsigned)ymin * (unsigned)(tpitch >> 2);
-#pragma unroll 3
-      for (int y = 0; y < ymax; ++y) {
-        const int k = __ldg(coef + (size_t)y * out_h + yy);
-        const uint32_t w = __ldg(p);
-        a0 += (int)(w & 0xffu) * k;
-        a1 += (int)((w >> 8) & 0xffu) * k;
-        a2 += (int)((w >> 16) & 0xffu) * k;
-        a3 += (int)(w >> 24) * k;
-        p += tpitch >> 2;
+      int a[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a[j] = 1 << (kPrecisionBits - 1);
+      const uint2* p = img + (size_t)(unsigned)ymin * pitch8;
+      auto tap = [&](int k) {
+        const uint2 w = __ldg(p);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          a[j] += (int)__byte_perm(w.x, 0u, 0x4440u + j) * k;
+          a[4 + j] += (int)__byte_perm(w.y, 0u, 0x4440u + j) * k;
+        }
+        p += pitch8;
+      };
+      if (staged) {
+        const int32_t* ks = s_coef[yy - yy0];
+#pragma unroll 4
+        for (int y = 0; y < ymax; ++y) tap(ks[y]);
+      } else {
+        const int32_t* kp = coef + yy;
+#pragma unroll 2
+        for (int y = 0; y < ymax; ++y, kp += out_h) tap(__ldg(kp));
       }
-      so[tid] = (uint32_t)clip8(a0) | ((uint32_t)clip8(a1) << 8) | ((uint32_t)clip8(a2) << 16) | ((uint32_t)clip8(a3) << 24);
+      uint2 o;
+      o.x = (uint32_t)clip8(a[0]) | ((uint32_t)clip8(a[1]) << 8) | ((uint32_t)clip8(a[2]) << 16) | ((uint32_t)clip8(a[3]) << 24);
+      o.y = (uint32_t)clip8(a[4]) | ((uint32_t)clip8(a[5]) << 8) | ((uint32_t)clip8(a[6]) << 16) | ((uint32_t)clip8(a[7]) << 24);
+      so[tid] = o;
     }
     __syncthreads();  // one barrier per row: the buffer written two rows ago was read before the previous barrier
-    if (xx < out_w) {
-      const uint8_t* sb = reinterpret_cast<const uint8_t*>(so) + tid * 3;
+    for (int px = tid; px < npx; px += kPrepVThreads) {
+      const int xx = px0 + px;
+      if (xx >= out_w) break;
+      const uint8_t* sb = reinterpret_cast<const uint8_t*>(so) + px * 3;
       const uint8_t v0 = sb[0], v1 = sb[1], v2 = sb[2];
       if (resized) {
-        rrow[0] = v0;
-        rrow[1] = v1;
-        rrow[2] = v2;
-        rrow += (size_t)out_w * 3;
+        uint8_t* r = resized + (((size_t)b * out_h + yy) * out_w + xx) * 3;
+        r[0] = v0;
+        r[1] = v1;
+        r[2] = v2;
       }
       if (input) {
-        irow[0] = __ldg(lut + v0);
-        irow[plane] = __ldg(lut + 256 + v1);
-        irow[2 * plane] = __ldg(lut + 512 + v2);
-        irow += out_w;
+        float* o = input + (size_t)b * 3 * plane + (size_t)yy * out_w + xx;
+        o[0] = __ldg(lut + v0);
+        o[plane] = __ldg(lut + 256 + v1);
+        o[2 * plane] = __ldg(lut + 512 + v2);
       }
     }
   }
@@ -510,9 +555,11 @@ int launch_preprocess(isb_handle* h, const uint8_t* images, int batch, int in_h,
 #undef ISB_PREP_H
 #undef ISB_PREP_HT
   ISB_LAUNCH_CHECK(h, "prep_horizontal_kernel");
-  const int colblocks = (out_w + kPrepThreads - 1) / kPrepThreads;
-  prep_vertical_kernel<<<dim3(colblocks, (out_h + kPrepRows - 1) / kPrepRows, batch), kPrepThreads, 0, s>>>(
-      st->temp, tpitch, in_h, out_h, out_w, ty.d_bounds, ty.d_coef, st->d_lut, resized, input);
+  // byte octets per block: a multiple of 3 (pixel boundaries), as even a split of the row as 222 per block allows
+  const int octets = tpitch >> 3, vblocks = (octets + kPrepVMaxOctets - 1) / kPrepVMaxOctets;
+  const int ppb = ((octets + vblocks - 1) / vblocks + 2) / 3 * 3;
+  prep_vertical_kernel<<<dim3((octets + ppb - 1) / ppb, (out_h + kPrepVRows - 1) / kPrepVRows, batch), kPrepVThreads, 0, s>>>(
+      st->temp, tpitch, in_h, out_h, out_w, ppb, ty.ksize, ty.d_bounds, ty.d_coef, st->d_lut, resized, input);
   ISB_LAUNCH_CHECK(h, "prep_vertical_kernel");
   return ISB_OK;
 }
@@ -524,7 +571,7 @@ extern "C" int isb_preprocess(isb_handle* h, const uint8_t* images, int32_t batc
                               isb_stream stream) {
   if (!h) return ISB_ERR_BAD_ARG;
   if (batch < 0 || in_h <= 0 || in_w <= 0 || out_h <= 0 || out_w <= 0) ISB_FAIL(h, ISB_ERR_BAD_ARG, "preprocess: bad size");
-  if (batch > 65535 || in_h > 65535 * 16 || out_h > 65535 * 16) ISB_FAIL(h, ISB_ERR_LIMIT, "preprocess: batch / height too large");
+  if (batch > 65535 || in_h > 65535 * 16 || out_h > 65535 * 8) ISB_FAIL(h, ISB_ERR_LIMIT, "preprocess: batch / height too large");
   if (batch == 0) return ISB_OK;
   if (!images || (!resized && !input)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "preprocess: null pointer");
   if (input && (!mean || !std)) ISB_FAIL(h, ISB_ERR_BAD_ARG, "preprocess: mean / std required for the float output");
