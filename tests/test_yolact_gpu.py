@@ -433,6 +433,35 @@ def test_detect_from_logits_matches_softmax_path(bu, a, c, bsz):
         assert float((rmask != gmask).float().mean()) <= 1e-3
 
 
+@pytest.mark.parametrize("a,c,scale", [(333, 81, 2.0), (333, 21, 3.0), (210, 100, 1.0), (210, 100, 3.0), (97, 84, 2.5)])
+def test_detect_from_logits_undecided_heads_and_wide_rows(bu, a, c, scale):
+    """Heads without a dominant background: most rows pass the max-only pre-test, so the register-resident lane-group
+    pass of the score filter runs instead of the warp-wide one; 100 classes take the shared-memory path for rows wider
+    than the register quarter rows.  Same candidates and detections as softmax-then-filter."""
+    g = torch.Generator().manual_seed(1234 + a + c)
+    bsz = 3
+    logits = (torch.randn(bsz, a, c, generator=g) * scale).cuda()
+    box = (torch.randn(bsz, a, 4, generator=g) * 0.3).cuda()
+    coef = torch.tanh(torch.randn(bsz, a, 32, generator=g)).cuda()
+    proto = torch.relu(torch.randn(bsz, 40, 40, 32, generator=g)).cuda()
+    anchors = torch.rand(a, 4, generator=g).mul(0.5).add(0.1).cuda()
+    conf = torch.softmax(logits, dim=-1)
+    for thr in (0.05, 0.3):
+        ref = bu.decode_nms_batch((box, conf, coef, proto), anchors, thr, 0.5, (96, 80))
+        got = bu.decode_nms_batch((box, logits, coef, proto), anchors, thr, 0.5, (96, 80), logits=True)
+        assert np.array_equal(host(ref.counts), host(got.counts))
+        for b in range(bsz):
+            m = int(host(ref.counts)[b])
+            if m == 0:  # 100 undecided classes at unit scale: no probability reaches the threshold, in either path
+                continue
+            rb, rs, rc, rarg, rmask = ref.image(b, m)
+            gb, gs, gc, garg, gmask = got.image(b, m)
+            assert torch.equal(rc, gc)
+            np.testing.assert_allclose(host(gs), host(rs), rtol=2e-6, atol=0)
+            assert torch.equal(rb, gb)
+    assert int(host(got.counts).sum()) > 0 or scale == 1.0
+
+
 # ------------------------------------------------------------------------------- COCO RLE (SURVEY 8f rank 3)
 def test_rle_encode_vs_oracle(bu):
     """utils_map.py:33-34 on the device: counts and strings equal the restated cocoapi algorithm, and decode back to the
