@@ -156,7 +156,7 @@ constexpr int kLgRows = 16;      // rows per tile = one bulk copy; a tile is sha
 constexpr int kLgThreads = 256;  // 8 warps
 constexpr int kLgWarps = kLgThreads / 32;
 constexpr int kLgPairs = kLgWarps / 2;
-constexpr int kLgBufs = 3;       // tile buffers per pair
+constexpr int kLgBufs = 2;       // tile buffers per pair
 constexpr int kLgStage = 96;     // parked keys per warp
 constexpr int kLgRegCols = 21;   // columns per lane kept in registers (four lanes per row: rows of up to 84 classes, COCO's 81)
 constexpr int kLgWideRows = 2;   // up to this many candidate rows of a half tile are summed warp-wide, one after the other
@@ -286,6 +286,24 @@ __device__ __forceinline__ void lg_tile(const float* tile, const CandParams& p, 
     sum = s0 + s1;
     sum += __shfl_xor_sync(0xffffffffu, sum, 1);
     sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+    // Candidate test on the register-resident columns, every row's four lanes for themselves: x - max > lim is necessary
+    // (with margin) for expf(x - max) / sum > threshold.  Inside an object's run of anchors all eight rows of the warp
+    // are candidate rows; scanning them one after the other with the whole warp cost ~100 instructions per row.
+    const float lim = p.threshold > 0.0f ? logf(p.threshold * sum) - 1e-4f : ninf;
+    unsigned hits = 0;
+#pragma unroll
+    for (int k = 0; k < kLgRegCols; ++k)
+      if (v[k] - mx > lim) hits |= 1u << k;  // padding columns are -inf
+    if (!valid) hits = 0;
+    if (q < p.col0) hits &= ~1u;  // col0 <= 1 here: column 0 is element 0 of lane q = 0
+    while (hits) {
+      const int k = __ffs(hits) - 1;
+      hits &= hits - 1;
+      const int c = q + 4 * k;
+      const float pr = expf(row[c] - mx) / sum;
+      if (pr > p.threshold) lg_emit_key(e, img, make_cand_key((uint32_t)(c - p.col0), pr, r0 + (uint32_t)lrow));
+    }
+    return;
   } else {  // wider rows: two passes over shared memory
     const int cf = p.col0 + ((q - p.col0) & 3);  // first foreground column of this lane's residue
     float m0 = ninf, m1 = ninf;
@@ -340,7 +358,7 @@ __device__ __forceinline__ void lg_tile(const float* tile, const CandParams& p, 
 }
 
 template <int CT>
-__global__ void __launch_bounds__(kLgThreads, 3)
+__global__ void __launch_bounds__(kLgThreads, 4)
 candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_t* __restrict__ cand_keys, int64_t cap,
                          int64_t key_stride, int tiles_per_img, int64_t total_floats) {
   asm volatile("griddepcontrol.launch_dependents;");  // fast_nms_kernel may be queued behind this grid (fused path)
@@ -386,17 +404,18 @@ candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_
   int b = first / tiles_per_img, t = first - b * tiles_per_img;  // (image, tile in image), advanced without divisions
   int cur_img = -1;
   const float lthr = p.threshold > 0.0f ? logf(p.threshold) - 1e-4f : -__int_as_float(0x7f800000);
-  // three buffers per pair: tiles it + 1 and it + 2 are in flight while tile it is reduced
+  // kLgBufs buffers per pair: tiles it + 1 .. it + kLgBufs - 1 are in flight while tile it is reduced
   int pb = b, pt = t;  // tile the producer issues next
   auto advance = [&](int& ib, int& itl) { if (++itl == tiles_per_img) { itl = 0; ++ib; } };
   if (producer) {
-    if (first < last) { issue(pb, pt, 0); advance(pb, pt); }
-    if (first + 1 < last) { issue(pb, pt, 1); advance(pb, pt); }
+#pragma unroll
+    for (int j = 0; j < kLgBufs - 1; ++j)
+      if (first + j < last) { issue(pb, pt, j); advance(pb, pt); }
   }
-  int it = 0, stage = 0, use = 0;  // stage = it % 3, use = it / 3
+  int it = 0, stage = 0, use = 0;  // stage = it % kLgBufs, use = it / kLgBufs
   for (int tile = first; tile < last; ++tile, ++it) {
-    if (producer && tile + 2 < last) {
-      // buffer (it + 2) % 3 held tile it - 1: this warp left it at its last __syncwarp, the partner says so on `empty`
+    if (producer && tile + kLgBufs - 1 < last) {
+      // the buffer of tile it + kLgBufs - 1 held tile it - 1: this warp left it at its last __syncwarp, the partner says so on `empty`
       const int ps = stage == 0 ? kLgBufs - 1 : stage - 1;
       if (it >= 1) mbar_wait(&empty[pair][ps], (stage == 0 ? use - 1 : use) & 1);
       issue(pb, pt, ps);
@@ -445,7 +464,7 @@ int launch_candidates(isb_handle* h, const CandParams& p, cudaStream_t s) {
     if (!p.use_threshold) ISB_FAIL(h, ISB_ERR_BAD_ARG, "detect from logits needs a threshold");
     const int tiles_per_img = (p.rows + kLgRows - 1) / kLgRows;
     int64_t grid = (int64_t)p.batch * tiles_per_img;
-    const int64_t per_sm = smem <= 72 * 1024 ? 3 : 2;  // resident CTAs: 227 KB of shared memory, 80 registers per thread
+    const int64_t per_sm = smem <= 50 * 1024 ? 4 : (smem <= 72 * 1024 ? 3 : 2);  // resident CTAs: 227 KB of shared memory
     if (grid > per_sm * h->num_sms) grid = per_sm * h->num_sms;
     auto kern = p.ncols == 81 ? candidates_logits_kernel<81> : (p.ncols == 21 ? candidates_logits_kernel<21> : candidates_logits_kernel<0>);
     kern<<<(unsigned)grid, kLgThreads, smem, s>>>(
