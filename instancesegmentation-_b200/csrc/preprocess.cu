@@ -120,20 +120,22 @@ __device__ __forceinline__ uint8_t clip8(int acc) {
   return (uint8_t)min(max(v, 0), 255);
 }
 
-// Horizontal pass (ImagingResampleHorizontal_8bpc): grid (blocks of 128 output columns, groups of kPrepRows rows,
-// pictures), thread = output column.  Row after row, the input pixels the block's columns can touch -- the taps of its
-// first to its last column -- are staged in one of two shared-memory buffers (the next row is in flight while this one
-// is reduced: one barrier per row), DE-INTERLEAVED into one byte plane per channel.  A staging thread owns 4 pixels =
-// 12 bytes: aligned 32-bit loads, funnel shifts for the row's byte misalignment, six byte permutes, one 32-bit store
-// per plane.  In a plane the taps of a column are consecutive bytes, so a thread reads them as aligned words, realigns
-// them with funnel shifts and multiplies four taps at a time with dp4a: the coefficient k is split on the host into
-// k0 + 256 k1 + 65536 k2 (unsigned, unsigned, signed bytes), one packed word per slice and group of four taps, held in
-// registers for all rows of the block; sum(pixel * k) = s0 + 256 s1 + 65536 s2 exactly.  No per-byte extraction, and
-// neighbouring columns start ~scale bytes apart in a plane, so a warp's loads fall into at most 32 consecutive words
-// (no bank conflicts; the interleaved layout cost 100 M conflict wavefronts of 185 M, ncu).  The result goes to an
-// intermediate 8-bit image whose row pitch is a multiple of 16 bytes, so that the vertical pass can read it with
-// aligned 32-bit loads whatever the output width.  NG = groups of four taps (template: coefficients in registers);
-// NG = 0: any tap count, coefficients re-read through L1.
+// Horizontal pass (ImagingResampleHorizontal_8bpc): grid (blocks of T = 128 or 192 output columns, groups of kPrepRows
+// rows, pictures), thread = output column.  Row after row, the input pixels the block's columns can touch -- the taps of
+// its first to its last column -- arrive in shared memory in two steps: the raw interleaved bytes of row y + 4 go global ->
+// shared with cp.async (LDGSTS, 16-byte chunks, one per thread) into a four-slot ring, and a row whose copy has landed
+// is DE-INTERLEAVED into one of two plane buffers, one byte plane per channel (a thread owns 4 pixels = 12 bytes: four
+// 32-bit shared loads, funnel shifts for the row's byte misalignment, six byte permutes, one 32-bit store per plane)
+// while the row before it is reduced: one barrier per row.  In a plane the taps of a column are consecutive bytes, so a
+// thread reads them as aligned words, realigns them with funnel shifts and multiplies four taps at a time with dp4a: the
+// coefficient k is split on the host into k0 + 256 k1 + 65536 k2 (unsigned, unsigned, signed bytes), one packed word per
+// slice and group of four taps, held in registers for all rows of the block; sum(pixel * k) = s0 + 256 s1 + 65536 s2
+// exactly.  No per-byte extraction, and neighbouring columns start ~scale bytes apart in a plane, so a warp's loads fall
+// into at most 32 consecutive words (no bank conflicts; the interleaved layout cost 100 M conflict wavefronts of 185 M,
+// ncu).  The result goes to an intermediate 8-bit image whose row pitch is a multiple of 16 bytes, so that the vertical
+// pass can read it with aligned 64-bit loads whatever the output width.  NG = groups of four taps (template:
+// coefficients in registers); NG = 0: any tap count, coefficients re-read through L1.  The first and the last block of
+// the whole batch, whose 16-byte chunks could leave the caller's buffer, stage through registers with guarded loads.
 constexpr int kPrepRows = 16;
 constexpr int kPrepMaxGroups = 6;  // register-resident coefficients up to 24 taps (reductions up to 5.5 : 1)
 
