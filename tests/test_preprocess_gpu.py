@@ -68,6 +68,24 @@ def test_batch_and_other_sizes_vs_oracle(pre):
             assert np.array_equal(out[i:i + 1].cpu().numpy(), P.normalize_chw(ref, mean, std))
 
 
+def test_wide_rows_and_long_columns_vs_oracle(pre):
+    """Shapes that leave the common paths of the two resize kernels: more than four input pixels per output column with
+    at least one full block of columns (a thread stages several pixel groups and several 16-byte chunks per row), widths
+    that make 192 columns per block the better split and widths that do not, rows wider than one 592-pixel block of the
+    vertical pass, more than 32 vertical taps (coefficients read from the table instead of shared memory), and a picture
+    whose first row is not 16-byte aligned in the batch."""
+    rng = np.random.RandomState(23)
+    for (h, w), (oh, ow), b in [((24, 1920), (11, 300), 2), ((19, 1601), (10, 260), 2), ((21, 1333), (9, 193), 3),
+                               ((18, 2500), (8, 1300), 1), ((700, 40), (35, 37), 2), ((26, 1999), (13, 640), 2), ((20, 1300), (9, 190), 2)]:
+        imgs = rng.randint(0, 256, (b, h, w, 3), dtype=np.uint8)
+        out, res = pre.image_to_input(imgs, (oh, ow), return_resized=True)
+        assert out.shape == (b, 3, oh, ow) and res.shape == (b, oh, ow, 3)
+        for i in range(b):
+            ref = P.resize_u8(imgs[i], ow, oh)
+            assert np.array_equal(res[i].cpu().numpy(), ref), f"{(h, w)} -> {(oh, ow)} image {i}"
+            assert np.array_equal(out[i:i + 1].cpu().numpy(), P.image_to_input(imgs[i], (oh, ow)))
+
+
 def test_pil_inputs_and_grey_pictures(pre):
     """PIL pictures go in as they are; a picture that is not RGB is converted first like utils.py:9-14 cvtColor."""
     Image = pytest.importorskip("PIL.Image")
