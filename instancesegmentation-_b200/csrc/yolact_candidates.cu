@@ -386,6 +386,10 @@ candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_
   em.cap = cap;
   em.key_stride = key_stride;
   const bool producer = half == 0 && lane == 0;
+  // the logits are read once: evict-first in the L2, like K1's ld.global.cs (in the step this kernel starts while ~100 MB
+  // of the previous call's mask bytes are still dirty in the L2; with the default policy its 400 MB of reads push them
+  // out and wait for the write-back)
+  const uint64_t stream_policy = l2_evict_first_policy();
 
   auto issue = [&](int b, int t, int stage) {  // producer lane only; tile t of image b
     const int r0 = t * kLgRows, nr = min(kLgRows, p.rows - r0);
@@ -394,7 +398,7 @@ candidates_logits_kernel(CandParams p, int32_t* __restrict__ cand_count, uint64_
     const int64_t a1 = min((f1 + 3) & ~(int64_t)3, total_floats & ~(int64_t)3);   // never past the tensor
     const uint32_t bytes = (uint32_t)((a1 - a0) * 4);
     mbar_expect_tx(&full[pair][stage], bytes);
-    bulk_g2s(wbuf + (size_t)stage * tile_bytes, base + a0, bytes, &full[pair][stage]);
+    bulk_g2s_stream(wbuf + (size_t)stage * tile_bytes, base + a0, bytes, &full[pair][stage], stream_policy);
   };
 
   // every pair of warps owns a run of consecutive tiles
